@@ -1,0 +1,115 @@
+/* lslam.h - C ABI of the B200-native LiDAR_SLAM hot path (liblslam.so).
+ *
+ * The reference (Farofeiro231/LiDAR_SLAM) is pure Python and has no FFI of its own; its
+ * boundary for this path is the Python module API of ransac_functions.py, landmarking.py,
+ * UKFMethods.py and systemClass.py.  The drop-in modules in lidar_slam_b200/ keep that
+ * API and bind the entry points below with ctypes (INTEGRATION.md shows the stub).  Each
+ * entry point cites the reference interface it replaces (file:line in the reference).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every data pointer is a DEVICE pointer unless its
+ *     name ends in _h; the caller owns all buffers; nothing is allocated per call
+ *   - `stream` is a cudaStream_t cast to void* (NULL = the legacy default stream); calls
+ *     are asynchronous on that stream and never synchronise the device
+ *   - return value: LSLAM_OK or a negative lslam_status; lslam_last_error() gives text
+ *   - a handle is bound to one device, holds no per-call state and may be used from any
+ *     one thread at a time (the reference calls the path from one worker thread,
+ *     ransac_functions.py:104); create it AFTER fork (SLAM.py:20 forks the worker)
+ *   - all arithmetic is IEEE fp64 like the reference's Python floats; indices are int32
+ */
+#ifndef LSLAM_H
+#define LSLAM_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum lslam_status {
+    LSLAM_OK = 0,
+    LSLAM_ERR_BAD_ARG = -1,        /* null pointer, size out of range, misaligned buffer */
+    LSLAM_ERR_TOO_FEW_POINTS = -2, /* chunk slot with <= 2 points (functions.py:71 never queues one) */
+    LSLAM_ERR_NO_MODEL = -3,       /* no trial found an inlier: upstream ransac returns (None, None)
+                                      and the reference raises AttributeError at ransac_functions.py:25 */
+    LSLAM_ERR_CUDA = -4,           /* CUDA runtime error, text in lslam_last_error() */
+    LSLAM_ERR_NONFINITE = -5,      /* NaN/Inf (or |coordinate| >= 2^400) in a chunk */
+    LSLAM_ERR_CAPACITY = -6        /* problem does not fit (shared memory, table capacity) */
+} lslam_status;
+
+/* ---- handle ---------------------------------------------------------------------- */
+int lslam_create(int device, void **handle);
+int lslam_destroy(void *handle);
+const char *lslam_last_error(void *handle);
+/* ABI version of the loaded library (LSLAM_ABI_VERSION at build time). */
+#define LSLAM_ABI_VERSION 1
+int lslam_abi_version(void);
+/* Launch-shape tuning knobs ("ransac.tpt", "ransac.slots_per_cta", "ransac.threads");
+ * 0 restores the built-in heuristic.  Results never depend on them. */
+int lslam_set_option(void *handle, const char *key, int64_t value);
+/* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */
+int64_t lslam_launch_count(void *handle);
+
+/* ---- input stage: polar -> cartesian ------------------------------------------------
+ * Replaces the per-measure conversion of scanning(), functions.py:59-60:
+ *   x = d * cos(-angle_deg * pi/180 + pi/2),  y = d * sin(-angle_deg * pi/180 + pi/2)
+ * dist[npts] mm, ang_deg[npts] degrees -> xy[npts,2] (x,y interleaved). */
+int lslam_polar_to_cart(void *handle, const double *dist, const double *ang_deg, double *xy,
+                        int64_t npts, void *stream);
+
+/* ---- RANSAC line / landmark extraction ---------------------------------------------
+ * Replaces, per chunk, ransac_functions.py:20-31: skimage.measure.ransac(data,
+ * LineModelND, min_samples=2, residual_threshold=thr, max_trials=trials) followed by the
+ * slope/intercept/tip computation.  One revolution is cut into chunks the way scanning()
+ * cuts it (functions.py:64-76): C = ceil(N/chunk) chunk slots per scan; slot c of scan b
+ * holds points [c*chunk, min((c+1)*chunk, npts[b])) and is processed when it is a full
+ * chunk or a remainder of more than 2 points.
+ *
+ *   xy        [B,N,2]  points, sensor frame, mm (x,y interleaved; 16-byte aligned)
+ *   npts      [B] valid points per scan (<= N), or NULL for all N
+ *   trials    hypotheses per chunk (MAX_TRIALS, ransac_functions.py:10)
+ *   thr       inlier distance, strict '<'   (THRESHOLD, ransac_functions.py:9)
+ *   seed, scan_base   Philox4x32-10 key and global index of scan 0 of this batch: trial t
+ *             of chunk c of scan b samples the pair derived from counter
+ *             (t>>1, c, scan_base+b) - see oracle/philox.py; results do not depend on
+ *             how a job is split into batches or over GPUs
+ * outputs (per chunk slot, [B,C,...])
+ *   line      [B,C,8]  a, b, origin_x, origin_y, dir_x, dir_y, tip_x, tip_y
+ *                      (dir normalised to dir_x > 0; a = dir_y/dir_x unguarded like :26)
+ *   ninl      [B,C]    inlier count (>= 2), or 0 for an unused slot, or a negative
+ *                      lslam_status (LSLAM_ERR_NO_MODEL, LSLAM_ERR_NONFINITE)
+ *   win_trial [B,C]    index of the selected hypothesis (first best in trial order)
+ *   win_pair  [B,C,2]  its two sample indices within the chunk
+ *   ssum      [B,C]    its sum of squared residuals over all points of the chunk
+ *   inl_mask  [B,C,W]  W = ceil(chunk/32) words, bit k of word w = point 32*w+k is an inlier
+ */
+int lslam_ransac_lines(void *handle, const double *xy, const int32_t *npts, int32_t B, int32_t N,
+                       int32_t chunk, int32_t trials, double thr, uint64_t seed,
+                       uint64_t scan_base, double *line, int32_t *ninl, int32_t *win_trial,
+                       int32_t *win_pair, double *ssum, uint32_t *inl_mask, void *stream);
+
+/* Diagnostics of the last lslam_ransac_lines calls on this handle (synchronises `stream`):
+ *   counters_h[0] trials re-scored with the literal formula (threshold band / degenerate pair)
+ *   counters_h[1] literal candidate evaluations in the tie-break stage
+ *   counters_h[2] consistency faults (fast and literal inlier counts disagree; must be 0)
+ * The counters are reset by this call. */
+int lslam_ransac_counters(void *handle, int64_t counters_h[3], void *stream);
+
+/* ---- synthetic scans (headless replacement for the capture process) ----------------
+ * Device twin of lidar_slam_b200/synth.py random_room_scans(): scan s (global index
+ * scan_base+s) is a `beams`-beam revolution in a random rectangular room, range noise
+ * N(0, noise_mm), `dropout` probability of a zero range, converted like functions.py:59-60.
+ * xy [B,beams,2]. */
+int lslam_synth_scans(void *handle, double *xy, int32_t B, int32_t beams, uint64_t seed,
+                      uint64_t scan_base, double noise_mm, double dropout, void *stream);
+
+/* ---- fp64 issue-rate probe (roofline denominator for the compute-bound kernels) ------
+ * Runs a dependent-chain DFMA kernel sized to fill the device for about `ms_target`
+ * milliseconds and returns the achieved rate in TFLOP/s (2 flop per DFMA) in *tflops_h.
+ * Synchronises the device. */
+int lslam_fp64_peak(void *handle, double ms_target, double *tflops_h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LSLAM_H */

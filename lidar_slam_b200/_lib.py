@@ -1,0 +1,127 @@
+"""ctypes binding of the C ABI (include/lslam.h) - the only door to the CUDA kernels.
+
+The library is built in-tree by ``lidar_slam_b200/_build.py`` (nvcc, sm_100a) as
+``lidar_slam_b200/csrc/liblslam.so``.  There is NO fallback: if the library is missing or a
+call fails, this module raises.  All pointer arguments are raw device addresses (ints), as
+the ABI takes them; tensor plumbing lives in ``lidar_slam_b200/batch.py``.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+DEFAULT_PATH = os.path.join(_HERE, "csrc", "liblslam.so")
+
+LSLAM_OK = 0
+LSLAM_ERR_BAD_ARG = -1
+LSLAM_ERR_TOO_FEW_POINTS = -2
+LSLAM_ERR_NO_MODEL = -3
+LSLAM_ERR_CUDA = -4
+LSLAM_ERR_NONFINITE = -5
+LSLAM_ERR_CAPACITY = -6
+ABI_VERSION = 1
+
+_vp = ctypes.c_void_p
+_i32 = ctypes.c_int32
+_i64 = ctypes.c_int64
+_u64 = ctypes.c_uint64
+_f64 = ctypes.c_double
+
+# name -> (restype, argtypes); mirrors include/lslam.h one to one
+SIGNATURES = {
+    "lslam_create": (ctypes.c_int, [ctypes.c_int, ctypes.POINTER(_vp)]),
+    "lslam_destroy": (ctypes.c_int, [_vp]),
+    "lslam_last_error": (ctypes.c_char_p, [_vp]),
+    "lslam_abi_version": (ctypes.c_int, []),
+    "lslam_set_option": (ctypes.c_int, [_vp, ctypes.c_char_p, _i64]),
+    "lslam_launch_count": (_i64, [_vp]),
+    "lslam_polar_to_cart": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i64, _vp]),
+    "lslam_ransac_lines": (ctypes.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _f64, _u64, _u64,
+                                          _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "lslam_ransac_counters": (ctypes.c_int, [_vp, ctypes.POINTER(_i64), _vp]),
+    "lslam_synth_scans": (ctypes.c_int, [_vp, _vp, _i32, _i32, _u64, _u64, _f64, _f64, _vp]),
+    "lslam_fp64_peak": (ctypes.c_int, [_vp, _f64, ctypes.POINTER(_f64)]),
+}
+
+
+class LslamError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__("liblslam error %d: %s" % (code, text))
+        self.code = code
+
+
+def load(path=None):
+    """dlopen the C-ABI library and attach the signatures.  Raises if it is absent."""
+    path = path or os.environ.get("LSLAM_LIBRARY") or DEFAULT_PATH
+    if not os.path.exists(path):
+        raise ImportError(
+            "%s not found: build it with `python -m lidar_slam_b200._build` "
+            "(nvcc, sm_100a). There is no CPU fallback." % path)
+    cdll = ctypes.CDLL(path)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(cdll, name)          # AttributeError if the symbol is missing
+        fn.restype = res
+        fn.argtypes = args
+    if cdll.lslam_abi_version() != ABI_VERSION:
+        raise ImportError("%s has ABI version %d, binding expects %d"
+                          % (path, cdll.lslam_abi_version(), ABI_VERSION))
+    return cdll
+
+
+class Handle:
+    """One lslam handle (one device).  Methods take raw addresses and mirror the ABI."""
+
+    def __init__(self, device=0, path=None, cdll=None):
+        self.cdll = cdll if cdll is not None else load(path)
+        self.device = device
+        h = _vp()
+        rc = self.cdll.lslam_create(device, ctypes.byref(h))
+        if rc != LSLAM_OK or not h.value:
+            raise LslamError(rc, "lslam_create(device=%d) failed (no usable CUDA device?)" % device)
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self.cdll.lslam_destroy(self._h)
+            self._h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != LSLAM_OK:
+            raise LslamError(rc, self.cdll.lslam_last_error(self._h).decode("utf-8", "replace"))
+
+    # -- plumbing --
+    def set_option(self, key, value):
+        self._check(self.cdll.lslam_set_option(self._h, key.encode(), int(value)))
+
+    def launch_count(self):
+        return int(self.cdll.lslam_launch_count(self._h))
+
+    # -- entry points --
+    def polar_to_cart(self, dist, ang_deg, xy, npts, stream=0):
+        self._check(self.cdll.lslam_polar_to_cart(self._h, dist, ang_deg, xy, npts, stream))
+
+    def ransac_lines(self, xy, npts, B, N, chunk, trials, thr, seed, scan_base,
+                     line, ninl, win_trial, win_pair, ssum, inl_mask, stream=0):
+        self._check(self.cdll.lslam_ransac_lines(
+            self._h, xy, npts, B, N, chunk, trials, float(thr), int(seed) & (2**64 - 1),
+            int(scan_base) & (2**64 - 1), line, ninl, win_trial, win_pair, ssum, inl_mask, stream))
+
+    def ransac_counters(self, stream=0):
+        out = (_i64 * 3)()
+        self._check(self.cdll.lslam_ransac_counters(self._h, out, stream))
+        return {"literal_rescored": int(out[0]), "extra_candidates": int(out[1]), "faults": int(out[2])}
+
+    def synth_scans(self, xy, B, beams, seed, scan_base, noise_mm, dropout, stream=0):
+        self._check(self.cdll.lslam_synth_scans(self._h, xy, B, beams, int(seed) & (2**64 - 1),
+                                                int(scan_base) & (2**64 - 1), float(noise_mm),
+                                                float(dropout), stream))
+
+    def fp64_peak(self, ms_target=50.0):
+        out = _f64(0.0)
+        self._check(self.cdll.lslam_fp64_peak(self._h, float(ms_target), ctypes.byref(out)))
+        return float(out.value)

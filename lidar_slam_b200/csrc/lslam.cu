@@ -1,0 +1,240 @@
+// lslam.cu - the C ABI of include/lslam.h: handle, argument checks, launch shapes.
+// One translation unit; kernels live in the .cuh files next to it.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -shared
+//        -Xcompiler -fPIC  (lidar_slam_b200/_build.py)
+#include "lslam_common.cuh"
+#include "ransac.cuh"
+#include "aux_kernels.cuh"
+
+#include "../../include/lslam.h"
+
+using namespace lslam;
+
+// ---- handle ------------------------------------------------------------------------------
+extern "C" int lslam_abi_version(void) { return LSLAM_ABI_VERSION; }
+
+extern "C" int lslam_create(int device, void **handle)
+{
+    if (handle == nullptr) return LSLAM_ERR_BAD_ARG;
+    *handle = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return LSLAM_ERR_CUDA;
+    Handle *h = new Handle();
+    h->device = device;
+    DeviceGuard g(device);
+    cudaError_t e = cudaDeviceGetAttribute(&h->sms, cudaDevAttrMultiProcessorCount, device);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&h->counters_d, 8 * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemset(h->counters_d, 0, 8 * sizeof(unsigned long long));
+    if (e != cudaSuccess) { delete h; return LSLAM_ERR_CUDA; }
+    *handle = h;
+    return LSLAM_OK;
+}
+
+extern "C" int lslam_destroy(void *handle)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr) return LSLAM_ERR_BAD_ARG;
+    DeviceGuard g(h->device);
+    cudaFree(h->counters_d);
+    delete h;
+    return LSLAM_OK;
+}
+
+extern "C" const char *lslam_last_error(void *handle)
+{
+    Handle *h = (Handle *)handle;
+    return h ? h->err : "null handle";
+}
+
+extern "C" int64_t lslam_launch_count(void *handle)
+{
+    Handle *h = (Handle *)handle;
+    return h ? h->launches : -1;
+}
+
+extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr || key == nullptr) return LSLAM_ERR_BAD_ARG;
+    if (!strcmp(key, "ransac.tpt")) {
+        if (value != 0 && value != 1 && value != 2 && value != 4) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.tpt must be 0, 1, 2 or 4");
+        h->opt_tpt = (int)value;
+    } else if (!strcmp(key, "ransac.slots_per_cta")) {
+        if (value < 0 || value > 4096) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.slots_per_cta out of range");
+        h->opt_slots = (int)value;
+    } else if (!strcmp(key, "ransac.threads")) {
+        if (value < 0 || value > 1024 || value % 32) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.threads must be a multiple of 32 <= 1024");
+        h->opt_threads = (int)value;
+    } else {
+        return fail(h, LSLAM_ERR_BAD_ARG, "unknown option '%s'", key);
+    }
+    return LSLAM_OK;
+}
+
+// ---- RANSAC ------------------------------------------------------------------------------
+template <int TPT, int MAXT>
+static int launch_ransac(Handle *h, RansacArgs a, int threads_target, cudaStream_t st)
+{
+    auto kern = ransac_lines_kernel<TPT, MAXT>;
+    a.ipc = (a.trials + TPT - 1) / TPT;
+    if (threads_target > MAXT) threads_target = MAXT;
+    // chunk slots per CTA: enough work items to fill the CTA, bounded by shared memory
+    int G = h->opt_slots ? h->opt_slots : (threads_target + a.ipc / 2) / a.ipc;
+    if (G < 1) G = 1;
+    if ((long long)G > a.nslots) G = (int)a.nslots;
+    int threads = 0;
+    size_t smem = 0;
+    for (;; --G) {
+        long long want = (long long)G * a.ipc;
+        threads = (int)(want < threads_target ? want : threads_target);
+        threads = (threads + 31) & ~31;
+        if (threads > MAXT) threads = MAXT & ~31;
+        smem = ransac_smem_bytes(G, a.chunk, a.trials, a.W, threads / 32);
+        if (smem <= (size_t)h->smem_optin || G == 1) break;
+    }
+    if (smem > (size_t)h->smem_optin)
+        return fail(h, LSLAM_ERR_CAPACITY, "chunk=%d with trials=%d needs %zu B of shared memory (> %d)",
+                    a.chunk, a.trials, smem, h->smem_optin);
+    a.G = G;
+    const long long grid = (a.nslots + G - 1) / G;
+    if (grid > 0x7fffffffLL) return fail(h, LSLAM_ERR_CAPACITY, "batch too large for one launch");
+    LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    LSLAM_LAUNCH(kern, (unsigned)grid, (unsigned)threads, smem, st, a);
+    h->launches++;
+    LSLAM_CUDA_TRY(h, cudaGetLastError());
+    return LSLAM_OK;
+}
+
+extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t *npts, int32_t B, int32_t N,
+                                  int32_t chunk, int32_t trials, double thr, uint64_t seed,
+                                  uint64_t scan_base, double *line, int32_t *ninl, int32_t *win_trial,
+                                  int32_t *win_pair, double *ssum, uint32_t *inl_mask, void *stream)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr) return LSLAM_ERR_BAD_ARG;
+    if (!xy || !line || !ninl || !win_trial || !win_pair || !ssum || !inl_mask)
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ransac_lines: null buffer");
+    if (B < 0 || N < 1 || chunk < 2 || trials < 1 || trials > (1 << 20) || chunk > 8192)
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ransac_lines: need B >= 0, N >= 1, 2 <= chunk <= 8192, 1 <= trials <= 2^20");
+    if (!(thr == thr)) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ransac_lines: thr is NaN");
+    if (((uintptr_t)xy & 15) != 0) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ransac_lines: xy must be 16-byte aligned");
+    if (B == 0) return LSLAM_OK;
+    DeviceGuard g(h->device);
+    RansacArgs a;
+    a.xy = reinterpret_cast<const double2 *>(xy);
+    a.npts = npts;
+    a.B = B; a.N = N; a.chunk = chunk;
+    a.C = (N + chunk - 1) / chunk;
+    a.W = (chunk + 31) / 32;
+    a.trials = trials; a.thr = thr; a.seed = seed; a.scan_base = scan_base;
+    a.line = line; a.ninl = ninl; a.win_trial = win_trial; a.win_pair = win_pair; a.ssum = ssum;
+    a.mask = inl_mask;
+    a.counters = h->counters_d;
+    a.nslots = (long long)B * a.C;
+    a.G = 0; a.ipc = 0;
+    const int tpt = h->opt_tpt ? h->opt_tpt : (trials >= 512 ? 4 : 2);
+    const int threads = h->opt_threads ? h->opt_threads : 512;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (tpt) {
+    case 1: return launch_ransac<1, 768>(h, a, threads, st);
+    case 2: return launch_ransac<2, 768>(h, a, threads, st);
+    default: return launch_ransac<4, 512>(h, a, threads, st);
+    }
+}
+
+extern "C" int lslam_ransac_counters(void *handle, int64_t counters_h[3], void *stream)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr || counters_h == nullptr) return LSLAM_ERR_BAD_ARG;
+    DeviceGuard g(h->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned long long tmp[3];
+    LSLAM_CUDA_TRY(h, cudaMemcpyAsync(tmp, h->counters_d, sizeof tmp, cudaMemcpyDeviceToHost, st));
+    LSLAM_CUDA_TRY(h, cudaMemsetAsync(h->counters_d, 0, sizeof tmp, st));
+    LSLAM_CUDA_TRY(h, cudaStreamSynchronize(st));
+    for (int k = 0; k < 3; ++k) counters_h[k] = (int64_t)tmp[k];
+    return LSLAM_OK;
+}
+
+// ---- input stage, synthetic scans, fp64 probe --------------------------------------------
+extern "C" int lslam_polar_to_cart(void *handle, const double *dist, const double *ang_deg, double *xy,
+                                   int64_t npts, void *stream)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr) return LSLAM_ERR_BAD_ARG;
+    if (npts < 0 || (npts > 0 && (!dist || !ang_deg || !xy)))
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_polar_to_cart: bad arguments");
+    if (((uintptr_t)xy & 15) != 0) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_polar_to_cart: xy must be 16-byte aligned");
+    if (npts == 0) return LSLAM_OK;
+    DeviceGuard g(h->device);
+    const int threads = 256;
+    const long long grid = (npts + threads - 1) / threads;
+    if (grid > 0x7fffffffLL) return fail(h, LSLAM_ERR_CAPACITY, "too many points for one launch");
+    auto kern = polar_to_cart_kernel;
+    LSLAM_LAUNCH(kern, (unsigned)grid, threads, 0, (cudaStream_t)stream, dist, ang_deg,
+                 reinterpret_cast<double2 *>(xy), (long long)npts);
+    h->launches++;
+    LSLAM_CUDA_TRY(h, cudaGetLastError());
+    return LSLAM_OK;
+}
+
+extern "C" int lslam_synth_scans(void *handle, double *xy, int32_t B, int32_t beams, uint64_t seed,
+                                 uint64_t scan_base, double noise_mm, double dropout, void *stream)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr) return LSLAM_ERR_BAD_ARG;
+    if (B < 0 || beams < 1 || !xy || ((uintptr_t)xy & 15) != 0)
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_synth_scans: bad arguments");
+    if (B == 0) return LSLAM_OK;
+    DeviceGuard g(h->device);
+    const long long total = (long long)B * beams;
+    const int threads = 256;
+    const long long grid = (total + threads - 1) / threads;
+    if (grid > 0x7fffffffLL) return fail(h, LSLAM_ERR_CAPACITY, "too many points for one launch");
+    auto kern = synth_scans_kernel;
+    LSLAM_LAUNCH(kern, (unsigned)grid, threads, 0, (cudaStream_t)stream, reinterpret_cast<double2 *>(xy),
+                 total, (int)beams, seed, scan_base, noise_mm, dropout);
+    h->launches++;
+    LSLAM_CUDA_TRY(h, cudaGetLastError());
+    return LSLAM_OK;
+}
+
+extern "C" int lslam_fp64_peak(void *handle, double ms_target, double *tflops_h)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr || tflops_h == nullptr) return LSLAM_ERR_BAD_ARG;
+    DeviceGuard g(h->device);
+    const int threads = 256, blocks = h->sms * 8;
+    double *sink = nullptr;
+    LSLAM_CUDA_TRY(h, cudaMalloc((void **)&sink, sizeof(double) * (size_t)blocks * threads));
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    auto kern = dfma_probe_kernel;
+    int iters = 1 << 12;
+    float ms = 0.f;
+    int rc = LSLAM_OK;
+    for (int round = 0; round < 8; ++round) {
+        LSLAM_LAUNCH(kern, blocks, threads, 0, (cudaStream_t)0, sink, iters);   // warm-up at this size
+        cudaEventRecord(e0, 0);
+        LSLAM_LAUNCH(kern, blocks, threads, 0, (cudaStream_t)0, sink, iters);
+        cudaEventRecord(e1, 0);
+        h->launches += 2;
+        if (cudaEventSynchronize(e1) != cudaSuccess || cudaGetLastError() != cudaSuccess) {
+            rc = fail(h, LSLAM_ERR_CUDA, "fp64 probe failed");
+            break;
+        }
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (ms >= ms_target || iters >= (1 << 24)) break;
+        iters *= 2;
+    }
+    if (rc == LSLAM_OK) {
+        const double flops = 2.0 * kDfmaChains * kDfmaUnroll * (double)iters * (double)blocks * threads;
+        *tflops_h = ms > 0.f ? flops / (ms * 1e-3) * 1e-12 : 0.0;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(sink);
+    return rc;
+}

@@ -1,0 +1,66 @@
+"""Test helper: build and drive tests/emu/liblslam_emu.so, the kernel sources of
+lidar_slam_b200/csrc compiled for the CPU with tests/emu/cuda_emu.h (test infrastructure:
+lets the CPU-only suite execute the real kernel code; never used by the product)."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+from lidar_slam_b200 import _lib
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_HERE)
+EMU_SO = os.path.join(_HERE, "emu", "liblslam_emu.so")
+CSRC = os.path.join(_ROOT, "lidar_slam_b200", "csrc")
+
+
+def build_emu(force=False):
+    srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))]
+    srcs += [os.path.join(_HERE, "emu", "cuda_emu.h"), os.path.join(_ROOT, "include", "lslam.h")]
+    if force or not os.path.exists(EMU_SO) or any(
+            os.path.getmtime(s) > os.path.getmtime(EMU_SO) for s in srcs):
+        gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+        subprocess.check_call([
+            gxx, "-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared",
+            "-Wall", "-Wno-unknown-pragmas", "-include", os.path.join(_HERE, "emu", "cuda_emu.h"),
+            "-x", "c++", os.path.join(CSRC, "lslam.cu"), "-o", EMU_SO, "-lpthread"])
+    return EMU_SO
+
+
+_HANDLE = None
+
+
+def emu_handle():
+    global _HANDLE
+    if _HANDLE is None:
+        _HANDLE = _lib.Handle(0, path=build_emu())
+    return _HANDLE
+
+
+def ptr(a):
+    return None if a is None else a.ctypes.data
+
+
+def emu_ransac_lines(xy, npts=None, chunk=100, trials=100, thr=20.0, seed=0, scan_base=0, handle=None):
+    """lslam_ransac_lines on the emulated library with NumPy buffers standing in for device
+    memory.  Same outputs as oracle.cport.ransac_lines."""
+    h = handle or emu_handle()
+    xy = np.ascontiguousarray(xy, dtype=np.float64)
+    B, N, _ = xy.shape
+    C = (N + chunk - 1) // chunk
+    W = (chunk + 31) // 32
+    if npts is not None:
+        npts = np.ascontiguousarray(npts, dtype=np.int32)
+    out = {
+        "line": np.full((B, C, 8), -7.0, np.float64),
+        "ninl": np.full((B, C), -77, np.int32),
+        "win_trial": np.full((B, C), -77, np.int32),
+        "win_pair": np.full((B, C, 2), -77, np.int32),
+        "ssum": np.full((B, C), -7.0, np.float64),
+        "inl_mask": np.full((B, C, W), 0xdeadbeef, np.uint32),
+    }
+    h.ransac_lines(ptr(xy), ptr(npts), B, N, chunk, trials, thr, seed, scan_base,
+                   ptr(out["line"]), ptr(out["ninl"]), ptr(out["win_trial"]), ptr(out["win_pair"]),
+                   ptr(out["ssum"]), ptr(out["inl_mask"]))
+    return out
