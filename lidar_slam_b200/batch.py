@@ -1,0 +1,128 @@
+"""Batched device API: torch tensors in, torch tensors out, kernels through the C ABI.
+
+PyTorch is plumbing only here (device memory, streams): every computation is a call into
+liblslam.so (include/lslam.h) with ``tensor.data_ptr()`` and the current CUDA stream.  There
+is no CPU or eager fallback: without a CUDA device or without the built library the
+constructor raises.
+"""
+import torch
+
+from . import _lib
+
+# defaults = the reference's module constants (ransac_functions.py:9-11, functions.py:14)
+THRESHOLD = 20
+MAX_TRIALS = 100
+CHUNK = 100
+
+
+def _dev_index(device):
+    if device is None:
+        return torch.cuda.current_device()
+    d = torch.device(device)
+    if d.type != "cuda":
+        raise ValueError("lidar_slam_b200 runs on CUDA devices only, got %r" % (device,))
+    return d.index if d.index is not None else torch.cuda.current_device()
+
+
+class Engine:
+    """One liblslam handle bound to one CUDA device."""
+
+    def __init__(self, device=None, library_path=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("lidar_slam_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.index = _dev_index(device)
+        self.device = torch.device("cuda", self.index)
+        self.handle = _lib.Handle(self.index, path=library_path)
+
+    # ---- helpers -------------------------------------------------------------------------
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _check(self, t, dtype, name):
+        if not isinstance(t, torch.Tensor) or t.device != self.device:
+            raise ValueError("%s must be a tensor on %s" % (name, self.device))
+        if t.dtype != dtype or not t.is_contiguous():
+            raise ValueError("%s must be contiguous %s" % (name, dtype))
+        return t
+
+    def launch_count(self):
+        return self.handle.launch_count()
+
+    def set_option(self, key, value):
+        self.handle.set_option(key, value)
+
+    # ---- entry points --------------------------------------------------------------------
+    def polar_to_cart(self, dist_mm, angle_deg):
+        """functions.py:59-60 for device tensors of any (equal) shape -> xy[..., 2]."""
+        dist_mm = self._check(dist_mm, torch.float64, "dist_mm")
+        angle_deg = self._check(angle_deg, torch.float64, "angle_deg")
+        if dist_mm.shape != angle_deg.shape:
+            raise ValueError("dist_mm and angle_deg must have the same shape")
+        xy = torch.empty(dist_mm.shape + (2,), dtype=torch.float64, device=self.device)
+        self.handle.polar_to_cart(dist_mm.data_ptr(), angle_deg.data_ptr(), xy.data_ptr(),
+                                  dist_mm.numel(), self._stream())
+        return xy
+
+    def alloc_ransac_out(self, B, N, chunk=CHUNK):
+        C = (N + chunk - 1) // chunk
+        W = (chunk + 31) // 32
+        dev = self.device
+        return {
+            "line": torch.empty((B, C, 8), dtype=torch.float64, device=dev),
+            "ninl": torch.empty((B, C), dtype=torch.int32, device=dev),
+            "win_trial": torch.empty((B, C), dtype=torch.int32, device=dev),
+            "win_pair": torch.empty((B, C, 2), dtype=torch.int32, device=dev),
+            "ssum": torch.empty((B, C), dtype=torch.float64, device=dev),
+            "inl_mask": torch.empty((B, C, W), dtype=torch.int32, device=dev),
+        }
+
+    def ransac_lines(self, xy, npts=None, chunk=CHUNK, trials=MAX_TRIALS, thr=THRESHOLD,
+                     seed=0, scan_base=0, out=None):
+        """Batched landmark extraction (ransac_functions.py:20-31 per chunk).
+
+        xy [B, N, 2] float64 on this device; npts [B] int32 or None.  Returns the dict of
+        lslam_ransac_lines outputs (include/lslam.h); ``inl_mask`` words are int32 bit
+        patterns.  Asynchronous on the current stream.
+        """
+        xy = self._check(xy, torch.float64, "xy")
+        if xy.dim() != 3 or xy.shape[2] != 2:
+            raise ValueError("xy must be [B, N, 2]")
+        B, N = int(xy.shape[0]), int(xy.shape[1])
+        if npts is not None:
+            npts = self._check(npts, torch.int32, "npts")
+            if npts.numel() != B:
+                raise ValueError("npts must have B elements")
+        if out is None:
+            out = self.alloc_ransac_out(B, N, chunk)
+        self.handle.ransac_lines(
+            xy.data_ptr(), npts.data_ptr() if npts is not None else None, B, N, int(chunk),
+            int(trials), float(thr), seed, scan_base, out["line"].data_ptr(), out["ninl"].data_ptr(),
+            out["win_trial"].data_ptr(), out["win_pair"].data_ptr(), out["ssum"].data_ptr(),
+            out["inl_mask"].data_ptr(), self._stream())
+        return out
+
+    def ransac_counters(self):
+        return self.handle.ransac_counters(self._stream())
+
+    def synth_scans(self, B, beams=360, seed=0, scan_base=0, noise_mm=5.0, dropout=0.02, out=None):
+        """Random-room scans generated on the device (csrc/aux_kernels.cuh) -> xy[B, beams, 2]."""
+        if out is None:
+            out = torch.empty((B, beams, 2), dtype=torch.float64, device=self.device)
+        self.handle.synth_scans(out.data_ptr(), B, beams, seed, scan_base, noise_mm, dropout,
+                                self._stream())
+        return out
+
+    def fp64_peak(self, ms_target=50.0):
+        """Measured dependent-chain DFMA rate of this device, TFLOP/s (roofline denominator)."""
+        return self.handle.fp64_peak(ms_target)
+
+
+_ENGINES = {}
+
+
+def engine(device=None):
+    """Process-wide Engine per device, created on first use (after fork, SLAM.py:20)."""
+    idx = _dev_index(device)
+    if idx not in _ENGINES:
+        _ENGINES[idx] = Engine(idx)
+    return _ENGINES[idx]

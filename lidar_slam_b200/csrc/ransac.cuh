@@ -275,7 +275,7 @@ __global__ void __launch_bounds__(MAXT) ransac_lines_kernel(const RansacArgs a)
             mx = 0;
             for (int t = lane; t < T; t += 32) { const int v = cq[t] & ~kCntExact; mx = mx > v ? mx : v; }
             mx = __reduce_max_sync(LSLAM_FULL_MASK, mx);
-            if (mx == 0) break;
+            if (mx < 2) break;     // upstream's final estimate() needs 2 points
             // (3) smallest upper bound of the literal residual sum among the tied trials
             double minhi = __longlong_as_double(0x7ff0000000000000LL);
             for (int t = lane; t < T; t += 32) {
@@ -344,7 +344,7 @@ __global__ void __launch_bounds__(MAXT) ransac_lines_kernel(const RansacArgs a)
             if (n_cand > 1) atomicAdd(a.counters + 1, (unsigned long long)(n_cand - 1));
             if (n_fault) atomicAdd(a.counters + 2, (unsigned long long)n_fault);
         }
-        if (mx == 0 || best_t < 0) { write_empty_slot(a, s, kStatusNoModel, lane); continue; }
+        if (mx < 2 || best_t < 0) { write_empty_slot(a, s, kStatusNoModel, lane); continue; }
         __syncwarp();
 
         // (5) refit on the winner's inliers: LineModelND.estimate(data[inliers])

@@ -122,7 +122,7 @@ static void refit(const double *p, int n, const uint32_t *mask, int cnt, double 
 }
 
 /* One chunk: the ransac loop + refit + slope/intercept/tip (ransac_functions.py:23-30).
- * Returns inlier count (0 = no model).  line = a,b,ox,oy,dx,dy,tipx,tipy */
+ * Returns inlier count (>= 2) or -3 (LSLAM_ERR_NO_MODEL).  line = a,b,ox,oy,dx,dy,tipx,tipy */
 int oracle_ransac_chunk(const double *p, int n, int trials, double thr, uint64_t seed,
                         uint64_t scan, uint32_t chunk, double line[8], int32_t *win_trial,
                         int32_t win_pair[2], double *ssum_out, uint32_t *mask)
@@ -142,7 +142,13 @@ int oracle_ransac_chunk(const double *p, int n, int trials, double thr, uint64_t
         }
     }
     *win_trial = win; win_pair[0] = wi; win_pair[1] = wj; *ssum_out = best_ssum;
-    if (win < 0) { for (int k = 0; k < 8; ++k) line[k] = NAN; return 0; }
+    /* fewer than 2 inliers: upstream's final LineModelND.estimate raises ValueError (or ransac
+     * returned (None, None) and ransac_functions.py:25 raises) -> LSLAM_ERR_NO_MODEL */
+    if (win < 0 || best_n < 2) {
+        for (int k = 0; k < 8; ++k) line[k] = NAN;
+        *win_trial = -1; win_pair[0] = win_pair[1] = -1; *ssum_out = NAN;
+        return -3;
+    }
     double s2, m[4];
     score(p, n, bm, thr, &s2, mask);
     refit(p, n, mask, best_n, m);

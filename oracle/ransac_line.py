@@ -107,9 +107,12 @@ def ransac_line(data, residual_threshold=THRESHOLD, max_trials=MAX_TRIALS,
     """skimage.measure.ransac(data, LineModelND, 2, residual_threshold, max_trials).
 
     ``pairs`` overrides the Philox sampler with explicit (i[T], j[T]) index arrays.
-    Returns ``((origin, direction), inliers[N] bool, info)`` or ``(None, None, info)`` when
-    no trial has an inlier (upstream returns (None, None); the reference then raises
-    AttributeError at ransac_functions.py:25).  ``info`` holds the winning trial, its pair,
+    Returns ``((origin, direction), inliers[N] bool, info)``.  Like upstream: returns
+    ``(None, None, info)`` when no trial was ever accepted (the reference then raises
+    AttributeError at ransac_functions.py:25) and raises ValueError from the final
+    ``estimate`` when the accepted trial has fewer than 2 inliers (a trial with ZERO inliers
+    is accepted by the rule ``count == best and ssum < inf``).  Both cases are
+    LSLAM_ERR_NO_MODEL in the C ABI.  ``info`` holds the winning trial, its pair,
     inlier count and ssum, and with ``details=True`` the per-trial counts/ssums.
     """
     data = np.asarray(data, dtype=np.float64)

@@ -1,0 +1,106 @@
+"""The RANSAC kernel SOURCE (lidar_slam_b200/csrc/ransac.cuh) executed on the CPU through
+tests/emu/cuda_emu.h, compared with the C oracle through the same C ABI.  This is the
+CPU-side proof of the kernel logic (fast pass + exact re-check + literal tie-break); the
+`-m gpu` tests repeat it on the real sm_100a build."""
+import numpy as np
+import pytest
+
+from lidar_slam_b200 import synth
+from tests.parity_util import assert_ransac_equal
+
+
+def test_random_rooms_all_thread_layouts(emu, cport):
+    xy = synth.random_room_scans(12, seed=3)
+    want = cport.ransac_lines(xy, seed=7, scan_base=123456789012)
+    h = emu.emu_handle()
+    try:
+        for tpt in (1, 2, 4):
+            h.set_option("ransac.tpt", tpt)
+            got = emu.emu_ransac_lines(xy, seed=7, scan_base=123456789012)
+            assert_ransac_equal(want, got, "tpt=%d" % tpt)
+        h.set_option("ransac.tpt", 0)
+        for g in (1, 3, 7):
+            h.set_option("ransac.slots_per_cta", g)
+            got = emu.emu_ransac_lines(xy, seed=7, scan_base=123456789012)
+            assert_ransac_equal(want, got, "slots_per_cta=%d" % g)
+    finally:
+        h.set_option("ransac.tpt", 0)
+        h.set_option("ransac.slots_per_cta", 0)
+    assert h.ransac_counters()["faults"] == 0
+
+
+def test_ragged_scans(emu, cport):
+    xy = synth.random_room_scans(12, seed=5)
+    npts = np.array([360, 359, 303, 302, 301, 300, 100, 2, 1, 0, 57, 202], np.int32)
+    want = cport.ransac_lines(xy, npts=npts)
+    got = emu.emu_ransac_lines(xy, npts=npts)
+    assert_ransac_equal(want, got, "ragged")
+    assert want["ninl"][3, 3] == 0 and want["ninl"][2, 3] == 3      # remainder of 2 dropped, of 3 kept
+
+
+def test_highres_chunks(emu, cport):
+    xy = synth.polygon_scan(beams=1640, nsides=5)[None]
+    want = cport.ransac_lines(xy, chunk=410, trials=256, seed=1)
+    got = emu.emu_ransac_lines(xy, chunk=410, trials=256, seed=1)
+    assert_ransac_equal(want, got, "chunk 410")
+
+
+def test_degenerate_geometry(emu, cport):
+    t = np.linspace(-1000, 1000, 100)
+    cases = {
+        "collinear": np.stack([t, 0.5 * t + 100], -1),
+        "vertical": np.stack([np.full(100, 1500.0), t], -1),
+        "all-zero": np.zeros((100, 2)),
+        "two-clusters": np.concatenate([np.zeros((50, 2)), np.tile([[100.0, 5.0]], (50, 1))]),
+        "tiny-scale": np.stack([t, 0.5 * t], -1) * 1e-250,
+    }
+    h = emu.emu_handle()
+    for name, data in cases.items():
+        want = cport.ransac_lines(data[None], seed=4)
+        got = emu.emu_ransac_lines(data[None], seed=4)
+        assert_ransac_equal(want, got, name)
+    assert h.ransac_counters()["faults"] == 0
+
+
+def test_threshold_edge_points_are_rechecked(emu, cport):
+    """Points placed within rounding distance of the threshold force the re-check band: the
+    fast pass must hand those trials to the literal formula and still agree bit for bit."""
+    rng = np.random.default_rng(0)
+    t = np.arange(100, dtype=np.float64) * 16.0
+    y = np.zeros(100)
+    y[5::7] = 20.0                                    # exactly on the threshold of y = 0
+    y[3::11] = np.nextafter(20.0, 0.0)
+    y[2::13] = np.nextafter(20.0, 100.0)
+    data = np.stack([t, y], -1)
+    want = cport.ransac_lines(data[None], seed=2)
+    h = emu.emu_handle()
+    h.ransac_counters()
+    got = emu.emu_ransac_lines(data[None], seed=2)
+    assert_ransac_equal(want, got, "threshold edge")
+    c = h.ransac_counters()
+    assert c["literal_rescored"] > 0 and c["faults"] == 0
+
+
+def test_status_codes(emu):
+    bad = synth.random_room_scans(1, seed=1)
+    bad[0, 150, 0] = np.nan
+    bad[0, 250, 1] = np.inf
+    got = emu.emu_ransac_lines(bad)
+    assert got["ninl"][0, 1] == -5 and got["ninl"][0, 2] == -5      # LSLAM_ERR_NONFINITE
+    assert got["ninl"][0, 0] > 2 and got["ninl"][0, 3] > 2
+    data = np.array([[0.0, 0.0], [10.0, 0.0], [20.0, 5.0]])
+    got = emu.emu_ransac_lines(data[None], chunk=3, trials=10, thr=0.0)
+    assert got["ninl"][0, 0] == -3 and got["win_trial"][0, 0] == -1   # LSLAM_ERR_NO_MODEL
+
+
+def test_bad_arguments_raise(emu):
+    from lidar_slam_b200._lib import LslamError
+    xy = np.zeros((1, 10, 2))
+    with pytest.raises(LslamError):
+        emu.emu_ransac_lines(xy, chunk=1)
+    with pytest.raises(LslamError):
+        emu.emu_ransac_lines(xy, trials=0)
+    with pytest.raises(LslamError):
+        emu.emu_ransac_lines(xy, thr=float("nan"))
+    with pytest.raises(LslamError):
+        emu.emu_handle().set_option("no.such.option", 1)
