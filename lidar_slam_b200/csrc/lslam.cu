@@ -73,23 +73,28 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
 }
 
 // ---- RANSAC ------------------------------------------------------------------------------
-template <int TPT, int MAXT>
+template <int TPT, int MAXT, int MINB>
 static int launch_ransac(Handle *h, RansacArgs a, int threads_target, cudaStream_t st)
 {
-    auto kern = ransac_lines_kernel<TPT, MAXT>;
+    auto kern = ransac_lines_kernel<TPT, MAXT, MINB>;
     a.ipc = (a.trials + TPT - 1) / TPT;
     if (threads_target > MAXT) threads_target = MAXT;
     // chunk slots per CTA: enough work items to fill the CTA, bounded by shared memory
-    int G = h->opt_slots ? h->opt_slots : (threads_target + a.ipc / 2) / a.ipc;
+    // (measured on B200: about 3.2 items per thread and 256-thread CTAs, 4 CTAs per SM)
+    int G = h->opt_slots ? h->opt_slots : (int)((3.2 * threads_target + a.ipc / 2) / a.ipc);
     if (G < 1) G = 1;
     if ((long long)G > a.nslots) G = (int)a.nslots;
     int threads = 0;
     size_t smem = 0;
     for (;; --G) {
-        long long want = (long long)G * a.ipc;
-        threads = (int)(want < threads_target ? want : threads_target);
+        // threads: split the CTA's work items into equal rounds so the last round is not
+        // mostly empty (items = G * ipc; every thread takes one item per round)
+        const long long items = (long long)G * a.ipc;
+        const long long rounds = (items + threads_target - 1) / threads_target;
+        threads = (int)((items + rounds - 1) / rounds);
         threads = (threads + 31) & ~31;
         if (threads > MAXT) threads = MAXT & ~31;
+        if (threads < 4 * G) threads = (4 * G + 31) & ~31 > MAXT ? MAXT & ~31 : (4 * G + 31) & ~31;
         smem = ransac_smem_bytes(G, a.chunk, a.trials, a.W, threads / 32);
         if (smem <= (size_t)h->smem_optin || G == 1) break;
     }
@@ -133,13 +138,13 @@ extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t 
     a.counters = h->counters_d;
     a.nslots = (long long)B * a.C;
     a.G = 0; a.ipc = 0;
-    const int tpt = h->opt_tpt ? h->opt_tpt : (trials >= 512 ? 4 : 2);
-    const int threads = h->opt_threads ? h->opt_threads : 512;
+    const int tpt = h->opt_tpt ? h->opt_tpt : 2;
+    const int threads = h->opt_threads ? h->opt_threads : 256;
     cudaStream_t st = (cudaStream_t)stream;
     switch (tpt) {
-    case 1: return launch_ransac<1, 768>(h, a, threads, st);
-    case 2: return launch_ransac<2, 768>(h, a, threads, st);
-    default: return launch_ransac<4, 512>(h, a, threads, st);
+    case 1: return launch_ransac<1, 512, 2>(h, a, threads, st);
+    case 2: return launch_ransac<2, 512, 2>(h, a, threads, st);
+    default: return launch_ransac<4, 512, 1>(h, a, threads, st);
     }
 }
 

@@ -100,8 +100,7 @@ __device__ __forceinline__ FastLine fast_pair_model(double2 pi, double2 pj)
     const double n2s = f.degenerate ? 1.0 : n2;
     double y = (double)rsqrtf((float)n2s);
     const double h = 0.5 * n2s;
-    y = y * fma(-h * y, y, 1.5);
-    y = y * fma(-h * y, y, 1.5);
+    y = y * fma(-h * y, y, 1.5);      // one Newton step: relative error < 2^-42, far inside the band
     f.nx = -dy * y;
     f.ny = dx * y;
     f.negc = -fma(f.nx, ox, f.ny * oy);
@@ -130,11 +129,22 @@ __device__ __forceinline__ ChunkBand chunk_band(int max_abs_hi /* max over coord
 
 // Upper bound on |ssum_literal - ssum_fast| for a chunk of n points:
 //   per point | r^2 - s^2 | <= eabs * (2|s| + eabs);  sum |s| <= sqrt(n * ssf)  (Cauchy-Schwarz)
+//   2 sqrt(n * ssf) <= n*c + ssf/c for any c > 0 (AM-GM); c = the threshold clamped to
+//   [eabs, chunk scale] keeps the bound tight where it matters (residuals of the order of thr)
 //   plus 2^-38 * ssf for the differing summation orders and roundings (n <= 8192).
-__device__ __forceinline__ double ssum_bound(double ssf, double eabs, int n)
+// The bound is linear in ssf, E(ssf) = alpha + beta * ssf, so a sweep over the trials needs no sqrt.
+struct SsumBound { double alpha, beta; };
+__device__ __forceinline__ SsumBound ssum_bound_coeffs(double eabs, int n, double thr)
 {
     const double nn = (double)n;
-    return 1.0001 * (eabs * (2.0 * sqrt(nn * ssf) + nn * eabs) + 0x1p-38 * ssf);
+    const double scale = eabs * 0x1p36;                  // chunk scale 2^e2
+    double c = thr;
+    if (!(c > eabs)) c = eabs;
+    if (c > scale) c = scale;
+    SsumBound b;
+    b.alpha = 1.0001 * eabs * nn * (c + eabs);
+    b.beta = 1.0001 * (eabs / c + 0x1p-38);
+    return b;
 }
 
 // ---- principal axis of a 2x2 scatter matrix (closed form of the SVD upstream uses) --------

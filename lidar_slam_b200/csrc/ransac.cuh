@@ -3,23 +3,24 @@
 // Replaces, per chunk, /root/reference/ransac_functions.py:23-30 (skimage.measure.ransac with
 // LineModelND, then slope/intercept/tip).  Semantics = oracle/ransac_line.py.
 //
-// Work decomposition (one CTA = G consecutive chunk slots, staged once in shared memory):
-//   pass 1  one THREAD per (chunk, block of TPT trials): the thread derives its hypotheses
-//           from Philox (one block per two trials), then walks the chunk's points, which every
-//           lane of the warp reads from the same shared-memory address (broadcast LDS.128).
-//           Per point-hypothesis: 2 DFMA (signed distance in normal form), 1 DFMA (sum of
-//           squares), 1 DADD (|s| - thr), then integer-pipe work only: the sign bit is
-//           funnel-shifted into a 32-point bitmask (POPC every 32 points) and the high word of
-//           |s| - thr feeds an FMNMX that tracks how close any point came to the threshold.
+// One CTA owns G consecutive chunk slots, staged once in shared memory, and runs phases that
+// each use the parallel axis that fits them (block barriers in between):
+//   score   one THREAD per (chunk, TPT trials): hypotheses from Philox (one block per two
+//           trials), then a walk over the chunk's points, read by every lane from the same
+//           shared-memory address (broadcast LDS.128).  Per point-hypothesis: 2 DFMA (signed
+//           distance, normal form) + 1 DFMA (sum of squares) + 1 DADD (|s| - thr); the sign bit
+//           is funnel-shifted into a 32-point bitmask (POPC every 32 points) and the high word
+//           of |s| - thr feeds an FMNMX3 that tracks how close any point came to the threshold.
 //           No shuffles, no reductions, no divergence in the hot loop.
-//   pass 2  one WARP per chunk: trials that came within the re-check band of the threshold (or
-//           had coincident sample points) are re-scored with the literal formula; among the
-//           trials tied on the maximal inlier count, only those whose fast residual sum could
-//           still be the minimum (rigorous bound, lslam_core.cuh) are re-scored literally, in
-//           trial order, with the oracle's summation tree; the first best wins, exactly like
-//           the sequential accept rule.  The winner's literal inlier mask then drives the
-//           total-least-squares refit (principal axis of the 2x2 scatter), slope, intercept
-//           and tip.
+//   select  one WARP per chunk: trials that came within the re-check band of the threshold (or
+//           had coincident samples) are re-scored with the literal formula; the maximal inlier
+//           count and the trials whose fast residual sum could still be the minimum (rigorous
+//           linear bound, lslam_core.cuh) become the candidate list (usually one trial).
+//   models  one LANE per (chunk, candidate): Philox pair + literal 2-point model (sqrt, 2 div).
+//   decide  one WARP per chunk: literal score of each candidate in trial order with the
+//           oracle's summation tree; first best wins like the sequential accept rule.
+//   refit   four LANES per chunk: one pass over the winner's inliers for the 2x2 scatter, then
+//           the principal axis (closed form of the SVD), slope, intercept, tip and the stores.
 // The early exit of the sequential loop (sum of squares <= 0) never changes the winner, so all
 // trials are evaluated.
 #pragma once
@@ -49,20 +50,38 @@ struct RansacArgs {
     long long nslots;               // B * C
 };
 
-struct SlotInfo { int off, n, scale_hi, valid; };
-
+constexpr int kMaxCand = 8;         // candidates with precomputed models; more -> generic loop
 constexpr int kCntFlagged = -1;
 constexpr int kCntExact = 0x40000000;
 constexpr int kStatusNoModel = -3;
 constexpr int kStatusNonFinite = -5;
 
+// per-slot state in shared memory
+struct SlotState {
+    unsigned long long scan;        // global scan index (Philox counter words 2,3)
+    double best_ss;                 // literal residual sum of the winner
+    int off, n, valid, c;           // first point (index into the staged points), count, flag, chunk idx
+    int scale_hi;                   // high word of the largest |coordinate|
+    int flag;                       // some trial needs the literal re-score
+    int mx, ncand, minhi_q;         // maximal inlier count, number of candidates, quantised bound
+    int best_t, best_i, best_j;     // winner trial and its sample pair
+    int status;                     // 0 ok, else the value written to ninl
+    int pad;
+    int cand_t[kMaxCand], cand_i[kMaxCand], cand_j[kMaxCand];
+};
+
+__host__ __device__ inline size_t align16(size_t b) { return (b + 15) & ~(size_t)15; }
+
 __host__ __device__ inline size_t ransac_smem_bytes(int G, int chunk, int T, int W, int nwarps)
 {
-    size_t b = (size_t)G * chunk * 16;           // points
-    b += (size_t)G * T * 8;                      // fast residual sums
-    b += (((size_t)G * T * 4) + 15) & ~(size_t)15; // counts
-    b += (size_t)G * sizeof(SlotInfo);
-    b += (size_t)nwarps * 2 * W * 4;             // two mask buffers per warp
+    size_t b = (size_t)G * chunk * 16;                       // points
+    b += (size_t)G * T * 8;                                  // fast residual sums
+    b += align16((size_t)G * T * 4);                         // counts
+    b += align16((size_t)G * sizeof(SlotState));
+    b += (size_t)G * kMaxCand * sizeof(LitLine);             // candidate models
+    b += align16((size_t)G * W * 4);                         // winner masks
+    b += align16((size_t)nwarps * W * 4);                    // per-warp scratch mask
+    b += 16;                                                 // CTA-wide scale
     return b;
 }
 
@@ -89,90 +108,161 @@ __device__ __forceinline__ void warp_literal_score(const double2 *P, int n, cons
     ssum = warp_tree32(part);
 }
 
-__device__ __forceinline__ void write_empty_slot(const RansacArgs &a, long long s, int status, int lane)
+// order-preserving 32-bit keys of non-negative doubles (high word), rounded down / up
+__device__ __forceinline__ int key_down(double v) { return v > 0.0 ? __double2hiint(v) : 0; }
+__device__ __forceinline__ int key_up(double v) { return v > 0.0 ? __double2hiint(v) + 1 : 1; }
+
+// candidate test of trial t for the tie-break: tied on the maximal count and its lower bound
+// does not exceed the smallest upper bound
+__device__ __forceinline__ bool trial_is_candidate(int cv, double v, int mx, int minhi_q, const SsumBound &sb)
 {
-    if (lane == 0) {
-        const double qnan = __longlong_as_double(0x7ff8000000000000LL);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) a.line[s * 8 + k] = qnan;
-        a.ninl[s] = status;
-        a.win_trial[s] = -1;
-        a.win_pair[2 * s] = -1;
-        a.win_pair[2 * s + 1] = -1;
-        a.ssum[s] = qnan;
-    }
-    for (int w = lane; w < a.W; w += 32) a.mask[s * a.W + w] = 0u;
+    if ((cv & ~kCntExact) != mx) return false;
+    const double e = (cv & kCntExact) ? 0.0 : fma(sb.beta, v, sb.alpha);
+    return key_down(v - e) <= minhi_q;
 }
 
-template <int TPT, int MAXT>
-__global__ void __launch_bounds__(MAXT) ransac_lines_kernel(const RansacArgs a)
+// ---- CTA-level view of shared memory ---------------------------------------------------
+struct RansacSmem {
+    double2 *pts;
+    double *ssf;
+    int *cnt;
+    SlotState *slot;
+    LitLine *cmodel;
+    uint32_t *smask;    // [G][W] winner masks
+    uint32_t *wtmp;     // [nwarps][W] scratch masks
+    int *cta_scale;
+};
+
+__device__ __forceinline__ RansacSmem carve_smem(unsigned char *raw, int G, int chunk, int T, int W, int nwarps)
+{
+    RansacSmem s;
+    unsigned char *p = raw;
+    s.pts = reinterpret_cast<double2 *>(p);   p += (size_t)G * chunk * 16;
+    s.ssf = reinterpret_cast<double *>(p);    p += (size_t)G * T * 8;
+    s.cnt = reinterpret_cast<int *>(p);       p += align16((size_t)G * T * 4);
+    s.slot = reinterpret_cast<SlotState *>(p); p += align16((size_t)G * sizeof(SlotState));
+    s.cmodel = reinterpret_cast<LitLine *>(p); p += (size_t)G * kMaxCand * sizeof(LitLine);
+    s.smask = reinterpret_cast<uint32_t *>(p); p += align16((size_t)G * W * 4);
+    s.wtmp = reinterpret_cast<uint32_t *>(p);  p += align16((size_t)nwarps * W * 4);
+    s.cta_scale = reinterpret_cast<int *>(p);
+    return s;
+}
+
+// Exact, slow path for one chunk: literal score of EVERY trial and the sequential accept rule.
+// Used only when the fast pass was caught disagreeing with the literal count (never observed;
+// counted in counters[2]).  Leaves the winner in the slot state and its mask in smask.
+__device__ void slot_exact_fallback(const RansacArgs &a, SlotState *st, const double2 *P, uint32_t *smask_q,
+                                    uint32_t *wtmp_w, int lane)
+{
+    const int n = st->n, T = a.trials;
+    int best_n = 0, best_t = -1, best_i = -1, best_j = -1;
+    double best_ss = __longlong_as_double(0x7ff0000000000000LL);
+    for (int t = 0; t < T; ++t) {
+        int i, j, cl;
+        double sl;
+        sample_pair(a.seed, st->scan, (uint32_t)st->c, (uint32_t)t, (uint32_t)n, i, j);
+        warp_literal_score(P, n, lit_pair_model(P[i], P[j]), a.thr, lane, cl, sl, wtmp_w);
+        __syncwarp();
+        if (cl > best_n || (cl == best_n && sl < best_ss)) {
+            best_n = cl; best_ss = sl; best_t = t; best_i = i; best_j = j;
+            for (int w = lane; w * 32 < n; w += 32) smask_q[w] = wtmp_w[w];
+        }
+        __syncwarp();
+    }
+    if (lane == 0) {
+        st->mx = best_n; st->best_t = best_t; st->best_i = best_i; st->best_j = best_j; st->best_ss = best_ss;
+        st->status = (best_t < 0 || best_n < 2) ? kStatusNoModel : 0;
+    }
+    __syncwarp();
+}
+
+template <int TPT, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacArgs a)
 {
     LSLAM_SMEM_DECL;
-    const int T = a.trials, G = a.G, chunk = a.chunk;
-    double2 *pts = reinterpret_cast<double2 *>(smem_raw);
-    double *ssf_s = reinterpret_cast<double *>(pts + (size_t)G * chunk);
-    int *cnt_s = reinterpret_cast<int *>(ssf_s + (size_t)G * T);
-    SlotInfo *info = reinterpret_cast<SlotInfo *>(
-        reinterpret_cast<unsigned char *>(cnt_s) + ((((size_t)G * T * 4) + 15) & ~(size_t)15));
-    uint32_t *wmask = reinterpret_cast<uint32_t *>(info + G);
-
+    const int T = a.trials, G = a.G, chunk = a.chunk, W = a.W;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const RansacSmem sm = carve_smem(smem_raw, G, chunk, T, W, nwarps);
     const long long slot0 = (long long)blockIdx.x * G;
     const long long rem_slots = a.nslots - slot0;
     const int nsl = rem_slots < (long long)G ? (int)rem_slots : G;
     const int b0 = (int)(slot0 / a.C), c0 = (int)(slot0 % a.C);
     const long long gp0 = (long long)b0 * a.N + (long long)c0 * chunk;   // first staged point
 
-    // ---- stage the CTA's points (contiguous in global memory), 16 B per thread, coalesced ----
+    // ---- stage the CTA's points (contiguous in global memory): 16 B per thread, coalesced;
+    //      track the largest |coordinate| of the CTA on the way ----
+    if (tid == 0) *sm.cta_scale = 0;
+    __syncthreads();
     {
         const long long sl = slot0 + nsl - 1;
         const int bl = (int)(sl / a.C), cl = (int)(sl % a.C);
         const int cend = (cl + 1) * chunk < a.N ? (cl + 1) * chunk : a.N;
         const int nstage = (int)((long long)bl * a.N + cend - gp0);
         const double2 *src = a.xy + gp0;
-        for (int k = tid; k < nstage; k += blockDim.x) pts[k] = __ldg(src + k);
+        int mh = 0;
+        for (int k = tid; k < nstage; k += blockDim.x) {
+            const double2 p = __ldg(src + k);
+            sm.pts[k] = p;
+            const int hx = __double2hiint(p.x) & 0x7fffffff, hy = __double2hiint(p.y) & 0x7fffffff;
+            mh = mh > hx ? mh : hx;
+            mh = mh > hy ? mh : hy;
+        }
+        mh = __reduce_max_sync(LSLAM_FULL_MASK, mh);
+        if (lane == 0 && mh > 0) atomicMax(sm.cta_scale, mh);
     }
     __syncthreads();
-    // ---- per-slot geometry and coordinate scale (one warp per slot) ----
-    for (int q = warp; q < nsl; q += nwarps) {
+    // ---- per-slot geometry (one lane per slot) ----
+    const bool cta_scale_bad = chunk_band(*sm.cta_scale).bad;
+    for (int q = tid; q < nsl; q += blockDim.x) {
         const long long s = slot0 + q;
         const int b = (int)(s / a.C), c = (int)(s % a.C);
         int nb = a.npts ? a.npts[b] : a.N;
         nb = nb < 0 ? 0 : (nb > a.N ? a.N : nb);
         int n = nb - c * chunk;
         n = n < 0 ? 0 : (n > chunk ? chunk : n);
-        const int off = (int)((long long)b * a.N + (long long)c * chunk - gp0);
-        int mh = 0;
-        for (int k = lane; k < n; k += 32) {
-            const double2 p = pts[off + k];
-            const int hx = __double2hiint(p.x) & 0x7fffffff, hy = __double2hiint(p.y) & 0x7fffffff;
-            mh = mh > hx ? mh : hx;
-            mh = mh > hy ? mh : hy;
-        }
-        mh = __reduce_max_sync(LSLAM_FULL_MASK, mh);
-        if (lane == 0) {
-            SlotInfo si;
-            si.off = off; si.n = n; si.scale_hi = mh;
-            // functions.py:64-76: full chunks, or a remainder of MORE than 2 points
-            si.valid = (n >= 2) && (n == chunk || n > 2);
-            info[q] = si;
-        }
+        SlotState *st = sm.slot + q;
+        st->scan = a.scan_base + (uint64_t)b;
+        st->best_ss = 0.0;
+        st->off = (int)((long long)b * a.N + (long long)c * chunk - gp0);
+        st->n = n;
+        // functions.py:64-76: full chunks, or a remainder of MORE than 2 points
+        st->valid = (n >= 2) && (n == chunk || n > 2);
+        st->c = c;
+        st->scale_hi = *sm.cta_scale;
+        st->flag = 0; st->mx = 0; st->ncand = 0; st->minhi_q = 0;
+        st->best_t = -1; st->best_i = -1; st->best_j = -1;
+        st->status = 0;
     }
     __syncthreads();
+    if (cta_scale_bad) {
+        // some coordinate of the CTA is non-finite (or garbage past npts): find out per slot
+        for (int q = warp; q < nsl; q += nwarps) {
+            SlotState *st = sm.slot + q;
+            int mh = 0;
+            for (int k = lane; k < st->n; k += 32) {
+                const double2 p = sm.pts[st->off + k];
+                const int hx = __double2hiint(p.x) & 0x7fffffff, hy = __double2hiint(p.y) & 0x7fffffff;
+                mh = mh > hx ? mh : hx;
+                mh = mh > hy ? mh : hy;
+            }
+            mh = __reduce_max_sync(LSLAM_FULL_MASK, mh);
+            if (lane == 0) st->scale_hi = mh;
+        }
+        __syncthreads();
+    }
 
-    // ================= pass 1: thread per (chunk, TPT trials), loop over points =================
+    // ================= score: thread per (chunk, TPT trials), loop over the chunk's points =========
     const int items = nsl * a.ipc;
     for (int item = tid; item < items; item += blockDim.x) {
         const int q = item / a.ipc, tb = item - q * a.ipc;
-        const SlotInfo si = info[q];
-        const ChunkBand cb = chunk_band(si.scale_hi);
-        const bool skip = !si.valid || cb.bad;
-        const double2 *P = pts + si.off;
-        const long long s = slot0 + q;
-        const uint64_t scan = a.scan_base + (uint64_t)(s / a.C);
-        const uint32_t c = (uint32_t)(s % a.C);
+        SlotState *st = sm.slot + q;
+        const ChunkBand cb = chunk_band(st->scale_hi);
+        const bool skip = !st->valid || cb.bad;
+        const double2 *P = sm.pts + st->off;
+        const uint64_t scan = st->scan;
+        const uint32_t c = (uint32_t)st->c;
         const int t0 = tb * TPT;
-        const uint32_t n = (uint32_t)si.n;
+        const uint32_t n = (uint32_t)st->n;
 
         double nx[TPT], ny[TPT], ng[TPT], ss[TPT];
         unsigned bits[TPT];
@@ -218,44 +308,50 @@ __global__ void __launch_bounds__(MAXT) ransac_lines_kernel(const RansacArgs a)
         }
         const int rem = n_eff - k;
         if (rem > 0) {
-            for (int kk = 0; kk < rem; ++kk) LSLAM_PHE_STEP(P[k + kk]);
+            int kk = 0;
+            for (; kk + 4 <= rem; kk += 4) {
+                LSLAM_PHE_STEP(P[k + kk]);
+                LSLAM_PHE_STEP(P[k + kk + 1]);
+                LSLAM_PHE_STEP(P[k + kk + 2]);
+                LSLAM_PHE_STEP(P[k + kk + 3]);
+            }
+            for (; kk < rem; ++kk) LSLAM_PHE_STEP(P[k + kk]);
 #pragma unroll
             for (int k_ = 0; k_ < TPT; ++k_) cnt[k_] += __popc(bits[k_] & ((1u << rem) - 1u));
         }
 #undef LSLAM_PHE_STEP
+        bool any_flag = false;
 #pragma unroll
         for (int k_ = 0; k_ < TPT; ++k_) {
             const int t = t0 + k_;
             if (t < T) {
-                const bool flag = deg[k_] || cb.force_literal || __float_as_int(mab[k_]) < cb.band_hi;
-                cnt_s[q * T + t] = skip ? 0 : (flag ? kCntFlagged : cnt[k_]);
-                ssf_s[q * T + t] = ss[k_];
+                // literal re-score wanted: coincident samples, denormal-scale chunk, a point inside
+                // the band around the threshold, or a non-finite fast sum
+                const bool flag = deg[k_] || cb.force_literal || __float_as_int(mab[k_]) < cb.band_hi ||
+                                  !(ss[k_] <= 1.7976931348623157e308);
+                sm.cnt[q * T + t] = skip ? 0 : (flag ? kCntFlagged : cnt[k_]);
+                sm.ssf[q * T + t] = ss[k_];
+                any_flag |= flag && !skip;
             }
         }
+        if (any_flag) st->flag = 1;
     }
     __syncthreads();
 
-    // ================= pass 2: warp per chunk - exact selection, refit, outputs =================
-    uint32_t *mcur = wmask + (size_t)warp * 2 * a.W;
-    uint32_t *mbest = mcur + a.W;
+    // ================= select: warp per chunk - flagged re-score, max count, candidate list ========
     for (int q = warp; q < nsl; q += nwarps) {
-        const SlotInfo si = info[q];
-        const long long s = slot0 + q;
-        const ChunkBand cb = chunk_band(si.scale_hi);
-        if (!si.valid) { write_empty_slot(a, s, 0, lane); continue; }
-        if (cb.bad) { write_empty_slot(a, s, kStatusNonFinite, lane); continue; }
-        const int n = si.n;
-        const double2 *P = pts + si.off;
-        const uint64_t scan = a.scan_base + (uint64_t)(s / a.C);
-        const uint32_t c = (uint32_t)(s % a.C);
-        int *cq = cnt_s + q * T;
-        double *sq = ssf_s + q * T;
-        unsigned n_relit = 0, n_cand = 0, n_fault = 0;
-
-        int mx = 0, best_t = -1, best_i = -1, best_j = -1;
-        double best_ss = 0.0;
-        for (int attempt = 0; attempt < 2; ++attempt) {
-            // (1) literal re-score of flagged trials
+        SlotState *st = sm.slot + q;
+        const ChunkBand cb = chunk_band(st->scale_hi);
+        if (!st->valid || cb.bad) {
+            if (lane == 0) st->status = !st->valid ? 0x7fffffff : kStatusNonFinite;   // 0x7fffffff: unused slot
+            continue;
+        }
+        const int n = st->n;
+        const double2 *P = sm.pts + st->off;
+        int *cq = sm.cnt + q * T;
+        double *sq = sm.ssf + q * T;
+        if (st->flag) {
+            unsigned n_relit = 0;
             for (int t0 = 0; t0 < T; t0 += 32) {
                 const int t = t0 + lane;
                 unsigned m = __ballot_sync(LSLAM_FULL_MASK, t < T && cq[t] == kCntFlagged);
@@ -264,146 +360,207 @@ __global__ void __launch_bounds__(MAXT) ransac_lines_kernel(const RansacArgs a)
                     m &= m - 1;
                     int i, j, cl;
                     double sl;
-                    sample_pair(a.seed, scan, c, (uint32_t)tt, (uint32_t)n, i, j);
+                    sample_pair(a.seed, st->scan, (uint32_t)st->c, (uint32_t)tt, (uint32_t)n, i, j);
                     warp_literal_score(P, n, lit_pair_model(P[i], P[j]), a.thr, lane, cl, sl, nullptr);
                     if (lane == 0) { cq[tt] = cl | kCntExact; sq[tt] = sl; }
                     ++n_relit;
                 }
             }
+            if (lane == 0 && n_relit) atomicAdd(a.counters + 0, (unsigned long long)n_relit);
             __syncwarp();
-            // (2) maximal inlier count
-            mx = 0;
-            for (int t = lane; t < T; t += 32) { const int v = cq[t] & ~kCntExact; mx = mx > v ? mx : v; }
-            mx = __reduce_max_sync(LSLAM_FULL_MASK, mx);
-            if (mx < 2) break;     // upstream's final estimate() needs 2 points
-            // (3) smallest upper bound of the literal residual sum among the tied trials
-            double minhi = __longlong_as_double(0x7ff0000000000000LL);
-            for (int t = lane; t < T; t += 32) {
-                const int cv = cq[t];
-                if ((cv & ~kCntExact) == mx) {
-                    const double v = sq[t];
-                    const double e = (cv & kCntExact) ? 0.0 : ssum_bound(v, cb.eabs, n);
-                    minhi = fmin(minhi, v + e);
-                }
+        }
+        // maximal inlier count
+        int mx = 0;
+        for (int t = lane; t < T; t += 32) { const int v = cq[t] & ~kCntExact; mx = mx > v ? mx : v; }
+        mx = __reduce_max_sync(LSLAM_FULL_MASK, mx);
+        if (mx < 2) {                       // upstream's final estimate() needs 2 points
+            if (lane == 0) { st->mx = mx; st->status = kStatusNoModel; }
+            continue;
+        }
+        // smallest upper bound of the literal residual sum among the tied trials (quantised up)
+        const SsumBound sb = ssum_bound_coeffs(cb.eabs, n, a.thr);
+        int minhi_q = 0x7fffffff;
+        for (int t = lane; t < T; t += 32) {
+            const int cv = cq[t];
+            if ((cv & ~kCntExact) == mx) {
+                const double v = sq[t];
+                const double e = (cv & kCntExact) ? 0.0 : fma(sb.beta, v, sb.alpha);
+                const int k = key_up(v + e);
+                minhi_q = minhi_q < k ? minhi_q : k;
             }
-            minhi = warp_min(minhi);
-            // (4) literal evaluation of the trials that can still be the minimum, in trial order
-            best_t = -1;
-            best_ss = __longlong_as_double(0x7ff0000000000000LL);
-            bool fault = false;
-            int first_tied = -1;
+        }
+        minhi_q = __reduce_min_sync(LSLAM_FULL_MASK, minhi_q);
+        // candidate list in trial order
+        int ncand = 0;
+        for (int t0 = 0; t0 < T; t0 += 32) {
+            const int t = t0 + lane;
+            const bool cand = t < T && trial_is_candidate(cq[t], sq[t], mx, minhi_q, sb);
+            const unsigned m = __ballot_sync(LSLAM_FULL_MASK, cand);
+            if (cand) {
+                const int pos = ncand + __popc(m & ((1u << lane) - 1u));
+                if (pos < kMaxCand) st->cand_t[pos] = t;
+            }
+            ncand += __popc(m);
+        }
+        if (lane == 0) { st->mx = mx; st->ncand = ncand; st->minhi_q = minhi_q; }
+    }
+    __syncthreads();
+
+    // ================= models: lane per (chunk, candidate) - Philox pair + literal 2-point model ====
+    for (int e = tid; e < nsl * kMaxCand; e += blockDim.x) {
+        const int q = e / kMaxCand, ci = e - q * kMaxCand;
+        SlotState *st = sm.slot + q;
+        if (st->status == 0 && ci < st->ncand) {
+            const double2 *P = sm.pts + st->off;
+            int i, j;
+            sample_pair(a.seed, st->scan, (uint32_t)st->c, (uint32_t)st->cand_t[ci], (uint32_t)st->n, i, j);
+            st->cand_i[ci] = i;
+            st->cand_j[ci] = j;
+            sm.cmodel[e] = lit_pair_model(P[i], P[j]);
+        }
+    }
+    __syncthreads();
+
+    // ================= decide: warp per chunk - literal tie-break in trial order ====================
+    for (int q = warp; q < nsl; q += nwarps) {
+        SlotState *st = sm.slot + q;
+        if (st->status != 0) continue;
+        const int n = st->n, mx = st->mx, ncand = st->ncand;
+        const double2 *P = sm.pts + st->off;
+        uint32_t *wt = sm.wtmp + (size_t)warp * W;
+        uint32_t *mq = sm.smask + (size_t)q * W;
+        bool fault = false;
+        int best_t = -1, best_i = -1, best_j = -1;
+        double best_ss = __longlong_as_double(0x7ff0000000000000LL);
+        if (ncand <= kMaxCand) {
+            for (int ci = 0; ci < ncand; ++ci) {
+                int cl;
+                double sl;
+                warp_literal_score(P, n, sm.cmodel[q * kMaxCand + ci], a.thr, lane, cl, sl, ncand == 1 ? mq : wt);
+                __syncwarp();
+                if (cl != mx) fault = true;
+                if (sl < best_ss) {
+                    best_ss = sl; best_t = st->cand_t[ci]; best_i = st->cand_i[ci]; best_j = st->cand_j[ci];
+                    if (ncand > 1) for (int w = lane; w * 32 < n; w += 32) mq[w] = wt[w];
+                }
+                __syncwarp();
+            }
+        } else {
+            // many candidates (e.g. noise-free collinear data): sweep the trials again
+            int *cq = sm.cnt + q * T;
+            double *sq = sm.ssf + q * T;
+            const SsumBound sb = ssum_bound_coeffs(chunk_band(st->scale_hi).eabs, n, a.thr);
             for (int t0 = 0; t0 < T; t0 += 32) {
                 const int t = t0 + lane;
-                bool tied = false, cand = false;
-                if (t < T) {
-                    const int cv = cq[t];
-                    if ((cv & ~kCntExact) == mx) {
-                        tied = true;
-                        const double v = sq[t];
-                        const double e = (cv & kCntExact) ? 0.0 : ssum_bound(v, cb.eabs, n);
-                        cand = (v - e) <= minhi;
-                    }
-                }
-                const unsigned mt = __ballot_sync(LSLAM_FULL_MASK, tied);
-                if (first_tied < 0 && mt) first_tied = t0 + __ffs((int)mt) - 1;
+                const bool cand = t < T && trial_is_candidate(cq[t], sq[t], mx, st->minhi_q, sb);
                 unsigned m = __ballot_sync(LSLAM_FULL_MASK, cand);
                 while (m) {
                     const int tt = t0 + __ffs((int)m) - 1;
                     m &= m - 1;
                     int i, j, cl;
                     double sl;
-                    sample_pair(a.seed, scan, c, (uint32_t)tt, (uint32_t)n, i, j);
-                    warp_literal_score(P, n, lit_pair_model(P[i], P[j]), a.thr, lane, cl, sl, mcur);
-                    ++n_cand;
+                    sample_pair(a.seed, st->scan, (uint32_t)st->c, (uint32_t)tt, (uint32_t)n, i, j);
+                    warp_literal_score(P, n, lit_pair_model(P[i], P[j]), a.thr, lane, cl, sl, wt);
+                    __syncwarp();
                     if (cl != mx) fault = true;
                     if (sl < best_ss) {
                         best_ss = sl; best_t = tt; best_i = i; best_j = j;
-                        uint32_t *tmp = mcur; mcur = mbest; mbest = tmp;
+                        for (int w = lane; w * 32 < n; w += 32) mq[w] = wt[w];
                     }
+                    __syncwarp();
                 }
             }
-            if (!fault && best_t < 0 && first_tied >= 0) {
-                // every candidate had a non-finite sum: the sequential rule keeps the first trial
-                // that reached the maximal count
-                int cl;
-                sample_pair(a.seed, scan, c, (uint32_t)first_tied, (uint32_t)n, best_i, best_j);
-                warp_literal_score(P, n, lit_pair_model(P[best_i], P[best_j]), a.thr, lane, cl, best_ss, mbest);
-                best_t = first_tied;
-                if (cl != mx) fault = true;
-            }
-            if (!fault) break;
-            // A fast count disagreed with the literal one: the error bound was violated (never
-            // observed; counted in counters[2]).  Re-score EVERY trial literally and redo.
-            ++n_fault;
-            __syncwarp();
-            for (int t = lane; t < T; t += 32) cq[t] = kCntFlagged;
-            __syncwarp();
         }
         if (lane == 0) {
-            if (n_relit) atomicAdd(a.counters + 0, (unsigned long long)n_relit);
-            if (n_cand > 1) atomicAdd(a.counters + 1, (unsigned long long)(n_cand - 1));
-            if (n_fault) atomicAdd(a.counters + 2, (unsigned long long)n_fault);
+            st->best_t = best_t; st->best_i = best_i; st->best_j = best_j; st->best_ss = best_ss;
+            if (ncand > 1) atomicAdd(a.counters + 1, (unsigned long long)(ncand - 1));
         }
-        if (mx < 2 || best_t < 0) { write_empty_slot(a, s, kStatusNoModel, lane); continue; }
         __syncwarp();
+        if (fault || best_t < 0) {
+            // a fast count disagreed with the literal one (error bound violated - never observed):
+            // redo this chunk with the exact sequential rule
+            if (lane == 0) atomicAdd(a.counters + 2, 1ULL);
+            slot_exact_fallback(a, st, P, mq, wt, lane);
+        }
+    }
+    __syncthreads();
 
-        // (5) refit on the winner's inliers: LineModelND.estimate(data[inliers])
-        double ox, oy, dx, dy;
-        if (mx == 2) {
-            int i0 = -1, i1 = -1;
-            if (lane == 0) {
-                for (int w = 0; w * 32 < n; ++w) {
-                    unsigned mw = mbest[w];
-                    while (mw) {
-                        const int k = w * 32 + __ffs((int)mw) - 1;
-                        mw &= mw - 1;
-                        if (i0 < 0) i0 = k; else if (i1 < 0) i1 = k;
-                    }
+    // ================= refit + outputs: four lanes per chunk ========================================
+    // LineModelND.estimate(data[inliers]) as the principal axis of the 2x2 scatter, accumulated in
+    // one pass relative to the winner's first sample point (an inlier, so the shift is benign).
+    const int lanes_total = nsl * 4;
+    for (int base = warp * 32; base < lanes_total; base += nwarps * 32) {
+        const int e = base + lane;
+        const bool act = e < lanes_total;
+        const int q = act ? (e >> 2) : 0, r = e & 3;
+        SlotState *st = sm.slot + q;
+        const bool ok = act && st->status == 0;
+        const double2 *P = sm.pts + st->off;
+        const uint32_t *mq = sm.smask + (size_t)q * W;
+        const int n = st->n;
+        double sx = 0.0, sy = 0.0, sxx = 0.0, sxy = 0.0, syy = 0.0;
+        double2 p0 = make_double2(0.0, 0.0);
+        if (ok) {
+            p0 = P[st->best_i];
+            for (int k = r; k < n; k += 4) {
+                if ((mq[k >> 5] >> (k & 31)) & 1u) {
+                    const double2 p = P[k];
+                    const double dx = p.x - p0.x, dy = p.y - p0.y;
+                    sx += dx; sy += dy;
+                    sxx = fma(dx, dx, sxx); sxy = fma(dx, dy, sxy); syy = fma(dy, dy, syy);
                 }
             }
-            i0 = __shfl_sync(LSLAM_FULL_MASK, i0, 0);
-            i1 = __shfl_sync(LSLAM_FULL_MASK, i1, 0);
-            const LitLine m = lit_pair_model(P[i0], P[i1]);
-            ox = m.ox; oy = m.oy; dx = m.dx; dy = m.dy;
-            if (dx < 0.0 || (dx == 0.0 && dy < 0.0)) { dx = -dx; dy = -dy; }
-        } else {
-            double sx = 0.0, sy = 0.0;
-            for (int k = lane; k < n; k += 32)
-                if ((mbest[k >> 5] >> (k & 31)) & 1u) { const double2 p = P[k]; sx += p.x; sy += p.y; }
-            sx = warp_sum(sx); sy = warp_sum(sy);
-            ox = sx / (double)mx; oy = sy / (double)mx;
-            double sxx = 0.0, sxy = 0.0, syy = 0.0;
-            for (int k = lane; k < n; k += 32)
-                if ((mbest[k >> 5] >> (k & 31)) & 1u) {
-                    const double2 p = P[k];
-                    const double cx = p.x - ox, cy = p.y - oy;
-                    sxx = fma(cx, cx, sxx); sxy = fma(cx, cy, sxy); syy = fma(cy, cy, syy);
-                }
-            sxx = warp_sum(sxx); sxy = warp_sum(sxy); syy = warp_sum(syy);
-            principal_axis(sxx, sxy, syy, dx, dy);
         }
-        int last = -1;
-        for (int w = lane; w * 32 < n; w += 32) {
-            const unsigned mw = mbest[w];
-            if (mw) { const int k = w * 32 + 31 - __clz((int)mw); last = last > k ? last : k; }
+#pragma unroll
+        for (int o = 1; o <= 2; o <<= 1) {
+            sx += __shfl_xor_sync(LSLAM_FULL_MASK, sx, o);
+            sy += __shfl_xor_sync(LSLAM_FULL_MASK, sy, o);
+            sxx += __shfl_xor_sync(LSLAM_FULL_MASK, sxx, o);
+            sxy += __shfl_xor_sync(LSLAM_FULL_MASK, sxy, o);
+            syy += __shfl_xor_sync(LSLAM_FULL_MASK, syy, o);
         }
-        last = __reduce_max_sync(LSLAM_FULL_MASK, last);
-        if (lane == 0) {
-            // ransac_functions.py:26-30 (no guard for dir_x == 0, like the reference)
-            const double sl = __ddiv_rn(dy, dx);
-            const double ic = __dsub_rn(oy, __dmul_rn(sl, ox));
-            const double tipx = P[last].x;
-            const double tipy = __dadd_rn(__dmul_rn(tipx, sl), ic);
+        if (act && r == 0) {
+            const long long s = slot0 + q;
             double *L = a.line + s * 8;
-            L[0] = sl; L[1] = ic; L[2] = ox; L[3] = oy; L[4] = dx; L[5] = dy; L[6] = tipx; L[7] = tipy;
-            a.ninl[s] = mx;
-            a.win_trial[s] = best_t;
-            a.win_pair[2 * s] = best_i;
-            a.win_pair[2 * s + 1] = best_j;
-            a.ssum[s] = best_ss;
+            if (ok) {
+                const double m = (double)st->mx;
+                const double mdx = sx / m, mdy = sy / m;
+                const double ox = p0.x + mdx, oy = p0.y + mdy;
+                double dx, dy;
+                principal_axis(fma(-sx, mdx, sxx), fma(-sx, mdy, sxy), fma(-sy, mdy, syy), dx, dy);
+                int last = 0;
+                for (int w = (n - 1) >> 5; w >= 0; --w) {
+                    const unsigned mw = mq[w];
+                    if (mw) { last = w * 32 + 31 - __clz((int)mw); break; }
+                }
+                // ransac_functions.py:26-30 (no guard for dir_x == 0, like the reference)
+                const double sl = __ddiv_rn(dy, dx);
+                const double ic = __dsub_rn(oy, __dmul_rn(sl, ox));
+                const double tipx = P[last].x;
+                const double tipy = __dadd_rn(__dmul_rn(tipx, sl), ic);
+                L[0] = sl; L[1] = ic; L[2] = ox; L[3] = oy; L[4] = dx; L[5] = dy; L[6] = tipx; L[7] = tipy;
+                a.ninl[s] = st->mx;
+                a.win_trial[s] = st->best_t;
+                a.win_pair[2 * s] = st->best_i;
+                a.win_pair[2 * s + 1] = st->best_j;
+                a.ssum[s] = st->best_ss;
+            } else {
+                const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) L[k] = qnan;
+                a.ninl[s] = st->status == 0x7fffffff ? 0 : st->status;
+                a.win_trial[s] = -1;
+                a.win_pair[2 * s] = -1;
+                a.win_pair[2 * s + 1] = -1;
+                a.ssum[s] = qnan;
+            }
         }
-        for (int w = lane; w < a.W; w += 32) a.mask[s * a.W + w] = (w * 32 < n) ? mbest[w] : 0u;
-        __syncwarp();
+    }
+    // inlier masks: consecutive slots are consecutive in global memory -> coalesced stores
+    for (int i = tid; i < nsl * W; i += blockDim.x) {
+        const int q = i / W, w = i - q * W;
+        const SlotState *st = sm.slot + q;
+        a.mask[slot0 * W + i] = (st->status == 0 && w * 32 < st->n) ? sm.smask[i] : 0u;
     }
 }
 

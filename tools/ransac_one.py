@@ -1,0 +1,31 @@
+"""Run lslam_ransac_lines a few times on one configuration (for ncu captures).
+usage: ransac_one.py <c2|c3> [tpt slots threads] [B]"""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from lidar_slam_b200 import batch  # noqa: E402
+
+cfg = sys.argv[1] if len(sys.argv) > 1 else "c2"
+tpt, slots, threads = (int(v) for v in sys.argv[2:5]) if len(sys.argv) >= 5 else (0, 0, 0)
+eng = batch.Engine(0)
+eng.set_option("ransac.tpt", tpt)
+eng.set_option("ransac.slots_per_cta", slots)
+eng.set_option("ransac.threads", threads)
+if cfg == "c2":
+    B = int(sys.argv[5]) if len(sys.argv) > 5 else 262144
+    xy = eng.synth_scans(B, seed=1)
+    kw = {}
+else:
+    B = int(sys.argv[5]) if len(sys.argv) > 5 else 256
+    xy = eng.synth_scans(B, beams=8192, seed=2)
+    kw = {"chunk": 410, "trials": 1024}
+out = eng.alloc_ransac_out(B, xy.shape[1], kw.get("chunk", 100))
+for _ in range(3):
+    eng.ransac_lines(xy, out=out, **kw)
+torch.cuda.synchronize()
+e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+e0.record(); eng.ransac_lines(xy, out=out, **kw); e1.record(); torch.cuda.synchronize()
+print(cfg, tpt, slots, threads, B, "ms", e0.elapsed_time(e1), eng.ransac_counters())

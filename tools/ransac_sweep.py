@@ -34,10 +34,8 @@ def main():
     rows = []
     combos = [(0, 0, 0)]
     for tpt in (1, 2, 4):
-        for slots in (4, 8, 16, 32):
-            for threads in (256, 512, 768):
-                if tpt == 4 and threads > 512:
-                    continue
+        for slots in (8, 16, 32, 64):
+            for threads in (256, 384, 512):
                 combos.append((tpt, slots, threads))
     for tpt, slots, threads in combos:
         eng.set_option("ransac.tpt", tpt)
@@ -61,7 +59,7 @@ def main():
     xy3 = eng.synth_scans(B3, beams=8192, seed=2)
     out3 = eng.alloc_ransac_out(B3, 8192, 410)
     rows3 = []
-    for tpt, slots, threads in ((0, 0, 0), (4, 1, 256), (4, 2, 512), (2, 1, 512), (2, 1, 256), (1, 1, 512), (1, 1, 768)):
+    for tpt, slots, threads in ((0, 0, 0), (4, 1, 256), (4, 2, 512), (2, 1, 512), (2, 1, 256), (2, 2, 512), (2, 4, 512), (1, 1, 512), (1, 2, 512)):
         eng.set_option("ransac.tpt", tpt)
         eng.set_option("ransac.slots_per_cta", slots)
         eng.set_option("ransac.threads", threads)
