@@ -95,6 +95,40 @@ int lslam_ransac_lines(void *handle, const double *xy, const int32_t *npts, int3
  * The counters are reset by this call. */
 int lslam_ransac_counters(void *handle, int64_t counters_h[3], void *stream);
 
+/* ---- landmark data association ---------------------------------------------------------
+ * Replaces the association loop of landmark_extraction (ransac_functions.py:34-54) with
+ * Landmark.is_equal / decrease_life / reset_life (landmarking.py:48-77), plus what its caller
+ * check_ransac does with the result (ransac_functions.py:74-78): append the new landmark on a
+ * miss, advance the extraction counter on every extraction.  T independent streams, each with
+ * its own landmark table; the Q queries of a stream are applied IN ORDER (the list they are
+ * matched against changes as they go).
+ *
+ *   query    [T,Q,qstride] doubles; layout 0: a, b, pos_x, pos_y, end_x, end_y (qstride >= 6)
+ *            layout 1: a `line` record of lslam_ransac_lines (qstride >= 8; pos = origin,
+ *            end = tip, exactly the arguments of Landmark(...) at ransac_functions.py:31)
+ *   q_valid  [T,Q] a query is applied iff q_valid > 0 (ninl of lslam_ransac_lines fits), or NULL
+ *   table    [T,M,6] in/out, rows a, b, pos_x, pos_y, end_x, end_y in list order
+ *   life, ids [T,M] in/out; count [T] in/out live rows; next_id [T] in/out extraction counter
+ *   tolA, tolB, tol, life_init   TOLERANCE_A, TOLERANCE_B, TOLERANCE, LIFE (landmarking.py:3-6)
+ *   mode     0 first match in list order, reference-exact: a landmark whose life reaches 0 is
+ *              removed and the element that slides into its slot is skipped (the reference's
+ *              remove-while-indexing behaviour)
+ *            1 first match, every element visited
+ *            2 nearest gated landmark (smallest of the two gate distances); all others age
+ *   append   non-zero: a miss appends the query as a new landmark (id = next_id at the time)
+ * outputs
+ *   match    [T,Q] row index of the hit in the table as it is after this query's removals;
+ *            -1 miss (appended if `append`), -3 miss and table full, -2 query not applied
+ *   match_id [T,Q] id of the matched landmark, or the id given to the new one, -1 if not applied
+ *   proj_ab  [T,Q,2] or NULL: the (a, b) the reference projects the inliers with
+ *            (ransac_functions.py:46 on a hit: the STORED landmark's; :49,53 on a miss: the new)
+ */
+int lslam_associate(void *handle, const double *query, int32_t qstride, int32_t layout,
+                    const int32_t *q_valid, int32_t T, int32_t Q, int32_t M, double *table,
+                    int32_t *life, int32_t *ids, int32_t *count, int32_t *next_id, double tolA,
+                    double tolB, double tol, int32_t life_init, int32_t mode, int32_t append,
+                    int32_t *match, int32_t *match_id, double *proj_ab, void *stream);
+
 /* ---- synthetic scans (headless replacement for the capture process) ----------------
  * Device twin of lidar_slam_b200/synth.py random_room_scans(): scan s (global index
  * scan_base+s) is a `beams`-beam revolution in a random rectangular room, range noise

@@ -38,6 +38,8 @@ SIGNATURES = {
     "lslam_ransac_lines": (ctypes.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _f64, _u64, _u64,
                                           _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "lslam_ransac_counters": (ctypes.c_int, [_vp, ctypes.POINTER(_i64), _vp]),
+    "lslam_associate": (ctypes.c_int, [_vp, _vp, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp,
+                                       _f64, _f64, _f64, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "lslam_synth_scans": (ctypes.c_int, [_vp, _vp, _i32, _i32, _u64, _u64, _f64, _f64, _vp]),
     "lslam_fp64_peak": (ctypes.c_int, [_vp, _f64, ctypes.POINTER(_f64)]),
 }
@@ -115,6 +117,13 @@ class Handle:
         out = (_i64 * 3)()
         self._check(self.cdll.lslam_ransac_counters(self._h, out, stream))
         return {"literal_rescored": int(out[0]), "extra_candidates": int(out[1]), "faults": int(out[2])}
+
+    def associate(self, query, qstride, layout, q_valid, T, Q, M, table, life, ids, count, next_id,
+                  tolA, tolB, tol, life_init, mode, append, match, match_id, proj_ab, stream=0):
+        self._check(self.cdll.lslam_associate(
+            self._h, query, qstride, layout, q_valid, T, Q, M, table, life, ids, count, next_id,
+            float(tolA), float(tolB), float(tol), int(life_init), int(mode), int(bool(append)),
+            match, match_id, proj_ab, stream))
 
     def synth_scans(self, xy, B, beams, seed, scan_base, noise_mm, dropout, stream=0):
         self._check(self.cdll.lslam_synth_scans(self._h, xy, B, beams, int(seed) & (2**64 - 1),

@@ -1,0 +1,231 @@
+// assoc.cuh - K3: landmark data association, one warp per landmark table (stream).
+//
+// Replaces the association loop of landmark_extraction (/root/reference/ransac_functions.py:34-54,
+// is_equal from landmarking.py:66-77) plus the caller-side append and extraction counter of
+// check_ransac (ransac_functions.py:74-78).  Semantics = oracle/assoc.py.
+//
+// The stored landmarks of a table are tested against the query by the lanes of the warp (32 per
+// tile, table staged in shared memory); the reference's SEQUENTIAL side effects - every landmark
+// visited before the hit loses a life, an expired one is removed, and the element that slides
+// into a removed slot is skipped (mode 0, the reference's bug) - are then resolved on the ballot
+// masks with a handful of integer ops per event, so the walk costs O(events), not O(M).
+#pragma once
+#include "lslam_core.cuh"
+
+namespace lslam {
+
+struct AssocArgs {
+    const double *query;       // [T, Q, qstride]
+    const int32_t *q_valid;    // [T, Q] or null
+    int qstride, layout;       // layout 0: a,b,px,py,ex,ey ; 1: ransac line record (a,b,ox,oy,dx,dy,tipx,tipy)
+    int T, Q, M;
+    double *table;             // [T, M, 6]
+    int32_t *life, *ids;       // [T, M]
+    int32_t *count, *next_id;  // [T]
+    double tolA, tolB, tol;
+    int life_init, mode, append;
+    int32_t *match, *match_id; // [T, Q]
+    double *proj_ab;           // [T, Q, 2] or null
+};
+
+constexpr int kLifeRemoved = -1;
+
+__host__ __device__ inline size_t assoc_smem_per_warp(int M) { return (size_t)M * (6 * 8 + 2 * 4); }
+
+// ||(vx, vy)|| with the rounding pinned in oracle/assoc.py: sqrt(fma(vy, vy, vx*vx))
+__device__ __forceinline__ double norm2_pinned(double vx, double vy)
+{
+    return __dsqrt_rn(__fma_rn(vy, vy, __dmul_rn(vx, vx)));
+}
+
+// landmarking.py:66-77, self = stored entry e[6], other = query q[6]; also returns the smaller
+// of the two gate distances (used by the nearest mode)
+__device__ __forceinline__ bool landmark_is_equal(const double *e, const double *q, double tolA, double tolB,
+                                                  double tol, double &dmin)
+{
+    const double distA = fabs(__dsub_rn(e[0], q[0]));
+    const double distB = fabs(__dsub_rn(e[1], q[1]));
+    const double dEO = norm2_pinned(__dsub_rn(e[4], q[2]), __dsub_rn(e[5], q[3]));   // end_s - pos_q
+    const double dOE = norm2_pinned(__dsub_rn(e[2], q[4]), __dsub_rn(e[3], q[5]));   // pos_s - end_q
+    dmin = dEO < dOE ? dEO : dOE;
+    return distA <= tolA && distB <= tolB && (dEO <= tol || dOE <= tol);
+}
+
+__global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
+{
+    LSLAM_SMEM_DECL;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const int t = blockIdx.x * nwarps + warp;
+    if (t >= a.T) return;                       // whole warp leaves together
+    const int M = a.M;
+    unsigned char *base = smem_raw + (size_t)warp * ((assoc_smem_per_warp(M) + 15) & ~(size_t)15);
+    double *ent = reinterpret_cast<double *>(base);                 // [M][6]
+    int *life = reinterpret_cast<int *>(ent + (size_t)M * 6);       // [M]
+    int *ids = life + M;                                            // [M]
+
+    int cnt = a.count[t];
+    cnt = cnt < 0 ? 0 : (cnt > M ? M : cnt);
+    int next_id = a.next_id[t];
+    {
+        const double *src = a.table + (size_t)t * M * 6;
+        for (int k = lane; k < cnt * 6; k += 32) ent[k] = src[k];
+        for (int k = lane; k < cnt; k += 32) { life[k] = a.life[(size_t)t * M + k]; ids[k] = a.ids[(size_t)t * M + k]; }
+    }
+    __syncwarp();
+
+    for (int qi = 0; qi < a.Q; ++qi) {
+        const size_t qo = (size_t)t * a.Q + qi;
+        if (a.q_valid != nullptr && a.q_valid[qo] <= 0) {
+            if (lane == 0) {
+                a.match[qo] = -2; a.match_id[qo] = -1;
+                if (a.proj_ab) { a.proj_ab[2 * qo] = __longlong_as_double(0x7ff8000000000000LL); a.proj_ab[2 * qo + 1] = a.proj_ab[2 * qo]; }
+            }
+            continue;
+        }
+        const double *qs = a.query + qo * a.qstride;
+        double q[6];
+        q[0] = qs[0]; q[1] = qs[1]; q[2] = qs[2]; q[3] = qs[3];
+        q[4] = a.layout ? qs[6] : qs[4];
+        q[5] = a.layout ? qs[7] : qs[5];
+        const int qid = next_id++;
+
+        int hit = -1, removed = 0;
+        if (a.mode != 2) {
+            // ---- first match in list order with the reference's side effects ----
+            int p = 0;
+            for (int tb = 0; tb < cnt && hit < 0; tb += 32) {
+                const int m = tb + lane;
+                const bool in = m < cnt;
+                double dmin;
+                const bool eq = in && landmark_is_equal(ent + (size_t)m * 6, q, a.tolA, a.tolB, a.tol, dmin);
+                const int lf = in ? life[m] : 0;
+                const bool die = in && !eq && lf <= 1;           // decrease_life() would return True
+                const unsigned eqm = __ballot_sync(LSLAM_FULL_MASK, eq);
+                const unsigned diem = __ballot_sync(LSLAM_FULL_MASK, die);
+                const int tend = cnt - tb < 32 ? cnt - tb : 32;  // valid positions in this tile
+                unsigned vis = 0, rem = 0;
+                while (p < tb + tend) {
+                    const int pp = p - tb;
+                    const unsigned ev = (eqm | diem) >> pp;
+                    const unsigned upto_end = (tend == 32 ? 0xffffffffu : ((1u << tend) - 1u)) & ~((1u << pp) - 1u);
+                    if (ev == 0) { vis |= upto_end; p = tb + tend; break; }
+                    const int pe = pp + __ffs((int)ev) - 1;
+                    vis |= upto_end & ((1u << pe) - 1u);         // [pp, pe) visited, no event
+                    if ((eqm >> pe) & 1u) { hit = tb + pe; break; }
+                    vis |= 1u << pe;
+                    rem |= 1u << pe;
+                    p = tb + pe + (a.mode == 0 ? 2 : 1);         // mode 0: the slot after a removal is skipped
+                }
+                if (in && ((vis >> lane) & 1u)) life[m] = ((rem >> lane) & 1u) ? kLifeRemoved : (lf > 0 ? lf - 1 : 0);
+                removed += __popc(rem);
+            }
+        } else {
+            // ---- nearest gated landmark; every other landmark counts as "not seen" ----
+            double best = __longlong_as_double(0x7ff0000000000000LL);
+            for (int tb = 0; tb < cnt; tb += 32) {
+                const int m = tb + lane;
+                double dmin = best;
+                const bool eq = m < cnt && landmark_is_equal(ent + (size_t)m * 6, q, a.tolA, a.tolB, a.tol, dmin);
+                double cand = eq ? dmin : __longlong_as_double(0x7ff0000000000000LL);
+                int ci = eq ? m : 0x7fffffff;
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) {
+                    const double od = __shfl_xor_sync(LSLAM_FULL_MASK, cand, o);
+                    const int oi = __shfl_xor_sync(LSLAM_FULL_MASK, ci, o);
+                    if (od < cand || (od == cand && oi < ci)) { cand = od; ci = oi; }
+                }
+                if (ci != 0x7fffffff && cand < best) { best = cand; hit = ci; }
+            }
+            for (int tb = 0; tb < cnt; tb += 32) {
+                const int m = tb + lane;
+                bool rm = false;
+                if (m < cnt && m != hit) {
+                    const int lf = life[m];
+                    rm = lf <= 1;
+                    life[m] = rm ? kLifeRemoved : lf - 1;
+                }
+                removed += __popc(__ballot_sync(LSLAM_FULL_MASK, rm));
+            }
+        }
+        __syncwarp();
+        int hit_new = -1, hit_id = -1;
+        double pa = q[0], pb = q[1];
+        if (hit >= 0) {
+            if (lane == 0) life[hit] = a.life_init;              // reset_life(); a, b, pos, end NOT updated
+            // removals all precede the hit in first-match modes; count them for the nearest mode
+            int before = removed;
+            if (a.mode == 2) {
+                before = 0;
+                for (int tb = 0; tb < hit; tb += 32) {
+                    const int m = tb + lane;
+                    before += __popc(__ballot_sync(LSLAM_FULL_MASK, m < hit && life[m] == kLifeRemoved));
+                }
+            }
+            hit_new = hit - before;
+            hit_id = ids[hit];
+            pa = ent[(size_t)hit * 6];
+            pb = ent[(size_t)hit * 6 + 1];
+        }
+        __syncwarp();
+        // ---- stable compaction of the removed landmarks (list.remove shifts the tail left) ----
+        if (removed > 0) {
+            int outp = 0;
+            for (int tb = 0; tb < cnt; tb += 32) {
+                const int m = tb + lane;
+                const bool keep = m < cnt && life[m] != kLifeRemoved;
+                double e6[6];
+                int lf = 0, id = 0;
+                if (keep) {
+#pragma unroll
+                    for (int k = 0; k < 6; ++k) e6[k] = ent[(size_t)m * 6 + k];
+                    lf = life[m]; id = ids[m];
+                }
+                const unsigned km = __ballot_sync(LSLAM_FULL_MASK, keep);
+                __syncwarp();
+                if (keep) {
+                    const int d = outp + __popc(km & ((1u << lane) - 1u));
+#pragma unroll
+                    for (int k = 0; k < 6; ++k) ent[(size_t)d * 6 + k] = e6[k];
+                    life[d] = lf; ids[d] = id;
+                }
+                outp += __popc(km);
+                __syncwarp();
+            }
+            cnt = outp;
+        }
+        int result = hit_new, rid = hit_id;
+        if (hit < 0) {
+            rid = qid;
+            if (a.append && cnt < M) {
+                if (lane == 0) {
+#pragma unroll
+                    for (int k = 0; k < 6; ++k) ent[(size_t)cnt * 6 + k] = q[k];
+                    life[cnt] = a.life_init;
+                    ids[cnt] = qid;
+                }
+                ++cnt;
+                result = -1;
+            } else {
+                result = a.append ? -3 : -1;
+            }
+        }
+        __syncwarp();
+        if (lane == 0) {
+            a.match[qo] = result;
+            a.match_id[qo] = rid;
+            if (a.proj_ab) { a.proj_ab[2 * qo] = pa; a.proj_ab[2 * qo + 1] = pb; }
+        }
+    }
+    // ---- write the table back; slots past the live count are zeroed ----
+    {
+        double *dst = a.table + (size_t)t * M * 6;
+        for (int k = lane; k < M * 6; k += 32) dst[k] = k < cnt * 6 ? ent[k] : 0.0;
+        for (int k = lane; k < M; k += 32) {
+            a.life[(size_t)t * M + k] = k < cnt ? life[k] : 0;
+            a.ids[(size_t)t * M + k] = k < cnt ? ids[k] : 0;
+        }
+        if (lane == 0) { a.count[t] = cnt; a.next_id[t] = next_id; }
+    }
+}
+
+} // namespace lslam

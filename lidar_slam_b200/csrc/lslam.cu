@@ -5,6 +5,7 @@
 #include "lslam_common.cuh"
 #include "ransac.cuh"
 #include "aux_kernels.cuh"
+#include "assoc.cuh"
 
 #include "../../include/lslam.h"
 
@@ -94,7 +95,7 @@ static int launch_ransac(Handle *h, RansacArgs a, int threads_target, cudaStream
         threads = (int)((items + rounds - 1) / rounds);
         threads = (threads + 31) & ~31;
         if (threads > MAXT) threads = MAXT & ~31;
-        if (threads < 4 * G) threads = (4 * G + 31) & ~31 > MAXT ? MAXT & ~31 : (4 * G + 31) & ~31;
+        if (threads < 4 * G) threads = ((4 * G + 31) & ~31) > MAXT ? (MAXT & ~31) : ((4 * G + 31) & ~31);
         smem = ransac_smem_bytes(G, a.chunk, a.trials, a.W, threads / 32);
         if (smem <= (size_t)h->smem_optin || G == 1) break;
     }
@@ -159,6 +160,42 @@ extern "C" int lslam_ransac_counters(void *handle, int64_t counters_h[3], void *
     LSLAM_CUDA_TRY(h, cudaMemsetAsync(h->counters_d, 0, sizeof tmp, st));
     LSLAM_CUDA_TRY(h, cudaStreamSynchronize(st));
     for (int k = 0; k < 3; ++k) counters_h[k] = (int64_t)tmp[k];
+    return LSLAM_OK;
+}
+
+// ---- association --------------------------------------------------------------------------
+extern "C" int lslam_associate(void *handle, const double *query, int32_t qstride, int32_t layout,
+                               const int32_t *q_valid, int32_t T, int32_t Q, int32_t M, double *table,
+                               int32_t *life, int32_t *ids, int32_t *count, int32_t *next_id, double tolA,
+                               double tolB, double tol, int32_t life_init, int32_t mode, int32_t append,
+                               int32_t *match, int32_t *match_id, double *proj_ab, void *stream)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr) return LSLAM_ERR_BAD_ARG;
+    if (!query || !table || !life || !ids || !count || !next_id || !match || !match_id)
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_associate: null buffer");
+    if (T < 0 || Q < 0 || M < 1 || mode < 0 || mode > 2 || layout < 0 || layout > 1 ||
+        qstride < (layout ? 8 : 6) || life_init < 1)
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_associate: bad sizes / mode / layout");
+    if (T == 0 || Q == 0) return LSLAM_OK;
+    DeviceGuard g(h->device);
+    const size_t per_warp = (assoc_smem_per_warp(M) + 15) & ~(size_t)15;
+    int nwarps = (int)((size_t)h->smem_optin / per_warp);
+    if (nwarps < 1) return fail(h, LSLAM_ERR_CAPACITY, "lslam_associate: table capacity M=%d does not fit shared memory", M);
+    if (nwarps > 8) nwarps = 8;
+    AssocArgs a;
+    a.query = query; a.q_valid = q_valid; a.qstride = qstride; a.layout = layout;
+    a.T = T; a.Q = Q; a.M = M;
+    a.table = table; a.life = life; a.ids = ids; a.count = count; a.next_id = next_id;
+    a.tolA = tolA; a.tolB = tolB; a.tol = tol; a.life_init = life_init; a.mode = mode; a.append = append;
+    a.match = match; a.match_id = match_id; a.proj_ab = proj_ab;
+    auto kern = associate_kernel;
+    const size_t smem = per_warp * nwarps;
+    LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned grid = (unsigned)((T + nwarps - 1) / nwarps);
+    LSLAM_LAUNCH(kern, grid, (unsigned)(nwarps * 32), smem, (cudaStream_t)stream, a);
+    h->launches++;
+    LSLAM_CUDA_TRY(h, cudaGetLastError());
     return LSLAM_OK;
 }
 

@@ -64,3 +64,22 @@ def emu_ransac_lines(xy, npts=None, chunk=100, trials=100, thr=20.0, seed=0, sca
                    ptr(out["line"]), ptr(out["ninl"]), ptr(out["win_trial"]), ptr(out["win_pair"]),
                    ptr(out["ssum"]), ptr(out["inl_mask"]))
     return out
+
+
+def emu_associate(queries, tables, q_valid=None, mode=0, append=True, layout=0, handle=None,
+                  tolA=0.1, tolB=10, tol=100, life_init=40):
+    """lslam_associate on the emulated library.  queries [T,Q,6|8]; tables = dict with rows
+    [T,M,6], life [T,M], ids [T,M], count [T], next_id [T] (updated in place)."""
+    h = handle or emu_handle()
+    queries = np.ascontiguousarray(queries, dtype=np.float64)
+    T, Q, qs = queries.shape
+    M = tables["rows"].shape[1]
+    match = np.full((T, Q), -99, np.int32)
+    match_id = np.full((T, Q), -99, np.int32)
+    proj = np.full((T, Q, 2), -7.0)
+    if q_valid is not None:
+        q_valid = np.ascontiguousarray(q_valid, dtype=np.int32)
+    h.associate(ptr(queries), qs, layout, ptr(q_valid), T, Q, M, ptr(tables["rows"]), ptr(tables["life"]),
+                ptr(tables["ids"]), ptr(tables["count"]), ptr(tables["next_id"]), tolA, tolB, tol,
+                life_init, mode, append, ptr(match), ptr(match_id), ptr(proj))
+    return match, match_id, proj
