@@ -1,0 +1,308 @@
+#!/usr/bin/env python
+"""bench.py - the headline benchmark (contract: see DESIGN.md "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--scans S] [--impl ours|reference]
+
+Workload (BASELINE.json configs[4], per GPU): S = 1,048,576 synthetic 360-beam scans per
+step, generated on the device, each through RANSAC line extraction (4 chunks x 100 trials) ->
+landmark association (4 queries against the stream's 8-slot table) -> UKF predict/update.
+One process per GPU; scans shard by index (scan_base = rank * S), no data-path collective;
+the per-rank results are gathered over NCCL at the end of each step (N > 1).
+
+Prints ONE JSON line (rank 0).  `value` = scans/s, whole job, inputs resident in HBM;
+`e2e` = the same through the host-buffer API (pinned host scans in, host results out, copies
+inside the timed region); `roofline` = the RANSAC kernel against the measured fp64 issue rate
+of this GPU and its HBM traffic against MEASURED_PEAKS.json; `cpu_baseline` = the C oracle
+(all host threads) on a bounded sample, on rank 0 at N = 1.
+
+--impl reference times the CPU restatement of the reference path (oracle/, all host threads)
+on a bounded sample of the same workload (the reference itself is pure Python on top of
+skimage/filterpy, neither installable here: DESIGN.md "Reference arm").
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+BEAMS, CHUNK, TRIALS, THR, TABLE_M = 360, 100, 100, 20.0, 8
+PHE_PER_SCAN = BEAMS * TRIALS                      # point-hypothesis evaluations per scan
+FLOP_PER_PHE = 8                                   # algorithmic fp64 flop per PHE
+BYTES_PER_SCAN = BEAMS * 16 + 4 * 96               # 5,760 in + 4 x 96 out = 6,144 B
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--scans", type=int, default=1 << 20, help="scans per GPU per step")
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--cpu-sample", type=int, default=0, help="scans in the CPU sample (0 = auto)")
+    p.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    p.add_argument("--no-e2e", action="store_true")
+    return p.parse_args()
+
+
+# ---- clocks under load ----------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+    NAMES = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.rows, self.thread = index, None, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), line.strip()))
+
+    def stop(self, t0=None, t1=None):
+        if self.proc is None:
+            return None
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        for ts, line in self.rows:
+            if t0 is not None and not (t0 <= ts <= t1 + 0.1):
+                continue
+            f = [v.strip() for v in line.split(",")]
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+                pw.append(float(f[2]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(self.NAMES, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return None
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "power_w_max": max(pw),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---- CPU legs (the only place bench.py touches oracle/) -----------------------------------------
+def cpu_pipeline_rate(nscans, seed=0):
+    """Scans/s of the CPU restatement (C oracle, OpenMP over scans, all host threads) of the same
+    pipeline on `nscans` synthetic scans.  Returns (scans_per_s, threads, seconds)."""
+    import numpy as np
+    from lidar_slam_b200 import synth
+    from oracle import cport
+    xy = synth.random_room_scans(nscans, seed=seed)
+    threads = cport.max_threads()
+    cport.ransac_lines(xy[:64])                                   # warm-up (library load, page faults)
+    best = None
+    for _ in range(2):
+        t0 = time.perf_counter()
+        cport.pipeline(xy) if hasattr(cport, "pipeline") else cport.ransac_lines(xy)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return nscans / best, threads, best
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    n = args.cpu_sample or 16384
+    rates = []
+    for _ in range(args.warmup):
+        cpu_pipeline_rate(min(n, 2048))
+    t_all = time.perf_counter()
+    threads = 1
+    for _ in range(args.steps):
+        r, threads, _ = cpu_pipeline_rate(n)
+        rates.append(r)
+    dt = time.perf_counter() - t_all
+    value = statistics.median(rates)
+    sample = "%d scans per step (bounded sample of the %d-scan step), C oracle with OpenMP" % (n, args.scans)
+    line = {
+        "impl": "reference", "metric": "scans/s (RANSAC+assoc+UKF)", "value": value, "unit": "scans/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, world),
+        "cpu_baseline": {"value": value, "unit": "scans/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "scans/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, world):
+    return {"workload": "BASELINE.json configs[4]: 1M synthetic 360-beam scans end-to-end "
+                        "(RANSAC 4 chunks x 100 trials + association M=8 + UKF n=3) per GPU",
+            "scans_per_gpu_per_step": args.scans, "beams": BEAMS, "chunk": CHUNK, "trials": TRIALS,
+            "threshold_mm": THR, "table_capacity": TABLE_M, "sharding": "scans by index, %d rank(s)" % world,
+            "l2": "inputs (%.2f GB per step) exceed the 126 MB L2" % (args.scans * BEAMS * 16 / 1e9)}
+
+
+# ---- our arm ---------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from lidar_slam_b200 import batch, pipeline
+
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    eng = batch.Engine(local)
+    S = args.scans
+    pipe = pipeline.ScanPipeline(eng, S, beams=BEAMS, chunk=CHUNK, trials=TRIALS, thr=THR,
+                                 table_capacity=TABLE_M, seed=0, scan_base=rank * S)
+    xy = eng.synth_scans(S, beams=BEAMS, seed=0, scan_base=rank * S)       # resident in HBM
+    gather_buf = None
+
+    def gather(res):
+        """N > 1: all ranks' per-scan UKF/landmark results over NCCL (NVLink), one collective."""
+        nonlocal gather_buf
+        if world == 1:
+            return
+        src = res["x"] if "x" in res else res["match_id"]
+        if gather_buf is None:
+            gather_buf = torch.empty((world,) + tuple(src.shape), dtype=src.dtype, device=src.device)
+        dist.all_gather_into_tensor(gather_buf, src)
+
+    def one_step():
+        res = pipe.step(xy)
+        gather(res)
+        return res
+
+    fp64_peak = eng.fp64_peak(40.0) if rank == 0 else 0.0                   # TFLOP/s, dependent DFMA chains
+    for _ in range(max(args.warmup, 3)):
+        one_step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    n0 = eng.launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    t0 = time.perf_counter()
+    ev[0].record()
+    for k in range(args.steps):
+        # the dominant kernel (lslam_ransac_lines) is bracketed by its own events on the same stream
+        res = pipe.step(xy, ransac_events=kev[k])
+        gather(res)
+    ev[1].record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    launches = eng.launch_count() - n0
+    ms = ev[0].elapsed_time(ev[1])
+    k_ms = statistics.mean(a_.elapsed_time(b_) for a_, b_ in kev)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+    faults = eng.ransac_counters()["faults"]
+
+    # ---- end to end through the host-buffer API --------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        xy_h = pipe.alloc_host_io()
+        xy_h.copy_(xy)                                                       # untimed: fill the host buffer
+        torch.cuda.synchronize()
+        for _ in range(2):
+            pipe.step_host(xy_h)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            out_h = pipe.step_host(xy_h)
+            torch.cuda.current_stream().synchronize()                        # results are on the host
+            _ = float(out_h["ninl"][0, 0])
+        e1.record()
+        torch.cuda.synchronize()
+        ems = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ems], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ems = float(t.item())
+        h2d, d2h = pipe.io_bytes()
+        e2e = {"value": world * S * args.steps / (ems * 1e-3), "unit": "scans/s",
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ems / args.steps}
+
+    if rank == 0:
+        value = world * S * args.steps / (ms * 1e-3)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        ach_tflops = S * PHE_PER_SCAN * FLOP_PER_PHE / (k_ms * 1e-3) * 1e-12
+        roofline = {
+            "kernel": "ransac_lines_kernel", "bound": "fp64-issue", "achieved": ach_tflops, "peak": fp64_peak,
+            "unit": "TFLOP/s", "frac": ach_tflops / fp64_peak if fp64_peak > 0 else None, "traffic": None,
+            "peak_source": "measured in this run: lslam_fp64_peak (dependent DFMA chains, 2 flop each)",
+            "kernel_ms": k_ms, "hyps_per_s": S * 4 * TRIALS / (k_ms * 1e-3),
+            "hbm": {"achieved": S * BYTES_PER_SCAN / (k_ms * 1e-3) * 1e-9, "peak": hbm_peak, "unit": "GB/s",
+                    "frac": S * BYTES_PER_SCAN / (k_ms * 1e-3) * 1e-9 / hbm_peak,
+                    "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+        }
+        cpu = None
+        if world == 1 and not args.no_cpu:
+            n = args.cpu_sample or 16384
+            rate, threads, secs = cpu_pipeline_rate(n)
+            cpu = {"value": rate, "unit": "scans/s", "cores": threads, "kind": "port",
+                   "sample": "%d of the %d scans of one step, C oracle (OpenMP), %.1f s" % (n, S, secs)}
+        line = {
+            "metric": "scans/s (RANSAC+assoc+UKF)", "value": value, "unit": "scans/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": workload_config(args, world),
+            "stages": ["ransac", "associate"] + (["ukf"] if pipe.ukf is not None else []),
+            "ransac_hyps_per_s": world * S * 4 * TRIALS * args.steps / (ms * 1e-3),
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
+            "clocks": clocks, "parity_faults": faults,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

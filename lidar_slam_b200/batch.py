@@ -104,6 +104,66 @@ class Engine:
     def ransac_counters(self):
         return self.handle.ransac_counters(self._stream())
 
+    # landmarking.py:3-6
+    LIFE = 40
+    TOLERANCE_A = 0.1
+    TOLERANCE_B = 10
+    TOLERANCE = 100
+
+    def alloc_tables(self, T, M):
+        """Empty landmark tables for T independent streams, capacity M each (lslam_associate)."""
+        dev = self.device
+        return {
+            "rows": torch.zeros((T, M, 6), dtype=torch.float64, device=dev),
+            "life": torch.zeros((T, M), dtype=torch.int32, device=dev),
+            "ids": torch.zeros((T, M), dtype=torch.int32, device=dev),
+            "count": torch.zeros((T,), dtype=torch.int32, device=dev),
+            "next_id": torch.zeros((T,), dtype=torch.int32, device=dev),
+        }
+
+    def alloc_assoc_out(self, T, Q):
+        dev = self.device
+        return {
+            "match": torch.empty((T, Q), dtype=torch.int32, device=dev),
+            "match_id": torch.empty((T, Q), dtype=torch.int32, device=dev),
+            "proj_ab": torch.empty((T, Q, 2), dtype=torch.float64, device=dev),
+        }
+
+    def associate(self, query, tables, q_valid=None, mode=0, append=True, tolA=TOLERANCE_A,
+                  tolB=TOLERANCE_B, tol=TOLERANCE, life_init=LIFE, out=None):
+        """Batched data association (ransac_functions.py:34-54 + :74-78, landmarking.py:48-77).
+
+        query [T, Q, 6] (a, b, pos, end) or [T, Q, 8] (``line`` records of ransac_lines);
+        tables = dict from alloc_tables, updated IN PLACE; q_valid [T, Q] int32 or None (e.g.
+        ``ninl`` of ransac_lines).  Returns dict match / match_id / proj_ab (include/lslam.h).
+        """
+        query = self._check(query, torch.float64, "query")
+        if query.dim() != 3 or query.shape[2] not in (6, 8):
+            raise ValueError("query must be [T, Q, 6] or [T, Q, 8]")
+        T, Q, qs = (int(v) for v in query.shape)
+        rows = self._check(tables["rows"], torch.float64, "tables['rows']")
+        if rows.dim() != 3 or rows.shape[0] != T or rows.shape[2] != 6:
+            raise ValueError("tables['rows'] must be [T, M, 6]")
+        M = int(rows.shape[1])
+        life = self._check(tables["life"], torch.int32, "tables['life']")
+        ids = self._check(tables["ids"], torch.int32, "tables['ids']")
+        count = self._check(tables["count"], torch.int32, "tables['count']")
+        next_id = self._check(tables["next_id"], torch.int32, "tables['next_id']")
+        if life.shape != (T, M) or ids.shape != (T, M) or count.numel() != T or next_id.numel() != T:
+            raise ValueError("table field shapes do not match [T, M]")
+        if q_valid is not None:
+            q_valid = self._check(q_valid, torch.int32, "q_valid")
+            if q_valid.numel() != T * Q:
+                raise ValueError("q_valid must be [T, Q]")
+        if out is None:
+            out = self.alloc_assoc_out(T, Q)
+        self.handle.associate(
+            query.data_ptr(), qs, 1 if qs == 8 else 0, q_valid.data_ptr() if q_valid is not None else None,
+            T, Q, M, rows.data_ptr(), life.data_ptr(), ids.data_ptr(), count.data_ptr(), next_id.data_ptr(),
+            tolA, tolB, tol, life_init, mode, append, out["match"].data_ptr(), out["match_id"].data_ptr(),
+            out["proj_ab"].data_ptr(), self._stream())
+        return out
+
     def synth_scans(self, B, beams=360, seed=0, scan_base=0, noise_mm=5.0, dropout=0.02, out=None):
         """Random-room scans generated on the device (csrc/aux_kernels.cuh) -> xy[B, beams, 2]."""
         if out is None:
