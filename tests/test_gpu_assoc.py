@@ -61,10 +61,12 @@ def test_large_batch_properties(gpu_engine):
     eng = gpu_engine
     T, Q, M = 100000, 8, 8
     g = torch.Generator(device="cpu").manual_seed(1)
-    base = torch.randn((T, 1, 6), generator=g, dtype=torch.float64)
-    q = (base * torch.tensor([0.5, 500, 500, 500, 500, 500], dtype=torch.float64)
-         + torch.randn((T, Q, 6), generator=g, dtype=torch.float64) * torch.tensor([0.03, 3, 30, 30, 30, 30],
-                                                                                  dtype=torch.float64)).to(eng.device)
+    sc = torch.tensor([0.5, 500, 500, 500], dtype=torch.float64)
+    base = torch.randn((T, 1, 4), generator=g, dtype=torch.float64) * sc
+    ab_pos = base + torch.randn((T, Q, 4), generator=g, dtype=torch.float64) * torch.tensor(
+        [0.03, 3, 10, 10], dtype=torch.float64)
+    end = ab_pos[..., 2:4] + 30 * torch.randn((T, Q, 2), generator=g, dtype=torch.float64)
+    q = torch.cat([ab_pos, end], dim=-1).contiguous().to(eng.device)      # tip within the 100 mm gate
     t1, t2 = eng.alloc_tables(T, M), eng.alloc_tables(T, M)
     o1 = eng.associate(q, t1)
     o2 = eng.associate(q, t2)
