@@ -108,18 +108,24 @@ class ClockSampler:
 
 # ---- CPU legs (the only place bench.py touches oracle/) -----------------------------------------
 def cpu_pipeline_rate(nscans, seed=0):
-    """Scans/s of the CPU restatement (C oracle, OpenMP over scans, all host threads) of the same
-    pipeline on `nscans` synthetic scans.  Returns (scans_per_s, threads, seconds)."""
+    """Scans/s of the CPU restatement of the same step (oracle/: RANSAC, association and UKF in C,
+    OpenMP over scans, all host threads) on `nscans` synthetic scans with the same known-map set-up
+    as the GPU arm.  Returns (scans_per_s, threads, seconds)."""
     import numpy as np
     from lidar_slam_b200 import synth
     from oracle import cport
+    from tests import pipeline_util
     xy = synth.random_room_scans(nscans, seed=seed)
     threads = cport.max_threads()
-    cport.ransac_lines(xy[:64])                                   # warm-up (library load, page faults)
+    r0 = cport.ransac_lines(xy)                                    # untimed set-up: the known map
+    tables = pipeline_util.map_from_lines(r0["line"], r0["ninl"], TABLE_M)
+    x = np.zeros((nscans, 3))
+    P = np.tile(np.diag([0.1, 0.1, 0.05]), (nscans, 1, 1))
+    u = np.ones((nscans, 2))
     best = None
     for _ in range(2):
         t0 = time.perf_counter()
-        cport.pipeline(xy) if hasattr(cport, "pipeline") else cport.ransac_lines(xy)
+        _, _, x, P, _ = cport.pipeline_step(xy, tables, x, P, u)
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
     return nscans / best, threads, best
@@ -183,6 +189,9 @@ def main():
     pipe = pipeline.ScanPipeline(eng, S, beams=BEAMS, chunk=CHUNK, trials=TRIALS, thr=THR,
                                  table_capacity=TABLE_M, seed=0, scan_base=rank * S)
     xy = eng.synth_scans(S, beams=BEAMS, seed=0, scan_base=rank * S)       # resident in HBM
+    r0 = eng.ransac_lines(xy, chunk=CHUNK, trials=TRIALS, thr=THR, seed=0, scan_base=rank * S, out=pipe.rout)
+    pipe.install_map_from_lines(r0["line"], r0["ninl"])                     # untimed set-up: the known map
+    pipe.ukf["u"].fill_(1.0)
     gather_buf = None
 
     def gather(res):
@@ -190,10 +199,11 @@ def main():
         nonlocal gather_buf
         if world == 1:
             return
-        src = res["x"] if "x" in res else res["match_id"]
         if gather_buf is None:
-            gather_buf = torch.empty((world,) + tuple(src.shape), dtype=src.dtype, device=src.device)
-        dist.all_gather_into_tensor(gather_buf, src)
+            gather_buf = {k: torch.empty((world,) + tuple(res[k].shape), dtype=res[k].dtype, device=res[k].device)
+                          for k in ("x", "P", "match_id")}
+        for k, buf in gather_buf.items():
+            dist.all_gather_into_tensor(buf, res[k])
 
     def one_step():
         res = pipe.step(xy)
@@ -236,6 +246,8 @@ def main():
         ms = float(t.item())
     clocks = sampler.stop(t0, t1) if rank == 0 else None
     faults = eng.ransac_counters()["faults"]
+    hit_rate = float((pipe.aout["match"] >= 0).float().mean().item())
+    assert int(pipe.ukf["status"].abs().sum().item()) == 0, "UKF status flags set"
 
     # ---- end to end through the host-buffer API --------------------------------------------
     e2e = None
@@ -294,7 +306,7 @@ def main():
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": workload_config(args, world),
-            "stages": ["ransac", "associate"] + (["ukf"] if pipe.ukf is not None else []),
+            "stages": ["ransac", "associate", "ukf"], "hit_rate": hit_rate,
             "ransac_hyps_per_s": world * S * 4 * TRIALS * args.steps / (ms * 1e-3),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
             "clocks": clocks, "parity_faults": faults,

@@ -42,7 +42,7 @@ int lslam_create(int device, void **handle);
 int lslam_destroy(void *handle);
 const char *lslam_last_error(void *handle);
 /* ABI version of the loaded library (LSLAM_ABI_VERSION at build time). */
-#define LSLAM_ABI_VERSION 1
+#define LSLAM_ABI_VERSION 2
 int lslam_abi_version(void);
 /* Launch-shape tuning knobs ("ransac.tpt", "ransac.slots_per_cta", "ransac.threads");
  * 0 restores the built-in heuristic.  Results never depend on them. */
@@ -122,12 +122,61 @@ int lslam_ransac_counters(void *handle, int64_t counters_h[3], void *stream);
  *   match_id [T,Q] id of the matched landmark, or the id given to the new one, -1 if not applied
  *   proj_ab  [T,Q,2] or NULL: the (a, b) the reference projects the inliers with
  *            (ransac_functions.py:46 on a hit: the STORED landmark's; :49,53 on a miss: the new)
+ *   hit_pos  [T,Q,2] or NULL: get_pos() of the matched STORED landmark (what hx measures against,
+ *            UKFMethods.py:30); NaN on a miss
  */
 int lslam_associate(void *handle, const double *query, int32_t qstride, int32_t layout,
                     const int32_t *q_valid, int32_t T, int32_t Q, int32_t M, double *table,
                     int32_t *life, int32_t *ids, int32_t *count, int32_t *next_id, double tolA,
                     double tolB, double tol, int32_t life_init, int32_t mode, int32_t append,
-                    int32_t *match, int32_t *match_id, double *proj_ab, void *stream);
+                    int32_t *match, int32_t *match_id, double *proj_ab, double *hit_pos, void *stream);
+
+/* ---- UKF sigma-point predict / update ---------------------------------------------------
+ * Replaces filterpy's UnscentedKalmanFilter.predict(u=...) / update(z, landmarks=...) with
+ * MerweScaledSigmaPoints as systemClass.System wires them (/root/reference/systemClass.py:20-29)
+ * around the callbacks of /root/reference/UKFMethods.py:10-71 (fx = transition_function, hx =
+ * transfer_function, circular means state_mean / z_mean, angle-wrapping residual_x / residual_h),
+ * for F independent n = 3 filters (state x, y, theta).  Operation order: oracle/ukf.c.
+ *
+ *   x [F,3], P [F,3,3]   state and covariance, in/out
+ *   u [F,2]              wheel speeds (vl, vr) of the predict, NULL = zero
+ *   z [F,L,zstride]      measurement slots; zmode 0: (range, bearing) at [0],[1] of a slot
+ *                        zmode 1: a `line` record of lslam_ransac_lines - the measurement is the
+ *                        range/bearing of its inlier centroid, sqrt(ox^2+oy^2), atan2(oy, ox)
+ *   lm_pos [F,L,2]       landmark positions the slots are measured against (Landmark.get_pos(),
+ *                        UKFMethods.py:30), e.g. `hit_pos` of lslam_associate
+ *   lm_valid [F,L]       slot l is used iff lm_valid >= valid_min (NULL = all); e.g. `match` of
+ *                        lslam_associate with valid_min 0.  The used slots, in order, form
+ *                        z = [d0, b0, d1, b1, ...] (UKFMethods.py:33) and R = diag([var_dist,
+ *                        var_angle] * used) (systemClass.py:28); no used slot = no update
+ *   params_h [17] HOST   dt, wheel_r (UKFMethods.R), base_l (UKFMethods.L), alpha, beta, kappa,
+ *                        var_dist, var_angle, Q[3][3]   (systemClass.py:8-10,20,28-29)
+ *   flags                LSLAM_UKF_PREDICT | LSLAM_UKF_UPDATE | LSLAM_UKF_REDRAW (re-draw the sigma
+ *                        points from the prior at the end of predict, filterpy >= 1.4.5)
+ *   status [F] or NULL   0, or LSLAM_UKF_ST_* bits: a Cholesky factorisation met a matrix that is
+ *                        not positive definite (scipy raises LinAlgError there)
+ *   sigmas_f [F,7,3] or NULL  the propagated sigma points: written by a predict, read by an
+ *                        update-only call (NULL: re-drawn from x, P)
+ *   L <= 32.
+ */
+#define LSLAM_UKF_PREDICT 1
+#define LSLAM_UKF_UPDATE 2
+#define LSLAM_UKF_REDRAW 4
+#define LSLAM_UKF_ST_SIGMA 1  /* P not positive definite: step not applied                   */
+#define LSLAM_UKF_ST_REDRAW 2 /* prior P not positive definite: prior kept, update skipped    */
+#define LSLAM_UKF_ST_S 4      /* innovation covariance not positive definite: update skipped  */
+int lslam_ukf_step(void *handle, double *x, double *P, const double *u, const double *z, int32_t zstride,
+                   int32_t zmode, const double *lm_pos, const int32_t *lm_valid, int32_t valid_min,
+                   int32_t F, int32_t L, const double *params_h, int32_t flags, int32_t *status,
+                   double *sigmas_f, void *stream);
+/* filterpy-shaped halves of the same kernel: predict(u=u) and update(z, landmarks=...). */
+int lslam_ukf_predict(void *handle, double *x, double *P, const double *u, int32_t F,
+                      const double *params_h, int32_t redraw, int32_t *status, double *sigmas_f,
+                      void *stream);
+int lslam_ukf_update(void *handle, double *x, double *P, const double *z, int32_t zstride, int32_t zmode,
+                     const double *lm_pos, const int32_t *lm_valid, int32_t valid_min, int32_t F,
+                     int32_t L, const double *params_h, int32_t *status, const double *sigmas_f,
+                     void *stream);
 
 /* ---- synthetic scans (headless replacement for the capture process) ----------------
  * Device twin of lidar_slam_b200/synth.py random_room_scans(): scan s (global index

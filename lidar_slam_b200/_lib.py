@@ -18,7 +18,7 @@ LSLAM_ERR_NO_MODEL = -3
 LSLAM_ERR_CUDA = -4
 LSLAM_ERR_NONFINITE = -5
 LSLAM_ERR_CAPACITY = -6
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 _vp = ctypes.c_void_p
 _i32 = ctypes.c_int32
@@ -39,7 +39,12 @@ SIGNATURES = {
                                           _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "lslam_ransac_counters": (ctypes.c_int, [_vp, ctypes.POINTER(_i64), _vp]),
     "lslam_associate": (ctypes.c_int, [_vp, _vp, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp,
-                                       _f64, _f64, _f64, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
+                                       _f64, _f64, _f64, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp]),
+    "lslam_ukf_step": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32,
+                                      ctypes.POINTER(_f64), _i32, _vp, _vp, _vp]),
+    "lslam_ukf_predict": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i32, ctypes.POINTER(_f64), _i32, _vp, _vp, _vp]),
+    "lslam_ukf_update": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32,
+                                        ctypes.POINTER(_f64), _vp, _vp, _vp]),
     "lslam_synth_scans": (ctypes.c_int, [_vp, _vp, _i32, _i32, _u64, _u64, _f64, _f64, _vp]),
     "lslam_fp64_peak": (ctypes.c_int, [_vp, _f64, ctypes.POINTER(_f64)]),
 }
@@ -119,11 +124,32 @@ class Handle:
         return {"literal_rescored": int(out[0]), "extra_candidates": int(out[1]), "faults": int(out[2])}
 
     def associate(self, query, qstride, layout, q_valid, T, Q, M, table, life, ids, count, next_id,
-                  tolA, tolB, tol, life_init, mode, append, match, match_id, proj_ab, stream=0):
+                  tolA, tolB, tol, life_init, mode, append, match, match_id, proj_ab, hit_pos=None, stream=0):
         self._check(self.cdll.lslam_associate(
             self._h, query, qstride, layout, q_valid, T, Q, M, table, life, ids, count, next_id,
             float(tolA), float(tolB), float(tol), int(life_init), int(mode), int(bool(append)),
-            match, match_id, proj_ab, stream))
+            match, match_id, proj_ab, hit_pos, stream))
+
+    @staticmethod
+    def _params(params):
+        if len(params) != 17:
+            raise ValueError("UKF params: 17 doubles (dt, wheel_r, base_l, alpha, beta, kappa, var_dist, "
+                             "var_angle, Q[9])")
+        return (_f64 * 17)(*[float(v) for v in params])
+
+    def ukf_step(self, x, P, u, z, zstride, zmode, lm_pos, lm_valid, valid_min, F, L, params, flags,
+                 status=None, sigmas_f=None, stream=0):
+        self._check(self.cdll.lslam_ukf_step(self._h, x, P, u, z, zstride, zmode, lm_pos, lm_valid, valid_min,
+                                             F, L, self._params(params), flags, status, sigmas_f, stream))
+
+    def ukf_predict(self, x, P, u, F, params, redraw=True, status=None, sigmas_f=None, stream=0):
+        self._check(self.cdll.lslam_ukf_predict(self._h, x, P, u, F, self._params(params), int(bool(redraw)),
+                                                status, sigmas_f, stream))
+
+    def ukf_update(self, x, P, z, zstride, zmode, lm_pos, lm_valid, valid_min, F, L, params,
+                   status=None, sigmas_f=None, stream=0):
+        self._check(self.cdll.lslam_ukf_update(self._h, x, P, z, zstride, zmode, lm_pos, lm_valid, valid_min,
+                                               F, L, self._params(params), status, sigmas_f, stream))
 
     def synth_scans(self, xy, B, beams, seed, scan_base, noise_mm, dropout, stream=0):
         self._check(self.cdll.lslam_synth_scans(self._h, xy, B, beams, int(seed) & (2**64 - 1),

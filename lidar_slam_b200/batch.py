@@ -127,6 +127,7 @@ class Engine:
             "match": torch.empty((T, Q), dtype=torch.int32, device=dev),
             "match_id": torch.empty((T, Q), dtype=torch.int32, device=dev),
             "proj_ab": torch.empty((T, Q, 2), dtype=torch.float64, device=dev),
+            "hit_pos": torch.empty((T, Q, 2), dtype=torch.float64, device=dev),
         }
 
     def associate(self, query, tables, q_valid=None, mode=0, append=True, tolA=TOLERANCE_A,
@@ -161,8 +162,77 @@ class Engine:
             query.data_ptr(), qs, 1 if qs == 8 else 0, q_valid.data_ptr() if q_valid is not None else None,
             T, Q, M, rows.data_ptr(), life.data_ptr(), ids.data_ptr(), count.data_ptr(), next_id.data_ptr(),
             tolA, tolB, tol, life_init, mode, append, out["match"].data_ptr(), out["match_id"].data_ptr(),
-            out["proj_ab"].data_ptr(), self._stream())
+            out["proj_ab"].data_ptr(), out["hit_pos"].data_ptr() if "hit_pos" in out else None,
+            stream=self._stream())
         return out
+
+    # ---- UKF (systemClass.py:7-29, UKFMethods.py:6-8) ----------------------------------------
+    UKF_PREDICT, UKF_UPDATE, UKF_REDRAW = 1, 2, 4
+
+    @staticmethod
+    def ukf_params(dt=0.005, wheel_r=50.0, base_l=200.0, alpha=1e-4, beta=2.0, kappa=0.0,
+                   var_dist=0.5 ** 2, var_angle=0.3 ** 2, Q=None):
+        """The 17 doubles lslam_ukf_step takes; defaults = systemClass.py:8-10,20,28-29 (DT, VAR_DIST,
+        VAR_ANGLE, MerweScaledSigmaPoints(alpha=1e-4, beta=2, kappa=0), Q = 0.001 I) and
+        UKFMethods.py:6-7 (R = 50, L = 200)."""
+        q = [0.001, 0, 0, 0, 0.001, 0, 0, 0, 0.001] if Q is None else [float(v) for row in Q for v in row]
+        return [dt, wheel_r, base_l, alpha, beta, kappa, var_dist, var_angle] + q
+
+    def alloc_ukf(self, F, L=8):
+        """State of F filters as systemClass.config_ukf sets it (x = 0, P = diag(.1, .1, .05))."""
+        dev = self.device
+        P0 = torch.diag(torch.tensor([0.1, 0.1, 0.05], dtype=torch.float64, device=dev))
+        return {
+            "x": torch.zeros((F, 3), dtype=torch.float64, device=dev),
+            "P": P0.expand(F, 3, 3).contiguous(),
+            "u": torch.zeros((F, 2), dtype=torch.float64, device=dev),
+            "status": torch.zeros((F,), dtype=torch.int32, device=dev),
+            "params": self.ukf_params(),
+            "L": L,
+        }
+
+    def ukf_step(self, ukf, z, lm_pos, lm_valid=None, valid_min=1, u=None, zmode=None, flags=None,
+                 sigmas_f=None):
+        """predict(u) + update(z, landmarks) of every filter in ``ukf`` (dict of alloc_ukf), in place.
+
+        z [F, L, 2] (range, bearing) or [F, L, 8] line records of ransac_lines (zmode 1: the
+        measurement is the range/bearing of the line's inlier centroid); lm_pos [F, L, 2];
+        lm_valid [F, L] int32 (slot used iff >= valid_min) or None."""
+        x = self._check(ukf["x"], torch.float64, "ukf['x']")
+        P = self._check(ukf["P"], torch.float64, "ukf['P']")
+        F = int(x.shape[0])
+        if x.shape != (F, 3) or P.shape != (F, 3, 3):
+            raise ValueError("ukf['x'] must be [F, 3] and ukf['P'] [F, 3, 3]")
+        u = ukf.get("u") if u is None else u
+        if u is not None:
+            u = self._check(u, torch.float64, "u")
+            if u.shape != (F, 2):
+                raise ValueError("u must be [F, 2]")
+        if flags is None:
+            flags = self.UKF_PREDICT | self.UKF_UPDATE | self.UKF_REDRAW
+        L, zs = 0, 2
+        if z is not None:
+            z = self._check(z, torch.float64, "z")
+            if z.dim() != 3 or z.shape[0] != F:
+                raise ValueError("z must be [F, L, zstride]")
+            L, zs = int(z.shape[1]), int(z.shape[2])
+            if zmode is None:
+                zmode = 1 if zs == 8 else 0
+            lm_pos = self._check(lm_pos, torch.float64, "lm_pos")
+            if lm_pos.shape != (F, L, 2):
+                raise ValueError("lm_pos must be [F, L, 2]")
+            if lm_valid is not None:
+                lm_valid = self._check(lm_valid, torch.int32, "lm_valid")
+                if lm_valid.shape != (F, L):
+                    raise ValueError("lm_valid must be [F, L]")
+        st = ukf.get("status")
+        self.handle.ukf_step(
+            x.data_ptr(), P.data_ptr(), u.data_ptr() if u is not None else None,
+            z.data_ptr() if z is not None else None, zs, zmode or 0,
+            lm_pos.data_ptr() if z is not None else None, lm_valid.data_ptr() if lm_valid is not None else None,
+            valid_min, F, L, ukf["params"], flags, st.data_ptr() if st is not None else None,
+            sigmas_f.data_ptr() if sigmas_f is not None else None, self._stream())
+        return ukf
 
     def synth_scans(self, B, beams=360, seed=0, scan_base=0, noise_mm=5.0, dropout=0.02, out=None):
         """Random-room scans generated on the device (csrc/aux_kernels.cuh) -> xy[B, beams, 2]."""

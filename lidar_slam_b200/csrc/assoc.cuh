@@ -26,6 +26,7 @@ struct AssocArgs {
     int life_init, mode, append;
     int32_t *match, *match_id; // [T, Q]
     double *proj_ab;           // [T, Q, 2] or null
+    double *hit_pos;           // [T, Q, 2] or null
 };
 
 constexpr int kLifeRemoved = -1;
@@ -78,7 +79,9 @@ __global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
         if (a.q_valid != nullptr && a.q_valid[qo] <= 0) {
             if (lane == 0) {
                 a.match[qo] = -2; a.match_id[qo] = -1;
-                if (a.proj_ab) { a.proj_ab[2 * qo] = __longlong_as_double(0x7ff8000000000000LL); a.proj_ab[2 * qo + 1] = a.proj_ab[2 * qo]; }
+                const double qn = __longlong_as_double(0x7ff8000000000000LL);
+                if (a.proj_ab) { a.proj_ab[2 * qo] = qn; a.proj_ab[2 * qo + 1] = qn; }
+                if (a.hit_pos) { a.hit_pos[2 * qo] = qn; a.hit_pos[2 * qo + 1] = qn; }
             }
             continue;
         }
@@ -150,6 +153,7 @@ __global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
         __syncwarp();
         int hit_new = -1, hit_id = -1;
         double pa = q[0], pb = q[1];
+        double hx = __longlong_as_double(0x7ff8000000000000LL), hy = hx;
         if (hit >= 0) {
             if (lane == 0) life[hit] = a.life_init;              // reset_life(); a, b, pos, end NOT updated
             // removals all precede the hit in first-match modes; count them for the nearest mode
@@ -165,6 +169,8 @@ __global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
             hit_id = ids[hit];
             pa = ent[(size_t)hit * 6];
             pb = ent[(size_t)hit * 6 + 1];
+            hx = ent[(size_t)hit * 6 + 2];
+            hy = ent[(size_t)hit * 6 + 3];
         }
         __syncwarp();
         // ---- stable compaction of the removed landmarks (list.remove shifts the tail left) ----
@@ -214,6 +220,7 @@ __global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
             a.match[qo] = result;
             a.match_id[qo] = rid;
             if (a.proj_ab) { a.proj_ab[2 * qo] = pa; a.proj_ab[2 * qo + 1] = pb; }
+            if (a.hit_pos) { a.hit_pos[2 * qo] = hx; a.hit_pos[2 * qo + 1] = hy; }
         }
     }
     // ---- write the table back; slots past the live count are zeroed ----

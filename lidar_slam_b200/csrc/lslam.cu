@@ -6,6 +6,7 @@
 #include "ransac.cuh"
 #include "aux_kernels.cuh"
 #include "assoc.cuh"
+#include "ukf.cuh"
 
 #include "../../include/lslam.h"
 
@@ -168,7 +169,8 @@ extern "C" int lslam_associate(void *handle, const double *query, int32_t qstrid
                                const int32_t *q_valid, int32_t T, int32_t Q, int32_t M, double *table,
                                int32_t *life, int32_t *ids, int32_t *count, int32_t *next_id, double tolA,
                                double tolB, double tol, int32_t life_init, int32_t mode, int32_t append,
-                               int32_t *match, int32_t *match_id, double *proj_ab, void *stream)
+                               int32_t *match, int32_t *match_id, double *proj_ab, double *hit_pos,
+                               void *stream)
 {
     Handle *h = (Handle *)handle;
     if (h == nullptr) return LSLAM_ERR_BAD_ARG;
@@ -188,7 +190,7 @@ extern "C" int lslam_associate(void *handle, const double *query, int32_t qstrid
     a.T = T; a.Q = Q; a.M = M;
     a.table = table; a.life = life; a.ids = ids; a.count = count; a.next_id = next_id;
     a.tolA = tolA; a.tolB = tolB; a.tol = tol; a.life_init = life_init; a.mode = mode; a.append = append;
-    a.match = match; a.match_id = match_id; a.proj_ab = proj_ab;
+    a.match = match; a.match_id = match_id; a.proj_ab = proj_ab; a.hit_pos = hit_pos;
     auto kern = associate_kernel;
     const size_t smem = per_warp * nwarps;
     LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -197,6 +199,84 @@ extern "C" int lslam_associate(void *handle, const double *query, int32_t qstrid
     h->launches++;
     LSLAM_CUDA_TRY(h, cudaGetLastError());
     return LSLAM_OK;
+}
+
+// ---- UKF ------------------------------------------------------------------------------------
+template <int G>
+static int launch_ukf(Handle *h, const UkfArgs &a, cudaStream_t st)
+{
+    auto kern = ukf_kernel<G>;
+    const int nwarps = G >= 16 ? 2 : 4;
+    const size_t smem = ukf_smem_doubles_per_warp(G) * sizeof(double) * nwarps;
+    if (smem > (size_t)h->smem_optin) return fail(h, LSLAM_ERR_CAPACITY, "lslam_ukf: shared memory");
+    LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const long long per_cta = (long long)nwarps * (32 / G);
+    const long long grid = (a.F + per_cta - 1) / per_cta;
+    if (grid > 0x7fffffffLL) return fail(h, LSLAM_ERR_CAPACITY, "too many filters for one launch");
+    LSLAM_LAUNCH(kern, (unsigned)grid, (unsigned)(nwarps * 32), smem, st, a);
+    h->launches++;
+    LSLAM_CUDA_TRY(h, cudaGetLastError());
+    return LSLAM_OK;
+}
+
+extern "C" int lslam_ukf_step(void *handle, double *x, double *P, const double *u, const double *z,
+                              int32_t zstride, int32_t zmode, const double *lm_pos, const int32_t *lm_valid,
+                              int32_t valid_min, int32_t F, int32_t L, const double *params_h, int32_t flags,
+                              int32_t *status, double *sigmas_f, void *stream)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr) return LSLAM_ERR_BAD_ARG;
+    if (!x || !P || !params_h) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_step: null buffer");
+    if (F < 0 || L < 0 || L > 32 || (flags & ~7) || !(flags & 3))
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_step: need F >= 0, 0 <= L <= 32, flags of PREDICT|UPDATE|REDRAW");
+    const bool upd = (flags & LSLAM_UKF_UPDATE) && L > 0;
+    if (upd && (!z || !lm_pos || zmode < 0 || zmode > 1 || zstride < (zmode ? 4 : 2)))
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_step: update needs z, lm_pos and a zstride that fits zmode");
+    if (F == 0) return LSLAM_OK;
+    DeviceGuard g(h->device);
+    UkfArgs a;
+    a.x = x; a.P = P; a.u = u; a.z = z; a.lm_pos = lm_pos; a.lm_valid = lm_valid; a.status = status;
+    a.sigmas_f = sigmas_f;
+    a.F = F; a.L = upd ? L : 0; a.zstride = zstride; a.zmode = zmode; a.valid_min = valid_min;
+    a.flags = upd ? flags : (flags & ~LSLAM_UKF_UPDATE);
+    if (!(a.flags & 3)) {                          // update-only call without slots: nothing to do
+        if (status) LSLAM_CUDA_TRY(h, cudaMemsetAsync(status, 0, sizeof(int32_t) * (size_t)F, (cudaStream_t)stream));
+        return LSLAM_OK;
+    }
+    const double dt = params_h[0], wheel_r = params_h[1], base_l = params_h[2];
+    const double alpha = params_h[3], beta = params_h[4], kappa = params_h[5];
+    // weights exactly as MerweScaledSigmaPoints._compute_weights (and oracle/ukf.c) round them
+    const int n = 3;
+    const double lam = alpha * alpha * (n + kappa) - n;
+    const double c = n + lam;
+    a.dt = dt; a.half_r = wheel_r / 2.0; a.r_over_l = wheel_r / base_l; a.cscale = c;
+    a.wi = 0.5 / c; a.wm0 = lam / c; a.wc0 = lam / c + (1 - alpha * alpha + beta);
+    a.var_dist = params_h[6]; a.var_angle = params_h[7];
+    for (int i = 0; i < 9; ++i) a.Q[i] = params_h[8 + i];
+    if (!(c == c) || c == 0.0) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_step: alpha/kappa give n + lambda = 0");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int Lk = a.L;
+    if (Lk <= 4) return launch_ukf<4>(h, a, st);
+    if (Lk <= 8) return launch_ukf<8>(h, a, st);
+    if (Lk <= 16) return launch_ukf<16>(h, a, st);
+    return launch_ukf<32>(h, a, st);
+}
+
+extern "C" int lslam_ukf_predict(void *handle, double *x, double *P, const double *u, int32_t F,
+                                 const double *params_h, int32_t redraw, int32_t *status, double *sigmas_f,
+                                 void *stream)
+{
+    return lslam_ukf_step(handle, x, P, u, nullptr, 2, 0, nullptr, nullptr, 0, F, 0, params_h,
+                          LSLAM_UKF_PREDICT | (redraw ? LSLAM_UKF_REDRAW : 0), status, sigmas_f, stream);
+}
+
+extern "C" int lslam_ukf_update(void *handle, double *x, double *P, const double *z, int32_t zstride,
+                                int32_t zmode, const double *lm_pos, const int32_t *lm_valid, int32_t valid_min,
+                                int32_t F, int32_t L, const double *params_h, int32_t *status,
+                                const double *sigmas_f, void *stream)
+{
+    return lslam_ukf_step(handle, x, P, nullptr, z, zstride, zmode, lm_pos, lm_valid, valid_min, F, L, params_h,
+                          LSLAM_UKF_UPDATE, status, const_cast<double *>(sigmas_f), stream);
 }
 
 // ---- input stage, synthetic scans, fp64 probe --------------------------------------------

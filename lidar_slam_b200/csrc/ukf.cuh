@@ -1,0 +1,365 @@
+// ukf.cuh - K4: UKF sigma-point predict / update for many independent n = 3 filters.
+//
+// Replaces filterpy's UnscentedKalmanFilter.predict/update + MerweScaledSigmaPoints driven by the
+// callbacks of /root/reference/UKFMethods.py:10-71 with the configuration of
+// /root/reference/systemClass.py:14-29.  Semantics and operation order = oracle/ukf.c (every
+// product and sum below is an explicit round-to-nearest intrinsic or an explicit fma, in the
+// order that file pins), so the only differences to the CPU oracle are the last-ulp differences
+// of sin/cos/atan2 between the CUDA math library and libm.
+//
+// Work decomposition: a GROUP of G lanes (G = 4, 8, 16 or 32, the smallest that holds the L
+// landmark slots) owns one filter, so a warp advances 32/G filters at once.
+//   * everything of dimension n = 3 (Cholesky of P, the 7 sigma points, fx, the circular state
+//     mean, the prior covariance) is computed redundantly by every lane of the group in
+//     registers: replicated scalar work costs the same issue slots as doing it on one lane and
+//     needs no communication;
+//   * the measurement side is spread over the group: lane q owns the q-th valid landmark - its
+//     7 hx evaluations, its circular mean, its residual columns and its 3x2 block of Pxz;
+//   * S (2L x 2L) is built by row pairs (rows q and 2L-1-q have 2L+1 lower-triangle entries
+//     together, so the lanes are balanced), factorised by a group-cooperative column Cholesky
+//     in shared memory, and K, x, P follow from triangular solves and small products.
+// Shared memory is interleaved across the groups of a warp (element e of group g at e*NG + g)
+// so replicated reads are one broadcast wavefront and per-lane reads are conflict free.
+#pragma once
+#include "lslam_core.cuh"
+
+namespace lslam {
+
+enum { kUkfPredict = 1, kUkfUpdate = 2, kUkfRedraw = 4 };
+enum { kUkfStSigma = 1, kUkfStRedraw = 2, kUkfStS = 4 };
+
+struct UkfArgs {
+    double *x, *P;                 // [F,3], [F,3,3] in/out
+    const double *u;               // [F,2] or null (zero controls)
+    const double *z;               // [F,L,zstride]
+    const double *lm_pos;          // [F,L,2]
+    const int32_t *lm_valid;       // [F,L] or null
+    int32_t *status;               // [F] or null
+    double *sigmas_f;              // [F,7,3] or null
+    int F, L, zstride, zmode, valid_min, flags;
+    double dt, half_r, r_over_l, cscale;     // R/2, R/L, n + lambda
+    double wm0, wc0, wi;                     // weights
+    double var_dist, var_angle;
+    double Q[9];
+};
+
+__host__ __device__ inline size_t ukf_smem_doubles_per_warp(int G) { return (size_t)(18 * 2 * G + 4 * G * G) * (32 / G); }
+
+__device__ __forceinline__ double ukf_normalize_angle(double a)
+{
+    const double kPi = 3.141592653589793, kTwoPi = 2 * 3.141592653589793;
+    double m = fmod(a, kTwoPi);                     // exact; Python's float % then fixes the sign
+    if (m != 0.0) { if (m < 0.0) m = __dadd_rn(m, kTwoPi); }
+    else m = 0.0;
+    if (m > kPi) m = __dsub_rn(m, kTwoPi);
+    return m;
+}
+
+// upper Cholesky of c*P (3x3, upper triangle read) and the 7 sigma points; false if not PD
+__device__ __forceinline__ bool ukf_sigma_points(const double x[3], const double P[9], double c, double sg[7][3])
+{
+    double U[9];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        double s = __dmul_rn(c, P[j * 3 + j]);
+#pragma unroll
+        for (int p = 0; p < j; ++p) s = __fma_rn(-U[p * 3 + j], U[p * 3 + j], s);
+        if (!(s > 0.0)) return false;
+        const double d = __dsqrt_rn(s);
+        U[j * 3 + j] = d;
+#pragma unroll
+        for (int i = j + 1; i < 3; ++i) {
+            double t = __dmul_rn(c, P[j * 3 + i]);
+#pragma unroll
+            for (int p = 0; p < j; ++p) t = __fma_rn(-U[p * 3 + j], U[p * 3 + i], t);
+            U[j * 3 + i] = __ddiv_rn(t, d);
+        }
+#pragma unroll
+        for (int i = 0; i < j; ++i) U[j * 3 + i] = 0.0;
+    }
+#pragma unroll
+    for (int i = 0; i < 3; ++i) sg[0][i] = x[i];
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            sg[k + 1][i] = __dadd_rn(x[i], U[k * 3 + i]);
+            sg[3 + k + 1][i] = __dsub_rn(x[i], U[k * 3 + i]);
+        }
+    return true;
+}
+
+template <int G>
+__global__ void __launch_bounds__(128) ukf_kernel(const UkfArgs a)
+{
+    LSLAM_SMEM_DECL;
+    constexpr int NG = 32 / G;                 // groups (filters) per warp
+    constexpr int DZ = 2 * G;                  // leading dimension of the measurement arrays
+    constexpr int oE = 0, oPxz = 7 * DZ, oK = 10 * DZ, oY = 13 * DZ, oSd = 14 * DZ, oM = 15 * DZ, oS = 18 * DZ;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const int grp = lane / G, g = lane % G;
+    double *smw = reinterpret_cast<double *>(smem_raw) + (size_t)warp * ukf_smem_doubles_per_warp(G);
+#define UKF_SM(e) smw[(e) * NG + grp]
+    const long long f = ((long long)blockIdx.x * nwarps + warp) * NG + grp;
+    const bool live = f < a.F;
+    const unsigned gmask = (G == 32 ? 0xffffffffu : ((1u << G) - 1u)) << (grp * G);
+
+    double Wm[7], Wc[7];
+#pragma unroll
+    for (int k = 0; k < 7; ++k) { Wm[k] = a.wi; Wc[k] = a.wi; }
+    Wm[0] = a.wm0; Wc[0] = a.wc0;
+
+    double x[3] = {0.0, 0.0, 0.0}, P[9] = {1.0, 0.0, 0.0, 0.0, 1.0, 0.0, 0.0, 0.0, 1.0};
+    double sf[7][3];
+    int st = 0;
+    bool run = live;
+    if (live) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) x[i] = a.x[f * 3 + i];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) P[i] = a.P[f * 9 + i];
+    }
+#pragma unroll
+    for (int k = 0; k < 7; ++k) { sf[k][0] = 0.0; sf[k][1] = 0.0; sf[k][2] = 0.0; }
+
+    // ================= predict (replicated over the lanes of the group) =======================
+    if (a.flags & kUkfPredict) {
+        double sg[7][3];
+        if (run && !ukf_sigma_points(x, P, a.cscale, sg)) { st = kUkfStSigma; run = false; }
+        if (run) {
+            const double u0 = a.u ? a.u[f * 2] : 0.0, u1 = a.u ? a.u[f * 2 + 1] : 0.0;
+            const double wth = __dmul_rn(a.dt, __dadd_rn(__dmul_rn(-a.r_over_l, u0), __dmul_rn(a.r_over_l, u1)));
+            double a0 = 0.0, a1 = 0.0, ss = 0.0, sc = 0.0;
+#pragma unroll
+            for (int k = 0; k < 7; ++k) {                       // UKFMethods.py:17-24
+                double sn, cs;
+                sincos(sg[k][2], &sn, &cs);
+                const double rc = __dmul_rn(a.half_r, cs), rs = __dmul_rn(a.half_r, sn);
+                sf[k][0] = __dadd_rn(sg[k][0], __dmul_rn(a.dt, __dadd_rn(__dmul_rn(rc, u0), __dmul_rn(rc, u1))));
+                sf[k][1] = __dadd_rn(sg[k][1], __dmul_rn(a.dt, __dadd_rn(__dmul_rn(rs, u0), __dmul_rn(rs, u1))));
+                sf[k][2] = __dadd_rn(sg[k][2], wth);
+                sincos(sf[k][2], &sn, &cs);                     // UKFMethods.py:37-45
+                ss = __fma_rn(sn, Wm[k], ss);
+                sc = __fma_rn(cs, Wm[k], sc);
+                a0 = __fma_rn(sf[k][0], Wm[k], a0);
+                a1 = __fma_rn(sf[k][1], Wm[k], a1);
+            }
+            x[0] = a0; x[1] = a1; x[2] = atan2(ss, sc);
+            double Pn[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};      // lower triangle 00 10 11 20 21 22
+#pragma unroll
+            for (int k = 0; k < 7; ++k) {
+                const double y0 = __dsub_rn(sf[k][0], x[0]), y1 = __dsub_rn(sf[k][1], x[1]);
+                const double y2 = ukf_normalize_angle(__dsub_rn(sf[k][2], x[2]));
+                Pn[0] = __fma_rn(Wc[k], __dmul_rn(y0, y0), Pn[0]);
+                Pn[1] = __fma_rn(Wc[k], __dmul_rn(y1, y0), Pn[1]);
+                Pn[2] = __fma_rn(Wc[k], __dmul_rn(y1, y1), Pn[2]);
+                Pn[3] = __fma_rn(Wc[k], __dmul_rn(y2, y0), Pn[3]);
+                Pn[4] = __fma_rn(Wc[k], __dmul_rn(y2, y1), Pn[4]);
+                Pn[5] = __fma_rn(Wc[k], __dmul_rn(y2, y2), Pn[5]);
+            }
+            P[0] = __dadd_rn(Pn[0], a.Q[0]); P[1] = __dadd_rn(Pn[1], a.Q[1]); P[2] = __dadd_rn(Pn[3], a.Q[2]);
+            P[3] = __dadd_rn(Pn[1], a.Q[3]); P[4] = __dadd_rn(Pn[2], a.Q[4]); P[5] = __dadd_rn(Pn[4], a.Q[5]);
+            P[6] = __dadd_rn(Pn[3], a.Q[6]); P[7] = __dadd_rn(Pn[4], a.Q[7]); P[8] = __dadd_rn(Pn[5], a.Q[8]);
+            bool wrote_prior = false;
+            if (a.flags & kUkfRedraw) {
+                if (!ukf_sigma_points(x, P, a.cscale, sf)) { st = kUkfStRedraw; run = false; wrote_prior = true; }
+            }
+            if (wrote_prior && g == 0) {                        // prior stands, update skipped
+#pragma unroll
+                for (int i = 0; i < 3; ++i) a.x[f * 3 + i] = x[i];
+#pragma unroll
+                for (int i = 0; i < 9; ++i) a.P[f * 9 + i] = P[i];
+            }
+            if (run && a.sigmas_f != nullptr && g == 0) {
+#pragma unroll
+                for (int k = 0; k < 7; ++k)
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) a.sigmas_f[(f * 7 + k) * 3 + i] = sf[k][i];
+            }
+        }
+    } else if (a.flags & kUkfUpdate) {
+        if (run) {
+            if (a.sigmas_f != nullptr) {
+#pragma unroll
+                for (int k = 0; k < 7; ++k)
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) sf[k][i] = a.sigmas_f[(f * 7 + k) * 3 + i];
+            } else if (!ukf_sigma_points(x, P, a.cscale, sf)) { st = kUkfStRedraw; run = false; }
+        }
+    }
+
+    // ================= update ===================================================================
+    int m = 0, sel = 0;
+    if (a.flags & kUkfUpdate) {
+        const bool ok = run && g < a.L && (a.lm_valid == nullptr || a.lm_valid[f * a.L + g] >= a.valid_min);
+        const unsigned bits = (__ballot_sync(LSLAM_FULL_MASK, ok) & gmask) >> (grp * G);
+        m = __popc(bits);
+        sel = (g < m) ? (int)__fns(bits, 0, g + 1) : 0;         // the g-th valid slot
+    }
+    const int dz = 2 * m;
+    const int dzmax = __reduce_max_sync(LSLAM_FULL_MASK, dz);   // warp-uniform loop bound
+    if (dzmax > 0) {
+        const bool mine = g < m;                                // this lane owns measurement q = g
+        const int q = g;
+        // ---- hx, z_mean, residual columns of the lane's landmark (registers) ----
+        double e_d[7], e_b[7], zz_d = 0.0, zz_b = 0.0, zp_d = 0.0, zp_b = 0.0;
+#pragma unroll
+        for (int k = 0; k < 7; ++k) { e_d[k] = 0.0; e_b[k] = 0.0; }
+        if (mine) {
+            const double px = a.lm_pos[(f * a.L + sel) * 2], py = a.lm_pos[(f * a.L + sel) * 2 + 1];
+            double acc = 0.0, ss = 0.0, sc = 0.0;
+#pragma unroll
+            for (int k = 0; k < 7; ++k) {                       // UKFMethods.py:26-34, 47-57
+                const double dx = __dsub_rn(px, sf[k][0]), dy = __dsub_rn(py, sf[k][1]);
+                e_d[k] = __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+                e_b[k] = ukf_normalize_angle(__dsub_rn(atan2(dy, dx), sf[k][2]));
+                double sn, cs;
+                sincos(e_b[k], &sn, &cs);
+                ss = __fma_rn(sn, Wm[k], ss);
+                sc = __fma_rn(cs, Wm[k], sc);
+                acc = __fma_rn(e_d[k], Wm[k], acc);
+            }
+            zp_d = acc;
+            zp_b = atan2(ss, sc);
+            const double *zs = a.z + (f * a.L + sel) * (long long)a.zstride;
+            if (a.zmode == 0) { zz_d = zs[0]; zz_b = zs[1]; }
+            else {
+                const double ox = zs[2], oy = zs[3];
+                zz_d = __dsqrt_rn(__dadd_rn(__dmul_rn(ox, ox), __dmul_rn(oy, oy)));
+                zz_b = atan2(oy, ox);
+            }
+#pragma unroll
+            for (int k = 0; k < 7; ++k) {                       // residual_h (UKFMethods.py:66-71)
+                e_d[k] = __dsub_rn(e_d[k], zp_d);
+                e_b[k] = ukf_normalize_angle(__dsub_rn(e_b[k], zp_b));
+                UKF_SM(oE + k * DZ + 2 * q) = e_d[k];
+                UKF_SM(oE + k * DZ + 2 * q + 1) = e_b[k];
+            }
+            UKF_SM(oY + 2 * q) = __dsub_rn(zz_d, zp_d);
+            UKF_SM(oY + 2 * q + 1) = ukf_normalize_angle(__dsub_rn(zz_b, zp_b));
+            // ---- the lane's 3x2 block of Pxz: sum_k Wc_k * y_k[i] * e_k[j] ----
+            double pd[3] = {0.0, 0.0, 0.0}, pb[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+            for (int k = 0; k < 7; ++k) {
+                const double y0 = __dsub_rn(sf[k][0], x[0]), y1 = __dsub_rn(sf[k][1], x[1]);
+                const double y2 = ukf_normalize_angle(__dsub_rn(sf[k][2], x[2]));
+                pd[0] = __fma_rn(Wc[k], __dmul_rn(y0, e_d[k]), pd[0]);
+                pd[1] = __fma_rn(Wc[k], __dmul_rn(y1, e_d[k]), pd[1]);
+                pd[2] = __fma_rn(Wc[k], __dmul_rn(y2, e_d[k]), pd[2]);
+                pb[0] = __fma_rn(Wc[k], __dmul_rn(y0, e_b[k]), pb[0]);
+                pb[1] = __fma_rn(Wc[k], __dmul_rn(y1, e_b[k]), pb[1]);
+                pb[2] = __fma_rn(Wc[k], __dmul_rn(y2, e_b[k]), pb[2]);
+            }
+#pragma unroll
+            for (int i = 0; i < 3; ++i) { UKF_SM(oPxz + i * DZ + 2 * q) = pd[i]; UKF_SM(oPxz + i * DZ + 2 * q + 1) = pb[i]; }
+        }
+        __syncwarp();
+        // ---- S = sum_k Wc_k e_k e_k^T + R: rows q and dz-1-q by lane q (lower triangle, mirrored) ----
+        if (mine) {
+#pragma unroll 1
+            for (int half = 0; half < 2; ++half) {
+                const int i = half ? dz - 1 - q : q;
+                double ei[7];
+#pragma unroll
+                for (int k = 0; k < 7; ++k) ei[k] = UKF_SM(oE + k * DZ + i);
+                for (int j = 0; j <= i; ++j) {
+                    double s = 0.0;
+#pragma unroll
+                    for (int k = 0; k < 7; ++k) s = __fma_rn(Wc[k], __dmul_rn(ei[k], UKF_SM(oE + k * DZ + j)), s);
+                    if (i == j) {
+                        s = __dadd_rn(s, (i & 1) ? a.var_angle : a.var_dist);
+                        UKF_SM(oSd + i) = s;
+                    }
+                    UKF_SM(oS + i * DZ + j) = s;                // strict lower keeps S, upper will hold U
+                    UKF_SM(oS + j * DZ + i) = s;
+                }
+            }
+        }
+        __syncwarp();
+        // ---- upper Cholesky U^T U = S in the upper triangle (diagonal included), cooperative ----
+        bool spd = true;
+        for (int j = 0; j < dzmax; ++j) {
+            if (j < dz) {
+                double s = UKF_SM(oSd + j);                     // every lane of the group: the pivot
+                for (int p = 0; p < j; ++p) { const double v = UKF_SM(oS + p * DZ + j); s = __fma_rn(-v, v, s); }
+                if (!(s > 0.0)) spd = false;
+                const double d = __dsqrt_rn(spd ? s : 1.0);
+                for (int i = j + 1 + g; i < dz; i += G) {       // row j of U, columns dealt to the lanes
+                    double t = UKF_SM(oS + i * DZ + j);         // S[j][i] = S[i][j], read from the lower triangle
+                    for (int p = 0; p < j; ++p) t = __fma_rn(-UKF_SM(oS + p * DZ + j), UKF_SM(oS + p * DZ + i), t);
+                    UKF_SM(oS + j * DZ + i) = __ddiv_rn(t, d);
+                }
+                if (g == 0) UKF_SM(oS + j * DZ + j) = d;
+            }
+            __syncwarp();
+        }
+        if (m > 0 && !spd) { st |= kUkfStS; }
+        const bool upd = m > 0 && spd;
+        // ---- K rows: U^T w = Pxz_r, U k = w (lanes 0..2 of the group, one row each) ----
+        if (upd && g < 3) {
+            const int r = g;
+            for (int i = 0; i < dz; ++i) {
+                double s = UKF_SM(oPxz + r * DZ + i);
+                for (int p = 0; p < i; ++p) s = __fma_rn(-UKF_SM(oS + p * DZ + i), UKF_SM(oK + r * DZ + p), s);
+                UKF_SM(oK + r * DZ + i) = __ddiv_rn(s, UKF_SM(oS + i * DZ + i));
+            }
+            for (int i = dz - 1; i >= 0; --i) {
+                double s = UKF_SM(oK + r * DZ + i);
+                for (int p = i + 1; p < dz; ++p) s = __fma_rn(-UKF_SM(oS + i * DZ + p), UKF_SM(oK + r * DZ + p), s);
+                UKF_SM(oK + r * DZ + i) = __ddiv_rn(s, UKF_SM(oS + i * DZ + i));
+            }
+        }
+        __syncwarp();
+        // ---- M = S K^T: rows 2q, 2q+1 by lane q ----
+        if (upd && mine) {
+#pragma unroll 1
+            for (int half = 0; half < 2; ++half) {
+                const int j = 2 * q + half;
+                double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+                for (int c = 0; c < dz; ++c) {
+                    const double sv = c == j ? UKF_SM(oSd + j) : (c < j ? UKF_SM(oS + j * DZ + c) : UKF_SM(oS + c * DZ + j));
+                    s0 = __fma_rn(sv, UKF_SM(oK + 0 * DZ + c), s0);
+                    s1 = __fma_rn(sv, UKF_SM(oK + 1 * DZ + c), s1);
+                    s2 = __fma_rn(sv, UKF_SM(oK + 2 * DZ + c), s2);
+                }
+                UKF_SM(oM + j * 3 + 0) = s0; UKF_SM(oM + j * 3 + 1) = s1; UKF_SM(oM + j * 3 + 2) = s2;
+            }
+        }
+        __syncwarp();
+        // ---- x = x + K y ; P = P - K M (replicated) ----
+        if (upd) {
+            double xn[3], Pn[9];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+                double s = 0.0;
+                for (int j = 0; j < dz; ++j) s = __fma_rn(UKF_SM(oK + i * DZ + j), UKF_SM(oY + j), s);
+                xn[i] = __dadd_rn(x[i], s);
+            }
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+#pragma unroll
+                for (int r = 0; r < 3; ++r) {
+                    double s = 0.0;
+                    for (int j = 0; j < dz; ++j) s = __fma_rn(UKF_SM(oK + i * DZ + j), UKF_SM(oM + j * 3 + r), s);
+                    Pn[i * 3 + r] = __dsub_rn(P[i * 3 + r], s);
+                }
+#pragma unroll
+            for (int i = 0; i < 3; ++i) x[i] = xn[i];
+#pragma unroll
+            for (int i = 0; i < 9; ++i) P[i] = Pn[i];
+        }
+    }
+    // ================= outputs ==================================================================
+    if (live && g == 0) {
+        if (run) {
+#pragma unroll
+            for (int i = 0; i < 3; ++i) a.x[f * 3 + i] = x[i];
+#pragma unroll
+            for (int i = 0; i < 9; ++i) a.P[f * 9 + i] = P[i];
+        }
+        if (a.status != nullptr) a.status[f] = st;
+    }
+#undef UKF_SM
+}
+
+} // namespace lslam

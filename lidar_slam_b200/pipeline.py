@@ -26,7 +26,7 @@ class ScanPipeline:
         self.rout = eng.alloc_ransac_out(self.S, self.N, self.chunk)
         self.tables = eng.alloc_tables(self.S, self.M)
         self.aout = eng.alloc_assoc_out(self.S, self.C)
-        self.ukf = eng.alloc_ukf(self.S, self.M) if hasattr(eng, "alloc_ukf") else None
+        self.ukf = eng.alloc_ukf(self.S, self.C)
         self.xy_dev = None
         self._host_out = None
 
@@ -43,16 +43,39 @@ class ScanPipeline:
         if ransac_events is not None:
             ransac_events[1].record()
         a = eng.associate(r["line"], self.tables, q_valid=r["ninl"], out=self.aout)
-        res = {"line": r["line"], "ninl": r["ninl"], "match": a["match"], "match_id": a["match_id"]}
-        if self.ukf is not None:
-            eng.ukf_step(self.ukf, r["line"], a["match"], u=u)
-            res["x"] = self.ukf["x"]
-            res["P"] = self.ukf["P"]
-        return res
+        # measurement slot c = chunk c's line: range/bearing of its inlier centroid against the matched
+        # stored landmark's position; slots whose line missed (match < 0) are not used
+        eng.ukf_step(self.ukf, r["line"], a["hit_pos"], lm_valid=a["match"], valid_min=0, u=u)
+        return {"line": r["line"], "ninl": r["ninl"], "match": a["match"], "match_id": a["match_id"],
+                "x": self.ukf["x"], "P": self.ukf["P"]}
+
+    # ---- a known map (benchmark / test set-up; data movement only) -----------------------------
+    def install_map_from_lines(self, line, ninl, life=batch.Engine.LIFE):
+        """Fill every stream's table from line records [S, C, 8] of a first pass over its scan:
+        landmark c = line c with its tip placed on its centroid, so that a re-observation of the same
+        wall passes the 100 mm tip/centroid gate of Landmark.is_equal (landmarking.py:66-77; two
+        observations of one wall from the same pose do NOT pass it - tip and centroid are half a
+        chunk apart); the remaining slots hold the next stream's lines as clutter.  Lines that were
+        not extracted (ninl <= 0) become NaN rows, which never match."""
+        C, M, t = self.C, self.M, self.tables
+        own = line[..., [0, 1, 2, 3, 2, 3]].clone()
+        own[ninl <= 0] = float("nan")
+        k = min(C, M)
+        t["rows"].zero_()
+        t["rows"][:, :k] = own[:, :k]
+        k2 = min(2 * C, M)
+        if k2 > k:
+            t["rows"][:, k:k2] = torch.roll(own, 1, dims=0)[:, :k2 - k]
+        t["life"].zero_()
+        t["life"][:, :k2] = life
+        t["ids"].zero_()
+        t["ids"][:, :k2] = torch.arange(k2, dtype=torch.int32, device=line.device)
+        t["count"].fill_(k2)
+        t["next_id"].fill_(k2)
 
     # ---- end-to-end step: host buffers in, host buffers out -----------------------------
     def result_keys(self):
-        return ("line", "ninl", "match_id") + (("x", "P") if self.ukf is not None else ())
+        return ("line", "ninl", "match_id", "x", "P")
 
     def alloc_host_io(self):
         """Pinned host buffers for step_host: the scans in, the per-step results out."""

@@ -70,3 +70,92 @@ def ransac_lines(xy, npts=None, chunk=100, trials=100, thr=20.0, seed=0, scan_ba
 
 def max_threads():
     return int(lib().oracle_max_threads())
+
+
+# ---- UKF (oracle/ukf.c) ----------------------------------------------------------------------
+UKF_PREDICT, UKF_UPDATE, UKF_REDRAW = 1, 2, 4
+
+
+def ukf_params(dt=0.005, wheel_r=50.0, base_l=200.0, alpha=1e-4, beta=2.0, kappa=0.0,
+               var_dist=0.25, var_angle=0.09, Q=None):
+    """The 17 doubles oracle_ukf_step / lslam_ukf_step take (defaults: systemClass.py:7-29,
+    UKFMethods.py:6-7)."""
+    Q = np.eye(3) * 0.001 if Q is None else np.asarray(Q, dtype=np.float64)
+    return np.concatenate([[dt, wheel_r, base_l, alpha, beta, kappa, var_dist, var_angle],
+                           Q.reshape(9)]).astype(np.float64)
+
+
+def ukf_step(x, P, u, z, lm_pos, lm_valid=None, valid_min=1, zmode=0, params=None,
+             flags=UKF_PREDICT | UKF_UPDATE | UKF_REDRAW, sigmas_f=None, nthreads=0):
+    """Batched pinned-order UKF step.  x [F,3], P [F,3,3], u [F,2], z [F,L,zs], lm_pos [F,L,2],
+    lm_valid [F,L] int32 or None.  Returns (x_new, P_new, status[F]); inputs are not modified
+    (sigmas_f [F,7,3], when given, is read/written in place)."""
+    x = np.array(x, dtype=np.float64, order="C")
+    P = np.array(P, dtype=np.float64, order="C")
+    F = x.shape[0]
+    u = None if u is None else np.ascontiguousarray(u, dtype=np.float64)
+    if z is not None:
+        z = np.ascontiguousarray(z, dtype=np.float64)
+        L, zs = z.shape[1], z.shape[2]
+        lm_pos = np.ascontiguousarray(lm_pos, dtype=np.float64)
+    else:
+        L, zs = 0, 2
+    if lm_valid is not None:
+        lm_valid = np.ascontiguousarray(lm_valid, dtype=np.int32)
+    params = ukf_params() if params is None else np.ascontiguousarray(params, dtype=np.float64)
+    status = np.zeros(F, np.int32)
+    fn = lib().oracle_ukf_step
+    fn.restype = ctypes.c_int
+    rc = fn(_p(x, c_double_p), _p(P, c_double_p), _p(u, c_double_p), _p(z, c_double_p),
+            ctypes.c_int32(zs), ctypes.c_int32(zmode), _p(lm_pos, c_double_p) if z is not None else None,
+            _p(lm_valid, c_int32_p), ctypes.c_int32(valid_min), ctypes.c_int32(F), ctypes.c_int32(L),
+            _p(params, c_double_p), ctypes.c_int32(flags), _p(status, c_int32_p),
+            _p(sigmas_f, c_double_p), ctypes.c_int32(nthreads))
+    if rc != 0:
+        raise RuntimeError("oracle_ukf_step failed: %d" % rc)
+    return x, P, status
+
+
+# ---- association (oracle/assoc.c) and the whole pipeline -------------------------------------------
+def associate(query, tables, q_valid=None, mode=0, append=True, tolA=0.1, tolB=10.0, tol=100.0,
+              life_init=40, nthreads=0):
+    """Batched C association; same meaning as lslam_associate.  query [T,Q,6|8]; tables = dict of
+    rows [T,M,6], life, ids [T,M], count, next_id [T], updated IN PLACE.  Returns dict."""
+    query = np.ascontiguousarray(query, dtype=np.float64)
+    T, Q, qs = query.shape
+    M = tables["rows"].shape[1]
+    for k, ty in (("rows", np.float64), ("life", np.int32), ("ids", np.int32), ("count", np.int32), ("next_id", np.int32)):
+        assert tables[k].dtype == ty and tables[k].flags.c_contiguous, k
+    if q_valid is not None:
+        q_valid = np.ascontiguousarray(q_valid, dtype=np.int32)
+    out = {"match": np.empty((T, Q), np.int32), "match_id": np.empty((T, Q), np.int32),
+           "proj_ab": np.empty((T, Q, 2)), "hit_pos": np.empty((T, Q, 2))}
+    fn = lib().oracle_associate
+    fn.restype = ctypes.c_int
+    rc = fn(_p(query, c_double_p), ctypes.c_int32(qs), ctypes.c_int32(1 if qs == 8 else 0), _p(q_valid, c_int32_p),
+            ctypes.c_int32(T), ctypes.c_int32(Q), ctypes.c_int32(M), _p(tables["rows"], c_double_p),
+            _p(tables["life"], c_int32_p), _p(tables["ids"], c_int32_p), _p(tables["count"], c_int32_p),
+            _p(tables["next_id"], c_int32_p), ctypes.c_double(tolA), ctypes.c_double(tolB), ctypes.c_double(tol),
+            ctypes.c_int32(life_init), ctypes.c_int32(mode), ctypes.c_int32(int(bool(append))),
+            _p(out["match"], c_int32_p), _p(out["match_id"], c_int32_p), _p(out["proj_ab"], c_double_p),
+            _p(out["hit_pos"], c_double_p), ctypes.c_int32(nthreads))
+    if rc != 0:
+        raise RuntimeError("oracle_associate failed: %d" % rc)
+    return out
+
+
+def empty_tables(T, M):
+    return {"rows": np.zeros((T, M, 6)), "life": np.zeros((T, M), np.int32), "ids": np.zeros((T, M), np.int32),
+            "count": np.zeros(T, np.int32), "next_id": np.zeros(T, np.int32)}
+
+
+def pipeline_step(xy, tables, x, P, u=None, chunk=100, trials=100, thr=20.0, seed=0, scan_base=0,
+                  params=None, nthreads=0):
+    """One step of lidar_slam_b200.pipeline.ScanPipeline on the CPU (all three stages in C, OpenMP
+    over scans): RANSAC -> association (tables updated in place) -> UKF predict/update with the
+    matched lines as measurements.  Returns (ransac_out, assoc_out, x_new, P_new, status)."""
+    r = ransac_lines(xy, chunk=chunk, trials=trials, thr=thr, seed=seed, scan_base=scan_base, nthreads=nthreads)
+    a = associate(r["line"], tables, q_valid=r["ninl"], nthreads=nthreads)
+    xn, Pn, st = ukf_step(x, P, u, r["line"], a["hit_pos"], a["match"], valid_min=0, zmode=1, params=params,
+                          nthreads=nthreads)
+    return r, a, xn, Pn, st

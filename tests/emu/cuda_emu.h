@@ -157,6 +157,11 @@ static inline unsigned __reduce_or_sync(unsigned, unsigned v) { return emu_reduc
 // ---- scalar intrinsics ----
 static inline int __popc(unsigned v) { return __builtin_popcount(v); }
 static inline int __ffs(int v) { return __builtin_ffs(v); }
+static inline unsigned __fns(unsigned mask, unsigned base, int offset) {   // offset > 0 only
+    int cnt = 0;
+    for (unsigned b = base; b < 32; ++b) if ((mask >> b) & 1u) { if (++cnt == offset) return b; }
+    return 0xffffffffu;
+}
 static inline int __clz(int v) { return v ? __builtin_clz((unsigned)v) : 32; }
 static inline unsigned __brev(unsigned v) { unsigned r = 0; for (int i = 0; i < 32; ++i) r |= ((v >> i) & 1u) << (31 - i); return r; }
 static inline unsigned __funnelshift_l(unsigned lo, unsigned hi, unsigned s) {

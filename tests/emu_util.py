@@ -67,7 +67,7 @@ def emu_ransac_lines(xy, npts=None, chunk=100, trials=100, thr=20.0, seed=0, sca
 
 
 def emu_associate(queries, tables, q_valid=None, mode=0, append=True, layout=0, handle=None,
-                  tolA=0.1, tolB=10, tol=100, life_init=40):
+                  tolA=0.1, tolB=10, tol=100, life_init=40, hit_pos=None):
     """lslam_associate on the emulated library.  queries [T,Q,6|8]; tables = dict with rows
     [T,M,6], life [T,M], ids [T,M], count [T], next_id [T] (updated in place)."""
     h = handle or emu_handle()
@@ -81,5 +81,29 @@ def emu_associate(queries, tables, q_valid=None, mode=0, append=True, layout=0, 
         q_valid = np.ascontiguousarray(q_valid, dtype=np.int32)
     h.associate(ptr(queries), qs, layout, ptr(q_valid), T, Q, M, ptr(tables["rows"]), ptr(tables["life"]),
                 ptr(tables["ids"]), ptr(tables["count"]), ptr(tables["next_id"]), tolA, tolB, tol,
-                life_init, mode, append, ptr(match), ptr(match_id), ptr(proj))
+                life_init, mode, append, ptr(match), ptr(match_id), ptr(proj), ptr(hit_pos))
     return match, match_id, proj
+
+
+def emu_ukf_step(x, P, u, z, lm_pos, lm_valid=None, valid_min=1, zmode=0, params=None, flags=7,
+                 sigmas_f=None, handle=None):
+    """lslam_ukf_step on the emulated library (NumPy buffers stand in for device memory).
+    Returns (x_new, P_new, status); inputs are copied."""
+    from lidar_slam_b200 import batch
+    h = handle or emu_handle()
+    x = np.array(x, dtype=np.float64, order="C")
+    P = np.array(P, dtype=np.float64, order="C")
+    F = x.shape[0]
+    u = None if u is None else np.ascontiguousarray(u, dtype=np.float64)
+    L, zs = 0, 2
+    if z is not None:
+        z = np.ascontiguousarray(z, dtype=np.float64)
+        L, zs = z.shape[1], z.shape[2]
+        lm_pos = np.ascontiguousarray(lm_pos, dtype=np.float64)
+    if lm_valid is not None:
+        lm_valid = np.ascontiguousarray(lm_valid, dtype=np.int32)
+    status = np.full(F, -99, np.int32)
+    params = batch.Engine.ukf_params() if params is None else list(params)
+    h.ukf_step(ptr(x), ptr(P), ptr(u), ptr(z), zs, zmode, ptr(lm_pos) if z is not None else None,
+               ptr(lm_valid), valid_min, F, L, params, flags, ptr(status), ptr(sigmas_f))
+    return x, P, status

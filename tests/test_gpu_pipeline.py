@@ -1,0 +1,65 @@
+"""GPU parity of the whole step (lidar_slam_b200/pipeline.py: RANSAC -> association -> UKF through
+the C ABI) against the C pipeline on the same seeded scans, several steps with persistent tables
+and filters, device-resident and through the host-buffer path."""
+import numpy as np
+import pytest
+
+from lidar_slam_b200 import synth
+from tests import pipeline_util as pu, ukf_util as uu
+from tests.parity_util import assert_ransac_equal
+
+pytestmark = pytest.mark.gpu
+
+
+def test_pipeline_steps_match_cpu(gpu_engine):
+    import torch
+    from lidar_slam_b200 import pipeline
+    eng = gpu_engine
+    S, M, steps = 2048, 8, 3
+    xy = synth.random_room_scans(S, seed=12)
+    u = np.full((S, 2), 1.0)
+    want = pu.cpu_pipeline(xy, steps, M=M, u=u, seed=3, scan_base=77)
+    pipe = pipeline.ScanPipeline(eng, S, table_capacity=M, seed=3, scan_base=77)
+    pipe.ukf["u"].fill_(1.0)
+    xy_d = torch.from_numpy(xy).to(eng.device)
+    r = eng.ransac_lines(xy_d, seed=3, scan_base=77)
+    torch.cuda.synchronize()
+    assert_ransac_equal(want[0]["ransac"], {k: v.cpu().numpy() for k, v in r.items()}, "pipeline RANSAC")
+    # chain both sides from the oracle's line records for the map (they agree to 1e-5, not bitwise)
+    line_o = torch.from_numpy(want[0]["ransac"]["line"]).to(eng.device)
+    pipe.install_map_from_lines(line_o, r["ninl"])
+    for k in range(steps):
+        res = pipe.step(xy_d)
+        torch.cuda.synchronize()
+        m = res["match"].cpu().numpy()
+        assert np.array_equal(m, want[k]["assoc"]["match"]), "step %d match" % k
+        assert np.array_equal(res["match_id"].cpu().numpy(), want[k]["assoc"]["match_id"])
+        assert np.array_equal(pipe.tables["life"].cpu().numpy(), want[k]["tables"]["life"])
+        uu.assert_ukf_close((want[k]["x"], want[k]["P"], want[k]["status"]),
+                            (res["x"].cpu().numpy(), res["P"].cpu().numpy(), pipe.ukf["status"].cpu().numpy()),
+                            "pipeline step %d" % k)
+    assert (m >= 0).mean() > 0.9
+
+
+def test_host_path_equals_device_path(gpu_engine):
+    import torch
+    from lidar_slam_b200 import pipeline
+    eng = gpu_engine
+    S = 4096
+    xy = eng.synth_scans(S, seed=21)
+    a = pipeline.ScanPipeline(eng, S, seed=1)
+    b = pipeline.ScanPipeline(eng, S, seed=1)
+    r0 = eng.ransac_lines(xy, seed=1)
+    a.install_map_from_lines(r0["line"], r0["ninl"])
+    b.install_map_from_lines(r0["line"], r0["ninl"])
+    xy_h = b.alloc_host_io()
+    xy_h.copy_(xy)
+    torch.cuda.synchronize()
+    for _ in range(2):
+        ra = a.step(xy)
+        hb = b.step_host(xy_h)
+        torch.cuda.synchronize()
+        for k in b.result_keys():
+            assert torch.equal(ra[k].cpu().view(torch.uint8), hb[k].view(torch.uint8)), k
+    h2d, d2h = b.io_bytes()
+    assert h2d == xy_h.numel() * 8 and d2h == sum(hb[k].numel() * hb[k].element_size() for k in b.result_keys())

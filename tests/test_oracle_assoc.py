@@ -3,6 +3,7 @@
 import os
 
 import numpy as np
+import pytest
 
 from oracle import assoc
 
@@ -86,3 +87,17 @@ def test_table_roundtrip_and_stream():
     assert list(match) == [-1, 0, -1] and list(mid) == [0, 0, 2] and t.count == 2 and t.next_id == 3
     assert tuple(proj[1]) == (0.0, 100.0)        # a hit projects with the STORED landmark's a, b (:46)
     assert list(t.life[:2]) == [assoc.LIFE - 1, assoc.LIFE]
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_c_twin_matches_python(cport, mode):
+    """oracle/assoc.c (the fast CPU baseline) against oracle/assoc.py (pinned to the real module)."""
+    from tests import assoc_util as au
+    for T, M, pre, Q in [(50, 8, 0, 12), (50, 8, 8, 6), (20, 40, 37, 10), (10, 70, 66, 5)]:
+        queries, valid, tables = au.random_streams(T, Q, M, seed=M + mode, prefill=pre)
+        want = au.oracle_associate(queries, valid, tables, mode=mode)
+        t2 = {k: v.copy() for k, v in tables.items()}
+        o = cport.associate(queries, t2, q_valid=valid, mode=mode)
+        au.assert_assoc_equal(want, (o["match"], o["match_id"], o["proj_ab"], t2), "C twin")
+        hit = o["match"] >= 0
+        assert np.isnan(o["hit_pos"][~hit]).all() and not np.isnan(o["hit_pos"][hit]).any()

@@ -1,0 +1,112 @@
+"""UKF oracle: the literal NumPy restatement of filterpy + repaired UKFMethods (oracle/ukf.py), its
+frozen golden vector (tests/golden/ukf_kat7.npz, cross-checked in 60-digit arithmetic by the
+generator), and the pinned-order C restatement (oracle/ukf.c) against both."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import ukf
+from tests import ukf_util as uu
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "ukf_kat7.npz")
+
+
+def test_kat6_normalize_angle():
+    na = ukf.normalize_angle
+    assert na(0.0) == 0.0 and na(np.pi) == np.pi and na(-np.pi) == np.pi
+    assert na(2 * np.pi) == 0.0 and abs(na(3 * np.pi + 1e-9) - (-np.pi + 1e-9)) < 1e-12
+    assert abs(na(3 * np.pi - 1e-9) - (np.pi - 1e-9)) < 1e-12 and na(-0.5) == -0.5
+    for a in np.linspace(-20, 20, 401):
+        r = na(a)
+        assert -np.pi < r <= np.pi and abs(np.sin(r) - np.sin(a)) < 1e-12
+
+
+def test_callbacks_follow_the_reference_lines():
+    x = np.array([10.0, -5.0, 0.3])
+    # UKFMethods.py:17-24 by hand: R = 50, L = 200
+    got = ukf.transition_function(x, 0.01, np.array([1.0, 2.0]))
+    want = x + 0.01 * np.array([25 * np.cos(0.3) * 3.0, 25 * np.sin(0.3) * 3.0, -0.25 * 1.0 + 0.25 * 2.0])
+    np.testing.assert_allclose(got, want, rtol=1e-15)
+    z = ukf.transfer_function(x, [ukf._Pos(13.0, -1.0)])                  # :26-34
+    np.testing.assert_allclose(z, [5.0, np.arctan2(4.0, 3.0) - 0.3], rtol=1e-15)
+    s = np.array([[0., 0., np.pi - 0.1], [2., 4., -np.pi + 0.1]])
+    m = ukf.state_mean(s, np.array([0.5, 0.5]))                           # circular mean across the wrap
+    assert abs(abs(m[2]) - np.pi) < 1e-12 and m[0] == 1.0 and m[1] == 2.0
+    zm = ukf.z_mean(np.array([[1., np.pi - 0.1], [3., -np.pi + 0.1]]), np.array([0.5, 0.5]))
+    assert zm[0] == 2.0 and abs(abs(zm[1]) - np.pi) < 1e-12
+    assert ukf.residual_x(np.array([0., 0., 3.1]), np.array([0., 0., -3.1]))[2] == pytest.approx(6.2 - 2 * np.pi)
+    r = ukf.residual_h(np.array([5., 3.1, 7., -3.0]), np.array([1., -3.1, 2., 3.0]))
+    np.testing.assert_allclose(r, [4., 6.2 - 2 * np.pi, 5., 2 * np.pi - 6.0], rtol=1e-12)
+
+
+def test_system_wiring_matches_systemClass():
+    s = ukf.System([])
+    assert s.dt == 0.005 and s.varDist == 0.25 and s.varAngle == pytest.approx(0.09)
+    assert s.sigmas.n == 3 and s.sigmas.alpha == 1e-4 and s.sigmas.beta == 2 and s.sigmas.kappa == 0
+    assert np.array_equal(s.ukf.x, [0, 0, 0]) and np.array_equal(s.ukf.P, np.diag([.1, .1, .05]))
+    assert s.ukf.R.shape == (16, 16) and np.allclose(np.diag(s.ukf.R)[:2], [0.25, 0.09])
+    assert np.array_equal(s.ukf.Q, np.eye(3) * 0.001)
+    w = s.sigmas
+    assert w.Wm.sum() == pytest.approx(1.0, abs=1e-6) and w.Wm[0] == pytest.approx(1 - 1e8, rel=1e-6)
+
+
+def test_sigma_points_and_cholesky():
+    rng = np.random.default_rng(0)
+    A = rng.normal(size=(5, 5))
+    A = A @ A.T + np.eye(5)
+    U = ukf.cholesky_upper(A)
+    np.testing.assert_allclose(U.T @ U, A, rtol=1e-13)
+    assert np.allclose(U, np.triu(U))
+    with pytest.raises(np.linalg.LinAlgError):
+        ukf.cholesky_upper(-np.eye(2))
+    pts = ukf.MerweScaledSigmaPoints(3, 0.5, 2, 0)
+    sg = pts.sigma_points(np.array([1., 2., 3.]), np.diag([4., 9., 16.]))
+    assert sg.shape == (7, 3) and np.allclose(sg[1] - sg[0], [np.sqrt(0.75 * 4), 0, 0])
+    np.testing.assert_allclose(pts.Wm @ sg, [1., 2., 3.], atol=1e-12)
+
+
+def test_golden_kat7_literal_and_c_oracle(cport):
+    g = np.load(GOLD)
+    lm, u = g["lm"], g["u"]
+    # the literal restatement reproduces its frozen values (guards oracle/ukf.py against edits)
+    sysm = ukf.System([ukf._Pos(*p) for p in lm])
+    xc, Pc = np.zeros((1, 3)), np.diag([.1, .1, .05])[None]
+    for k in range(5):
+        sysm.ukf.predict(u=u)
+        sysm.ukf.update(g["z"][k], landmarks=sysm.landmarks)
+        np.testing.assert_allclose(sysm.ukf.x, g["x"][k], rtol=1e-9, atol=1e-12)
+        np.testing.assert_allclose(sysm.ukf.P, g["P"][k], rtol=1e-9, atol=1e-14)
+        # pinned-order C oracle, stepped with its own state: 1e-5 against the golden values AND
+        # against the 60-digit evaluation
+        xc, Pc, st = cport.ukf_step(xc, Pc, u[None], g["z"][k].reshape(1, 8, 2), lm[None])
+        assert st[0] == 0
+        for want_x, want_P in ((g["x"][k], g["P"][k]), (g["x_mp"][k], g["P_mp"][k])):
+            uu.assert_ukf_close((want_x[None], want_P[None], st), (xc, Pc, st), "KAT-7 step %d" % k)
+
+
+@pytest.mark.parametrize("alpha,rtol,scale", [(1e-4, 1e-5, 30.0), (1e-2, 1e-8, 300.0), (0.5, 1e-11, 300.0)])
+def test_c_oracle_matches_literal(cport, alpha, rtol, scale):
+    """The only differences are summation order / fma / solve-vs-inv, amplified by the sigma weights
+    (~1/alpha^2): 1e-5 at the reference's alpha = 1e-4, 1e-11 for a benign alpha."""
+    for L in (1, 4, 8):
+        d = uu.random_filters(24, L, seed=L, pos_scale=scale)
+        got = cport.ukf_step(d["x"], d["P"], d["u"], d["z"], d["lm_pos"], d["lm_valid"],
+                             params=cport.ukf_params(alpha=alpha))
+        wx, wP = np.zeros_like(d["x"]), np.zeros_like(d["P"])
+        for f in range(24):
+            sel = d["lm_valid"][f] > 0
+            wx[f], wP[f] = ukf.step_literal(d["x"][f], d["P"][f], d["u"][f], d["z"][f][sel].reshape(-1),
+                                            d["lm_pos"][f][sel], alpha=alpha)
+        uu.assert_ukf_close((wx, wP, got[2]), got, "alpha %g L %d" % (alpha, L), rtol=rtol)
+
+
+def test_no_redraw_variant(cport):
+    d = uu.random_filters(8, 4, seed=2, pos_scale=30.0)
+    got = cport.ukf_step(d["x"], d["P"], d["u"], d["z"], d["lm_pos"], None, flags=3,
+                         params=cport.ukf_params(alpha=1e-2))
+    for f in range(8):
+        wx, wP = ukf.step_literal(d["x"][f], d["P"][f], d["u"][f], d["z"][f].reshape(-1), d["lm_pos"][f],
+                                  alpha=1e-2, redraw=False)
+        uu.assert_ukf_close((wx[None], wP[None], got[2][f:f + 1]), (got[0][f:f + 1], got[1][f:f + 1], got[2][f:f + 1]),
+                            "no-redraw", rtol=1e-8)

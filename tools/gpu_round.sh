@@ -23,3 +23,8 @@ CMD2="python tools/ransac_one.py c2 0 0 0 262144"
 timeout 300 $CMD2 > $OUT/${TAG}_plain2.log 2>&1 && \
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:ransac_lines -s 2 -c 1 -f -o $OUT/${TAG}_ransac_c2 $CMD2 > $OUT/${TAG}_ncu_full.log 2>&1
 echo "full rc=$?" ; cat $OUT/${TAG}_plain2.log
+CMD3="python tools/ukf_one.py 1048576 4"
+timeout 300 $CMD3 > $OUT/${TAG}_plain3.log 2>&1 && \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:ukf_kernel -s 2 -c 1 -f -o $OUT/${TAG}_ukf $CMD3 > $OUT/${TAG}_ncu_full_ukf.log 2>&1
+echo "full ukf rc=$?" ; cat $OUT/${TAG}_plain3.log
+timeout 300 python tools/ukf_one.py 1048576 8 ; timeout 300 python tools/ukf_one.py 131072 32
