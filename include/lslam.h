@@ -44,8 +44,11 @@ const char *lslam_last_error(void *handle);
 /* ABI version of the loaded library (LSLAM_ABI_VERSION at build time). */
 #define LSLAM_ABI_VERSION 2
 int lslam_abi_version(void);
-/* Launch-shape tuning knobs ("ransac.tpt", "ransac.slots_per_cta", "ransac.threads");
- * 0 restores the built-in heuristic.  Results never depend on them. */
+/* Launch-shape tuning knobs; 0 restores the built-in heuristic.  Results never depend on them.
+ *   "ransac.kernel"  0 warp-specialised persistent kernel (default), 1 phase-structured kernel
+ *   "ransac.tpt"     trials per work item (1, 2, 4);  "ransac.slots_per_cta"  chunk slots per tile
+ *   "ransac.scorers", "ransac.posts", "ransac.ring"   warp counts / ring depth of kernel 0
+ *   "ransac.threads" CTA size of kernel 1 */
 int lslam_set_option(void *handle, const char *key, int64_t value);
 /* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */
 int64_t lslam_launch_count(void *handle);

@@ -4,6 +4,7 @@
 //        -Xcompiler -fPIC  (lidar_slam_b200/_build.py)
 #include "lslam_common.cuh"
 #include "ransac.cuh"
+#include "ransac_ws.cuh"
 #include "aux_kernels.cuh"
 #include "assoc.cuh"
 #include "ukf.cuh"
@@ -68,6 +69,15 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
     } else if (!strcmp(key, "ransac.threads")) {
         if (value < 0 || value > 1024 || value % 32) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.threads must be a multiple of 32 <= 1024");
         h->opt_threads = (int)value;
+    } else if (!strcmp(key, "ransac.kernel")) {
+        if (value < 0 || value > 1) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.kernel: 0 warp-specialised, 1 phase-structured");
+        h->opt_kernel = (int)value;
+    } else if (!strcmp(key, "ransac.scorers") || !strcmp(key, "ransac.posts")) {
+        if (value < 0 || value > 16) return fail(h, LSLAM_ERR_BAD_ARG, "%s out of range (0..16)", key);
+        (key[7] == 's' ? h->opt_scorers : h->opt_posts) = (int)value;
+    } else if (!strcmp(key, "ransac.ring")) {
+        if (value < 0 || value == 1 || value > 16) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.ring must be 0 or 2..16");
+        h->opt_ring = (int)value;
     } else {
         return fail(h, LSLAM_ERR_BAD_ARG, "unknown option '%s'", key);
     }
@@ -113,6 +123,44 @@ static int launch_ransac(Handle *h, RansacArgs a, int threads_target, cudaStream
     return LSLAM_OK;
 }
 
+// warp-specialised persistent kernel (ransac_ws.cuh): one CTA per SM
+template <int TPT>
+static int launch_ransac_ws(Handle *h, RansacArgs a, cudaStream_t st)
+{
+    auto kern = ransac_ws_kernel<TPT>;
+    a.ipc = (a.trials + TPT - 1) / TPT;
+    a.ws_ns = h->opt_scorers ? h->opt_scorers : 8;
+    a.ws_np = h->opt_posts ? h->opt_posts : 8;
+    if (a.ws_ns + a.ws_np + 1 > 20) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.scorers + ransac.posts must not exceed 19 warps");
+    // chunk slots per tile: about 800 work items (25 rounds of 32), bounded by the ring in shared memory
+    int G = h->opt_slots ? h->opt_slots : (800 + a.ipc / 2) / a.ipc;
+    if (G < 1) G = 1;
+    if ((long long)G > a.nslots) G = (int)a.nslots;
+    const int want_nb = h->opt_ring ? h->opt_ring : 4;
+    int NB = 0;
+    WsLayout L;
+    for (;; --G) {
+        for (NB = want_nb; NB >= 2; --NB) {
+            L = ws_layout(G, a.chunk, a.trials, a.W, NB, a.ws_np);
+            if (L.total <= (size_t)h->smem_optin) break;
+        }
+        if (NB >= 2 || G == 1) break;
+    }
+    if (NB < 2)
+        return fail(h, LSLAM_ERR_CAPACITY, "chunk=%d with trials=%d does not fit a 2-deep ring in %d B of shared memory",
+                    a.chunk, a.trials, h->smem_optin);
+    a.G = G;
+    a.ws_nb = NB;
+    const long long ntiles = (a.nslots + G - 1) / G;
+    const long long grid = ntiles < (long long)h->sms ? ntiles : (long long)h->sms;
+    const int threads = (a.ws_ns + a.ws_np + 1) * 32;
+    LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
+    LSLAM_LAUNCH(kern, (unsigned)grid, (unsigned)threads, L.total, st, a);
+    h->launches++;
+    LSLAM_CUDA_TRY(h, cudaGetLastError());
+    return LSLAM_OK;
+}
+
 extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t *npts, int32_t B, int32_t N,
                                   int32_t chunk, int32_t trials, double thr, uint64_t seed,
                                   uint64_t scan_base, double *line, int32_t *ninl, int32_t *win_trial,
@@ -143,6 +191,14 @@ extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t 
     const int tpt = h->opt_tpt ? h->opt_tpt : 2;
     const int threads = h->opt_threads ? h->opt_threads : 256;
     cudaStream_t st = (cudaStream_t)stream;
+    a.ws_ns = a.ws_np = a.ws_nb = 0;
+    if (h->opt_kernel == 0) {
+        switch (tpt) {
+        case 1: return launch_ransac_ws<1>(h, a, st);
+        case 2: return launch_ransac_ws<2>(h, a, st);
+        default: return launch_ransac_ws<4>(h, a, st);
+        }
+    }
     switch (tpt) {
     case 1: return launch_ransac<1, 512, 2>(h, a, threads, st);
     case 2: return launch_ransac<2, 512, 2>(h, a, threads, st);

@@ -21,6 +21,7 @@ struct Handle {
     int smem_optin = 0;
     int64_t launches = 0;
     int opt_tpt = 0, opt_slots = 0, opt_threads = 0;
+    int opt_kernel = 0, opt_scorers = 0, opt_posts = 0, opt_ring = 0;
     unsigned long long *counters_d = nullptr;
     char err[512] = "";
 };

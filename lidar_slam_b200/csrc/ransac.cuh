@@ -48,6 +48,7 @@ struct RansacArgs {
     int G;                          // chunk slots per CTA
     int ipc;                        // work items (threads) per chunk = ceil(trials / TPT)
     long long nslots;               // B * C
+    int ws_ns, ws_np, ws_nb;        // warp-specialised kernel: scorer warps, post warps, ring depth
 };
 
 constexpr int kMaxCand = 8;         // candidates with precomputed models; more -> generic loop

@@ -9,6 +9,38 @@ from lidar_slam_b200 import synth
 from tests.parity_util import assert_ransac_equal
 
 
+@pytest.fixture(params=[0, 1], ids=["ws", "phased"], autouse=True)
+def ransac_kernel(request, emu):
+    """Every test runs on both RANSAC kernels: 0 = warp-specialised persistent (csrc/ransac_ws.cuh,
+    the default), 1 = phase-structured (csrc/ransac.cuh)."""
+    h = emu.emu_handle()
+    h.set_option("ransac.kernel", request.param)
+    yield request.param
+    h.set_option("ransac.kernel", 0)
+
+
+def test_ws_role_shapes(emu, cport, ransac_kernel):
+    """Warp-specialised kernel: results do not depend on the number of scorer / post warps, the ring
+    depth or the tile size (incl. a ring deeper than the tile count and a single post warp)."""
+    if ransac_kernel != 0:
+        pytest.skip("options of kernel 0")
+    xy = synth.random_room_scans(9, seed=8)
+    npts = np.array([360, 360, 301, 360, 2, 360, 360, 259, 360], np.int32)
+    want = cport.ransac_lines(xy, npts=npts, seed=2)
+    h = emu.emu_handle()
+    try:
+        for ns, np_, ring, g in ((1, 1, 2, 1), (3, 2, 2, 5), (8, 8, 4, 0), (2, 5, 6, 3), (12, 7, 3, 16)):
+            h.set_option("ransac.scorers", ns)
+            h.set_option("ransac.posts", np_)
+            h.set_option("ransac.ring", ring)
+            h.set_option("ransac.slots_per_cta", g)
+            got = emu.emu_ransac_lines(xy, npts=npts, seed=2)
+            assert_ransac_equal(want, got, "ns=%d np=%d ring=%d g=%d" % (ns, np_, ring, g))
+    finally:
+        for k in ("ransac.scorers", "ransac.posts", "ransac.ring", "ransac.slots_per_cta"):
+            h.set_option(k, 0)
+
+
 def test_random_rooms_all_thread_layouts(emu, cport):
     xy = synth.random_room_scans(12, seed=3)
     want = cport.ransac_lines(xy, seed=7, scan_base=123456789012)

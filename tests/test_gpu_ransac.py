@@ -13,6 +13,33 @@ from tests.parity_util import assert_ransac_equal
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(params=[0, 1], ids=["ws", "phased"], autouse=True)
+def ransac_kernel(request, gpu_engine):
+    """Both RANSAC kernels: 0 = warp-specialised persistent (default), 1 = phase-structured."""
+    gpu_engine.set_option("ransac.kernel", request.param)
+    yield request.param
+    gpu_engine.set_option("ransac.kernel", 0)
+
+
+def test_ws_role_shapes(gpu_engine, cport, ransac_kernel):
+    if ransac_kernel != 0:
+        pytest.skip("options of kernel 0")
+    xy = synth.random_room_scans(3000, seed=8)
+    npts = np.full(3000, 360, np.int32)
+    npts[::7] = 301
+    npts[5::11] = 2
+    want = cport.ransac_lines(xy, npts=npts, seed=2)
+    try:
+        for ns, np_, ring, g in ((1, 1, 2, 1), (3, 2, 2, 5), (8, 8, 4, 0), (2, 5, 6, 3), (12, 7, 3, 16), (10, 6, 4, 16)):
+            for k, v in (("ransac.scorers", ns), ("ransac.posts", np_), ("ransac.ring", ring), ("ransac.slots_per_cta", g)):
+                gpu_engine.set_option(k, v)
+            got = run_gpu(gpu_engine, xy, npts=npts, seed=2)
+            assert_ransac_equal(want, got, "ns=%d np=%d ring=%d g=%d" % (ns, np_, ring, g))
+    finally:
+        for k in ("ransac.scorers", "ransac.posts", "ransac.ring", "ransac.slots_per_cta"):
+            gpu_engine.set_option(k, 0)
+
+
 def to_np(out):
     import torch
     torch.cuda.synchronize()

@@ -11,7 +11,7 @@ echo "== smoke" ; timeout 300 python __graft_entry__.py --smoke > $OUT/${TAG}_sm
 echo "== bench" ; timeout 600 python bench.py > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err ; echo "bench rc=$?" ; cat $OUT/${TAG}_bench.json ; tail -3 $OUT/${TAG}_bench.err
 echo "== bench reference" ; timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $OUT/${TAG}_bench_ref.json 2>> $OUT/${TAG}_bench.err ; cat $OUT/${TAG}_bench_ref.json
 if [ "${2:-}" != "skip-sweep" ]; then
-  echo "== sweep" ; timeout 600 python tools/ransac_sweep.py > $OUT/${TAG}_sweep.log 2>&1 ; echo "sweep rc=$?" ; tail -5 $OUT/${TAG}_sweep.log
+  echo "== sweep" ; timeout 900 python tools/ransac_sweep.py > $OUT/${TAG}_sweep.log 2>&1 ; echo "sweep rc=$?" ; tail -5 $OUT/${TAG}_sweep.log
 fi
 echo "== ncu launches"
 CMD="python bench.py --steps 2 --warmup 3 --scans 262144 --no-cpu --no-e2e"
@@ -19,9 +19,9 @@ timeout 300 $CMD > $OUT/${TAG}_plain.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu_launches.log 2>&1
 echo "launches rc=$?"
 echo "== ncu full"
-CMD2="python tools/ransac_one.py c2 0 0 0 262144"
+CMD2="python tools/ransac_one.py c2 262144"
 timeout 300 $CMD2 > $OUT/${TAG}_plain2.log 2>&1 && \
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:ransac_lines -s 2 -c 1 -f -o $OUT/${TAG}_ransac_c2 $CMD2 > $OUT/${TAG}_ncu_full.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:ransac_ -s 2 -c 1 -f -o $OUT/${TAG}_ransac_c2 $CMD2 > $OUT/${TAG}_ncu_full.log 2>&1
 echo "full rc=$?" ; cat $OUT/${TAG}_plain2.log
 CMD3="python tools/ukf_one.py 1048576 4"
 timeout 300 $CMD3 > $OUT/${TAG}_plain3.log 2>&1 && \

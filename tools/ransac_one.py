@@ -1,5 +1,5 @@
 """Run lslam_ransac_lines a few times on one configuration (for ncu captures).
-usage: ransac_one.py <c2|c3> [tpt slots threads] [B]"""
+usage: ransac_one.py <c2|c3> [B] [key=value ...]   e.g. ransac_one.py c2 262144 kernel=1 tpt=2"""
 import os
 import sys
 
@@ -9,17 +9,16 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from lidar_slam_b200 import batch  # noqa: E402
 
 cfg = sys.argv[1] if len(sys.argv) > 1 else "c2"
-tpt, slots, threads = (int(v) for v in sys.argv[2:5]) if len(sys.argv) >= 5 else (0, 0, 0)
 eng = batch.Engine(0)
-eng.set_option("ransac.tpt", tpt)
-eng.set_option("ransac.slots_per_cta", slots)
-eng.set_option("ransac.threads", threads)
+for kv in sys.argv[3:]:
+    k, v = kv.split("=")
+    eng.set_option("ransac." + k, int(v))
 if cfg == "c2":
-    B = int(sys.argv[5]) if len(sys.argv) > 5 else 262144
+    B = int(sys.argv[2]) if len(sys.argv) > 2 else 262144
     xy = eng.synth_scans(B, seed=1)
     kw = {}
 else:
-    B = int(sys.argv[5]) if len(sys.argv) > 5 else 256
+    B = int(sys.argv[2]) if len(sys.argv) > 2 else 256
     xy = eng.synth_scans(B, beams=8192, seed=2)
     kw = {"chunk": 410, "trials": 1024}
 out = eng.alloc_ransac_out(B, xy.shape[1], kw.get("chunk", 100))
@@ -28,4 +27,4 @@ for _ in range(3):
 torch.cuda.synchronize()
 e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
 e0.record(); eng.ransac_lines(xy, out=out, **kw); e1.record(); torch.cuda.synchronize()
-print(cfg, tpt, slots, threads, B, "ms", e0.elapsed_time(e1), eng.ransac_counters())
+print(cfg, sys.argv[3:], B, "ms", e0.elapsed_time(e1), eng.ransac_counters())

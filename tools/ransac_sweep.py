@@ -1,5 +1,6 @@
 """GPU exploration: time lslam_ransac_lines over launch shapes (CUDA events, device-resident
-input larger than L2), and probe the fp64 issue rate.  Writes gpurun_out/ransac_sweep.json."""
+input larger than L2).  Writes gpurun_out/ransac_sweep.json.
+usage: ransac_sweep.py [c2|c3|both]"""
 import json
 import os
 import sys
@@ -8,6 +9,9 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from lidar_slam_b200 import batch  # noqa: E402
+
+KEYS = ("ransac.kernel", "ransac.tpt", "ransac.slots_per_cta", "ransac.scorers", "ransac.posts", "ransac.ring",
+        "ransac.threads")
 
 
 def time_call(fn, iters=5, warm=2):
@@ -24,52 +28,54 @@ def time_call(fn, iters=5, warm=2):
     return e0.elapsed_time(e1) / iters
 
 
-def main():
-    eng = batch.Engine(0)
-    res = {"fp64_peak_tflops": [eng.fp64_peak(30.0) for _ in range(3)]}
-    print("fp64 probe TFLOP/s:", res["fp64_peak_tflops"], flush=True)
-    B = int(os.environ.get("SWEEP_B", 262144))
-    xy = eng.synth_scans(B, seed=1)
-    out = eng.alloc_ransac_out(B, 360)
-    rows = []
-    combos = [(0, 0, 0)]
-    for tpt in (1, 2, 4):
-        for slots in (8, 16, 32, 64):
-            for threads in (256, 384, 512):
-                combos.append((tpt, slots, threads))
-    for tpt, slots, threads in combos:
-        eng.set_option("ransac.tpt", tpt)
-        eng.set_option("ransac.slots_per_cta", slots)
-        eng.set_option("ransac.threads", threads)
+def run(eng, combos, fn, phe, tag, rows):
+    for combo in combos:
+        for k, v in zip(KEYS, combo):
+            eng.set_option(k, v)
         try:
-            ms = time_call(lambda: eng.ransac_lines(xy, out=out))
-        except Exception as exc:  # capacity errors for some shapes
-            print(tpt, slots, threads, "ERR", exc, flush=True)
+            ms = time_call(fn)
+        except Exception as exc:
+            print(tag, combo, "ERR", exc, flush=True)
             continue
-        phe = B * 36000.0
-        row = {"tpt": tpt, "slots": slots, "threads": threads, "ms": ms, "scans_per_s": B / ms * 1e3,
-               "alg_tflops": phe * 8 / ms * 1e-9}
+        row = dict(zip([k.split(".")[1] for k in KEYS], combo))
+        row.update(ms=ms, alg_tflops=phe * 8 / ms * 1e-9)
         rows.append(row)
-        print(row, flush=True)
-    res["c2"] = rows
-    for k in ("ransac.tpt", "ransac.slots_per_cta", "ransac.threads"):
+        print(tag, row, flush=True)
+    for k in KEYS:
         eng.set_option(k, 0)
-    # C3: 8192-point scans, chunk 410, 1024 trials
-    B3 = 256
-    xy3 = eng.synth_scans(B3, beams=8192, seed=2)
-    out3 = eng.alloc_ransac_out(B3, 8192, 410)
-    rows3 = []
-    for tpt, slots, threads in ((0, 0, 0), (4, 1, 256), (4, 2, 512), (2, 1, 512), (2, 1, 256), (2, 2, 512), (2, 4, 512), (1, 1, 512), (1, 2, 512)):
-        eng.set_option("ransac.tpt", tpt)
-        eng.set_option("ransac.slots_per_cta", slots)
-        eng.set_option("ransac.threads", threads)
-        ms = time_call(lambda: eng.ransac_lines(xy3, chunk=410, trials=1024, out=out3), iters=3, warm=1)
-        phe = B3 * 8192.0 * 1024
-        row = {"tpt": tpt, "slots": slots, "threads": threads, "ms": ms, "scans_per_s": B3 / ms * 1e3,
-               "alg_tflops": phe * 8 / ms * 1e-9}
-        rows3.append(row)
-        print("C3", row, flush=True)
-    res["c3"] = rows3
+
+
+def main():
+    which = sys.argv[1] if len(sys.argv) > 1 else "both"
+    eng = batch.Engine(0)
+    res = {"fp64_peak_tflops": eng.fp64_peak(30.0)}
+    print("fp64 probe TFLOP/s:", res["fp64_peak_tflops"], flush=True)
+    if which in ("c2", "both"):
+        B = int(os.environ.get("SWEEP_B", 262144))
+        xy = eng.synth_scans(B, seed=1)
+        out = eng.alloc_ransac_out(B, 360)
+        combos = [(1, 0, 0, 0, 0, 0, 0), (0, 0, 0, 0, 0, 0, 0)]
+        for tpt in (2, 4):
+            for slots in (8, 16, 32):
+                for ns, np_ in ((8, 8), (12, 7), (8, 4), (12, 4), (10, 9), (6, 6), (4, 4)):
+                    for ring in (3, 4):
+                        combos.append((0, tpt, slots, ns, np_, ring, 0))
+        rows = []
+        run(eng, combos, lambda: eng.ransac_lines(xy, out=out), B * 36000.0, "C2", rows)
+        res["c2"] = rows
+        del xy, out
+    if which in ("c3", "both"):
+        B3 = 256
+        xy3 = eng.synth_scans(B3, beams=8192, seed=2)
+        out3 = eng.alloc_ransac_out(B3, 8192, 410)
+        combos = [(1, 0, 0, 0, 0, 0, 0), (0, 0, 0, 0, 0, 0, 0)]
+        for tpt in (2, 4):
+            for slots in (1, 2, 4):
+                for ns, np_ in ((8, 8), (12, 4), (12, 7), (16, 3)):
+                    combos.append((0, tpt, slots, ns, np_, 0, 0))
+        rows3 = []
+        run(eng, combos, lambda: eng.ransac_lines(xy3, chunk=410, trials=1024, out=out3), B3 * 8192.0 * 1024, "C3", rows3)
+        res["c3"] = rows3
     print(eng.ransac_counters())
     os.makedirs("gpurun_out", exist_ok=True)
     json.dump(res, open("gpurun_out/ransac_sweep.json", "w"), indent=1)
