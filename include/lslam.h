@@ -45,9 +45,9 @@ const char *lslam_last_error(void *handle);
 #define LSLAM_ABI_VERSION 2
 int lslam_abi_version(void);
 /* Launch-shape tuning knobs; 0 restores the built-in heuristic.  Results never depend on them.
- *   "ransac.kernel"  0 warp-specialised persistent kernel (default), 1 phase-structured kernel
+ *   "ransac.kernel"  0 default, 1 phase-structured kernel, 2 warp-specialised persistent kernel
  *   "ransac.tpt"     trials per work item (1, 2, 4);  "ransac.slots_per_cta"  chunk slots per tile
- *   "ransac.scorers", "ransac.posts", "ransac.ring"   warp counts / ring depth of kernel 0
+ *   "ransac.scorers", "ransac.posts", "ransac.ring"   warp counts / ring depth of kernel 2
  *   "ransac.threads" CTA size of kernel 1 */
 int lslam_set_option(void *handle, const char *key, int64_t value);
 /* Number of kernels this handle has launched since creation (bench.py's gpu_launches). */

@@ -13,6 +13,12 @@
 
 using namespace lslam;
 
+// which RANSAC kernel "ransac.kernel = 0" means: 1 phase-structured (ransac.cuh), 2 warp-specialised
+// persistent (ransac_ws.cuh); set from the measurements in profiles/
+#ifndef LSLAM_DEFAULT_RANSAC_KERNEL
+#define LSLAM_DEFAULT_RANSAC_KERNEL 1
+#endif
+
 // ---- handle ------------------------------------------------------------------------------
 extern "C" int lslam_abi_version(void) { return LSLAM_ABI_VERSION; }
 
@@ -70,7 +76,7 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
         if (value < 0 || value > 1024 || value % 32) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.threads must be a multiple of 32 <= 1024");
         h->opt_threads = (int)value;
     } else if (!strcmp(key, "ransac.kernel")) {
-        if (value < 0 || value > 1) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.kernel: 0 warp-specialised, 1 phase-structured");
+        if (value < 0 || value > 2) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.kernel: 0 default, 1 phase-structured, 2 warp-specialised");
         h->opt_kernel = (int)value;
     } else if (!strcmp(key, "ransac.scorers") || !strcmp(key, "ransac.posts")) {
         if (value < 0 || value > 16) return fail(h, LSLAM_ERR_BAD_ARG, "%s out of range (0..16)", key);
@@ -192,7 +198,8 @@ extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t 
     const int threads = h->opt_threads ? h->opt_threads : 256;
     cudaStream_t st = (cudaStream_t)stream;
     a.ws_ns = a.ws_np = a.ws_nb = 0;
-    if (h->opt_kernel == 0) {
+    const int kernel = h->opt_kernel ? h->opt_kernel : LSLAM_DEFAULT_RANSAC_KERNEL;
+    if (kernel == 2) {
         switch (tpt) {
         case 1: return launch_ransac_ws<1>(h, a, st);
         case 2: return launch_ransac_ws<2>(h, a, st);

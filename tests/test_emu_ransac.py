@@ -9,10 +9,10 @@ from lidar_slam_b200 import synth
 from tests.parity_util import assert_ransac_equal
 
 
-@pytest.fixture(params=[0, 1], ids=["ws", "phased"], autouse=True)
+@pytest.fixture(params=[2, 1], ids=["ws", "phased"], autouse=True)
 def ransac_kernel(request, emu):
-    """Every test runs on both RANSAC kernels: 0 = warp-specialised persistent (csrc/ransac_ws.cuh,
-    the default), 1 = phase-structured (csrc/ransac.cuh)."""
+    """Every test runs on both RANSAC kernels: 2 = warp-specialised persistent (csrc/ransac_ws.cuh),
+    1 = phase-structured (csrc/ransac.cuh)."""
     h = emu.emu_handle()
     h.set_option("ransac.kernel", request.param)
     yield request.param
@@ -22,8 +22,8 @@ def ransac_kernel(request, emu):
 def test_ws_role_shapes(emu, cport, ransac_kernel):
     """Warp-specialised kernel: results do not depend on the number of scorer / post warps, the ring
     depth or the tile size (incl. a ring deeper than the tile count and a single post warp)."""
-    if ransac_kernel != 0:
-        pytest.skip("options of kernel 0")
+    if ransac_kernel != 2:
+        pytest.skip("options of kernel 2")
     xy = synth.random_room_scans(9, seed=8)
     npts = np.array([360, 360, 301, 360, 2, 360, 360, 259, 360], np.int32)
     want = cport.ransac_lines(xy, npts=npts, seed=2)

@@ -13,17 +13,17 @@ from tests.parity_util import assert_ransac_equal
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=[0, 1], ids=["ws", "phased"], autouse=True)
+@pytest.fixture(params=[2, 1], ids=["ws", "phased"], autouse=True)
 def ransac_kernel(request, gpu_engine):
-    """Both RANSAC kernels: 0 = warp-specialised persistent (default), 1 = phase-structured."""
+    """Both RANSAC kernels: 2 = warp-specialised persistent, 1 = phase-structured."""
     gpu_engine.set_option("ransac.kernel", request.param)
     yield request.param
     gpu_engine.set_option("ransac.kernel", 0)
 
 
 def test_ws_role_shapes(gpu_engine, cport, ransac_kernel):
-    if ransac_kernel != 0:
-        pytest.skip("options of kernel 0")
+    if ransac_kernel != 2:
+        pytest.skip("options of kernel 2")
     xy = synth.random_room_scans(3000, seed=8)
     npts = np.full(3000, 360, np.int32)
     npts[::7] = 301

@@ -4,6 +4,7 @@ usage: ncu_lines.py <report.ncu-rep> <kernel-mangled-substring> [topN]"""
 import csv, io, re, subprocess, sys, os, tempfile
 rep, ksub = sys.argv[1], sys.argv[2]
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
+SRC = sys.argv[4] if len(sys.argv) > 4 else 'ransac.cuh'
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 so = os.path.join(root, "lidar_slam_b200/csrc/liblslam.so")
 tmp = tempfile.mkdtemp()
@@ -36,19 +37,19 @@ for r in rows[2:]:
     if fr:
         key = fr[-1]
         for f, l in fr[::-1]:
-            if f == 'ransac.cuh': key = (f, l); break
+            if f == SRC: key = (f, l); break
     a = agg.setdefault(key, [0, 0]); a[0] += ex; a[1] += smp
-src = open(os.path.join(root, "lidar_slam_b200/csrc/ransac.cuh")).read().split("\n")
+src = open(os.path.join(root, "lidar_slam_b200/csrc", SRC)).read().split("\n")
 print("total warp-instructions %d, samples %d" % (tot, ts))
 # phase totals by line ranges (markers in the source)
 marks = [(i + 1, l.strip()) for i, l in enumerate(src) if "=================" in l]
 marks = [(1, "prologue/staging")] + marks + [(len(src) + 1, "end")]
 for (a, name), (b, _) in zip(marks[:-1], marks[1:]):
-    e = sum(v[0] for k, v in agg.items() if k[0] == 'ransac.cuh' and a <= k[1] < b)
-    s = sum(v[1] for k, v in agg.items() if k[0] == 'ransac.cuh' and a <= k[1] < b)
+    e = sum(v[0] for k, v in agg.items() if k[0] == SRC and a <= k[1] < b)
+    s = sum(v[1] for k, v in agg.items() if k[0] == SRC and a <= k[1] < b)
     print("  %5.1f%% inst %5.1f%% smp  lines %d-%d %s" % (100 * e / tot, 100 * s / ts, a, b - 1, name[:70]))
-e = sum(v[0] for k, v in agg.items() if k[0] != 'ransac.cuh'); s = sum(v[1] for k, v in agg.items() if k[0] != 'ransac.cuh')
+e = sum(v[0] for k, v in agg.items() if k[0] != SRC); s = sum(v[1] for k, v in agg.items() if k[0] != SRC)
 print("  %5.1f%% inst %5.1f%% smp  (other files / unmapped)" % (100 * e / tot, 100 * s / ts))
 for k, v in sorted(agg.items(), key=lambda x: -x[1][1])[:top]:
-    txt = src[k[1] - 1].strip()[:80] if k[0] == 'ransac.cuh' and k[1] > 0 else ''
+    txt = src[k[1] - 1].strip()[:80] if k[0] == SRC and k[1] > 0 else ''
     print('%5.1f%% inst %5.1f%% smp  %s:%d  %s' % (100 * v[0] / tot, 100 * v[1] / ts, k[0], k[1], txt))
