@@ -79,7 +79,7 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
         if (value < 0 || value > 2) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.kernel: 0 default, 1 phase-structured, 2 warp-specialised");
         h->opt_kernel = (int)value;
     } else if (!strcmp(key, "ransac.scorers") || !strcmp(key, "ransac.posts")) {
-        if (value < 0 || value > 16) return fail(h, LSLAM_ERR_BAD_ARG, "%s out of range (0..16)", key);
+        if (value < 0 || value > 29) return fail(h, LSLAM_ERR_BAD_ARG, "%s out of range (0..29)", key);
         (key[7] == 's' ? h->opt_scorers : h->opt_posts) = (int)value;
     } else if (!strcmp(key, "ransac.ring")) {
         if (value < 0 || value == 1 || value > 16) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.ring must be 0 or 2..16");
@@ -130,19 +130,15 @@ static int launch_ransac(Handle *h, RansacArgs a, int threads_target, cudaStream
 }
 
 // warp-specialised persistent kernel (ransac_ws.cuh): one CTA per SM
-template <int TPT>
+template <int TPT, int MAXT>
 static int launch_ransac_ws(Handle *h, RansacArgs a, cudaStream_t st)
 {
-    auto kern = ransac_ws_kernel<TPT>;
-    a.ipc = (a.trials + TPT - 1) / TPT;
-    a.ws_ns = h->opt_scorers ? h->opt_scorers : 8;
-    a.ws_np = h->opt_posts ? h->opt_posts : 8;
-    if (a.ws_ns + a.ws_np + 1 > 20) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.scorers + ransac.posts must not exceed 19 warps");
+    auto kern = ransac_ws_kernel<TPT, MAXT>;
     // chunk slots per tile: about 800 work items (25 rounds of 32), bounded by the ring in shared memory
     int G = h->opt_slots ? h->opt_slots : (800 + a.ipc / 2) / a.ipc;
     if (G < 1) G = 1;
     if ((long long)G > a.nslots) G = (int)a.nslots;
-    const int want_nb = h->opt_ring ? h->opt_ring : 4;
+    const int want_nb = h->opt_ring ? h->opt_ring : 3;
     int NB = 0;
     WsLayout L;
     for (;; --G) {
@@ -159,12 +155,25 @@ static int launch_ransac_ws(Handle *h, RansacArgs a, cudaStream_t st)
     a.ws_nb = NB;
     const long long ntiles = (a.nslots + G - 1) / G;
     const long long grid = ntiles < (long long)h->sms ? ntiles : (long long)h->sms;
-    const int threads = (a.ws_ns + a.ws_np + 1) * 32;
+    const int threads = (a.ws_ns + a.ws_np + 2) * 32;
     LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
     LSLAM_LAUNCH(kern, (unsigned)grid, (unsigned)threads, L.total, st, a);
     h->launches++;
     LSLAM_CUDA_TRY(h, cudaGetLastError());
     return LSLAM_OK;
+}
+
+// warp-specialised persistent kernel (ransac_ws.cuh): one CTA per SM; register budget by CTA size
+template <int TPT>
+static int dispatch_ransac_ws(Handle *h, RansacArgs a, cudaStream_t st)
+{
+    a.ipc = (a.trials + TPT - 1) / TPT;
+    a.ws_ns = h->opt_scorers ? h->opt_scorers : 8;
+    a.ws_np = h->opt_posts ? h->opt_posts : 8;
+    const int warps = a.ws_ns + a.ws_np + 2;
+    if (warps > 32) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.scorers + ransac.posts must not exceed 30 warps");
+    if (warps <= 20) return launch_ransac_ws<TPT, 640>(h, a, st);
+    return launch_ransac_ws<TPT, 1024>(h, a, st);
 }
 
 extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t *npts, int32_t B, int32_t N,
@@ -201,9 +210,9 @@ extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t 
     const int kernel = h->opt_kernel ? h->opt_kernel : LSLAM_DEFAULT_RANSAC_KERNEL;
     if (kernel == 2) {
         switch (tpt) {
-        case 1: return launch_ransac_ws<1>(h, a, st);
-        case 2: return launch_ransac_ws<2>(h, a, st);
-        default: return launch_ransac_ws<4>(h, a, st);
+        case 1: return dispatch_ransac_ws<1>(h, a, st);
+        case 2: return dispatch_ransac_ws<2>(h, a, st);
+        default: return dispatch_ransac_ws<4>(h, a, st);
         }
     }
     switch (tpt) {

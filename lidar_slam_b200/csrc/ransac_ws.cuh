@@ -1,21 +1,24 @@
-// ransac_ws.cuh - K1/K2, warp-specialised persistent form (the default RANSAC kernel).
+// ransac_ws.cuh - K1/K2, warp-specialised persistent form (`ransac.kernel = 2`).
 //
 // Same semantics and the same arithmetic building blocks as ransac.cuh (the phase-structured
-// kernel, kept as `ransac.kernel = 1`); what changes is how the work is scheduled on an SM.
-// Measured on B200 (profiles/r01a_ransac_c2_ncu_summary.txt): with every warp of a CTA walking
-// through stage -> score -> select -> decide -> refit between block barriers, and the co-resident
-// CTAs doing so in lock step, the fp64 pipe - the unit that bounds this kernel - idles whenever the
-// CTAs are in their latency-bound phases (52 % busy).  Here ONE persistent CTA per SM runs three
-// roles concurrently on a ring of NB tile buffers in shared memory:
-//   producer  (1 thread)   TMA bulk copy (cp.async.bulk, SASS UBLKCP) of the next tile's points,
-//                          completion on an mbarrier; runs NB tiles ahead of the scorers
+// kernel, `ransac.kernel = 1`); what changes is how the work is scheduled on an SM.  Measured on
+// B200 (profiles/r01a_ransac_c2_ncu_summary.txt): with every warp of a CTA walking through
+// stage -> score -> select -> decide -> refit between block barriers, and the co-resident CTAs
+// doing so in lock step, the fp64 pipe - the unit that bounds this kernel - idles whenever the CTAs
+// are in their latency-bound phases (52 % busy).  Here ONE persistent CTA per SM runs four roles
+// concurrently on a ring of NB tile buffers in shared memory:
+//   loader    (1 warp)     per tile: slot table (geometry of the G chunk slots), TMA bulk copy of the
+//                          tile's points (cp.async.bulk, SASS UBLKCP, completion on an mbarrier), then
+//                          the per-chunk coordinate scale the re-check band is derived from
 //   scorers   (NS warps)   the hot loop only: thread per (chunk, TPT trials), 3 DFMA + 1 DADD per
-//                          point-hypothesis; rounds of 32 work items are claimed with a shared-memory
-//                          counter, so a warp moves on to the next tile as soon as one runs dry
-//   post      (NP warps)   per chunk, start to finish inside one warp: re-check band, literal
-//                          re-scores, candidate selection, tie-break, refit, outputs
-// Tiles flow producer -> scorers -> post -> producer through three mbarriers per buffer
-// (full / scored / free); there is no block-wide barrier after start-up.
+//                          point-hypothesis; rounds of 32 work items are claimed from a shared-memory
+//                          counter, so a warp flows into the next tile as soon as one runs dry
+//   post      (NP warps)   warp per chunk: re-check band, literal re-scores, candidate selection,
+//                          literal tie-break, refit sums -> a small per-slot record
+//   epilogue  (1 warp)     LANE per chunk slot: the scalar tail (divisions, principal axis, slope,
+//                          intercept, tip) and the result stores, for all slots of a tile at once
+// Tiles flow loader -> scorers -> post -> epilogue -> loader through four mbarriers per ring slot
+// (full / scored / postdone / free); there is no block-wide barrier after start-up.
 #pragma once
 #include "async_copy.cuh"
 #include "ransac.cuh"
@@ -23,18 +26,30 @@
 namespace lslam {
 
 struct WsCtl {                      // per ring buffer
-    Mbar full, scored, freeb;
+    Mbar full, scored, postdone, freeb;
     int next_round;
     int pad;
 };
 
+struct WsSlotInfo {                 // written by the loader warp
+    unsigned long long scan;        // global scan index (Philox counter words 2, 3)
+    int off, n, c, valid;           // first point within the staged tile, points, chunk index, flag
+    int scale_hi, pad;              // high word of the largest |coordinate| of the chunk
+};
+
+struct WsRec {                      // post -> epilogue
+    double sx, sy, sxx, sxy, syy;   // sums over the inliers relative to p0
+    double p0x, p0y, tipx, best_ss;
+    int mx, best_t, best_i, best_j; // inlier count, winner trial and pair
+    int status, pad0, pad1, pad2;   // 0 ok; else the value for ninl (0 = unused slot)
+};
+
 struct WsPostScratch {              // per post warp (followed by 2*W mask words)
-    int cand_t[kMaxCand], cand_i[kMaxCand], cand_j[kMaxCand];
-    LitLine cmodel[kMaxCand];
+    int cand_t[kMaxCand];
 };
 
 struct WsLayout {
-    size_t ctl, bufs, buf_stride, o_ssf, o_cm, post, post_stride, total;
+    size_t ctl, bufs, buf_stride, o_ssf, o_cm, o_pij, o_info, o_rec, post, post_stride, total;
 };
 
 __host__ __device__ inline size_t align128(size_t b) { return (b + 127) & ~(size_t)127; }
@@ -46,47 +61,49 @@ __host__ __device__ inline WsLayout ws_layout(int G, int chunk, int T, int W, in
     L.bufs = align128((size_t)NB * sizeof(WsCtl));
     L.o_ssf = align128((size_t)G * chunk * 16);
     L.o_cm = L.o_ssf + align128((size_t)G * T * 8);
-    L.buf_stride = L.o_cm + align128((size_t)G * T * 4);
+    L.o_pij = L.o_cm + align128((size_t)G * T * 4);
+    L.o_info = L.o_pij + align128((size_t)G * T * 4);
+    L.o_rec = L.o_info + align128((size_t)G * sizeof(WsSlotInfo));
+    L.buf_stride = L.o_rec + align128((size_t)G * sizeof(WsRec));
     L.post = L.bufs + (size_t)NB * L.buf_stride;
     L.post_stride = align128(sizeof(WsPostScratch) + (size_t)2 * W * 4);
     L.total = L.post + (size_t)NP * L.post_stride;
     return L;
 }
 
+// wait with back-off: the roles that are not the bottleneck wait a lot, and a bare spin would
+// compete with the scorers for issue slots
+__device__ __forceinline__ void ws_wait(Mbar *bar, unsigned parity)
+{
+#ifndef LSLAM_EMU
+    if (mbar_try_wait(bar, parity)) return;
+    for (unsigned tries = 0; !mbar_try_wait(bar, parity); ++tries) {
+        __nanosleep(64);
+        if (tries > (1u << 26)) __trap();      // a protocol bug must surface as an error, not a hang
+    }
+#else
+    mbar_wait(bar, parity);
+#endif
+}
+
 // packed per-trial word written by the scorers: inlier count (low 16 bits) and the high half of the
 // float whose bits are the high word of min_k | |s_k| - thr |  (0 = "re-score me literally")
 __device__ __forceinline__ uint32_t ws_pack(int cnt, float mab) { return ((uint32_t)__float_as_int(mab) & 0x7fff0000u) | (uint32_t)cnt; }
 
-// geometry of chunk slot s: scan b, chunk c, point count n, validity (functions.py:64-76)
-struct WsSlot { int b, c, n; bool valid; };
-__device__ __forceinline__ WsSlot ws_slot(const RansacArgs &a, long long s)
-{
-    WsSlot g;
-    g.b = (int)(s / a.C);
-    g.c = (int)(s - (long long)g.b * a.C);
-    int nb = a.npts ? a.npts[g.b] : a.N;
-    nb = nb < 0 ? 0 : (nb > a.N ? a.N : nb);
-    int n = nb - g.c * a.chunk;
-    g.n = n < 0 ? 0 : (n > a.chunk ? a.chunk : n);
-    g.valid = (g.n >= 2) && (g.n == a.chunk || g.n > 2);
-    return g;
-}
-
 // ---- scorer: one work item = TPT consecutive trials of one chunk --------------------------------
 template <int TPT>
-__device__ __forceinline__ void ws_score_item(const RansacArgs &a, long long slot0, long long gp0, int item,
-                                              const double2 *pts, double *ssf, uint32_t *cm)
+__device__ __forceinline__ void ws_score_item(const RansacArgs &a, int item, const WsSlotInfo *info,
+                                              const double2 *pts, double *ssf, uint32_t *cm, uint32_t *pij)
 {
     const int T = a.trials;
     const int q = item / a.ipc, tb = item - q * a.ipc;
-    const WsSlot g = ws_slot(a, slot0 + q);
-    const double2 *P = pts + ((long long)g.b * a.N + (long long)g.c * a.chunk - gp0);
-    const uint64_t scan = a.scan_base + (uint64_t)g.b;
+    const WsSlotInfo g = info[q];
+    const double2 *P = pts + g.off;
     const int t0 = tb * TPT;
     const uint32_t n = (uint32_t)g.n;
 
     double nx[TPT], ny[TPT], ng[TPT], ss[TPT];
-    unsigned bits[TPT];
+    unsigned bits[TPT], pr[TPT];
     int cnt[TPT];
     float mab[TPT];
     Philox4 ph;
@@ -94,14 +111,15 @@ __device__ __forceinline__ void ws_score_item(const RansacArgs &a, long long slo
     for (int k = 0; k < TPT; ++k) {
         const int t = t0 + k;
         if ((k & 1) == 0 || TPT == 1)
-            ph = philox4x32_10((uint32_t)t >> 1, (uint32_t)g.c, (uint32_t)scan, (uint32_t)(scan >> 32),
+            ph = philox4x32_10((uint32_t)t >> 1, (uint32_t)g.c, (uint32_t)g.scan, (uint32_t)(g.scan >> 32),
                                (uint32_t)a.seed, (uint32_t)(a.seed >> 32));
         nx[k] = 0.0; ny[k] = 0.0; ng[k] = 0.0; ss[k] = 0.0;
-        bits[k] = 0u; cnt[k] = 0; mab[k] = __int_as_float(0x7f800000);
+        bits[k] = 0u; pr[k] = 0u; cnt[k] = 0; mab[k] = __int_as_float(0x7f800000);
         if (g.valid && t < T) {
             int i, j;
             const bool odd = t & 1;
             pair_from_words(odd ? ph.r[2] : ph.r[0], odd ? ph.r[3] : ph.r[1], n, i, j);
+            pr[k] = (uint32_t)i | ((uint32_t)j << 16);
             const FastLine f = fast_pair_model(P[i], P[j]);
             nx[k] = f.nx; ny[k] = f.ny; ng[k] = f.negc;
             if (f.degenerate) mab[k] = 0.0f;                     // coincident samples: literal re-score
@@ -147,108 +165,145 @@ __device__ __forceinline__ void ws_score_item(const RansacArgs &a, long long slo
             const bool finite = ss[k_] <= 1.7976931348623157e308;
             ssf[q * T + t] = ss[k_];
             cm[q * T + t] = ws_pack(cnt[k_], finite ? mab[k_] : 0.0f);
+            pij[q * T + t] = pr[k_];
         }
     }
 }
 
-// ---- post: everything after the scores of one chunk, inside one warp ---------------------------
-__device__ __forceinline__ void ws_write_empty(const RansacArgs &a, long long s, int status, int lane)
+// ---- post: from the scores of one chunk to its record, inside one warp --------------------------
+__device__ __forceinline__ void ws_rec_status(WsRec *rec, int status, const RansacArgs &a, long long s, int lane)
 {
-    const double qnan = __longlong_as_double(0x7ff8000000000000LL);
-    if (lane < 8) a.line[s * 8 + lane] = qnan;
-    if (lane == 0) {
-        a.ninl[s] = status;
-        a.win_trial[s] = -1;
-        a.win_pair[2 * s] = -1;
-        a.win_pair[2 * s + 1] = -1;
-        a.ssum[s] = qnan;
-    }
+    if (lane == 0) rec->status = status;
     for (int w = lane; w < a.W; w += 32) a.mask[s * a.W + w] = 0u;
 }
 
-__device__ __forceinline__ void ws_post_chunk(const RansacArgs &a, long long s, long long gp0, const double2 *pts,
-                                              double *sq, uint32_t *cmq, WsPostScratch *sc, uint32_t *smask,
-                                              uint32_t *wtmp, int lane)
+// literal model of trial t from the pair the scorer stored
+__device__ __forceinline__ LitLine ws_trial_model(const double2 *P, const uint32_t *pq, int t, int &i, int &j)
+{
+    const uint32_t p = pq[t];
+    i = (int)(p & 0xffffu);
+    j = (int)(p >> 16);
+    return lit_pair_model(P[i], P[j]);
+}
+
+__device__ __forceinline__ void ws_post_chunk(const RansacArgs &a, long long s, const WsSlotInfo &g, const double2 *pts,
+                                              double *sq, uint32_t *cmq, const uint32_t *pq, WsRec *rec,
+                                              WsPostScratch *sc, uint32_t *smask, uint32_t *wtmp, int lane)
 {
     const int T = a.trials;
-    const WsSlot g = ws_slot(a, s);
-    if (!g.valid) { ws_write_empty(a, s, 0, lane); return; }                 // unused slot
+    if (!g.valid) { ws_rec_status(rec, 0x7fffffff, a, s, lane); return; }    // unused slot
     const int n = g.n;
-    const double2 *P = pts + ((long long)g.b * a.N + (long long)g.c * a.chunk - gp0);
-    const uint64_t scan = a.scan_base + (uint64_t)g.b;
-    // ---- scale of the chunk -> re-check band ----
-    int mh = 0;
-    for (int k = lane; k < n; k += 32) {
-        const double2 p = P[k];
-        const int hx = __double2hiint(p.x) & 0x7fffffff, hy = __double2hiint(p.y) & 0x7fffffff;
-        mh = mh > hx ? mh : hx;
-        mh = mh > hy ? mh : hy;
-    }
-    mh = __reduce_max_sync(LSLAM_FULL_MASK, mh);
-    const ChunkBand cb = chunk_band(mh);
-    if (cb.bad) { ws_write_empty(a, s, kStatusNonFinite, lane); return; }
-    int *cq = reinterpret_cast<int *>(cmq);
-    // ---- flagged trials: literal re-score; unpack the counts; maximal count ----
-    int mx = 0;
-    unsigned n_relit = 0;
-    for (int t0 = 0; t0 < T; t0 += 32) {
-        const int t = t0 + lane;
-        const uint32_t w = t < T ? cmq[t] : 0x7fff0000u;
-        int cv = (int)(w & 0xffffu);
-        const bool flag = t < T && (cb.force_literal || (int)(w & 0x7fff0000u) < cb.band_hi);
-        unsigned m = __ballot_sync(LSLAM_FULL_MASK, flag);
-        while (m) {
-            const int tt = t0 + __ffs((int)m) - 1;
-            m &= m - 1;
-            int i, j, cl;
-            double sl;
-            sample_pair(a.seed, scan, (uint32_t)g.c, (uint32_t)tt, (uint32_t)n, i, j);
-            warp_literal_score(P, n, lit_pair_model(P[i], P[j]), a.thr, lane, cl, sl, nullptr);
-            if (tt == t) { cv = cl | kCntExact; sq[t] = sl; }
-            ++n_relit;
-        }
-        if (t < T) cq[t] = cv;
-        const int v = cv & ~kCntExact;
-        mx = mx > v ? mx : v;
-    }
-    mx = __reduce_max_sync(LSLAM_FULL_MASK, mx);
-    if (lane == 0 && n_relit) atomicAdd(a.counters + 0, (unsigned long long)n_relit);
-    __syncwarp();
-    if (mx < 2) { ws_write_empty(a, s, kStatusNoModel, lane); return; }     // upstream's final estimate() needs 2 points
-    // ---- smallest upper bound of the literal residual sum among the tied trials ----
+    const double2 *P = pts + g.off;
+    const ChunkBand cb = chunk_band(g.scale_hi);
+    if (cb.bad) { ws_rec_status(rec, kStatusNonFinite, a, s, lane); return; }
     const SsumBound sb = ssum_bound_coeffs(cb.eabs, n, a.thr);
-    int minhi_q = 0x7fffffff;
-    for (int t = lane; t < T; t += 32) {
-        const int cv = cq[t];
-        if ((cv & ~kCntExact) == mx) {
-            const double v = sq[t];
-            const double e = (cv & kCntExact) ? 0.0 : fma(sb.beta, v, sb.alpha);
-            const int k = key_up(v + e);
-            minhi_q = minhi_q < k ? minhi_q : k;
+    int *cq = reinterpret_cast<int *>(cmq);
+    int mx = 0, minhi_q = 0x7fffffff, ncand = 0;
+    unsigned n_relit = 0;
+    if (T <= 128) {
+        // ---- the chunk's trials live in registers: lane holds trials lane, lane+32, lane+64, lane+96 ----
+        int cv[4];
+        double v[4];
+        unsigned fl[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int t = lane + 32 * k;
+            const uint32_t w = t < T ? cmq[t] : 0x7fff0000u;
+            v[k] = t < T ? sq[t] : 0.0;
+            cv[k] = t < T ? (int)(w & 0xffffu) : -1;
+            fl[k] = __ballot_sync(LSLAM_FULL_MASK, t < T && (cb.force_literal || (int)(w & 0x7fff0000u) < cb.band_hi));
+        }
+        if (fl[0] | fl[1] | fl[2] | fl[3]) {                    // literal re-scores (0.16 % of the trials)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                unsigned m = fl[k];
+                while (m) {
+                    const int src = __ffs((int)m) - 1, tt = src + 32 * k;
+                    m &= m - 1;
+                    int i, j, cl;
+                    double sl;
+                    const LitLine mdl = ws_trial_model(P, pq, tt, i, j);
+                    warp_literal_score(P, n, mdl, a.thr, lane, cl, sl, nullptr);
+                    if (src == lane) { cv[k] = cl | kCntExact; v[k] = sl; }
+                    ++n_relit;
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { const int c = cv[k] < 0 ? 0 : (cv[k] & ~kCntExact); mx = mx > c ? mx : c; }
+        mx = __reduce_max_sync(LSLAM_FULL_MASK, mx);
+        if (mx >= 2) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (cv[k] >= 0 && (cv[k] & ~kCntExact) == mx) {
+                    const double e = (cv[k] & kCntExact) ? 0.0 : fma(sb.beta, v[k], sb.alpha);
+                    const int key = key_up(v[k] + e);
+                    minhi_q = minhi_q < key ? minhi_q : key;
+                }
+            }
+            minhi_q = __reduce_min_sync(LSLAM_FULL_MASK, minhi_q);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int t = lane + 32 * k;
+                const bool cand = cv[k] >= 0 && trial_is_candidate(cv[k], v[k], mx, minhi_q, sb);
+                const unsigned m = __ballot_sync(LSLAM_FULL_MASK, cand);
+                if (cand) {
+                    const int pos = ncand + __popc(m & ((1u << lane) - 1u));
+                    if (pos < kMaxCand) sc->cand_t[pos] = t;
+                }
+                ncand += __popc(m);
+                if (t < T) { cq[t] = cv[k]; sq[t] = v[k]; }     // unpacked form for the rare sweeps below
+            }
+        }
+    } else {
+        // ---- generic trial count: the same steps as loops over shared memory ----
+        for (int t0 = 0; t0 < T; t0 += 32) {
+            const int t = t0 + lane;
+            const uint32_t w = t < T ? cmq[t] : 0x7fff0000u;
+            int cv = (int)(w & 0xffffu);
+            const bool flag = t < T && (cb.force_literal || (int)(w & 0x7fff0000u) < cb.band_hi);
+            unsigned m = __ballot_sync(LSLAM_FULL_MASK, flag);
+            while (m) {
+                const int tt = t0 + __ffs((int)m) - 1;
+                m &= m - 1;
+                int i, j, cl;
+                double sl;
+                const LitLine mdl = ws_trial_model(P, pq, tt, i, j);
+                warp_literal_score(P, n, mdl, a.thr, lane, cl, sl, nullptr);
+                if (tt == t) { cv = cl | kCntExact; sq[t] = sl; }
+                ++n_relit;
+            }
+            if (t < T) cq[t] = cv;
+            const int c = cv & ~kCntExact;
+            mx = mx > c ? mx : c;
+        }
+        mx = __reduce_max_sync(LSLAM_FULL_MASK, mx);
+        __syncwarp();
+        if (mx >= 2) {
+            for (int t = lane; t < T; t += 32) {
+                const int cv = cq[t];
+                if ((cv & ~kCntExact) == mx) {
+                    const double v = sq[t];
+                    const double e = (cv & kCntExact) ? 0.0 : fma(sb.beta, v, sb.alpha);
+                    const int key = key_up(v + e);
+                    minhi_q = minhi_q < key ? minhi_q : key;
+                }
+            }
+            minhi_q = __reduce_min_sync(LSLAM_FULL_MASK, minhi_q);
+            for (int t0 = 0; t0 < T; t0 += 32) {
+                const int t = t0 + lane;
+                const bool cand = t < T && trial_is_candidate(cq[t], sq[t], mx, minhi_q, sb);
+                const unsigned m = __ballot_sync(LSLAM_FULL_MASK, cand);
+                if (cand) {
+                    const int pos = ncand + __popc(m & ((1u << lane) - 1u));
+                    if (pos < kMaxCand) sc->cand_t[pos] = t;
+                }
+                ncand += __popc(m);
+            }
         }
     }
-    minhi_q = __reduce_min_sync(LSLAM_FULL_MASK, minhi_q);
-    // ---- candidate list in trial order ----
-    int ncand = 0;
-    for (int t0 = 0; t0 < T; t0 += 32) {
-        const int t = t0 + lane;
-        const bool cand = t < T && trial_is_candidate(cq[t], sq[t], mx, minhi_q, sb);
-        const unsigned m = __ballot_sync(LSLAM_FULL_MASK, cand);
-        if (cand) {
-            const int pos = ncand + __popc(m & ((1u << lane) - 1u));
-            if (pos < kMaxCand) sc->cand_t[pos] = t;
-        }
-        ncand += __popc(m);
-    }
-    __syncwarp();
-    // ---- candidate models: one lane each ----
-    if (lane < ncand && lane < kMaxCand) {
-        int i, j;
-        sample_pair(a.seed, scan, (uint32_t)g.c, (uint32_t)sc->cand_t[lane], (uint32_t)n, i, j);
-        sc->cand_i[lane] = i;
-        sc->cand_j[lane] = j;
-        sc->cmodel[lane] = lit_pair_model(P[i], P[j]);
-    }
+    if (lane == 0 && n_relit) atomicAdd(a.counters + 0, (unsigned long long)n_relit);
+    if (mx < 2) { ws_rec_status(rec, kStatusNoModel, a, s, lane); return; }  // upstream's final estimate() needs 2 points
     __syncwarp();
     // ---- literal tie-break in trial order (first best wins, like the sequential accept rule) ----
     bool fault = false;
@@ -256,13 +311,15 @@ __device__ __forceinline__ void ws_post_chunk(const RansacArgs &a, long long s, 
     double best_ss = __longlong_as_double(0x7ff0000000000000LL);
     if (ncand <= kMaxCand) {
         for (int ci = 0; ci < ncand; ++ci) {
-            int cl;
+            int i, j, cl;
             double sl;
-            warp_literal_score(P, n, sc->cmodel[ci], a.thr, lane, cl, sl, ncand == 1 ? smask : wtmp);
+            const int tt = sc->cand_t[ci];
+            const LitLine mdl = ws_trial_model(P, pq, tt, i, j);      // every lane, redundantly: no hand-off
+            warp_literal_score(P, n, mdl, a.thr, lane, cl, sl, ncand == 1 ? smask : wtmp);
             __syncwarp();
             if (cl != mx) fault = true;
             if (sl < best_ss) {
-                best_ss = sl; best_t = sc->cand_t[ci]; best_i = sc->cand_i[ci]; best_j = sc->cand_j[ci];
+                best_ss = sl; best_t = tt; best_i = i; best_j = j;
                 if (ncand > 1) for (int w = lane; w * 32 < n; w += 32) smask[w] = wtmp[w];
             }
             __syncwarp();
@@ -277,8 +334,8 @@ __device__ __forceinline__ void ws_post_chunk(const RansacArgs &a, long long s, 
                 m &= m - 1;
                 int i, j, cl;
                 double sl;
-                sample_pair(a.seed, scan, (uint32_t)g.c, (uint32_t)tt, (uint32_t)n, i, j);
-                warp_literal_score(P, n, lit_pair_model(P[i], P[j]), a.thr, lane, cl, sl, wtmp);
+                const LitLine mdl = ws_trial_model(P, pq, tt, i, j);
+                warp_literal_score(P, n, mdl, a.thr, lane, cl, sl, wtmp);
                 __syncwarp();
                 if (cl != mx) fault = true;
                 if (sl < best_ss) {
@@ -299,8 +356,8 @@ __device__ __forceinline__ void ws_post_chunk(const RansacArgs &a, long long s, 
         for (int t = 0; t < T; ++t) {
             int i, j, cl;
             double sl;
-            sample_pair(a.seed, scan, (uint32_t)g.c, (uint32_t)t, (uint32_t)n, i, j);
-            warp_literal_score(P, n, lit_pair_model(P[i], P[j]), a.thr, lane, cl, sl, wtmp);
+            const LitLine mdl = ws_trial_model(P, pq, t, i, j);
+            warp_literal_score(P, n, mdl, a.thr, lane, cl, sl, wtmp);
             __syncwarp();
             if (cl > best_n || (cl == best_n && sl < best_ss)) {
                 best_n = cl; best_ss = sl; best_t = t; best_i = i; best_j = j;
@@ -309,9 +366,9 @@ __device__ __forceinline__ void ws_post_chunk(const RansacArgs &a, long long s, 
             __syncwarp();
         }
         mx = best_n;
-        if (best_t < 0 || best_n < 2) { ws_write_empty(a, s, kStatusNoModel, lane); return; }
+        if (best_t < 0 || best_n < 2) { ws_rec_status(rec, kStatusNoModel, a, s, lane); return; }
     }
-    // ---- refit on the inliers (principal axis of the 2x2 scatter, relative to the first sample) ----
+    // ---- refit sums over the inliers, relative to the winner's first sample point ----
     const double2 p0 = P[best_i];
     double sx = 0.0, sy = 0.0, sxx = 0.0, sxy = 0.0, syy = 0.0;
     for (int k = lane; k < n; k += 32) {
@@ -331,37 +388,56 @@ __device__ __forceinline__ void ws_post_chunk(const RansacArgs &a, long long s, 
         syy += __shfl_xor_sync(LSLAM_FULL_MASK, syy, o);
     }
     if (lane == 0) {
-        const double m = (double)mx;
-        const double mdx = sx / m, mdy = sy / m;
-        const double ox = p0.x + mdx, oy = p0.y + mdy;
-        double dx, dy;
-        principal_axis(fma(-sx, mdx, sxx), fma(-sx, mdy, sxy), fma(-sy, mdy, syy), dx, dy);
         int last = 0;
         for (int w = (n - 1) >> 5; w >= 0; --w) {
             const unsigned mw = smask[w];
             if (mw) { last = w * 32 + 31 - __clz((int)mw); break; }
         }
-        // ransac_functions.py:26-30 (no guard for dir_x == 0, like the reference)
-        const double sl = __ddiv_rn(dy, dx);
-        const double ic = __dsub_rn(oy, __dmul_rn(sl, ox));
-        const double tipx = P[last].x;
-        const double tipy = __dadd_rn(__dmul_rn(tipx, sl), ic);
-        double *L = a.line + s * 8;
-        L[0] = sl; L[1] = ic; L[2] = ox; L[3] = oy; L[4] = dx; L[5] = dy; L[6] = tipx; L[7] = tipy;
-        a.ninl[s] = mx;
-        a.win_trial[s] = best_t;
-        a.win_pair[2 * s] = best_i;
-        a.win_pair[2 * s + 1] = best_j;
-        a.ssum[s] = best_ss;
+        rec->sx = sx; rec->sy = sy; rec->sxx = sxx; rec->sxy = sxy; rec->syy = syy;
+        rec->p0x = p0.x; rec->p0y = p0.y; rec->tipx = P[last].x; rec->best_ss = best_ss;
+        rec->mx = mx; rec->best_t = best_t; rec->best_i = best_i; rec->best_j = best_j;
+        rec->status = 0;
     }
     for (int w = lane; w < a.W; w += 32) a.mask[s * a.W + w] = (w * 32 < n) ? smask[w] : 0u;
     __syncwarp();
 }
 
-// ---- the kernel: one persistent CTA per SM, (NS + NP + 1) warps -----------------------------------
+// ---- epilogue: one LANE per chunk slot - LineModelND.estimate tail + ransac_functions.py:26-30 ----
+__device__ __forceinline__ void ws_epilogue_slot(const RansacArgs &a, long long s, const WsRec &r)
+{
+    double *L = a.line + s * 8;
+    if (r.status == 0) {
+        const double m = (double)r.mx;
+        const double mdx = r.sx / m, mdy = r.sy / m;
+        const double ox = r.p0x + mdx, oy = r.p0y + mdy;
+        double dx, dy;
+        principal_axis(fma(-r.sx, mdx, r.sxx), fma(-r.sx, mdy, r.sxy), fma(-r.sy, mdy, r.syy), dx, dy);
+        // no guard for dir_x == 0, like the reference
+        const double sl = __ddiv_rn(dy, dx);
+        const double ic = __dsub_rn(oy, __dmul_rn(sl, ox));
+        const double tipy = __dadd_rn(__dmul_rn(r.tipx, sl), ic);
+        L[0] = sl; L[1] = ic; L[2] = ox; L[3] = oy; L[4] = dx; L[5] = dy; L[6] = r.tipx; L[7] = tipy;
+        a.ninl[s] = r.mx;
+        a.win_trial[s] = r.best_t;
+        a.win_pair[2 * s] = r.best_i;
+        a.win_pair[2 * s + 1] = r.best_j;
+        a.ssum[s] = r.best_ss;
+    } else {
+        const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) L[k] = qnan;
+        a.ninl[s] = r.status == 0x7fffffff ? 0 : r.status;
+        a.win_trial[s] = -1;
+        a.win_pair[2 * s] = -1;
+        a.win_pair[2 * s + 1] = -1;
+        a.ssum[s] = qnan;
+    }
+}
+
+// ---- the kernel: one persistent CTA per SM, (NS + NP + 2) warps -----------------------------------
 // a.G = chunk slots per tile, a.ws_ns / a.ws_np / a.ws_nb = scorer warps, post warps, ring depth.
-template <int TPT>
-__global__ void __launch_bounds__(640, 1) ransac_ws_kernel(const RansacArgs a)
+template <int TPT, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1) ransac_ws_kernel(const RansacArgs a)
 {
     LSLAM_SMEM_DECL;
     const int T = a.trials, G = a.G, NS = a.ws_ns, NP = a.ws_np, NB = a.ws_nb;
@@ -373,56 +449,96 @@ __global__ void __launch_bounds__(640, 1) ransac_ws_kernel(const RansacArgs a)
     if (tid == 0) {
         for (int b = 0; b < NB; ++b) {
             mbar_init(&ctl[b].full, 1);
-            mbar_init(&ctl[b].scored, (unsigned)NS);
-            mbar_init(&ctl[b].freeb, (unsigned)NP);
+            mbar_init(&ctl[b].scored, (unsigned)NS + 1u);
+            mbar_init(&ctl[b].postdone, (unsigned)NP);
+            mbar_init(&ctl[b].freeb, 1);
             ctl[b].next_round = 0;
         }
         mbar_fence_init();
     }
     __syncthreads();
 
-    // first staged point and byte count of tile `tile`
-    auto tile_span = [&](long long tile, long long &slot0, int &nsl, long long &gp0, unsigned &bytes) {
-        slot0 = tile * G;
-        const long long rem = a.nslots - slot0;
-        nsl = rem < (long long)G ? (int)rem : G;
-        const long long b0 = slot0 / a.C, c0 = slot0 - b0 * a.C;
-        gp0 = b0 * a.N + c0 * a.chunk;
-        const long long sl = slot0 + nsl - 1;
-        const long long bl = sl / a.C, cl = sl - bl * a.C;
-        const long long cend = (cl + 1) * a.chunk < a.N ? (cl + 1) * a.chunk : a.N;
-        bytes = (unsigned)((bl * a.N + cend - gp0) * 16);
-    };
-
+    long long k = 0;                                   // this CTA's k-th tile goes to ring slot k % NB
     if (warp == NS + NP) {
-        // ================= producer =================
-        if (lane == 0) {
-            long long k = 0;
-            for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++k) {
-                const int b = (int)(k % NB);
-                const long long j = k / NB;
-                if (j > 0) mbar_wait(&ctl[b].freeb, (unsigned)((j - 1) & 1));
-                long long slot0, gp0;
-                int nsl;
-                unsigned bytes;
-                tile_span(tile, slot0, nsl, gp0, bytes);
+        // ================= loader =================
+        for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++k) {
+            const int b = (int)(k % NB);
+            const long long use = k / NB;
+            unsigned char *buf = smem_raw + L.bufs + (size_t)b * L.buf_stride;
+            WsSlotInfo *info = reinterpret_cast<WsSlotInfo *>(buf + L.o_info);
+            const double2 *pts = reinterpret_cast<const double2 *>(buf);
+            if (use > 0) ws_wait(&ctl[b].freeb, (unsigned)((use - 1) & 1));
+            const long long slot0 = tile * G;
+            const long long remain = a.nslots - slot0;
+            const int nsl = remain < (long long)G ? (int)remain : G;
+            const long long b0 = slot0 / a.C;
+            const int c0 = (int)(slot0 - b0 * a.C);
+            const long long gp0 = b0 * a.N + (long long)c0 * a.chunk;       // first staged point
+            for (int q = lane; q < nsl; q += 32) {                          // slot table (functions.py:64-76)
+                const int cc = c0 + q;
+                const int db = cc / a.C, c = cc - db * a.C;
+                const long long bb = b0 + db;
+                int nb = a.npts ? a.npts[bb] : a.N;
+                nb = nb < 0 ? 0 : (nb > a.N ? a.N : nb);
+                int n = nb - c * a.chunk;
+                n = n < 0 ? 0 : (n > a.chunk ? a.chunk : n);
+                WsSlotInfo g;
+                g.scan = a.scan_base + (unsigned long long)bb;
+                g.off = (int)(bb * a.N + (long long)c * a.chunk - gp0);
+                g.n = n; g.c = c;
+                g.valid = (n >= 2) && (n == a.chunk || n > 2);
+                g.scale_hi = 0; g.pad = 0;
+                info[q] = g;
+            }
+            __syncwarp();
+            if (lane == 0) {
+                const long long sl = slot0 + nsl - 1;
+                const long long bl = sl / a.C, cl = sl - bl * a.C;
+                const long long cend = (cl + 1) * a.chunk < a.N ? (cl + 1) * a.chunk : a.N;
+                const unsigned bytes = (unsigned)((bl * a.N + cend - gp0) * 16);
                 ctl[b].next_round = 0;
                 mbar_expect_tx(&ctl[b].full, bytes);
-                bulk_g2s(smem_raw + L.bufs + (size_t)b * L.buf_stride, a.xy + gp0, bytes, &ctl[b].full);
+                bulk_g2s(buf, a.xy + gp0, bytes, &ctl[b].full);
             }
+            ws_wait(&ctl[b].full, (unsigned)(use & 1));
+            for (int q = 0; q < nsl; ++q) {                                 // coordinate scale per chunk
+                const int off = info[q].off, n = info[q].n;
+                int mh = 0;
+                for (int i = lane; i < n; i += 32) {
+                    const double2 p = pts[off + i];
+                    const int hx = __double2hiint(p.x) & 0x7fffffff, hy = __double2hiint(p.y) & 0x7fffffff;
+                    mh = mh > hx ? mh : hx;
+                    mh = mh > hy ? mh : hy;
+                }
+                mh = __reduce_max_sync(LSLAM_FULL_MASK, mh);
+                if (lane == 0) info[q].scale_hi = mh;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&ctl[b].scored);
         }
-    } else if (warp < NS) {
-        // ================= scorers =================
-        long long k = 0;
+    } else if (warp == NS + NP + 1) {
+        // ================= epilogue =================
         for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++k) {
             const int b = (int)(k % NB);
             unsigned char *buf = smem_raw + L.bufs + (size_t)b * L.buf_stride;
-            long long slot0, gp0;
-            int nsl;
-            unsigned bytes;
-            tile_span(tile, slot0, nsl, gp0, bytes);
+            const WsRec *rec = reinterpret_cast<const WsRec *>(buf + L.o_rec);
+            const long long slot0 = tile * G;
+            const long long remain = a.nslots - slot0;
+            const int nsl = remain < (long long)G ? (int)remain : G;
+            ws_wait(&ctl[b].postdone, (unsigned)((k / NB) & 1));
+            for (int q = lane; q < nsl; q += 32) ws_epilogue_slot(a, slot0 + q, rec[q]);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&ctl[b].freeb);
+        }
+    } else if (warp < NS) {
+        // ================= scorers =================
+        for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++k) {
+            const int b = (int)(k % NB);
+            unsigned char *buf = smem_raw + L.bufs + (size_t)b * L.buf_stride;
+            const long long remain = a.nslots - tile * G;
+            const int nsl = remain < (long long)G ? (int)remain : G;
             const int items = nsl * a.ipc, nrounds = (items + 31) >> 5;
-            mbar_wait(&ctl[b].full, (unsigned)((k / NB) & 1));
+            ws_wait(&ctl[b].full, (unsigned)((k / NB) & 1));
             for (;;) {
                 int r = 0;
                 if (lane == 0) r = atomicAdd(&ctl[b].next_round, 1);
@@ -430,8 +546,9 @@ __global__ void __launch_bounds__(640, 1) ransac_ws_kernel(const RansacArgs a)
                 if (r >= nrounds) break;
                 const int item = r * 32 + lane;
                 if (item < items)
-                    ws_score_item<TPT>(a, slot0, gp0, item, reinterpret_cast<const double2 *>(buf),
-                                       reinterpret_cast<double *>(buf + L.o_ssf), reinterpret_cast<uint32_t *>(buf + L.o_cm));
+                    ws_score_item<TPT>(a, item, reinterpret_cast<const WsSlotInfo *>(buf + L.o_info),
+                                       reinterpret_cast<const double2 *>(buf), reinterpret_cast<double *>(buf + L.o_ssf),
+                                       reinterpret_cast<uint32_t *>(buf + L.o_cm), reinterpret_cast<uint32_t *>(buf + L.o_pij));
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&ctl[b].scored);
@@ -443,21 +560,23 @@ __global__ void __launch_bounds__(640, 1) ransac_ws_kernel(const RansacArgs a)
         WsPostScratch *sc = reinterpret_cast<WsPostScratch *>(ps);
         uint32_t *smask = reinterpret_cast<uint32_t *>(ps + sizeof(WsPostScratch));
         uint32_t *wtmp = smask + a.W;
-        long long k = 0;
         for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++k) {
             const int b = (int)(k % NB);
             unsigned char *buf = smem_raw + L.bufs + (size_t)b * L.buf_stride;
-            long long slot0, gp0;
-            int nsl;
-            unsigned bytes;
-            tile_span(tile, slot0, nsl, gp0, bytes);
-            mbar_wait(&ctl[b].scored, (unsigned)((k / NB) & 1));
+            const WsSlotInfo *info = reinterpret_cast<const WsSlotInfo *>(buf + L.o_info);
+            WsRec *rec = reinterpret_cast<WsRec *>(buf + L.o_rec);
+            const long long slot0 = tile * G;
+            const long long remain = a.nslots - slot0;
+            const int nsl = remain < (long long)G ? (int)remain : G;
+            ws_wait(&ctl[b].scored, (unsigned)((k / NB) & 1));
             for (int q = pw; q < nsl; q += NP)
-                ws_post_chunk(a, slot0 + q, gp0, reinterpret_cast<const double2 *>(buf),
+                ws_post_chunk(a, slot0 + q, info[q], reinterpret_cast<const double2 *>(buf),
                               reinterpret_cast<double *>(buf + L.o_ssf) + (size_t)q * T,
-                              reinterpret_cast<uint32_t *>(buf + L.o_cm) + (size_t)q * T, sc, smask, wtmp, lane);
+                              reinterpret_cast<uint32_t *>(buf + L.o_cm) + (size_t)q * T,
+                              reinterpret_cast<const uint32_t *>(buf + L.o_pij) + (size_t)q * T, rec + q, sc, smask,
+                              wtmp, lane);
             __syncwarp();
-            if (lane == 0) mbar_arrive(&ctl[b].freeb);
+            if (lane == 0) mbar_arrive(&ctl[b].postdone);
         }
     }
 }

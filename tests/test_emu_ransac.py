@@ -29,7 +29,7 @@ def test_ws_role_shapes(emu, cport, ransac_kernel):
     want = cport.ransac_lines(xy, npts=npts, seed=2)
     h = emu.emu_handle()
     try:
-        for ns, np_, ring, g in ((1, 1, 2, 1), (3, 2, 2, 5), (8, 8, 4, 0), (2, 5, 6, 3), (12, 7, 3, 16)):
+        for ns, np_, ring, g in ((1, 1, 2, 1), (3, 2, 2, 5), (8, 8, 4, 0), (2, 5, 6, 3), (12, 7, 3, 16), (14, 16, 2, 4)):
             h.set_option("ransac.scorers", ns)
             h.set_option("ransac.posts", np_)
             h.set_option("ransac.ring", ring)

@@ -30,7 +30,7 @@ def test_ws_role_shapes(gpu_engine, cport, ransac_kernel):
     npts[5::11] = 2
     want = cport.ransac_lines(xy, npts=npts, seed=2)
     try:
-        for ns, np_, ring, g in ((1, 1, 2, 1), (3, 2, 2, 5), (8, 8, 4, 0), (2, 5, 6, 3), (12, 7, 3, 16), (10, 6, 4, 16)):
+        for ns, np_, ring, g in ((1, 1, 2, 1), (3, 2, 2, 5), (8, 8, 4, 0), (2, 5, 6, 3), (12, 7, 3, 16), (10, 6, 3, 16), (16, 14, 3, 16), (8, 22, 2, 8)):
             for k, v in (("ransac.scorers", ns), ("ransac.posts", np_), ("ransac.ring", ring), ("ransac.slots_per_cta", g)):
                 gpu_engine.set_option(k, v)
             got = run_gpu(gpu_engine, xy, npts=npts, seed=2)

@@ -54,12 +54,13 @@ def main():
         B = int(os.environ.get("SWEEP_B", 262144))
         xy = eng.synth_scans(B, seed=1)
         out = eng.alloc_ransac_out(B, 360)
-        combos = [(1, 0, 0, 0, 0, 0, 0), (0, 0, 0, 0, 0, 0, 0)]
+        combos = [(1, 0, 0, 0, 0, 0, 0), (2, 0, 0, 0, 0, 0, 0)]
         for tpt in (2, 4):
             for slots in (8, 16, 32):
-                for ns, np_ in ((8, 8), (12, 7), (8, 4), (12, 4), (10, 9), (6, 6), (4, 4)):
-                    for ring in (3, 4):
-                        combos.append((0, tpt, slots, ns, np_, ring, 0))
+                for ns, np_ in ((8, 8), (8, 12), (12, 8), (12, 12), (16, 8), (16, 12), (10, 6), (8, 16), (6, 6), (20, 10)):
+                    combos.append((2, tpt, slots, ns, np_, 0, 0))
+        for ring in (2, 4):
+            combos.append((2, 2, 16, 8, 8, ring, 0))
         rows = []
         run(eng, combos, lambda: eng.ransac_lines(xy, out=out), B * 36000.0, "C2", rows)
         res["c2"] = rows
@@ -68,11 +69,11 @@ def main():
         B3 = 256
         xy3 = eng.synth_scans(B3, beams=8192, seed=2)
         out3 = eng.alloc_ransac_out(B3, 8192, 410)
-        combos = [(1, 0, 0, 0, 0, 0, 0), (0, 0, 0, 0, 0, 0, 0)]
+        combos = [(1, 0, 0, 0, 0, 0, 0), (2, 0, 0, 0, 0, 0, 0)]
         for tpt in (2, 4):
             for slots in (1, 2, 4):
-                for ns, np_ in ((8, 8), (12, 4), (12, 7), (16, 3)):
-                    combos.append((0, tpt, slots, ns, np_, 0, 0))
+                for ns, np_ in ((8, 8), (12, 4), (16, 4), (16, 8), (20, 4), (24, 4)):
+                    combos.append((2, tpt, slots, ns, np_, 0, 0))
         rows3 = []
         run(eng, combos, lambda: eng.ransac_lines(xy3, chunk=410, trials=1024, out=out3), B3 * 8192.0 * 1024, "C3", rows3)
         res["c3"] = rows3
