@@ -192,18 +192,13 @@ def main():
     r0 = eng.ransac_lines(xy, chunk=CHUNK, trials=TRIALS, thr=THR, seed=0, scan_base=rank * S, out=pipe.rout)
     pipe.install_map_from_lines(r0["line"], r0["ninl"])                     # untimed set-up: the known map
     pipe.ukf["u"].fill_(1.0)
-    gather_buf = None
+    from lidar_slam_b200 import dist as ldist
+    gatherer = ldist.ResultGather()
 
     def gather(res):
-        """N > 1: all ranks' per-scan UKF/landmark results over NCCL (NVLink), one collective."""
-        nonlocal gather_buf
-        if world == 1:
-            return
-        if gather_buf is None:
-            gather_buf = {k: torch.empty((world,) + tuple(res[k].shape), dtype=res[k].dtype, device=res[k].device)
-                          for k in ("x", "P", "match_id")}
-        for k, buf in gather_buf.items():
-            dist.all_gather_into_tensor(buf, res[k])
+        """N > 1: all ranks' per-scan UKF/landmark results over NCCL (NVLink), inside the timed region."""
+        if world > 1:
+            gatherer(res)
 
     def one_step():
         res = pipe.step(xy)

@@ -73,13 +73,14 @@ __host__ __device__ inline WsLayout ws_layout(int G, int chunk, int T, int W, in
 
 // wait with back-off: the roles that are not the bottleneck wait a lot, and a bare spin would
 // compete with the scorers for issue slots
+template <unsigned NS_SLEEP>
 __device__ __forceinline__ void ws_wait(Mbar *bar, unsigned parity)
 {
 #ifndef LSLAM_EMU
     if (mbar_try_wait(bar, parity)) return;
     for (unsigned tries = 0; !mbar_try_wait(bar, parity); ++tries) {
-        __nanosleep(64);
-        if (tries > (1u << 26)) __trap();      // a protocol bug must surface as an error, not a hang
+        __nanosleep(NS_SLEEP);                 // measured: a 64 ns sleep still spent 33 % of all issued instructions here
+        if (tries > (1u << 24)) __trap();      // a protocol bug must surface as an error, not a hang
     }
 #else
     mbar_wait(bar, parity);
@@ -252,7 +253,10 @@ __device__ __forceinline__ void ws_post_chunk(const RansacArgs &a, long long s, 
                     if (pos < kMaxCand) sc->cand_t[pos] = t;
                 }
                 ncand += __popc(m);
-                if (t < T) { cq[t] = cv[k]; sq[t] = v[k]; }     // unpacked form for the rare sweeps below
+            }
+            if (ncand > kMaxCand) {                              // unpacked form for the rare sweep below
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { const int t = lane + 32 * k; if (t < T) { cq[t] = cv[k]; sq[t] = v[k]; } }
             }
         }
     } else {
@@ -467,7 +471,7 @@ __global__ void __launch_bounds__(MAXT, 1) ransac_ws_kernel(const RansacArgs a)
             unsigned char *buf = smem_raw + L.bufs + (size_t)b * L.buf_stride;
             WsSlotInfo *info = reinterpret_cast<WsSlotInfo *>(buf + L.o_info);
             const double2 *pts = reinterpret_cast<const double2 *>(buf);
-            if (use > 0) ws_wait(&ctl[b].freeb, (unsigned)((use - 1) & 1));
+            if (use > 0) ws_wait<400>(&ctl[b].freeb, (unsigned)((use - 1) & 1));
             const long long slot0 = tile * G;
             const long long remain = a.nslots - slot0;
             const int nsl = remain < (long long)G ? (int)remain : G;
@@ -500,7 +504,7 @@ __global__ void __launch_bounds__(MAXT, 1) ransac_ws_kernel(const RansacArgs a)
                 mbar_expect_tx(&ctl[b].full, bytes);
                 bulk_g2s(buf, a.xy + gp0, bytes, &ctl[b].full);
             }
-            ws_wait(&ctl[b].full, (unsigned)(use & 1));
+            ws_wait<200>(&ctl[b].full, (unsigned)(use & 1));
             for (int q = 0; q < nsl; ++q) {                                 // coordinate scale per chunk
                 const int off = info[q].off, n = info[q].n;
                 int mh = 0;
@@ -525,7 +529,7 @@ __global__ void __launch_bounds__(MAXT, 1) ransac_ws_kernel(const RansacArgs a)
             const long long slot0 = tile * G;
             const long long remain = a.nslots - slot0;
             const int nsl = remain < (long long)G ? (int)remain : G;
-            ws_wait(&ctl[b].postdone, (unsigned)((k / NB) & 1));
+            ws_wait<800>(&ctl[b].postdone, (unsigned)((k / NB) & 1));
             for (int q = lane; q < nsl; q += 32) ws_epilogue_slot(a, slot0 + q, rec[q]);
             __syncwarp();
             if (lane == 0) mbar_arrive(&ctl[b].freeb);
@@ -538,7 +542,7 @@ __global__ void __launch_bounds__(MAXT, 1) ransac_ws_kernel(const RansacArgs a)
             const long long remain = a.nslots - tile * G;
             const int nsl = remain < (long long)G ? (int)remain : G;
             const int items = nsl * a.ipc, nrounds = (items + 31) >> 5;
-            ws_wait(&ctl[b].full, (unsigned)((k / NB) & 1));
+            ws_wait<100>(&ctl[b].full, (unsigned)((k / NB) & 1));
             for (;;) {
                 int r = 0;
                 if (lane == 0) r = atomicAdd(&ctl[b].next_round, 1);
@@ -568,7 +572,7 @@ __global__ void __launch_bounds__(MAXT, 1) ransac_ws_kernel(const RansacArgs a)
             const long long slot0 = tile * G;
             const long long remain = a.nslots - slot0;
             const int nsl = remain < (long long)G ? (int)remain : G;
-            ws_wait(&ctl[b].scored, (unsigned)((k / NB) & 1));
+            ws_wait<400>(&ctl[b].scored, (unsigned)((k / NB) & 1));
             for (int q = pw; q < nsl; q += NP)
                 ws_post_chunk(a, slot0 + q, info[q], reinterpret_cast<const double2 *>(buf),
                               reinterpret_cast<double *>(buf + L.o_ssf) + (size_t)q * T,
