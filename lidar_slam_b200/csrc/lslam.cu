@@ -13,11 +13,6 @@
 
 using namespace lslam;
 
-// which RANSAC kernel "ransac.kernel = 0" means: 1 phase-structured (ransac.cuh), 2 warp-specialised
-// persistent (ransac_ws.cuh); set from the measurements in profiles/
-#ifndef LSLAM_DEFAULT_RANSAC_KERNEL
-#define LSLAM_DEFAULT_RANSAC_KERNEL 1
-#endif
 
 // ---- handle ------------------------------------------------------------------------------
 extern "C" int lslam_abi_version(void) { return LSLAM_ABI_VERSION; }
@@ -136,7 +131,7 @@ static int launch_ransac_ws(Handle *h, RansacArgs a, cudaStream_t st)
     auto kern = ransac_ws_kernel<TPT, MAXT>;
     // chunk slots per tile: about 800 work items (25 rounds of 32), bounded by the ring in shared memory
     int G = h->opt_slots ? h->opt_slots : (800 + a.ipc / 2) / a.ipc;
-    if (G < 1) G = 1;
+    if (G < 2) G = 2;
     if ((long long)G > a.nslots) G = (int)a.nslots;
     const int want_nb = h->opt_ring ? h->opt_ring : 3;
     int NB = 0;
@@ -168,8 +163,10 @@ template <int TPT>
 static int dispatch_ransac_ws(Handle *h, RansacArgs a, cudaStream_t st)
 {
     a.ipc = (a.trials + TPT - 1) / TPT;
-    a.ws_ns = h->opt_scorers ? h->opt_scorers : 8;
-    a.ws_np = h->opt_posts ? h->opt_posts : 8;
+    // measured (profiles/r01e_ransac_sweep_ws.json): big chunks want scorers, small chunks want post warps
+    const bool big = (long long)a.chunk * a.trials >= 65536;
+    a.ws_ns = h->opt_scorers ? h->opt_scorers : (big ? 12 : 8);
+    a.ws_np = h->opt_posts ? h->opt_posts : (big ? 4 : 8);
     const int warps = a.ws_ns + a.ws_np + 2;
     if (warps > 32) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.scorers + ransac.posts must not exceed 30 warps");
     if (warps <= 20) return launch_ransac_ws<TPT, 640>(h, a, st);
@@ -203,11 +200,15 @@ extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t 
     a.counters = h->counters_d;
     a.nslots = (long long)B * a.C;
     a.G = 0; a.ipc = 0;
-    const int tpt = h->opt_tpt ? h->opt_tpt : 2;
+    // default kernel by problem shape (profiles/r01e_ransac_sweep_ws.json): the warp-specialised kernel wins
+    // when a chunk carries enough scoring work to amortise its per-chunk stages (C3: 410 points x 1024
+    // trials, 22.5 vs 20.6 TFLOP/s); the phase-structured kernel wins on small chunks (C2: 14.3 vs 13.1)
+    const bool big_chunks = (long long)chunk * trials >= 65536;
+    const int kernel = h->opt_kernel ? h->opt_kernel : (big_chunks ? 2 : 1);
+    const int tpt = h->opt_tpt ? h->opt_tpt : ((kernel == 2 && big_chunks) ? 4 : 2);
     const int threads = h->opt_threads ? h->opt_threads : 256;
     cudaStream_t st = (cudaStream_t)stream;
     a.ws_ns = a.ws_np = a.ws_nb = 0;
-    const int kernel = h->opt_kernel ? h->opt_kernel : LSLAM_DEFAULT_RANSAC_KERNEL;
     if (kernel == 2) {
         switch (tpt) {
         case 1: return dispatch_ransac_ws<1>(h, a, st);
