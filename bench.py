@@ -33,9 +33,14 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 BEAMS, CHUNK, TRIALS, THR, TABLE_M = 360, 100, 100, 20.0, 8
+PACKETS = 12                                       # express packets per revolution (32 measures each)
+E2E_SLICES = 8                                     # slices of the overlapped host path
 PHE_PER_SCAN = BEAMS * TRIALS                      # point-hypothesis evaluations per scan
 FLOP_PER_PHE = 8                                   # algorithmic fp64 flop per PHE
 BYTES_PER_SCAN = BEAMS * 16 + 4 * 96               # 5,760 in + 4 x 96 out = 6,144 B
+# DRAM bytes per scan of the RANSAC kernel from the ncu --set full capture of 262,144 scans
+# (profiles/r01f_ransac_c2_ncu_summary.txt: 1.5106 GB read + 0.1072 GB written)
+NCU_DRAM_BYTES_PER_SCAN = (1.510555e9 + 107.172864e6) / 262144
 
 
 def parse():
@@ -108,15 +113,17 @@ class ClockSampler:
 
 # ---- CPU legs (the only place bench.py touches oracle/) -----------------------------------------
 def cpu_pipeline_rate(nscans, seed=0):
-    """Scans/s of the CPU restatement of the same step (oracle/: RANSAC, association and UKF in C,
-    OpenMP over scans, all host threads) on `nscans` synthetic scans with the same known-map set-up
-    as the GPU arm.  Returns (scans_per_s, threads, seconds)."""
+    """Scans/s of the CPU restatement of the same job (oracle/: express-packet decode + polar->cartesian,
+    RANSAC, association and UKF in C, OpenMP over scans, all host threads) on `nscans` synthetic
+    revolutions given as raw sensor packets, with the same known-map set-up as the GPU arm.
+    Returns (scans_per_s, threads, seconds)."""
     import numpy as np
     from lidar_slam_b200 import synth
     from oracle import cport
     from tests import pipeline_util
-    xy = synth.random_room_scans(nscans, seed=seed)
+    pk = synth.random_room_express(nscans, PACKETS, seed=seed)
     threads = cport.max_threads()
+    xy, _, _ = cport.express_to_cart(pk, BEAMS)
     r0 = cport.ransac_lines(xy)                                    # untimed set-up: the known map
     tables = pipeline_util.map_from_lines(r0["line"], r0["ninl"], TABLE_M)
     x = np.zeros((nscans, 3))
@@ -125,6 +132,7 @@ def cpu_pipeline_rate(nscans, seed=0):
     best = None
     for _ in range(2):
         t0 = time.perf_counter()
+        xy, _, _ = cport.express_to_cart(pk, BEAMS)
         _, _, x, P, _ = cport.pipeline_step(xy, tables, x, P, u)
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
@@ -162,7 +170,10 @@ def workload_config(args, world):
     return {"workload": "BASELINE.json configs[4]: 1M synthetic 360-beam scans end-to-end "
                         "(RANSAC 4 chunks x 100 trials + association M=8 + UKF n=3) per GPU",
             "scans_per_gpu_per_step": args.scans, "beams": BEAMS, "chunk": CHUNK, "trials": TRIALS,
-            "threshold_mm": THR, "table_capacity": TABLE_M, "sharding": "scans by index, %d rank(s)" % world,
+            "threshold_mm": THR, "table_capacity": TABLE_M,
+            "input": "synthetic sensor: %d express packets (84 B, 32 measures) per revolution, first %d measures "
+                     "form the scan; `value` starts from the decoded points resident in HBM, `e2e` and the CPU "
+                     "legs start from the packet bytes in host memory" % (PACKETS, BEAMS), "sharding": "scans by index, %d rank(s)" % world,
             "l2": "inputs (%.2f GB per step) exceed the 126 MB L2" % (args.scans * BEAMS * 16 / 1e9)}
 
 
@@ -188,7 +199,10 @@ def main():
     S = args.scans
     pipe = pipeline.ScanPipeline(eng, S, beams=BEAMS, chunk=CHUNK, trials=TRIALS, thr=THR,
                                  table_capacity=TABLE_M, seed=0, scan_base=rank * S)
-    xy = eng.synth_scans(S, beams=BEAMS, seed=0, scan_base=rank * S)       # resident in HBM
+    # untimed set-up: the synthetic sensor's bytes, decoded once; xy stays resident in HBM
+    pk = eng.synth_express(S, PACKETS, seed=0, scan_base=rank * S)
+    xy, _, pk_status = eng.express_to_cart(pk, BEAMS)
+    assert not bool(pk_status.any().item()), "synthetic packets rejected"
     r0 = eng.ransac_lines(xy, chunk=CHUNK, trials=TRIALS, thr=THR, seed=0, scan_base=rank * S, out=pipe.rout)
     pipe.install_map_from_lines(r0["line"], r0["ninl"])                     # untimed set-up: the known map
     pipe.ukf["u"].fill_(1.0)
@@ -245,20 +259,17 @@ def main():
     assert int(pipe.ukf["status"].abs().sum().item()) == 0, "UKF status flags set"
 
     # ---- end to end through the host-buffer API --------------------------------------------
-    e2e = None
-    if not args.no_e2e:
-        xy_h = pipe.alloc_host_io()
-        xy_h.copy_(xy)                                                       # untimed: fill the host buffer
-        torch.cuda.synchronize()
+    def e2e_leg(host_in):
         for _ in range(2):
-            pipe.step_host(xy_h)
+            pipe.step_host(host_in, slices=E2E_SLICES)
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
+        n0e = eng.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(args.steps):
-            out_h = pipe.step_host(xy_h)
+            out_h = pipe.step_host(host_in, slices=E2E_SLICES)
             torch.cuda.current_stream().synchronize()                        # results are on the host
             _ = float(out_h["ninl"][0, 0])
         e1.record()
@@ -268,9 +279,28 @@ def main():
             t = torch.tensor([ems], dtype=torch.float64, device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ems = float(t.item())
-        h2d, d2h = pipe.io_bytes()
-        e2e = {"value": world * S * args.steps / (ems * 1e-3), "unit": "scans/s",
-               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ems / args.steps}
+        h2d, d2h = pipe.io_bytes(host_in)
+        return {"value": world * S * args.steps / (ems * 1e-3), "unit": "scans/s",
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ems / args.steps,
+                "slices": E2E_SLICES, "gpu_launches": eng.launch_count() - n0e}
+
+    e2e = e2e_xy = None
+    if not args.no_e2e:
+        # headline: the sensor's own bytes in (what Lidar._read_response returns, lidar.py:161-167),
+        # decoded on the device, per-scan results out
+        pk_h = pipe.alloc_host_io("packets", PACKETS)
+        pk_h.copy_(pk)                                                       # untimed: fill the host buffer
+        torch.cuda.synchronize()
+        e2e = e2e_leg(pk_h)
+        e2e["input"] = "RPLidar express packets, %d x 84 B per scan, decoded on the device" % PACKETS
+        del pk_h
+        # the same with cartesian float64 scans in (what scanning() queues, functions.py:59-66)
+        xy_h = pipe.alloc_host_io("xy")
+        xy_h.copy_(xy)
+        torch.cuda.synchronize()
+        e2e_xy = e2e_leg(xy_h)
+        e2e_xy["input"] = "cartesian float64 points, 5760 B per scan"
+        del xy_h
 
     if rank == 0:
         value = world * S * args.steps / (ms * 1e-3)
@@ -283,7 +313,10 @@ def main():
         ach_tflops = S * PHE_PER_SCAN * FLOP_PER_PHE / (k_ms * 1e-3) * 1e-12
         roofline = {
             "kernel": "ransac_lines_kernel", "bound": "fp64-issue", "achieved": ach_tflops, "peak": fp64_peak,
-            "unit": "TFLOP/s", "frac": ach_tflops / fp64_peak if fp64_peak > 0 else None, "traffic": None,
+            "unit": "TFLOP/s", "frac": ach_tflops / fp64_peak if fp64_peak > 0 else None,
+            "traffic": S * NCU_DRAM_BYTES_PER_SCAN if (S % 4 == 0 and BEAMS == 360) else None,
+            "traffic_source": "ncu dram__bytes_read+write of one launch at 262,144 scans, scaled per scan "
+                              "(profiles/r01f_ransac_c2_ncu_summary.txt); algorithmic bytes per launch: %d" % (S * BYTES_PER_SCAN),
             "peak_source": "measured in this run: lslam_fp64_peak (dependent DFMA chains, 2 flop each)",
             "kernel_ms": k_ms, "hyps_per_s": S * 4 * TRIALS / (k_ms * 1e-3),
             "hbm": {"achieved": S * BYTES_PER_SCAN / (k_ms * 1e-3) * 1e-9, "peak": hbm_peak, "unit": "GB/s",
@@ -295,7 +328,7 @@ def main():
             n = args.cpu_sample or 16384
             rate, threads, secs = cpu_pipeline_rate(n)
             cpu = {"value": rate, "unit": "scans/s", "cores": threads, "kind": "port",
-                   "sample": "%d of the %d scans of one step, C oracle (OpenMP), %.1f s" % (n, S, secs)}
+                   "sample": "%d of the %d scans of one step from packet bytes, C oracle (OpenMP), %.1f s" % (n, S, secs)}
         line = {
             "metric": "scans/s (RANSAC+assoc+UKF)", "value": value, "unit": "scans/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
@@ -303,7 +336,7 @@ def main():
             "data": "synthetic", "config": workload_config(args, world),
             "stages": ["ransac", "associate", "ukf"], "hit_rate": hit_rate,
             "ransac_hyps_per_s": world * S * 4 * TRIALS * args.steps / (ms * 1e-3),
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_xy": e2e_xy, "gpu_launches": launches,
             "clocks": clocks, "parity_faults": faults,
         }
         print(json.dumps(line), flush=True)

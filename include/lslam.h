@@ -42,7 +42,7 @@ int lslam_create(int device, void **handle);
 int lslam_destroy(void *handle);
 const char *lslam_last_error(void *handle);
 /* ABI version of the loaded library (LSLAM_ABI_VERSION at build time). */
-#define LSLAM_ABI_VERSION 2
+#define LSLAM_ABI_VERSION 3
 int lslam_abi_version(void);
 /* Launch-shape tuning knobs; 0 restores the built-in heuristic.  Results never depend on them.
  *   "ransac.kernel"  0 default, 1 phase-structured kernel, 2 warp-specialised persistent kernel
@@ -180,6 +180,29 @@ int lslam_ukf_update(void *handle, double *x, double *P, const double *z, int32_
                      const double *lm_pos, const int32_t *lm_valid, int32_t valid_min, int32_t F,
                      int32_t L, const double *params_h, int32_t *status, const double *sigmas_f,
                      void *stream);
+
+/* ---- input stage from raw sensor bytes: RPLidar express packets -> cartesian -------
+ * Replaces ExpressPacket.decode (/root/reference/lidar.py:66-91), Lidar._process_express_scan
+ * (lidar.py:179-187) and the conversion inside scanning() (functions.py:59-60) for a batch of
+ * revolutions.  packets [nscans][packets_per_scan][84] bytes (4-byte aligned): one revolution =
+ * packets_per_scan consecutive packets; the start angle after a revolution's last packet is its
+ * first packet's.  The first `beams` (<= 32*packets_per_scan) measures of each revolution are
+ * written to xy [nscans,beams,2]; meas (nullable) [nscans,beams,2] receives (angle_deg, distance_mm),
+ * bit-identical to the reference's Python floats; status (nullable) [nscans] receives
+ * LSLAM_EXPRESS_BAD_SYNC / _BAD_CHECKSUM bits where the reference raises ValueError (lidar.py:70-77),
+ * and the points of a rejected packet are NaN (lslam_ransac_lines then reports LSLAM_ERR_NONFINITE
+ * for the chunks they fall in). */
+#define LSLAM_EXPRESS_BAD_SYNC 1
+#define LSLAM_EXPRESS_BAD_CHECKSUM 2
+#define LSLAM_EXPRESS_PACKET_BYTES 84
+int lslam_express_to_cart(void *handle, const uint8_t *packets, int64_t nscans, int32_t packets_per_scan,
+                          int32_t beams, double *xy, double *meas, int32_t *status, void *stream);
+
+/* Synthetic sensor: revolutions scan_base.. of the random-room scene of lslam_synth_scans, emitted
+ * as express packets (uniform rotation, random start phase, +-0.5 degree correction codes, integer
+ * millimetre ranges, new-scan flag on the first packet).  packets [nscans][packets_per_scan][84]. */
+int lslam_synth_express(void *handle, uint8_t *packets, int64_t nscans, int32_t packets_per_scan,
+                        uint64_t seed, uint64_t scan_base, double noise_mm, double dropout, void *stream);
 
 /* ---- synthetic scans (headless replacement for the capture process) ----------------
  * Device twin of lidar_slam_b200/synth.py random_room_scans(): scan s (global index

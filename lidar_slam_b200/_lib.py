@@ -18,7 +18,7 @@ LSLAM_ERR_NO_MODEL = -3
 LSLAM_ERR_CUDA = -4
 LSLAM_ERR_NONFINITE = -5
 LSLAM_ERR_CAPACITY = -6
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 _vp = ctypes.c_void_p
 _i32 = ctypes.c_int32
@@ -45,6 +45,8 @@ SIGNATURES = {
     "lslam_ukf_predict": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i32, ctypes.POINTER(_f64), _i32, _vp, _vp, _vp]),
     "lslam_ukf_update": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32,
                                         ctypes.POINTER(_f64), _vp, _vp, _vp]),
+    "lslam_express_to_cart": (ctypes.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _vp, _vp, _vp]),
+    "lslam_synth_express": (ctypes.c_int, [_vp, _vp, _i64, _i32, _u64, _u64, _f64, _f64, _vp]),
     "lslam_synth_scans": (ctypes.c_int, [_vp, _vp, _i32, _i32, _u64, _u64, _f64, _f64, _vp]),
     "lslam_fp64_peak": (ctypes.c_int, [_vp, _f64, ctypes.POINTER(_f64)]),
 }
@@ -111,6 +113,15 @@ class Handle:
     # -- entry points --
     def polar_to_cart(self, dist, ang_deg, xy, npts, stream=0):
         self._check(self.cdll.lslam_polar_to_cart(self._h, dist, ang_deg, xy, npts, stream))
+
+    def express_to_cart(self, packets, nscans, packets_per_scan, beams, xy, meas=None, status=None, stream=0):
+        self._check(self.cdll.lslam_express_to_cart(self._h, packets, nscans, packets_per_scan, beams, xy, meas,
+                                                    status, stream))
+
+    def synth_express(self, packets, nscans, packets_per_scan, seed, scan_base, noise_mm, dropout, stream=0):
+        self._check(self.cdll.lslam_synth_express(self._h, packets, nscans, packets_per_scan,
+                                                  int(seed) & (2**64 - 1), int(scan_base) & (2**64 - 1),
+                                                  float(noise_mm), float(dropout), stream))
 
     def ransac_lines(self, xy, npts, B, N, chunk, trials, thr, seed, scan_base,
                      line, ninl, win_trial, win_pair, ssum, inl_mask, stream=0):

@@ -63,6 +63,30 @@ class Engine:
                                   dist_mm.numel(), self._stream())
         return xy
 
+    def express_to_cart(self, packets, beams, xy=None, want_meas=False, status=None):
+        """Raw RPLidar express packets [B, P, 84] uint8 on this device -> xy [B, beams, 2] (lidar.py:66-91,
+        179-187 + functions.py:59-60 on the device).  Returns (xy, meas or None, status [B] int32)."""
+        packets = self._check(packets, torch.uint8, "packets")
+        if packets.dim() != 3 or packets.shape[2] != 84:
+            raise ValueError("packets must be [B, P, 84]")
+        B, P = int(packets.shape[0]), int(packets.shape[1])
+        if xy is None:
+            xy = torch.empty((B, beams, 2), dtype=torch.float64, device=self.device)
+        meas = torch.empty((B, beams, 2), dtype=torch.float64, device=self.device) if want_meas else None
+        if status is None:
+            status = torch.empty(B, dtype=torch.int32, device=self.device)
+        self.handle.express_to_cart(packets.data_ptr(), B, P, int(beams), xy.data_ptr(),
+                                    meas.data_ptr() if want_meas else None, status.data_ptr(), self._stream())
+        return xy, meas, status
+
+    def synth_express(self, B, packets_per_scan=12, seed=0, scan_base=0, noise_mm=5.0, dropout=0.01, out=None):
+        """Synthetic sensor bytes [B, P, 84] uint8 (device twin of the random-room scene)."""
+        if out is None:
+            out = torch.empty((B, packets_per_scan, 84), dtype=torch.uint8, device=self.device)
+        self.handle.synth_express(out.data_ptr(), B, packets_per_scan, seed, scan_base, noise_mm, dropout,
+                                  self._stream())
+        return out
+
     def alloc_ransac_out(self, B, N, chunk=CHUNK):
         C = (N + chunk - 1) // chunk
         W = (chunk + 31) // 32

@@ -8,6 +8,7 @@
 #include "aux_kernels.cuh"
 #include "assoc.cuh"
 #include "ukf.cuh"
+#include "express.cuh"
 
 #include "../../include/lslam.h"
 
@@ -390,6 +391,57 @@ extern "C" int lslam_synth_scans(void *handle, double *xy, int32_t B, int32_t be
     auto kern = synth_scans_kernel;
     LSLAM_LAUNCH(kern, (unsigned)grid, threads, 0, (cudaStream_t)stream, reinterpret_cast<double2 *>(xy),
                  total, (int)beams, seed, scan_base, noise_mm, dropout);
+    h->launches++;
+    LSLAM_CUDA_TRY(h, cudaGetLastError());
+    return LSLAM_OK;
+}
+
+// ---- N2 input stage: express packets -> points; synthetic packets --------------------------
+static int express_shape(Handle *h, int64_t nscans, int P, unsigned *grid, int *threads)
+{
+    *threads = 32 * (P < kExpressMaxWarps ? P : kExpressMaxWarps);
+    const long long cap = (long long)h->sms * 64;
+    *grid = (unsigned)(nscans < cap ? nscans : cap);
+    return 0;
+}
+
+extern "C" int lslam_express_to_cart(void *handle, const uint8_t *packets, int64_t nscans, int32_t packets_per_scan,
+                                     int32_t beams, double *xy, double *meas, int32_t *status, void *stream)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr) return LSLAM_ERR_BAD_ARG;
+    if (nscans < 0 || packets_per_scan < 1 || beams < 1 || beams > 32 * (int64_t)packets_per_scan ||
+        (nscans > 0 && (!packets || !xy)))
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_express_to_cart: bad arguments");
+    if (((uintptr_t)xy & 15) != 0 || ((uintptr_t)meas & 15) != 0 || ((uintptr_t)packets & 3) != 0)
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_express_to_cart: xy/meas must be 16-byte, packets 4-byte aligned");
+    if (nscans == 0) return LSLAM_OK;
+    DeviceGuard g(h->device);
+    unsigned grid; int threads;
+    express_shape(h, nscans, packets_per_scan, &grid, &threads);
+    auto kern = express_to_cart_kernel;
+    LSLAM_LAUNCH(kern, grid, threads, kExpressSmem, (cudaStream_t)stream, reinterpret_cast<const uint32_t *>(packets),
+                 (long long)nscans, (int)packets_per_scan, (int)beams, reinterpret_cast<double2 *>(xy),
+                 reinterpret_cast<double2 *>(meas), status);
+    h->launches++;
+    LSLAM_CUDA_TRY(h, cudaGetLastError());
+    return LSLAM_OK;
+}
+
+extern "C" int lslam_synth_express(void *handle, uint8_t *packets, int64_t nscans, int32_t packets_per_scan,
+                                   uint64_t seed, uint64_t scan_base, double noise_mm, double dropout, void *stream)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr) return LSLAM_ERR_BAD_ARG;
+    if (nscans < 0 || packets_per_scan < 1 || (nscans > 0 && !packets) || ((uintptr_t)packets & 3) != 0)
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_synth_express: bad arguments");
+    if (nscans == 0) return LSLAM_OK;
+    DeviceGuard g(h->device);
+    unsigned grid; int threads;
+    express_shape(h, nscans, packets_per_scan, &grid, &threads);
+    auto kern = synth_express_kernel;
+    LSLAM_LAUNCH(kern, grid, threads, kExpressSmem, (cudaStream_t)stream, reinterpret_cast<uint32_t *>(packets),
+                 (long long)nscans, (int)packets_per_scan, seed, scan_base, noise_mm, dropout);
     h->launches++;
     LSLAM_CUDA_TRY(h, cudaGetLastError());
     return LSLAM_OK;

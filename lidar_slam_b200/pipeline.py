@@ -28,26 +28,48 @@ class ScanPipeline:
         self.aout = eng.alloc_assoc_out(self.S, self.C)
         self.ukf = eng.alloc_ukf(self.S, self.C)
         self.xy_dev = None
+        self.pk_dev = None
+        self.status_dev = None
         self._host_out = None
+        self._view_cache = {}
+        self._ov = None
 
     # ---- device-resident step: inputs already in HBM ------------------------------------
-    def step(self, xy, u=None, ransac_events=None):
-        """xy [S, N, 2] float64 on the device.  Asynchronous on the current stream.  Returns the
-        dict of result tensors (views of buffers owned by the pipeline, overwritten next step).
-        ``ransac_events`` = (start, end) torch.cuda.Event pair recorded around the RANSAC launch."""
+    @staticmethod
+    def _slice(d, s0, s1):
+        return {k: (v[s0:s1] if isinstance(v, torch.Tensor) and v.dim() > 0 and k != "params" else v)
+                for k, v in d.items()}
+
+    def _views(self, s0, s1):
+        """Views of the pipeline's state and result buffers for streams [s0, s1) (cached)."""
+        key = (s0, s1)
+        v = self._view_cache.get(key)
+        if v is None:
+            v = {"rout": self._slice(self.rout, s0, s1), "tables": self._slice(self.tables, s0, s1),
+                 "aout": self._slice(self.aout, s0, s1), "ukf": self._slice(self.ukf, s0, s1)}
+            self._view_cache[key] = v
+        return v
+
+    def step(self, xy, u=None, ransac_events=None, s0=0, s1=None):
+        """xy [s1-s0, N, 2] float64 on the device: the scans of streams [s0, s1) (default: all).
+        Asynchronous on the current stream.  Returns the dict of result tensors (views of buffers
+        owned by the pipeline, overwritten next step).  ``ransac_events`` = (start, end)
+        torch.cuda.Event pair recorded around the RANSAC launch."""
         eng = self.eng
+        s1 = self.S if s1 is None else s1
+        v = self._views(s0, s1)
         if ransac_events is not None:
             ransac_events[0].record()
         r = eng.ransac_lines(xy, chunk=self.chunk, trials=self.trials, thr=self.thr, seed=self.seed,
-                             scan_base=self.scan_base, out=self.rout)
+                             scan_base=self.scan_base + s0, out=v["rout"])
         if ransac_events is not None:
             ransac_events[1].record()
-        a = eng.associate(r["line"], self.tables, q_valid=r["ninl"], out=self.aout)
+        a = eng.associate(r["line"], v["tables"], q_valid=r["ninl"], out=v["aout"])
         # measurement slot c = chunk c's line: range/bearing of its inlier centroid against the matched
         # stored landmark's position; slots whose line missed (match < 0) are not used
-        eng.ukf_step(self.ukf, r["line"], a["hit_pos"], lm_valid=a["match"], valid_min=0, u=u)
+        eng.ukf_step(v["ukf"], r["line"], a["hit_pos"], lm_valid=a["match"], valid_min=0, u=u)
         return {"line": r["line"], "ninl": r["ninl"], "match": a["match"], "match_id": a["match_id"],
-                "x": self.ukf["x"], "P": self.ukf["P"]}
+                "x": v["ukf"]["x"], "P": v["ukf"]["P"]}
 
     # ---- a known map (benchmark / test set-up; data movement only) -----------------------------
     def install_map_from_lines(self, line, ninl, life=batch.Engine.LIFE):
@@ -73,34 +95,113 @@ class ScanPipeline:
         t["count"].fill_(k2)
         t["next_id"].fill_(k2)
 
-    # ---- end-to-end step: host buffers in, host buffers out -----------------------------
+    # ---- end-to-end steps: host buffers in, host buffers out ------------------------------
     def result_keys(self):
         return ("line", "ninl", "match_id", "x", "P")
 
-    def alloc_host_io(self):
-        """Pinned host buffers for step_host: the scans in, the per-step results out."""
-        xy_h = torch.empty((self.S, self.N, 2), dtype=torch.float64).pin_memory()
-        return xy_h
+    def alloc_host_io(self, kind="xy", packets_per_scan=12):
+        """Pinned host input buffer for step_host: cartesian scans ("xy": [S, N, 2] float64, what
+        scanning() puts on the queue, functions.py:59-66) or raw sensor bytes ("packets":
+        [S, P, 84] uint8, what Lidar._read_response returns, lidar.py:161-167)."""
+        if kind == "xy":
+            return torch.empty((self.S, self.N, 2), dtype=torch.float64).pin_memory()
+        if kind == "packets":
+            if 32 * packets_per_scan < self.N:
+                raise ValueError("packets_per_scan * 32 must cover the scan's beams")
+            return torch.empty((self.S, packets_per_scan, 84), dtype=torch.uint8).pin_memory()
+        raise ValueError("kind must be 'xy' or 'packets'")
 
-    def step_host(self, xy_host):
-        """xy_host [S, N, 2] float64 in pinned host memory -> dict of pinned host result tensors.
-        Host->device copy, the three kernels and the device->host copies are queued on the current
-        stream; the caller synchronises."""
-        if self.xy_dev is None:
-            self.xy_dev = torch.empty((self.S, self.N, 2), dtype=torch.float64, device=self.eng.device)
-        self.xy_dev.copy_(xy_host, non_blocking=True)
-        res = self.step(self.xy_dev)
+    def _ensure_host_out(self):
         if self._host_out is None:
-            self._host_out = {k: torch.empty(res[k].shape, dtype=res[k].dtype).pin_memory()
-                              for k in self.result_keys()}
-        for k in self.result_keys():
-            self._host_out[k].copy_(res[k], non_blocking=True)
+            shapes = {"line": ((self.S, self.C, 8), torch.float64), "ninl": ((self.S, self.C), torch.int32),
+                      "match_id": ((self.S, self.C), torch.int32), "x": ((self.S, 3), torch.float64),
+                      "P": ((self.S, 3, 3), torch.float64), "status": ((self.S,), torch.int32)}
+            self._host_out = {k: torch.empty(sh, dtype=dt).pin_memory() for k, (sh, dt) in shapes.items()}
         return self._host_out
 
-    def io_bytes(self):
-        h2d = self.S * self.N * 16
+    def step_host(self, host_in, slices=1):
+        """One step from pinned host memory to pinned host memory.
+
+        host_in: [S, N, 2] float64 scans, or [S, P, 84] uint8 express packets (decoded on the device:
+        lslam_express_to_cart).  With slices == 1 everything is queued on the current stream.  With
+        slices > 1 the streams are cut into that many contiguous slices and the host->device copies,
+        the kernels and the device->host copies of successive slices run on three CUDA streams, so
+        the PCIe transfers in both directions overlap the kernels (slice k's kernels wait for slice
+        k's input only).  The current stream waits for all three at the end; the caller synchronises
+        it before reading the returned pinned tensors (result_keys(), plus "status" per scan for
+        packets)."""
+        packets = host_in.dtype == torch.uint8
+        dev = self.eng.device
+        if packets:
+            if self.pk_dev is None or self.pk_dev.shape != host_in.shape:
+                self.pk_dev = torch.empty(host_in.shape, dtype=torch.uint8, device=dev)
+                self.status_dev = torch.zeros((self.S,), dtype=torch.int32, device=dev)
+            dev_in = self.pk_dev
+        if self.xy_dev is None:
+            self.xy_dev = torch.empty((self.S, self.N, 2), dtype=torch.float64, device=dev)
+        if not packets:
+            dev_in = self.xy_dev
+        out = self._ensure_host_out()
+        keys = self.result_keys()
+        K = max(1, min(int(slices), self.S))
+        bounds = [(self.S * k // K, self.S * (k + 1) // K) for k in range(K)]
+        if K == 1:
+            dev_in.copy_(host_in, non_blocking=True)
+            if packets:
+                self.eng.express_to_cart(dev_in, self.N, xy=self.xy_dev, status=self.status_dev)
+            res = self.step(self.xy_dev)
+            for k in keys:
+                out[k].copy_(res[k], non_blocking=True)
+            if packets:
+                out["status"].copy_(self.status_dev, non_blocking=True)
+            return out
+        if self._ov is None or self._ov["K"] != K:
+            self._ov = {"K": K, "in": torch.cuda.Stream(dev), "run": torch.cuda.Stream(dev),
+                        "out": torch.cuda.Stream(dev), "ev_in": [torch.cuda.Event() for _ in range(K)],
+                        "ev_run": [torch.cuda.Event() for _ in range(K)],
+                        "ev_out": [torch.cuda.Event() for _ in range(K)], "primed": False}
+        ov = self._ov
+        cur = torch.cuda.current_stream(dev)
+        for st in ("in", "run", "out"):
+            ov[st].wait_stream(cur)
+        for k, (a, b) in enumerate(bounds):
+            with torch.cuda.stream(ov["in"]):
+                if ov["primed"]:
+                    ov["in"].wait_event(ov["ev_run"][k])      # the previous step's kernels have read this slice
+                dev_in[a:b].copy_(host_in[a:b], non_blocking=True)
+                ov["ev_in"][k].record()
+        for k, (a, b) in enumerate(bounds):
+            with torch.cuda.stream(ov["run"]):
+                ov["run"].wait_event(ov["ev_in"][k])
+                if ov["primed"]:
+                    ov["run"].wait_event(ov["ev_out"][k])     # the previous step's results have left
+                if packets:
+                    self.eng.express_to_cart(dev_in[a:b], self.N, xy=self.xy_dev[a:b], status=self.status_dev[a:b])
+                res = self.step(self.xy_dev[a:b], s0=a, s1=b)
+                ov["ev_run"][k].record()
+            with torch.cuda.stream(ov["out"]):
+                ov["out"].wait_event(ov["ev_run"][k])
+                for key in keys:
+                    out[key][a:b].copy_(res[key], non_blocking=True)
+                if packets:
+                    out["status"][a:b].copy_(self.status_dev[a:b], non_blocking=True)
+                ov["ev_out"][k].record()
+        ov["primed"] = True
+        for st in ("in", "run", "out"):
+            cur.wait_stream(ov[st])
+        return out
+
+    def io_bytes(self, host_in=None):
+        h2d = self.S * self.N * 16 if host_in is None else host_in.numel() * host_in.element_size()
         d2h = 0
         per = {"line": self.C * 64, "ninl": self.C * 4, "match_id": self.C * 4, "x": 24, "P": 72}
         for k in self.result_keys():
             d2h += self.S * per[k]
+        if host_in is not None and host_in.dtype == torch.uint8:
+            d2h += self.S * 4
         return h2d, d2h
+
+    def launches_per_step(self, host_in=None, slices=1):
+        """Kernel launches of this library inside one step (lslam_launch_count difference)."""
+        per = 3 + (1 if host_in is not None and host_in.dtype == torch.uint8 else 0)
+        return per * max(1, min(int(slices), self.S))

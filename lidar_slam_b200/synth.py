@@ -111,3 +111,58 @@ def chunk_revolution(xy, chunk=MIN_NEIGHBOORS):
         out.append(xy[s:].tolist())
     out.append(0)
     return out
+
+
+# ---- raw sensor bytes: RPLidar express packets (lidar.py:66-91 is the decoder) --------------------
+def pack_express(dist, code, start_q6, new_scan):
+    """Vectorised packet assembly: dist [..., 32] ints < 2**14, code [..., 32] 6-bit angle-correction
+    codes as the reference's decoder assembles them (low nibble in the cabin's fifth byte, bits 4-5 in
+    the two low bits of the distance byte), start_q6 / new_scan [...] -> uint8 [..., 84] with sync
+    nibbles and XOR checksum."""
+    dist = np.asarray(dist, dtype=np.int64)
+    code = np.asarray(code, dtype=np.int64)
+    lead = dist.shape[:-1]
+    p = np.zeros(lead + (84,), dtype=np.uint8)
+    sq = np.asarray(start_q6, dtype=np.int64)
+    p[..., 2] = sq & 0xFF
+    p[..., 3] = ((sq >> 8) & 0x7F) | ((np.asarray(new_scan, dtype=np.int64) & 1) << 7)
+    d1, d2, c1, c2 = dist[..., 0::2], dist[..., 1::2], code[..., 0::2], code[..., 1::2]
+    cab = np.zeros(lead + (16, 5), dtype=np.uint8)
+    cab[..., 0] = ((d1 & 0x3F) << 2) | ((c1 >> 4) & 3)
+    cab[..., 1] = (d1 >> 6) & 0xFF
+    cab[..., 2] = ((d2 & 0x3F) << 2) | ((c2 >> 4) & 3)
+    cab[..., 3] = (d2 >> 6) & 0xFF
+    cab[..., 4] = (c1 & 0xF) | ((c2 & 0xF) << 4)
+    p[..., 4:] = cab.reshape(lead + (80,))
+    cs = np.bitwise_xor.reduce(p[..., 2:], axis=-1)
+    p[..., 0] = 0xA0 | (cs & 0x0F)
+    p[..., 1] = 0x50 | (cs >> 4)
+    return p
+
+
+def random_room_express(nscans, packets_per_scan=12, seed=0, noise_mm=5.0, dropout=0.01):
+    """The random-room scene as the sensor would send it: [nscans, P, 84] uint8.  Uniform rotation
+    (P*32 measures per revolution), random start phase, correction codes within +-0.5 degree, integer
+    millimetre ranges.  Host twin of lslam_synth_express (same scene model, NumPy streams)."""
+    P = packets_per_scan
+    out = np.empty((nscans, P, 84), dtype=np.uint8)
+    i = np.arange(1, 33, dtype=np.float64)
+    for s in range(nscans):
+        rng = np.random.default_rng([seed, s, 7])
+        w, h = rng.uniform(2000.0, 6000.0, size=2)
+        px = rng.uniform(-w / 2 + 300.0, w / 2 - 300.0)
+        py = rng.uniform(-h / 2 + 300.0, h / 2 - 300.0)
+        th = rng.uniform(-np.pi, np.pi)
+        phase = int(rng.integers(0, 360 * 64))
+        sq = (phase + (np.arange(P + 1) % P) * 360 * 64 // P) % (360 * 64)
+        start, nxt = sq[:P] / 64.0, sq[1:] / 64.0
+        r3 = rng.integers(0, 8, size=(P, 32))
+        code = np.where(r3 & 4, 28 + (r3 & 3), r3 & 3)
+        dth = np.where(code & 16, code - 32, code) / 8.0
+        ang = (start[:, None] + (((nxt - start) % 360) / 32)[:, None] * i[None, :] - dth) % 360
+        d = room_ranges((px, py, th), w, h, ang) + noise_mm * rng.standard_normal((P, 32))
+        if dropout > 0:
+            d = np.where(rng.random((P, 32)) < dropout, 0.0, d)
+        di = np.clip(np.rint(d), 0, 16383).astype(np.int64)
+        out[s] = pack_express(di, code, sq[:P], (np.arange(P) == 0).astype(np.int64))
+    return out

@@ -149,6 +149,19 @@ def empty_tables(T, M):
             "count": np.zeros(T, np.int32), "next_id": np.zeros(T, np.int32)}
 
 
+def express_to_cart(packets, beams, want_meas=False, nthreads=0):
+    """oracle_express_to_cart: packets [B, P, 84] uint8 -> (xy [B, beams, 2], meas or None, status [B])."""
+    packets = np.ascontiguousarray(packets, dtype=np.uint8)
+    B, P, _ = packets.shape
+    xy = np.empty((B, beams, 2), np.float64)
+    meas = np.empty((B, beams, 2), np.float64) if want_meas else None
+    status = np.empty(B, np.int32)
+    lib().oracle_express_to_cart(packets.ctypes.data_as(ctypes.c_void_p), ctypes.c_longlong(B), ctypes.c_int(P),
+                                 ctypes.c_int(beams), _p(xy, c_double_p), _p(meas, c_double_p),
+                                 _p(status, c_int32_p), ctypes.c_int32(nthreads))
+    return xy, meas, status
+
+
 def pipeline_step(xy, tables, x, P, u=None, chunk=100, trials=100, thr=20.0, seed=0, scan_base=0,
                   params=None, nthreads=0):
     """One step of lidar_slam_b200.pipeline.ScanPipeline on the CPU (all three stages in C, OpenMP

@@ -153,6 +153,7 @@ static inline unsigned __reduce_max_sync(unsigned, unsigned v) { return emu_redu
 static inline unsigned __reduce_min_sync(unsigned, unsigned v) { return emu_reduce(v, [](unsigned a, unsigned b) { return a < b ? a : b; }); }
 static inline unsigned __reduce_add_sync(unsigned, unsigned v) { return emu_reduce(v, [](unsigned a, unsigned b) { return a + b; }); }
 static inline unsigned __reduce_or_sync(unsigned, unsigned v) { return emu_reduce(v, [](unsigned a, unsigned b) { return a | b; }); }
+static inline unsigned __reduce_xor_sync(unsigned, unsigned v) { return emu_reduce(v, [](unsigned a, unsigned b) { return a ^ b; }); }
 
 // ---- scalar intrinsics ----
 static inline int __popc(unsigned v) { return __builtin_popcount(v); }
@@ -199,6 +200,7 @@ static inline int atomicMax(int *p, int v) {
     return old;
 }
 static inline unsigned atomicOr(unsigned *p, unsigned v) { return __atomic_fetch_or(p, v, __ATOMIC_SEQ_CST); }
+static inline int atomicOr(int *p, int v) { return __atomic_fetch_or(p, v, __ATOMIC_SEQ_CST); }
 
 // ---- runtime API stubs: "device memory" is host memory ----
 typedef int cudaError_t;

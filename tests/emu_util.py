@@ -107,3 +107,22 @@ def emu_ukf_step(x, P, u, z, lm_pos, lm_valid=None, valid_min=1, zmode=0, params
     h.ukf_step(ptr(x), ptr(P), ptr(u), ptr(z), zs, zmode, ptr(lm_pos) if z is not None else None,
                ptr(lm_valid), valid_min, F, L, params, flags, ptr(status), ptr(sigmas_f))
     return x, P, status
+
+
+def emu_express_to_cart(packets, beams, want_meas=True, handle=None):
+    """lslam_express_to_cart on the emulated library."""
+    h = handle or emu_handle()
+    packets = np.ascontiguousarray(packets, dtype=np.uint8)
+    B, P, _ = packets.shape
+    xy = np.full((B, beams, 2), -7.0)
+    meas = np.full((B, beams, 2), -7.0) if want_meas else None
+    status = np.full(B, -99, np.int32)
+    h.express_to_cart(ptr(packets), B, P, beams, ptr(xy), ptr(meas), ptr(status))
+    return xy, meas, status
+
+
+def emu_synth_express(B, P=12, seed=0, scan_base=0, noise_mm=5.0, dropout=0.01, handle=None):
+    h = handle or emu_handle()
+    packets = np.zeros((B, P, 84), np.uint8)
+    h.synth_express(ptr(packets), B, P, seed, scan_base, noise_mm, dropout)
+    return packets

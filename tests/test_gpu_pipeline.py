@@ -63,3 +63,34 @@ def test_host_path_equals_device_path(gpu_engine):
             assert torch.equal(ra[k].cpu().view(torch.uint8), hb[k].view(torch.uint8)), k
     h2d, d2h = b.io_bytes()
     assert h2d == xy_h.numel() * 8 and d2h == sum(hb[k].numel() * hb[k].element_size() for k in b.result_keys())
+
+
+@pytest.mark.parametrize("kind,slices", [("xy", 4), ("packets", 1), ("packets", 5)])
+def test_overlapped_and_packet_host_paths(gpu_engine, kind, slices):
+    """Sliced three-stream host path and the raw-packet input give exactly the single-stream results."""
+    import torch
+    from lidar_slam_b200 import pipeline
+    eng = gpu_engine
+    S = 3000                      # not a multiple of the slice count
+    pk = eng.synth_express(S, 12, seed=8)
+    xy, _, st = eng.express_to_cart(pk, 360)
+    assert not st.any().item()
+    a = pipeline.ScanPipeline(eng, S, seed=2, scan_base=5)
+    b = pipeline.ScanPipeline(eng, S, seed=2, scan_base=5)
+    r0 = eng.ransac_lines(xy, seed=2, scan_base=5)
+    a.install_map_from_lines(r0["line"], r0["ninl"])
+    b.install_map_from_lines(r0["line"], r0["ninl"])
+    h_in = b.alloc_host_io(kind, 12)
+    h_in.copy_(pk if kind == "packets" else xy)
+    torch.cuda.synchronize()
+    for _ in range(3):
+        ra = a.step(xy)
+        hb = b.step_host(h_in, slices=slices)
+        torch.cuda.synchronize()
+        for k in b.result_keys():
+            assert torch.equal(ra[k].cpu().view(torch.uint8), hb[k].view(torch.uint8)), k
+        if kind == "packets":
+            assert not hb["status"].any().item()
+    assert torch.equal(a.tables["life"], b.tables["life"])
+    h2d, d2h = b.io_bytes(h_in)
+    assert h2d == h_in.numel() * h_in.element_size()
