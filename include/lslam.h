@@ -181,6 +181,28 @@ int lslam_ukf_update(void *handle, double *x, double *P, const double *z, int32_
                      int32_t L, const double *params_h, int32_t *status, const double *sigmas_f,
                      void *stream);
 
+/* ---- OLS-flavour RANSAC ------------------------------------------------------------
+ * Replaces sklearn.linear_model.RANSACRegressor(residual_threshold=3).fit(x[i:k], y[i:k]) +
+ * inlier_mask_ / estimator_.coef_ / predict of /root/reference/line_detection.py:51-73 for every
+ * window of `window` (PNT_NBR = 50, :9) consecutive points of every scan.
+ *   xy [B,N,2], npts [B] or NULL as for lslam_ransac_lines; C = ceil(N/window) window slots per scan
+ *   (the last window of a scan may be short, :53-56).
+ *   thr: inlier iff |y - y_hat| <= thr (non-strict); stop_probability: sklearn's (default 0.99);
+ *   trials: max_trials (default 100).
+ *   pairs: NULL = the library's Philox sampler (seed, scan_base as for lslam_ransac_lines), or
+ *          [B,C,trials,2] explicit sample index pairs per trial (what sklearn's RandomState drew).
+ * out: fit [B,C,8] = coef, intercept, R^2 score of the accepted trial on its inliers, min x, max x of
+ *          the window (the span line_detection.py:66 draws), mean x, mean y of the inliers, 0
+ *      ninl [B,C] inlier count, or 0 (empty slot), LSLAM_ERR_TOO_FEW_POINTS (1-point window: sklearn's
+ *          "min_samples may not be larger than number of samples" ValueError), LSLAM_ERR_NO_MODEL
+ *          (no trial accepted: sklearn's "could not find a valid consensus set" ValueError)
+ *      ntrials [B,C] = n_trials_ (trials actually run), best_trial [B,C] (index of the accepted trial)
+ *      inl_mask [B,C,ceil(window/32)] = inlier_mask_ as bit words */
+int lslam_ransac_ols(void *handle, const double *xy, const int32_t *npts, int32_t B, int32_t N,
+                     int32_t window, int32_t trials, double thr, double stop_probability, uint64_t seed,
+                     uint64_t scan_base, const int32_t *pairs, double *fit, int32_t *ninl,
+                     int32_t *ntrials, int32_t *best_trial, uint32_t *inl_mask, void *stream);
+
 /* ---- input stage from raw sensor bytes: RPLidar express packets -> cartesian -------
  * Replaces ExpressPacket.decode (/root/reference/lidar.py:66-91), Lidar._process_express_scan
  * (lidar.py:179-187) and the conversion inside scanning() (functions.py:59-60) for a batch of

@@ -45,6 +45,8 @@ SIGNATURES = {
     "lslam_ukf_predict": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i32, ctypes.POINTER(_f64), _i32, _vp, _vp, _vp]),
     "lslam_ukf_update": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32,
                                         ctypes.POINTER(_f64), _vp, _vp, _vp]),
+    "lslam_ransac_ols": (ctypes.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _f64, _f64, _u64, _u64,
+                                        _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "lslam_express_to_cart": (ctypes.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _vp, _vp, _vp]),
     "lslam_synth_express": (ctypes.c_int, [_vp, _vp, _i64, _i32, _u64, _u64, _f64, _f64, _vp]),
     "lslam_synth_scans": (ctypes.c_int, [_vp, _vp, _i32, _i32, _u64, _u64, _f64, _f64, _vp]),
@@ -113,6 +115,13 @@ class Handle:
     # -- entry points --
     def polar_to_cart(self, dist, ang_deg, xy, npts, stream=0):
         self._check(self.cdll.lslam_polar_to_cart(self._h, dist, ang_deg, xy, npts, stream))
+
+    def ransac_ols(self, xy, npts, B, N, window, trials, thr, stop_probability, seed, scan_base, pairs,
+                   fit, ninl, ntrials, best_trial, inl_mask, stream=0):
+        self._check(self.cdll.lslam_ransac_ols(
+            self._h, xy, npts, B, N, window, trials, float(thr), float(stop_probability),
+            int(seed) & (2**64 - 1), int(scan_base) & (2**64 - 1), pairs, fit, ninl, ntrials, best_trial,
+            inl_mask, stream))
 
     def express_to_cart(self, packets, nscans, packets_per_scan, beams, xy, meas=None, status=None, stream=0):
         self._check(self.cdll.lslam_express_to_cart(self._h, packets, nscans, packets_per_scan, beams, xy, meas,

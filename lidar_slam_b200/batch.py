@@ -125,6 +125,38 @@ class Engine:
             out["inl_mask"].data_ptr(), self._stream())
         return out
 
+    def ransac_ols(self, xy, npts=None, window=50, trials=100, thr=3.0, stop_probability=0.99, seed=0,
+                   scan_base=0, pairs=None):
+        """Batched OLS-flavour RANSAC (line_detection.py:51-73: RANSACRegressor(residual_threshold=3) per
+        50-point window).  xy [B, N, 2] float64 on this device; pairs None (Philox sampler) or
+        [B, C, trials, 2] int32 explicit sample pairs.  Returns the dict of lslam_ransac_ols outputs."""
+        xy = self._check(xy, torch.float64, "xy")
+        if xy.dim() != 3 or xy.shape[2] != 2:
+            raise ValueError("xy must be [B, N, 2]")
+        B, N = int(xy.shape[0]), int(xy.shape[1])
+        C = (N + window - 1) // window
+        W = (window + 31) // 32
+        if npts is not None:
+            npts = self._check(npts, torch.int32, "npts")
+            if npts.numel() != B:
+                raise ValueError("npts must have B elements")
+        if pairs is not None:
+            pairs = self._check(pairs, torch.int32, "pairs")
+            if tuple(pairs.shape) != (B, C, trials, 2):
+                raise ValueError("pairs must be [B, C, trials, 2]")
+        dev = self.device
+        out = {"fit": torch.empty((B, C, 8), dtype=torch.float64, device=dev),
+               "ninl": torch.empty((B, C), dtype=torch.int32, device=dev),
+               "n_trials": torch.empty((B, C), dtype=torch.int32, device=dev),
+               "best_trial": torch.empty((B, C), dtype=torch.int32, device=dev),
+               "inl_mask": torch.empty((B, C, W), dtype=torch.int32, device=dev)}
+        self.handle.ransac_ols(xy.data_ptr(), npts.data_ptr() if npts is not None else None, B, N, int(window),
+                               int(trials), thr, stop_probability, seed, scan_base,
+                               pairs.data_ptr() if pairs is not None else None, out["fit"].data_ptr(),
+                               out["ninl"].data_ptr(), out["n_trials"].data_ptr(), out["best_trial"].data_ptr(),
+                               out["inl_mask"].data_ptr(), self._stream())
+        return out
+
     def ransac_counters(self):
         return self.handle.ransac_counters(self._stream())
 

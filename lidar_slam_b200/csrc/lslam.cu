@@ -9,6 +9,8 @@
 #include "assoc.cuh"
 #include "ukf.cuh"
 #include "express.cuh"
+#include "ransac_ols.cuh"
+#include <cfloat>
 
 #include "../../include/lslam.h"
 
@@ -391,6 +393,46 @@ extern "C" int lslam_synth_scans(void *handle, double *xy, int32_t B, int32_t be
     auto kern = synth_scans_kernel;
     LSLAM_LAUNCH(kern, (unsigned)grid, threads, 0, (cudaStream_t)stream, reinterpret_cast<double2 *>(xy),
                  total, (int)beams, seed, scan_base, noise_mm, dropout);
+    h->launches++;
+    LSLAM_CUDA_TRY(h, cudaGetLastError());
+    return LSLAM_OK;
+}
+
+// ---- R7 / N4: OLS-flavour RANSAC (line_detection.py:57-58) -------------------------------------
+extern "C" int lslam_ransac_ols(void *handle, const double *xy, const int32_t *npts, int32_t B, int32_t N,
+                                int32_t window, int32_t trials, double thr, double stop_probability, uint64_t seed,
+                                uint64_t scan_base, const int32_t *pairs, double *fit, int32_t *ninl,
+                                int32_t *ntrials, int32_t *best_trial, uint32_t *inl_mask, void *stream)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr) return LSLAM_ERR_BAD_ARG;
+    if (B < 0 || N < 1 || window < 2 || trials < 0 || !(thr >= 0.0) || !(stop_probability >= 0.0 && stop_probability <= 1.0))
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ransac_ols: bad sizes or parameters");
+    if (B > 0 && (!xy || !fit || !ninl || !ntrials || !best_trial || !inl_mask))
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ransac_ols: null buffer");
+    if (((uintptr_t)xy & 15) != 0) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ransac_ols: xy must be 16-byte aligned");
+    if (window > 1024) return fail(h, LSLAM_ERR_CAPACITY, "lslam_ransac_ols: window > 1024 points");
+    if (B == 0) return LSLAM_OK;
+    DeviceGuard g(h->device);
+    OlsArgs a;
+    a.xy = reinterpret_cast<const double2 *>(xy); a.npts = npts; a.pairs = pairs;
+    a.B = B; a.N = N; a.window = window; a.C = (N + window - 1) / window; a.W = (window + 31) / 32; a.trials = trials;
+    a.thr = thr;
+    a.nom = std::fmax(DBL_EPSILON, 1.0 - stop_probability);
+    a.seed = seed; a.scan_base = scan_base;
+    a.fit = fit; a.ninl = ninl; a.ntrials = ntrials; a.best_trial = best_trial; a.inl_mask = inl_mask;
+    const long long total = (long long)B * a.C;
+    int nwarps = 8;
+    size_t smem = (size_t)nwarps * 2 * window * sizeof(double);
+    while (nwarps > 1 && smem > (size_t)h->smem_optin) { nwarps >>= 1; smem = (size_t)nwarps * 2 * window * sizeof(double); }
+    auto kern = ransac_ols_kernel;
+#ifndef LSLAM_EMU
+    if (smem > 48 * 1024) LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+#endif
+    long long blocks = (total + nwarps - 1) / nwarps;
+    const long long cap = (long long)h->sms * 32;
+    if (blocks > cap) blocks = cap;
+    LSLAM_LAUNCH(kern, (unsigned)blocks, nwarps * 32, smem, (cudaStream_t)stream, a);
     h->launches++;
     LSLAM_CUDA_TRY(h, cudaGetLastError());
     return LSLAM_OK;

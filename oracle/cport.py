@@ -149,6 +149,32 @@ def empty_tables(T, M):
             "count": np.zeros(T, np.int32), "next_id": np.zeros(T, np.int32)}
 
 
+def ransac_ols(xy, npts=None, window=50, trials=100, thr=3.0, probability=0.99, seed=0, scan_base=0, pairs=None,
+               nthreads=0):
+    """Batched C oracle of the OLS flavour; argument meaning and outputs of lslam_ransac_ols."""
+    xy = np.ascontiguousarray(xy, dtype=np.float64)
+    B, N, _ = xy.shape
+    C = (N + window - 1) // window
+    W = (window + 31) // 32
+    if npts is not None:
+        npts = np.ascontiguousarray(npts, dtype=np.int32)
+    if pairs is not None:
+        pairs = np.ascontiguousarray(pairs, dtype=np.int32)
+        assert pairs.shape == (B, C, trials, 2)
+    out = {"fit": np.empty((B, C, 8), np.float64), "ninl": np.empty((B, C), np.int32),
+           "n_trials": np.empty((B, C), np.int32), "best_trial": np.empty((B, C), np.int32),
+           "inl_mask": np.empty((B, C, W), np.uint32)}
+    rc = lib().oracle_ransac_ols(
+        _p(xy, c_double_p), _p(npts, c_int32_p), ctypes.c_int32(B), ctypes.c_int32(N), ctypes.c_int32(window),
+        ctypes.c_int32(trials), ctypes.c_double(thr), ctypes.c_double(probability), ctypes.c_uint64(seed),
+        ctypes.c_uint64(scan_base), _p(pairs, c_int32_p), _p(out["fit"], c_double_p), _p(out["ninl"], c_int32_p),
+        _p(out["n_trials"], c_int32_p), _p(out["best_trial"], c_int32_p), _p(out["inl_mask"], c_uint32_p),
+        ctypes.c_int32(nthreads))
+    if rc != 0:
+        raise ValueError("oracle_ransac_ols: bad arguments")
+    return out
+
+
 def express_to_cart(packets, beams, want_meas=False, nthreads=0):
     """oracle_express_to_cart: packets [B, P, 84] uint8 -> (xy [B, beams, 2], meas or None, status [B])."""
     packets = np.ascontiguousarray(packets, dtype=np.uint8)

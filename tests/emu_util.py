@@ -126,3 +126,23 @@ def emu_synth_express(B, P=12, seed=0, scan_base=0, noise_mm=5.0, dropout=0.01, 
     packets = np.zeros((B, P, 84), np.uint8)
     h.synth_express(ptr(packets), B, P, seed, scan_base, noise_mm, dropout)
     return packets
+
+
+def emu_ransac_ols(xy, npts=None, window=50, trials=100, thr=3.0, probability=0.99, seed=0, scan_base=0, pairs=None,
+                   handle=None):
+    """lslam_ransac_ols on the emulated library; same outputs as oracle.cport.ransac_ols."""
+    h = handle or emu_handle()
+    xy = np.ascontiguousarray(xy, dtype=np.float64)
+    B, N, _ = xy.shape
+    C = (N + window - 1) // window
+    W = (window + 31) // 32
+    if npts is not None:
+        npts = np.ascontiguousarray(npts, dtype=np.int32)
+    if pairs is not None:
+        pairs = np.ascontiguousarray(pairs, dtype=np.int32)
+    out = {"fit": np.full((B, C, 8), -7.0), "ninl": np.full((B, C), -77, np.int32),
+           "n_trials": np.full((B, C), -77, np.int32), "best_trial": np.full((B, C), -77, np.int32),
+           "inl_mask": np.full((B, C, W), 0xdeadbeef, np.uint32)}
+    h.ransac_ols(ptr(xy), ptr(npts), B, N, window, trials, thr, probability, seed, scan_base, ptr(pairs),
+                 ptr(out["fit"]), ptr(out["ninl"]), ptr(out["n_trials"]), ptr(out["best_trial"]), ptr(out["inl_mask"]))
+    return out
