@@ -222,15 +222,14 @@ def main():
     fp64_peak = eng.fp64_peak(40.0) if rank == 0 else 0.0                   # TFLOP/s, dependent DFMA chains
     for _ in range(max(args.warmup, 3)):
         one_step()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-
     sampler = ClockSampler(local)
     if rank == 0:
-        sampler.start()
+        sampler.start()                                                     # nvidia-smi needs a moment to start
         time.sleep(0.3)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()                                                      # all ranks enter the timed region together
+    torch.cuda.synchronize()
     n0 = eng.launch_count()
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
