@@ -53,6 +53,8 @@ def parse():
     p.add_argument("--cpu-sample", type=int, default=0, help="scans in the CPU sample (0 = auto)")
     p.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--gather", default="peer", choices=["peer", "nccl"],
+                   help="N > 1 result gather: fused into the UKF kernel over peer memory, or an NCCL all_gather")
     return p.parse_args()
 
 
@@ -208,11 +210,27 @@ def main():
     pipe.ukf["u"].fill_(1.0)
     from lidar_slam_b200 import dist as ldist
     gatherer = ldist.ResultGather()
+    gather_mode = "none (1 rank)"
+    if world > 1:
+        gather_mode = "nccl all_gather"
+        if args.gather == "peer":
+            # the product path: every filter's (x, P, match_id) is stored into all ranks' symmetric-memory
+            # buffers by the UKF kernel itself; the step ends with a cross-rank barrier on the stream
+            try:
+                pg = pipe.enable_peer_gather()
+                gather_mode = "fused in the UKF kernel over %s" % (
+                    "NVSwitch multicast (multimem stores)" if pg.multicast else "NVLink peer stores")
+            except Exception as e:                                          # transport set-up, not compute
+                gather_mode = "nccl all_gather (peer-memory rendezvous failed: %s)" % (str(e).splitlines()[0][:120])
+                pipe.peer_gather = None
 
     def gather(res):
-        """N > 1: all ranks' per-scan UKF/landmark results over NCCL (NVLink), inside the timed region."""
+        """N > 1: all ranks' per-scan UKF/landmark results, inside the timed region."""
         if world > 1:
-            gatherer(res)
+            if pipe.peer_gather is not None:
+                pipe.peer_gather.barrier()
+            else:
+                gatherer(res)
 
     def one_step():
         res = pipe.step(xy)
@@ -333,7 +351,7 @@ def main():
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": workload_config(args, world),
-            "stages": ["ransac", "associate", "ukf"], "hit_rate": hit_rate,
+            "stages": ["ransac", "associate", "ukf"], "hit_rate": hit_rate, "gather": gather_mode,
             "ransac_hyps_per_s": world * S * 4 * TRIALS * args.steps / (ms * 1e-3),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_xy": e2e_xy, "gpu_launches": launches,
             "clocks": clocks, "parity_faults": faults,

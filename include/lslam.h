@@ -42,7 +42,7 @@ int lslam_create(int device, void **handle);
 int lslam_destroy(void *handle);
 const char *lslam_last_error(void *handle);
 /* ABI version of the loaded library (LSLAM_ABI_VERSION at build time). */
-#define LSLAM_ABI_VERSION 3
+#define LSLAM_ABI_VERSION 4
 int lslam_abi_version(void);
 /* Launch-shape tuning knobs; 0 restores the built-in heuristic.  Results never depend on them.
  *   "ransac.kernel"  0 default, 1 phase-structured kernel, 2 warp-specialised persistent kernel
@@ -172,6 +172,25 @@ int lslam_ukf_step(void *handle, double *x, double *P, const double *u, const do
                    int32_t zmode, const double *lm_pos, const int32_t *lm_valid, int32_t valid_min,
                    int32_t F, int32_t L, const double *params_h, int32_t flags, int32_t *status,
                    double *sigmas_f, void *stream);
+/* Fused UKF step + all-gather of its results over peer memory (NVLink / NVSwitch): same arguments and
+ * arithmetic as lslam_ukf_step, and in the same kernel every filter's (x[3], P[9]) - and, when `ids` is
+ * given, its id_slots per-slot landmark ids (lslam_associate's match_id) - is stored into record
+ * first_record + f of EVERY rank's gather buffers: state [records,12] double, ids [records,id_slots]
+ * int32 (rank r publishing F_r filters per step uses first_record = sum of F over the ranks before it,
+ * plus the offset of this call's first filter when a step is issued in slices).
+ * Replaces the result gather north_star names (one NCCL all-gather per step) by stores issued while the
+ * remaining filters still compute.  Buffers: either the multicast address of the ranks' buffers
+ * (mc_state / mc_ids, e.g. torch symmetric memory's multicast_ptr: one store per element, NVSwitch
+ * replicates it) or host arrays peer_state_h / peer_ids_h of `world` device addresses: every rank's
+ * buffer as mapped on THIS GPU, the local one included.  The caller synchronises the ranks after the
+ * kernel (a barrier on the stream) before anyone reads the gathered records.  world <= 8. */
+int lslam_ukf_step_gather(void *handle, double *x, double *P, const double *u, const double *z,
+                          int32_t zstride, int32_t zmode, const double *lm_pos, const int32_t *lm_valid,
+                          int32_t valid_min, int32_t F, int32_t L, const double *params_h, int32_t flags,
+                          int32_t *status, const int32_t *ids, int32_t id_slots, int32_t world,
+                          int64_t first_record, void *const *peer_state_h, void *mc_state,
+                          void *const *peer_ids_h, void *mc_ids, void *stream);
+
 /* filterpy-shaped halves of the same kernel: predict(u=u) and update(z, landmarks=...). */
 int lslam_ukf_predict(void *handle, double *x, double *P, const double *u, int32_t F,
                       const double *params_h, int32_t redraw, int32_t *status, double *sigmas_f,

@@ -18,7 +18,7 @@ LSLAM_ERR_NO_MODEL = -3
 LSLAM_ERR_CUDA = -4
 LSLAM_ERR_NONFINITE = -5
 LSLAM_ERR_CAPACITY = -6
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 _vp = ctypes.c_void_p
 _i32 = ctypes.c_int32
@@ -42,6 +42,9 @@ SIGNATURES = {
                                        _f64, _f64, _f64, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp]),
     "lslam_ukf_step": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32,
                                       ctypes.POINTER(_f64), _i32, _vp, _vp, _vp]),
+    "lslam_ukf_step_gather": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32,
+                                             ctypes.POINTER(_f64), _i32, _vp, _vp, _i32, _i32, _i64,
+                                             ctypes.POINTER(_vp), _vp, ctypes.POINTER(_vp), _vp, _vp]),
     "lslam_ukf_predict": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i32, ctypes.POINTER(_f64), _i32, _vp, _vp, _vp]),
     "lslam_ukf_update": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32,
                                         ctypes.POINTER(_f64), _vp, _vp, _vp]),
@@ -161,6 +164,18 @@ class Handle:
                  status=None, sigmas_f=None, stream=0):
         self._check(self.cdll.lslam_ukf_step(self._h, x, P, u, z, zstride, zmode, lm_pos, lm_valid, valid_min,
                                              F, L, self._params(params), flags, status, sigmas_f, stream))
+
+    def ukf_step_gather(self, x, P, u, z, zstride, zmode, lm_pos, lm_valid, valid_min, F, L, params, flags,
+                        status, ids, id_slots, world, first_record, peer_state=None, mc_state=None, peer_ids=None,
+                        mc_ids=None, stream=0):
+        """peer_state / peer_ids: sequences of `world` device addresses (or None with a multicast address)."""
+        def arr(ptrs):
+            if ptrs is None:
+                return None
+            return (_vp * world)(*[int(p) for p in ptrs])
+        self._check(self.cdll.lslam_ukf_step_gather(
+            self._h, x, P, u, z, zstride, zmode, lm_pos, lm_valid, valid_min, F, L, self._params(params), flags,
+            status, ids, id_slots, world, first_record, arr(peer_state), mc_state, arr(peer_ids), mc_ids, stream))
 
     def ukf_predict(self, x, P, u, F, params, redraw=True, status=None, sigmas_f=None, stream=0):
         self._check(self.cdll.lslam_ukf_predict(self._h, x, P, u, F, self._params(params), int(bool(redraw)),

@@ -248,7 +248,7 @@ class Engine:
         }
 
     def ukf_step(self, ukf, z, lm_pos, lm_valid=None, valid_min=1, u=None, zmode=None, flags=None,
-                 sigmas_f=None):
+                 sigmas_f=None, gather=None):
         """predict(u) + update(z, landmarks) of every filter in ``ukf`` (dict of alloc_ukf), in place.
 
         z [F, L, 2] (range, bearing) or [F, L, 8] line records of ransac_lines (zmode 1: the
@@ -282,12 +282,23 @@ class Engine:
                 if lm_valid.shape != (F, L):
                     raise ValueError("lm_valid must be [F, L]")
         st = ukf.get("status")
-        self.handle.ukf_step(
-            x.data_ptr(), P.data_ptr(), u.data_ptr() if u is not None else None,
-            z.data_ptr() if z is not None else None, zs, zmode or 0,
-            lm_pos.data_ptr() if z is not None else None, lm_valid.data_ptr() if lm_valid is not None else None,
-            valid_min, F, L, ukf["params"], flags, st.data_ptr() if st is not None else None,
-            sigmas_f.data_ptr() if sigmas_f is not None else None, self._stream())
+        common = (x.data_ptr(), P.data_ptr(), u.data_ptr() if u is not None else None,
+                  z.data_ptr() if z is not None else None, zs, zmode or 0,
+                  lm_pos.data_ptr() if z is not None else None, lm_valid.data_ptr() if lm_valid is not None else None,
+                  valid_min, F, L, ukf["params"], flags, st.data_ptr() if st is not None else None)
+        if gather is None:
+            self.handle.ukf_step(*common, sigmas_f.data_ptr() if sigmas_f is not None else None, self._stream())
+        else:
+            # fused all-gather over peer memory: gather = dict(world, first_record, ids, id_slots, and either
+            # mc_state/mc_ids (multicast addresses) or peer_state/peer_ids (lists of device addresses));
+            # built by lidar_slam_b200/dist.PeerGather.descriptor
+            ids = gather.get("ids")
+            if ids is not None:
+                ids = self._check(ids, torch.int32, "gather ids")
+            self.handle.ukf_step_gather(*common, ids.data_ptr() if ids is not None else None,
+                                        int(gather.get("id_slots", 0)), int(gather["world"]), int(gather["first_record"]),
+                                        gather.get("peer_state"), gather.get("mc_state"), gather.get("peer_ids"),
+                                        gather.get("mc_ids"), self._stream())
         return ukf
 
     def synth_scans(self, B, beams=360, seed=0, scan_base=0, noise_mm=5.0, dropout=0.02, out=None):

@@ -295,10 +295,18 @@ static int launch_ukf(Handle *h, const UkfArgs &a, cudaStream_t st)
     return LSLAM_OK;
 }
 
-extern "C" int lslam_ukf_step(void *handle, double *x, double *P, const double *u, const double *z,
-                              int32_t zstride, int32_t zmode, const double *lm_pos, const int32_t *lm_valid,
-                              int32_t valid_min, int32_t F, int32_t L, const double *params_h, int32_t flags,
-                              int32_t *status, double *sigmas_f, void *stream)
+struct UkfGather {
+    int world = 0, id_slots = 0;
+    long long first_record = 0;
+    const int32_t *ids = nullptr;
+    void *const *peer_state_h = nullptr; void *mc_state = nullptr;
+    void *const *peer_ids_h = nullptr; void *mc_ids = nullptr;
+};
+
+static int ukf_step_impl(void *handle, double *x, double *P, const double *u, const double *z,
+                         int32_t zstride, int32_t zmode, const double *lm_pos, const int32_t *lm_valid,
+                         int32_t valid_min, int32_t F, int32_t L, const double *params_h, int32_t flags,
+                         int32_t *status, double *sigmas_f, const UkfGather &gd, void *stream)
 {
     Handle *h = (Handle *)handle;
     if (h == nullptr) return LSLAM_ERR_BAD_ARG;
@@ -315,6 +323,14 @@ extern "C" int lslam_ukf_step(void *handle, double *x, double *P, const double *
     a.sigmas_f = sigmas_f;
     a.F = F; a.L = upd ? L : 0; a.zstride = zstride; a.zmode = zmode; a.valid_min = valid_min;
     a.flags = upd ? flags : (flags & ~LSLAM_UKF_UPDATE);
+    a.gather_world = gd.world; a.gather_first = gd.first_record; a.gather_L = gd.id_slots; a.gather_ids = gd.ids;
+    a.gather_state_mc = (double *)gd.mc_state; a.gather_ids_mc = (int32_t *)gd.mc_ids;
+    for (int p = 0; p < kUkfMaxPeers; ++p) {
+        a.gather_state[p] = (p < gd.world && gd.peer_state_h) ? (double *)gd.peer_state_h[p] : nullptr;
+        a.gather_idbuf[p] = (p < gd.world && gd.peer_ids_h) ? (int32_t *)gd.peer_ids_h[p] : nullptr;
+    }
+    if (gd.world > 0 && !(a.flags & 3))
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_step_gather: nothing to run (update without slots)");
     if (!(a.flags & 3)) {                          // update-only call without slots: nothing to do
         if (status) LSLAM_CUDA_TRY(h, cudaMemsetAsync(status, 0, sizeof(int32_t) * (size_t)F, (cudaStream_t)stream));
         return LSLAM_OK;
@@ -336,6 +352,41 @@ extern "C" int lslam_ukf_step(void *handle, double *x, double *P, const double *
     if (Lk <= 8) return launch_ukf<8>(h, a, st);
     if (Lk <= 16) return launch_ukf<16>(h, a, st);
     return launch_ukf<32>(h, a, st);
+}
+
+extern "C" int lslam_ukf_step(void *handle, double *x, double *P, const double *u, const double *z,
+                              int32_t zstride, int32_t zmode, const double *lm_pos, const int32_t *lm_valid,
+                              int32_t valid_min, int32_t F, int32_t L, const double *params_h, int32_t flags,
+                              int32_t *status, double *sigmas_f, void *stream)
+{
+    return ukf_step_impl(handle, x, P, u, z, zstride, zmode, lm_pos, lm_valid, valid_min, F, L, params_h, flags,
+                         status, sigmas_f, UkfGather(), stream);
+}
+
+extern "C" int lslam_ukf_step_gather(void *handle, double *x, double *P, const double *u, const double *z,
+                                     int32_t zstride, int32_t zmode, const double *lm_pos, const int32_t *lm_valid,
+                                     int32_t valid_min, int32_t F, int32_t L, const double *params_h, int32_t flags,
+                                     int32_t *status, const int32_t *ids, int32_t id_slots, int32_t world,
+                                     int64_t first_record, void *const *peer_state_h, void *mc_state,
+                                     void *const *peer_ids_h, void *mc_ids, void *stream)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr) return LSLAM_ERR_BAD_ARG;
+    if (world < 1 || world > kUkfMaxPeers || first_record < 0 || id_slots < 0)
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_step_gather: need 1 <= world <= 8, first_record >= 0");
+    if (!mc_state && !peer_state_h) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_step_gather: no gather buffers");
+    if (ids && id_slots > 0 && !mc_ids && !peer_ids_h)
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_step_gather: ids given without id gather buffers");
+    for (int p = 0; p < world; ++p) {
+        if (!mc_state && !peer_state_h[p]) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_step_gather: null peer buffer");
+        if (ids && id_slots > 0 && !mc_ids && !peer_ids_h[p])
+            return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_step_gather: null peer id buffer");
+    }
+    UkfGather gd;
+    gd.world = world; gd.first_record = first_record; gd.id_slots = (ids && id_slots > 0) ? id_slots : 0; gd.ids = gd.id_slots ? ids : nullptr;
+    gd.peer_state_h = peer_state_h; gd.mc_state = mc_state; gd.peer_ids_h = peer_ids_h; gd.mc_ids = mc_ids;
+    return ukf_step_impl(handle, x, P, u, z, zstride, zmode, lm_pos, lm_valid, valid_min, F, L, params_h, flags,
+                         status, nullptr, gd, stream);
 }
 
 extern "C" int lslam_ukf_predict(void *handle, double *x, double *P, const double *u, int32_t F,

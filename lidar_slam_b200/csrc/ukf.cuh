@@ -28,6 +28,8 @@ namespace lslam {
 enum { kUkfPredict = 1, kUkfUpdate = 2, kUkfRedraw = 4 };
 enum { kUkfStSigma = 1, kUkfStRedraw = 2, kUkfStS = 4 };
 
+constexpr int kUkfMaxPeers = 8;
+
 struct UkfArgs {
     double *x, *P;                 // [F,3], [F,3,3] in/out
     const double *u;               // [F,2] or null (zero controls)
@@ -41,7 +43,33 @@ struct UkfArgs {
     double wm0, wc0, wi;                     // weights
     double var_dist, var_angle;
     double Q[9];
+    // fused all-gather of the step's results over peer memory (lslam_ukf_step_gather); world == 0: off
+    int gather_world, gather_L;
+    long long gather_first;        // record index of this call's filter 0 in the gather buffers
+    const int32_t *gather_ids;     // [F, gather_L] local per-slot ids to publish, or null
+    double *gather_state_mc;       // multicast address of the [world, F, 12] state buffers, or null
+    int32_t *gather_ids_mc;        // multicast address of the [world, F, gather_L] id buffers, or null
+    double *gather_state[kUkfMaxPeers];     // every rank's state buffer as mapped on this GPU (unicast path)
+    int32_t *gather_idbuf[kUkfMaxPeers];
 };
+
+// One store that NVSwitch replicates into the same offset of every rank's buffer (multicast object).
+__device__ __forceinline__ void multimem_store(double *mc_addr, double v)
+{
+#ifndef LSLAM_EMU
+    asm volatile("multimem.st.relaxed.sys.global.f64 [%0], %1;" ::"l"(mc_addr), "d"(v) : "memory");
+#else
+    *mc_addr = v;
+#endif
+}
+__device__ __forceinline__ void multimem_store(int32_t *mc_addr, int32_t v)
+{
+#ifndef LSLAM_EMU
+    asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(mc_addr), "r"(v) : "memory");
+#else
+    *mc_addr = v;
+#endif
+}
 
 __host__ __device__ inline size_t ukf_smem_doubles_per_warp(int G) { return (size_t)(18 * 2 * G + 4 * G * G) * (32 / G); }
 
@@ -358,6 +386,32 @@ __global__ void __launch_bounds__(128) ukf_kernel(const UkfArgs a)
             for (int i = 0; i < 9; ++i) a.P[f * 9 + i] = P[i];
         }
         if (a.status != nullptr) a.status[f] = st;
+    }
+    // ================= fused all-gather over peer memory =========================================
+    // The group publishes what this call left in (x, P) - and the slots' landmark ids - into record
+    // gather_first + f of EVERY rank's gather buffer: one multimem store per element when the buffers have a
+    // multicast mapping (NVSwitch replicates it), else one peer store per rank over NVLink.  The stores
+    // are fire-and-forget and overlap the remaining filters' arithmetic; the caller orders them
+    // against the readers with a cross-rank barrier after the kernel (lidar_slam_b200/dist.py).
+    if (a.gather_world > 0) {
+        __syncwarp();
+        if (live) {
+            const size_t rec = (size_t)a.gather_first + (size_t)f;
+            for (int e = g; e < 12; e += G) {
+                const double v = e < 3 ? a.x[f * 3 + e] : a.P[f * 9 + (e - 3)];
+                if (a.gather_state_mc != nullptr) multimem_store(a.gather_state_mc + rec * 12 + e, v);
+                else
+                    for (int p = 0; p < a.gather_world; ++p) a.gather_state[p][rec * 12 + e] = v;
+            }
+            if (a.gather_ids != nullptr) {
+                for (int e = g; e < a.gather_L; e += G) {
+                    const int32_t v = a.gather_ids[f * a.gather_L + e];
+                    if (a.gather_ids_mc != nullptr) multimem_store(a.gather_ids_mc + rec * a.gather_L + e, v);
+                    else
+                        for (int p = 0; p < a.gather_world; ++p) a.gather_idbuf[p][rec * a.gather_L + e] = v;
+                }
+            }
+        }
     }
 #undef UKF_SM
 }

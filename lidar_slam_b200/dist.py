@@ -1,5 +1,13 @@
 """Multi-GPU plumbing: the path shards by scan / stream index with no data-path exchange
-(SURVEY.md 8(e)); the only collective is the gather of fixed-size per-scan results."""
+(SURVEY.md 8(e)); the only collective is the gather of fixed-size per-scan results.
+
+Two implementations of that gather:
+  * ``PeerGather`` - the product path on GPUs: the ranks' gather buffers live in symmetric memory
+    (peer-mapped over NVLink, with an NVSwitch multicast mapping when the fabric offers one) and the UKF
+    kernel itself stores every filter's result into all of them (lslam_ukf_step_gather): no separate
+    collective, only a cross-rank barrier on the stream before the records are read;
+  * ``ResultGather`` - a plain all_gather (NCCL on GPUs; gloo in the CPU tests of the host logic),
+    kept as the baseline the fused path is measured against (bench.py --gather nccl)."""
 import torch
 import torch.distributed as dist
 
@@ -33,3 +41,42 @@ class ResultGather:
             else:                                   # gloo (CPU tests): list form into views of the same buffer
                 dist.all_gather(list(self.buf[k].unbind(0)), res[k].contiguous())
         return self.buf
+
+
+class PeerGather:
+    """Gather buffers in symmetric memory + the descriptor lslam_ukf_step_gather needs.
+
+    state [world, F, 12] float64 (x[3], P[9] of every filter of every rank) and ids
+    [world, F, id_slots] int32, identical on every rank once ``barrier()`` has passed on the stream
+    that ran the step.  ``multicast=None`` uses the multicast mapping when there is one."""
+
+    def __init__(self, filters_per_rank, id_slots, device, group=None, multicast=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        group = group or dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.F, self.id_slots = int(filters_per_rank), int(id_slots)
+        self.state = symm_mem.empty((self.world, self.F, 12), dtype=torch.float64, device=device)
+        self.ids = symm_mem.empty((self.world, self.F, max(self.id_slots, 1)), dtype=torch.int32, device=device)
+        self.h_state = symm_mem.rendezvous(self.state, group)
+        self.h_ids = symm_mem.rendezvous(self.ids, group)
+        has_mc = bool(self.h_state.has_multicast_support and self.h_state.multicast_ptr and self.h_ids.multicast_ptr)
+        if multicast and not has_mc:
+            raise RuntimeError("symmetric memory has no multicast mapping on this system")
+        self.multicast = has_mc if multicast is None else bool(multicast)
+
+    def descriptor(self, ids, s0=0):
+        """For a call that runs the local filters [s0, s0 + n): ``ids`` = its [n, id_slots] int32 tensor."""
+        d = {"world": self.world, "first_record": self.rank * self.F + s0, "ids": ids if self.id_slots else None,
+             "id_slots": self.id_slots}
+        if self.multicast:
+            d["mc_state"], d["mc_ids"] = int(self.h_state.multicast_ptr), int(self.h_ids.multicast_ptr)
+        else:
+            d["peer_state"], d["peer_ids"] = list(self.h_state.buffer_ptrs), list(self.h_ids.buffer_ptrs)
+        return d
+
+    def barrier(self):
+        """Cross-rank barrier on the current stream: every rank's stores of the step have landed."""
+        self.h_state.barrier(channel=0)
+
+    def result(self):
+        return {"state": self.state, "ids": self.ids}

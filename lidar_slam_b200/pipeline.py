@@ -33,6 +33,15 @@ class ScanPipeline:
         self._host_out = None
         self._view_cache = {}
         self._ov = None
+        self.peer_gather = None
+
+    def enable_peer_gather(self, group=None, multicast=None):
+        """N > 1: publish every step's (x, P, match_id) into all ranks' gather buffers from inside the UKF
+        kernel (lidar_slam_b200/dist.PeerGather).  Call ``self.peer_gather.barrier()`` after the step
+        before reading ``self.peer_gather.result()``."""
+        from . import dist as ldist
+        self.peer_gather = ldist.PeerGather(self.S, self.C, self.eng.device, group=group, multicast=multicast)
+        return self.peer_gather
 
     # ---- device-resident step: inputs already in HBM ------------------------------------
     @staticmethod
@@ -67,7 +76,8 @@ class ScanPipeline:
         a = eng.associate(r["line"], v["tables"], q_valid=r["ninl"], out=v["aout"])
         # measurement slot c = chunk c's line: range/bearing of its inlier centroid against the matched
         # stored landmark's position; slots whose line missed (match < 0) are not used
-        eng.ukf_step(v["ukf"], r["line"], a["hit_pos"], lm_valid=a["match"], valid_min=0, u=u)
+        gd = self.peer_gather.descriptor(a["match_id"], s0) if self.peer_gather is not None else None
+        eng.ukf_step(v["ukf"], r["line"], a["hit_pos"], lm_valid=a["match"], valid_min=0, u=u, gather=gd)
         return {"line": r["line"], "ninl": r["ninl"], "match": a["match"], "match_id": a["match_id"],
                 "x": v["ukf"]["x"], "P": v["ukf"]["P"]}
 

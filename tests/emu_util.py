@@ -109,6 +109,32 @@ def emu_ukf_step(x, P, u, z, lm_pos, lm_valid=None, valid_min=1, zmode=0, params
     return x, P, status
 
 
+def emu_ukf_step_gather(x, P, u, z, lm_pos, lm_valid, ids, first_record, peer_state, peer_ids, multicast=False,
+                        valid_min=0, zmode=1, params=None, flags=7, handle=None):
+    """lslam_ukf_step_gather on the emulated library: peer_state / peer_ids are lists of NumPy arrays
+    standing in for the ranks' gather buffers (multicast=True: a single array reached through the
+    'multicast' address).  Returns (x_new, P_new, status)."""
+    from lidar_slam_b200 import batch
+    h = handle or emu_handle()
+    x = np.array(x, dtype=np.float64, order="C")
+    P = np.array(P, dtype=np.float64, order="C")
+    F = x.shape[0]
+    u = None if u is None else np.ascontiguousarray(u, dtype=np.float64)
+    z = np.ascontiguousarray(z, dtype=np.float64)
+    L, zs = z.shape[1], z.shape[2]
+    lm_pos = np.ascontiguousarray(lm_pos, dtype=np.float64)
+    lm_valid = np.ascontiguousarray(lm_valid, dtype=np.int32)
+    ids = None if ids is None else np.ascontiguousarray(ids, dtype=np.int32)
+    status = np.full(F, -99, np.int32)
+    params = batch.Engine.ukf_params() if params is None else list(params)
+    world = len(peer_state)
+    kw = ({"mc_state": ptr(peer_state[0]), "mc_ids": ptr(peer_ids[0]) if peer_ids else None} if multicast else
+          {"peer_state": [ptr(b) for b in peer_state], "peer_ids": [ptr(b) for b in peer_ids] if peer_ids else None})
+    h.ukf_step_gather(ptr(x), ptr(P), ptr(u), ptr(z), zs, zmode, ptr(lm_pos), ptr(lm_valid), valid_min, F, L, params,
+                      flags, ptr(status), ptr(ids), 0 if ids is None else ids.shape[1], world, first_record, **kw)
+    return x, P, status
+
+
 def emu_express_to_cart(packets, beams, want_meas=True, handle=None):
     """lslam_express_to_cart on the emulated library."""
     h = handle or emu_handle()
