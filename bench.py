@@ -194,6 +194,8 @@ def main():
     from lidar_slam_b200 import batch, pipeline
 
     torch.cuda.set_device(local)
+    from lidar_slam_b200 import dist as ldist
+    numa_cpus = ldist.bind_to_gpu_numa(local) if world > 1 else None       # host buffers on the GPU's socket
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -208,7 +210,6 @@ def main():
     r0 = eng.ransac_lines(xy, chunk=CHUNK, trials=TRIALS, thr=THR, seed=0, scan_base=rank * S, out=pipe.rout)
     pipe.install_map_from_lines(r0["line"], r0["ninl"])                     # untimed set-up: the known map
     pipe.ukf["u"].fill_(1.0)
-    from lidar_slam_b200 import dist as ldist
     gatherer = ldist.ResultGather()
     gather_mode = "none (1 rank)"
     if world > 1:

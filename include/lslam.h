@@ -83,7 +83,9 @@ int lslam_polar_to_cart(void *handle, const double *dist, const double *ang_deg,
  *                      lslam_status (LSLAM_ERR_NO_MODEL, LSLAM_ERR_NONFINITE)
  *   win_trial [B,C]    index of the selected hypothesis (first best in trial order)
  *   win_pair  [B,C,2]  its two sample indices within the chunk
- *   ssum      [B,C]    its sum of squared residuals over all points of the chunk
+ *   ssum      [B,C]    its sum of squared residuals over all points of the chunk; may be NULL
+ *                      (not needed by the reference's outputs: the kernel then decides a chunk whose
+ *                      winner is unambiguous without the literal residual pass)
  *   inl_mask  [B,C,W]  W = ceil(chunk/32) words, bit k of word w = point 32*w+k is an inlier
  */
 int lslam_ransac_lines(void *handle, const double *xy, const int32_t *npts, int32_t B, int32_t N,

@@ -87,11 +87,14 @@ class Engine:
                                   self._stream())
         return out
 
-    def alloc_ransac_out(self, B, N, chunk=CHUNK):
+    def alloc_ransac_out(self, B, N, chunk=CHUNK, ssum=True):
+        """Output buffers of ransac_lines.  ``ssum=False`` leaves out the winner's residual sum (a
+        diagnostic the reference never exposes); the kernel then skips the literal residual pass for
+        chunks with an unambiguous winner."""
         C = (N + chunk - 1) // chunk
         W = (chunk + 31) // 32
         dev = self.device
-        return {
+        out = {
             "line": torch.empty((B, C, 8), dtype=torch.float64, device=dev),
             "ninl": torch.empty((B, C), dtype=torch.int32, device=dev),
             "win_trial": torch.empty((B, C), dtype=torch.int32, device=dev),
@@ -99,6 +102,9 @@ class Engine:
             "ssum": torch.empty((B, C), dtype=torch.float64, device=dev),
             "inl_mask": torch.empty((B, C, W), dtype=torch.int32, device=dev),
         }
+        if not ssum:
+            del out["ssum"]
+        return out
 
     def ransac_lines(self, xy, npts=None, chunk=CHUNK, trials=MAX_TRIALS, thr=THRESHOLD,
                      seed=0, scan_base=0, out=None):
@@ -121,8 +127,8 @@ class Engine:
         self.handle.ransac_lines(
             xy.data_ptr(), npts.data_ptr() if npts is not None else None, B, N, int(chunk),
             int(trials), float(thr), seed, scan_base, out["line"].data_ptr(), out["ninl"].data_ptr(),
-            out["win_trial"].data_ptr(), out["win_pair"].data_ptr(), out["ssum"].data_ptr(),
-            out["inl_mask"].data_ptr(), self._stream())
+            out["win_trial"].data_ptr(), out["win_pair"].data_ptr(),
+            out["ssum"].data_ptr() if "ssum" in out else None, out["inl_mask"].data_ptr(), self._stream())
         return out
 
     def ransac_ols(self, xy, npts=None, window=50, trials=100, thr=3.0, stop_probability=0.99, seed=0,

@@ -1,4 +1,4 @@
-// assoc.cuh - K3: landmark data association, one warp per landmark table (stream).
+// assoc.cuh - K3: landmark data association, one lane group (8, 16 or 32 lanes) per landmark table (stream).
 //
 // Replaces the association loop of landmark_extraction (/root/reference/ransac_functions.py:34-54,
 // is_equal from landmarking.py:66-77) plus the caller-side append and extraction counter of
@@ -52,32 +52,43 @@ __device__ __forceinline__ bool landmark_is_equal(const double *e, const double 
     return distA <= tolA && distB <= tolB && (dEO <= tol || dOE <= tol);
 }
 
+// GS lanes (8, 16 or 32) serve one table; a warp serves 32/GS tables.  GS < 32 requires M <= GS (one
+// tile per table), so that the reference's table sizes (LANDMARK_NUMBER = 8) do not leave three
+// quarters of every warp idle.  Collectives are restricted to the group's lanes: groups of one warp
+// run different tables and diverge freely.
+template <int GS>
 __global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
 {
     LSLAM_SMEM_DECL;
+    constexpr int NG = 32 / GS;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    const int t = blockIdx.x * nwarps + warp;
-    if (t >= a.T) return;                       // whole warp leaves together
+    const int grp = lane / GS, g = lane % GS;
+    const unsigned gfull = GS == 32 ? 0xffffffffu : ((1u << GS) - 1u);
+    const unsigned gmask = gfull << (grp * GS);
+    const long long tl = ((long long)blockIdx.x * nwarps + warp) * NG + grp;
+    if (tl >= a.T) return;                      // the whole group leaves together
+    const int t = (int)tl;
     const int M = a.M;
-    unsigned char *base = smem_raw + (size_t)warp * ((assoc_smem_per_warp(M) + 15) & ~(size_t)15);
+    unsigned char *base = smem_raw + (size_t)(warp * NG + grp) * ((assoc_smem_per_warp(M) + 15) & ~(size_t)15);
     double *ent = reinterpret_cast<double *>(base);                 // [M][6]
     int *life = reinterpret_cast<int *>(ent + (size_t)M * 6);       // [M]
     int *ids = life + M;                                            // [M]
+#define GBALLOT(pred) ((__ballot_sync(gmask, (pred)) >> (grp * GS)) & gfull)
 
     int cnt = a.count[t];
     cnt = cnt < 0 ? 0 : (cnt > M ? M : cnt);
     int next_id = a.next_id[t];
     {
         const double *src = a.table + (size_t)t * M * 6;
-        for (int k = lane; k < cnt * 6; k += 32) ent[k] = src[k];
-        for (int k = lane; k < cnt; k += 32) { life[k] = a.life[(size_t)t * M + k]; ids[k] = a.ids[(size_t)t * M + k]; }
+        for (int k = g; k < cnt * 6; k += GS) ent[k] = src[k];
+        for (int k = g; k < cnt; k += GS) { life[k] = a.life[(size_t)t * M + k]; ids[k] = a.ids[(size_t)t * M + k]; }
     }
-    __syncwarp();
+    __syncwarp(gmask);
 
     for (int qi = 0; qi < a.Q; ++qi) {
         const size_t qo = (size_t)t * a.Q + qi;
         if (a.q_valid != nullptr && a.q_valid[qo] <= 0) {
-            if (lane == 0) {
+            if (g == 0) {
                 a.match[qo] = -2; a.match_id[qo] = -1;
                 const double qn = __longlong_as_double(0x7ff8000000000000LL);
                 if (a.proj_ab) { a.proj_ab[2 * qo] = qn; a.proj_ab[2 * qo + 1] = qn; }
@@ -96,16 +107,16 @@ __global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
         if (a.mode != 2) {
             // ---- first match in list order with the reference's side effects ----
             int p = 0;
-            for (int tb = 0; tb < cnt && hit < 0; tb += 32) {
-                const int m = tb + lane;
+            for (int tb = 0; tb < cnt && hit < 0; tb += GS) {
+                const int m = tb + g;
                 const bool in = m < cnt;
                 double dmin;
                 const bool eq = in && landmark_is_equal(ent + (size_t)m * 6, q, a.tolA, a.tolB, a.tol, dmin);
                 const int lf = in ? life[m] : 0;
                 const bool die = in && !eq && lf <= 1;           // decrease_life() would return True
-                const unsigned eqm = __ballot_sync(LSLAM_FULL_MASK, eq);
-                const unsigned diem = __ballot_sync(LSLAM_FULL_MASK, die);
-                const int tend = cnt - tb < 32 ? cnt - tb : 32;  // valid positions in this tile
+                const unsigned eqm = GBALLOT(eq);
+                const unsigned diem = GBALLOT(die);
+                const int tend = cnt - tb < GS ? cnt - tb : GS;  // valid positions in this tile
                 unsigned vis = 0, rem = 0;
                 while (p < tb + tend) {
                     const int pp = p - tb;
@@ -119,50 +130,50 @@ __global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
                     rem |= 1u << pe;
                     p = tb + pe + (a.mode == 0 ? 2 : 1);         // mode 0: the slot after a removal is skipped
                 }
-                if (in && ((vis >> lane) & 1u)) life[m] = ((rem >> lane) & 1u) ? kLifeRemoved : (lf > 0 ? lf - 1 : 0);
+                if (in && ((vis >> g) & 1u)) life[m] = ((rem >> g) & 1u) ? kLifeRemoved : (lf > 0 ? lf - 1 : 0);
                 removed += __popc(rem);
             }
         } else {
             // ---- nearest gated landmark; every other landmark counts as "not seen" ----
             double best = __longlong_as_double(0x7ff0000000000000LL);
-            for (int tb = 0; tb < cnt; tb += 32) {
-                const int m = tb + lane;
+            for (int tb = 0; tb < cnt; tb += GS) {
+                const int m = tb + g;
                 double dmin = best;
                 const bool eq = m < cnt && landmark_is_equal(ent + (size_t)m * 6, q, a.tolA, a.tolB, a.tol, dmin);
                 double cand = eq ? dmin : __longlong_as_double(0x7ff0000000000000LL);
                 int ci = eq ? m : 0x7fffffff;
 #pragma unroll
-                for (int o = 16; o >= 1; o >>= 1) {
-                    const double od = __shfl_xor_sync(LSLAM_FULL_MASK, cand, o);
-                    const int oi = __shfl_xor_sync(LSLAM_FULL_MASK, ci, o);
+                for (int o = GS / 2; o >= 1; o >>= 1) {
+                    const double od = __shfl_xor_sync(gmask, cand, o);
+                    const int oi = __shfl_xor_sync(gmask, ci, o);
                     if (od < cand || (od == cand && oi < ci)) { cand = od; ci = oi; }
                 }
                 if (ci != 0x7fffffff && cand < best) { best = cand; hit = ci; }
             }
-            for (int tb = 0; tb < cnt; tb += 32) {
-                const int m = tb + lane;
+            for (int tb = 0; tb < cnt; tb += GS) {
+                const int m = tb + g;
                 bool rm = false;
                 if (m < cnt && m != hit) {
                     const int lf = life[m];
                     rm = lf <= 1;
                     life[m] = rm ? kLifeRemoved : lf - 1;
                 }
-                removed += __popc(__ballot_sync(LSLAM_FULL_MASK, rm));
+                removed += __popc(GBALLOT(rm));
             }
         }
-        __syncwarp();
+        __syncwarp(gmask);
         int hit_new = -1, hit_id = -1;
         double pa = q[0], pb = q[1];
         double hx = __longlong_as_double(0x7ff8000000000000LL), hy = hx;
         if (hit >= 0) {
-            if (lane == 0) life[hit] = a.life_init;              // reset_life(); a, b, pos, end NOT updated
+            if (g == 0) life[hit] = a.life_init;                 // reset_life(); a, b, pos, end NOT updated
             // removals all precede the hit in first-match modes; count them for the nearest mode
             int before = removed;
             if (a.mode == 2) {
                 before = 0;
-                for (int tb = 0; tb < hit; tb += 32) {
-                    const int m = tb + lane;
-                    before += __popc(__ballot_sync(LSLAM_FULL_MASK, m < hit && life[m] == kLifeRemoved));
+                for (int tb = 0; tb < hit; tb += GS) {
+                    const int m = tb + g;
+                    before += __popc(GBALLOT(m < hit && life[m] == kLifeRemoved));
                 }
             }
             hit_new = hit - before;
@@ -172,12 +183,12 @@ __global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
             hx = ent[(size_t)hit * 6 + 2];
             hy = ent[(size_t)hit * 6 + 3];
         }
-        __syncwarp();
+        __syncwarp(gmask);
         // ---- stable compaction of the removed landmarks (list.remove shifts the tail left) ----
         if (removed > 0) {
             int outp = 0;
-            for (int tb = 0; tb < cnt; tb += 32) {
-                const int m = tb + lane;
+            for (int tb = 0; tb < cnt; tb += GS) {
+                const int m = tb + g;
                 const bool keep = m < cnt && life[m] != kLifeRemoved;
                 double e6[6];
                 int lf = 0, id = 0;
@@ -186,16 +197,16 @@ __global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
                     for (int k = 0; k < 6; ++k) e6[k] = ent[(size_t)m * 6 + k];
                     lf = life[m]; id = ids[m];
                 }
-                const unsigned km = __ballot_sync(LSLAM_FULL_MASK, keep);
-                __syncwarp();
+                const unsigned km = GBALLOT(keep);
+                __syncwarp(gmask);
                 if (keep) {
-                    const int d = outp + __popc(km & ((1u << lane) - 1u));
+                    const int d = outp + __popc(km & ((1u << g) - 1u));
 #pragma unroll
                     for (int k = 0; k < 6; ++k) ent[(size_t)d * 6 + k] = e6[k];
                     life[d] = lf; ids[d] = id;
                 }
                 outp += __popc(km);
-                __syncwarp();
+                __syncwarp(gmask);
             }
             cnt = outp;
         }
@@ -203,7 +214,7 @@ __global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
         if (hit < 0) {
             rid = qid;
             if (a.append && cnt < M) {
-                if (lane == 0) {
+                if (g == 0) {
 #pragma unroll
                     for (int k = 0; k < 6; ++k) ent[(size_t)cnt * 6 + k] = q[k];
                     life[cnt] = a.life_init;
@@ -215,8 +226,8 @@ __global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
                 result = a.append ? -3 : -1;
             }
         }
-        __syncwarp();
-        if (lane == 0) {
+        __syncwarp(gmask);
+        if (g == 0) {
             a.match[qo] = result;
             a.match_id[qo] = rid;
             if (a.proj_ab) { a.proj_ab[2 * qo] = pa; a.proj_ab[2 * qo + 1] = pb; }
@@ -226,13 +237,14 @@ __global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
     // ---- write the table back; slots past the live count are zeroed ----
     {
         double *dst = a.table + (size_t)t * M * 6;
-        for (int k = lane; k < M * 6; k += 32) dst[k] = k < cnt * 6 ? ent[k] : 0.0;
-        for (int k = lane; k < M; k += 32) {
+        for (int k = g; k < M * 6; k += GS) dst[k] = k < cnt * 6 ? ent[k] : 0.0;
+        for (int k = g; k < M; k += GS) {
             a.life[(size_t)t * M + k] = k < cnt ? life[k] : 0;
             a.ids[(size_t)t * M + k] = k < cnt ? ids[k] : 0;
         }
-        if (lane == 0) { a.count[t] = cnt; a.next_id[t] = next_id; }
+        if (g == 0) { a.count[t] = cnt; a.next_id[t] = next_id; }
     }
+#undef GBALLOT
 }
 
 } // namespace lslam

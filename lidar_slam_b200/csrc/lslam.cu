@@ -183,7 +183,7 @@ extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t 
 {
     Handle *h = (Handle *)handle;
     if (h == nullptr) return LSLAM_ERR_BAD_ARG;
-    if (!xy || !line || !ninl || !win_trial || !win_pair || !ssum || !inl_mask)
+    if (!xy || !line || !ninl || !win_trial || !win_pair || !inl_mask)
         return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ransac_lines: null buffer");
     if (B < 0 || N < 1 || chunk < 2 || trials < 1 || trials > (1 << 20) || chunk > 8192)
         return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ransac_lines: need B >= 0, N >= 1, 2 <= chunk <= 8192, 1 <= trials <= 2^20");
@@ -257,8 +257,11 @@ extern "C" int lslam_associate(void *handle, const double *query, int32_t qstrid
         return fail(h, LSLAM_ERR_BAD_ARG, "lslam_associate: bad sizes / mode / layout");
     if (T == 0 || Q == 0) return LSLAM_OK;
     DeviceGuard g(h->device);
-    const size_t per_warp = (assoc_smem_per_warp(M) + 15) & ~(size_t)15;
-    int nwarps = (int)((size_t)h->smem_optin / per_warp);
+    // lane group per table: the smallest of 8 / 16 / 32 lanes that covers the table in one tile
+    const int GS = M <= 8 ? 8 : (M <= 16 ? 16 : 32);
+    const int NG = 32 / GS;
+    const size_t per_table = (assoc_smem_per_warp(M) + 15) & ~(size_t)15;
+    int nwarps = (int)((size_t)h->smem_optin / (per_table * NG));
     if (nwarps < 1) return fail(h, LSLAM_ERR_CAPACITY, "lslam_associate: table capacity M=%d does not fit shared memory", M);
     if (nwarps > 8) nwarps = 8;
     AssocArgs a;
@@ -267,14 +270,19 @@ extern "C" int lslam_associate(void *handle, const double *query, int32_t qstrid
     a.table = table; a.life = life; a.ids = ids; a.count = count; a.next_id = next_id;
     a.tolA = tolA; a.tolB = tolB; a.tol = tol; a.life_init = life_init; a.mode = mode; a.append = append;
     a.match = match; a.match_id = match_id; a.proj_ab = proj_ab; a.hit_pos = hit_pos;
-    auto kern = associate_kernel;
-    const size_t smem = per_warp * nwarps;
-    LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const unsigned grid = (unsigned)((T + nwarps - 1) / nwarps);
-    LSLAM_LAUNCH(kern, grid, (unsigned)(nwarps * 32), smem, (cudaStream_t)stream, a);
-    h->launches++;
-    LSLAM_CUDA_TRY(h, cudaGetLastError());
-    return LSLAM_OK;
+    const size_t smem = per_table * NG * nwarps;
+    const long long per_cta = (long long)nwarps * NG;
+    const unsigned grid = (unsigned)((T + per_cta - 1) / per_cta);
+    auto launch = [&](auto kern) -> int {
+        LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        LSLAM_LAUNCH(kern, grid, (unsigned)(nwarps * 32), smem, (cudaStream_t)stream, a);
+        h->launches++;
+        LSLAM_CUDA_TRY(h, cudaGetLastError());
+        return LSLAM_OK;
+    };
+    if (GS == 8) return launch(associate_kernel<8>);
+    if (GS == 16) return launch(associate_kernel<16>);
+    return launch(associate_kernel<32>);
 }
 
 // ---- UKF ------------------------------------------------------------------------------------

@@ -82,7 +82,7 @@ __host__ __device__ inline size_t ransac_smem_bytes(int G, int chunk, int T, int
     b += (size_t)G * kMaxCand * sizeof(LitLine);             // candidate models
     b += align16((size_t)G * W * 4);                         // winner masks
     b += align16((size_t)nwarps * W * 4);                    // per-warp scratch mask
-    b += 16;                                                 // CTA-wide scale
+    b += 32;                                                 // CTA-wide scale + CTA geometry
     return b;
 }
 
@@ -132,6 +132,7 @@ struct RansacSmem {
     uint32_t *smask;    // [G][W] winner masks
     uint32_t *wtmp;     // [nwarps][W] scratch masks
     int *cta_scale;
+    int *geo;           // b0, c0, number of staged points
 };
 
 __device__ __forceinline__ RansacSmem carve_smem(unsigned char *raw, int G, int chunk, int T, int W, int nwarps)
@@ -146,6 +147,7 @@ __device__ __forceinline__ RansacSmem carve_smem(unsigned char *raw, int G, int 
     s.smask = reinterpret_cast<uint32_t *>(p); p += align16((size_t)G * W * 4);
     s.wtmp = reinterpret_cast<uint32_t *>(p);  p += align16((size_t)nwarps * W * 4);
     s.cta_scale = reinterpret_cast<int *>(p);
+    s.geo = s.cta_scale + 4;
     return s;
 }
 
@@ -187,18 +189,25 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
     const long long slot0 = (long long)blockIdx.x * G;
     const long long rem_slots = a.nslots - slot0;
     const int nsl = rem_slots < (long long)G ? (int)rem_slots : G;
-    const int b0 = (int)(slot0 / a.C), c0 = (int)(slot0 % a.C);
+
+    // ---- CTA geometry: the 64-bit divisions are done by one thread and shared (a 64-bit division is
+    //      ~100 instructions; doing it in every warp cost 3-4 % of the kernel) ----
+    if (tid == 0) {
+        *sm.cta_scale = 0;
+        const int b0_ = (int)(slot0 / a.C), c0_ = (int)(slot0 - (long long)b0_ * a.C);
+        const int lastc = c0_ + nsl - 1;                      // last slot, counted from scan b0_
+        const int bl_ = b0_ + lastc / a.C, cl_ = lastc % a.C;
+        const int cend = (cl_ + 1) * chunk < a.N ? (cl_ + 1) * chunk : a.N;
+        sm.geo[0] = b0_; sm.geo[1] = c0_;
+        sm.geo[2] = (int)((long long)(bl_ - b0_) * a.N + cend - (long long)c0_ * chunk);   // points to stage
+    }
+    __syncthreads();
+    const int b0 = sm.geo[0], c0 = sm.geo[1], nstage = sm.geo[2];
     const long long gp0 = (long long)b0 * a.N + (long long)c0 * chunk;   // first staged point
 
     // ---- stage the CTA's points (contiguous in global memory): 16 B per thread, coalesced;
     //      track the largest |coordinate| of the CTA on the way ----
-    if (tid == 0) *sm.cta_scale = 0;
-    __syncthreads();
     {
-        const long long sl = slot0 + nsl - 1;
-        const int bl = (int)(sl / a.C), cl = (int)(sl % a.C);
-        const int cend = (cl + 1) * chunk < a.N ? (cl + 1) * chunk : a.N;
-        const int nstage = (int)((long long)bl * a.N + cend - gp0);
         const double2 *src = a.xy + gp0;
         int mh = 0;
         for (int k = tid; k < nstage; k += blockDim.x) {
@@ -215,8 +224,8 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
     // ---- per-slot geometry (one lane per slot) ----
     const bool cta_scale_bad = chunk_band(*sm.cta_scale).bad;
     for (int q = tid; q < nsl; q += blockDim.x) {
-        const long long s = slot0 + q;
-        const int b = (int)(s / a.C), c = (int)(s % a.C);
+        const int cq_ = c0 + q;                               // 32-bit: counted from scan b0
+        const int b = b0 + cq_ / a.C, c = cq_ % a.C;
         int nb = a.npts ? a.npts[b] : a.N;
         nb = nb < 0 ? 0 : (nb > a.N ? a.N : nb);
         int n = nb - c * chunk;
@@ -370,8 +379,48 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
             if (lane == 0 && n_relit) atomicAdd(a.counters + 0, (unsigned long long)n_relit);
             __syncwarp();
         }
+        int mx = 0, minhi_q = 0x7fffffff, ncand = 0;
+        if (T <= 128) {
+            // the chunk's (count, fast sum) pairs live in registers: 4 per lane, trial t = lane + 32 r
+            int cv[4];
+            double sv[4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int t = lane + 32 * r;
+                cv[r] = t < T ? cq[t] : -2;                  // -2: never the maximum, never a candidate
+                sv[r] = t < T ? sq[t] : 0.0;
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r) { const int v = cv[r] < 0 ? 0 : (cv[r] & ~kCntExact); mx = mx > v ? mx : v; }
+            mx = __reduce_max_sync(LSLAM_FULL_MASK, mx);
+            if (mx < 2) {                   // upstream's final estimate() needs 2 points
+                if (lane == 0) { st->mx = mx; st->status = kStatusNoModel; }
+                continue;
+            }
+            const SsumBound sb = ssum_bound_coeffs(cb.eabs, n, a.thr);
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                if (cv[r] >= 0 && (cv[r] & ~kCntExact) == mx) {
+                    const double e = (cv[r] & kCntExact) ? 0.0 : fma(sb.beta, sv[r], sb.alpha);
+                    const int k = key_up(sv[r] + e);
+                    minhi_q = minhi_q < k ? minhi_q : k;
+                }
+            }
+            minhi_q = __reduce_min_sync(LSLAM_FULL_MASK, minhi_q);
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                if (32 * r < T) {                            // uniform
+                    const bool cand = cv[r] >= 0 && trial_is_candidate(cv[r], sv[r], mx, minhi_q, sb);
+                    const unsigned m = __ballot_sync(LSLAM_FULL_MASK, cand);
+                    if (cand) {
+                        const int pos = ncand + __popc(m & ((1u << lane) - 1u));
+                        if (pos < kMaxCand) st->cand_t[pos] = lane + 32 * r;
+                    }
+                    ncand += __popc(m);
+                }
+            }
+        } else {
         // maximal inlier count
-        int mx = 0;
         for (int t = lane; t < T; t += 32) { const int v = cq[t] & ~kCntExact; mx = mx > v ? mx : v; }
         mx = __reduce_max_sync(LSLAM_FULL_MASK, mx);
         if (mx < 2) {                       // upstream's final estimate() needs 2 points
@@ -380,7 +429,6 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
         }
         // smallest upper bound of the literal residual sum among the tied trials (quantised up)
         const SsumBound sb = ssum_bound_coeffs(cb.eabs, n, a.thr);
-        int minhi_q = 0x7fffffff;
         for (int t = lane; t < T; t += 32) {
             const int cv = cq[t];
             if ((cv & ~kCntExact) == mx) {
@@ -392,7 +440,6 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
         }
         minhi_q = __reduce_min_sync(LSLAM_FULL_MASK, minhi_q);
         // candidate list in trial order
-        int ncand = 0;
         for (int t0 = 0; t0 < T; t0 += 32) {
             const int t = t0 + lane;
             const bool cand = t < T && trial_is_candidate(cq[t], sq[t], mx, minhi_q, sb);
@@ -402,6 +449,7 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
                 if (pos < kMaxCand) st->cand_t[pos] = t;
             }
             ncand += __popc(m);
+        }
         }
         if (lane == 0) { st->mx = mx; st->ncand = ncand; st->minhi_q = minhi_q; }
     }
@@ -417,7 +465,9 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
             sample_pair(a.seed, st->scan, (uint32_t)st->c, (uint32_t)st->cand_t[ci], (uint32_t)st->n, i, j);
             st->cand_i[ci] = i;
             st->cand_j[ci] = j;
-            sm.cmodel[e] = lit_pair_model(P[i], P[j]);
+            // a single unflagged candidate with no residual sum requested is decided on the fast model
+            if (!(st->ncand == 1 && a.ssum == nullptr && !(sm.cnt[q * T + st->cand_t[0]] & kCntExact)))
+                sm.cmodel[e] = lit_pair_model(P[i], P[j]);
         }
     }
     __syncthreads();
@@ -433,7 +483,30 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
         bool fault = false;
         int best_t = -1, best_i = -1, best_j = -1;
         double best_ss = __longlong_as_double(0x7ff0000000000000LL);
-        if (ncand <= kMaxCand) {
+        if (ncand == 1 && a.ssum == nullptr && !(sm.cnt[q * T + st->cand_t[0]] & kCntExact)) {
+            // One candidate, the caller does not want its residual sum: the winner is known and was
+            // not flagged, i.e. no point lies inside the re-check band, so its literal inlier mask
+            // is the fast one.  Rebuild the mask from the fast model (2 DFMA per point) instead of
+            // the literal score; the count is still checked against the selected maximum.
+            const int i = st->cand_i[0], j = st->cand_j[0];
+            const FastLine f = fast_pair_model(P[i], P[j]);
+            int c = 0;
+            for (int k0 = 0; k0 < n; k0 += 32) {
+                const int k = k0 + lane;
+                bool in = false;
+                if (k < n) {
+                    const double2 p = P[k];
+                    in = fabs(fma(p.y, f.ny, fma(p.x, f.nx, f.negc))) < a.thr;
+                }
+                const unsigned b = __ballot_sync(LSLAM_FULL_MASK, in);
+                c += __popc(b);
+                if (lane == 0) mq[k0 >> 5] = b;
+            }
+            __syncwarp();
+            if (c != mx) fault = true;
+            best_t = st->cand_t[0]; best_i = i; best_j = j;
+            best_ss = __longlong_as_double(0x7ff8000000000000LL);
+        } else if (ncand <= kMaxCand) {
             for (int ci = 0; ci < ncand; ++ci) {
                 int cl;
                 double sl;
@@ -544,7 +617,7 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
                 a.win_trial[s] = st->best_t;
                 a.win_pair[2 * s] = st->best_i;
                 a.win_pair[2 * s + 1] = st->best_j;
-                a.ssum[s] = st->best_ss;
+                if (a.ssum != nullptr) a.ssum[s] = st->best_ss;
             } else {
                 const double qnan = __longlong_as_double(0x7ff8000000000000LL);
 #pragma unroll
@@ -553,7 +626,7 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
                 a.win_trial[s] = -1;
                 a.win_pair[2 * s] = -1;
                 a.win_pair[2 * s + 1] = -1;
-                a.ssum[s] = qnan;
+                if (a.ssum != nullptr) a.ssum[s] = qnan;
             }
         }
     }

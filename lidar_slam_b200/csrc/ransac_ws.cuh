@@ -425,7 +425,7 @@ __device__ __forceinline__ void ws_epilogue_slot(const RansacArgs &a, long long 
         a.win_trial[s] = r.best_t;
         a.win_pair[2 * s] = r.best_i;
         a.win_pair[2 * s + 1] = r.best_j;
-        a.ssum[s] = r.best_ss;
+        if (a.ssum != nullptr) a.ssum[s] = r.best_ss;
     } else {
         const double qnan = __longlong_as_double(0x7ff8000000000000LL);
 #pragma unroll
@@ -434,7 +434,7 @@ __device__ __forceinline__ void ws_epilogue_slot(const RansacArgs &a, long long 
         a.win_trial[s] = -1;
         a.win_pair[2 * s] = -1;
         a.win_pair[2 * s + 1] = -1;
-        a.ssum[s] = qnan;
+        if (a.ssum != nullptr) a.ssum[s] = qnan;
     }
 }
 

@@ -12,6 +12,26 @@ import torch
 import torch.distributed as dist
 
 
+def bind_to_gpu_numa(device_index):
+    """Pin this process to the CPUs NVML reports as local to the GPU, so that pinned host buffers
+    (first touch) and the copy-issuing thread sit on the GPU's own socket.  Returns the CPU set used, or
+    None when NVML or the affinity call is unavailable (the process then stays where it is)."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(int(device_index))
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return sorted(cpus)
+    except Exception:
+        return None
+
+
 def shard_range(total, rank, world):
     """Contiguous block partition: rank r owns [r*ceil(total/world), min(total, (r+1)*ceil(total/world)))."""
     per = (total + world - 1) // world

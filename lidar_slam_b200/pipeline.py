@@ -23,7 +23,7 @@ class ScanPipeline:
         self.C = (self.N + self.chunk - 1) // self.chunk
         self.M = int(table_capacity)
         self.seed, self.scan_base = seed, scan_base
-        self.rout = eng.alloc_ransac_out(self.S, self.N, self.chunk)
+        self.rout = eng.alloc_ransac_out(self.S, self.N, self.chunk, ssum=False)
         self.tables = eng.alloc_tables(self.S, self.M)
         self.aout = eng.alloc_assoc_out(self.S, self.C)
         self.ukf = eng.alloc_ukf(self.S, self.C)

@@ -22,6 +22,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <map>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -72,6 +73,16 @@ class Barrier {
 struct WarpCtx {
     Barrier bar{32};
     uint64_t slot[32];
+    // collectives over a sub-mask (lane groups that run divergent code): one barrier per distinct mask
+    std::mutex sub_m;
+    std::map<unsigned, std::unique_ptr<Barrier>> sub;
+    Barrier &bar_for(unsigned mask) {
+        if (mask == 0xffffffffu) return bar;
+        std::lock_guard<std::mutex> lk(sub_m);
+        auto it = sub.find(mask);
+        if (it == sub.end()) it = sub.emplace(mask, std::make_unique<Barrier>((unsigned)__builtin_popcount(mask))).first;
+        return *it->second;
+    }
 };
 
 struct BlockCtx {
@@ -102,12 +113,13 @@ template <class T> inline uint64_t to_bits(T v) {
 }
 template <class T> inline T from_bits(uint64_t b) { T v; std::memcpy(&v, &b, sizeof(T)); return v; }
 
-template <class T> inline T exchange(T v, int src_lane) {
+template <class T> inline T exchange(T v, int src_lane, unsigned mask = 0xffffffffu) {
     WarpCtx &w = *ts.warp;
+    Barrier &b = w.bar_for(mask);
     w.slot[ts.lane] = to_bits(v);
-    w.bar.wait();
+    b.wait();
     T r = from_bits<T>(w.slot[src_lane & 31]);
-    w.bar.wait();
+    b.wait();
     return r;
 }
 
@@ -117,22 +129,23 @@ inline thread_local dim3 threadIdx, blockIdx, blockDim, gridDim;
 
 // ---- block / warp synchronisation and collectives ----
 static inline void __syncthreads() { emu::ts.blk->bar.wait(); }
-static inline void __syncwarp(unsigned = 0xffffffffu) { emu::ts.warp->bar.wait(); }
-template <class T> static inline T __shfl_sync(unsigned, T v, int src) { return emu::exchange(v, src); }
-template <class T> static inline T __shfl_xor_sync(unsigned, T v, int m) { return emu::exchange(v, emu::ts.lane ^ m); }
-template <class T> static inline T __shfl_down_sync(unsigned, T v, unsigned d) {
-    int src = emu::ts.lane + (int)d; return emu::exchange(v, src < 32 ? src : emu::ts.lane);
+static inline void __syncwarp(unsigned mask = 0xffffffffu) { emu::ts.warp->bar_for(mask).wait(); }
+template <class T> static inline T __shfl_sync(unsigned m, T v, int src) { return emu::exchange(v, src, m); }
+template <class T> static inline T __shfl_xor_sync(unsigned m, T v, int x) { return emu::exchange(v, emu::ts.lane ^ x, m); }
+template <class T> static inline T __shfl_down_sync(unsigned m, T v, unsigned d) {
+    int src = emu::ts.lane + (int)d; return emu::exchange(v, src < 32 ? src : emu::ts.lane, m);
 }
-template <class T> static inline T __shfl_up_sync(unsigned, T v, unsigned d) {
-    int src = emu::ts.lane - (int)d; return emu::exchange(v, src >= 0 ? src : emu::ts.lane);
+template <class T> static inline T __shfl_up_sync(unsigned m, T v, unsigned d) {
+    int src = emu::ts.lane - (int)d; return emu::exchange(v, src >= 0 ? src : emu::ts.lane, m);
 }
-static inline unsigned __ballot_sync(unsigned, int pred) {
+static inline unsigned __ballot_sync(unsigned mask, int pred) {
     emu::WarpCtx &w = *emu::ts.warp;
+    emu::Barrier &b = w.bar_for(mask);
     w.slot[emu::ts.lane] = pred ? 1 : 0;
-    w.bar.wait();
+    b.wait();
     unsigned r = 0;
-    for (int l = 0; l < 32; ++l) r |= (unsigned)(w.slot[l] & 1) << l;
-    w.bar.wait();
+    for (int l = 0; l < 32; ++l) if ((mask >> l) & 1u) r |= (unsigned)(w.slot[l] & 1) << l;
+    b.wait();
     return r;
 }
 static inline int __any_sync(unsigned m, int pred) { return __ballot_sync(m, pred) != 0; }

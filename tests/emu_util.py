@@ -29,6 +29,7 @@ def build_emu(force=False):
 
 
 _HANDLE = None
+WANT_SSUM = True      # default of emu_ransac_lines(want_ssum=None); the RANSAC tests run both ways
 
 
 def emu_handle():
@@ -42,7 +43,8 @@ def ptr(a):
     return None if a is None else a.ctypes.data
 
 
-def emu_ransac_lines(xy, npts=None, chunk=100, trials=100, thr=20.0, seed=0, scan_base=0, handle=None):
+def emu_ransac_lines(xy, npts=None, chunk=100, trials=100, thr=20.0, seed=0, scan_base=0, handle=None,
+                     want_ssum=None):
     """lslam_ransac_lines on the emulated library with NumPy buffers standing in for device
     memory.  Same outputs as oracle.cport.ransac_lines."""
     h = handle or emu_handle()
@@ -60,9 +62,11 @@ def emu_ransac_lines(xy, npts=None, chunk=100, trials=100, thr=20.0, seed=0, sca
         "ssum": np.full((B, C), -7.0, np.float64),
         "inl_mask": np.full((B, C, W), 0xdeadbeef, np.uint32),
     }
+    if not (WANT_SSUM if want_ssum is None else want_ssum):
+        del out["ssum"]
     h.ransac_lines(ptr(xy), ptr(npts), B, N, chunk, trials, thr, seed, scan_base,
                    ptr(out["line"]), ptr(out["ninl"]), ptr(out["win_trial"]), ptr(out["win_pair"]),
-                   ptr(out["ssum"]), ptr(out["inl_mask"]))
+                   ptr(out.get("ssum")), ptr(out["inl_mask"]))
     return out
 
 

@@ -8,7 +8,7 @@ from tests import assoc_util as au
 
 
 @pytest.mark.parametrize("mode", [0, 1])
-@pytest.mark.parametrize("M,prefill,Q", [(8, 0, 12), (8, 8, 6), (40, 37, 10), (70, 66, 5)])
+@pytest.mark.parametrize("M,prefill,Q", [(8, 0, 12), (8, 8, 6), (5, 4, 9), (16, 13, 9), (12, 12, 7), (40, 37, 10), (70, 66, 5)])
 def test_first_match_modes(emu, mode, M, prefill, Q):
     queries, valid, tables = au.random_streams(6, Q, M, seed=M + mode, prefill=prefill)
     want = au.oracle_associate(queries, valid, tables, mode=mode)

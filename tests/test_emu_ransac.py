@@ -9,14 +9,17 @@ from lidar_slam_b200 import synth
 from tests.parity_util import assert_ransac_equal
 
 
-@pytest.fixture(params=[2, 1], ids=["ws", "phased"], autouse=True)
+@pytest.fixture(params=[(2, True), (1, True), (1, False)], ids=["ws", "phased", "phased-nossum"], autouse=True)
 def ransac_kernel(request, emu):
     """Every test runs on both RANSAC kernels: 2 = warp-specialised persistent (csrc/ransac_ws.cuh),
-    1 = phase-structured (csrc/ransac.cuh)."""
+    1 = phase-structured (csrc/ransac.cuh) - the latter also without the optional residual-sum output,
+    which switches the decide stage of unambiguous chunks to the fast model."""
     h = emu.emu_handle()
-    h.set_option("ransac.kernel", request.param)
-    yield request.param
+    h.set_option("ransac.kernel", request.param[0])
+    emu.WANT_SSUM = request.param[1]
+    yield request.param[0]
     h.set_option("ransac.kernel", 0)
+    emu.WANT_SSUM = True
 
 
 def test_ws_role_shapes(emu, cport, ransac_kernel):

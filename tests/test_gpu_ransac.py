@@ -13,12 +13,19 @@ from tests.parity_util import assert_ransac_equal
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=[2, 1], ids=["ws", "phased"], autouse=True)
+WANT_SSUM = True
+
+
+@pytest.fixture(params=[(2, True), (1, True), (1, False)], ids=["ws", "phased", "phased-nossum"], autouse=True)
 def ransac_kernel(request, gpu_engine):
-    """Both RANSAC kernels: 2 = warp-specialised persistent, 1 = phase-structured."""
-    gpu_engine.set_option("ransac.kernel", request.param)
-    yield request.param
+    """Both RANSAC kernels: 2 = warp-specialised persistent, 1 = phase-structured (also without the
+    optional residual-sum output: the fast decide path)."""
+    global WANT_SSUM
+    gpu_engine.set_option("ransac.kernel", request.param[0])
+    WANT_SSUM = request.param[1]
+    yield request.param[0]
     gpu_engine.set_option("ransac.kernel", 0)
+    WANT_SSUM = True
 
 
 def test_ws_role_shapes(gpu_engine, cport, ransac_kernel):
@@ -50,7 +57,10 @@ def run_gpu(eng, xy, npts=None, **kw):
     import torch
     t = torch.from_numpy(np.ascontiguousarray(xy)).to(eng.device)
     n = torch.from_numpy(npts).to(eng.device) if npts is not None else None
-    return to_np(eng.ransac_lines(t, npts=n, **kw))
+    out = None
+    if not WANT_SSUM:
+        out = eng.alloc_ransac_out(t.shape[0], t.shape[1], kw.get("chunk", 100), ssum=False)
+    return to_np(eng.ransac_lines(t, npts=n, out=out, **kw))
 
 
 def test_library_is_the_cuda_build(gpu_engine):
@@ -65,7 +75,8 @@ def test_c1_golden(gpu_engine, cport):
     assert np.array_equal(got["ninl"][0], g["ninl"])
     assert np.array_equal(got["win_trial"][0], g["win_trial"])
     assert np.array_equal(got["win_pair"][0], g["win_pair"])
-    assert np.array_equal(got["ssum"][0].view(np.uint64), g["ssum"].view(np.uint64))
+    if "ssum" in got:
+        assert np.array_equal(got["ssum"][0].view(np.uint64), g["ssum"].view(np.uint64))
     np.testing.assert_allclose(got["line"][0, :, 0], g["a"], rtol=1e-5)
     np.testing.assert_allclose(got["line"][0, :, 1], g["b"], rtol=1e-5)
     np.testing.assert_allclose(got["line"][0, :, 6:8], g["tip"], rtol=1e-5)

@@ -25,7 +25,7 @@ __global__ void __launch_bounds__(256) mix(float *sink, int iters, float thr2)
         float nx[CH], ny[CH], ng[CH], ss[CH], mab[CH];
         unsigned bits[CH];
 #pragma unroll
-        for (int c = 0; c < CH; ++c) { nx[c] = 0.6f + 1e-3f * c; ny[c] = 0.8f - 1e-3f * c; ng[c] = -1.0f - c + threadIdx.x * 1e-6f; ss[c] = 0; bits[c] = 0; mab[c] = 1e30f; }
+        for (int c = 0; c < CH; ++c) { nx[c] = 0.6f + 1e-3f * c + threadIdx.x * 1e-7f; ny[c] = 0.8f - 1e-3f * c - threadIdx.x * 1e-7f; ng[c] = -1.0f - c + threadIdx.x * 1e-6f; ss[c] = 0; bits[c] = 0; mab[c] = 1e30f; }
         for (int it = 0; it < iters; ++it) {
 #pragma unroll 8
             for (int k = 0; k < 32; ++k) {
@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(256) mix(float *sink, int iters, float thr2)
         unsigned bits[CH];
         const unsigned long long mthr = pack(-thr2, -thr2);
 #pragma unroll
-        for (int c = 0; c < CH / 2; ++c) { nx[c] = pack(0.6f + 1e-3f * c, 0.61f); ny[c] = pack(0.8f - 1e-3f * c, 0.79f); ng[c] = pack(-1.0f - c + threadIdx.x * 1e-6f, -2.f); ss[c] = 0; mab[c] = 1e30f; bits[2 * c] = bits[2 * c + 1] = 0; }
+        for (int c = 0; c < CH / 2; ++c) { nx[c] = pack(0.6f + 1e-3f * c + threadIdx.x * 1e-7f, 0.61f + threadIdx.x * 1e-7f); ny[c] = pack(0.8f - 1e-3f * c - threadIdx.x * 1e-7f, 0.79f - threadIdx.x * 1e-7f); ng[c] = pack(-1.0f - c + threadIdx.x * 1e-6f, -2.f); ss[c] = 0; mab[c] = 1e30f; bits[2 * c] = bits[2 * c + 1] = 0; }
         for (int it = 0; it < iters; ++it) {
 #pragma unroll 8
             for (int k = 0; k < 32; ++k) {

@@ -10,7 +10,8 @@ from lidar_slam_b200 import batch  # noqa: E402
 
 cfg = sys.argv[1] if len(sys.argv) > 1 else "c2"
 eng = batch.Engine(0)
-for kv in sys.argv[3:]:
+NOSSUM = "nossum" in sys.argv
+for kv in [a for a in sys.argv[3:] if a != "nossum"]:
     k, v = kv.split("=")
     eng.set_option("ransac." + k, int(v))
 if cfg == "c2":
@@ -21,7 +22,7 @@ else:
     B = int(sys.argv[2]) if len(sys.argv) > 2 else 256
     xy = eng.synth_scans(B, beams=8192, seed=2)
     kw = {"chunk": 410, "trials": 1024}
-out = eng.alloc_ransac_out(B, xy.shape[1], kw.get("chunk", 100))
+out = eng.alloc_ransac_out(B, xy.shape[1], kw.get("chunk", 100), ssum=not NOSSUM)
 for _ in range(3):
     eng.ransac_lines(xy, out=out, **kw)
 torch.cuda.synchronize()
