@@ -9,7 +9,7 @@
 // lanes load one 32-bit word each (coalesced, 84 B per packet), the XOR checksum is one warp reduction,
 // lane l is measure l (trame l+1).  All angle arithmetic is exact in binary floating point (multiples
 // of 1/2048 degree below 2^11), so the angles are bit-identical to the reference's Python doubles;
-// only cos/sin differ from glibc's by their last bits.
+// cos/sin come from two small tables and the angle-sum formulas (about 1 ulp, like glibc's).
 // HBM traffic per point: 84/32 = 2.6 B read, 16 B written (+16 B when `meas` is requested).
 #pragma once
 #include "ransac.cuh"      // LSLAM_SMEM_DECL
@@ -22,6 +22,10 @@ constexpr int kExpressWords = 21;
 constexpr int kExpressMaxWarps = 12;
 constexpr int kExpressRow = kExpressWords + 3;                 // words per warp row in shared memory
 constexpr int kExpressSmem = kExpressRow * kExpressMaxWarps * 4 + 16;
+// sin/cos tables of the decoder: 360 whole degrees + 2048 steps of 1/2048 degree, (sin, cos) pairs
+constexpr int kExpressTabPairs = 360 + 2048;
+constexpr int kExpressTabDoubles = 2 * kExpressTabPairs;
+constexpr int kExpressDecodeSmem = kExpressSmem + 16 + kExpressTabDoubles * 8;
 
 // Python's float `%` with a positive divisor: fmod, then shifted into [0, m).
 __device__ __forceinline__ double py_mod(double a, double m)
@@ -40,67 +44,93 @@ __device__ __forceinline__ unsigned express_byte(const uint32_t *w, int off) { r
 // status bits per revolution
 constexpr int kExpressBadSync = 1, kExpressBadChecksum = 2;
 
+// Persistent warps, one packet per warp iteration, no block-level synchronisation: packet pk of the
+// batch (revolution pk / P, position pk % P) goes to warp pk mod (warps in the grid).  The next
+// packet's words are loaded before the current one is decoded (software pipelining), so every warp keeps
+// two 84-byte loads and one 512-byte store in flight.  `status` must be zero on entry (the entry point
+// clears it): a rejected packet ORs its bit into its revolution's word.
 __global__ void express_to_cart_kernel(const uint32_t *__restrict__ packets, long long nscans, int P, int beams,
-                                       double2 *__restrict__ xy, double2 *__restrict__ meas, int32_t *__restrict__ status)
+                                       double2 *__restrict__ xy, double2 *__restrict__ meas, int32_t *__restrict__ status,
+                                       const double2 *__restrict__ trig)
 {
     LSLAM_SMEM_DECL;
-    uint32_t (*words)[kExpressRow] = reinterpret_cast<uint32_t (*)[kExpressRow]>(smem_raw);
-    int &bad = *reinterpret_cast<int *>(smem_raw + sizeof(uint32_t) * kExpressRow * kExpressMaxWarps);
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    const double kPi = 3.141592653589793, kAngleToRad = kPi / 180.0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    uint32_t *ww = reinterpret_cast<uint32_t *>(smem_raw) + warp * kExpressRow;       // this warp's packet bytes
+    // (sin, cos) of d degrees [0, 360) and of b/2048 degree [0, 2048): staged once per CTA
+    double2 *tab = reinterpret_cast<double2 *>(smem_raw + ((kExpressSmem + 15) & ~15));
+    for (int k = threadIdx.x; k < kExpressTabPairs; k += blockDim.x) tab[k] = trig[k];
+    __syncthreads();
     const double nan = __longlong_as_double(0x7ff8000000000000LL);
-    for (long long scan = blockIdx.x; scan < nscans; scan += gridDim.x) {
-        if (threadIdx.x == 0) bad = 0;
-        __syncthreads();
-        const uint32_t *sp = packets + (size_t)scan * P * kExpressWords;
-        for (int p = warp; p < P; p += nwarps) {
-            const uint32_t *pk = sp + (size_t)p * kExpressWords;
-            const uint32_t w = lane < kExpressWords ? pk[lane] : 0u;
-            const uint32_t nw0 = sp[(size_t)((p + 1 == P) ? 0 : p + 1) * kExpressWords];   // next packet's first word
-            if (lane < kExpressWords) words[warp][lane] = w;
-            // checksum over bytes 2..83 = all words with the two sync bytes masked off
-            uint32_t x = __reduce_xor_sync(0xffffffffu, lane == 0 ? (w & 0xffff0000u) : w);
-            x ^= x >> 16;
-            x = (x ^ (x >> 8)) & 0xffu;
-            const uint32_t w0 = __shfl_sync(0xffffffffu, w, 0);
-            int st = 0;
-            if (((w0 >> 4) & 0xfu) != 0xAu || ((w0 >> 12) & 0xfu) != 0x5u) st |= kExpressBadSync;
-            else if (x != ((w0 & 0xfu) | (((w0 >> 8) & 0xfu) << 4))) st |= kExpressBadChecksum;
-            __syncwarp();
-            const int k = p * 32 + lane;
-            if (k < beams) {
-                const uint32_t *ww = words[warp];
-                const int i = 5 * (lane >> 1);
-                const int lo = (lane & 1) ? i + 6 : i + 4;
-                const unsigned b_lo = express_byte(ww, lo), b_hi = express_byte(ww, lo + 1), b_a = express_byte(ww, i + 8);
-                const int dist = (int)(b_lo >> 2) + (int)(b_hi << 6);                       // lidar.py:85,88
-                int code = (int)(((lane & 1) ? (b_a >> 4) : b_a) & 0xfu) + (int)((b_lo & 3u) << 4);
-                if (code & 16) code -= 32;                                                   // twos_comp(., 5)
-                const double dth = (double)code / 8.0;
-                const double start = (double)(((w0 >> 16) & 0xffu) + (((w0 >> 24) & 0x7fu) << 8)) / 64.0;   // :80
-                const double nstart = (double)(((nw0 >> 16) & 0xffu) + (((nw0 >> 24) & 0x7fu) << 8)) / 64.0;
-                // lidar.py:185  (start + ((next - start) % 360)/32 * trame - dtheta) % 360
-                const double step = py_mod(__dsub_rn(nstart, start), 360.0) / 32.0;
-                const double ang = py_mod(__dsub_rn(__dadd_rn(start, __dmul_rn(step, (double)(lane + 1))), dth), 360.0);
-                const double d = (double)dist;
-                const size_t o = (size_t)scan * beams + k;
-                if (st == 0) {
-                    const double t = __dadd_rn(__dmul_rn(-ang, kAngleToRad), kPi / 2.0);     // functions.py:59-60
-                    double s, c;
-                    sincos(t, &s, &c);
-                    xy[o] = make_double2(__dmul_rn(d, c), __dmul_rn(d, s));
-                    if (meas) meas[o] = make_double2(ang, d);
-                } else {
-                    xy[o] = make_double2(nan, nan);
-                    if (meas) meas[o] = make_double2(nan, nan);
-                }
+    const long long stride = (long long)gridDim.x * wpb, first = (long long)blockIdx.x * wpb + warp;
+    const long long npk = nscans * P;
+    if (first >= npk) return;
+    const long long stride_scan = stride / P;
+    const int stride_p = (int)(stride - stride_scan * P);
+    long long scan = first / P;
+    int p = (int)(first - scan * P);
+    auto load = [&](long long sc, int pp, uint32_t &w_, uint32_t &n_) {
+        const uint32_t *sp = packets + (size_t)sc * P * kExpressWords;
+        w_ = lane < kExpressWords ? sp[(size_t)pp * kExpressWords + lane] : 0u;
+        n_ = sp[(size_t)((pp + 1 == P) ? 0 : pp + 1) * kExpressWords];          // next packet's first word
+    };
+    uint32_t w, nw0;
+    load(scan, p, w, nw0);
+    for (long long pk = first; pk < npk; pk += stride) {
+        // prefetch the following packet of this warp
+        long long scan_n = scan + stride_scan;
+        int p_n = p + stride_p;
+        if (p_n >= P) { p_n -= P; ++scan_n; }
+        uint32_t w_n = 0u, nw0_n = 0u;
+        if (pk + stride < npk) load(scan_n, p_n, w_n, nw0_n);
+
+        if (lane < kExpressWords) ww[lane] = w;
+        // checksum over bytes 2..83 = all words with the two sync bytes masked off
+        uint32_t x = __reduce_xor_sync(0xffffffffu, lane == 0 ? (w & 0xffff0000u) : w);
+        x ^= x >> 16;
+        x = (x ^ (x >> 8)) & 0xffu;
+        const uint32_t w0 = __shfl_sync(0xffffffffu, w, 0);
+        int st = 0;
+        if (((w0 >> 4) & 0xfu) != 0xAu || ((w0 >> 12) & 0xfu) != 0x5u) st |= kExpressBadSync;
+        else if (x != ((w0 & 0xfu) | (((w0 >> 8) & 0xfu) << 4))) st |= kExpressBadChecksum;
+        __syncwarp();
+        const int k = p * 32 + lane;
+        if (k < beams) {
+            const int i = 5 * (lane >> 1);
+            const int lo = (lane & 1) ? i + 6 : i + 4;
+            const unsigned b_lo = express_byte(ww, lo), b_hi = express_byte(ww, lo + 1), b_a = express_byte(ww, i + 8);
+            const int dist = (int)(b_lo >> 2) + (int)(b_hi << 6);                       // lidar.py:85,88
+            int code = (int)(((lane & 1) ? (b_a >> 4) : b_a) & 0xfu) + (int)((b_lo & 3u) << 4);
+            if (code & 16) code -= 32;                                                   // twos_comp(., 5)
+            // lidar.py:80,185  angle = (start + ((next - start) % 360)/32 * trame - dtheta) % 360 with
+            // start = q6/64, dtheta = code/8.  Every term is a multiple of 1/2048 degree below 2^11, so
+            // the reference's float arithmetic is exact and the same value comes out of integers in
+            // units of 1/2048 degree (Python's % on floats = floor-mod, as below).
+            const int sq = (int)(((w0 >> 16) & 0xffu) + (((w0 >> 24) & 0x7fu) << 8));      // start, q6
+            const int nq = (int)(((nw0 >> 16) & 0xffu) + (((nw0 >> 24) & 0x7fu) << 8));    // next start, q6
+            int dq = (nq - sq) % 23040;                                                   // q6 units, 360 * 64
+            if (dq < 0) dq += 23040;
+            int k2048 = (sq * 32 + dq * (lane + 1) - code * 256) % 737280;                // 360 * 2048
+            if (k2048 < 0) k2048 += 737280;
+            const double d = (double)dist;
+            const size_t o = (size_t)scan * beams + k;
+            if (st == 0) {
+                // functions.py:59-60: x = d cos(pi/2 - theta), y = d sin(pi/2 - theta), theta = ang pi/180,
+                // i.e. x = d sin(theta), y = d cos(theta).  ang is an exact multiple of 1/2048 degree:
+                // theta = (a + b/2048) degrees, and the angle-sum formulas on two table entries give
+                // sin/cos to ~1 ulp without the ~100 fp64 instructions of a general sincos.
+                const double2 A = tab[k2048 >> 11], Bq = tab[360 + (k2048 & 2047)];       // (sin, cos)
+                const double sn = fma(A.x, Bq.y, A.y * Bq.x);                             // sin(a + b)
+                const double cs = fma(A.y, Bq.y, -(A.x * Bq.x));                          // cos(a + b)
+                xy[o] = make_double2(__dmul_rn(d, sn), __dmul_rn(d, cs));
+                if (meas) meas[o] = make_double2((double)k2048 * (1.0 / 2048.0), d);
+            } else {
+                xy[o] = make_double2(nan, nan);
+                if (meas) meas[o] = make_double2(nan, nan);
             }
-            if (st != 0 && lane == 0) atomicOr(&bad, st);
-            __syncwarp();
         }
-        __syncthreads();
-        if (threadIdx.x == 0 && status) status[scan] = bad;
-        __syncthreads();
+        if (st != 0 && lane == 0 && status) atomicOr(status + scan, st);
+        __syncwarp();
+        w = w_n; nw0 = nw0_n; scan = scan_n; p = p_n;
     }
 }
 

@@ -11,6 +11,8 @@
 #include "express.cuh"
 #include "ransac_ols.cuh"
 #include <cfloat>
+#include <vector>
+#include <cmath>
 
 #include "../../include/lslam.h"
 
@@ -33,6 +35,26 @@ extern "C" int lslam_create(int device, void **handle)
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
     if (e == cudaSuccess) e = cudaMalloc((void **)&h->counters_d, 8 * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMemset(h->counters_d, 0, 8 * sizeof(unsigned long long));
+    if (e == cudaSuccess) {
+        // sin/cos of whole degrees and of the 2048 sub-degree steps, rounded from long double
+        std::vector<double> tab(kExpressTabDoubles);
+        const long double pi = 3.14159265358979323846264338327950288L;
+        for (int d = 0; d < 360; ++d) {
+            const long double th = (long double)d * pi / 180.0L;
+            tab[2 * d] = (double)sinl(th); tab[2 * d + 1] = (double)cosl(th);
+        }
+        for (int b = 0; b < 2048; ++b) {
+            const long double th = (long double)b * pi / (180.0L * 2048.0L);
+            tab[720 + 2 * b] = (double)sinl(th); tab[720 + 2 * b + 1] = (double)cosl(th);
+        }
+        // exact values where the true result is exactly representable (sin 180 = 0, cos 90 = 0, ...)
+        for (int q = 0; q < 4; ++q) {
+            const double sv[4] = {0.0, 1.0, 0.0, -1.0}, cv[4] = {1.0, 0.0, -1.0, 0.0};
+            tab[2 * 90 * q] = sv[q]; tab[2 * 90 * q + 1] = cv[q];
+        }
+        e = cudaMalloc((void **)&h->express_tab_d, sizeof(double) * kExpressTabDoubles);
+        if (e == cudaSuccess) e = cudaMemcpy(h->express_tab_d, tab.data(), sizeof(double) * kExpressTabDoubles, cudaMemcpyHostToDevice);
+    }
     if (e != cudaSuccess) { delete h; return LSLAM_ERR_CUDA; }
     *handle = h;
     return LSLAM_OK;
@@ -44,6 +66,7 @@ extern "C" int lslam_destroy(void *handle)
     if (h == nullptr) return LSLAM_ERR_BAD_ARG;
     DeviceGuard g(h->device);
     cudaFree(h->counters_d);
+    cudaFree(h->express_tab_d);
     delete h;
     return LSLAM_OK;
 }
@@ -501,7 +524,7 @@ extern "C" int lslam_ransac_ols(void *handle, const double *xy, const int32_t *n
 static int express_shape(Handle *h, int64_t nscans, int P, unsigned *grid, int *threads)
 {
     *threads = 32 * (P < kExpressMaxWarps ? P : kExpressMaxWarps);
-    const long long cap = (long long)h->sms * 64;
+    const long long cap = (long long)h->sms * 5;          // persistent: 5 CTAs per SM by shared memory
     *grid = (unsigned)(nscans < cap ? nscans : cap);
     return 0;
 }
@@ -520,10 +543,15 @@ extern "C" int lslam_express_to_cart(void *handle, const uint8_t *packets, int64
     DeviceGuard g(h->device);
     unsigned grid; int threads;
     express_shape(h, nscans, packets_per_scan, &grid, &threads);
+    threads = 32 * kExpressMaxWarps;
+    if (status) LSLAM_CUDA_TRY(h, cudaMemsetAsync(status, 0, sizeof(int32_t) * (size_t)nscans, (cudaStream_t)stream));
     auto kern = express_to_cart_kernel;
-    LSLAM_LAUNCH(kern, grid, threads, kExpressSmem, (cudaStream_t)stream, reinterpret_cast<const uint32_t *>(packets),
+#ifndef LSLAM_EMU
+    LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kExpressDecodeSmem));
+#endif
+    LSLAM_LAUNCH(kern, grid, threads, kExpressDecodeSmem, (cudaStream_t)stream, reinterpret_cast<const uint32_t *>(packets),
                  (long long)nscans, (int)packets_per_scan, (int)beams, reinterpret_cast<double2 *>(xy),
-                 reinterpret_cast<double2 *>(meas), status);
+                 reinterpret_cast<double2 *>(meas), status, reinterpret_cast<const double2 *>(h->express_tab_d));
     h->launches++;
     LSLAM_CUDA_TRY(h, cudaGetLastError());
     return LSLAM_OK;
