@@ -96,6 +96,9 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
     } else if (!strcmp(key, "ransac.threads")) {
         if (value < 0 || value > 1024 || value % 32) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.threads must be a multiple of 32 <= 1024");
         h->opt_threads = (int)value;
+    } else if (!strcmp(key, "ransac.screen")) {
+        if (value < 0 || value > 2) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.screen: 0 default, 1 fp64, 2 fp32");
+        h->opt_screen = (int)value;
     } else if (!strcmp(key, "ransac.kernel")) {
         if (value < 0 || value > 2) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.kernel: 0 default, 1 phase-structured, 2 warp-specialised");
         h->opt_kernel = (int)value;
@@ -112,10 +115,10 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
 }
 
 // ---- RANSAC ------------------------------------------------------------------------------
-template <int TPT, int MAXT, int MINB>
+template <int TPT, int MAXT, int MINB, bool F32>
 static int launch_ransac(Handle *h, RansacArgs a, int threads_target, cudaStream_t st)
 {
-    auto kern = ransac_lines_kernel<TPT, MAXT, MINB>;
+    auto kern = ransac_lines_kernel<TPT, MAXT, MINB, F32>;
     a.ipc = (a.trials + TPT - 1) / TPT;
     if (threads_target > MAXT) threads_target = MAXT;
     // chunk slots per CTA: enough work items to fill the CTA, bounded by shared memory
@@ -134,7 +137,7 @@ static int launch_ransac(Handle *h, RansacArgs a, int threads_target, cudaStream
         threads = (threads + 31) & ~31;
         if (threads > MAXT) threads = MAXT & ~31;
         if (threads < 4 * G) threads = ((4 * G + 31) & ~31) > MAXT ? (MAXT & ~31) : ((4 * G + 31) & ~31);
-        smem = ransac_smem_bytes(G, a.chunk, a.trials, a.W, threads / 32);
+        smem = ransac_smem_bytes(G, a.chunk, a.trials, a.W, threads / 32, F32);
         if (smem <= (size_t)h->smem_optin || G == 1) break;
     }
     if (smem > (size_t)h->smem_optin)
@@ -233,6 +236,9 @@ extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t 
     const int kernel = h->opt_kernel ? h->opt_kernel : (big_chunks ? 2 : 1);
     const int tpt = h->opt_tpt ? h->opt_tpt : ((kernel == 2 && big_chunks) ? 4 : 2);
     const int threads = h->opt_threads ? h->opt_threads : 256;
+    // screening precision of the phase-structured kernel: 1 = fp64, 2 = fp32 (FFMA2 trial pairs); default fp64
+    // until the fp32 path has its own measured win (ransac.screen)
+    const bool f32 = h->opt_screen == 2;
     cudaStream_t st = (cudaStream_t)stream;
     a.ws_ns = a.ws_np = a.ws_nb = 0;
     if (kernel == 2) {
@@ -243,9 +249,9 @@ extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t 
         }
     }
     switch (tpt) {
-    case 1: return launch_ransac<1, 512, 2>(h, a, threads, st);
-    case 2: return launch_ransac<2, 512, 2>(h, a, threads, st);
-    default: return launch_ransac<4, 512, 1>(h, a, threads, st);
+    case 1: return launch_ransac<1, 512, 2, false>(h, a, threads, st);
+    case 2: return f32 ? launch_ransac<2, 512, 2, true>(h, a, threads, st) : launch_ransac<2, 512, 2, false>(h, a, threads, st);
+    default: return f32 ? launch_ransac<4, 512, 1, true>(h, a, threads, st) : launch_ransac<4, 512, 1, false>(h, a, threads, st);
     }
 }
 

@@ -21,7 +21,7 @@ struct Handle {
     int smem_optin = 0;
     int64_t launches = 0;
     int opt_tpt = 0, opt_slots = 0, opt_threads = 0;
-    int opt_kernel = 0, opt_scorers = 0, opt_posts = 0, opt_ring = 0;
+    int opt_kernel = 0, opt_scorers = 0, opt_posts = 0, opt_ring = 0, opt_screen = 0;
     double *express_tab_d = nullptr;   // sin/cos tables of the packet decoder (csrc/express.cuh)
     unsigned long long *counters_d = nullptr;
     char err[512] = "";

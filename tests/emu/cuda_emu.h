@@ -47,6 +47,7 @@ struct alignas(8) uint2 { unsigned x, y; };
 struct alignas(16) uint4 { unsigned x, y, z, w; };
 struct alignas(16) int4 { int x, y, z, w; };
 static inline double2 make_double2(double x, double y) { return double2{x, y}; }
+static inline float2 make_float2(float x, float y) { return float2{x, y}; }
 static inline int2 make_int2(int x, int y) { return int2{x, y}; }
 static inline uint2 make_uint2(unsigned x, unsigned y) { return uint2{x, y}; }
 static inline uint4 make_uint4(unsigned x, unsigned y, unsigned z, unsigned w) { return uint4{x, y, z, w}; }
@@ -189,6 +190,9 @@ static inline double __hiloint2double(int hi, int lo) {
 }
 static inline float __int_as_float(int i) { float f; std::memcpy(&f, &i, 4); return f; }
 static inline int __float_as_int(float f) { int i; std::memcpy(&i, &f, 4); return i; }
+static inline float __double2float_ru(double d) { float f = (float)d; return (double)f < d ? std::nextafterf(f, INFINITY) : f; }
+static inline unsigned __float_as_uint(float f) { unsigned i; std::memcpy(&i, &f, 4); return i; }
+static inline float __uint_as_float(unsigned i) { float f; std::memcpy(&f, &i, 4); return f; }
 static inline long long __double_as_longlong(double d) { long long i; std::memcpy(&i, &d, 8); return i; }
 static inline double __longlong_as_double(long long i) { double d; std::memcpy(&d, &i, 8); return d; }
 static inline float rsqrtf(float x) { return 1.0f / sqrtf(x); }

@@ -16,15 +16,18 @@ pytestmark = pytest.mark.gpu
 WANT_SSUM = True
 
 
-@pytest.fixture(params=[(2, True), (1, True), (1, False)], ids=["ws", "phased", "phased-nossum"], autouse=True)
+@pytest.fixture(params=[(2, True, 0), (1, True, 1), (1, False, 1), (1, True, 2), (1, False, 2)],
+                ids=["ws", "phased", "phased-nossum", "phased-f32", "phased-f32-nossum"], autouse=True)
 def ransac_kernel(request, gpu_engine):
     """Both RANSAC kernels: 2 = warp-specialised persistent, 1 = phase-structured (also without the
     optional residual-sum output: the fast decide path)."""
     global WANT_SSUM
     gpu_engine.set_option("ransac.kernel", request.param[0])
+    gpu_engine.set_option("ransac.screen", request.param[2])
     WANT_SSUM = request.param[1]
     yield request.param[0]
     gpu_engine.set_option("ransac.kernel", 0)
+    gpu_engine.set_option("ransac.screen", 0)
     WANT_SSUM = True
 
 
