@@ -34,7 +34,7 @@ if ROOT not in sys.path:
 
 BEAMS, CHUNK, TRIALS, THR, TABLE_M = 360, 100, 100, 20.0, 8
 PACKETS = 12                                       # express packets per revolution (32 measures each)
-E2E_SLICES = 8                                     # slices of the overlapped host path
+E2E_SLICES = 16                                    # slices of the overlapped host path
 PHE_PER_SCAN = BEAMS * TRIALS                      # point-hypothesis evaluations per scan
 FLOP_PER_PHE = 8                                   # algorithmic fp64 flop per PHE
 BYTES_PER_SCAN = BEAMS * 16 + 4 * 96               # 5,760 in + 4 x 96 out = 6,144 B
@@ -53,6 +53,7 @@ def parse():
     p.add_argument("--cpu-sample", type=int, default=0, help="scans in the CPU sample (0 = auto)")
     p.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--slices", type=int, default=0, help="slices of the overlapped host path (0 = default)")
     p.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                    help="N > 1 result gather: fused into the UKF kernel over peer memory, or an NCCL all_gather")
     return p.parse_args()
@@ -182,6 +183,9 @@ def workload_config(args, world):
 # ---- our arm ---------------------------------------------------------------------------------------
 def main():
     args = parse()
+    global E2E_SLICES
+    if args.slices > 0:
+        E2E_SLICES = args.slices
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
