@@ -42,7 +42,7 @@ int lslam_create(int device, void **handle);
 int lslam_destroy(void *handle);
 const char *lslam_last_error(void *handle);
 /* ABI version of the loaded library (LSLAM_ABI_VERSION at build time). */
-#define LSLAM_ABI_VERSION 4
+#define LSLAM_ABI_VERSION 5
 int lslam_abi_version(void);
 /* Launch-shape tuning knobs; 0 restores the built-in heuristic.  Results never depend on them.
  *   "ransac.kernel"  0 default, 1 phase-structured kernel, 2 warp-specialised persistent kernel
@@ -201,6 +201,23 @@ int lslam_ukf_update(void *handle, double *x, double *P, const double *z, int32_
                      const double *lm_pos, const int32_t *lm_valid, int32_t valid_min, int32_t F,
                      int32_t L, const double *params_h, int32_t *status, const double *sigmas_f,
                      void *stream);
+
+/* ---- augmented-state UKF (BASELINE.json configs[3]: pose + L landmarks in the state) ------------
+ * The same filterpy engine and UKFMethods callbacks as above (/root/reference/systemClass.py:20-29,
+ * UKFMethods.py:10-71) for F independent filters of dimension n = 3 + 2L: x = (x, y, theta, l0x, l0y,
+ * l1x, ...), fx moves the pose and leaves the landmarks, hx is UKFMethods.transfer_function with the
+ * landmark positions read from the state (oracle/ukf.py transfer_function_augmented), dim_z = 2L,
+ * R = diag([var_dist, var_angle] * L), Q = params' 3x3 on the pose block and zero elsewhere,
+ * 2n + 1 sigma points.  K = Pxz S^-1 is formed through the Cholesky factor of S (filterpy: inv(S)).
+ *   x [F,n], P [F,n,n] in/out;  u [F,2] or NULL;  z [F,L,2] (range, bearing) per landmark;
+ *   params_h, flags, status as for lslam_ukf_step; a filter whose status is non-zero keeps its (x, P).
+ *   workspace: device scratch; filters are processed in batches of as many as fit
+ *   (lslam_ukf_aug_workspace_bytes(L, k) bytes hold k filters; at least one must fit).  1 <= L <= 1024.
+ */
+int lslam_ukf_aug_workspace_bytes(int32_t L, int32_t filters, int64_t *bytes);
+int lslam_ukf_aug_step(void *handle, double *x, double *P, const double *u, const double *z, int32_t F,
+                       int32_t L, const double *params_h, int32_t flags, int32_t *status, void *workspace,
+                       int64_t workspace_bytes, void *stream);
 
 /* ---- OLS-flavour RANSAC ------------------------------------------------------------
  * Replaces sklearn.linear_model.RANSACRegressor(residual_threshold=3).fit(x[i:k], y[i:k]) +

@@ -18,7 +18,7 @@ LSLAM_ERR_NO_MODEL = -3
 LSLAM_ERR_CUDA = -4
 LSLAM_ERR_NONFINITE = -5
 LSLAM_ERR_CAPACITY = -6
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 _vp = ctypes.c_void_p
 _i32 = ctypes.c_int32
@@ -48,6 +48,9 @@ SIGNATURES = {
     "lslam_ukf_predict": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i32, ctypes.POINTER(_f64), _i32, _vp, _vp, _vp]),
     "lslam_ukf_update": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32,
                                         ctypes.POINTER(_f64), _vp, _vp, _vp]),
+    "lslam_ukf_aug_workspace_bytes": (ctypes.c_int, [_i32, _i32, ctypes.POINTER(_i64)]),
+    "lslam_ukf_aug_step": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, ctypes.POINTER(_f64), _i32, _vp, _vp,
+                                          _i64, _vp]),
     "lslam_ransac_ols": (ctypes.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _f64, _f64, _u64, _u64,
                                         _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "lslam_express_to_cart": (ctypes.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _vp, _vp, _vp]),
@@ -185,6 +188,16 @@ class Handle:
                    status=None, sigmas_f=None, stream=0):
         self._check(self.cdll.lslam_ukf_update(self._h, x, P, z, zstride, zmode, lm_pos, lm_valid, valid_min,
                                                F, L, self._params(params), status, sigmas_f, stream))
+
+    def ukf_aug_workspace_bytes(self, L, filters):
+        out = _i64(0)
+        if self.cdll.lslam_ukf_aug_workspace_bytes(int(L), int(filters), ctypes.byref(out)) != LSLAM_OK:
+            raise LslamError(-1, "lslam_ukf_aug_workspace_bytes: need 1 <= L <= 1024, filters >= 1")
+        return int(out.value)
+
+    def ukf_aug_step(self, x, P, u, z, F, L, params, flags, status, workspace, workspace_bytes, stream=0):
+        self._check(self.cdll.lslam_ukf_aug_step(self._h, x, P, u, z, F, L, self._params(params), flags, status,
+                                                 workspace, int(workspace_bytes), stream))
 
     def synth_scans(self, xy, B, beams, seed, scan_base, noise_mm, dropout, stream=0):
         self._check(self.cdll.lslam_synth_scans(self._h, xy, B, beams, int(seed) & (2**64 - 1),

@@ -307,6 +307,59 @@ class Engine:
                                         gather.get("mc_ids"), self._stream())
         return ukf
 
+    # ---- augmented-state filters (pose + L landmarks in the state; BASELINE.json configs[3]) ----
+    def alloc_ukf_aug(self, F, L, workspace_filters=None, workspace_bytes=None):
+        """F filters of dimension n = 3 + 2L: x = 0, P = diag(.1, .1, .05, 25, 25, ...) (pose prior of
+        systemClass.config_ukf, 5 mm landmark sigma), and the scratch lslam_ukf_aug_step needs.
+        The scratch holds ``workspace_filters`` filters at a time (default: all F, capped at ~1/4 of the
+        device's memory); more filters are processed in batches."""
+        dev = self.device
+        n = 3 + 2 * L
+        per = self.handle.ukf_aug_workspace_bytes(L, 1)
+        if workspace_bytes is None:
+            k = F if workspace_filters is None else int(workspace_filters)
+            cap = torch.cuda.get_device_properties(dev).total_memory // 4 if dev.type == "cuda" else per * k
+            k = max(1, min(k, cap // per))
+            workspace_bytes = self.handle.ukf_aug_workspace_bytes(L, k)
+        d = torch.tensor([0.1, 0.1, 0.05] + [25.0] * (2 * L), dtype=torch.float64, device=dev)
+        return {
+            "x": torch.zeros((F, n), dtype=torch.float64, device=dev),
+            "P": torch.diag(d).expand(F, n, n).contiguous(),
+            "u": torch.zeros((F, 2), dtype=torch.float64, device=dev),
+            "status": torch.zeros((F,), dtype=torch.int32, device=dev),
+            "params": self.ukf_params(),
+            "workspace": torch.empty((workspace_bytes,), dtype=torch.uint8, device=dev),
+            "L": L,
+        }
+
+    def ukf_aug_step(self, ukf, z, u=None, flags=None):
+        """predict(u) + update(z) of every augmented filter in ``ukf`` (dict of alloc_ukf_aug), in place.
+        z [F, L, 2]: (range, bearing) of every landmark of the state."""
+        L = int(ukf["L"])
+        n = 3 + 2 * L
+        x = self._check(ukf["x"], torch.float64, "ukf['x']")
+        P = self._check(ukf["P"], torch.float64, "ukf['P']")
+        F = int(x.shape[0])
+        if x.shape != (F, n) or P.shape != (F, n, n):
+            raise ValueError("ukf['x'] must be [F, 3 + 2L] and ukf['P'] [F, 3 + 2L, 3 + 2L]")
+        u = ukf.get("u") if u is None else u
+        if u is not None:
+            u = self._check(u, torch.float64, "u")
+            if u.shape != (F, 2):
+                raise ValueError("u must be [F, 2]")
+        if flags is None:
+            flags = self.UKF_PREDICT | self.UKF_UPDATE | self.UKF_REDRAW
+        if z is not None:
+            z = self._check(z, torch.float64, "z")
+            if z.shape != (F, L, 2):
+                raise ValueError("z must be [F, L, 2]")
+        st = self._check(ukf["status"], torch.int32, "ukf['status']")
+        ws = ukf["workspace"]
+        self.handle.ukf_aug_step(x.data_ptr(), P.data_ptr(), u.data_ptr() if u is not None else None,
+                                 z.data_ptr() if z is not None else None, F, L, ukf["params"], flags, st.data_ptr(),
+                                 ws.data_ptr(), ws.numel(), self._stream())
+        return ukf
+
     def synth_scans(self, B, beams=360, seed=0, scan_base=0, noise_mm=5.0, dropout=0.02, out=None):
         """Random-room scans generated on the device (csrc/aux_kernels.cuh) -> xy[B, beams, 2]."""
         if out is None:

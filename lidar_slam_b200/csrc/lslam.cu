@@ -8,6 +8,7 @@
 #include "aux_kernels.cuh"
 #include "assoc.cuh"
 #include "ukf.cuh"
+#include "ukf_aug.cuh"
 #include "express.cuh"
 #include "ransac_ols.cuh"
 #include <cfloat>
@@ -441,6 +442,188 @@ extern "C" int lslam_ukf_update(void *handle, double *x, double *P, const double
 {
     return lslam_ukf_step(handle, x, P, nullptr, z, zstride, zmode, lm_pos, lm_valid, valid_min, F, L, params_h,
                           LSLAM_UKF_UPDATE, status, const_cast<double *>(sigmas_f), stream);
+}
+
+// ---- augmented-state UKF ------------------------------------------------------------------------
+namespace {
+struct AugLayout {
+    long long per_filter;           // doubles
+    long long U, X, Y, H, S, ST, Kt, T, Pbar, xbar, xnew, zhat;   // sizes in doubles per filter
+};
+AugLayout aug_layout(int L)
+{
+    const long long n = 3 + 2LL * L, m = 2 * n + 1, dz = 2LL * L;
+    AugLayout y;
+    y.U = n * n; y.X = m * n; y.Y = m * n; y.H = m * dz; y.S = dz * dz; y.ST = dz * dz; y.Kt = dz * n; y.T = dz * n;
+    y.Pbar = n * n; y.xbar = n; y.xnew = n; y.zhat = dz;
+    y.per_filter = y.U + y.X + y.Y + y.H + y.S + y.ST + y.Kt + y.T + y.Pbar + y.xbar + y.xnew + y.zhat;
+    return y;
+}
+constexpr int kAugMaxBatch = 32768;
+
+struct AugRun {
+    Handle *h; cudaStream_t st; int F;
+    int gemm(const double *A, long long sA, int lda, const double *B, long long sB, int ldb, double *C, long long sC, int ldc,
+             int M, int N, int K, const double *w, double alpha, double beta, const int32_t *skip, int upper)
+    {
+        if (M <= 0 || N <= 0) return LSLAM_OK;
+        AugGemm g;
+        g.A = A; g.B = B; g.w = w; g.C = C; g.sA = sA; g.sB = sB; g.sC = sC; g.M = M; g.N = N; g.K = K;
+        g.lda = lda; g.ldb = ldb; g.ldc = ldc; g.alpha = alpha; g.beta = beta; g.skip = skip; g.upper = upper;
+        dim3 grid((N + kAugTile - 1) / kAugTile, (M + kAugTile - 1) / kAugTile, F);
+        LSLAM_LAUNCH(aug_gemm_tn_kernel, grid, 256, kAugGemmSmem, st, g);
+        h->launches++;
+        return LSLAM_OK;
+    }
+    // in-place upper Cholesky of F matrices (dim x dim, ld = dim, stride sA)
+    int chol(double *A, long long sA, int dim, int32_t *status, int fail_bit)
+    {
+        for (int jb = 0; jb < dim; jb += 32) {
+            const int nb = dim - jb < 32 ? dim - jb : 32;
+            LSLAM_LAUNCH(aug_chol_panel_kernel, dim3(F), 256, kAugBlockSmem, st, A, sA, dim, dim, jb, nb, status, fail_bit);
+            h->launches++;
+            const int rest = dim - jb - nb;
+            if (rest > 0) {
+                const double *panel = A + (size_t)jb * dim + jb + nb;
+                gemm(panel, sA, dim, panel, sA, dim, A + (size_t)(jb + nb) * dim + jb + nb, sA, dim, rest, rest, nb,
+                     nullptr, -1.0, 1.0, status, 1);
+            }
+        }
+        return LSLAM_OK;
+    }
+};
+} // namespace
+
+extern "C" int lslam_ukf_aug_workspace_bytes(int32_t L, int32_t filters, int64_t *bytes)
+{
+    if (L < 1 || L > 1024 || filters < 1 || !bytes) return LSLAM_ERR_BAD_ARG;
+    const AugLayout y = aug_layout(L);
+    const long long n = 3 + 2LL * L;
+    *bytes = (int64_t)sizeof(double) * (y.per_filter * filters + 2 * (2 * n + 1));
+    return LSLAM_OK;
+}
+
+extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const double *u, const double *z, int32_t F,
+                                  int32_t L, const double *params_h, int32_t flags, int32_t *status, void *workspace,
+                                  int64_t workspace_bytes, void *stream)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr) return LSLAM_ERR_BAD_ARG;
+    if (!x || !P || !params_h || !status || !workspace)
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_aug_step: null buffer (x, P, params_h, status, workspace)");
+    if (F < 0 || L < 1 || L > 1024 || (flags & ~7) || !(flags & 3))
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_aug_step: need F >= 0, 1 <= L <= 1024, flags of PREDICT|UPDATE|REDRAW");
+    const bool pred = flags & LSLAM_UKF_PREDICT, upd = flags & LSLAM_UKF_UPDATE;
+    if (upd && !z) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_aug_step: update needs z");
+    if (F == 0) return LSLAM_OK;
+    const int n = 3 + 2 * L, m = 2 * n + 1, dz = 2 * L;
+    const AugLayout lay = aug_layout(L);
+    const long long avail = workspace_bytes / (long long)sizeof(double) - 2LL * m;
+    long long cap = avail > 0 ? avail / lay.per_filter : 0;
+    if (cap < 1) return fail(h, LSLAM_ERR_CAPACITY, "lslam_ukf_aug_step: workspace holds no filter (lslam_ukf_aug_workspace_bytes)");
+    if (cap > kAugMaxBatch) cap = kAugMaxBatch;
+    DeviceGuard g(h->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const double alpha = params_h[3], beta = params_h[4], kappa = params_h[5];
+    const double lam = alpha * alpha * (n + kappa) - n;
+    const double c = n + lam;
+    if (!(c == c) || c == 0.0) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_aug_step: alpha/kappa give n + lambda = 0");
+    double *ws = (double *)workspace;
+    double *wm = ws, *wc = ws + m;
+    ws += 2 * m;
+    LSLAM_LAUNCH(aug_weights_kernel, dim3((m + 255) / 256), 256, 0, st, wm, wc, m, 0.5 / c, lam / c, lam / c + (1 - alpha * alpha + beta));
+    h->launches++;
+    LSLAM_CUDA_TRY(h, cudaMemsetAsync(status, 0, sizeof(int32_t) * (size_t)F, st));
+    const unsigned ew = (unsigned)(2 * h->sms);                 // elementwise grids: x-blocks per filter
+    for (long long f0 = 0; f0 < F; f0 += cap) {
+        const int Fb = (int)(F - f0 < cap ? F - f0 : cap);
+        AugArgs a;
+        a.F = Fb; a.L = L; a.n = n; a.m = m; a.dz = dz;
+        a.x = x + (size_t)f0 * n; a.P = P + (size_t)f0 * n * n;
+        a.u = u ? u + (size_t)f0 * 2 : nullptr; a.z = z ? z + (size_t)f0 * dz : nullptr;
+        a.status = status + f0;
+        double *p = ws;
+        a.U = p; p += lay.U * Fb; a.X = p; p += lay.X * Fb; a.Y = p; p += lay.Y * Fb; a.H = p; p += lay.H * Fb;
+        a.S = p; p += lay.S * Fb; a.ST = p; p += lay.ST * Fb; a.Kt = p; p += lay.Kt * Fb; a.T = p; p += lay.T * Fb;
+        a.Pbar = p; p += lay.Pbar * Fb; a.xbar = p; p += lay.xbar * Fb;
+        double *xnew = p; p += lay.xnew * Fb;
+        a.zhat = p; a.wm = wm; a.wc = wc;
+        a.dt = params_h[0]; a.half_r = params_h[1] / 2.0; a.r_over_l = params_h[1] / params_h[2]; a.cscale = c;
+        a.var_dist = params_h[6]; a.var_angle = params_h[7];
+        for (int i = 0; i < 9; ++i) a.Q[i] = params_h[8 + i];
+        AugRun run{h, st, Fb};
+        const long long nn = (long long)n * n, mn = (long long)m * n;
+        const dim3 gew(Fb < 64 ? ew : 8, Fb);
+        // sigma points of (x, P)
+        LSLAM_LAUNCH(aug_scale_upper_kernel, gew, 256, 0, st, (const double *)a.P, nn, a.U, nn, n, c, (const int32_t *)a.status);
+        run.chol(a.U, nn, n, a.status, LSLAM_UKF_ST_SIGMA);
+        LSLAM_LAUNCH(aug_sigmas_kernel, gew, 256, 0, st, a, (const double *)a.x);
+        h->launches += 2;
+        if (pred) {
+            LSLAM_LAUNCH(aug_fx_kernel, dim3((m + 127) / 128, Fb), 128, 0, st, a);
+            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3(Fb), 256, 0, st, a, (const double *)a.X, n, 0, 0, a.xbar, a.Y);
+            LSLAM_LAUNCH(aug_fill_noise_kernel, gew, 256, 0, st, a, a.Pbar, n, 0);
+            h->launches += 3;
+            run.gemm(a.Y, mn, n, a.Y, mn, n, a.Pbar, nn, n, n, n, m, wc, 1.0, 1.0, a.status, 0);
+            if (upd && (flags & LSLAM_UKF_REDRAW)) {
+                LSLAM_LAUNCH(aug_scale_upper_kernel, gew, 256, 0, st, (const double *)a.Pbar, nn, a.U, nn, n, c, (const int32_t *)a.status);
+                run.chol(a.U, nn, n, a.status, LSLAM_UKF_ST_REDRAW);
+                LSLAM_LAUNCH(aug_sigmas_kernel, gew, 256, 0, st, a, (const double *)a.xbar);
+                LSLAM_LAUNCH(aug_mean_resid_kernel, dim3(Fb), 256, 0, st, a, (const double *)a.X, n, 0, 1, a.xbar, a.Y);
+                h->launches += 3;
+            }
+        } else {
+            LSLAM_CUDA_TRY(h, cudaMemcpyAsync(a.xbar, a.x, sizeof(double) * (size_t)Fb * n, cudaMemcpyDeviceToDevice, st));
+            LSLAM_CUDA_TRY(h, cudaMemcpyAsync(a.Pbar, a.P, sizeof(double) * (size_t)Fb * nn, cudaMemcpyDeviceToDevice, st));
+            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3(Fb), 256, 0, st, a, (const double *)a.X, n, 0, 1, a.xbar, a.Y);
+            h->launches++;
+        }
+        const double *xres = a.xbar;
+        if (upd) {
+            const long long zz = (long long)dz * dz, zn = (long long)dz * n, mz = (long long)m * dz;
+            LSLAM_LAUNCH(aug_hx_kernel, gew, 256, 0, st, a);
+            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3(Fb), 256, 0, st, a, (const double *)a.H, dz, 1, 0, a.zhat, a.H);
+            LSLAM_LAUNCH(aug_fill_noise_kernel, gew, 256, 0, st, a, a.S, dz, 1);
+            h->launches += 3;
+            run.gemm(a.H, mz, dz, a.H, mz, dz, a.S, zz, dz, dz, dz, m, wc, 1.0, 1.0, a.status, 0);          // S
+            run.gemm(a.H, mz, dz, a.Y, mn, n, a.Kt, zn, n, dz, n, m, wc, 1.0, 0.0, a.status, 0);            // Pzx
+            // Cholesky of S into U (dz x dz), its transpose into ST
+            LSLAM_LAUNCH(aug_scale_upper_kernel, gew, 256, 0, st, (const double *)a.S, zz, a.U, nn, dz, 1.0, (const int32_t *)a.status);
+            h->launches++;
+            // a.U is laid out with stride n*n per filter; keep that stride for the dz x dz factor
+            run.chol(a.U, nn, dz, a.status, LSLAM_UKF_ST_S);
+            // (transpose kernel works on dense [F, dim, dim]; the factor lives at stride nn, so transpose per stride)
+            LSLAM_LAUNCH(aug_transpose_kernel, gew, 256, 0, st, (const double *)a.U, nn, a.ST, zz, dz, (const int32_t *)a.status);
+            h->launches++;
+            for (int jb = 0; jb < dz; jb += 32) {                 // U^T W = Pzx
+                const int nb = dz - jb < 32 ? dz - jb : 32;
+                if (jb > 0)
+                    run.gemm(a.U + jb, nn, dz, a.Kt, zn, n, a.Kt + (size_t)jb * n, zn, n, nb, n, jb, nullptr, -1.0, 1.0, a.status, 0);
+                LSLAM_LAUNCH(aug_trsm_block_kernel, dim3((n + 255) / 256, Fb), 256, kAugBlockSmem, st, (const double *)a.U, nn, dz,
+                             a.Kt, zn, n, n, jb, nb, 0, (const int32_t *)a.status);
+                h->launches++;
+            }
+            for (int jb = ((dz - 1) / 32) * 32; jb >= 0; jb -= 32) {   // U K^T = W
+                const int nb = dz - jb < 32 ? dz - jb : 32;
+                const int below = dz - jb - nb;
+                if (below > 0)
+                    run.gemm(a.ST + (size_t)(jb + nb) * dz + jb, zz, dz, a.Kt + (size_t)(jb + nb) * n, zn, n,
+                             a.Kt + (size_t)jb * n, zn, n, nb, n, below, nullptr, -1.0, 1.0, a.status, 0);
+                LSLAM_LAUNCH(aug_trsm_block_kernel, dim3((n + 255) / 256, Fb), 256, kAugBlockSmem, st, (const double *)a.U, nn, dz,
+                             a.Kt, zn, n, n, jb, nb, 1, (const int32_t *)a.status);
+                h->launches++;
+            }
+            LSLAM_LAUNCH(aug_update_x_kernel, dim3(Fb), 256, sizeof(double) * (size_t)dz, st, a, xnew);
+            h->launches++;
+            run.gemm(a.S, zz, dz, a.Kt, zn, n, a.T, zn, n, dz, n, dz, nullptr, 1.0, 0.0, a.status, 0);       // T = S K^T
+            run.gemm(a.Kt, zn, n, a.T, zn, n, a.Pbar, nn, n, n, n, dz, nullptr, -1.0, 1.0, a.status, 0);    // P = Pbar - K T
+            xres = xnew;
+        }
+        LSLAM_LAUNCH(aug_commit_kernel, gew, 256, 0, st, a, xres, (const double *)a.Pbar);
+        h->launches++;
+        LSLAM_CUDA_TRY(h, cudaGetLastError());
+    }
+    return LSLAM_OK;
 }
 
 // ---- input stage, synthetic scans, fp64 probe --------------------------------------------

@@ -341,3 +341,29 @@ def step_literal(x, P, u, z, lm_pos, dt=DT, alpha=1e-4, beta=2.0, kappa=0.0, Q=N
     if do_update and nl > 0:
         f.update(np.asarray(z, dtype=np.float64), landmarks=[_Pos(p[0], p[1]) for p in lm_pos])
     return f.x, f.P
+
+
+def step_literal_augmented(x, P, u, z, dt=DT, alpha=1e-4, beta=2.0, kappa=0.0, Q3=None, var_dist=VAR_DIST,
+                           var_angle=VAR_ANGLE, redraw=True, do_predict=True, do_update=True):
+    """One predict(u=u) + update(z) of an augmented filter (BASELINE.json configs[3])
+    with the literal engine: x [3 + 2L] = pose + landmark positions, z [2L], hx reads the landmarks from
+    the state (transfer_function_augmented), Q = the pose's 3x3 on the top-left block, zero elsewhere.
+    Returns (x, P).  parity unpinned: the reference never builds this filter (it is a localiser)."""
+    x = np.array(x, dtype=np.float64)
+    n = x.shape[0]
+    nl = (n - 3) // 2
+    pts = MerweScaledSigmaPoints(n, alpha, beta, kappa)
+    f = UKF(n, 2 * nl, dt, transfer_function_augmented, transition_function, pts, x_mean_fn=state_mean,
+            z_mean_fn=z_mean, residual_x=residual_x, residual_z=residual_h, redraw=redraw)
+    f.x = x
+    f.P = np.array(P, dtype=np.float64)
+    f.Q = np.zeros((n, n))
+    f.Q[:3, :3] = np.eye(3) * 0.001 if Q3 is None else np.array(Q3, dtype=np.float64)
+    f.R = np.diag([var_dist, var_angle] * nl)
+    if do_predict:
+        f.predict(u=np.asarray(u, dtype=np.float64))
+    else:
+        f.sigmas_f = pts.sigma_points(f.x, f.P)
+    if do_update:
+        f.update(np.asarray(z, dtype=np.float64).reshape(-1))
+    return f.x, f.P

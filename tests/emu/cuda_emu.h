@@ -264,17 +264,19 @@ namespace emu {
 
 template <class K, class... A>
 inline void launch(K kernel, dim3 grid, dim3 block, size_t smem, A... args) {
-    if (block.x % 32 != 0 || block.y != 1 || block.z != 1 || grid.y != 1 || grid.z != 1) {
-        std::fprintf(stderr, "cuda_emu: only 1-D grids/blocks with blockDim.x %% 32 == 0\n");
+    if (block.x % 32 != 0 || block.y != 1 || block.z != 1) {
+        std::fprintf(stderr, "cuda_emu: only 1-D blocks with blockDim.x %% 32 == 0\n");
         std::abort();
     }
+    for (unsigned bz = 0; bz < grid.z; ++bz)
+    for (unsigned by = 0; by < grid.y; ++by)
     for (unsigned b = 0; b < grid.x; ++b) {
         BlockCtx ctx(block.x, smem);
         std::vector<std::thread> th;
         th.reserve(block.x);
         for (unsigned t = 0; t < block.x; ++t) {
-            th.emplace_back([&, t, b] {
-                threadIdx = dim3(t); blockIdx = dim3(b); blockDim = block; gridDim = grid;
+            th.emplace_back([&, t, b, by, bz] {
+                threadIdx = dim3(t); blockIdx = dim3(b, by, bz); blockDim = block; gridDim = grid;
                 ts.blk = &ctx; ts.warp = ctx.warps[t / 32].get(); ts.lane = (int)(t % 32);
                 kernel(args...);
             });

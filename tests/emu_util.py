@@ -113,6 +113,25 @@ def emu_ukf_step(x, P, u, z, lm_pos, lm_valid=None, valid_min=1, zmode=0, params
     return x, P, status
 
 
+def emu_ukf_aug_step(x, P, u, z, params=None, flags=7, workspace_filters=None, handle=None):
+    """lslam_ukf_aug_step on the emulated library.  x [F, n], P [F, n, n], z [F, L, 2]; returns copies
+    (x_new, P_new, status).  workspace_filters < F exercises the batching."""
+    from lidar_slam_b200 import batch
+    h = handle or emu_handle()
+    x = np.array(x, dtype=np.float64, order="C")
+    P = np.array(P, dtype=np.float64, order="C")
+    F, n = x.shape
+    L = (n - 3) // 2
+    u = None if u is None else np.ascontiguousarray(u, dtype=np.float64)
+    z = None if z is None else np.ascontiguousarray(z, dtype=np.float64)
+    status = np.full(F, -99, np.int32)
+    params = batch.Engine.ukf_params() if params is None else list(params)
+    nbytes = h.ukf_aug_workspace_bytes(L, workspace_filters or F)
+    ws = np.zeros(nbytes, np.uint8)
+    h.ukf_aug_step(ptr(x), ptr(P), ptr(u), ptr(z), F, L, params, flags, ptr(status), ptr(ws), nbytes)
+    return x, P, status
+
+
 def emu_ukf_step_gather(x, P, u, z, lm_pos, lm_valid, ids, first_record, peer_state, peer_ids, multicast=False,
                         valid_min=0, zmode=1, params=None, flags=7, handle=None):
     """lslam_ukf_step_gather on the emulated library: peer_state / peer_ids are lists of NumPy arrays

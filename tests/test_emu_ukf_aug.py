@@ -1,0 +1,71 @@
+"""The augmented-state UKF kernels (lidar_slam_b200/csrc/ukf_aug.cuh behind lslam_ukf_aug_step), compiled
+for the CPU with tests/emu/cuda_emu.h, against the literal filterpy restatement
+(oracle/ukf.py step_literal_augmented).  Small state sizes: the emulator runs one OS thread per CUDA
+thread.  The -m gpu twin (tests/test_gpu_ukf_aug.py) runs L up to 200."""
+import numpy as np
+import pytest
+
+from tests import emu_util as eu, ukf_aug_util as au
+from lidar_slam_b200 import batch
+
+
+@pytest.mark.parametrize("L,F,flags", [(4, 3, 7), (4, 2, 3), (3, 2, 1), (3, 2, 2), (18, 1, 7)],
+                         ids=["L4", "L4-noredraw", "L3-predict", "L3-update", "L18-two-panels"])
+def test_aug_step_matches_literal(L, F, flags):
+    x, P, u, z = au.aug_case(F, L, seed=10 + L)
+    want = au.oracle_aug(x, P, u, z, flags)
+    cond = au.oracle_conditioning(x, P, u, z, want, flags)
+    xg, Pg, st = eu.emu_ukf_aug_step(x, P, u, z, flags=flags)
+    assert not st.any()
+    au.assert_aug_close(want, (xg, Pg), "emu L=%d flags=%d" % (L, flags), cond=cond)
+    assert np.abs(want[1] - P).max() > 1e-3          # the step did something
+
+
+def test_aug_strict_tolerance_with_wider_sigma_spread():
+    """alpha = 0.05 instead of the reference's 1e-4: the central weight is ~ -400, the filter is well
+    conditioned and the plain 1e-5 bound holds without the conditioning term."""
+    L, F = 4, 2
+    x, P, u, z = au.aug_case(F, L, seed=3)
+    params = batch.Engine.ukf_params(alpha=0.05)
+    want = au.oracle_aug(x, P, u, z, 7, alpha=0.05)
+    xg, Pg, st = eu.emu_ukf_aug_step(x, P, u, z, params=params)
+    assert not st.any()
+    ex, eP = au.assert_aug_close(want, (xg, Pg), "alpha 0.05")
+    assert ex < 1e-8 and eP < 1e-8
+
+
+def test_aug_batching_and_failed_filters_keep_state():
+    """Workspace for one filter at a time gives the same bits as all at once; a filter whose P is not
+    positive definite reports LSLAM_UKF_ST_SIGMA and keeps (x, P), its neighbours are unaffected."""
+    L, F = 3, 3
+    x, P, u, z = au.aug_case(F, L, seed=5)
+    P[1, 4, 4] = -1.0
+    a = eu.emu_ukf_aug_step(x, P, u, z)
+    b = eu.emu_ukf_aug_step(x, P, u, z, workspace_filters=1)
+    for p, q in zip(a, b):
+        assert np.array_equal(p, q)
+    assert a[2].tolist() == [0, 1, 0]
+    assert np.array_equal(a[0][1], x[1]) and np.array_equal(a[1][1], P[1])
+    with pytest.raises(np.linalg.LinAlgError):
+        au.oracle_aug(x[1:2], P[1:2], u[1:2], z[1:2])
+    keep = [0, 2]
+    want = au.oracle_aug(x[keep], P[keep], u[keep], z[keep])
+    cond = au.oracle_conditioning(x[keep], P[keep], u[keep], z[keep], want)
+    au.assert_aug_close(want, (a[0][keep], a[1][keep]), "neighbours", cond=cond)
+
+
+def test_aug_bad_arguments():
+    h = eu.emu_handle()
+    from lidar_slam_b200._lib import LslamError
+    x, P, u, z = au.aug_case(1, 2, seed=1)
+    st = np.zeros(1, np.int32)
+    ws = np.zeros(h.ukf_aug_workspace_bytes(2, 1), np.uint8)
+    par = batch.Engine.ukf_params()
+    with pytest.raises(LslamError):      # workspace too small for one filter
+        h.ukf_aug_step(eu.ptr(x), eu.ptr(P), eu.ptr(u), eu.ptr(z), 1, 2, par, 7, eu.ptr(st), eu.ptr(ws), 1024)
+    with pytest.raises(LslamError):      # update without z
+        h.ukf_aug_step(eu.ptr(x), eu.ptr(P), eu.ptr(u), None, 1, 2, par, 7, eu.ptr(st), eu.ptr(ws), ws.size)
+    with pytest.raises(LslamError):      # L = 0
+        h.ukf_aug_step(eu.ptr(x), eu.ptr(P), eu.ptr(u), eu.ptr(z), 1, 0, par, 7, eu.ptr(st), eu.ptr(ws), ws.size)
+    with pytest.raises(LslamError):
+        h.ukf_aug_workspace_bytes(0, 1)

@@ -1,0 +1,84 @@
+"""GPU parity of the augmented-state UKF (csrc/ukf_aug.cuh through lslam_ukf_aug_step) against the
+literal filterpy restatement (oracle/ukf.py step_literal_augmented) up to BASELINE.json configs[3]'s
+n = 403 (L = 200).  Bar: 1e-5 relative; where the filter itself is ill-conditioned (alpha = 1e-4, large
+n) the bar is 8 x the oracle's own sensitivity to a one-ulp change of its input (tests/ukf_aug_util.py)."""
+import numpy as np
+import pytest
+
+from tests import ukf_aug_util as au
+
+pytestmark = pytest.mark.gpu
+
+
+def run_gpu(eng, x, P, u, z, flags=None, params=None, workspace_filters=None):
+    import torch
+    dev = eng.device
+    F, n = x.shape
+    L = (n - 3) // 2
+    st = eng.alloc_ukf_aug(F, L, workspace_filters=workspace_filters)
+    st["x"] = torch.from_numpy(x).to(dev)
+    st["P"] = torch.from_numpy(P).to(dev)
+    if params is not None:
+        st["params"] = list(params)
+    eng.ukf_aug_step(st, torch.from_numpy(z).to(dev), u=torch.from_numpy(u).to(dev), flags=flags)
+    torch.cuda.synchronize()
+    return st["x"].cpu().numpy(), st["P"].cpu().numpy(), st["status"].cpu().numpy()
+
+
+@pytest.mark.parametrize("L,F", [(1, 40), (5, 64), (16, 16), (40, 6), (200, 2)])
+def test_aug_step_matches_literal(gpu_engine, L, F):
+    x, P, u, z = au.aug_case(F, L, seed=L)
+    want = au.oracle_aug(x, P, u, z)
+    cond = au.oracle_conditioning(x, P, u, z, want)
+    xg, Pg, st = run_gpu(gpu_engine, x, P, u, z)
+    assert not st.any()
+    ex, eP = au.assert_aug_close(want, (xg, Pg), "L=%d" % L, cond=cond)
+    print("L=%d err x %.2e P %.2e (oracle one-ulp sensitivity %.2e %.2e)" % (L, ex, eP, cond[0], cond[1]))
+
+
+@pytest.mark.parametrize("flags", [1, 2, 3])
+def test_aug_halves(gpu_engine, flags):
+    x, P, u, z = au.aug_case(8, 20, seed=flags)
+    want = au.oracle_aug(x, P, u, z, flags)
+    cond = au.oracle_conditioning(x, P, u, z, want, flags)
+    xg, Pg, st = run_gpu(gpu_engine, x, P, u, z, flags=flags)
+    assert not st.any()
+    au.assert_aug_close(want, (xg, Pg), "flags %d" % flags, cond=cond)
+
+
+def test_aug_strict_tolerance_with_wider_sigma_spread(gpu_engine):
+    """alpha = 0.05: well conditioned, plain 1e-5 (in fact ~1e-9) without the conditioning term, n = 403."""
+    from lidar_slam_b200 import batch
+    x, P, u, z = au.aug_case(1, 200, seed=9)
+    want = au.oracle_aug(x, P, u, z, 7, alpha=0.05)
+    xg, Pg, st = run_gpu(gpu_engine, x, P, u, z, params=batch.Engine.ukf_params(alpha=0.05))
+    assert not st.any()
+    ex, eP = au.assert_aug_close(want, (xg, Pg), "alpha 0.05 L=200")
+    assert ex < 1e-7 and eP < 1e-7
+
+
+def test_aug_batching_failures_and_repeat_steps(gpu_engine):
+    import torch
+    L, F = 12, 37
+    x, P, u, z = au.aug_case(F, L, seed=6)
+    P[5, 7, 7] = -2.0
+    a = run_gpu(gpu_engine, x, P, u, z)
+    b = run_gpu(gpu_engine, x, P, u, z, workspace_filters=4)        # 10 batches, the last one short
+    for p, q in zip(a, b):
+        assert np.array_equal(p, q)
+    assert a[2][5] == 1 and a[2].sum() == 1
+    assert np.array_equal(a[0][5], x[5]) and np.array_equal(a[1][5], P[5])
+    # posterior stays symmetric positive definite over repeated steps
+    eng = gpu_engine
+    st = eng.alloc_ukf_aug(4, 30)
+    xs, Ps, us, zs = au.aug_case(4, 30, seed=8)
+    st["x"] = torch.from_numpy(xs).to(eng.device)
+    st["P"] = torch.from_numpy(Ps).to(eng.device)
+    zt = torch.from_numpy(zs).to(eng.device)
+    for _ in range(5):
+        eng.ukf_aug_step(st, zt, u=torch.from_numpy(us).to(eng.device))
+    torch.cuda.synchronize()
+    assert not st["status"].any().item()
+    Pn = st["P"].cpu().numpy()
+    assert np.abs(Pn - Pn.transpose(0, 2, 1)).max() <= 1e-6 * np.abs(Pn).max()
+    assert np.all(np.linalg.eigvalsh((Pn + Pn.transpose(0, 2, 1)) / 2) > 0)

@@ -110,3 +110,35 @@ def test_no_redraw_variant(cport):
                                   alpha=1e-2, redraw=False)
         uu.assert_ukf_close((wx[None], wP[None], got[2][f:f + 1]), (got[0][f:f + 1], got[1][f:f + 1], got[2][f:f + 1]),
                             "no-redraw", rtol=1e-8)
+
+
+# ---- augmented state (BASELINE.json configs[3]; parity unpinned: the reference never builds it) ----
+@pytest.mark.parametrize("alpha,tol", [(1e-4, 1e-4), (1e-2, 1e-6)])
+def test_augmented_filter_reduces_to_localiser(alpha, tol):
+    """With (almost) certain landmarks in the state the augmented filter is the reference's n = 3
+    localiser measured against those landmarks: same pose posterior, landmarks do not move."""
+    from tests import ukf_aug_util as au
+    L = 4
+    x, P, u, z = au.aug_case(1, L, seed=2)
+    x, u, z = x[0], u[0], z[0]
+    P = np.diag([0.1, 0.1, 0.05] + [1e-10] * (2 * L))
+    xa, Pa = ukf.step_literal_augmented(x, P, u, z, alpha=alpha)
+    x3, P3 = ukf.step_literal(x[:3], P[:3, :3], u, z.reshape(-1), x[3:].reshape(L, 2), alpha=alpha)
+    assert np.abs(xa[:3] - x3).max() <= tol * 10
+    assert np.abs(Pa[:3, :3] - P3).max() <= tol * np.abs(P3).max()
+    assert np.abs(xa[3:] - x[3:]).max() <= tol
+
+
+def test_augmented_update_shrinks_landmark_covariance_and_keeps_symmetry():
+    from tests import ukf_aug_util as au
+    x, P, u, z = au.aug_case(1, 6, seed=4)
+    xa, Pa = ukf.step_literal_augmented(x[0], P[0], u[0], z[0], alpha=1e-2)
+    assert np.abs(Pa - Pa.T).max() <= 1e-9 * np.abs(Pa).max()
+    assert np.all(np.linalg.eigvalsh((Pa + Pa.T) / 2) > 0)
+    assert np.all(np.diag(Pa)[3:] < np.diag(P[0])[3:])          # every landmark was measured
+    # predict alone moves the pose by dt * B(theta) u and leaves the landmarks
+    xp, Pp = ukf.step_literal_augmented(x[0], P[0], u[0], z[0], alpha=1e-2, do_update=False)
+    want = ukf.transition_function(x[0], ukf.DT, u[0])
+    assert np.allclose(xp[2:], want[2:], rtol=0, atol=1e-6)
+    assert np.allclose(xp[:2], want[:2], rtol=0, atol=0.05)         # E[cos] over the heading spread: second order
+    assert np.allclose(Pp[3:, 3:], P[0][3:, 3:], rtol=1e-6, atol=1e-9)
