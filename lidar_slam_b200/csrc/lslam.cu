@@ -464,14 +464,19 @@ constexpr int kAugMaxBatch = 32768;
 struct AugRun {
     Handle *h; cudaStream_t st; int F;
     int gemm(const double *A, long long sA, int lda, const double *B, long long sB, int ldb, double *C, long long sC, int ldc,
-             int M, int N, int K, const double *w, double alpha, double beta, const int32_t *skip, int upper)
+             int M, int N, int K, double w0, double alpha, double beta, const int32_t *skip, int upper)
     {
         if (M <= 0 || N <= 0) return LSLAM_OK;
         AugGemm g;
-        g.A = A; g.B = B; g.w = w; g.C = C; g.sA = sA; g.sB = sB; g.sC = sC; g.M = M; g.N = N; g.K = K;
-        g.lda = lda; g.ldb = ldb; g.ldc = ldc; g.alpha = alpha; g.beta = beta; g.skip = skip; g.upper = upper;
-        dim3 grid((N + kAugTile - 1) / kAugTile, (M + kAugTile - 1) / kAugTile, F);
-        LSLAM_LAUNCH(aug_gemm_tn_kernel, grid, 256, kAugGemmSmem, st, g);
+        g.A = A; g.B = B; g.C = C; g.sA = sA; g.sB = sB; g.sC = sC; g.M = M; g.N = N; g.K = K;
+        g.lda = lda; g.ldb = ldb; g.ldc = ldc; g.alpha = alpha; g.beta = beta; g.w0 = w0; g.skip = skip; g.upper = upper;
+        if (M <= 32) {
+            dim3 grid((N + kAugTile - 1) / kAugTile, 1, F);
+            LSLAM_LAUNCH(aug_gemm_tn_kernel<32>, grid, 256, aug_gemm_smem(32), st, g);
+        } else {
+            dim3 grid((N + kAugTile - 1) / kAugTile, (M + 63) / 64, F);
+            LSLAM_LAUNCH(aug_gemm_tn_kernel<64>, grid, 256, aug_gemm_smem(64), st, g);
+        }
         h->launches++;
         return LSLAM_OK;
     }
@@ -486,7 +491,7 @@ struct AugRun {
             if (rest > 0) {
                 const double *panel = A + (size_t)jb * dim + jb + nb;
                 gemm(panel, sA, dim, panel, sA, dim, A + (size_t)(jb + nb) * dim + jb + nb, sA, dim, rest, rest, nb,
-                     nullptr, -1.0, 1.0, status, 1);
+                     0.0, -1.0, 1.0, status, 1);
             }
         }
         return LSLAM_OK;
@@ -531,7 +536,8 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
     double *ws = (double *)workspace;
     double *wm = ws, *wc = ws + m;
     ws += 2 * m;
-    LSLAM_LAUNCH(aug_weights_kernel, dim3((m + 255) / 256), 256, 0, st, wm, wc, m, 0.5 / c, lam / c, lam / c + (1 - alpha * alpha + beta));
+    const double wi = 0.5 / c, wc0 = lam / c + (1 - alpha * alpha + beta);
+    LSLAM_LAUNCH(aug_weights_kernel, dim3((m + 255) / 256), 256, 0, st, wm, wc, m, wi, lam / c, wc0);
     h->launches++;
     LSLAM_CUDA_TRY(h, cudaMemsetAsync(status, 0, sizeof(int32_t) * (size_t)F, st));
     const unsigned ew = (unsigned)(2 * h->sms);                 // elementwise grids: x-blocks per filter
@@ -561,32 +567,34 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
         h->launches += 2;
         if (pred) {
             LSLAM_LAUNCH(aug_fx_kernel, dim3((m + 127) / 128, Fb), 128, 0, st, a);
-            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3(Fb), 256, 0, st, a, (const double *)a.X, n, 0, 0, a.xbar, a.Y);
+            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3((n + 31) / 32, Fb), 256, kAugMeanSmem, st, a, (const double *)a.X, n, 0, 0, a.xbar, a.Y);
             LSLAM_LAUNCH(aug_fill_noise_kernel, gew, 256, 0, st, a, a.Pbar, n, 0);
             h->launches += 3;
-            run.gemm(a.Y, mn, n, a.Y, mn, n, a.Pbar, nn, n, n, n, m, wc, 1.0, 1.0, a.status, 0);
+            run.gemm(a.Y, mn, n, a.Y, mn, n, a.Pbar, nn, n, n, n, m, wc0 - wi, wi, 1.0, a.status, 1);
             if (upd && (flags & LSLAM_UKF_REDRAW)) {
                 LSLAM_LAUNCH(aug_scale_upper_kernel, gew, 256, 0, st, (const double *)a.Pbar, nn, a.U, nn, n, c, (const int32_t *)a.status);
                 run.chol(a.U, nn, n, a.status, LSLAM_UKF_ST_REDRAW);
                 LSLAM_LAUNCH(aug_sigmas_kernel, gew, 256, 0, st, a, (const double *)a.xbar);
-                LSLAM_LAUNCH(aug_mean_resid_kernel, dim3(Fb), 256, 0, st, a, (const double *)a.X, n, 0, 1, a.xbar, a.Y);
+                LSLAM_LAUNCH(aug_mean_resid_kernel, dim3((n + 31) / 32, Fb), 256, kAugMeanSmem, st, a, (const double *)a.X, n, 0, 1, a.xbar, a.Y);
                 h->launches += 3;
             }
         } else {
             LSLAM_CUDA_TRY(h, cudaMemcpyAsync(a.xbar, a.x, sizeof(double) * (size_t)Fb * n, cudaMemcpyDeviceToDevice, st));
             LSLAM_CUDA_TRY(h, cudaMemcpyAsync(a.Pbar, a.P, sizeof(double) * (size_t)Fb * nn, cudaMemcpyDeviceToDevice, st));
-            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3(Fb), 256, 0, st, a, (const double *)a.X, n, 0, 1, a.xbar, a.Y);
+            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3((n + 31) / 32, Fb), 256, kAugMeanSmem, st, a, (const double *)a.X, n, 0, 1, a.xbar, a.Y);
             h->launches++;
         }
         const double *xres = a.xbar;
         if (upd) {
             const long long zz = (long long)dz * dz, zn = (long long)dz * n, mz = (long long)m * dz;
             LSLAM_LAUNCH(aug_hx_kernel, gew, 256, 0, st, a);
-            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3(Fb), 256, 0, st, a, (const double *)a.H, dz, 1, 0, a.zhat, a.H);
+            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3((dz + 31) / 32, Fb), 256, kAugMeanSmem, st, a, (const double *)a.H, dz, 1, 0, a.zhat, a.H);
             LSLAM_LAUNCH(aug_fill_noise_kernel, gew, 256, 0, st, a, a.S, dz, 1);
             h->launches += 3;
-            run.gemm(a.H, mz, dz, a.H, mz, dz, a.S, zz, dz, dz, dz, m, wc, 1.0, 1.0, a.status, 0);          // S
-            run.gemm(a.H, mz, dz, a.Y, mn, n, a.Kt, zn, n, dz, n, m, wc, 1.0, 0.0, a.status, 0);            // Pzx
+            run.gemm(a.H, mz, dz, a.H, mz, dz, a.S, zz, dz, dz, dz, m, wc0 - wi, wi, 1.0, a.status, 1);   // S (upper)
+            run.gemm(a.H, mz, dz, a.Y, mn, n, a.Kt, zn, n, dz, n, m, wc0 - wi, wi, 0.0, a.status, 0);    // Pzx
+            LSLAM_LAUNCH(aug_mirror_kernel, gew, 256, 0, st, a.S, zz, dz, (const int32_t *)a.status);
+            h->launches++;
             // Cholesky of S into U (dz x dz), its transpose into ST
             LSLAM_LAUNCH(aug_scale_upper_kernel, gew, 256, 0, st, (const double *)a.S, zz, a.U, nn, dz, 1.0, (const int32_t *)a.status);
             h->launches++;
@@ -598,7 +606,7 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
             for (int jb = 0; jb < dz; jb += 32) {                 // U^T W = Pzx
                 const int nb = dz - jb < 32 ? dz - jb : 32;
                 if (jb > 0)
-                    run.gemm(a.U + jb, nn, dz, a.Kt, zn, n, a.Kt + (size_t)jb * n, zn, n, nb, n, jb, nullptr, -1.0, 1.0, a.status, 0);
+                    run.gemm(a.U + jb, nn, dz, a.Kt, zn, n, a.Kt + (size_t)jb * n, zn, n, nb, n, jb, 0.0, -1.0, 1.0, a.status, 0);
                 LSLAM_LAUNCH(aug_trsm_block_kernel, dim3((n + 255) / 256, Fb), 256, kAugBlockSmem, st, (const double *)a.U, nn, dz,
                              a.Kt, zn, n, n, jb, nb, 0, (const int32_t *)a.status);
                 h->launches++;
@@ -608,15 +616,15 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
                 const int below = dz - jb - nb;
                 if (below > 0)
                     run.gemm(a.ST + (size_t)(jb + nb) * dz + jb, zz, dz, a.Kt + (size_t)(jb + nb) * n, zn, n,
-                             a.Kt + (size_t)jb * n, zn, n, nb, n, below, nullptr, -1.0, 1.0, a.status, 0);
+                             a.Kt + (size_t)jb * n, zn, n, nb, n, below, 0.0, -1.0, 1.0, a.status, 0);
                 LSLAM_LAUNCH(aug_trsm_block_kernel, dim3((n + 255) / 256, Fb), 256, kAugBlockSmem, st, (const double *)a.U, nn, dz,
                              a.Kt, zn, n, n, jb, nb, 1, (const int32_t *)a.status);
                 h->launches++;
             }
             LSLAM_LAUNCH(aug_update_x_kernel, dim3(Fb), 256, sizeof(double) * (size_t)dz, st, a, xnew);
             h->launches++;
-            run.gemm(a.S, zz, dz, a.Kt, zn, n, a.T, zn, n, dz, n, dz, nullptr, 1.0, 0.0, a.status, 0);       // T = S K^T
-            run.gemm(a.Kt, zn, n, a.T, zn, n, a.Pbar, nn, n, n, n, dz, nullptr, -1.0, 1.0, a.status, 0);    // P = Pbar - K T
+            run.gemm(a.S, zz, dz, a.Kt, zn, n, a.T, zn, n, dz, n, dz, 0.0, 1.0, 0.0, a.status, 0);       // T = S K^T
+            run.gemm(a.Kt, zn, n, a.T, zn, n, a.Pbar, nn, n, n, n, dz, 0.0, -1.0, 1.0, a.status, 1);    // P = Pbar - K T (upper; commit mirrors)
             xres = xnew;
         }
         LSLAM_LAUNCH(aug_commit_kernel, gew, 256, 0, st, a, xres, (const double *)a.Pbar);

@@ -28,78 +28,120 @@
 namespace lslam {
 
 // ---- batched TN GEMM -------------------------------------------------------------------------
-// C (M x N, ldc) = beta * C + alpha * sum_{k < K} w[k] * A[k, i] * B[k, j];  A: K x M (lda), B: K x N (ldb).
-// grid = (ceil(N/64), ceil(M/64), batch); 256 threads, 4 x 4 outputs per thread; tiles staged in shared
-// memory k-major so that the global loads are contiguous along i / j.
+// C (M x N, ldc) = beta * C + alpha * sum_{k < K} A[k, i] * B[k, j] + w0 * A[0, i] * B[0, j]
+// A: K x M (lda), B: K x N (ldb), both k-major.  The w0 term carries the central sigma point's weight:
+// sum_k Wc[k] a_k b_k = wi * sum_k a_k b_k + (Wc[0] - wi) a_0 b_0 (Merwe weights are equal for k >= 1).
+// grid = (ceil(N/64), ceil(M/TM), batch); 256 threads as 16 x 16, (TM/16) x 4 outputs per thread, rows
+// {2ty, 2ty+1 (+32)} and columns {2tx, 2tx+1, 32+2tx, 33+2tx} so that each operand pair is one 16-byte
+// shared-memory load.  Tiles of 16 k-rows go global -> shared with 8-byte cp.async (LDGSTS; the row pitch
+// n = 403 is odd, so rows are only 8-byte aligned) through a 3-stage ring: the loads of tiles t+1, t+2
+// are in flight while tile t is multiplied.
 struct AugGemm {
-    const double *A, *B, *w;        // w may be null (all ones); w is shared by the batch
+    const double *A, *B;
     double *C;
     long long sA, sB, sC;           // element strides between consecutive filters
     int M, N, K, lda, ldb, ldc;
-    double alpha, beta;
+    double alpha, beta, w0;
     const int32_t *skip;            // per-filter status: non-zero -> leave C alone (may be null)
     int upper;                      // 1: C is square and only its upper triangle (j >= i) is computed / stored
 };
 
-constexpr int kAugTile = 64, kAugBK = 16, kAugLd = kAugTile + 1;
-constexpr size_t kAugGemmSmem = 2 * kAugBK * kAugLd * sizeof(double);
+constexpr int kAugTile = 64, kAugBK = 16, kAugStages = 3;
+constexpr size_t aug_gemm_smem(int TM) { return (size_t)kAugStages * kAugBK * (TM + kAugTile) * sizeof(double); }
 constexpr size_t kAugBlockSmem = (32 * 33 + 2) * sizeof(double);
+constexpr size_t kAugMeanSmem = (8 * 32 * 2 + 32) * sizeof(double);
 
+#ifndef LSLAM_EMU
+__device__ __forceinline__ void cp_async8(double *dst_smem, const double *src, bool valid)
+{
+    const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
+    const int bytes = valid ? 8 : 0;               // src-size 0: nothing is read, the 8 bytes are zero-filled
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(d), "l"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+#else
+inline void cp_async8(double *dst, const double *src, bool valid) { *dst = valid ? *src : 0.0; }
+inline void cp_async_commit() {}
+template <int N> inline void cp_async_wait() {}
+#endif
+
+template <int TM>
 __global__ void __launch_bounds__(256) aug_gemm_tn_kernel(const AugGemm g)
 {
     LSLAM_SMEM_DECL;
-    double (*As)[kAugLd] = reinterpret_cast<double (*)[kAugLd]>(smem_raw);
-    double (*Bs)[kAugLd] = As + kAugBK;
+    constexpr int RA = TM / 32;                                       // row pairs per thread (2 or 1)
+    constexpr int STAGE = kAugBK * (TM + kAugTile);                   // doubles per stage: A tile then B tile
+    double *sm = reinterpret_cast<double *>(smem_raw);
     const int f = blockIdx.z;
     if (g.skip != nullptr && g.skip[f] != 0) return;
-    if (g.upper && blockIdx.y > blockIdx.x) return;
+    const int i0 = blockIdx.y * TM, j0 = blockIdx.x * kAugTile;
+    if (g.upper && i0 > j0 + kAugTile - 1) return;
     const double *A = g.A + (size_t)f * g.sA, *B = g.B + (size_t)f * g.sB;
     double *C = g.C + (size_t)f * g.sC;
-    const int i0 = blockIdx.y * kAugTile, j0 = blockIdx.x * kAugTile;
-    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;          // 16 x 16 threads, 4 x 4 each
-    double acc[4][4];
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const int ntiles = (g.K + kAugBK - 1) / kAugBK;
+    auto issue = [&](int t) {
+        if (t < ntiles) {
+            double *as = sm + (size_t)(t % kAugStages) * STAGE, *bs = as + kAugBK * TM;
+            const int k0 = t * kAugBK;
+            for (int e = threadIdx.x; e < kAugBK * TM; e += 256) {
+                const int kk = e / TM, c = e % TM;
+                const bool ok = k0 + kk < g.K && i0 + c < g.M;
+                cp_async8(as + e, ok ? A + (size_t)(k0 + kk) * g.lda + i0 + c : A, ok);
+            }
+            for (int e = threadIdx.x; e < kAugBK * kAugTile; e += 256) {
+                const int kk = e >> 6, c = e & 63;
+                const bool ok = k0 + kk < g.K && j0 + c < g.N;
+                cp_async8(bs + e, ok ? B + (size_t)(k0 + kk) * g.ldb + j0 + c : B, ok);
+            }
+        }
+        cp_async_commit();                                            // one group per tile slot, even when empty
+    };
+    double acc[2 * RA][4];
 #pragma unroll
-    for (int a = 0; a < 4; ++a)
+    for (int a = 0; a < 2 * RA; ++a)
 #pragma unroll
         for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
-    for (int k0 = 0; k0 < g.K; k0 += kAugBK) {
-        // 16 x 64 elements per tile, 256 threads: 4 elements each, contiguous along the row
-        for (int e = threadIdx.x; e < kAugBK * kAugTile; e += 256) {
-            const int kk = e >> 6, c = e & 63;
-            const int k = k0 + kk;
-            double av = 0.0, bv = 0.0;
-            if (k < g.K) {
-                const double wk = g.w ? g.w[k] : 1.0;
-                if (i0 + c < g.M) av = wk * A[(size_t)k * g.lda + i0 + c];
-                if (j0 + c < g.N) bv = B[(size_t)k * g.ldb + j0 + c];
-            }
-            As[kk][c] = av; Bs[kk][c] = bv;
-        }
-        __syncthreads();
+    issue(0);
+    issue(1);
+    for (int t = 0; t < ntiles; ++t) {
+        cp_async_wait<1>();                                           // tile t has landed (t+1 may be in flight)
+        __syncthreads();                                              // ... for every thread; tile t-1 fully read
+        issue(t + 2);                                                 // refills the stage tile t-1 used
+        const double *as = sm + (size_t)(t % kAugStages) * STAGE, *bs = as + kAugBK * TM;
 #pragma unroll
         for (int kk = 0; kk < kAugBK; ++kk) {
-            double a4[4], b4[4];
+            double2 av[RA], bv[2];
 #pragma unroll
-            for (int a = 0; a < 4; ++a) a4[a] = As[kk][ty + 16 * a];
+            for (int a = 0; a < RA; ++a) av[a] = *reinterpret_cast<const double2 *>(as + kk * TM + 32 * a + 2 * ty);
 #pragma unroll
-            for (int b = 0; b < 4; ++b) b4[b] = Bs[kk][tx + 16 * b];
+            for (int b = 0; b < 2; ++b) bv[b] = *reinterpret_cast<const double2 *>(bs + kk * kAugTile + 32 * b + 2 * tx);
 #pragma unroll
-            for (int a = 0; a < 4; ++a)
+            for (int a = 0; a < RA; ++a)
 #pragma unroll
-                for (int b = 0; b < 4; ++b) acc[a][b] = fma(a4[a], b4[b], acc[a][b]);
+                for (int b = 0; b < 2; ++b) {
+                    acc[2 * a][2 * b] = fma(av[a].x, bv[b].x, acc[2 * a][2 * b]);
+                    acc[2 * a][2 * b + 1] = fma(av[a].x, bv[b].y, acc[2 * a][2 * b + 1]);
+                    acc[2 * a + 1][2 * b] = fma(av[a].y, bv[b].x, acc[2 * a + 1][2 * b]);
+                    acc[2 * a + 1][2 * b + 1] = fma(av[a].y, bv[b].y, acc[2 * a + 1][2 * b + 1]);
+                }
         }
-        __syncthreads();
     }
+    cp_async_wait<0>();
 #pragma unroll
-    for (int a = 0; a < 4; ++a) {
-        const int i = i0 + ty + 16 * a;
+    for (int a = 0; a < 2 * RA; ++a) {
+        const int i = i0 + 32 * (a >> 1) + 2 * ty + (a & 1);
         if (i >= g.M) continue;
+        const double a0 = g.w0 != 0.0 ? g.w0 * A[i] : 0.0;
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
-            const int j = j0 + tx + 16 * b;
+            const int j = j0 + 32 * (b >> 1) + 2 * tx + (b & 1);
             if (j >= g.N || (g.upper && j < i)) continue;
             double *c = C + (size_t)i * g.ldc + j;
-            *c = (g.beta == 0.0 ? 0.0 : g.beta * *c) + g.alpha * acc[a][b];
+            double v = g.alpha * acc[a][b];
+            if (g.w0 != 0.0) v = fma(a0, B[j], v);
+            *c = (g.beta == 0.0 ? 0.0 : g.beta * *c) + v;
         }
     }
 }
@@ -284,35 +326,53 @@ __global__ void aug_fx_kernel(const AugArgs a)
     s[2] = __dadd_rn(s[2], __dmul_rn(a.dt, d2));
 }
 
-// weighted column means of V [m x cols] with circular means on the angle columns, then residuals in place
-// or into R.  angle columns: state -> {2}; measurement -> odd columns.  One CTA per filter.
+// weighted column means of V [m x cols] with circular means on the angle columns (state: column 2;
+// measurement: odd columns), then the residuals V[k] - mean (angles wrapped) into R (may alias V).
+// One CTA per (32-column group, filter): warp w sums rows w, w+8, ... with lanes across 32 consecutive
+// columns (coalesced), the 8 partial sums are added in warp order, then every warp writes the residuals
+// of its rows.  mean_given: the mean is an input (residuals of re-drawn sigma points about the prior).
 __global__ void __launch_bounds__(256) aug_mean_resid_kernel(const AugArgs a, const double *Vbase, int cols, int is_meas,
                                                              int mean_given, double *mean_base, double *Rbase)
 {
-    const int f = blockIdx.x;
+    LSLAM_SMEM_DECL;
+    double *part = reinterpret_cast<double *>(smem_raw);             // [8][32][2], then mu at [512 + lane]
+    const int f = blockIdx.y;
     if (a.status[f] != 0) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + lane;
+    const bool live = c < cols;
     const double *V = Vbase + (size_t)f * a.m * cols;
     double *mean = mean_base + (size_t)f * cols, *R = Rbase + (size_t)f * a.m * cols;
-    for (int c = threadIdx.x; c < cols; c += blockDim.x) {
-        const bool ang = is_meas ? (c & 1) : (c == 2);
-        double mu;
-        if (mean_given) {
-            mu = mean[c];
-        } else {
-            double s0 = 0.0, s1 = 0.0;
-            for (int k = 0; k < a.m; ++k) {
+    const bool ang = is_meas ? (c & 1) : (c == 2);
+    if (!mean_given) {
+        double s0 = 0.0, s1 = 0.0;
+        if (live) {
+            for (int k = warp; k < a.m; k += 8) {
                 const double v = V[(size_t)k * cols + c], w = a.wm[k];
                 if (ang) { double sn, cs; sincos(v, &sn, &cs); s0 = fma(sn, w, s0); s1 = fma(cs, w, s1); }
                 else s0 = fma(v, w, s0);
             }
-            mu = ang ? atan2(s0, s1) : s0;
-            mean[c] = mu;
         }
-        for (int k = 0; k < a.m; ++k) {
-            double d = __dsub_rn(V[(size_t)k * cols + c], mu);
-            if (ang) d = ukf_normalize_angle(d);
-            R[(size_t)k * cols + c] = d;
+        part[(warp * 32 + lane) * 2] = s0; part[(warp * 32 + lane) * 2 + 1] = s1;
+        __syncthreads();
+        if (warp == 0) {
+            double t0 = 0.0, t1 = 0.0;
+            for (int w = 0; w < 8; ++w) { t0 = __dadd_rn(t0, part[(w * 32 + lane) * 2]); t1 = __dadd_rn(t1, part[(w * 32 + lane) * 2 + 1]); }
+            const double mu = ang ? atan2(t0, t1) : t0;
+            part[512 + lane] = mu;
+            if (live) mean[c] = mu;
         }
+        __syncthreads();
+    } else {
+        if (warp == 0) part[512 + lane] = live ? mean[c] : 0.0;
+        __syncthreads();
+    }
+    if (!live) return;
+    const double mu = part[512 + lane];
+    for (int k = warp; k < a.m; k += 8) {
+        double d = __dsub_rn(V[(size_t)k * cols + c], mu);
+        if (ang) d = ukf_normalize_angle(d);
+        R[(size_t)k * cols + c] = d;
     }
 }
 
@@ -359,6 +419,18 @@ __global__ void aug_transpose_kernel(const double *src, long long s_src, double 
     }
 }
 
+// lower triangle <- transpose of the upper one (the GEMM computed j >= i only)
+__global__ void aug_mirror_kernel(double *base, long long stride, int dim, const int32_t *status)
+{
+    const int f = blockIdx.y;
+    if (status[f] != 0) return;
+    double *A = base + (size_t)f * stride;
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < (long long)dim * dim; e += (long long)gridDim.x * blockDim.x) {
+        const int r = (int)(e / dim), c = (int)(e % dim);
+        if (c < r) A[e] = A[(size_t)c * dim + r];
+    }
+}
+
 // x = xbar + K residual_h(z, zhat) (K^T stored: Kt [dz x n]); one CTA per filter
 __global__ void __launch_bounds__(256) aug_update_x_kernel(const AugArgs a, double *xnew_base)
 {
@@ -389,7 +461,8 @@ __global__ void aug_commit_kernel(const AugArgs a, const double *xnew, const dou
     if (a.status[f] != 0) return;
     const long long nn = (long long)a.n * a.n;
     for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < nn; e += (long long)gridDim.x * blockDim.x) {
-        a.P[(size_t)f * nn + e] = Pnew[(size_t)f * nn + e];
+        const int r = (int)(e / a.n), c = (int)(e % a.n);             // Pnew holds the upper triangle
+        a.P[(size_t)f * nn + e] = Pnew[(size_t)f * nn + (c >= r ? e : (long long)c * a.n + r)];
         if (e < a.n) a.x[(size_t)f * a.n + e] = xnew[(size_t)f * a.n + e];
     }
 }

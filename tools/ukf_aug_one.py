@@ -34,7 +34,7 @@ for r in range(reps + 1):
     torch.cuda.synchronize()
     ms.append(e0.elapsed_time(e1))
     launches = eng.launch_count() - l0
-best = min(ms[1:])
+best = min(ms[1:] or ms)
 print("ukf_aug L=%d n=%d F=%d: %.2f ms/step (runs %s) -> %.0f filter-steps/s, %.2f TFLOP/s useful fp64 "
       "(%.3f GFLOP/filter), %d launches, workspace %.2f GB, status nonzero %d"
       % (L, n, F, best, ["%.1f" % v for v in ms], F / best * 1e3, flop * F / best / 1e9, flop / 1e9, launches,
