@@ -109,6 +109,9 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
     } else if (!strcmp(key, "ransac.ring")) {
         if (value < 0 || value == 1 || value > 16) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.ring must be 0 or 2..16");
         h->opt_ring = (int)value;
+    } else if (!strcmp(key, "ukf_aug.gemm")) {
+        if (value < 0 || value > 1) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.gemm: 0 default (DMMA), 1 DFMA");
+        h->opt_aug_gemm = (int)value;
     } else {
         return fail(h, LSLAM_ERR_BAD_ARG, "unknown option '%s'", key);
     }
@@ -448,15 +451,15 @@ extern "C" int lslam_ukf_update(void *handle, double *x, double *P, const double
 namespace {
 struct AugLayout {
     long long per_filter;           // doubles
-    long long U, X, Y, H, S, ST, Kt, T, Pbar, xbar, xnew, zhat;   // sizes in doubles per filter
+    long long U, X, Y, H, S, Kt, Pbar, xbar, xnew, zhat;   // sizes in doubles per filter
 };
 AugLayout aug_layout(int L)
 {
     const long long n = 3 + 2LL * L, m = 2 * n + 1, dz = 2LL * L;
     AugLayout y;
-    y.U = n * n; y.X = m * n; y.Y = m * n; y.H = m * dz; y.S = dz * dz; y.ST = dz * dz; y.Kt = dz * n; y.T = dz * n;
+    y.U = n * n; y.X = m * n; y.Y = m * n; y.H = m * dz; y.S = dz * dz; y.Kt = dz * (n + 1);
     y.Pbar = n * n; y.xbar = n; y.xnew = n; y.zhat = dz;
-    y.per_filter = y.U + y.X + y.Y + y.H + y.S + y.ST + y.Kt + y.T + y.Pbar + y.xbar + y.xnew + y.zhat;
+    y.per_filter = y.U + y.X + y.Y + y.H + y.S + y.Kt + y.Pbar + y.xbar + y.xnew + y.zhat;
     return y;
 }
 constexpr int kAugMaxBatch = 32768;
@@ -470,7 +473,19 @@ struct AugRun {
         AugGemm g;
         g.A = A; g.B = B; g.C = C; g.sA = sA; g.sB = sB; g.sC = sC; g.M = M; g.N = N; g.K = K;
         g.lda = lda; g.ldb = ldb; g.ldc = ldc; g.alpha = alpha; g.beta = beta; g.w0 = w0; g.skip = skip; g.upper = upper;
-        if (M <= 32) {
+        if (h->opt_aug_gemm != 1) {                               // DMMA kernels (default)
+            if (M <= 32) {
+                auto kern = aug_gemm_dmma_kernel<32, 64, 1, 4>;
+                LSLAM_LAUNCH(kern, dim3((N + 63) / 64, 1, F), 128, (aug_dmma_smem<32, 64>()), st, g);
+            } else {
+                auto kern = aug_gemm_dmma_kernel<64, 64, 2, 2>;
+                if (!h->aug_attr_set) {
+                    LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)aug_dmma_smem<64, 64>()));
+                    h->aug_attr_set = true;
+                }
+                LSLAM_LAUNCH(kern, dim3((N + 63) / 64, (M + 63) / 64, F), 128, (aug_dmma_smem<64, 64>()), st, g);
+            }
+        } else if (M <= 32) {
             dim3 grid((N + kAugTile - 1) / kAugTile, 1, F);
             LSLAM_LAUNCH(aug_gemm_tn_kernel<32>, grid, 256, aug_gemm_smem(32), st, g);
         } else {
@@ -550,7 +565,7 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
         a.status = status + f0;
         double *p = ws;
         a.U = p; p += lay.U * Fb; a.X = p; p += lay.X * Fb; a.Y = p; p += lay.Y * Fb; a.H = p; p += lay.H * Fb;
-        a.S = p; p += lay.S * Fb; a.ST = p; p += lay.ST * Fb; a.Kt = p; p += lay.Kt * Fb; a.T = p; p += lay.T * Fb;
+        a.S = p; p += lay.S * Fb; a.Kt = p; p += lay.Kt * Fb;
         a.Pbar = p; p += lay.Pbar * Fb; a.xbar = p; p += lay.xbar * Fb;
         double *xnew = p; p += lay.xnew * Fb;
         a.zhat = p; a.wm = wm; a.wc = wc;
@@ -586,45 +601,30 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
         }
         const double *xres = a.xbar;
         if (upd) {
-            const long long zz = (long long)dz * dz, zn = (long long)dz * n, mz = (long long)m * dz;
+            const int n1 = n + 1;                                 // W: dz x (n + 1), right-hand sides [Pzx | r]
+            const long long zz = (long long)dz * dz, zn = (long long)dz * n1, mz = (long long)m * dz;
             LSLAM_LAUNCH(aug_hx_kernel, gew, 256, 0, st, a);
             LSLAM_LAUNCH(aug_mean_resid_kernel, dim3((dz + 31) / 32, Fb), 256, kAugMeanSmem, st, a, (const double *)a.H, dz, 1, 0, a.zhat, a.H);
             LSLAM_LAUNCH(aug_fill_noise_kernel, gew, 256, 0, st, a, a.S, dz, 1);
-            h->launches += 3;
+            LSLAM_LAUNCH(aug_innovation_kernel, dim3(Fb), 256, 0, st, a);
+            h->launches += 4;
             run.gemm(a.H, mz, dz, a.H, mz, dz, a.S, zz, dz, dz, dz, m, wc0 - wi, wi, 1.0, a.status, 1);   // S (upper)
-            run.gemm(a.H, mz, dz, a.Y, mn, n, a.Kt, zn, n, dz, n, m, wc0 - wi, wi, 0.0, a.status, 0);    // Pzx
-            LSLAM_LAUNCH(aug_mirror_kernel, gew, 256, 0, st, a.S, zz, dz, (const int32_t *)a.status);
-            h->launches++;
-            // Cholesky of S into U (dz x dz), its transpose into ST
+            run.gemm(a.H, mz, dz, a.Y, mn, n, a.Kt, zn, n1, dz, n, m, wc0 - wi, wi, 0.0, a.status, 0);   // Pzx
+            // Cholesky of S into U (dz x dz; a.U keeps its n * n stride per filter)
             LSLAM_LAUNCH(aug_scale_upper_kernel, gew, 256, 0, st, (const double *)a.S, zz, a.U, nn, dz, 1.0, (const int32_t *)a.status);
             h->launches++;
-            // a.U is laid out with stride n*n per filter; keep that stride for the dz x dz factor
             run.chol(a.U, nn, dz, a.status, LSLAM_UKF_ST_S);
-            // (transpose kernel works on dense [F, dim, dim]; the factor lives at stride nn, so transpose per stride)
-            LSLAM_LAUNCH(aug_transpose_kernel, gew, 256, 0, st, (const double *)a.U, nn, a.ST, zz, dz, (const int32_t *)a.status);
-            h->launches++;
-            for (int jb = 0; jb < dz; jb += 32) {                 // U^T W = Pzx
+            for (int jb = 0; jb < dz; jb += 32) {                 // U^T W = [Pzx | r]
                 const int nb = dz - jb < 32 ? dz - jb : 32;
                 if (jb > 0)
-                    run.gemm(a.U + jb, nn, dz, a.Kt, zn, n, a.Kt + (size_t)jb * n, zn, n, nb, n, jb, 0.0, -1.0, 1.0, a.status, 0);
-                LSLAM_LAUNCH(aug_trsm_block_kernel, dim3((n + 255) / 256, Fb), 256, kAugBlockSmem, st, (const double *)a.U, nn, dz,
-                             a.Kt, zn, n, n, jb, nb, 0, (const int32_t *)a.status);
+                    run.gemm(a.U + jb, nn, dz, a.Kt, zn, n1, a.Kt + (size_t)jb * n1, zn, n1, nb, n1, jb, 0.0, -1.0, 1.0, a.status, 0);
+                LSLAM_LAUNCH(aug_trsm_block_kernel, dim3((n1 + 255) / 256, Fb), 256, kAugBlockSmem, st, (const double *)a.U, nn, dz,
+                             a.Kt, zn, n1, n1, jb, nb, 0, (const int32_t *)a.status);
                 h->launches++;
             }
-            for (int jb = ((dz - 1) / 32) * 32; jb >= 0; jb -= 32) {   // U K^T = W
-                const int nb = dz - jb < 32 ? dz - jb : 32;
-                const int below = dz - jb - nb;
-                if (below > 0)
-                    run.gemm(a.ST + (size_t)(jb + nb) * dz + jb, zz, dz, a.Kt + (size_t)(jb + nb) * n, zn, n,
-                             a.Kt + (size_t)jb * n, zn, n, nb, n, below, 0.0, -1.0, 1.0, a.status, 0);
-                LSLAM_LAUNCH(aug_trsm_block_kernel, dim3((n + 255) / 256, Fb), 256, kAugBlockSmem, st, (const double *)a.U, nn, dz,
-                             a.Kt, zn, n, n, jb, nb, 1, (const int32_t *)a.status);
-                h->launches++;
-            }
-            LSLAM_LAUNCH(aug_update_x_kernel, dim3(Fb), 256, sizeof(double) * (size_t)dz, st, a, xnew);
+            LSLAM_LAUNCH(aug_update_x_kernel, dim3((n + 31) / 32, Fb), 256, kAugUpdateXSmem, st, a, xnew);
             h->launches++;
-            run.gemm(a.S, zz, dz, a.Kt, zn, n, a.T, zn, n, dz, n, dz, 0.0, 1.0, 0.0, a.status, 0);       // T = S K^T
-            run.gemm(a.Kt, zn, n, a.T, zn, n, a.Pbar, nn, n, n, n, dz, 0.0, -1.0, 1.0, a.status, 1);    // P = Pbar - K T (upper; commit mirrors)
+            run.gemm(a.Kt, zn, n1, a.Kt, zn, n1, a.Pbar, nn, n, n, n, dz, 0.0, -1.0, 1.0, a.status, 1);   // P = Pbar - W^T W (upper; commit mirrors)
             xres = xnew;
         }
         LSLAM_LAUNCH(aug_commit_kernel, gew, 256, 0, st, a, xres, (const double *)a.Pbar);

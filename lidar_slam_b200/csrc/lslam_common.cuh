@@ -22,6 +22,8 @@ struct Handle {
     int64_t launches = 0;
     int opt_tpt = 0, opt_slots = 0, opt_threads = 0;
     int opt_kernel = 0, opt_scorers = 0, opt_posts = 0, opt_ring = 0, opt_screen = 0;
+    int opt_aug_gemm = 0;              // ukf_aug.gemm: 0 DMMA (default), 1 DFMA
+    bool aug_attr_set = false;
     double *express_tab_d = nullptr;   // sin/cos tables of the packet decoder (csrc/express.cuh)
     unsigned long long *counters_d = nullptr;
     char err[512] = "";

@@ -15,9 +15,10 @@
 //   redraw          Cholesky of (n + lambda) Pbar, X = sigma points of (xbar, Pbar)      (filterpy >= 1.4.5)
 //   hx              H[k] = (range, bearing) of every landmark of sigma point k; zhat; E = residual_h(H, zhat)
 //   S               = E^T diag(Wc) E + R,   Pzx = E^T diag(Wc) Y                          batched GEMM
-//   gain            K^T = S^-1 Pzx through the Cholesky of S and two blocked triangular solves
-//                   (filterpy forms inv(S) explicitly; same K to rounding)
-//   update          x = xbar + K residual_h(z, zhat);  P = Pbar - K (S K^T)               batched GEMM
+//   gain            through the Cholesky S = U^T U and ONE blocked forward solve W = U^-T [Pzx | r]:
+//                   K S K^T = Pzx^T S^-1 Pzx = W^T W and K r = W^T (U^-T r), so neither K nor inv(S) is formed
+//                   (filterpy forms inv(S) and K explicitly; same x, P to rounding, 129 MFMA less per step)
+//   update          x = xbar + W^T v;  P = Pbar - W^T W (upper triangle, mirrored by the commit)   batched GEMM
 // One GEMM form serves all of them: C[i,j] = beta C[i,j] + alpha sum_k w_k A[k,i] B[k,j] with A and B
 // stored k-major ("TN"), which is how the sigma-point arrays and the factor rows lie in memory.
 #pragma once
@@ -50,6 +51,7 @@ constexpr int kAugTile = 64, kAugBK = 16, kAugStages = 3;
 constexpr size_t aug_gemm_smem(int TM) { return (size_t)kAugStages * kAugBK * (TM + kAugTile) * sizeof(double); }
 constexpr size_t kAugBlockSmem = (32 * 33 + 2) * sizeof(double);
 constexpr size_t kAugMeanSmem = (8 * 32 * 2 + 32) * sizeof(double);
+constexpr size_t kAugUpdateXSmem = 8 * 33 * sizeof(double);
 
 #ifndef LSLAM_EMU
 __device__ __forceinline__ void cp_async8(double *dst_smem, const double *src, bool valid)
@@ -146,6 +148,145 @@ __global__ void __launch_bounds__(256) aug_gemm_tn_kernel(const AugGemm g)
     }
 }
 
+// ---- the same GEMM on the fp64 tensor-core instruction (DMMA) ---------------------------------------------
+// mma.sync.m8n8k4.f64: one warp instruction = an 8 x 8 x 4 product, 256 FMA, one operand double per lane.
+// tools/probe/dmma_probe.cu measures it at the DFMA rate on B200 (37.1 TFLOP/s against 36.9; the two share
+// the fp64 pipe, mixed streams add up) - so it buys no flops, it buys everything AROUND the flops: the
+// DFMA kernel above needs one 16-byte shared-memory operand load per 4 FMA-instructions and runs into the
+// shared-memory pipe (ncu: l1tex 93 %, fp64 pipe 48 %); here a warp tile of WM x WN takes
+// (WM + WN) / 8 8-byte loads per (WM / 8)(WN / 8) DMMAs, 8 x fewer shared-memory wavefronts per flop, and
+// one issue slot per 256 FMA.
+// Fragment layout (PTX ISA, mma.m8n8k4 .f64): A (8 x 4, row): lane holds A[lane >> 2][lane & 3];
+// B (4 x 8, col): lane holds B[lane & 3][lane >> 2]; C/D: lane holds C[lane >> 2][2 (lane & 3) + {0, 1}].
+// With the tiles k-major in shared memory (as[k][i], bs[k][j]) both operand loads are
+// tile[(k0 + (lane & 3)) * LD + c0 + (lane >> 2)]; LD = T + 4 = 4 (mod 16) makes the 16 addresses of each
+// half-warp fall in 16 different 8-byte banks.
+#ifndef LSLAM_EMU
+__device__ __forceinline__ void dmma_m8n8k4(double &c0, double &c1, double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+#else
+inline void dmma_m8n8k4(double &c0, double &c1, double a, double b)
+{
+    double av[32], bv[32];
+    emu::gather_all(a, av);
+    emu::gather_all(b, bv);
+    const int r = emu::ts.lane >> 2, c = (emu::ts.lane & 3) * 2;
+    for (int k = 0; k < 4; ++k) {
+        c0 = fma(av[r * 4 + k], bv[c * 4 + k], c0);
+        c1 = fma(av[r * 4 + k], bv[(c + 1) * 4 + k], c1);
+    }
+}
+#endif
+
+template <int TM, int TN> constexpr size_t aug_dmma_smem() { return (size_t)kAugStages * kAugBK * (TM + 4 + TN + 4) * sizeof(double); }
+
+// CTA tile TM x TN, WARPS_M x WARPS_N warps, warp tile (TM / WARPS_M) x (TN / WARPS_N).
+template <int TM, int TN, int WARPS_M, int WARPS_N>
+__global__ void __launch_bounds__(32 * WARPS_M * WARPS_N) aug_gemm_dmma_kernel(const AugGemm g)
+{
+    LSLAM_SMEM_DECL;
+    constexpr int NT = 32 * WARPS_M * WARPS_N, WM = TM / WARPS_M, WN = TN / WARPS_N, FM = WM / 8, FN = WN / 8;
+    constexpr int LDA = TM + 4, LDB = TN + 4, STAGE = kAugBK * (LDA + LDB);
+    static_assert(TM % 16 == 0 && TN % 16 == 0 && WM % 8 == 0 && WN % 8 == 0, "tile shape");
+    double *sm = reinterpret_cast<double *>(smem_raw);
+    const int f = blockIdx.z;
+    if (g.skip != nullptr && g.skip[f] != 0) return;
+    const int i0 = blockIdx.y * TM, j0 = blockIdx.x * TN;
+    if (g.upper && i0 > j0 + TN - 1) return;
+    const double *A = g.A + (size_t)f * g.sA, *B = g.B + (size_t)f * g.sB;
+    double *C = g.C + (size_t)f * g.sC;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int wm0 = (warp / WARPS_N) * WM, wn0 = (warp % WARPS_N) * WN;
+    // fragment liveness (warp-uniform): an 8 x 8 fragment is skipped when it lies outside C or, for an
+    // upper-triangle product, entirely below the diagonal - n = 403 is 6.3 tiles of 64 but 50.4 fragments
+    unsigned live = 0;
+#pragma unroll
+    for (int a = 0; a < FM; ++a)
+#pragma unroll
+        for (int b = 0; b < FN; ++b) {
+            const int fi = i0 + wm0 + 8 * a, fj = j0 + wn0 + 8 * b;
+            if (fi < g.M && fj < g.N && !(g.upper && fi > fj + 7)) live |= 1u << (a * FN + b);
+        }
+    const bool dead = live == 0;
+    const bool full = live == (FM * FN == 32 ? 0xffffffffu : (1u << (FM * FN)) - 1u);
+    const int ntiles = (g.K + kAugBK - 1) / kAugBK;
+    auto issue = [&](int t) {
+        if (t < ntiles) {
+            double *as = sm + (size_t)(t % kAugStages) * STAGE, *bs = as + kAugBK * LDA;
+            const int k0 = t * kAugBK;
+            for (int e = threadIdx.x; e < kAugBK * TM; e += NT) {
+                const int kk = e / TM, c = e % TM;
+                const bool ok = k0 + kk < g.K && i0 + c < g.M;
+                cp_async8(as + kk * LDA + c, ok ? A + (size_t)(k0 + kk) * g.lda + i0 + c : A, ok);
+            }
+            for (int e = threadIdx.x; e < kAugBK * TN; e += NT) {
+                const int kk = e / TN, c = e % TN;
+                const bool ok = k0 + kk < g.K && j0 + c < g.N;
+                cp_async8(bs + kk * LDB + c, ok ? B + (size_t)(k0 + kk) * g.ldb + j0 + c : B, ok);
+            }
+        }
+        cp_async_commit();
+    };
+    double acc[FM][FN][2];
+#pragma unroll
+    for (int a = 0; a < FM; ++a)
+#pragma unroll
+        for (int b = 0; b < FN; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+    const int frag = (lane & 3), fcol = (lane >> 2);
+    issue(0);
+    issue(1);
+    for (int t = 0; t < ntiles; ++t) {
+        cp_async_wait<1>();
+        __syncthreads();
+        issue(t + 2);
+        if (dead) continue;
+        const double *as = sm + (size_t)(t % kAugStages) * STAGE + wm0 + fcol;
+        const double *bs = sm + (size_t)(t % kAugStages) * STAGE + kAugBK * LDA + wn0 + fcol;
+#pragma unroll
+        for (int ks = 0; ks < kAugBK; ks += 4) {
+            double av[FM], bv[FN];
+#pragma unroll
+            for (int a = 0; a < FM; ++a) av[a] = as[(ks + frag) * LDA + 8 * a];
+#pragma unroll
+            for (int b = 0; b < FN; ++b) bv[b] = bs[(ks + frag) * LDB + 8 * b];
+            if (full) {
+#pragma unroll
+                for (int a = 0; a < FM; ++a)
+#pragma unroll
+                    for (int b = 0; b < FN; ++b) dmma_m8n8k4(acc[a][b][0], acc[a][b][1], av[a], bv[b]);
+            } else {
+#pragma unroll
+                for (int a = 0; a < FM; ++a)
+#pragma unroll
+                    for (int b = 0; b < FN; ++b)
+                        if ((live >> (a * FN + b)) & 1u) dmma_m8n8k4(acc[a][b][0], acc[a][b][1], av[a], bv[b]);
+            }
+        }
+    }
+    cp_async_wait<0>();
+    if (dead) return;
+#pragma unroll
+    for (int a = 0; a < FM; ++a) {
+        const int i = i0 + wm0 + 8 * a + fcol;
+        if (i >= g.M) continue;
+        const double a0 = g.w0 != 0.0 ? g.w0 * A[i] : 0.0;
+#pragma unroll
+        for (int b = 0; b < FN; ++b)
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const int j = j0 + wn0 + 8 * b + 2 * frag + q;
+                if (j >= g.N || (g.upper && j < i)) continue;
+                double *c = C + (size_t)i * g.ldc + j;
+                double v = g.alpha * acc[a][b][q];
+                if (g.w0 != 0.0) v = fma(a0, B[j], v);
+                *c = (g.beta == 0.0 ? 0.0 : g.beta * *c) + v;
+            }
+    }
+}
+
 // ---- blocked Cholesky (upper, U^T U = A, in place; only the upper triangle is read / written) --------
 // Panel step jb (width nb <= 32), one CTA per matrix: factor the nb x nb diagonal block, then the panel
 // row U[jb:jb+nb, jb+nb:n] = D^-T A[jb:jb+nb, jb+nb:n].  The trailing update A22 -= panel^T panel is the
@@ -208,7 +349,8 @@ __global__ void __launch_bounds__(256) aug_chol_panel_kernel(double *Abase, long
     }
 }
 
-// ---- blocked triangular solves for K^T = S^-1 Pzx with S = U^T U ----------------------------------
+// ---- blocked triangular solve W = U^-T [Pzx | r] with S = U^T U (the backward step is kept for callers
+// that want K^T = U^-1 W itself; the filter step does not) ---------------------------------------------
 // forward (U^T W = Pzx) block step: rows [jb, jb+nb) of W, after the GEMM subtracted the rows above:
 //   W[jb+r, :] = (W[jb+r, :] - sum_{k<r} U[jb+k, jb+r] W[jb+k, :]) / U[jb+r, jb+r]
 // backward (U K^T = W) block step, rows descending inside the block:
@@ -262,7 +404,7 @@ struct AugArgs {
     double *x, *P;                  // [F, n], [F, n, n] in / out
     const double *u, *z;            // [F, 2], [F, L, 2]
     int32_t *status;                // [F]
-    double *U, *X, *Y, *H, *S, *ST, *Kt, *T, *Pbar, *xbar, *zhat, *wm, *wc;   // workspace
+    double *U, *X, *Y, *H, *S, *Kt, *Pbar, *xbar, *zhat, *wm, *wc;   // workspace (Kt: W = U^-T [Pzx | r], dz x (n + 1))
     double dt, half_r, r_over_l, cscale, var_dist, var_angle;
     double Q[9];
 };
@@ -407,50 +549,41 @@ __global__ void aug_fill_noise_kernel(const AugArgs a, double *Cbase, int dim, i
     }
 }
 
-__global__ void aug_transpose_kernel(const double *src, long long s_src, double *dst, long long s_dst, int dim,
-                                     const int32_t *status)
+// innovation r = residual_h(z, zhat) into column n of W (W: dz x (n + 1), the right-hand sides of the
+// forward solve: Pzx in columns 0..n-1, r in column n)
+__global__ void __launch_bounds__(256) aug_innovation_kernel(const AugArgs a)
 {
-    const int f = blockIdx.y;
-    if (status[f] != 0) return;
-    src += (size_t)f * s_src; dst += (size_t)f * s_dst;
-    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < (long long)dim * dim; e += (long long)gridDim.x * blockDim.x) {
-        const int r = (int)(e / dim), c = (int)(e % dim);
-        dst[(size_t)c * dim + r] = src[e];
-    }
-}
-
-// lower triangle <- transpose of the upper one (the GEMM computed j >= i only)
-__global__ void aug_mirror_kernel(double *base, long long stride, int dim, const int32_t *status)
-{
-    const int f = blockIdx.y;
-    if (status[f] != 0) return;
-    double *A = base + (size_t)f * stride;
-    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < (long long)dim * dim; e += (long long)gridDim.x * blockDim.x) {
-        const int r = (int)(e / dim), c = (int)(e % dim);
-        if (c < r) A[e] = A[(size_t)c * dim + r];
-    }
-}
-
-// x = xbar + K residual_h(z, zhat) (K^T stored: Kt [dz x n]); one CTA per filter
-__global__ void __launch_bounds__(256) aug_update_x_kernel(const AugArgs a, double *xnew_base)
-{
-    LSLAM_SMEM_DECL;
-    double *ysh = reinterpret_cast<double *>(smem_raw);
     const int f = blockIdx.x;
     if (a.status[f] != 0) return;
     const double *zh = a.zhat + (size_t)f * a.dz, *z = a.z + (size_t)f * a.dz;
+    double *W = a.Kt + (size_t)f * a.dz * (a.n + 1);
     for (int j = threadIdx.x; j < a.dz; j += blockDim.x) {
         double d = __dsub_rn(z[j], zh[j]);
         if (j & 1) d = ukf_normalize_angle(d);
-        ysh[j] = d;
+        W[(size_t)j * (a.n + 1) + a.n] = d;
     }
+}
+
+// x = xbar + K r with K r = Pxz S^-1 r = W^T v, W = U^-T Pzx (columns 0..n-1), v = U^-T r (column n);
+// grid (ceil(n / 32), F): warp w sums rows w, w+8, ... of its 32 columns, partial sums added in warp order
+__global__ void __launch_bounds__(256) aug_update_x_kernel(const AugArgs a, double *xnew_base)
+{
+    LSLAM_SMEM_DECL;
+    double (*part)[33] = reinterpret_cast<double (*)[33]>(smem_raw);
+    const int f = blockIdx.y;
+    if (a.status[f] != 0) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n1 = a.n + 1;
+    const int i = blockIdx.x * 32 + lane;
+    const double *W = a.Kt + (size_t)f * a.dz * n1;
+    double s = 0.0;
+    if (i < a.n)
+        for (int j = warp; j < a.dz; j += 8) s = fma(W[(size_t)j * n1 + i], W[(size_t)j * n1 + a.n], s);
+    part[warp][lane] = s;
     __syncthreads();
-    const double *Kt = a.Kt + (size_t)f * a.dz * a.n, *xb = a.xbar + (size_t)f * a.n;
-    double *xn = xnew_base + (size_t)f * a.n;
-    for (int i = threadIdx.x; i < a.n; i += blockDim.x) {
-        double s = 0.0;
-        for (int j = 0; j < a.dz; ++j) s = fma(Kt[(size_t)j * a.n + i], ysh[j], s);
-        xn[i] = __dadd_rn(xb[i], s);
+    if (warp == 0 && i < a.n) {
+        double t = 0.0;
+        for (int w = 0; w < 8; ++w) t = __dadd_rn(t, part[w][lane]);
+        xnew_base[(size_t)f * a.n + i] = __dadd_rn(a.xbar[(size_t)f * a.n + i], t);
     }
 }
 

@@ -124,6 +124,15 @@ template <class T> inline T exchange(T v, int src_lane, unsigned mask = 0xffffff
     return r;
 }
 
+// every lane's value to every lane (full warp): the operand exchange of an emulated warp-wide MMA
+template <class T> inline void gather_all(T v, T *out) {
+    WarpCtx &w = *ts.warp;
+    w.slot[ts.lane] = to_bits(v);
+    w.bar.wait();
+    for (int l = 0; l < 32; ++l) out[l] = from_bits<T>(w.slot[l]);
+    w.bar.wait();
+}
+
 } // namespace emu
 
 inline thread_local dim3 threadIdx, blockIdx, blockDim, gridDim;
