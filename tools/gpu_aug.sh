@@ -1,0 +1,18 @@
+#!/bin/bash
+# Augmented-UKF GPU session: timing at the C4 shape, ncu launch list, one full capture of the Pbar GEMM.
+# usage (under gpurun): bash tools/gpu_aug.sh <tag>
+set -u
+TAG=${1:-r1}
+OUT=gpurun_out
+mkdir -p $OUT
+echo "== aug timing"
+timeout 600 python tools/ukf_aug_one.py 200 1024 3 > $OUT/${TAG}_aug_time.log 2>&1 ; cat $OUT/${TAG}_aug_time.log
+timeout 300 python tools/ukf_aug_one.py 200 256 3 >> $OUT/${TAG}_aug_time.log 2>&1 ; tail -1 $OUT/${TAG}_aug_time.log
+timeout 300 python tools/ukf_aug_one.py 8 16384 3 >> $OUT/${TAG}_aug_time.log 2>&1 ; tail -1 $OUT/${TAG}_aug_time.log
+echo "== aug launch list"
+CMD="python tools/ukf_aug_one.py 200 256 1"
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $OUT/${TAG}_aug_launches.csv $CMD > $OUT/${TAG}_aug_ncu_launches.log 2>&1
+echo "launches rc=$?" ; python tools/aug_launch_summary.py $OUT/${TAG}_aug_launches.csv | tee $OUT/${TAG}_aug_launch_summary.txt
+echo "== aug ncu full (Pbar GEMM = 13th DMMA launch)"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:aug_gemm_dmma -s 12 -c 1 -f -o $OUT/${TAG}_aug_gemm $CMD > $OUT/${TAG}_aug_ncu_full.log 2>&1
+echo "full rc=$?"
