@@ -11,6 +11,7 @@
 #include <stdint.h>
 
 #ifndef LSLAM_EMU
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 namespace lslam {
@@ -57,6 +58,17 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned by
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// ---- tiled TMA (cp.async.bulk.tensor, SASS UTMALDG): a box of a 3-D tensor global -> shared, addressed
+// through a tensor map the host encodes (tmap_encode_3d in lslam.cu); coordinates outside the tensor are
+// zero-filled by the copy engine and still count towards the barrier's byte total.
+typedef CUtensorMap Tmap;
+__device__ __forceinline__ void tma_load_3d(void *dst, const Tmap *map, int c0, int c1, int c2, Mbar *bar)
+{
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar)) : "memory");
+}
+#define LSLAM_GRID_CONSTANT __grid_constant__
+
 } // namespace lslam
 
 #else // ---------------------------------------------------------------- CPU emulation (tests/emu)
@@ -98,6 +110,27 @@ inline void bulk_g2s(void *dst, const void *src, unsigned bytes, Mbar *bar)
     bar->tx.fetch_sub(bytes);
     mbar_emu_check(bar);
 }
+
+// emulated tensor map: fp64 elements, dim[0] fastest; strides in elements
+struct Tmap {
+    const double *base;
+    long long dim[3], stride[2];
+    int box[3];
+};
+inline void tma_load_3d(void *dst, const Tmap *m, int c0, int c1, int c2, Mbar *bar)
+{
+    double *d = static_cast<double *>(dst);
+    for (int z = 0; z < m->box[2]; ++z)
+        for (int y = 0; y < m->box[1]; ++y)
+            for (int x = 0; x < m->box[0]; ++x) {
+                const long long gx = c0 + x, gy = c1 + y, gz = c2 + z;
+                const bool in = gx >= 0 && gx < m->dim[0] && gy >= 0 && gy < m->dim[1] && gz >= 0 && gz < m->dim[2];
+                *d++ = in ? m->base[gz * m->stride[1] + gy * m->stride[0] + gx] : 0.0;
+            }
+    bar->tx.fetch_sub((int64_t)sizeof(double) * m->box[0] * m->box[1] * m->box[2]);
+    mbar_emu_check(bar);
+}
+#define LSLAM_GRID_CONSTANT
 
 } // namespace lslam
 #endif

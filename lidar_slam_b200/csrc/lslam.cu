@@ -110,8 +110,11 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
         if (value < 0 || value == 1 || value > 16) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.ring must be 0 or 2..16");
         h->opt_ring = (int)value;
     } else if (!strcmp(key, "ukf_aug.gemm")) {
-        if (value < 0 || value > 1) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.gemm: 0 default (DMMA), 1 DFMA");
+        if (value < 0 || value > 2) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.gemm: 0 default (DMMA fed by TMA), 1 DFMA, 2 DMMA fed by cp.async");
         h->opt_aug_gemm = (int)value;
+    } else if (!strcmp(key, "ukf_aug.tile")) {
+        if (value != 0 && value != 64 && value != 128) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.tile: 0 default (64), 64, 128");
+        h->opt_aug_tile = (int)value;
     } else {
         return fail(h, LSLAM_ERR_BAD_ARG, "unknown option '%s'", key);
     }
@@ -451,21 +454,81 @@ extern "C" int lslam_ukf_update(void *handle, double *x, double *P, const double
 namespace {
 struct AugLayout {
     long long per_filter;           // doubles
-    long long U, X, Y, H, S, Kt, Pbar, xbar, xnew, zhat;   // sizes in doubles per filter
+    long long U, X, Y, H, Kt, Pbar, xbar, xnew, zhat;   // sizes in doubles per filter (all even: 16-byte aligned arrays)
 };
 AugLayout aug_layout(int L)
 {
-    const long long n = 3 + 2LL * L, m = 2 * n + 1, dz = 2LL * L;
+    // arrays with n columns are stored with the even row pitch ldn = n + 1 (TMA needs 16-byte pitches)
+    const long long n = 3 + 2LL * L, ldn = n + 1, m = 2 * n + 1, dz = 2LL * L;
     AugLayout y;
-    y.U = n * n; y.X = m * n; y.Y = m * n; y.H = m * dz; y.S = dz * dz; y.Kt = dz * (n + 1);
-    y.Pbar = n * n; y.xbar = n; y.xnew = n; y.zhat = dz;
-    y.per_filter = y.U + y.X + y.Y + y.H + y.S + y.Kt + y.Pbar + y.xbar + y.xnew + y.zhat;
+    y.U = n * ldn; y.X = m * ldn; y.Y = m * ldn; y.H = m * dz; y.Kt = dz * ldn;
+    y.Pbar = n * ldn; y.xbar = ldn; y.xnew = ldn; y.zhat = dz;
+    y.per_filter = y.U + y.X + y.Y + y.H + y.Kt + y.Pbar + y.xbar + y.xnew + y.zhat;
     return y;
 }
 constexpr int kAugMaxBatch = 32768;
 
+// tensor map of a k-major operand: element (col, row, filter) at base[filter * sF + row * ld + col]; the
+// box is box_cols x kAugBK x 1.  Columns >= cols, rows >= rows read as zero.
+#ifndef LSLAM_EMU
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled_fn()
+{
+    static EncodeTiledFn fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+#endif
+int tmap_encode_3d(Handle *h, Tmap *map, const double *base, long long cols, long long rows, long long nf, long long ld,
+                   long long sF, int box_cols)
+{
+#ifndef LSLAM_EMU
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn) return fail(h, LSLAM_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    if (((uintptr_t)base & 15) || (ld & 1) || (sF & 1))
+        return fail(h, LSLAM_ERR_BAD_ARG, "TMA operand needs a 16-byte aligned base and even pitches (base %p, ld %lld, stride %lld)",
+                    (const void *)base, ld, sF);
+    const cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)nf};
+    const cuuint64_t strides[2] = {(cuuint64_t)ld * 8, (cuuint64_t)sF * 8};
+    const cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)kAugBK, 1}, es[3] = {1, 1, 1};
+    const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, (void *)base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(h, LSLAM_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+#else
+    (void)h;
+    map->base = base; map->dim[0] = cols; map->dim[1] = rows; map->dim[2] = nf; map->stride[0] = ld; map->stride[1] = sF;
+    map->box[0] = box_cols; map->box[1] = kAugBK; map->box[2] = 1;
+#endif
+    return LSLAM_OK;
+}
+
 struct AugRun {
     Handle *h; cudaStream_t st; int F;
+    template <int TM, int TN, int WM, int WN>
+    int gemm_tma(const AugGemm &g, bool &attr_set)
+    {
+        auto kern = aug_gemm_tma_kernel<TM, TN, WM, WN>;
+        if (!attr_set) {
+            LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)aug_tma_smem<TM, TN>()));
+            attr_set = true;
+        }
+        Tmap ma, mb;
+        int rc = tmap_encode_3d(h, &ma, g.A, g.M, g.K, F, g.lda, g.sA, TM + 4);
+        if (rc == LSLAM_OK) rc = tmap_encode_3d(h, &mb, g.B, g.N, g.K, F, g.ldb, g.sB, TN + 4);
+        if (rc != LSLAM_OK) return rc;
+        LSLAM_LAUNCH(kern, dim3((g.N + TN - 1) / TN, (g.M + TM - 1) / TM, F), 32 * (WM * WN + 1), (aug_tma_smem<TM, TN>()), st, g, ma, mb);
+        return LSLAM_OK;
+    }
+    // epilogue extras of the next gemm() call (reset by it): noise 1 = + Q (nq[9]) on the pose block, 2 = + R (nq[0], nq[1])
+    // on the diagonal; C2 = a second, scaled copy of the result
+    int noise = 0; double nq[9] = {0}; double *C2 = nullptr; long long sC2 = 0; int ldc2 = 0; double scale2 = 0.0;
     int gemm(const double *A, long long sA, int lda, const double *B, long long sB, int ldb, double *C, long long sC, int ldc,
              int M, int N, int K, double w0, double alpha, double beta, const int32_t *skip, int upper)
     {
@@ -473,15 +536,26 @@ struct AugRun {
         AugGemm g;
         g.A = A; g.B = B; g.C = C; g.sA = sA; g.sB = sB; g.sC = sC; g.M = M; g.N = N; g.K = K;
         g.lda = lda; g.ldb = ldb; g.ldc = ldc; g.alpha = alpha; g.beta = beta; g.w0 = w0; g.skip = skip; g.upper = upper;
-        if (h->opt_aug_gemm != 1) {                               // DMMA kernels (default)
+        g.noise = noise; for (int i = 0; i < 9; ++i) g.nq[i] = nq[i];
+        g.C2 = C2; g.sC2 = sC2; g.ldc2 = ldc2; g.scale2 = scale2;
+        noise = 0; C2 = nullptr;
+        if (h->opt_aug_gemm == 0) {                               // DMMA fed by TMA (default)
+            // CTA tile: 64 x 64 with three CTAs per SM.  ukf_aug.tile = 128 selects 128 x 128 (16 consumer warps, one
+            // CTA per SM, half the L2 -> shared traffic per flop): measured SLOWER on B200 (Pzx 2.96 vs 2.54 ms per
+            // 256 filters) - L2 is at 10 % of its throughput with either tile, the DMMA pipe is what saturates.
+            const int rc = M <= 32 ? gemm_tma<32, 64, 1, 4>(g, h->aug_attr_set[0])
+                         : (M <= 64 || h->opt_aug_tile != 128) ? gemm_tma<64, 64, 2, 2>(g, h->aug_attr_set[1])
+                                                               : gemm_tma<128, 128, 4, 4>(g, h->aug_attr_set[3]);
+            if (rc != LSLAM_OK) return rc;
+        } else if (h->opt_aug_gemm == 2) {                        // DMMA fed by 8-byte cp.async
             if (M <= 32) {
                 auto kern = aug_gemm_dmma_kernel<32, 64, 1, 4>;
                 LSLAM_LAUNCH(kern, dim3((N + 63) / 64, 1, F), 128, (aug_dmma_smem<32, 64>()), st, g);
             } else {
                 auto kern = aug_gemm_dmma_kernel<64, 64, 2, 2>;
-                if (!h->aug_attr_set) {
+                if (!h->aug_attr_set[2]) {
                     LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)aug_dmma_smem<64, 64>()));
-                    h->aug_attr_set = true;
+                    h->aug_attr_set[2] = true;
                 }
                 LSLAM_LAUNCH(kern, dim3((N + 63) / 64, (M + 63) / 64, F), 128, (aug_dmma_smem<64, 64>()), st, g);
             }
@@ -495,23 +569,28 @@ struct AugRun {
         h->launches++;
         return LSLAM_OK;
     }
-    // in-place upper Cholesky of F matrices (dim x dim, ld = dim, stride sA)
-    int chol(double *A, long long sA, int dim, int32_t *status, int fail_bit)
+    // in-place upper Cholesky of F matrices (dim x dim, row pitch ld, stride sA), LEFT-looking: block row jb
+    // first takes the contributions of all the rows above it in one GEMM of depth K = jb
+    //   A[jb:jb+nb, jb:dim] -= U[0:jb, jb:jb+nb]^T U[0:jb, jb:dim]
+    // (each element of the factor is written once, and the GEMMs are deep enough to keep their pipelines
+    // busy - the right-looking form did dim/32 rank-32 updates of the whole trailing matrix), then the panel
+    // kernel factors the diagonal block and solves the block row.
+    int chol(double *A, long long sA, int ld, int dim, int32_t *status, int fail_bit)
     {
         for (int jb = 0; jb < dim; jb += 32) {
             const int nb = dim - jb < 32 ? dim - jb : 32;
-            LSLAM_LAUNCH(aug_chol_panel_kernel, dim3(F), 256, kAugBlockSmem, st, A, sA, dim, dim, jb, nb, status, fail_bit);
-            h->launches++;
-            const int rest = dim - jb - nb;
-            if (rest > 0) {
-                const double *panel = A + (size_t)jb * dim + jb + nb;
-                gemm(panel, sA, dim, panel, sA, dim, A + (size_t)(jb + nb) * dim + jb + nb, sA, dim, rest, rest, nb,
-                     0.0, -1.0, 1.0, status, 1);
+            if (jb > 0) {
+                const int rc = gemm(A + jb, sA, ld, A + jb, sA, ld, A + (size_t)jb * ld + jb, sA, ld, nb, dim - jb, jb,
+                                    0.0, -1.0, 1.0, status, 1);
+                if (rc != LSLAM_OK) return rc;
             }
+            LSLAM_LAUNCH(aug_chol_panel_kernel, dim3(F), 256, kAugBlockSmem, st, A, sA, dim, ld, jb, nb, status, fail_bit);
+            h->launches++;
         }
         return LSLAM_OK;
     }
 };
+#define AUG_TRY(expr) do { const int rc_ = (expr); if (rc_ != LSLAM_OK) return rc_; } while (0)
 } // namespace
 
 extern "C" int lslam_ukf_aug_workspace_bytes(int32_t L, int32_t filters, int64_t *bytes)
@@ -519,7 +598,7 @@ extern "C" int lslam_ukf_aug_workspace_bytes(int32_t L, int32_t filters, int64_t
     if (L < 1 || L > 1024 || filters < 1 || !bytes) return LSLAM_ERR_BAD_ARG;
     const AugLayout y = aug_layout(L);
     const long long n = 3 + 2LL * L;
-    *bytes = (int64_t)sizeof(double) * (y.per_filter * filters + 2 * (2 * n + 1));
+    *bytes = (int64_t)sizeof(double) * (y.per_filter * filters + 2 * (2 * n + 2));
     return LSLAM_OK;
 }
 
@@ -535,10 +614,11 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
         return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_aug_step: need F >= 0, 1 <= L <= 1024, flags of PREDICT|UPDATE|REDRAW");
     const bool pred = flags & LSLAM_UKF_PREDICT, upd = flags & LSLAM_UKF_UPDATE;
     if (upd && !z) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_aug_step: update needs z");
+    if ((uintptr_t)workspace & 15) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_aug_step: workspace must be 16-byte aligned");
     if (F == 0) return LSLAM_OK;
-    const int n = 3 + 2 * L, m = 2 * n + 1, dz = 2 * L;
+    const int n = 3 + 2 * L, ldn = n + 1, m = 2 * n + 1, dz = 2 * L;
     const AugLayout lay = aug_layout(L);
-    const long long avail = workspace_bytes / (long long)sizeof(double) - 2LL * m;
+    const long long avail = workspace_bytes / (long long)sizeof(double) - 2LL * (m + 1);
     long long cap = avail > 0 ? avail / lay.per_filter : 0;
     if (cap < 1) return fail(h, LSLAM_ERR_CAPACITY, "lslam_ukf_aug_step: workspace holds no filter (lslam_ukf_aug_workspace_bytes)");
     if (cap > kAugMaxBatch) cap = kAugMaxBatch;
@@ -549,8 +629,8 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
     const double c = n + lam;
     if (!(c == c) || c == 0.0) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_aug_step: alpha/kappa give n + lambda = 0");
     double *ws = (double *)workspace;
-    double *wm = ws, *wc = ws + m;
-    ws += 2 * m;
+    double *wm = ws, *wc = ws + m + 1;
+    ws += 2 * (m + 1);
     const double wi = 0.5 / c, wc0 = lam / c + (1 - alpha * alpha + beta);
     LSLAM_LAUNCH(aug_weights_kernel, dim3((m + 255) / 256), 256, 0, st, wm, wc, m, wi, lam / c, wc0);
     h->launches++;
@@ -559,13 +639,13 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
     for (long long f0 = 0; f0 < F; f0 += cap) {
         const int Fb = (int)(F - f0 < cap ? F - f0 : cap);
         AugArgs a;
-        a.F = Fb; a.L = L; a.n = n; a.m = m; a.dz = dz;
+        a.F = Fb; a.L = L; a.n = n; a.m = m; a.dz = dz; a.ldn = ldn;
         a.x = x + (size_t)f0 * n; a.P = P + (size_t)f0 * n * n;
         a.u = u ? u + (size_t)f0 * 2 : nullptr; a.z = z ? z + (size_t)f0 * dz : nullptr;
         a.status = status + f0;
         double *p = ws;
         a.U = p; p += lay.U * Fb; a.X = p; p += lay.X * Fb; a.Y = p; p += lay.Y * Fb; a.H = p; p += lay.H * Fb;
-        a.S = p; p += lay.S * Fb; a.Kt = p; p += lay.Kt * Fb;
+        a.Kt = p; p += lay.Kt * Fb;
         a.Pbar = p; p += lay.Pbar * Fb; a.xbar = p; p += lay.xbar * Fb;
         double *xnew = p; p += lay.xnew * Fb;
         a.zhat = p; a.wm = wm; a.wc = wc;
@@ -573,58 +653,67 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
         a.var_dist = params_h[6]; a.var_angle = params_h[7];
         for (int i = 0; i < 9; ++i) a.Q[i] = params_h[8 + i];
         AugRun run{h, st, Fb};
-        const long long nn = (long long)n * n, mn = (long long)m * n;
-        const dim3 gew(Fb < 64 ? ew : 8, Fb);
-        // sigma points of (x, P)
-        LSLAM_LAUNCH(aug_scale_upper_kernel, gew, 256, 0, st, (const double *)a.P, nn, a.U, nn, n, c, (const int32_t *)a.status);
-        run.chol(a.U, nn, n, a.status, LSLAM_UKF_ST_SIGMA);
-        LSLAM_LAUNCH(aug_sigmas_kernel, gew, 256, 0, st, a, (const double *)a.x);
-        h->launches += 2;
+        const long long nn = (long long)n * n, nl = (long long)n * ldn, ml = (long long)m * ldn;
+        const dim3 gew(Fb < 64 ? ew : 8, Fb), gcol((n + 31) / 32, Fb);
+        const bool redraw = pred && upd && (flags & LSLAM_UKF_REDRAW);
+        // sigma points of (x, P): U^T U = (n + lambda) P.  The points themselves are not stored: every consumer
+        // recomputes them from (x, U) (aug_sigma_value)
+        LSLAM_LAUNCH(aug_scale_upper_kernel, gew, 256, 0, st, (const double *)a.P, nn, n, a.U, nl, ldn, n, c, (const int32_t *)a.status);
+        h->launches++;
+        AUG_TRY(run.chol(a.U, nl, ldn, n, a.status, LSLAM_UKF_ST_SIGMA));
+        const double *xs = a.x;                                   // centre of the sigma points hx sees, and its stride
+        int xs_stride = n;
+        bool hx_from_U = true;
         if (pred) {
-            LSLAM_LAUNCH(aug_fx_kernel, dim3((m + 127) / 128, Fb), 128, 0, st, a);
-            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3((n + 31) / 32, Fb), 256, kAugMeanSmem, st, a, (const double *)a.X, n, 0, 0, a.xbar, a.Y);
-            LSLAM_LAUNCH(aug_fill_noise_kernel, gew, 256, 0, st, a, a.Pbar, n, 0);
-            h->launches += 3;
-            run.gemm(a.Y, mn, n, a.Y, mn, n, a.Pbar, nn, n, n, n, m, wc0 - wi, wi, 1.0, a.status, 1);
-            if (upd && (flags & LSLAM_UKF_REDRAW)) {
-                LSLAM_LAUNCH(aug_scale_upper_kernel, gew, 256, 0, st, (const double *)a.Pbar, nn, a.U, nn, n, c, (const int32_t *)a.status);
-                run.chol(a.U, nn, n, a.status, LSLAM_UKF_ST_REDRAW);
-                LSLAM_LAUNCH(aug_sigmas_kernel, gew, 256, 0, st, a, (const double *)a.xbar);
-                LSLAM_LAUNCH(aug_mean_resid_kernel, dim3((n + 31) / 32, Fb), 256, kAugMeanSmem, st, a, (const double *)a.X, n, 0, 1, a.xbar, a.Y);
-                h->launches += 3;
+            // fx, circular mean, residuals in one pass over the factor; X kept only if hx needs the fx'd points
+            LSLAM_LAUNCH(aug_sigma_resid_kernel, gcol, 256, kAugMeanSmem, st, a, (const double *)a.x, n, 1, 0, (upd && !redraw) ? a.X : nullptr);
+            h->launches++;
+            // Pbar = Y^T diag(Wc) Y + Q; with a re-draw the same epilogue also writes (n + lambda) Pbar, the matrix
+            // the next Cholesky factors, into U
+            run.noise = 1; for (int i = 0; i < 9; ++i) run.nq[i] = a.Q[i];
+            if (redraw) { run.C2 = a.U; run.sC2 = nl; run.ldc2 = ldn; run.scale2 = c; }
+            AUG_TRY(run.gemm(a.Y, ml, ldn, a.Y, ml, ldn, a.Pbar, nl, ldn, n, n, m, wc0 - wi, wi, 0.0, a.status, 1));
+            if (redraw) {
+                AUG_TRY(run.chol(a.U, nl, ldn, n, a.status, LSLAM_UKF_ST_REDRAW));
+                LSLAM_LAUNCH(aug_sigma_resid_kernel, gcol, 256, kAugMeanSmem, st, a, (const double *)a.xbar, ldn, 0, 1, (double *)nullptr);
+                h->launches++;
+                xs = a.xbar; xs_stride = ldn;
+            } else {
+                hx_from_U = false;
             }
         } else {
-            LSLAM_CUDA_TRY(h, cudaMemcpyAsync(a.xbar, a.x, sizeof(double) * (size_t)Fb * n, cudaMemcpyDeviceToDevice, st));
-            LSLAM_CUDA_TRY(h, cudaMemcpyAsync(a.Pbar, a.P, sizeof(double) * (size_t)Fb * nn, cudaMemcpyDeviceToDevice, st));
-            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3((n + 31) / 32, Fb), 256, kAugMeanSmem, st, a, (const double *)a.X, n, 0, 1, a.xbar, a.Y);
+            LSLAM_CUDA_TRY(h, cudaMemcpy2DAsync(a.xbar, sizeof(double) * ldn, a.x, sizeof(double) * n, sizeof(double) * n, (size_t)Fb,
+                                                cudaMemcpyDeviceToDevice, st));
+            LSLAM_CUDA_TRY(h, cudaMemcpy2DAsync(a.Pbar, sizeof(double) * ldn, a.P, sizeof(double) * n, sizeof(double) * n, (size_t)Fb * n,
+                                                cudaMemcpyDeviceToDevice, st));
+            LSLAM_LAUNCH(aug_sigma_resid_kernel, gcol, 256, kAugMeanSmem, st, a, (const double *)a.x, n, 0, 1, (double *)nullptr);
             h->launches++;
         }
         const double *xres = a.xbar;
         if (upd) {
-            const int n1 = n + 1;                                 // W: dz x (n + 1), right-hand sides [Pzx | r]
-            const long long zz = (long long)dz * dz, zn = (long long)dz * n1, mz = (long long)m * dz;
-            LSLAM_LAUNCH(aug_hx_kernel, gew, 256, 0, st, a);
-            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3((dz + 31) / 32, Fb), 256, kAugMeanSmem, st, a, (const double *)a.H, dz, 1, 0, a.zhat, a.H);
-            LSLAM_LAUNCH(aug_fill_noise_kernel, gew, 256, 0, st, a, a.S, dz, 1);
+            const int n1 = ldn;                                   // W: dz x (n + 1), right-hand sides [Pzx | r]
+            const long long zn = (long long)dz * n1, mz = (long long)m * dz;
+            LSLAM_LAUNCH(aug_hx_kernel, gew, 256, 0, st, a, xs, xs_stride, hx_from_U ? 1 : 0);
+            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3((dz + 31) / 32, Fb), 256, kAugMeanSmem, st, a, (const double *)a.H, dz, dz, 1, 0, a.zhat, dz, a.H);
             LSLAM_LAUNCH(aug_innovation_kernel, dim3(Fb), 256, 0, st, a);
-            h->launches += 4;
-            run.gemm(a.H, mz, dz, a.H, mz, dz, a.S, zz, dz, dz, dz, m, wc0 - wi, wi, 1.0, a.status, 1);   // S (upper)
-            run.gemm(a.H, mz, dz, a.Y, mn, n, a.Kt, zn, n1, dz, n, m, wc0 - wi, wi, 0.0, a.status, 0);   // Pzx
-            // Cholesky of S into U (dz x dz; a.U keeps its n * n stride per filter)
-            LSLAM_LAUNCH(aug_scale_upper_kernel, gew, 256, 0, st, (const double *)a.S, zz, a.U, nn, dz, 1.0, (const int32_t *)a.status);
-            h->launches++;
-            run.chol(a.U, nn, dz, a.status, LSLAM_UKF_ST_S);
+            h->launches += 3;
+            // S = E^T diag(Wc) E + R straight into U (pitch dz; a.U keeps its n * ldn stride per filter), where its
+            // Cholesky is taken in place - S itself is not needed again (W-form update)
+            run.noise = 2; run.nq[0] = a.var_dist; run.nq[1] = a.var_angle;
+            AUG_TRY(run.gemm(a.H, mz, dz, a.H, mz, dz, a.U, nl, dz, dz, dz, m, wc0 - wi, wi, 0.0, a.status, 1));   // S (upper)
+            AUG_TRY(run.gemm(a.H, mz, dz, a.Y, ml, ldn, a.Kt, zn, n1, dz, n, m, wc0 - wi, wi, 0.0, a.status, 0));  // Pzx
+            AUG_TRY(run.chol(a.U, nl, dz, dz, a.status, LSLAM_UKF_ST_S));
             for (int jb = 0; jb < dz; jb += 32) {                 // U^T W = [Pzx | r]
                 const int nb = dz - jb < 32 ? dz - jb : 32;
                 if (jb > 0)
-                    run.gemm(a.U + jb, nn, dz, a.Kt, zn, n1, a.Kt + (size_t)jb * n1, zn, n1, nb, n1, jb, 0.0, -1.0, 1.0, a.status, 0);
-                LSLAM_LAUNCH(aug_trsm_block_kernel, dim3((n1 + 255) / 256, Fb), 256, kAugBlockSmem, st, (const double *)a.U, nn, dz,
+                    AUG_TRY(run.gemm(a.U + jb, nl, dz, a.Kt, zn, n1, a.Kt + (size_t)jb * n1, zn, n1, nb, n1, jb, 0.0, -1.0, 1.0, a.status, 0));
+                LSLAM_LAUNCH(aug_trsm_block_kernel, dim3((n1 + 255) / 256, Fb), 256, kAugBlockSmem, st, (const double *)a.U, nl, dz,
                              a.Kt, zn, n1, n1, jb, nb, 0, (const int32_t *)a.status);
                 h->launches++;
             }
             LSLAM_LAUNCH(aug_update_x_kernel, dim3((n + 31) / 32, Fb), 256, kAugUpdateXSmem, st, a, xnew);
             h->launches++;
-            run.gemm(a.Kt, zn, n1, a.Kt, zn, n1, a.Pbar, nn, n, n, n, dz, 0.0, -1.0, 1.0, a.status, 1);   // P = Pbar - W^T W (upper; commit mirrors)
+            AUG_TRY(run.gemm(a.Kt, zn, n1, a.Kt, zn, n1, a.Pbar, nl, ldn, n, n, dz, 0.0, -1.0, 1.0, a.status, 1));   // P = Pbar - W^T W (upper; commit mirrors)
             xres = xnew;
         }
         LSLAM_LAUNCH(aug_commit_kernel, gew, 256, 0, st, a, xres, (const double *)a.Pbar);

@@ -23,6 +23,7 @@
 // stored k-major ("TN"), which is how the sigma-point arrays and the factor rows lie in memory.
 #pragma once
 #include "lslam_core.cuh"
+#include "async_copy.cuh"
 #include "ransac.cuh"
 #include "ukf.cuh"
 
@@ -45,7 +46,28 @@ struct AugGemm {
     double alpha, beta, w0;
     const int32_t *skip;            // per-filter status: non-zero -> leave C alone (may be null)
     int upper;                      // 1: C is square and only its upper triangle (j >= i) is computed / stored
+    // epilogue extras (fused former elementwise passes):
+    int noise;                      // 1: + nq[3 i + j] on the 3 x 3 pose block (Q);  2: + nq[i & 1] on the diagonal (R)
+    double nq[9];
+    double *C2;                     // second output C2[i, j] = scale2 * C[i, j] (the matrix the next Cholesky factors), or null
+    long long sC2;
+    int ldc2;
+    double scale2;
 };
+
+// one output element: C = beta C + alpha acc (+ the central-weight term) (+ noise), optional scaled copy
+__device__ __forceinline__ void aug_gemm_store(const AugGemm &g, double *C, double *C2, const double *B, int i, int j, double a0,
+                                               double accv)
+{
+    double *c = C + (size_t)i * g.ldc + j;
+    double v = g.alpha * accv;
+    if (g.w0 != 0.0) v = fma(a0, B[j], v);
+    v = (g.beta == 0.0 ? 0.0 : g.beta * *c) + v;
+    if (g.noise == 1) { if (i < 3 && j < 3) v = __dadd_rn(v, g.nq[i * 3 + j]); }
+    else if (g.noise == 2) { if (i == j) v = __dadd_rn(v, g.nq[i & 1]); }
+    *c = v;
+    if (C2 != nullptr) C2[(size_t)i * g.ldc2 + j] = __dmul_rn(g.scale2, v);
+}
 
 constexpr int kAugTile = 64, kAugBK = 16, kAugStages = 3;
 constexpr size_t aug_gemm_smem(int TM) { return (size_t)kAugStages * kAugBK * (TM + kAugTile) * sizeof(double); }
@@ -80,7 +102,7 @@ __global__ void __launch_bounds__(256) aug_gemm_tn_kernel(const AugGemm g)
     const int i0 = blockIdx.y * TM, j0 = blockIdx.x * kAugTile;
     if (g.upper && i0 > j0 + kAugTile - 1) return;
     const double *A = g.A + (size_t)f * g.sA, *B = g.B + (size_t)f * g.sB;
-    double *C = g.C + (size_t)f * g.sC;
+    double *C = g.C + (size_t)f * g.sC, *C2 = g.C2 ? g.C2 + (size_t)f * g.sC2 : nullptr;
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
     const int ntiles = (g.K + kAugBK - 1) / kAugBK;
     auto issue = [&](int t) {
@@ -140,10 +162,7 @@ __global__ void __launch_bounds__(256) aug_gemm_tn_kernel(const AugGemm g)
         for (int b = 0; b < 4; ++b) {
             const int j = j0 + 32 * (b >> 1) + 2 * tx + (b & 1);
             if (j >= g.N || (g.upper && j < i)) continue;
-            double *c = C + (size_t)i * g.ldc + j;
-            double v = g.alpha * acc[a][b];
-            if (g.w0 != 0.0) v = fma(a0, B[j], v);
-            *c = (g.beta == 0.0 ? 0.0 : g.beta * *c) + v;
+            aug_gemm_store(g, C, C2, B, i, j, a0, acc[a][b]);
         }
     }
 }
@@ -197,7 +216,7 @@ __global__ void __launch_bounds__(32 * WARPS_M * WARPS_N) aug_gemm_dmma_kernel(c
     const int i0 = blockIdx.y * TM, j0 = blockIdx.x * TN;
     if (g.upper && i0 > j0 + TN - 1) return;
     const double *A = g.A + (size_t)f * g.sA, *B = g.B + (size_t)f * g.sB;
-    double *C = g.C + (size_t)f * g.sC;
+    double *C = g.C + (size_t)f * g.sC, *C2 = g.C2 ? g.C2 + (size_t)f * g.sC2 : nullptr;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int wm0 = (warp / WARPS_N) * WM, wn0 = (warp % WARPS_N) * WN;
     // fragment liveness (warp-uniform): an 8 x 8 fragment is skipped when it lies outside C or, for an
@@ -279,10 +298,147 @@ __global__ void __launch_bounds__(32 * WARPS_M * WARPS_N) aug_gemm_dmma_kernel(c
             for (int q = 0; q < 2; ++q) {
                 const int j = j0 + wn0 + 8 * b + 2 * frag + q;
                 if (j >= g.N || (g.upper && j < i)) continue;
-                double *c = C + (size_t)i * g.ldc + j;
-                double v = g.alpha * acc[a][b][q];
-                if (g.w0 != 0.0) v = fma(a0, B[j], v);
-                *c = (g.beta == 0.0 ? 0.0 : g.beta * *c) + v;
+                aug_gemm_store(g, C, C2, B, i, j, a0, acc[a][b][q]);
+            }
+    }
+}
+
+// ---- the DMMA GEMM fed by the TMA engine (default) ---------------------------------------------------------
+// ncu on the cp.async version above (profiles/r01m_aug_gemm_ncu_summary.txt): DMMA is 7.6 % of the issued
+// warp-instructions, the 64-bit address arithmetic and predicates of the 8-byte LDGSTS copies are 70 %, and
+// the tensor pipe is 58 % busy.  Here one elected lane of a PRODUCER warp issues two tiled TMA copies per
+// k-tile (cp.async.bulk.tensor.3d, SASS UTMALDG): boxes of 16 k-rows x (T + 4) columns of the k-major
+// operands, through tensor maps the host encodes per call (dims = (columns, K, filters), so rows >= K and
+// columns >= M / N arrive as zeros from the copy engine - no predicates, no address arithmetic in the
+// kernel).  The 4 extra box columns make the shared-memory row pitch T + 4 = 4 (mod 16) doubles, the
+// bank-conflict-free pitch of the fragment loads (see above); they are over-fetch, never used.  The
+// consumer warps only wait (mbarrier full[s]), load fragments, issue DMMAs and release the stage
+// (mbarrier empty[s], one arrival per live warp): no block-wide barrier inside the k-loop.
+// Needs 16-byte aligned operands with even pitches - lslam_ukf_aug_step pads the workspace pitch of the
+// n-column arrays to n + 1 (n = 3 + 2L is odd).
+constexpr int kAugTmaStages = 4;
+template <int TM, int TN> constexpr size_t aug_tma_smem()
+{
+    return (size_t)kAugTmaStages * kAugBK * (TM + 4 + TN + 4) * sizeof(double) + 2 * kAugTmaStages * sizeof(Mbar) + 128;
+}
+
+template <int TM, int TN, int WARPS_M, int WARPS_N>
+__global__ void __launch_bounds__(32 * (WARPS_M * WARPS_N + 1))
+aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const LSLAM_GRID_CONSTANT Tmap mapB)
+{
+    LSLAM_SMEM_DECL;
+    constexpr int NW = WARPS_M * WARPS_N, WM = TM / WARPS_M, WN = TN / WARPS_N, FM = WM / 8, FN = WN / 8;
+    constexpr int LDA = TM + 4, LDB = TN + 4, STAGE = kAugBK * (LDA + LDB), S = kAugTmaStages;
+    static_assert(TM % 16 == 0 && TN % 16 == 0 && WM % 8 == 0 && WN % 8 == 0, "tile shape");
+    static_assert((kAugBK * LDA * sizeof(double)) % 128 == 0 && (kAugBK * LDB * sizeof(double)) % 128 == 0, "TMA box alignment");
+    const int f = blockIdx.z;
+    if (g.skip != nullptr && g.skip[f] != 0) return;
+    const int i0 = blockIdx.y * TM, j0 = blockIdx.x * TN;
+    if (g.upper && i0 > j0 + TN - 1) return;
+    // 128-byte aligned tile ring, then the barriers
+    // (the pad is computed on the shared-window address so that the pointer stays a SHARED pointer for the
+    // compiler: fragment loads must be LDS, not generic LD)
+#ifndef LSLAM_EMU
+    double *sm = reinterpret_cast<double *>(smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u));
+#else
+    double *sm = reinterpret_cast<double *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+#endif
+    Mbar *full = reinterpret_cast<Mbar *>(sm + (size_t)S * STAGE), *empty = full + S;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // fragment liveness per consumer warp (see aug_gemm_dmma_kernel); a warp without a live fragment leaves
+    auto live_mask = [&](int w) {
+        const int m0 = (w / WARPS_N) * WM, n0 = (w % WARPS_N) * WN;
+        unsigned live = 0;
+        for (int a = 0; a < FM; ++a)
+            for (int b = 0; b < FN; ++b) {
+                const int fi = i0 + m0 + 8 * a, fj = j0 + n0 + 8 * b;
+                if (fi < g.M && fj < g.N && !(g.upper && fi > fj + 7)) live |= 1u << (a * FN + b);
+            }
+        return live;
+    };
+    if (threadIdx.x == 0) {
+        int nlive = 0;
+        for (int w = 0; w < NW; ++w) nlive += live_mask(w) != 0;
+        for (int s = 0; s < S; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], nlive > 0 ? nlive : 1); }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    const int ntiles = (g.K + kAugBK - 1) / kAugBK;
+    if (warp == NW) {                                                 // ---- producer
+        if (lane == 0) {
+            bool any = false;
+            for (int w = 0; w < NW; ++w) any = any || live_mask(w) != 0;
+            if (any)
+                for (int t = 0; t < ntiles; ++t) {
+                    const int s = t % S;
+                    if (t >= S) mbar_wait(&empty[s], ((t / S) - 1) & 1);
+                    double *as = sm + (size_t)s * STAGE, *bs = as + kAugBK * LDA;
+                    mbar_expect_tx(&full[s], (unsigned)(STAGE * sizeof(double)));
+                    tma_load_3d(as, &mapA, i0, t * kAugBK, f, &full[s]);
+                    tma_load_3d(bs, &mapB, j0, t * kAugBK, f, &full[s]);
+                }
+        }
+        return;
+    }
+    const int wm0 = (warp / WARPS_N) * WM, wn0 = (warp % WARPS_N) * WN;
+    const unsigned live = live_mask(warp);
+    if (live == 0) return;
+    const bool fullw = live == (FM * FN == 32 ? 0xffffffffu : (1u << (FM * FN)) - 1u);
+    double acc[FM][FN][2];
+#pragma unroll
+    for (int a = 0; a < FM; ++a)
+#pragma unroll
+        for (int b = 0; b < FN; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+    const int frag = (lane & 3), fcol = (lane >> 2);
+    for (int t = 0; t < ntiles; ++t) {
+        const int s = t % S;
+        mbar_wait(&full[s], (t / S) & 1);
+        const double *as = sm + (size_t)s * STAGE + frag * LDA + wm0 + fcol;
+        const double *bs = sm + (size_t)s * STAGE + kAugBK * LDA + frag * LDB + wn0 + fcol;
+        // fragments double-buffered in registers: the loads of k-step q + 1 are in flight under the DMMAs of q
+        double av[2][FM], bv[2][FN];
+#pragma unroll
+        for (int a = 0; a < FM; ++a) av[0][a] = as[8 * a];
+#pragma unroll
+        for (int b = 0; b < FN; ++b) bv[0][b] = bs[8 * b];
+#pragma unroll
+        for (int q = 0; q < kAugBK / 4; ++q) {
+            if (q + 1 < kAugBK / 4) {
+#pragma unroll
+                for (int a = 0; a < FM; ++a) av[(q + 1) & 1][a] = as[4 * (q + 1) * LDA + 8 * a];
+#pragma unroll
+                for (int b = 0; b < FN; ++b) bv[(q + 1) & 1][b] = bs[4 * (q + 1) * LDB + 8 * b];
+            }
+            if (fullw) {
+#pragma unroll
+                for (int a = 0; a < FM; ++a)
+#pragma unroll
+                    for (int b = 0; b < FN; ++b) dmma_m8n8k4(acc[a][b][0], acc[a][b][1], av[q & 1][a], bv[q & 1][b]);
+            } else {
+#pragma unroll
+                for (int a = 0; a < FM; ++a)
+#pragma unroll
+                    for (int b = 0; b < FN; ++b)
+                        if ((live >> (a * FN + b)) & 1u) dmma_m8n8k4(acc[a][b][0], acc[a][b][1], av[q & 1][a], bv[q & 1][b]);
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[s]);
+    }
+    const double *A = g.A + (size_t)f * g.sA, *B = g.B + (size_t)f * g.sB;
+    double *C = g.C + (size_t)f * g.sC, *C2 = g.C2 ? g.C2 + (size_t)f * g.sC2 : nullptr;
+#pragma unroll
+    for (int a = 0; a < FM; ++a) {
+        const int i = i0 + wm0 + 8 * a + fcol;
+        if (i >= g.M) continue;
+        const double a0 = g.w0 != 0.0 ? g.w0 * A[i] : 0.0;
+#pragma unroll
+        for (int b = 0; b < FN; ++b)
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const int j = j0 + wn0 + 8 * b + 2 * frag + q;
+                if (j >= g.N || (g.upper && j < i)) continue;
+                aug_gemm_store(g, C, C2, B, i, j, a0, acc[a][b][q]);
             }
     }
 }
@@ -401,10 +557,11 @@ __global__ void __launch_bounds__(256) aug_trsm_block_kernel(const double *Ubase
 // ---- elementwise stages -----------------------------------------------------------------------
 struct AugArgs {
     int F, L, n, m, dz;             // filters in this batch, landmarks, 3 + 2L, 2n + 1, 2L
+    int ldn;                        // row pitch of the workspace arrays with n columns (U, X, Y, Pbar): n + 1, even
     double *x, *P;                  // [F, n], [F, n, n] in / out
     const double *u, *z;            // [F, 2], [F, L, 2]
     int32_t *status;                // [F]
-    double *U, *X, *Y, *H, *S, *Kt, *Pbar, *xbar, *zhat, *wm, *wc;   // workspace (Kt: W = U^-T [Pzx | r], dz x (n + 1))
+    double *U, *X, *Y, *H, *Kt, *Pbar, *xbar, *zhat, *wm, *wc;   // workspace (Kt: W = U^-T [Pzx | r], dz x (n + 1))
     double dt, half_r, r_over_l, cscale, var_dist, var_angle;
     double Q[9];
 };
@@ -416,56 +573,101 @@ __global__ void aug_weights_kernel(double *wm, double *wc, int m, double wi, dou
     if (k < m) { wm[k] = k ? wi : wm0; wc[k] = k ? wi : wc0; }
 }
 
-// dst = scale * src on the upper triangle (lower zeroed), n x n
-__global__ void aug_scale_upper_kernel(const double *src, long long s_src, double *dst, long long s_dst, int n, double scale,
-                                       const int32_t *status)
+// dst = scale * src on the upper triangle (lower zeroed), n x n with row pitches lds / ldd
+__global__ void aug_scale_upper_kernel(const double *src, long long s_src, int lds, double *dst, long long s_dst, int ldd, int n,
+                                       double scale, const int32_t *status)
 {
     const int f = blockIdx.y;
     if (status[f] != 0) return;
     src += (size_t)f * s_src; dst += (size_t)f * s_dst;
     for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < (long long)n * n; e += (long long)gridDim.x * blockDim.x) {
         const int r = (int)(e / n), c = (int)(e % n);
-        dst[e] = c >= r ? __dmul_rn(scale, src[e]) : 0.0;
+        dst[(size_t)r * ldd + c] = c >= r ? __dmul_rn(scale, src[(size_t)r * lds + c]) : 0.0;
     }
 }
 
-// sigma points of (x0, U) [MerweScaledSigmaPoints.sigma_points]: rows x0, x0 + U[k], x0 - U[k]
-__global__ void aug_sigmas_kernel(const AugArgs a, const double *x0)
+// ---- fused sigma points -> fx -> mean -> residuals (state side) ---------------------------------------------
+// The sigma points of (x0, U) are never stored: element (k, c) is x0[c], x0[c] + U[k-1, c] or x0[c] - U[k-n-1, c]
+// (MerweScaledSigmaPoints.sigma_points; U upper triangular - entries left of the diagonal are taken as 0
+// whatever the memory holds), so every pass recomputes it from the factor (n x n) instead of reading a
+// stored (2n+1) x n array.
+__device__ __forceinline__ double aug_sigma_value(const double *x, const double *U, int ld, int n, int k, int c)
 {
-    const int f = blockIdx.y;
-    if (a.status[f] != 0) return;
-    const int n = a.n;
-    const double *x = x0 + (size_t)f * n, *U = a.U + (size_t)f * n * n;
-    double *X = a.X + (size_t)f * a.m * n;
-    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < (long long)a.m * n; e += (long long)gridDim.x * blockDim.x) {
-        const int k = (int)(e / n), c = (int)(e % n);
-        double v = x[c];
-        if (k >= 1 && k <= n) v = __dadd_rn(v, U[(size_t)(k - 1) * n + c]);
-        else if (k > n) v = __dsub_rn(v, U[(size_t)(k - n - 1) * n + c]);
-        X[e] = v;
+    double v = x[c];
+    if (k >= 1) {
+        const int r = k <= n ? k - 1 : k - n - 1;
+        const double uv = c >= r ? U[(size_t)r * ld + c] : 0.0;
+        v = k <= n ? __dadd_rn(v, uv) : __dsub_rn(v, uv);
     }
+    return v;
 }
 
-// fx on the pose columns of every sigma point: the differential-drive transition (UKFMethods.py:17-24);
-// landmarks unchanged
-__global__ void aug_fx_kernel(const AugArgs a)
+// pose component c (< 3) of fx(sigma point k): the differential-drive transition (UKFMethods.py:17-24),
+// x' = x + dt * B(theta) u,  B = [[R/2 cos, R/2 cos], [R/2 sin, R/2 sin], [-R/L, R/L]]  (oracle/ukf.py order)
+__device__ __forceinline__ double aug_fx_pose(const AugArgs &a, const double *x, const double *U, int k, int c, double ul, double ur)
 {
-    const int f = blockIdx.y;
-    if (a.status[f] != 0) return;
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= a.m) return;
-    double *s = a.X + ((size_t)f * a.m + k) * a.n;
-    const double ul = a.u ? a.u[2 * f] : 0.0, ur = a.u ? a.u[2 * f + 1] : 0.0;
+    const double p0 = aug_sigma_value(x, U, a.ldn, a.n, k, 0), p1 = aug_sigma_value(x, U, a.ldn, a.n, k, 1),
+                 p2 = aug_sigma_value(x, U, a.ldn, a.n, k, 2);
     double sn, cs;
-    sincos(s[2], &sn, &cs);
-    // x' = x + dt * B(theta) u,  B = [[R/2 cos, R/2 cos], [R/2 sin, R/2 sin], [-R/L, R/L]]  (oracle/ukf.py order)
+    sincos(p2, &sn, &cs);
     const double b0 = __dmul_rn(a.half_r, cs), b1 = __dmul_rn(a.half_r, sn);
     const double d0 = __dadd_rn(__dmul_rn(b0, ul), __dmul_rn(b0, ur));
     const double d1 = __dadd_rn(__dmul_rn(b1, ul), __dmul_rn(b1, ur));
     const double d2 = __dadd_rn(__dmul_rn(-a.r_over_l, ul), __dmul_rn(a.r_over_l, ur));
-    s[0] = __dadd_rn(s[0], __dmul_rn(a.dt, d0));
-    s[1] = __dadd_rn(s[1], __dmul_rn(a.dt, d1));
-    s[2] = __dadd_rn(s[2], __dmul_rn(a.dt, d2));
+    return c == 0 ? __dadd_rn(p0, __dmul_rn(a.dt, d0)) : c == 1 ? __dadd_rn(p1, __dmul_rn(a.dt, d1)) : __dadd_rn(p2, __dmul_rn(a.dt, d2));
+}
+
+// One CTA per (32-column group, filter), 8 warps over the sigma points, lanes across 32 consecutive columns
+// (coalesced rows of U and Y).  Pass 1 (skipped when the mean is given - residuals of re-drawn points about
+// the prior): weighted column sums, circular for the heading (column 2), partial sums of the 8 warps added
+// in warp order; pass 2: Y[k] = residual_x(sigma_k, mean), and the points themselves into Xout if the
+// caller still needs them (update without re-draw).
+__global__ void __launch_bounds__(256) aug_sigma_resid_kernel(const AugArgs a, const double *x0, int sx, int do_fx, int mean_given,
+                                                              double *Xout)
+{
+    LSLAM_SMEM_DECL;
+    double *part = reinterpret_cast<double *>(smem_raw);             // [8][32][2], then mu at [512 + lane]
+    const int f = blockIdx.y;
+    if (a.status[f] != 0) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n = a.n, ld = a.ldn;
+    const int c = blockIdx.x * 32 + lane;
+    const bool live = c < n, ang = c == 2, posefx = do_fx && c < 3;
+    const double *x = x0 + (size_t)f * sx, *U = a.U + (size_t)f * n * ld;
+    double *mean = a.xbar + (size_t)f * ld, *Y = a.Y + (size_t)f * a.m * ld;
+    const double ul = a.u ? a.u[2 * f] : 0.0, ur = a.u ? a.u[2 * f + 1] : 0.0;
+    if (!mean_given) {
+        double s0 = 0.0, s1 = 0.0;
+        if (live) {
+            for (int k = warp; k < a.m; k += 8) {
+                const double v = posefx ? aug_fx_pose(a, x, U, k, c, ul, ur) : aug_sigma_value(x, U, ld, n, k, c), w = a.wm[k];
+                if (ang) { double sn, cs; sincos(v, &sn, &cs); s0 = fma(sn, w, s0); s1 = fma(cs, w, s1); }
+                else s0 = fma(v, w, s0);
+            }
+        }
+        part[(warp * 32 + lane) * 2] = s0; part[(warp * 32 + lane) * 2 + 1] = s1;
+        __syncthreads();
+        if (warp == 0) {
+            double t0 = 0.0, t1 = 0.0;
+            for (int w = 0; w < 8; ++w) { t0 = __dadd_rn(t0, part[(w * 32 + lane) * 2]); t1 = __dadd_rn(t1, part[(w * 32 + lane) * 2 + 1]); }
+            const double mu = ang ? atan2(t0, t1) : t0;
+            part[512 + lane] = mu;
+            if (live) mean[c] = mu;
+        }
+        __syncthreads();
+    } else {
+        if (warp == 0) part[512 + lane] = live ? mean[c] : 0.0;
+        __syncthreads();
+    }
+    if (!live) return;
+    const double mu = part[512 + lane];
+    double *X = Xout ? Xout + (size_t)f * a.m * ld : nullptr;
+    for (int k = warp; k < a.m; k += 8) {
+        const double v = posefx ? aug_fx_pose(a, x, U, k, c, ul, ur) : aug_sigma_value(x, U, ld, n, k, c);
+        double d = __dsub_rn(v, mu);
+        if (ang) d = ukf_normalize_angle(d);
+        Y[(size_t)k * ld + c] = d;
+        if (X) X[(size_t)k * ld + c] = v;
+    }
 }
 
 // weighted column means of V [m x cols] with circular means on the angle columns (state: column 2;
@@ -473,8 +675,8 @@ __global__ void aug_fx_kernel(const AugArgs a)
 // One CTA per (32-column group, filter): warp w sums rows w, w+8, ... with lanes across 32 consecutive
 // columns (coalesced), the 8 partial sums are added in warp order, then every warp writes the residuals
 // of its rows.  mean_given: the mean is an input (residuals of re-drawn sigma points about the prior).
-__global__ void __launch_bounds__(256) aug_mean_resid_kernel(const AugArgs a, const double *Vbase, int cols, int is_meas,
-                                                             int mean_given, double *mean_base, double *Rbase)
+__global__ void __launch_bounds__(256) aug_mean_resid_kernel(const AugArgs a, const double *Vbase, int cols, int ld, int is_meas,
+                                                             int mean_given, double *mean_base, int mean_stride, double *Rbase)
 {
     LSLAM_SMEM_DECL;
     double *part = reinterpret_cast<double *>(smem_raw);             // [8][32][2], then mu at [512 + lane]
@@ -483,14 +685,14 @@ __global__ void __launch_bounds__(256) aug_mean_resid_kernel(const AugArgs a, co
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + lane;
     const bool live = c < cols;
-    const double *V = Vbase + (size_t)f * a.m * cols;
-    double *mean = mean_base + (size_t)f * cols, *R = Rbase + (size_t)f * a.m * cols;
+    const double *V = Vbase + (size_t)f * a.m * ld;
+    double *mean = mean_base + (size_t)f * mean_stride, *R = Rbase + (size_t)f * a.m * ld;
     const bool ang = is_meas ? (c & 1) : (c == 2);
     if (!mean_given) {
         double s0 = 0.0, s1 = 0.0;
         if (live) {
             for (int k = warp; k < a.m; k += 8) {
-                const double v = V[(size_t)k * cols + c], w = a.wm[k];
+                const double v = V[(size_t)k * ld + c], w = a.wm[k];
                 if (ang) { double sn, cs; sincos(v, &sn, &cs); s0 = fma(sn, w, s0); s1 = fma(cs, w, s1); }
                 else s0 = fma(v, w, s0);
             }
@@ -512,40 +714,51 @@ __global__ void __launch_bounds__(256) aug_mean_resid_kernel(const AugArgs a, co
     if (!live) return;
     const double mu = part[512 + lane];
     for (int k = warp; k < a.m; k += 8) {
-        double d = __dsub_rn(V[(size_t)k * cols + c], mu);
+        double d = __dsub_rn(V[(size_t)k * ld + c], mu);
         if (ang) d = ukf_normalize_angle(d);
-        R[(size_t)k * cols + c] = d;
+        R[(size_t)k * ld + c] = d;
     }
 }
 
 // hx of every sigma point: (range, bearing) of every landmark read from the state (oracle/ukf.py
-// transfer_function_augmented, UKFMethods.py:26-34)
-__global__ void aug_hx_kernel(const AugArgs a)
+// transfer_function_augmented, UKFMethods.py:26-34).  from_U: the sigma points are those of (x0, U) and are
+// recomputed from the factor (one thread does the + and the - point of a factor row: the row is read once);
+// otherwise they are read from the stored array X.
+__device__ __forceinline__ void aug_hx_one(double s0, double s1, double s2, double lx, double ly, double *h)
 {
-    const int f = blockIdx.y;
-    if (a.status[f] != 0) return;
-    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < (long long)a.m * a.L; e += (long long)gridDim.x * blockDim.x) {
-        const int k = (int)(e / a.L), l = (int)(e % a.L);
-        const double *s = a.X + ((size_t)f * a.m + k) * a.n;
-        const double dx = __dsub_rn(s[3 + 2 * l], s[0]), dy = __dsub_rn(s[4 + 2 * l], s[1]);
-        double *h = a.H + ((size_t)f * a.m + k) * a.dz + 2 * l;
-        h[0] = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
-        h[1] = ukf_normalize_angle(__dsub_rn(atan2(dy, dx), s[2]));
-    }
+    const double dx = __dsub_rn(lx, s0), dy = __dsub_rn(ly, s1);
+    h[0] = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+    h[1] = ukf_normalize_angle(__dsub_rn(atan2(dy, dx), s2));
 }
-
-// C = diag block: Pbar <- Q on the pose block, zero elsewhere; S <- R = diag(var_dist, var_angle, ...)
-__global__ void aug_fill_noise_kernel(const AugArgs a, double *Cbase, int dim, int is_meas)
+__global__ void aug_hx_kernel(const AugArgs a, const double *x0, int sx, int from_U)
 {
     const int f = blockIdx.y;
     if (a.status[f] != 0) return;
-    double *C = Cbase + (size_t)f * dim * dim;
-    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < (long long)dim * dim; e += (long long)gridDim.x * blockDim.x) {
-        const int r = (int)(e / dim), c = (int)(e % dim);
-        double v = 0.0;
-        if (is_meas) { if (r == c) v = (r & 1) ? a.var_angle : a.var_dist; }
-        else if (r < 3 && c < 3) v = a.Q[r * 3 + c];
-        C[e] = v;
+    const int n = a.n, ld = a.ldn;
+    double *H = a.H + (size_t)f * a.m * a.dz;
+    if (!from_U) {
+        for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < (long long)a.m * a.L; e += (long long)gridDim.x * blockDim.x) {
+            const int k = (int)(e / a.L), l = (int)(e % a.L);
+            const double *s = a.X + ((size_t)f * a.m + k) * ld;
+            aug_hx_one(s[0], s[1], s[2], s[3 + 2 * l], s[4 + 2 * l], H + (size_t)k * a.dz + 2 * l);
+        }
+        return;
+    }
+    const double *x = x0 + (size_t)f * sx, *U = a.U + (size_t)f * n * ld;
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < (long long)(n + 1) * a.L; e += (long long)gridDim.x * blockDim.x) {
+        const int kk = (int)(e / a.L), l = (int)(e % a.L), cx = 3 + 2 * l;
+        if (kk == 0) {
+            aug_hx_one(x[0], x[1], x[2], x[cx], x[cx + 1], H + 2 * l);
+            continue;
+        }
+        const int r = kk - 1;
+        const double *Ur = U + (size_t)r * ld;
+        const double u0 = 0 >= r ? Ur[0] : 0.0, u1 = 1 >= r ? Ur[1] : 0.0, u2 = 2 >= r ? Ur[2] : 0.0;
+        const double ux = cx >= r ? Ur[cx] : 0.0, uy = cx + 1 >= r ? Ur[cx + 1] : 0.0;
+        aug_hx_one(__dadd_rn(x[0], u0), __dadd_rn(x[1], u1), __dadd_rn(x[2], u2), __dadd_rn(x[cx], ux), __dadd_rn(x[cx + 1], uy),
+                   H + (size_t)kk * a.dz + 2 * l);
+        aug_hx_one(__dsub_rn(x[0], u0), __dsub_rn(x[1], u1), __dsub_rn(x[2], u2), __dsub_rn(x[cx], ux), __dsub_rn(x[cx + 1], uy),
+                   H + (size_t)(n + kk) * a.dz + 2 * l);
     }
 }
 
@@ -583,7 +796,7 @@ __global__ void __launch_bounds__(256) aug_update_x_kernel(const AugArgs a, doub
     if (warp == 0 && i < a.n) {
         double t = 0.0;
         for (int w = 0; w < 8; ++w) t = __dadd_rn(t, part[w][lane]);
-        xnew_base[(size_t)f * a.n + i] = __dadd_rn(a.xbar[(size_t)f * a.n + i], t);
+        xnew_base[(size_t)f * n1 + i] = __dadd_rn(a.xbar[(size_t)f * n1 + i], t);
     }
 }
 
@@ -592,11 +805,11 @@ __global__ void aug_commit_kernel(const AugArgs a, const double *xnew, const dou
 {
     const int f = blockIdx.y;
     if (a.status[f] != 0) return;
-    const long long nn = (long long)a.n * a.n;
+    const long long nn = (long long)a.n * a.n, nl = (long long)a.n * a.ldn;
     for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < nn; e += (long long)gridDim.x * blockDim.x) {
-        const int r = (int)(e / a.n), c = (int)(e % a.n);             // Pnew holds the upper triangle
-        a.P[(size_t)f * nn + e] = Pnew[(size_t)f * nn + (c >= r ? e : (long long)c * a.n + r)];
-        if (e < a.n) a.x[(size_t)f * a.n + e] = xnew[(size_t)f * a.n + e];
+        const int r = (int)(e / a.n), c = (int)(e % a.n);             // Pnew (pitch ldn) holds the upper triangle
+        a.P[(size_t)f * nn + e] = Pnew[(size_t)f * nl + (c >= r ? (long long)r * a.ldn + c : (long long)c * a.ldn + r)];
+        if (e < a.n) a.x[(size_t)f * a.n + e] = xnew[(size_t)f * a.ldn + e];
     }
 }
 

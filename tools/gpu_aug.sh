@@ -13,6 +13,6 @@ echo "== aug launch list"
 CMD="python tools/ukf_aug_one.py 200 256 1"
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $OUT/${TAG}_aug_launches.csv $CMD > $OUT/${TAG}_aug_ncu_launches.log 2>&1
 echo "launches rc=$?" ; python tools/aug_launch_summary.py $OUT/${TAG}_aug_launches.csv | tee $OUT/${TAG}_aug_launch_summary.txt
-echo "== aug ncu full (Pbar GEMM = 13th DMMA launch)"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:aug_gemm_dmma -s 12 -c 1 -f -o $OUT/${TAG}_aug_gemm $CMD > $OUT/${TAG}_aug_ncu_full.log 2>&1
+echo "== aug ncu full (Pzx GEMM = 27th GEMM launch)"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:aug_gemm_tma -s 26 -c 1 -f -o $OUT/${TAG}_aug_gemm $CMD > $OUT/${TAG}_aug_ncu_full.log 2>&1
 echo "full rc=$?"

@@ -1,5 +1,5 @@
 """Time lslam_ukf_aug_step: F augmented filters with L landmarks in the state (n = 3 + 2L).
-usage: ukf_aug_one.py [L] [F] [reps] [gemm: 0 DMMA (default), 1 DFMA]"""
+usage: ukf_aug_one.py [L] [F] [reps] [gemm: 0 DMMA+TMA (default), 1 DFMA, 2 DMMA+cp.async] [tile: 0 (default 64), 128]"""
 import sys
 
 import numpy as np
@@ -15,6 +15,8 @@ reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 eng = batch.Engine(0)
 if len(sys.argv) > 4:
     eng.set_option("ukf_aug.gemm", int(sys.argv[4]))
+if len(sys.argv) > 5:
+    eng.set_option("ukf_aug.tile", int(sys.argv[5]))
 dev = eng.device
 x, P, u, z = au.aug_case(min(F, 16), L, seed=0)
 rep = (F + len(x) - 1) // len(x)
