@@ -68,6 +68,7 @@ __device__ __forceinline__ void tma_load_3d(void *dst, const Tmap *map, int c0, 
                  ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar)) : "memory");
 }
 #define LSLAM_GRID_CONSTANT __grid_constant__
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 } // namespace lslam
 
@@ -131,6 +132,7 @@ inline void tma_load_3d(void *dst, const Tmap *m, int c0, int c1, int c2, Mbar *
     mbar_emu_check(bar);
 }
 #define LSLAM_GRID_CONSTANT
+inline void prefetch_l2(const void *) {}
 
 } // namespace lslam
 #endif

@@ -454,7 +454,7 @@ extern "C" int lslam_ukf_update(void *handle, double *x, double *P, const double
 namespace {
 struct AugLayout {
     long long per_filter;           // doubles
-    long long U, X, Y, H, Kt, Pbar, xbar, xnew, zhat;   // sizes in doubles per filter (all even: 16-byte aligned arrays)
+    long long U, X, Y, H, Kt, Pbar, Dinv, xbar, xnew, zhat;   // sizes in doubles per filter (all even: 16-byte aligned arrays)
 };
 AugLayout aug_layout(int L)
 {
@@ -463,7 +463,8 @@ AugLayout aug_layout(int L)
     AugLayout y;
     y.U = n * ldn; y.X = m * ldn; y.Y = m * ldn; y.H = m * dz; y.Kt = dz * ldn;
     y.Pbar = n * ldn; y.xbar = ldn; y.xnew = ldn; y.zhat = dz;
-    y.per_filter = y.U + y.X + y.Y + y.H + y.Kt + y.Pbar + y.xbar + y.xnew + y.zhat;
+    y.Dinv = ((n + 31) / 32) * 1024;                              // inverted 32 x 32 diagonal blocks of the factor in progress
+    y.per_filter = y.U + y.X + y.Y + y.H + y.Kt + y.Pbar + y.Dinv + y.xbar + y.xnew + y.zhat;
     return y;
 }
 constexpr int kAugMaxBatch = 32768;
@@ -495,7 +496,7 @@ int tmap_encode_3d(Handle *h, Tmap *map, const double *base, long long cols, lon
     if (((uintptr_t)base & 15) || (ld & 1) || (sF & 1))
         return fail(h, LSLAM_ERR_BAD_ARG, "TMA operand needs a 16-byte aligned base and even pitches (base %p, ld %lld, stride %lld)",
                     (const void *)base, ld, sF);
-    const cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)nf};
+    const cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)(rows > 0 ? rows : 1), (cuuint64_t)nf};
     const cuuint64_t strides[2] = {(cuuint64_t)ld * 8, (cuuint64_t)sF * 8};
     const cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)kAugBK, 1}, es[3] = {1, 1, 1};
     const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, (void *)base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -511,19 +512,21 @@ int tmap_encode_3d(Handle *h, Tmap *map, const double *base, long long cols, lon
 
 struct AugRun {
     Handle *h; cudaStream_t st; int F;
-    template <int TM, int TN, int WM, int WN>
+    double *Dinv = nullptr; long long sDinv = 0;                  // inverted diagonal blocks (aug_chol_diag_kernel), [F][blocks][32][32]
+    template <int TM, int TN, int WM, int WN, int S = 4, bool SOLVE = false>
     int gemm_tma(const AugGemm &g, bool &attr_set)
     {
-        auto kern = aug_gemm_tma_kernel<TM, TN, WM, WN>;
+        auto kern = aug_gemm_tma_kernel<TM, TN, WM, WN, S, SOLVE>;
+        constexpr size_t smem = aug_tma_smem<TM, TN, WN, S, SOLVE>();
         if (!attr_set) {
-            LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)aug_tma_smem<TM, TN>()));
+            LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             attr_set = true;
         }
         Tmap ma, mb;
         int rc = tmap_encode_3d(h, &ma, g.A, g.M, g.K, F, g.lda, g.sA, TM + 4);
         if (rc == LSLAM_OK) rc = tmap_encode_3d(h, &mb, g.B, g.N, g.K, F, g.ldb, g.sB, TN + 4);
         if (rc != LSLAM_OK) return rc;
-        LSLAM_LAUNCH(kern, dim3((g.N + TN - 1) / TN, (g.M + TM - 1) / TM, F), 32 * (WM * WN + 1), (aug_tma_smem<TM, TN>()), st, g, ma, mb);
+        LSLAM_LAUNCH(kern, dim3((g.N + TN - 1) / TN, (g.M + TM - 1) / TM, F), 32 * (WM * WN + 1), smem, st, g, ma, mb);
         return LSLAM_OK;
     }
     // epilogue extras of the next gemm() call (reset by it): noise 1 = + Q (nq[9]) on the pose block, 2 = + R (nq[0], nq[1])
@@ -537,7 +540,7 @@ struct AugRun {
         g.A = A; g.B = B; g.C = C; g.sA = sA; g.sB = sB; g.sC = sC; g.M = M; g.N = N; g.K = K;
         g.lda = lda; g.ldb = ldb; g.ldc = ldc; g.alpha = alpha; g.beta = beta; g.w0 = w0; g.skip = skip; g.upper = upper;
         g.noise = noise; for (int i = 0; i < 9; ++i) g.nq[i] = nq[i];
-        g.C2 = C2; g.sC2 = sC2; g.ldc2 = ldc2; g.scale2 = scale2;
+        g.C2 = C2; g.sC2 = sC2; g.ldc2 = ldc2; g.scale2 = scale2; g.Dinv = nullptr; g.sDinv = 0;
         noise = 0; C2 = nullptr;
         if (h->opt_aug_gemm == 0) {                               // DMMA fed by TMA (default)
             // CTA tile: 64 x 64 with three CTAs per SM.  ukf_aug.tile = 128 selects 128 x 128 (16 consumer warps, one
@@ -553,9 +556,9 @@ struct AugRun {
                 LSLAM_LAUNCH(kern, dim3((N + 63) / 64, 1, F), 128, (aug_dmma_smem<32, 64>()), st, g);
             } else {
                 auto kern = aug_gemm_dmma_kernel<64, 64, 2, 2>;
-                if (!h->aug_attr_set[2]) {
+                if (!h->aug_attr_set[4]) {
                     LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)aug_dmma_smem<64, 64>()));
-                    h->aug_attr_set[2] = true;
+                    h->aug_attr_set[4] = true;
                 }
                 LSLAM_LAUNCH(kern, dim3((N + 63) / 64, (M + 63) / 64, F), 128, (aug_dmma_smem<64, 64>()), st, g);
             }
@@ -569,22 +572,72 @@ struct AugRun {
         h->launches++;
         return LSLAM_OK;
     }
+    // block-row step of a blocked forward solve on the tensor pipe (SOLVE kernel):
+    //   C[0:nb, 0:N] = Dinv_blk^T (C - A^T B),  A: K x nb, B: K x N (k-major), Dinv_blk = block `blk` of this->Dinv
+    int gemm_solve(const double *A, long long sA, int lda, const double *B, long long sB, int ldb, double *C, long long sC, int ldc,
+                   int nb, int N, int K, int blk, const int32_t *skip)
+    {
+        if (nb <= 0 || N <= 0) return LSLAM_OK;
+        AugGemm g;
+        g.A = A; g.B = B; g.C = C; g.sA = sA; g.sB = sB; g.sC = sC; g.M = nb; g.N = N; g.K = K;
+        g.lda = lda; g.ldb = ldb; g.ldc = ldc; g.alpha = -1.0; g.beta = 1.0; g.w0 = 0.0; g.skip = skip; g.upper = 0;
+        g.noise = 0; for (int i = 0; i < 9; ++i) g.nq[i] = 0.0;
+        g.C2 = nullptr; g.sC2 = 0; g.ldc2 = 0; g.scale2 = 0.0;
+        g.Dinv = Dinv + (size_t)blk * 1024; g.sDinv = sDinv;
+        const int rc = gemm_tma<32, 64, 1, 4, 3, true>(g, h->aug_attr_set[2]);
+        if (rc == LSLAM_OK) h->launches++;
+        return rc;
+    }
     // in-place upper Cholesky of F matrices (dim x dim, row pitch ld, stride sA), LEFT-looking: block row jb
-    // first takes the contributions of all the rows above it in one GEMM of depth K = jb
-    //   A[jb:jb+nb, jb:dim] -= U[0:jb, jb:jb+nb]^T U[0:jb, jb:dim]
-    // (each element of the factor is written once, and the GEMMs are deep enough to keep their pipelines
-    // busy - the right-looking form did dim/32 rank-32 updates of the whole trailing matrix), then the panel
-    // kernel factors the diagonal block and solves the block row.
+    // takes the contributions of all the rows above it in products of depth K = jb (each element of the
+    // factor is written once; the right-looking form did dim/32 rank-32 updates of the whole trailing matrix):
+    //   diagonal block  D = A_jj - U[0:jb, jb:jb+nb]^T U[0:jb, jb:jb+nb] = Ud^T Ud, Dinv = Ud^-1   (aug_chol_diag_kernel)
+    //   block row       U[jb:jb+nb, jb+nb:] = Dinv^T (A[jb:jb+nb, jb+nb:] - U[0:jb, jb:jb+nb]^T U[0:jb, jb+nb:])   (SOLVE GEMM)
+    // The inverted diagonal blocks stay in this->Dinv for a following solve with the same factor.
     int chol(double *A, long long sA, int ld, int dim, int32_t *status, int fail_bit)
     {
+        const bool fused = h->opt_aug_gemm == 0;
         for (int jb = 0; jb < dim; jb += 32) {
             const int nb = dim - jb < 32 ? dim - jb : 32;
+            if (fused) {
+                Tmap mu;                                          // the block's 32 columns of the rows above it
+                int rc0 = tmap_encode_3d(h, &mu, A + jb, nb, jb, F, ld, sA, 36);
+                if (rc0 != LSLAM_OK) return rc0;
+                LSLAM_LAUNCH(aug_chol_diag_kernel, dim3(F), 160, kAugDiagSmem, st, A, sA, ld, jb, nb, Dinv + (size_t)(jb / 32) * 1024, sDinv,
+                             status, fail_bit, mu);
+                h->launches++;
+                const int rc = gemm_solve(A + jb, sA, ld, A + jb + nb, sA, ld, A + (size_t)jb * ld + jb + nb, sA, ld, nb, dim - jb - nb, jb,
+                                          jb / 32, status);
+                if (rc != LSLAM_OK) return rc;
+                continue;
+            }
             if (jb > 0) {
                 const int rc = gemm(A + jb, sA, ld, A + jb, sA, ld, A + (size_t)jb * ld + jb, sA, ld, nb, dim - jb, jb,
                                     0.0, -1.0, 1.0, status, 1);
                 if (rc != LSLAM_OK) return rc;
             }
             LSLAM_LAUNCH(aug_chol_panel_kernel, dim3(F), 256, kAugBlockSmem, st, A, sA, dim, ld, jb, nb, status, fail_bit);
+            h->launches++;
+        }
+        return LSLAM_OK;
+    }
+    // W = U^-T W in place (U: dim x dim factor just produced by chol(), W: dim x ncols), block rows top down
+    int forward_solve(const double *U, long long sU, int ldu, int dim, double *W, long long sW, int ldw, int ncols, const int32_t *status)
+    {
+        const bool fused = h->opt_aug_gemm == 0;
+        for (int jb = 0; jb < dim; jb += 32) {
+            const int nb = dim - jb < 32 ? dim - jb : 32;
+            if (fused) {
+                const int rc = gemm_solve(U + jb, sU, ldu, W, sW, ldw, W + (size_t)jb * ldw, sW, ldw, nb, ncols, jb, jb / 32, status);
+                if (rc != LSLAM_OK) return rc;
+                continue;
+            }
+            if (jb > 0) {
+                const int rc = gemm(U + jb, sU, ldu, W, sW, ldw, W + (size_t)jb * ldw, sW, ldw, nb, ncols, jb, 0.0, -1.0, 1.0, status, 0);
+                if (rc != LSLAM_OK) return rc;
+            }
+            LSLAM_LAUNCH(aug_trsm_block_kernel, dim3((ncols + 255) / 256, F), 256, kAugBlockSmem, st, U, sU, ldu, W, sW, ldw, ncols, jb, nb, 0,
+                         status);
             h->launches++;
         }
         return LSLAM_OK;
@@ -646,13 +699,16 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
         double *p = ws;
         a.U = p; p += lay.U * Fb; a.X = p; p += lay.X * Fb; a.Y = p; p += lay.Y * Fb; a.H = p; p += lay.H * Fb;
         a.Kt = p; p += lay.Kt * Fb;
-        a.Pbar = p; p += lay.Pbar * Fb; a.xbar = p; p += lay.xbar * Fb;
+        a.Pbar = p; p += lay.Pbar * Fb;
+        double *dinv = p; p += lay.Dinv * Fb;
+        a.xbar = p; p += lay.xbar * Fb;
         double *xnew = p; p += lay.xnew * Fb;
         a.zhat = p; a.wm = wm; a.wc = wc;
         a.dt = params_h[0]; a.half_r = params_h[1] / 2.0; a.r_over_l = params_h[1] / params_h[2]; a.cscale = c;
         a.var_dist = params_h[6]; a.var_angle = params_h[7];
         for (int i = 0; i < 9; ++i) a.Q[i] = params_h[8 + i];
         AugRun run{h, st, Fb};
+        run.Dinv = dinv; run.sDinv = lay.Dinv;
         const long long nn = (long long)n * n, nl = (long long)n * ldn, ml = (long long)m * ldn;
         const dim3 gew(Fb < 64 ? ew : 8, Fb), gcol((n + 31) / 32, Fb);
         const bool redraw = pred && upd && (flags & LSLAM_UKF_REDRAW);
@@ -703,14 +759,7 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
             AUG_TRY(run.gemm(a.H, mz, dz, a.H, mz, dz, a.U, nl, dz, dz, dz, m, wc0 - wi, wi, 0.0, a.status, 1));   // S (upper)
             AUG_TRY(run.gemm(a.H, mz, dz, a.Y, ml, ldn, a.Kt, zn, n1, dz, n, m, wc0 - wi, wi, 0.0, a.status, 0));  // Pzx
             AUG_TRY(run.chol(a.U, nl, dz, dz, a.status, LSLAM_UKF_ST_S));
-            for (int jb = 0; jb < dz; jb += 32) {                 // U^T W = [Pzx | r]
-                const int nb = dz - jb < 32 ? dz - jb : 32;
-                if (jb > 0)
-                    AUG_TRY(run.gemm(a.U + jb, nl, dz, a.Kt, zn, n1, a.Kt + (size_t)jb * n1, zn, n1, nb, n1, jb, 0.0, -1.0, 1.0, a.status, 0));
-                LSLAM_LAUNCH(aug_trsm_block_kernel, dim3((n1 + 255) / 256, Fb), 256, kAugBlockSmem, st, (const double *)a.U, nl, dz,
-                             a.Kt, zn, n1, n1, jb, nb, 0, (const int32_t *)a.status);
-                h->launches++;
-            }
+            AUG_TRY(run.forward_solve(a.U, nl, dz, dz, a.Kt, zn, n1, n1, a.status));   // U^T W = [Pzx | r]
             LSLAM_LAUNCH(aug_update_x_kernel, dim3((n + 31) / 32, Fb), 256, kAugUpdateXSmem, st, a, xnew);
             h->launches++;
             AUG_TRY(run.gemm(a.Kt, zn, n1, a.Kt, zn, n1, a.Pbar, nl, ldn, n, n, dz, 0.0, -1.0, 1.0, a.status, 1));   // P = Pbar - W^T W (upper; commit mirrors)

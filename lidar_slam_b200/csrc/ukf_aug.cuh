@@ -53,6 +53,8 @@ struct AugGemm {
     long long sC2;
     int ldc2;
     double scale2;
+    const double *Dinv;             // SOLVE kernels: the inverted 32 x 32 diagonal block, row-major [k][r] (aug_chol_diag_kernel)
+    long long sDinv;
 };
 
 // one output element: C = beta C + alpha acc (+ the central-weight term) (+ noise), optional scaled copy
@@ -316,19 +318,27 @@ __global__ void __launch_bounds__(32 * WARPS_M * WARPS_N) aug_gemm_dmma_kernel(c
 // (mbarrier empty[s], one arrival per live warp): no block-wide barrier inside the k-loop.
 // Needs 16-byte aligned operands with even pitches - lslam_ukf_aug_step pads the workspace pitch of the
 // n-column arrays to n + 1 (n = 3 + 2L is odd).
-constexpr int kAugTmaStages = 4;
-template <int TM, int TN> constexpr size_t aug_tma_smem()
+//
+// SOLVE variant (TM = 32, one row of warps): the block-row step of a blocked triangular solve.  After the
+// product the 32 x TN tile V = beta C + alpha acc is multiplied from the left by the transposed inverse of
+// the 32 x 32 diagonal block, out = Dinv^T V (Dinv = D^-1 upper triangular, from aug_chol_diag_kernel): the
+// forward substitution with D^T as one more K = 32 product on the tensor pipe - each warp parks its V tile
+// in shared memory as the k-major B operand, Dinv is the k-major A operand.  Used for the block rows of the
+// Cholesky factor and of W = U^-T [Pzx | r].
+template <int TM, int TN, int WARPS_N, int S, bool SOLVE> constexpr size_t aug_tma_smem()
 {
-    return (size_t)kAugTmaStages * kAugBK * (TM + 4 + TN + 4) * sizeof(double) + 2 * kAugTmaStages * sizeof(Mbar) + 128;
+    return (size_t)S * kAugBK * (TM + 4 + TN + 4) * sizeof(double) + (2 * S + 2) * sizeof(Mbar) + 128 +
+           (SOLVE ? (size_t)(32 * 36 + 32 * (TN + 4 * WARPS_N)) * sizeof(double) : 0);
 }
 
-template <int TM, int TN, int WARPS_M, int WARPS_N>
+template <int TM, int TN, int WARPS_M, int WARPS_N, int S, bool SOLVE>
 __global__ void __launch_bounds__(32 * (WARPS_M * WARPS_N + 1))
 aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const LSLAM_GRID_CONSTANT Tmap mapB)
 {
     LSLAM_SMEM_DECL;
     constexpr int NW = WARPS_M * WARPS_N, WM = TM / WARPS_M, WN = TN / WARPS_N, FM = WM / 8, FN = WN / 8;
-    constexpr int LDA = TM + 4, LDB = TN + 4, STAGE = kAugBK * (LDA + LDB), S = kAugTmaStages;
+    constexpr int LDA = TM + 4, LDB = TN + 4, STAGE = kAugBK * (LDA + LDB);
+    static_assert(!SOLVE || (TM == 32 && WARPS_M == 1), "SOLVE: one 32-row block");
     static_assert(TM % 16 == 0 && TN % 16 == 0 && WM % 8 == 0 && WN % 8 == 0, "tile shape");
     static_assert((kAugBK * LDA * sizeof(double)) % 128 == 0 && (kAugBK * LDB * sizeof(double)) % 128 == 0, "TMA box alignment");
     const int f = blockIdx.z;
@@ -344,6 +354,8 @@ aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const 
     double *sm = reinterpret_cast<double *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
 #endif
     Mbar *full = reinterpret_cast<Mbar *>(sm + (size_t)S * STAGE), *empty = full + S;
+    Mbar *dbar = empty + S;                                           // SOLVE: Dinv has landed
+    double *Ds = reinterpret_cast<double *>(empty + S + 2);           // SOLVE: Dinv [32][36], then V tiles [NW][32][WN + 4]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     // fragment liveness per consumer warp (see aug_gemm_dmma_kernel); a warp without a live fragment leaves
     auto live_mask = [&](int w) {
@@ -360,6 +372,7 @@ aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const 
         int nlive = 0;
         for (int w = 0; w < NW; ++w) nlive += live_mask(w) != 0;
         for (int s = 0; s < S; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], nlive > 0 ? nlive : 1); }
+        mbar_init(dbar, 1);
         mbar_fence_init();
     }
     __syncthreads();
@@ -368,6 +381,11 @@ aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const 
         if (lane == 0) {
             bool any = false;
             for (int w = 0; w < NW; ++w) any = any || live_mask(w) != 0;
+            if (any && SOLVE) {                                       // the inverted diagonal block: 32 rows of 256 B into pitch-36 rows
+                const double *Dinv = g.Dinv + (size_t)f * g.sDinv;
+                mbar_expect_tx(dbar, 32 * 32 * (unsigned)sizeof(double));
+                for (int r = 0; r < 32; ++r) bulk_g2s(Ds + r * 36, Dinv + r * 32, 32 * (unsigned)sizeof(double), dbar);
+            }
             if (any)
                 for (int t = 0; t < ntiles; ++t) {
                     const int s = t % S;
@@ -384,6 +402,10 @@ aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const 
     const unsigned live = live_mask(warp);
     if (live == 0) return;
     const bool fullw = live == (FM * FN == 32 ? 0xffffffffu : (1u << (FM * FN)) - 1u);
+    if (SOLVE) {                                                      // the epilogue reads this warp's C tile: start it towards L2 now
+        const double *crow = g.C + (size_t)f * g.sC + (size_t)lane * g.ldc + j0 + wn0;
+        if (lane < g.M && j0 + wn0 < g.N) { prefetch_l2(crow); prefetch_l2(crow + WN - 1 < crow + (g.N - j0 - wn0) ? crow + WN - 1 : crow); }
+    }
     double acc[FM][FN][2];
 #pragma unroll
     for (int a = 0; a < FM; ++a)
@@ -427,19 +449,241 @@ aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const 
     }
     const double *A = g.A + (size_t)f * g.sA, *B = g.B + (size_t)f * g.sB;
     double *C = g.C + (size_t)f * g.sC, *C2 = g.C2 ? g.C2 + (size_t)f * g.sC2 : nullptr;
+    if (SOLVE) {
+        constexpr int LDV = WN + 4;
+        double *Vs = Ds + 32 * 36 + (size_t)warp * 32 * LDV;
 #pragma unroll
-    for (int a = 0; a < FM; ++a) {
-        const int i = i0 + wm0 + 8 * a + fcol;
-        if (i >= g.M) continue;
-        const double a0 = g.w0 != 0.0 ? g.w0 * A[i] : 0.0;
+        for (int a = 0; a < FM; ++a) {
+            const int i = 8 * a + fcol;
 #pragma unroll
-        for (int b = 0; b < FN; ++b)
+            for (int b = 0; b < FN; ++b)
 #pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                const int j = j0 + wn0 + 8 * b + 2 * frag + q;
-                if (j >= g.N || (g.upper && j < i)) continue;
-                aug_gemm_store(g, C, C2, B, i, j, a0, acc[a][b][q]);
+                for (int q = 0; q < 2; ++q) {
+                    const int jl = 8 * b + 2 * frag + q, j = j0 + wn0 + jl;
+                    double v = 0.0;
+                    if (i < g.M && j < g.N) v = fma(g.alpha, acc[a][b][q], g.beta == 0.0 ? 0.0 : g.beta * C[(size_t)i * g.ldc + j]);
+                    Vs[i * LDV + jl] = v;
+                    acc[a][b][0 + q] = 0.0;
+                }
+        }
+        __syncwarp();
+        mbar_wait(dbar, 0);
+#pragma unroll
+        for (int ks = 0; ks < 32; ks += 4) {
+            double av[FM], bv[FN];
+#pragma unroll
+            for (int a = 0; a < FM; ++a) av[a] = Ds[(ks + frag) * 36 + 8 * a + fcol];
+#pragma unroll
+            for (int b = 0; b < FN; ++b) bv[b] = Vs[(ks + frag) * LDV + 8 * b + fcol];
+#pragma unroll
+            for (int a = 0; a < FM; ++a)
+#pragma unroll
+                for (int b = 0; b < FN; ++b) dmma_m8n8k4(acc[a][b][0], acc[a][b][1], av[a], bv[b]);
+        }
+#pragma unroll
+        for (int a = 0; a < FM; ++a) {
+            const int i = 8 * a + fcol;
+            if (i >= g.M) continue;
+#pragma unroll
+            for (int b = 0; b < FN; ++b)
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    const int j = j0 + wn0 + 8 * b + 2 * frag + q;
+                    if (j < g.N) C[(size_t)i * g.ldc + j] = acc[a][b][q];
+                }
+        }
+    } else {
+#pragma unroll
+        for (int a = 0; a < FM; ++a) {
+            const int i = i0 + wm0 + 8 * a + fcol;
+            if (i >= g.M) continue;
+            const double a0 = g.w0 != 0.0 ? g.w0 * A[i] : 0.0;
+#pragma unroll
+            for (int b = 0; b < FN; ++b)
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    const int j = j0 + wn0 + 8 * b + 2 * frag + q;
+                    if (j >= g.N || (g.upper && j < i)) continue;
+                    aug_gemm_store(g, C, C2, B, i, j, a0, acc[a][b][q]);
+                }
+        }
+    }
+}
+
+// ---- diagonal block of the left-looking blocked Cholesky -------------------------------------------------------
+// One CTA per matrix, block step jb (nb <= 32 rows), 4 DMMA warps + 1 TMA producer warp:
+//   D = A[jb:jb+nb, jb:jb+nb] - U[0:jb, jb:jb+nb]^T U[0:jb, jb:jb+nb]     the GEMM pipeline of aug_gemm_tma_kernel with ONE
+//                                                                          operand (A = B = the 32 columns of the block):
+//                                                                          2 x 2 warps of 16 x 16, fragments below the
+//                                                                          diagonal skipped
+//   D = Ud^T Ud                                                            right-looking in shared memory, all warps
+//   Dinv = Ud^-1                                                           blocked: the four 8 x 8 diagonal blocks by back
+//                                                                          substitution (a warp each), then the block
+//                                                                          super-diagonals X_ij = -X_ii sum_k U_ik X_kj
+// Ud goes back into A, Dinv (row-major, zero-padded to 32 x 32) to the workspace: the block row
+// U[jb:jb+nb, jb+nb:] = Ud^-T (A - U^T U) = Dinv^T (...) is then the SOLVE epilogue of the GEMM that forms
+// the bracket - the triangular solve of every block step runs on the tensor pipe instead of as a serial
+// substitution per column.  A non-positive pivot sets bit `fail_bit` of status[f] (scipy raises
+// LinAlgError) and the matrix is left alone from then on.
+// (History, B200, 256 matrices of 403: DFMA accumulation from a shared-memory tile + one-warp inverse 68 us
+// per launch - profiles/r01r; a fully unrolled in-register factorisation was no faster: ~80 KB of
+// straight-line code executed once per CTA runs at the speed of instruction-cache misses.)
+constexpr int kAugDiagStages = 4;
+constexpr size_t kAugDiagSmem = 128 + (size_t)kAugDiagStages * kAugBK * 36 * sizeof(double) + 2 * kAugDiagStages * sizeof(Mbar) +
+                                (2 * 32 * 33 + 4 * 8 * 9 + 64) * sizeof(double) + 16;
+__global__ void __launch_bounds__(160) aug_chol_diag_kernel(double *Abase, long long sA, int lda, int jb, int nb, double *Dinv_base,
+                                                            long long sD, int32_t *status, int fail_bit,
+                                                            const LSLAM_GRID_CONSTANT Tmap mapU)
+{
+    LSLAM_SMEM_DECL;
+    constexpr int S = kAugDiagStages, LDT = 36, STAGE = kAugBK * LDT, NW = 4;
+    const int f = blockIdx.x;
+    if (status[f] != 0) return;
+#ifndef LSLAM_EMU
+    double *sm = reinterpret_cast<double *>(smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u));
+#else
+    double *sm = reinterpret_cast<double *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+#endif
+    Mbar *full = reinterpret_cast<Mbar *>(sm + (size_t)S * STAGE), *empty = full + S;
+    double (*Ub)[33] = reinterpret_cast<double (*)[33]>(empty + S);
+    double (*Xs)[33] = Ub + 32;
+    double (*Ts)[8][9] = reinterpret_cast<double (*)[8][9]>(Xs + 32);
+    double *rinv = reinterpret_cast<double *>(Ts + 4), *dsave = rinv + 32;
+    int &bad = *reinterpret_cast<int *>(dsave + 32);
+    double *A = Abase + (size_t)f * sA;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthr = blockDim.x, nwarp = nthr >> 5;
+    // ---- phase 1: D = A_jj - U^T U into Ub
+    auto live_mask = [&](int w) {
+        const int m0 = (w >> 1) * 16, n0 = (w & 1) * 16;
+        unsigned live = 0;
+        for (int a = 0; a < 2; ++a)
+            for (int b = 0; b < 2; ++b) {
+                const int fi = m0 + 8 * a, fj = n0 + 8 * b;
+                if (fi < nb && fj < nb && fi <= fj + 7) live |= 1u << (a * 2 + b);
             }
+        return live;
+    };
+    for (int e = tid; e < 32 * 33; e += nthr) { (&Ub[0][0])[e] = 0.0; (&Xs[0][0])[e] = 0.0; }
+    if (tid < 32) rinv[tid] = 0.0;
+    if (tid == 0) {
+        int nlive = 0;
+        for (int w = 0; w < NW; ++w) nlive += live_mask(w) != 0;
+        for (int s = 0; s < S; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], nlive); }
+        mbar_fence_init();
+        bad = 0;
+    }
+    __syncthreads();
+    const int ntiles = (jb + kAugBK - 1) / kAugBK;
+    if (warp == NW) {
+        if (lane == 0)
+            for (int t = 0; t < ntiles; ++t) {
+                const int s = t % S;
+                if (t >= S) mbar_wait(&empty[s], ((t / S) - 1) & 1);
+                mbar_expect_tx(&full[s], (unsigned)(STAGE * sizeof(double)));
+                tma_load_3d(sm + (size_t)s * STAGE, &mapU, 0, t * kAugBK, f, &full[s]);
+            }
+    } else if (warp < NW) {
+        const unsigned live = live_mask(warp);
+        if (live != 0) {
+            const int wm0 = (warp >> 1) * 16, wn0 = (warp & 1) * 16, frag = lane & 3, fcol = lane >> 2;
+            double acc[2][2][2] = {};
+            for (int t = 0; t < ntiles; ++t) {
+                const int s = t % S;
+                mbar_wait(&full[s], (t / S) & 1);
+                const double *ts = sm + (size_t)s * STAGE + frag * LDT + fcol;
+#pragma unroll
+                for (int q = 0; q < kAugBK / 4; ++q) {
+                    double av[2], bv[2];
+#pragma unroll
+                    for (int a = 0; a < 2; ++a) av[a] = ts[4 * q * LDT + wm0 + 8 * a];
+#pragma unroll
+                    for (int b = 0; b < 2; ++b) bv[b] = ts[4 * q * LDT + wn0 + 8 * b];
+#pragma unroll
+                    for (int a = 0; a < 2; ++a)
+#pragma unroll
+                        for (int b = 0; b < 2; ++b)
+                            if ((live >> (a * 2 + b)) & 1u) dmma_m8n8k4(acc[a][b][0], acc[a][b][1], av[a], bv[b]);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty[s]);
+            }
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int b = 0; b < 2; ++b)
+#pragma unroll
+                    for (int q = 0; q < 2; ++q) {
+                        const int i = wm0 + 8 * a + fcol, j = wn0 + 8 * b + 2 * frag + q;
+                        if (((live >> (a * 2 + b)) & 1u) && i < nb && j < nb && j >= i)
+                            Ub[i][j] = __dsub_rn(A[(size_t)(jb + i) * lda + jb + j], acc[a][b][q]);
+                    }
+        }
+    }
+    __syncthreads();
+    // ---- phase 2: right-looking factorisation in shared memory, all warps: row r is scaled by warp 0, the trailing
+    // rows are updated by the warps round-robin, lanes over columns.  The diagonal keeps the pivots until the end
+    // (dsave holds the roots), so reading the next pivot needs no extra barrier.
+    int ok = 1;
+    for (int r = 0; r < nb; ++r) {
+        const double piv = Ub[r][r];
+        if (!(piv > 0.0)) { ok = 0; break; }                          // uniform: every thread reads the same pivot
+        const double d = sqrt(piv), ri = 1.0 / d;
+        if (warp == 0) {
+            if (lane > r) Ub[r][lane] = __dmul_rn(Ub[r][lane], ri);
+            if (lane == 0) { rinv[r] = ri; dsave[r] = d; }
+        }
+        __syncthreads();
+        for (int ii = r + 1 + warp; ii < nb; ii += nwarp)
+            if (lane >= ii) Ub[ii][lane] = fma(-Ub[r][ii], Ub[r][lane], Ub[ii][lane]);
+        __syncthreads();
+    }
+    if (!ok) {
+        if (tid == 0) status[f] |= fail_bit;
+        return;
+    }
+    if (tid < nb) Ub[tid][tid] = dsave[tid];
+    // ---- phase 3: Dinv = Ud^-1, 8 x 8 blocks.  Padded rows / columns (>= nb) have rinv = 0 and zero entries: they stay 0.
+    if (warp < 4 && lane < 8) {                                       // diagonal block `warp`: column lane by back substitution
+        const int b0 = 8 * warp, c = lane;
+        double x[8];
+#pragma unroll
+        for (int rr = 7; rr >= 0; --rr) {
+            double sum = 0.0;
+#pragma unroll
+            for (int kk = rr + 1; kk < 8; ++kk) sum = fma(Ub[b0 + rr][b0 + kk], kk <= c ? x[kk] : 0.0, sum);
+            x[rr] = rr > c ? 0.0 : (rr == c ? rinv[b0 + rr] : -sum * rinv[b0 + rr]);
+        }
+#pragma unroll
+        for (int rr = 0; rr < 8; ++rr) Xs[b0 + rr][b0 + c] = x[rr];
+    }
+    __syncthreads();
+    for (int dd = 1; dd < 4; ++dd) {                                  // block super-diagonal dd: X_ij = -X_ii (sum_{i < k <= j} U_ik X_kj), j = i + dd
+        if (warp < 4 - dd) {
+            const int bi = warp, bj = warp + dd, c = lane & 7, r0 = lane >> 3;   // this lane: rows r0 and r0 + 4, column c
+            double t0 = 0.0, t1 = 0.0;
+            for (int k = 8 * (bi + 1); k < 8 * (bj + 1); ++k) {
+                const double xk = Xs[k][8 * bj + c];
+                t0 = fma(Ub[8 * bi + r0][k], xk, t0);
+                t1 = fma(Ub[8 * bi + r0 + 4][k], xk, t1);
+            }
+            Ts[warp][r0][c] = t0; Ts[warp][r0 + 4][c] = t1;
+            __syncwarp();
+            double y0 = 0.0, y1 = 0.0;
+#pragma unroll
+            for (int kk = 0; kk < 8; ++kk) {
+                const double tk = Ts[warp][kk][c];
+                y0 = fma(Xs[8 * bi + r0][8 * bi + kk], tk, y0);
+                y1 = fma(Xs[8 * bi + r0 + 4][8 * bi + kk], tk, y1);
+            }
+            Xs[8 * bi + r0][8 * bj + c] = -y0; Xs[8 * bi + r0 + 4][8 * bj + c] = -y1;
+        }
+        __syncthreads();
+    }
+    double *Dinv = Dinv_base + (size_t)f * sD;
+    for (int e = tid; e < 32 * 32; e += nthr) Dinv[e] = Xs[e >> 5][e & 31];
+    for (int e = tid; e < nb * nb; e += nthr) {
+        const int r = e / nb, c = e % nb;
+        if (c >= r) A[(size_t)(jb + r) * lda + jb + c] = Ub[r][c];
     }
 }
 
