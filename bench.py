@@ -53,6 +53,8 @@ def parse():
     p.add_argument("--cpu-sample", type=int, default=0, help="scans in the CPU sample (0 = auto)")
     p.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--no-aug", action="store_true", help="skip the configs[3] leg (augmented-state UKF)")
+    p.add_argument("--aug-filters", type=int, default=1024)
     p.add_argument("--slices", type=int, default=0, help="slices of the overlapped host path (0 = default)")
     p.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                    help="N > 1 result gather: fused into the UKF kernel over peer memory, or an NCCL all_gather")
@@ -167,6 +169,48 @@ def run_reference(args, rank, world):
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def aug_leg(eng, F, steps, fp64_peak, L=200):
+    """BASELINE.json configs[3]: F independent filters with 3-DOF pose + L landmarks in the state (n = 3 + 2L),
+    one predict + update per step through lslam_ukf_aug_step, state and measurements resident in HBM (the
+    per-step working set, 13 MB of scratch per filter, is far larger than L2).  filter-steps/s; the flop
+    figure is SURVEY.md 8(d)'s literal-filterpy dense count (1.34 GFLOP per step at L = 200, scaled by n^3)."""
+    import numpy as np
+    import torch
+    from lidar_slam_b200 import synth
+    nb = min(F, 16)
+    x, P, u, z = synth.random_aug_filters(nb, L, seed=0)
+    rep = (F + nb - 1) // nb
+    dev = eng.device
+    t = lambda a: torch.from_numpy(np.tile(a, (rep,) + (1,) * (a.ndim - 1))[:F].copy()).to(dev)
+    st = eng.alloc_ukf_aug(F, L)
+    x0, P0, ut, zt = t(x), t(P), t(u), t(z)
+    ms, launches = [], 0
+    for r in range(steps + 2):
+        st["x"].copy_(x0); st["P"].copy_(P0)
+        torch.cuda.synchronize()
+        l0 = eng.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        eng.ukf_aug_step(st, zt, u=ut)
+        e1.record()
+        torch.cuda.synchronize()
+        ms.append(e0.elapsed_time(e1))
+        launches = eng.launch_count() - l0
+    bad = int((st["status"] != 0).sum().item())
+    t_ms = sum(ms[2:]) / len(ms[2:])
+    n = 3 + 2 * L
+    flop = 1.34e9 * (n / 403.0) ** 3
+    tf = flop * F / (t_ms * 1e-3) * 1e-12
+    del st, x0, P0
+    torch.cuda.empty_cache()
+    return {"workload": "BASELINE.json configs[3]: %d filters, pose + %d landmarks in the state (n = %d), predict + update" % (F, L, n),
+            "value": F / (t_ms * 1e-3), "unit": "filter-steps/s", "ms_per_step": t_ms, "gpu_launches": launches,
+            "status_nonzero": bad,
+            "roofline": {"bound": "fp64 tensor pipe (DMMA = DFMA rate)", "achieved": tf, "peak": fp64_peak, "unit": "TFLOP/s",
+                         "frac": tf / fp64_peak if fp64_peak > 0 else None,
+                         "flop_per_filter_step": flop, "flop_source": "SURVEY.md 8(d) literal filterpy count"}}
 
 
 def workload_config(args, world):
@@ -324,6 +368,11 @@ def main():
         e2e_xy["input"] = "cartesian float64 points, 5760 B per scan"
         del xy_h
 
+    # ---- BASELINE.json configs[3]: augmented-state UKF (pose + 200 landmarks, n = 403), reported beside the headline
+    aug = None
+    if world == 1 and not args.no_aug:
+        aug = aug_leg(eng, args.aug_filters, args.steps, fp64_peak)
+
     if rank == 0:
         value = world * S * args.steps / (ms * 1e-3)
         peaks = {}
@@ -359,7 +408,7 @@ def main():
             "stages": ["ransac", "associate", "ukf"], "hit_rate": hit_rate, "gather": gather_mode,
             "ransac_hyps_per_s": world * S * 4 * TRIALS * args.steps / (ms * 1e-3),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_xy": e2e_xy, "gpu_launches": launches,
-            "clocks": clocks, "parity_faults": faults,
+            "clocks": clocks, "parity_faults": faults, "ukf_aug": aug,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -208,11 +208,13 @@ int lslam_ukf_update(void *handle, double *x, double *P, const double *z, int32_
  * l1x, ...), fx moves the pose and leaves the landmarks, hx is UKFMethods.transfer_function with the
  * landmark positions read from the state (oracle/ukf.py transfer_function_augmented), dim_z = 2L,
  * R = diag([var_dist, var_angle] * L), Q = params' 3x3 on the pose block and zero elsewhere,
- * 2n + 1 sigma points.  K = Pxz S^-1 is formed through the Cholesky factor of S (filterpy: inv(S)).
+ * 2n + 1 sigma points.  The gain is applied through the Cholesky factor of S and one forward solve
+ * W = U^-T [Pzx | r]: x = xbar + W^T v, P = Pbar - W^T W (filterpy forms inv(S) and K; same x, P to rounding).
  *   x [F,n], P [F,n,n] in/out;  u [F,2] or NULL;  z [F,L,2] (range, bearing) per landmark;
  *   params_h, flags, status as for lslam_ukf_step; a filter whose status is non-zero keeps its (x, P).
  *   workspace: device scratch; filters are processed in batches of as many as fit
  *   (lslam_ukf_aug_workspace_bytes(L, k) bytes hold k filters; at least one must fit).  1 <= L <= 1024.
+ *   The workspace must be 16-byte aligned (its arrays are read through TMA tensor maps).
  */
 int lslam_ukf_aug_workspace_bytes(int32_t L, int32_t filters, int64_t *bytes);
 int lslam_ukf_aug_step(void *handle, double *x, double *P, const double *u, const double *z, int32_t F,

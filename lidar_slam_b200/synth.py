@@ -166,3 +166,29 @@ def random_room_express(nscans, packets_per_scan=12, seed=0, noise_mm=5.0, dropo
         di = np.clip(np.rint(d), 0, 16383).astype(np.int64)
         out[s] = pack_express(di, code, sq[:P], (np.arange(P) == 0).astype(np.int64))
     return out
+
+
+def random_aug_filters(F, L, seed=0, spread=3000.0):
+    """F augmented-state filters (BASELINE.json configs[3]: pose + L landmarks in the state, n = 3 + 2L):
+    the true pose near the origin, landmarks 1-4 m away, the filter's state = truth + prior-sized noise,
+    P = diag(.1, .1, .05, 25, ...) (systemClass.py:27, 5 mm landmark sigma) + a little correlation,
+    u ~ U(0.5, 2)^2, z = the true (range, bearing) of every landmark + sensor noise.
+    Returns x [F, n], P [F, n, n], u [F, 2], z [F, L, 2] (float64)."""
+    rng = np.random.default_rng(seed)
+    n = 3 + 2 * L
+    pose = np.column_stack([rng.normal(0, 50, F), rng.normal(0, 50, F), rng.uniform(-np.pi, np.pi, F)])
+    ang = rng.uniform(-np.pi, np.pi, (F, L))
+    rad = rng.uniform(1000.0, 1000.0 + spread, (F, L))
+    lm = np.stack([pose[:, :1] + rad * np.cos(ang), pose[:, 1:2] + rad * np.sin(ang)], axis=2)
+    x = np.zeros((F, n))
+    x[:, :3] = pose + rng.normal(0, 1, (F, 3)) * np.array([0.3, 0.3, 0.02])
+    x[:, 3:] = (lm + rng.normal(0, 5.0, lm.shape)).reshape(F, -1)
+    d = np.array([0.1, 0.1, 0.05] + [25.0] * (2 * L))
+    A = rng.normal(0, 0.05, (F, n, n))
+    P = np.broadcast_to(np.diag(d), (F, n, n)) + np.einsum("fij,fkj->fik", A, A)
+    u = rng.uniform(0.5, 2.0, (F, 2))
+    dx, dy = lm[..., 0] - pose[:, :1], lm[..., 1] - pose[:, 1:2]
+    rg = np.hypot(dx, dy) + rng.normal(0, 0.5, (F, L))
+    br = np.arctan2(dy, dx) - pose[:, 2:3] + rng.normal(0, 0.05, (F, L))
+    br = (br + np.pi) % (2 * np.pi) - np.pi
+    return x, P, u, np.stack([rg, br], axis=2)

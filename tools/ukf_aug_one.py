@@ -7,7 +7,7 @@ import torch
 
 sys.path.insert(0, ".")
 from lidar_slam_b200 import batch  # noqa: E402
-from tests import ukf_aug_util as au  # noqa: E402
+from lidar_slam_b200 import synth  # noqa: E402
 
 L = int(sys.argv[1]) if len(sys.argv) > 1 else 200
 F = int(sys.argv[2]) if len(sys.argv) > 2 else 1024
@@ -18,7 +18,7 @@ if len(sys.argv) > 4:
 if len(sys.argv) > 5:
     eng.set_option("ukf_aug.tile", int(sys.argv[5]))
 dev = eng.device
-x, P, u, z = au.aug_case(min(F, 16), L, seed=0)
+x, P, u, z = synth.random_aug_filters(min(F, 16), L, seed=0)
 rep = (F + len(x) - 1) // len(x)
 t = lambda a: torch.from_numpy(np.tile(a, (rep,) + (1,) * (a.ndim - 1))[:F].copy()).to(dev)
 st = eng.alloc_ukf_aug(F, L)
