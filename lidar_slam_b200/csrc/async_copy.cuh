@@ -49,6 +49,15 @@ __device__ __forceinline__ void mbar_wait(Mbar *bar, unsigned parity)
         if (tries > (1u << 24)) __trap();
     }
 }
+// The same for a thread that is far ahead of what it waits for (a TMA producer waiting for a stage to be
+// released): sleep between polls, so the spin does not take issue slots from the warps doing the math.
+__device__ __forceinline__ void mbar_wait_relaxed(Mbar *bar, unsigned parity, unsigned ns = 256)
+{
+    for (unsigned tries = 0; !mbar_try_wait(bar, parity); ++tries) {
+        __nanosleep(ns);
+        if (tries > (1u << 22)) __trap();
+    }
+}
 // generic-proxy writes to shared memory (e.g. a counter reset) ordered before later async-proxy traffic
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
@@ -105,6 +114,7 @@ inline void mbar_arrive(Mbar *bar) { bar->pending.fetch_sub(1); mbar_emu_check(b
 inline void mbar_expect_tx(Mbar *bar, unsigned bytes) { bar->tx.fetch_add(bytes); bar->pending.fetch_sub(1); mbar_emu_check(bar); }
 inline bool mbar_try_wait(Mbar *bar, unsigned parity) { return ((bar->state.load() >> 32) & 1u) != parity; }
 inline void mbar_wait(Mbar *bar, unsigned parity) { while (!mbar_try_wait(bar, parity)) std::this_thread::yield(); }
+inline void mbar_wait_relaxed(Mbar *bar, unsigned parity, unsigned = 0) { mbar_wait(bar, parity); }
 inline void bulk_g2s(void *dst, const void *src, unsigned bytes, Mbar *bar)
 {
     std::memcpy(dst, src, bytes);

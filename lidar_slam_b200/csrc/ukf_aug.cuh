@@ -389,7 +389,7 @@ aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const 
             if (any)
                 for (int t = 0; t < ntiles; ++t) {
                     const int s = t % S;
-                    if (t >= S) mbar_wait(&empty[s], ((t / S) - 1) & 1);
+                    if (t >= S) mbar_wait_relaxed(&empty[s], ((t / S) - 1) & 1);
                     double *as = sm + (size_t)s * STAGE, *bs = as + kAugBK * LDA;
                     mbar_expect_tx(&full[s], (unsigned)(STAGE * sizeof(double)));
                     tma_load_3d(as, &mapA, i0, t * kAugBK, f, &full[s]);
@@ -578,7 +578,7 @@ __global__ void __launch_bounds__(160) aug_chol_diag_kernel(double *Abase, long 
         if (lane == 0)
             for (int t = 0; t < ntiles; ++t) {
                 const int s = t % S;
-                if (t >= S) mbar_wait(&empty[s], ((t / S) - 1) & 1);
+                if (t >= S) mbar_wait_relaxed(&empty[s], ((t / S) - 1) & 1);
                 mbar_expect_tx(&full[s], (unsigned)(STAGE * sizeof(double)));
                 tma_load_3d(sm + (size_t)s * STAGE, &mapU, 0, t * kAugBK, f, &full[s]);
             }
