@@ -200,6 +200,28 @@ def aug_leg(eng, F, steps, fp64_peak, L=200):
         launches = eng.launch_count() - l0
     bad = int((st["status"] != 0).sum().item())
     t_ms = sum(ms[2:]) / len(ms[2:])
+    # configs[3]'s association: L queries (the observed landmarks) against the filter's table of L stored landmarks,
+    # first-match mode; the stored rows are the queries of the previous revolution, slightly moved, so most queries hit
+    g = torch.Generator(device="cpu").manual_seed(3)
+    ab = torch.randn((F, L, 2), generator=g, dtype=torch.float64) * torch.tensor([0.5, 1500.0], dtype=torch.float64)
+    px = torch.randn((F, L, 1), generator=g, dtype=torch.float64) * 2000.0
+    ex = px + 80.0 * torch.randn((F, L, 1), generator=g, dtype=torch.float64)
+    rows = torch.cat([ab, px, ab[..., :1] * px + ab[..., 1:], ex, ab[..., :1] * ex + ab[..., 1:]], dim=-1).contiguous().to(dev)
+    q = rows.clone()
+    q[..., 1] += 2.0                                                          # b moves by 2 mm: inside every gate
+    a_ms = []
+    for r in range(3):
+        tb = eng.alloc_tables(F, L)
+        tb["rows"].copy_(rows); tb["life"].fill_(40); tb["count"].fill_(L); tb["next_id"].fill_(L)
+        tb["ids"].copy_(torch.arange(L, dtype=torch.int32, device=dev).expand(F, L))
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ao = eng.associate(q, tb, mode=1)
+        e1.record()
+        torch.cuda.synchronize()
+        a_ms.append(e0.elapsed_time(e1))
+    assoc_hits = float((ao["match"] >= 0).float().mean().item())
     n = 3 + 2 * L
     flop = 1.34e9 * (n / 403.0) ** 3
     tf = flop * F / (t_ms * 1e-3) * 1e-12
@@ -208,6 +230,7 @@ def aug_leg(eng, F, steps, fp64_peak, L=200):
     return {"workload": "BASELINE.json configs[3]: %d filters, pose + %d landmarks in the state (n = %d), predict + update" % (F, L, n),
             "value": F / (t_ms * 1e-3), "unit": "filter-steps/s", "ms_per_step": t_ms, "gpu_launches": launches,
             "status_nonzero": bad,
+            "associate": {"queries": L, "stored": L, "mode": "first match", "ms": min(a_ms), "hit_rate": assoc_hits},
             "roofline": {"bound": "fp64 tensor pipe (DMMA = DFMA rate)", "achieved": tf, "peak": fp64_peak, "unit": "TFLOP/s",
                          "frac": tf / fp64_peak if fp64_peak > 0 else None,
                          "flop_per_filter_step": flop, "flop_source": "SURVEY.md 8(d) literal filterpy count"}}

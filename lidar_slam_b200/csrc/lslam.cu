@@ -112,6 +112,9 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
     } else if (!strcmp(key, "ukf_aug.gemm")) {
         if (value < 0 || value > 2) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.gemm: 0 default (DMMA fed by TMA), 1 DFMA, 2 DMMA fed by cp.async");
         h->opt_aug_gemm = (int)value;
+    } else if (!strcmp(key, "ukf_aug.solve_tile")) {
+        if (value != 0 && value != 64 && value != 128) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.solve_tile: 0 default (64), 64, 128");
+        h->opt_aug_solve_tile = (int)value;
     } else if (!strcmp(key, "ukf_aug.tile")) {
         if (value != 0 && value != 64 && value != 128) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.tile: 0 default (64), 64, 128");
         h->opt_aug_tile = (int)value;
@@ -584,7 +587,10 @@ struct AugRun {
         g.noise = 0; for (int i = 0; i < 9; ++i) g.nq[i] = 0.0;
         g.C2 = nullptr; g.sC2 = 0; g.ldc2 = 0; g.scale2 = 0.0;
         g.Dinv = Dinv + (size_t)blk * 1024; g.sDinv = sDinv;
-        const int rc = gemm_tma<32, 64, 1, 4, 3, true>(g, h->aug_attr_set[2]);
+        // 32 x 64 tiles (warp tile 32 x 16, 3 CTAs per SM); ukf_aug.solve_tile = 128 selects 32 x 128 (warp tile 32 x 32,
+        // 2 CTAs per SM): measured slower on B200 (45.1 against 42.4 ms per 1,024 filters at L = 200)
+        const int rc = h->opt_aug_solve_tile != 128 ? gemm_tma<32, 64, 1, 4, 3, true>(g, h->aug_attr_set[2])
+                                                    : gemm_tma<32, 128, 1, 4, 3, true>(g, h->aug_attr_set[5]);
         if (rc == LSLAM_OK) h->launches++;
         return rc;
     }

@@ -24,7 +24,8 @@ def run_gpu(eng, queries, tables, valid=None, **kw):
 @pytest.mark.parametrize("mode", [0, 1])
 @pytest.mark.parametrize("T,M,prefill,Q", [(300, 8, 0, 12), (300, 8, 8, 6), (301, 5, 4, 9), (203, 16, 13, 9), (99, 12, 12, 7),
                                            (64, 40, 37, 10), (40, 70, 66, 5),
-                                           (17, 200, 190, 8)])
+                                           (17, 200, 190, 8),
+                                           (9, 200, 150, 200)])          # BASELINE.json configs[3]: 200 queries vs 200 stored
 def test_first_match_modes(gpu_engine, mode, T, M, prefill, Q):
     queries, valid, tables = au.random_streams(T, Q, M, seed=M + mode, prefill=prefill)
     want = au.oracle_associate(queries, valid, tables, mode=mode)

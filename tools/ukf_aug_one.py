@@ -17,6 +17,8 @@ if len(sys.argv) > 4:
     eng.set_option("ukf_aug.gemm", int(sys.argv[4]))
 if len(sys.argv) > 5:
     eng.set_option("ukf_aug.tile", int(sys.argv[5]))
+if len(sys.argv) > 6:
+    eng.set_option("ukf_aug.solve_tile", int(sys.argv[6]))
 dev = eng.device
 x, P, u, z = synth.random_aug_filters(min(F, 16), L, seed=0)
 rep = (F + len(x) - 1) // len(x)
