@@ -516,10 +516,10 @@ int tmap_encode_3d(Handle *h, Tmap *map, const double *base, long long cols, lon
 struct AugRun {
     Handle *h; cudaStream_t st; int F;
     double *Dinv = nullptr; long long sDinv = 0;                  // inverted diagonal blocks (aug_chol_diag_kernel), [F][blocks][32][32]
-    template <int TM, int TN, int WM, int WN, int S = 4, bool SOLVE = false>
+    template <int TM, int TN, int WM, int WN, int S = 4, bool SOLVE = false, int MINB = 1>
     int gemm_tma(const AugGemm &g, bool &attr_set)
     {
-        auto kern = aug_gemm_tma_kernel<TM, TN, WM, WN, S, SOLVE>;
+        auto kern = aug_gemm_tma_kernel<TM, TN, WM, WN, S, SOLVE, MINB>;
         constexpr size_t smem = aug_tma_smem<TM, TN, WN, S, SOLVE>();
         if (!attr_set) {
             LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -549,9 +549,11 @@ struct AugRun {
             // CTA tile: 64 x 64 with three CTAs per SM.  ukf_aug.tile = 128 selects 128 x 128 (16 consumer warps, one
             // CTA per SM, half the L2 -> shared traffic per flop): measured SLOWER on B200 (Pzx 2.96 vs 2.54 ms per
             // 256 filters) - L2 is at 10 % of its throughput with either tile, the DMMA pipe is what saturates.
+            // Also measured and dropped: 64 x 128 with 8 consumer warps (52.4 against 42.4 ms per 1,024 filters) and
+            // 64 x 64 at 4 CTAs per SM (3 stages, 96 registers: 43.7 ms).
             const int rc = M <= 32 ? gemm_tma<32, 64, 1, 4>(g, h->aug_attr_set[0])
-                         : (M <= 64 || h->opt_aug_tile != 128) ? gemm_tma<64, 64, 2, 2>(g, h->aug_attr_set[1])
-                                                               : gemm_tma<128, 128, 4, 4>(g, h->aug_attr_set[3]);
+                         : (M > 64 && h->opt_aug_tile == 128) ? gemm_tma<128, 128, 4, 4>(g, h->aug_attr_set[3])
+                                                            : gemm_tma<64, 64, 2, 2>(g, h->aug_attr_set[1]);
             if (rc != LSLAM_OK) return rc;
         } else if (h->opt_aug_gemm == 2) {                        // DMMA fed by 8-byte cp.async
             if (M <= 32) {

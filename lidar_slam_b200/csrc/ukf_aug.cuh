@@ -331,8 +331,8 @@ template <int TM, int TN, int WARPS_N, int S, bool SOLVE> constexpr size_t aug_t
            (SOLVE ? (size_t)(32 * 36 + 32 * (TN + 4 * WARPS_N)) * sizeof(double) : 0);
 }
 
-template <int TM, int TN, int WARPS_M, int WARPS_N, int S, bool SOLVE>
-__global__ void __launch_bounds__(32 * (WARPS_M * WARPS_N + 1))
+template <int TM, int TN, int WARPS_M, int WARPS_N, int S, bool SOLVE, int MINB = 1>
+__global__ void __launch_bounds__(32 * (WARPS_M * WARPS_N + 1), MINB)
 aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const LSLAM_GRID_CONSTANT Tmap mapB)
 {
     LSLAM_SMEM_DECL;
