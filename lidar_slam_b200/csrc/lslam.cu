@@ -534,7 +534,7 @@ struct AugRun {
     }
     // epilogue extras of the next gemm() call (reset by it): noise 1 = + Q (nq[9]) on the pose block, 2 = + R (nq[0], nq[1])
     // on the diagonal; C2 = a second, scaled copy of the result
-    int noise = 0; double nq[9] = {0}; double *C2 = nullptr; long long sC2 = 0; int ldc2 = 0; double scale2 = 0.0;
+    int noise = 0; double nq[9] = {0}; double *C2 = nullptr; long long sC2 = 0; int ldc2 = 0; double scale2 = 0.0; int ktri = 0;
     int gemm(const double *A, long long sA, int lda, const double *B, long long sB, int ldb, double *C, long long sC, int ldc,
              int M, int N, int K, double w0, double alpha, double beta, const int32_t *skip, int upper)
     {
@@ -544,7 +544,8 @@ struct AugRun {
         g.lda = lda; g.ldb = ldb; g.ldc = ldc; g.alpha = alpha; g.beta = beta; g.w0 = w0; g.skip = skip; g.upper = upper;
         g.noise = noise; for (int i = 0; i < 9; ++i) g.nq[i] = nq[i];
         g.C2 = C2; g.sC2 = sC2; g.ldc2 = ldc2; g.scale2 = scale2; g.Dinv = nullptr; g.sDinv = 0;
-        noise = 0; C2 = nullptr;
+        g.ktri = h->opt_aug_gemm == 0 ? ktri : 0;
+        noise = 0; C2 = nullptr; ktri = 0;
         if (h->opt_aug_gemm == 0) {                               // DMMA fed by TMA (default)
             // CTA tile: 64 x 64 with three CTAs per SM.  ukf_aug.tile = 128 selects 128 x 128 (16 consumer warps, one
             // CTA per SM, half the L2 -> shared traffic per flop): measured SLOWER on B200 (Pzx 2.96 vs 2.54 ms per
@@ -588,7 +589,7 @@ struct AugRun {
         g.lda = lda; g.ldb = ldb; g.ldc = ldc; g.alpha = -1.0; g.beta = 1.0; g.w0 = 0.0; g.skip = skip; g.upper = 0;
         g.noise = 0; for (int i = 0; i < 9; ++i) g.nq[i] = 0.0;
         g.C2 = nullptr; g.sC2 = 0; g.ldc2 = 0; g.scale2 = 0.0;
-        g.Dinv = Dinv + (size_t)blk * 1024; g.sDinv = sDinv;
+        g.Dinv = Dinv + (size_t)blk * 1024; g.sDinv = sDinv; g.ktri = 0;
         // 32 x 64 tiles (warp tile 32 x 16, 3 CTAs per SM); ukf_aug.solve_tile = 128 selects 32 x 128 (warp tile 32 x 32,
         // 2 CTAs per SM): measured slower on B200 (45.1 against 42.4 ms per 1,024 filters at L = 200)
         const int rc = h->opt_aug_solve_tile != 128 ? gemm_tma<32, 64, 1, 4, 3, true>(g, h->aug_attr_set[2])
@@ -765,6 +766,9 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
             // Cholesky is taken in place - S itself is not needed again (W-form update)
             run.noise = 2; run.nq[0] = a.var_dist; run.nq[1] = a.var_angle;
             AUG_TRY(run.gemm(a.H, mz, dz, a.H, mz, dz, a.U, nl, dz, dz, dz, m, wc0 - wi, wi, 0.0, a.status, 1));   // S (upper)
+            // Pzx = E^T diag(Wc) Y.  When Y holds residuals of points about their own centre (re-draw, or no predict) its rows
+            // are 0, +T, -T with T upper triangular and exact zeros below: the product skips the k-tiles that are all zero
+            if (hx_from_U) run.ktri = n;
             AUG_TRY(run.gemm(a.H, mz, dz, a.Y, ml, ldn, a.Kt, zn, n1, dz, n, m, wc0 - wi, wi, 0.0, a.status, 0));  // Pzx
             AUG_TRY(run.chol(a.U, nl, dz, dz, a.status, LSLAM_UKF_ST_S));
             AUG_TRY(run.forward_solve(a.U, nl, dz, dz, a.Kt, zn, n1, n1, a.status));   // U^T W = [Pzx | r]

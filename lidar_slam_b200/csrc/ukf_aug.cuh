@@ -55,6 +55,9 @@ struct AugGemm {
     double scale2;
     const double *Dinv;             // SOLVE kernels: the inverted 32 x 32 diagonal block, row-major [k][r] (aug_chol_diag_kernel)
     long long sDinv;
+    int ktri;                       // > 0: B holds residuals of sigma points about their own centre, B = [0; +T; -T] with T
+                                    // (ktri x ktri) upper triangular: B[k, j] is an exact 0 for 1 + j < k <= ktri and for
+                                    // ktri + 1 + j < k, so a column tile only walks the k-tiles that can be non-zero
 };
 
 // one output element: C = beta C + alpha acc (+ the central-weight term) (+ noise), optional scaled copy
@@ -376,7 +379,19 @@ aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const 
         mbar_fence_init();
     }
     __syncthreads();
-    const int ntiles = (g.K + kAugBK - 1) / kAugBK;
+    // k-tiles this CTA walks: all of them, or (ktri) the two runs that can hold non-zeros of B's columns
+    // [j0, j0 + TN): rows [0, j0 + TN + 1) and [ktri + 1, ktri + 1 + j0 + TN) - skipped terms are products
+    // with exact zeros, the sums do not change by a bit
+    const int ntiles_all = (g.K + kAugBK - 1) / kAugBK;
+    int run1 = ntiles_all, skip12 = 0;                                // tiles [0, run1) then [run1 + skip12, ...)
+    int ntiles = ntiles_all;
+    if (g.ktri > 0) {
+        const int e1 = j0 + TN + 1 < g.K ? j0 + TN + 1 : g.K;          // end of the first run (rows)
+        const int b2 = g.ktri + 1, e2 = b2 + j0 + TN < g.K ? b2 + j0 + TN : g.K;
+        const int t1 = (e1 + kAugBK - 1) / kAugBK, tb2 = b2 / kAugBK, te2 = (e2 + kAugBK - 1) / kAugBK;
+        if (tb2 > t1) { run1 = t1; skip12 = tb2 - t1; ntiles = t1 + (te2 - tb2); }
+        else { ntiles = te2 > t1 ? te2 : t1; run1 = ntiles; }
+    }
     if (warp == NW) {                                                 // ---- producer
         if (lane == 0) {
             bool any = false;
@@ -392,8 +407,9 @@ aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const 
                     if (t >= S) mbar_wait_relaxed(&empty[s], ((t / S) - 1) & 1);
                     double *as = sm + (size_t)s * STAGE, *bs = as + kAugBK * LDA;
                     mbar_expect_tx(&full[s], (unsigned)(STAGE * sizeof(double)));
-                    tma_load_3d(as, &mapA, i0, t * kAugBK, f, &full[s]);
-                    tma_load_3d(bs, &mapB, j0, t * kAugBK, f, &full[s]);
+                    const int kt = t < run1 ? t : t + skip12;
+                    tma_load_3d(as, &mapA, i0, kt * kAugBK, f, &full[s]);
+                    tma_load_3d(bs, &mapB, j0, kt * kAugBK, f, &full[s]);
                 }
         }
         return;

@@ -9,8 +9,8 @@ from tests import emu_util as eu, ukf_aug_util as au
 from lidar_slam_b200 import batch
 
 
-@pytest.mark.parametrize("L,F,flags", [(4, 3, 7), (4, 2, 3), (3, 2, 1), (3, 2, 2), (18, 1, 7)],
-                         ids=["L4", "L4-noredraw", "L3-predict", "L3-update", "L18-two-panels"])
+@pytest.mark.parametrize("L,F,flags", [(4, 3, 7), (4, 2, 3), (3, 2, 1), (3, 2, 2), (18, 1, 7), (48, 1, 7)],
+                         ids=["L4", "L4-noredraw", "L3-predict", "L3-update", "L18-two-panels", "L48-skips-zero-k-tiles"])
 def test_aug_step_matches_literal(L, F, flags):
     x, P, u, z = au.aug_case(F, L, seed=10 + L)
     want = au.oracle_aug(x, P, u, z, flags)
