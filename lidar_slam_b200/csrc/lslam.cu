@@ -534,7 +534,7 @@ struct AugRun {
     }
     // epilogue extras of the next gemm() call (reset by it): noise 1 = + Q (nq[9]) on the pose block, 2 = + R (nq[0], nq[1])
     // on the diagonal; C2 = a second, scaled copy of the result
-    int noise = 0; double nq[9] = {0}; double *C2 = nullptr; long long sC2 = 0; int ldc2 = 0; double scale2 = 0.0; int ktri = 0;
+    int noise = 0; double nq[9] = {0}; double *C2 = nullptr; long long sC2 = 0; int ldc2 = 0; double scale2 = 0.0; int ktri = 0, mirror = 0;
     int gemm(const double *A, long long sA, int lda, const double *B, long long sB, int ldb, double *C, long long sC, int ldc,
              int M, int N, int K, double w0, double alpha, double beta, const int32_t *skip, int upper)
     {
@@ -544,8 +544,8 @@ struct AugRun {
         g.lda = lda; g.ldb = ldb; g.ldc = ldc; g.alpha = alpha; g.beta = beta; g.w0 = w0; g.skip = skip; g.upper = upper;
         g.noise = noise; for (int i = 0; i < 9; ++i) g.nq[i] = nq[i];
         g.C2 = C2; g.sC2 = sC2; g.ldc2 = ldc2; g.scale2 = scale2; g.Dinv = nullptr; g.sDinv = 0;
-        g.ktri = h->opt_aug_gemm == 0 ? ktri : 0;
-        noise = 0; C2 = nullptr; ktri = 0;
+        g.ktri = h->opt_aug_gemm == 0 ? ktri : 0; g.mirror = mirror;
+        noise = 0; C2 = nullptr; ktri = 0; mirror = 0;
         if (h->opt_aug_gemm == 0) {                               // DMMA fed by TMA (default)
             // CTA tile: 64 x 64 with three CTAs per SM.  ukf_aug.tile = 128 selects 128 x 128 (16 consumer warps, one
             // CTA per SM, half the L2 -> shared traffic per flop): measured SLOWER on B200 (Pzx 2.96 vs 2.54 ms per
@@ -589,7 +589,7 @@ struct AugRun {
         g.lda = lda; g.ldb = ldb; g.ldc = ldc; g.alpha = -1.0; g.beta = 1.0; g.w0 = 0.0; g.skip = skip; g.upper = 0;
         g.noise = 0; for (int i = 0; i < 9; ++i) g.nq[i] = 0.0;
         g.C2 = nullptr; g.sC2 = 0; g.ldc2 = 0; g.scale2 = 0.0;
-        g.Dinv = Dinv + (size_t)blk * 1024; g.sDinv = sDinv; g.ktri = 0;
+        g.Dinv = Dinv + (size_t)blk * 1024; g.sDinv = sDinv; g.ktri = 0; g.mirror = 0;
         // 32 x 64 tiles (warp tile 32 x 16, 3 CTAs per SM); ukf_aug.solve_tile = 128 selects 32 x 128 (warp tile 32 x 32,
         // 2 CTAs per SM): measured slower on B200 (45.1 against 42.4 ms per 1,024 filters at L = 200)
         const int rc = h->opt_aug_solve_tile != 128 ? gemm_tma<32, 64, 1, 4, 3, true>(g, h->aug_attr_set[2])
@@ -711,7 +711,7 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
         a.Pbar = p; p += lay.Pbar * Fb;
         double *dinv = p; p += lay.Dinv * Fb;
         a.xbar = p; p += lay.xbar * Fb;
-        double *xnew = p; p += lay.xnew * Fb;
+        p += lay.xnew * Fb;                                       // (spare vector; the update writes x in place)
         a.zhat = p; a.wm = wm; a.wc = wc;
         a.dt = params_h[0]; a.half_r = params_h[1] / 2.0; a.r_over_l = params_h[1] / params_h[2]; a.cscale = c;
         a.var_dist = params_h[6]; a.var_angle = params_h[7];
@@ -772,13 +772,16 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
             AUG_TRY(run.gemm(a.H, mz, dz, a.Y, ml, ldn, a.Kt, zn, n1, dz, n, m, wc0 - wi, wi, 0.0, a.status, 0));  // Pzx
             AUG_TRY(run.chol(a.U, nl, dz, dz, a.status, LSLAM_UKF_ST_S));
             AUG_TRY(run.forward_solve(a.U, nl, dz, dz, a.Kt, zn, n1, n1, a.status));   // U^T W = [Pzx | r]
-            LSLAM_LAUNCH(aug_update_x_kernel, dim3((n + 31) / 32, Fb), 256, kAugUpdateXSmem, st, a, xnew);
+            // x = xbar + W^T v and P = Pbar - W^T W go straight into the caller's arrays (the epilogue stores both
+            // triangles); a filter that failed a factorisation is skipped by both kernels and keeps its state
+            LSLAM_LAUNCH(aug_update_x_kernel, dim3((n + 31) / 32, Fb), 256, kAugUpdateXSmem, st, a, (double *)nullptr);
             h->launches++;
-            AUG_TRY(run.gemm(a.Kt, zn, n1, a.Kt, zn, n1, a.Pbar, nl, ldn, n, n, dz, 0.0, -1.0, 1.0, a.status, 1));   // P = Pbar - W^T W (upper; commit mirrors)
-            xres = xnew;
+            run.mirror = 1; run.C2 = a.P; run.sC2 = nn; run.ldc2 = n; run.scale2 = 1.0;
+            AUG_TRY(run.gemm(a.Kt, zn, n1, a.Kt, zn, n1, a.Pbar, nl, ldn, n, n, dz, 0.0, -1.0, 1.0, a.status, 1));
+        } else {
+            LSLAM_LAUNCH(aug_commit_kernel, gew, 256, 0, st, a, xres, (const double *)a.Pbar);
+            h->launches++;
         }
-        LSLAM_LAUNCH(aug_commit_kernel, gew, 256, 0, st, a, xres, (const double *)a.Pbar);
-        h->launches++;
         LSLAM_CUDA_TRY(h, cudaGetLastError());
     }
     return LSLAM_OK;

@@ -55,6 +55,7 @@ struct AugGemm {
     double scale2;
     const double *Dinv;             // SOLVE kernels: the inverted 32 x 32 diagonal block, row-major [k][r] (aug_chol_diag_kernel)
     long long sDinv;
+    int mirror;                     // 1: upper-triangle result v goes to C2[i, j] and C2[j, i] (C itself is not written)
     int ktri;                       // > 0: B holds residuals of sigma points about their own centre, B = [0; +T; -T] with T
                                     // (ktri x ktri) upper triangular: B[k, j] is an exact 0 for 1 + j < k <= ktri and for
                                     // ktri + 1 + j < k, so a column tile only walks the k-tiles that can be non-zero
@@ -70,6 +71,11 @@ __device__ __forceinline__ void aug_gemm_store(const AugGemm &g, double *C, doub
     v = (g.beta == 0.0 ? 0.0 : g.beta * *c) + v;
     if (g.noise == 1) { if (i < 3 && j < 3) v = __dadd_rn(v, g.nq[i * 3 + j]); }
     else if (g.noise == 2) { if (i == j) v = __dadd_rn(v, g.nq[i & 1]); }
+    if (g.mirror) {                                                   // final covariance: both triangles straight into the caller's P
+        C2[(size_t)i * g.ldc2 + j] = v;
+        C2[(size_t)j * g.ldc2 + i] = v;
+        return;
+    }
     *c = v;
     if (C2 != nullptr) C2[(size_t)i * g.ldc2 + j] = __dmul_rn(g.scale2, v);
 }
@@ -1056,7 +1062,9 @@ __global__ void __launch_bounds__(256) aug_update_x_kernel(const AugArgs a, doub
     if (warp == 0 && i < a.n) {
         double t = 0.0;
         for (int w = 0; w < 8; ++w) t = __dadd_rn(t, part[w][lane]);
-        xnew_base[(size_t)f * n1 + i] = __dadd_rn(a.xbar[(size_t)f * n1 + i], t);
+        const double xv = __dadd_rn(a.xbar[(size_t)f * n1 + i], t);
+        if (xnew_base) xnew_base[(size_t)f * n1 + i] = xv;
+        else a.x[(size_t)f * a.n + i] = xv;                           // committed directly (status is final by now)
     }
 }
 
