@@ -25,7 +25,7 @@ def run_gpu(eng, x, P, u, z, flags=None, params=None, workspace_filters=None):
     return st["x"].cpu().numpy(), st["P"].cpu().numpy(), st["status"].cpu().numpy()
 
 
-@pytest.mark.parametrize("L,F", [(1, 40), (5, 64), (16, 16), (40, 6), (200, 2)])
+@pytest.mark.parametrize("L,F", [(1, 40), (5, 64), (16, 16), (32, 5), (40, 6), (64, 3), (200, 2), (256, 1)])   # dz = 64, 128, 512: tile-aligned edges
 def test_aug_step_matches_literal(gpu_engine, L, F):
     x, P, u, z = au.aug_case(F, L, seed=L)
     want = au.oracle_aug(x, P, u, z)
