@@ -112,6 +112,9 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
     } else if (!strcmp(key, "ukf_aug.gemm")) {
         if (value < 0 || value > 2) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.gemm: 0 default (DMMA fed by TMA), 1 DFMA, 2 DMMA fed by cp.async");
         h->opt_aug_gemm = (int)value;
+    } else if (!strcmp(key, "ukf_aug.pzx")) {
+        if (value < 0 || value > 1) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.pzx: 1 default (paired + / - points), 0 literal sum over all sigma points");
+        h->opt_aug_pzx = (int)value;
     } else if (!strcmp(key, "ukf_aug.solve_tile")) {
         if (value != 0 && value != 64 && value != 128) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.solve_tile: 0 default (64), 64, 128");
         h->opt_aug_solve_tile = (int)value;
@@ -721,6 +724,10 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
         const long long nn = (long long)n * n, nl = (long long)n * ldn, ml = (long long)m * ldn;
         const dim3 gew(Fb < 64 ? ew : 8, Fb), gcol((n + 31) / 32, Fb);
         const bool redraw = pred && upd && (flags & LSLAM_UKF_REDRAW);
+        // paired cross-covariance (ukf_aug.pzx = 1, default): when the residuals Y are those of sigma points about their own
+        // centre (re-draw, or no predict), Pzx = wi sum_r (e_{1+r} - e_{1+n+r}) y_{1+r}^T - half the depth, and only the
+        // + half of Y is needed (see the update below)
+        const bool paired = h->opt_aug_pzx != 0 && h->opt_aug_gemm == 0 && (redraw || !pred);
         // sigma points of (x, P): U^T U = (n + lambda) P.  The points themselves are not stored: every consumer
         // recomputes them from (x, U) (aug_sigma_value)
         LSLAM_LAUNCH(aug_scale_upper_kernel, gew, 256, 0, st, (const double *)a.P, nn, n, a.U, nl, ldn, n, c, (const int32_t *)a.status);
@@ -731,7 +738,7 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
         bool hx_from_U = true;
         if (pred) {
             // fx, circular mean, residuals in one pass over the factor; X kept only if hx needs the fx'd points
-            LSLAM_LAUNCH(aug_sigma_resid_kernel, gcol, 256, kAugMeanSmem, st, a, (const double *)a.x, n, 1, 0, (upd && !redraw) ? a.X : nullptr);
+            LSLAM_LAUNCH(aug_sigma_resid_kernel, gcol, 256, kAugMeanSmem, st, a, (const double *)a.x, n, 1, 0, (upd && !redraw) ? a.X : nullptr, m);
             h->launches++;
             // Pbar = Y^T diag(Wc) Y + Q; with a re-draw the same epilogue also writes (n + lambda) Pbar, the matrix
             // the next Cholesky factors, into U
@@ -740,7 +747,7 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
             AUG_TRY(run.gemm(a.Y, ml, ldn, a.Y, ml, ldn, a.Pbar, nl, ldn, n, n, m, wc0 - wi, wi, 0.0, a.status, 1));
             if (redraw) {
                 AUG_TRY(run.chol(a.U, nl, ldn, n, a.status, LSLAM_UKF_ST_REDRAW));
-                LSLAM_LAUNCH(aug_sigma_resid_kernel, gcol, 256, kAugMeanSmem, st, a, (const double *)a.xbar, ldn, 0, 1, (double *)nullptr);
+                LSLAM_LAUNCH(aug_sigma_resid_kernel, gcol, 256, kAugMeanSmem, st, a, (const double *)a.xbar, ldn, 0, 1, (double *)nullptr, paired ? n + 1 : m);
                 h->launches++;
                 xs = a.xbar; xs_stride = ldn;
             } else {
@@ -751,7 +758,7 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
                                                 cudaMemcpyDeviceToDevice, st));
             LSLAM_CUDA_TRY(h, cudaMemcpy2DAsync(a.Pbar, sizeof(double) * ldn, a.P, sizeof(double) * n, sizeof(double) * n, (size_t)Fb * n,
                                                 cudaMemcpyDeviceToDevice, st));
-            LSLAM_LAUNCH(aug_sigma_resid_kernel, gcol, 256, kAugMeanSmem, st, a, (const double *)a.x, n, 0, 1, (double *)nullptr);
+            LSLAM_LAUNCH(aug_sigma_resid_kernel, gcol, 256, kAugMeanSmem, st, a, (const double *)a.x, n, 0, 1, (double *)nullptr, upd && paired ? n + 1 : m);
             h->launches++;
         }
         const double *xres = a.xbar;
@@ -759,7 +766,8 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
             const int n1 = ldn;                                   // W: dz x (n + 1), right-hand sides [Pzx | r]
             const long long zn = (long long)dz * n1, mz = (long long)m * dz;
             LSLAM_LAUNCH(aug_hx_kernel, gew, 256, 0, st, a, xs, xs_stride, hx_from_U ? 1 : 0);
-            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3((dz + 31) / 32, Fb), 256, kAugMeanSmem, st, a, (const double *)a.H, dz, dz, 1, 0, a.zhat, dz, a.H);
+            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3((dz + 31) / 32, Fb), 256, kAugMeanSmem, st, a, (const double *)a.H, dz, dz, 1, 0, a.zhat, dz, a.H,
+                         paired ? a.X : (double *)nullptr);     // D = E+ - E- parks in X (unused when the points are not stored)
             LSLAM_LAUNCH(aug_innovation_kernel, dim3(Fb), 256, 0, st, a);
             h->launches += 3;
             // S = E^T diag(Wc) E + R straight into U (pitch dz; a.U keeps its n * ldn stride per filter), where its
@@ -767,9 +775,18 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
             run.noise = 2; run.nq[0] = a.var_dist; run.nq[1] = a.var_angle;
             AUG_TRY(run.gemm(a.H, mz, dz, a.H, mz, dz, a.U, nl, dz, dz, dz, m, wc0 - wi, wi, 0.0, a.status, 1));   // S (upper)
             // Pzx = E^T diag(Wc) Y.  When Y holds residuals of points about their own centre (re-draw, or no predict) its rows
-            // are 0, +T, -T with T upper triangular and exact zeros below: the product skips the k-tiles that are all zero
-            if (hx_from_U) run.ktri = n;
-            AUG_TRY(run.gemm(a.H, mz, dz, a.Y, ml, ldn, a.Kt, zn, n1, dz, n, m, wc0 - wi, wi, 0.0, a.status, 0));  // Pzx
+            // are 0, +T, -T with T upper triangular and exact zeros below.
+            if (paired) {
+                // The - point of factor row r has the residual -y_{1+r} up to one rounding of x (y = fl(fl(x + u) - x) against
+                // fl(fl(x - u) - x): both are u to within ulp(x)), so  Pzx = wi sum_r (e_{1+r} - e_{1+n+r}) y_{1+r}^T = wi D^T T:
+                // depth n instead of 2n + 1, the central point drops out (y_0 = 0), and a column tile walks rows [0, j0 + TN) of T.
+                // Differs from the literal sum by O(ulp(x) |e|) per term - the size of the rounding noise the literal sum carries.
+                run.ktri = -1;
+                AUG_TRY(run.gemm(a.X, (long long)n * dz, dz, a.Y + ldn, ml, ldn, a.Kt, zn, n1, dz, n, n, 0.0, wi, 0.0, a.status, 0));
+            } else {
+                if (hx_from_U) run.ktri = n;                      // literal sum, k-tiles that are all zero skipped
+                AUG_TRY(run.gemm(a.H, mz, dz, a.Y, ml, ldn, a.Kt, zn, n1, dz, n, m, wc0 - wi, wi, 0.0, a.status, 0));
+            }
             AUG_TRY(run.chol(a.U, nl, dz, dz, a.status, LSLAM_UKF_ST_S));
             AUG_TRY(run.forward_solve(a.U, nl, dz, dz, a.Kt, zn, n1, n1, a.status));   // U^T W = [Pzx | r]
             // x = xbar + W^T v and P = Pbar - W^T W go straight into the caller's arrays (the epilogue stores both

@@ -56,7 +56,8 @@ struct AugGemm {
     const double *Dinv;             // SOLVE kernels: the inverted 32 x 32 diagonal block, row-major [k][r] (aug_chol_diag_kernel)
     long long sDinv;
     int mirror;                     // 1: upper-triangle result v goes to C2[i, j] and C2[j, i] (C itself is not written)
-    int ktri;                       // > 0: B holds residuals of sigma points about their own centre, B = [0; +T; -T] with T
+    int ktri;                       // < 0: B is upper triangular (K x K), a column tile walks rows [0, j0 + TN) only;
+                                    // > 0: B holds residuals of sigma points about their own centre, B = [0; +T; -T] with T
                                     // (ktri x ktri) upper triangular: B[k, j] is an exact 0 for 1 + j < k <= ktri and for
                                     // ktri + 1 + j < k, so a column tile only walks the k-tiles that can be non-zero
 };
@@ -391,7 +392,10 @@ aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const 
     const int ntiles_all = (g.K + kAugBK - 1) / kAugBK;
     int run1 = ntiles_all, skip12 = 0;                                // tiles [0, run1) then [run1 + skip12, ...)
     int ntiles = ntiles_all;
-    if (g.ktri > 0) {
+    if (g.ktri < 0) {                                                 // B = T itself (K x K upper triangular): rows [0, j0 + TN)
+        const int e1 = j0 + TN < g.K ? j0 + TN : g.K;
+        ntiles = run1 = (e1 + kAugBK - 1) / kAugBK;
+    } else if (g.ktri > 0) {
         const int e1 = j0 + TN + 1 < g.K ? j0 + TN + 1 : g.K;          // end of the first run (rows)
         const int b2 = g.ktri + 1, e2 = b2 + j0 + TN < g.K ? b2 + j0 + TN : g.K;
         const int t1 = (e1 + kAugBK - 1) / kAugBK, tb2 = b2 / kAugBK, te2 = (e2 + kAugBK - 1) / kAugBK;
@@ -889,7 +893,7 @@ __device__ __forceinline__ double aug_fx_pose(const AugArgs &a, const double *x,
 // in warp order; pass 2: Y[k] = residual_x(sigma_k, mean), and the points themselves into Xout if the
 // caller still needs them (update without re-draw).
 __global__ void __launch_bounds__(256) aug_sigma_resid_kernel(const AugArgs a, const double *x0, int sx, int do_fx, int mean_given,
-                                                              double *Xout)
+                                                              double *Xout, int rows)
 {
     LSLAM_SMEM_DECL;
     double *part = reinterpret_cast<double *>(smem_raw);             // [8][32][2], then mu at [512 + lane]
@@ -927,7 +931,7 @@ __global__ void __launch_bounds__(256) aug_sigma_resid_kernel(const AugArgs a, c
     if (!live) return;
     const double mu = part[512 + lane];
     double *X = Xout ? Xout + (size_t)f * a.m * ld : nullptr;
-    for (int k = warp; k < a.m; k += 8) {
+    for (int k = warp; k < rows; k += 8) {                            // rows = 2n + 1, or n + 1 when only the + points are needed
         const double v = posefx ? aug_fx_pose(a, x, U, k, c, ul, ur) : aug_sigma_value(x, U, ld, n, k, c);
         double d = __dsub_rn(v, mu);
         if (ang) d = ukf_normalize_angle(d);
@@ -942,7 +946,8 @@ __global__ void __launch_bounds__(256) aug_sigma_resid_kernel(const AugArgs a, c
 // columns (coalesced), the 8 partial sums are added in warp order, then every warp writes the residuals
 // of its rows.  mean_given: the mean is an input (residuals of re-drawn sigma points about the prior).
 __global__ void __launch_bounds__(256) aug_mean_resid_kernel(const AugArgs a, const double *Vbase, int cols, int ld, int is_meas,
-                                                             int mean_given, double *mean_base, int mean_stride, double *Rbase)
+                                                             int mean_given, double *mean_base, int mean_stride, double *Rbase,
+                                                             double *Dbase)
 {
     LSLAM_SMEM_DECL;
     double *part = reinterpret_cast<double *>(smem_raw);             // [8][32][2], then mu at [512 + lane]
@@ -979,6 +984,24 @@ __global__ void __launch_bounds__(256) aug_mean_resid_kernel(const AugArgs a, co
     }
     if (!live) return;
     const double mu = part[512 + lane];
+    if (Dbase != nullptr) {
+        // also D[r] = R[1 + r] - R[1 + n + r], the difference of the residuals of the + and the - point of factor
+        // row r (n x cols, pitch ld): the operand of the paired cross-covariance product (lslam_ukf_aug_step)
+        double *D = Dbase + (size_t)f * a.n * ld;
+        if (warp == 0) {
+            double d = __dsub_rn(V[c], mu);
+            if (ang) d = ukf_normalize_angle(d);
+            R[c] = d;
+        }
+        for (int r = warp; r < a.n; r += 8) {
+            double d1 = __dsub_rn(V[(size_t)(1 + r) * ld + c], mu), d2 = __dsub_rn(V[(size_t)(1 + a.n + r) * ld + c], mu);
+            if (ang) { d1 = ukf_normalize_angle(d1); d2 = ukf_normalize_angle(d2); }
+            R[(size_t)(1 + r) * ld + c] = d1;
+            R[(size_t)(1 + a.n + r) * ld + c] = d2;
+            D[(size_t)r * ld + c] = __dsub_rn(d1, d2);
+        }
+        return;
+    }
     for (int k = warp; k < a.m; k += 8) {
         double d = __dsub_rn(V[(size_t)k * ld + c], mu);
         if (ang) d = ukf_normalize_angle(d);

@@ -36,6 +36,28 @@ def test_aug_step_matches_literal(gpu_engine, L, F):
     print("L=%d err x %.2e P %.2e (oracle one-ulp sensitivity %.2e %.2e)" % (L, ex, eP, cond[0], cond[1]))
 
 
+@pytest.mark.parametrize("L,F", [(40, 4), (200, 1)])
+def test_aug_literal_and_paired_cross_covariance(gpu_engine, L, F):
+    """ukf_aug.pzx = 0 (the literal sum over all 2n + 1 sigma points, zero k-tiles skipped) and 1 (default: + / - points
+    paired, half the depth) both hold the parity bar, and differ from each other by far less than the bar."""
+    x, P, u, z = au.aug_case(F, L, seed=100 + L)
+    want = au.oracle_aug(x, P, u, z)
+    cond = au.oracle_conditioning(x, P, u, z, want)
+    got = {}
+    try:
+        for mode in (0, 1):
+            gpu_engine.set_option("ukf_aug.pzx", mode)
+            xg, Pg, st = run_gpu(gpu_engine, x, P, u, z)
+            assert not st.any()
+            ex, eP = au.assert_aug_close(want, (xg, Pg), "pzx mode %d L=%d" % (mode, L), cond=cond)
+            print("L=%d pzx=%d err x %.2e P %.2e (oracle one-ulp sensitivity %.2e %.2e)" % (L, mode, ex, eP, cond[0], cond[1]))
+            got[mode] = (xg, Pg)
+    finally:
+        gpu_engine.set_option("ukf_aug.pzx", 1)
+    dx, dP = au._errors(got[0], got[1])
+    assert dx < 1e-6 and dP < 1e-6, (dx, dP)
+
+
 @pytest.mark.parametrize("flags", [1, 2, 3])
 def test_aug_halves(gpu_engine, flags):
     x, P, u, z = au.aug_case(8, 20, seed=flags)
