@@ -766,7 +766,7 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
             const int n1 = ldn;                                   // W: dz x (n + 1), right-hand sides [Pzx | r]
             const long long zn = (long long)dz * n1, mz = (long long)m * dz;
             LSLAM_LAUNCH(aug_hx_kernel, gew, 256, 0, st, a, xs, xs_stride, hx_from_U ? 1 : 0);
-            LSLAM_LAUNCH(aug_mean_resid_kernel, dim3((dz + 31) / 32, Fb), 256, kAugMeanSmem, st, a, (const double *)a.H, dz, dz, 1, 0, a.zhat, dz, a.H,
+            LSLAM_LAUNCH(aug_meas_resid_kernel, dim3((L + 31) / 32, Fb), 256, kAugMeasSmem, st, a,
                          paired ? a.X : (double *)nullptr);     // D = E+ - E- parks in X (unused when the points are not stored)
             LSLAM_LAUNCH(aug_innovation_kernel, dim3(Fb), 256, 0, st, a);
             h->launches += 3;

@@ -651,14 +651,17 @@ __global__ void __launch_bounds__(160) aug_chol_diag_kernel(double *Abase, long 
     // (dsave holds the roots), so reading the next pivot needs no extra barrier.
     int ok = 1;
     for (int r = 0; r < nb; ++r) {
-        const double piv = Ub[r][r];
-        if (!(piv > 0.0)) { ok = 0; break; }                          // uniform: every thread reads the same pivot
-        const double d = sqrt(piv), ri = 1.0 / d;
-        if (warp == 0) {
-            if (lane > r) Ub[r][lane] = __dmul_rn(Ub[r][lane], ri);
-            if (lane == 0) { rinv[r] = ri; dsave[r] = d; }
+        if (warp == 0) {                                              // root and reciprocal once, not by every warp: with several
+            const double piv = Ub[r][r];                              // CTAs per SM the redundant fp64 sqrt / divide chains of all
+            if (!(piv > 0.0)) { if (lane == 0) bad = 1; }             // warps were a third of the kernel
+            else {
+                const double d = sqrt(piv), ri = 1.0 / d;
+                if (lane > r) Ub[r][lane] = __dmul_rn(Ub[r][lane], ri);
+                if (lane == 0) { rinv[r] = ri; dsave[r] = d; }
+            }
         }
         __syncthreads();
+        if (bad) { ok = 0; break; }                                   // uniform: read after the barrier
         for (int ii = r + 1 + warp; ii < nb; ii += nwarp)
             if (lane >= ii) Ub[ii][lane] = fma(-Ub[r][ii], Ub[r][lane], Ub[ii][lane]);
         __syncthreads();
@@ -940,73 +943,69 @@ __global__ void __launch_bounds__(256) aug_sigma_resid_kernel(const AugArgs a, c
     }
 }
 
-// weighted column means of V [m x cols] with circular means on the angle columns (state: column 2;
-// measurement: odd columns), then the residuals V[k] - mean (angles wrapped) into R (may alias V).
-// One CTA per (32-column group, filter): warp w sums rows w, w+8, ... with lanes across 32 consecutive
-// columns (coalesced), the 8 partial sums are added in warp order, then every warp writes the residuals
-// of its rows.  mean_given: the mean is an input (residuals of re-drawn sigma points about the prior).
-__global__ void __launch_bounds__(256) aug_mean_resid_kernel(const AugArgs a, const double *Vbase, int cols, int ld, int is_meas,
-                                                             int mean_given, double *mean_base, int mean_stride, double *Rbase,
-                                                             double *Dbase)
+// Measurement side: zhat = z_mean(H, Wm) (UKFMethods.py:47-57: weighted mean of the ranges, circular mean of the
+// bearings), then E = residual_h(H, zhat) in place, and optionally D[r] = E[1 + r] - E[1 + n + r] (the operand
+// of the paired cross-covariance product, lslam_ukf_aug_step).  One CTA per (32 landmarks, filter); lane l owns
+// the (range, bearing) PAIR of one landmark - one 16-byte load per sigma point, and every lane of a warp runs
+// the bearing's sincos (with a column per lane half of the lanes idle through it: the pass was
+// instruction-bound on exactly that).  8 warps over the sigma points, partial sums added in warp order - the
+// same order of additions per column as a column-per-lane layout.
+constexpr size_t kAugMeasSmem = (8 * 32 * 3 + 64) * sizeof(double);
+__global__ void __launch_bounds__(256) aug_meas_resid_kernel(const AugArgs a, double *Dbase)
 {
     LSLAM_SMEM_DECL;
-    double *part = reinterpret_cast<double *>(smem_raw);             // [8][32][2], then mu at [512 + lane]
+    double *part = reinterpret_cast<double *>(smem_raw);             // [8][32][3], then (mu_r, mu_b) at [768 + 2 lane]
     const int f = blockIdx.y;
     if (a.status[f] != 0) return;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int c = blockIdx.x * 32 + lane;
-    const bool live = c < cols;
-    const double *V = Vbase + (size_t)f * a.m * ld;
-    double *mean = mean_base + (size_t)f * mean_stride, *R = Rbase + (size_t)f * a.m * ld;
-    const bool ang = is_meas ? (c & 1) : (c == 2);
-    if (!mean_given) {
-        double s0 = 0.0, s1 = 0.0;
-        if (live) {
-            for (int k = warp; k < a.m; k += 8) {
-                const double v = V[(size_t)k * ld + c], w = a.wm[k];
-                if (ang) { double sn, cs; sincos(v, &sn, &cs); s0 = fma(sn, w, s0); s1 = fma(cs, w, s1); }
-                else s0 = fma(v, w, s0);
-            }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, dz = a.dz, n = a.n;
+    const int l = blockIdx.x * 32 + lane;
+    const bool live = l < a.L;
+    double *H = a.H + (size_t)f * a.m * dz + 2 * l;                   // this landmark's column pair, row pitch dz
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+    if (live) {
+        for (int k = warp; k < a.m; k += 8) {
+            const double2 v = *reinterpret_cast<const double2 *>(H + (size_t)k * dz);
+            const double w = a.wm[k];
+            double sn, cs;
+            sincos(v.y, &sn, &cs);
+            s0 = fma(v.x, w, s0); s1 = fma(sn, w, s1); s2 = fma(cs, w, s2);
         }
-        part[(warp * 32 + lane) * 2] = s0; part[(warp * 32 + lane) * 2 + 1] = s1;
-        __syncthreads();
-        if (warp == 0) {
-            double t0 = 0.0, t1 = 0.0;
-            for (int w = 0; w < 8; ++w) { t0 = __dadd_rn(t0, part[(w * 32 + lane) * 2]); t1 = __dadd_rn(t1, part[(w * 32 + lane) * 2 + 1]); }
-            const double mu = ang ? atan2(t0, t1) : t0;
-            part[512 + lane] = mu;
-            if (live) mean[c] = mu;
-        }
-        __syncthreads();
-    } else {
-        if (warp == 0) part[512 + lane] = live ? mean[c] : 0.0;
-        __syncthreads();
     }
-    if (!live) return;
-    const double mu = part[512 + lane];
-    if (Dbase != nullptr) {
-        // also D[r] = R[1 + r] - R[1 + n + r], the difference of the residuals of the + and the - point of factor
-        // row r (n x cols, pitch ld): the operand of the paired cross-covariance product (lslam_ukf_aug_step)
-        double *D = Dbase + (size_t)f * a.n * ld;
-        if (warp == 0) {
-            double d = __dsub_rn(V[c], mu);
-            if (ang) d = ukf_normalize_angle(d);
-            R[c] = d;
+    part[(warp * 32 + lane) * 3] = s0; part[(warp * 32 + lane) * 3 + 1] = s1; part[(warp * 32 + lane) * 3 + 2] = s2;
+    __syncthreads();
+    if (warp == 0) {
+        double t0 = 0.0, t1 = 0.0, t2 = 0.0;
+        for (int w = 0; w < 8; ++w) {
+            t0 = __dadd_rn(t0, part[(w * 32 + lane) * 3]);
+            t1 = __dadd_rn(t1, part[(w * 32 + lane) * 3 + 1]);
+            t2 = __dadd_rn(t2, part[(w * 32 + lane) * 3 + 2]);
         }
-        for (int r = warp; r < a.n; r += 8) {
-            double d1 = __dsub_rn(V[(size_t)(1 + r) * ld + c], mu), d2 = __dsub_rn(V[(size_t)(1 + a.n + r) * ld + c], mu);
-            if (ang) { d1 = ukf_normalize_angle(d1); d2 = ukf_normalize_angle(d2); }
-            R[(size_t)(1 + r) * ld + c] = d1;
-            R[(size_t)(1 + a.n + r) * ld + c] = d2;
-            D[(size_t)r * ld + c] = __dsub_rn(d1, d2);
+        const double mb = atan2(t1, t2);
+        part[768 + 2 * lane] = t0; part[768 + 2 * lane + 1] = mb;
+        if (live) { a.zhat[(size_t)f * dz + 2 * l] = t0; a.zhat[(size_t)f * dz + 2 * l + 1] = mb; }
+    }
+    __syncthreads();
+    if (!live) return;
+    const double mr = part[768 + 2 * lane], mb = part[768 + 2 * lane + 1];
+    auto resid = [&](int k) {
+        double2 v = *reinterpret_cast<const double2 *>(H + (size_t)k * dz);
+        v.x = __dsub_rn(v.x, mr);
+        v.y = ukf_normalize_angle(__dsub_rn(v.y, mb));
+        *reinterpret_cast<double2 *>(H + (size_t)k * dz) = v;
+        return v;
+    };
+    if (Dbase != nullptr) {
+        double *D = Dbase + (size_t)f * n * dz + 2 * l;
+        if (warp == 0) resid(0);
+        for (int r = warp; r < n; r += 8) {
+            const double2 e1 = resid(1 + r), e2 = resid(1 + n + r);
+            double2 d;
+            d.x = __dsub_rn(e1.x, e2.x); d.y = __dsub_rn(e1.y, e2.y);
+            *reinterpret_cast<double2 *>(D + (size_t)r * dz) = d;
         }
         return;
     }
-    for (int k = warp; k < a.m; k += 8) {
-        double d = __dsub_rn(V[(size_t)k * ld + c], mu);
-        if (ang) d = ukf_normalize_angle(d);
-        R[(size_t)k * ld + c] = d;
-    }
+    for (int k = warp; k < a.m; k += 8) resid(k);
 }
 
 // hx of every sigma point: (range, bearing) of every landmark read from the state (oracle/ukf.py
