@@ -113,7 +113,7 @@ def emu_ukf_step(x, P, u, z, lm_pos, lm_valid=None, valid_min=1, zmode=0, params
     return x, P, status
 
 
-def emu_ukf_aug_step(x, P, u, z, params=None, flags=7, workspace_filters=None, handle=None):
+def emu_ukf_aug_step(x, P, u, z, params=None, flags=7, workspace_filters=None, handle=None, ws_fill=0):
     """lslam_ukf_aug_step on the emulated library.  x [F, n], P [F, n, n], z [F, L, 2]; returns copies
     (x_new, P_new, status).  workspace_filters < F exercises the batching."""
     from lidar_slam_b200 import batch
@@ -127,8 +127,14 @@ def emu_ukf_aug_step(x, P, u, z, params=None, flags=7, workspace_filters=None, h
     status = np.full(F, -99, np.int32)
     params = batch.Engine.ukf_params() if params is None else list(params)
     nbytes = h.ukf_aug_workspace_bytes(L, workspace_filters or F)
-    ws = np.zeros(nbytes, np.uint8)
+    # guard bands around the scratch (and ws_fill = 0xFF: a workspace full of NaNs) catch out-of-bounds writes and
+    # reads of scratch the step did not write first
+    guard = 4096
+    big = np.full(nbytes + 2 * guard, ws_fill, np.uint8)
+    big[:guard] = 0xA5; big[guard + nbytes:] = 0xA5
+    ws = big[guard:guard + nbytes]
     h.ukf_aug_step(ptr(x), ptr(P), ptr(u), ptr(z), F, L, params, flags, ptr(status), ptr(ws), nbytes)
+    assert (big[:guard] == 0xA5).all() and (big[guard + nbytes:] == 0xA5).all(), "lslam_ukf_aug_step wrote outside its workspace"
     return x, P, status
 
 

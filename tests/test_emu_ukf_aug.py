@@ -54,6 +54,18 @@ def test_aug_batching_and_failed_filters_keep_state():
     au.assert_aug_close(want, (a[0][keep], a[1][keep]), "neighbours", cond=cond)
 
 
+@pytest.mark.parametrize("flags", [7, 3, 2])
+def test_aug_scratch_is_written_before_it_is_read(flags):
+    """A workspace full of NaNs gives the same bits as a zeroed one (no stage reads scratch it did not write), in the
+    re-draw, no-re-draw and update-only orders of stages."""
+    x, P, u, z = au.aug_case(2, 18, seed=21)
+    a = eu.emu_ukf_aug_step(x, P, u, z, flags=flags)
+    b = eu.emu_ukf_aug_step(x, P, u, z, flags=flags, ws_fill=0xFF)
+    for p, q in zip(a, b):
+        assert np.array_equal(p, q)
+    assert np.isfinite(b[0]).all() and np.isfinite(b[1]).all()
+
+
 def test_aug_bad_arguments():
     h = eu.emu_handle()
     from lidar_slam_b200._lib import LslamError

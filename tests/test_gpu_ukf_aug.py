@@ -79,6 +79,39 @@ def test_aug_strict_tolerance_with_wider_sigma_spread(gpu_engine):
     assert ex < 1e-7 and eP < 1e-7
 
 
+@pytest.mark.parametrize("L,flags", [(40, 7), (40, 3), (40, 2), (200, 7)])
+def test_aug_scratch_guards_and_nan_workspace(gpu_engine, L, flags):
+    """Guard bands around x, P and the workspace stay untouched, and a workspace full of NaNs gives the same bits as a
+    zeroed one (no kernel reads scratch the step did not write first; TMA over-fetch columns are never used)."""
+    import torch
+    eng = gpu_engine
+    dev = eng.device
+    F = 3
+    n = 3 + 2 * L
+    x, P, u, z = au.aug_case(F, L, seed=300 + L)
+    nbytes = eng.handle.ukf_aug_workspace_bytes(L, F)
+    G = 4096
+    outs = []
+    for fill in (0, 0xFF):
+        big = torch.full((nbytes + 2 * G,), fill, dtype=torch.uint8, device=dev)
+        big[:G] = 0xA5; big[G + nbytes:] = 0xA5
+        xb = torch.full((F * n + 64,), 7.25, dtype=torch.float64, device=dev)
+        Pb = torch.full((F * n * n + 64,), 7.25, dtype=torch.float64, device=dev)
+        st = eng.alloc_ukf_aug(F, L, workspace_filters=1)
+        st["workspace"] = big[G:G + nbytes]
+        st["x"] = xb[32:32 + F * n].view(F, n); st["x"].copy_(torch.from_numpy(x))
+        st["P"] = Pb[32:32 + F * n * n].view(F, n, n); st["P"].copy_(torch.from_numpy(P))
+        eng.ukf_aug_step(st, torch.from_numpy(z).to(dev), u=torch.from_numpy(u).to(dev), flags=flags)
+        torch.cuda.synchronize()
+        assert not st["status"].any().item()
+        assert (big[:G] == 0xA5).all().item() and (big[G + nbytes:] == 0xA5).all().item(), "workspace guard"
+        for buf, m in ((xb, F * n), (Pb, F * n * n)):
+            assert (buf[:32] == 7.25).all().item() and (buf[32 + m:] == 7.25).all().item(), "state guard"
+        outs.append((st["x"].cpu().numpy().copy(), st["P"].cpu().numpy().copy()))
+    assert np.isfinite(outs[1][0]).all() and np.isfinite(outs[1][1]).all()
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+
+
 def test_aug_batching_failures_and_repeat_steps(gpu_engine):
     import torch
     L, F = 12, 37
