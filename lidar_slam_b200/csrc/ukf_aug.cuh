@@ -554,7 +554,7 @@ aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const 
 // (History, B200, 256 matrices of 403: DFMA accumulation from a shared-memory tile + one-warp inverse 68 us
 // per launch - profiles/r01r; a fully unrolled in-register factorisation was no faster: ~80 KB of
 // straight-line code executed once per CTA runs at the speed of instruction-cache misses.)
-constexpr int kAugDiagStages = 4;
+constexpr int kAugDiagStages = 2;      // 29 KB of shared memory: 7 CTAs per SM, so 1,024 matrices are one wave (4 stages: 5 per SM, two waves, 2 x the time)
 constexpr size_t kAugDiagSmem = 128 + (size_t)kAugDiagStages * kAugBK * 36 * sizeof(double) + 2 * kAugDiagStages * sizeof(Mbar) +
                                 (2 * 32 * 33 + 4 * 8 * 9 + 64) * sizeof(double) + 16;
 __global__ void __launch_bounds__(160) aug_chol_diag_kernel(double *Abase, long long sA, int lda, int jb, int nb, double *Dinv_base,
