@@ -8,19 +8,27 @@
 // linearly.  At this size one filter step is dense linear algebra, ~1.3 GFLOP of fp64, and the matrices
 // (P: 1.3 MB) do not fit on chip, so the step is a sequence of batched kernels over global-memory
 // matrices, all filters of a batch side by side:
-//   scale+Cholesky  U^T U = (n + lambda) P        blocked right-looking: panel kernel + GEMM update
-//   sigma points    X = x, x + U[k], x - U[k]; fx on the pose part
-//   mean, residuals xbar (circular mean for the heading), Y = residual_x(X, xbar)
-//   Pbar            = Y^T diag(Wc) Y + Q          batched GEMM
-//   redraw          Cholesky of (n + lambda) Pbar, X = sigma points of (xbar, Pbar)      (filterpy >= 1.4.5)
-//   hx              H[k] = (range, bearing) of every landmark of sigma point k; zhat; E = residual_h(H, zhat)
-//   S               = E^T diag(Wc) E + R,   Pzx = E^T diag(Wc) Y                          batched GEMM
-//   gain            through the Cholesky S = U^T U and ONE blocked forward solve W = U^-T [Pzx | r]:
+//   Cholesky        U^T U = (n + lambda) P        blocked left-looking, per 32-row block: aug_chol_diag_kernel (bracket of the
+//                                                 diagonal block on TMA + DMMA, factorisation, inverse) + a SOLVE GEMM (block row)
+//   sigma points    x, x + U[k], x - U[k] - never stored: every consumer recomputes them from (x, U)
+//   fx, mean, residuals   aug_sigma_resid_kernel: fx on the pose part, xbar (circular mean for the heading), Y = residual_x(., xbar)
+//   Pbar            = Y^T diag(Wc) Y + Q          GEMM (upper triangle); the epilogue adds Q and also stores (n + lambda) Pbar,
+//                                                 the matrix the re-draw factors
+//   redraw          Cholesky of (n + lambda) Pbar; Y = residuals of the new points about xbar (+ half only)   (filterpy >= 1.4.5)
+//   hx              H[k] = (range, bearing) of every landmark of sigma point k (aug_hx_kernel, from the factor)
+//   zhat, E, D      aug_meas_resid_kernel: zhat = z_mean(H), E = residual_h(H, zhat) in place, D = E+ - E-
+//   S               = E^T diag(Wc) E + R (upper, straight into the factor buffer);  Pzx = wi D^T Y+ (paired form; ukf_aug.pzx = 0:
+//                   the literal E^T diag(Wc) Y with the all-zero k-tiles skipped)
+//   gain            through the Cholesky S = U^T U and ONE blocked forward solve W = U^-T [Pzx | r] (SOLVE GEMMs with the
+//                   inverted diagonal blocks the factorisation left behind):
 //                   K S K^T = Pzx^T S^-1 Pzx = W^T W and K r = W^T (U^-T r), so neither K nor inv(S) is formed
 //                   (filterpy forms inv(S) and K explicitly; same x, P to rounding, 129 MFMA less per step)
-//   update          x = xbar + W^T v;  P = Pbar - W^T W (upper triangle, mirrored by the commit)   batched GEMM
+//   update          x = xbar + W^T v;  P = Pbar - W^T W, both triangles stored from the GEMM epilogue into the caller's P
 // One GEMM form serves all of them: C[i,j] = beta C[i,j] + alpha sum_k w_k A[k,i] B[k,j] with A and B
-// stored k-major ("TN"), which is how the sigma-point arrays and the factor rows lie in memory.
+// stored k-major ("TN"), which is how the sigma-point arrays and the factor rows lie in memory.  The default
+// kernel is aug_gemm_tma_kernel (TMA producer warp + DMMA consumer warps); aug_gemm_tn_kernel (DFMA) and
+// aug_gemm_dmma_kernel (cp.async) with the substitution kernels aug_chol_panel_kernel / aug_trsm_block_kernel are
+// the earlier formulations, kept selectable (ukf_aug.gemm = 1, 2) as measured baselines.  DESIGN.md 4.6 has the numbers.
 #pragma once
 #include "lslam_core.cuh"
 #include "async_copy.cuh"
