@@ -119,7 +119,7 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
         if (value != 0 && value != 64 && value != 128) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.solve_tile: 0 default (64), 64, 128");
         h->opt_aug_solve_tile = (int)value;
     } else if (!strcmp(key, "ukf_aug.tile")) {
-        if (value != 0 && value != 64 && value != 128) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.tile: 0 default (64), 64, 128");
+        if (value != 0 && value != 64 && value != 128) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.tile: 0 default (64 x 64, 8 warps), 64 (4 warps), 128 (128 x 128)");
         h->opt_aug_tile = (int)value;
     } else {
         return fail(h, LSLAM_ERR_BAD_ARG, "unknown option '%s'", key);
@@ -550,14 +550,16 @@ struct AugRun {
         g.ktri = h->opt_aug_gemm == 0 ? ktri : 0; g.mirror = mirror;
         noise = 0; C2 = nullptr; ktri = 0; mirror = 0;
         if (h->opt_aug_gemm == 0) {                               // DMMA fed by TMA (default)
-            // CTA tile: 64 x 64 with three CTAs per SM.  ukf_aug.tile = 128 selects 128 x 128 (16 consumer warps, one
+            // CTA tile: 64 x 64, EIGHT consumer warps (4 x 2, warp tile 16 x 32, 80 registers) by default: 33.0 against 33.9 ms per
+            // 1,024 filters for four warps of 32 x 32 (ukf_aug.tile = 64; 2 x 4 warps: 33.0, 4 x 4: 36.7, 5 ring stages: 33.2).  ukf_aug.tile = 128 selects 128 x 128 (16 consumer warps, one
             // CTA per SM, half the L2 -> shared traffic per flop): measured SLOWER on B200 (Pzx 2.96 vs 2.54 ms per
             // 256 filters) - L2 is at 10 % of its throughput with either tile, the DMMA pipe is what saturates.
             // Also measured and dropped: 64 x 128 with 8 consumer warps (52.4 against 42.4 ms per 1,024 filters) and
             // 64 x 64 at 4 CTAs per SM (3 stages, 96 registers: 43.7 ms).
             const int rc = M <= 32 ? gemm_tma<32, 64, 1, 4>(g, h->aug_attr_set[0])
                          : (M > 64 && h->opt_aug_tile == 128) ? gemm_tma<128, 128, 4, 4>(g, h->aug_attr_set[3])
-                                                            : gemm_tma<64, 64, 2, 2>(g, h->aug_attr_set[1]);
+                                                            : h->opt_aug_tile == 64 ? gemm_tma<64, 64, 2, 2>(g, h->aug_attr_set[1])
+                                                 : gemm_tma<64, 64, 4, 2>(g, h->aug_attr_set[6]);
             if (rc != LSLAM_OK) return rc;
         } else if (h->opt_aug_gemm == 2) {                        // DMMA fed by 8-byte cp.async
             if (M <= 32) {

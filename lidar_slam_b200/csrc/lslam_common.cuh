@@ -26,7 +26,7 @@ struct Handle {
     int opt_aug_tile = 0;              // ukf_aug.tile: CTA tile of the big GEMMs, 0 default (64), 128
     int opt_aug_pzx = 1;               // ukf_aug.pzx: 1 paired cross-covariance product (default), 0 literal
     int opt_aug_solve_tile = 0;        // ukf_aug.solve_tile: column tile of the SOLVE GEMMs, 0 default (64), 128
-    bool aug_attr_set[7] = {false, false, false, false, false, false, false};
+    bool aug_attr_set[10] = {};
     double *express_tab_d = nullptr;   // sin/cos tables of the packet decoder (csrc/express.cuh)
     unsigned long long *counters_d = nullptr;
     char err[512] = "";
