@@ -116,7 +116,7 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
         if (value < 0 || value > 1) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.pzx: 1 default (paired + / - points), 0 literal sum over all sigma points");
         h->opt_aug_pzx = (int)value;
     } else if (!strcmp(key, "ukf_aug.solve_tile")) {
-        if (value != 0 && value != 64 && value != 128) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.solve_tile: 0 default (64), 64, 128");
+        if (value != 0 && value != 64 && value != 128) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.solve_tile: 0 default (32 x 64, 8 warps), 64 (4 warps), 128 (32 x 128)");
         h->opt_aug_solve_tile = (int)value;
     } else if (!strcmp(key, "ukf_aug.tile")) {
         if (value != 0 && value != 64 && value != 128) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.tile: 0 default (64 x 64, 8 warps), 64 (4 warps), 128 (128 x 128)");
@@ -550,16 +550,18 @@ struct AugRun {
         g.ktri = h->opt_aug_gemm == 0 ? ktri : 0; g.mirror = mirror;
         noise = 0; C2 = nullptr; ktri = 0; mirror = 0;
         if (h->opt_aug_gemm == 0) {                               // DMMA fed by TMA (default)
-            // CTA tile: 64 x 64, EIGHT consumer warps (4 x 2, warp tile 16 x 32, 80 registers) by default: 33.0 against 33.9 ms per
-            // 1,024 filters for four warps of 32 x 32 (ukf_aug.tile = 64; 2 x 4 warps: 33.0, 4 x 4: 36.7, 5 ring stages: 33.2).  ukf_aug.tile = 128 selects 128 x 128 (16 consumer warps, one
+            // CTA tile: 64 x 64, EIGHT consumer warps (4 x 2, warp tile 16 x 32) and THREE CTAs per SM (launch bounds cap the
+            // registers at 72) by default: 24 DMMA warps per SM.  Per 1,024 filters: four warps of 32 x 32 at 3 CTAs/SM (ukf_aug.tile = 64)
+            // 33.9 ms, eight warps at 2 CTAs/SM (96 registers) 33.0 ms, at 3 CTAs/SM 31.6 ms, at 4 CTAs/SM (3 stages, spills) 36.0 ms
+            // (2 x 4 warps: as 4 x 2; 4 x 4 warps: +3.7 ms; 5 ring stages: +0.2 ms) - each with the 4-warp SOLVE kernel.  ukf_aug.tile = 128 selects 128 x 128 (16 consumer warps, one
             // CTA per SM, half the L2 -> shared traffic per flop): measured SLOWER on B200 (Pzx 2.96 vs 2.54 ms per
             // 256 filters) - L2 is at 10 % of its throughput with either tile, the DMMA pipe is what saturates.
             // Also measured and dropped: 64 x 128 with 8 consumer warps (52.4 against 42.4 ms per 1,024 filters) and
             // 64 x 64 at 4 CTAs per SM (3 stages, 96 registers: 43.7 ms).
             const int rc = M <= 32 ? gemm_tma<32, 64, 1, 4>(g, h->aug_attr_set[0])
                          : (M > 64 && h->opt_aug_tile == 128) ? gemm_tma<128, 128, 4, 4>(g, h->aug_attr_set[3])
-                                                            : h->opt_aug_tile == 64 ? gemm_tma<64, 64, 2, 2>(g, h->aug_attr_set[1])
-                                                 : gemm_tma<64, 64, 4, 2>(g, h->aug_attr_set[6]);
+                         : h->opt_aug_tile == 64 ? gemm_tma<64, 64, 2, 2>(g, h->aug_attr_set[1])
+                                                 : gemm_tma<64, 64, 4, 2, 4, false, 3>(g, h->aug_attr_set[6]);
             if (rc != LSLAM_OK) return rc;
         } else if (h->opt_aug_gemm == 2) {                        // DMMA fed by 8-byte cp.async
             if (M <= 32) {
@@ -597,7 +599,10 @@ struct AugRun {
         g.Dinv = Dinv + (size_t)blk * 1024; g.sDinv = sDinv; g.ktri = 0; g.mirror = 0;
         // 32 x 64 tiles (warp tile 32 x 16, 3 CTAs per SM); ukf_aug.solve_tile = 128 selects 32 x 128 (warp tile 32 x 32,
         // 2 CTAs per SM): measured slower on B200 (45.1 against 42.4 ms per 1,024 filters at L = 200)
-        const int rc = h->opt_aug_solve_tile != 128 ? gemm_tma<32, 64, 1, 4, 3, true>(g, h->aug_attr_set[2])
+        // default: EIGHT consumer warps per 32 x 64 tile (warp tile 32 x 8): 32.2 against 33.0 ms per 1,024 filters for four
+        // warps of 32 x 16 (ukf_aug.solve_tile = 64)
+        const int rc = h->opt_aug_solve_tile == 0 ? gemm_tma<32, 64, 1, 8, 3, true>(g, h->aug_attr_set[7])
+                     : h->opt_aug_solve_tile != 128 ? gemm_tma<32, 64, 1, 4, 3, true>(g, h->aug_attr_set[2])
                                                     : gemm_tma<32, 128, 1, 4, 3, true>(g, h->aug_attr_set[5]);
         if (rc == LSLAM_OK) h->launches++;
         return rc;
