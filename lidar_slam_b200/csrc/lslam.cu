@@ -119,7 +119,7 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
         if (value != 0 && value != 64 && value != 128) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.solve_tile: 0 default (32 x 64, 8 warps), 64 (4 warps), 128 (32 x 128)");
         h->opt_aug_solve_tile = (int)value;
     } else if (!strcmp(key, "ukf_aug.tile")) {
-        if (value != 0 && value != 64 && value != 128) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.tile: 0 default (64 x 64, 8 warps), 64 (4 warps), 128 (128 x 128)");
+        if (value != 0 && value != 64 && value != 128) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.tile: 0 default (32 x 64), 64 (64 x 64), 128 (128 x 128)");
         h->opt_aug_tile = (int)value;
     } else {
         return fail(h, LSLAM_ERR_BAD_ARG, "unknown option '%s'", key);
@@ -558,10 +558,13 @@ struct AugRun {
             // 256 filters) - L2 is at 10 % of its throughput with either tile, the DMMA pipe is what saturates.
             // Also measured and dropped: 64 x 128 with 8 consumer warps (52.4 against 42.4 ms per 1,024 filters) and
             // 64 x 64 at 4 CTAs per SM (3 stages, 96 registers: 43.7 ms).
+            // Final shape of the big products: 32 x 64 tiles, eight consumer warps of 32 x 8, FOUR CTAs per SM (53 KB, 55
+            // registers) = 32 DMMA warps per SM: 29.6 ms per 1,024 filters (64 x 64 with 8 warps at 3 CTAs/SM, ukf_aug.tile = 64:
+            // 30.8 ms; 32 x 64 at 5 CTAs/SM with 3 stages and 40 registers: 31.3 ms; 2 x 4 warps of 16 x 16: 30.9 ms).
             const int rc = M <= 32 ? gemm_tma<32, 64, 1, 4>(g, h->aug_attr_set[0])
                          : (M > 64 && h->opt_aug_tile == 128) ? gemm_tma<128, 128, 4, 4>(g, h->aug_attr_set[3])
-                         : h->opt_aug_tile == 64 ? gemm_tma<64, 64, 2, 2>(g, h->aug_attr_set[1])
-                                                 : gemm_tma<64, 64, 4, 2, 4, false, 3>(g, h->aug_attr_set[6]);
+                         : h->opt_aug_tile == 64 ? gemm_tma<64, 64, 4, 2, 4, false, 3>(g, h->aug_attr_set[6])
+                                                 : gemm_tma<32, 64, 1, 8, 4, false, 4>(g, h->aug_attr_set[8]);
             if (rc != LSLAM_OK) return rc;
         } else if (h->opt_aug_gemm == 2) {                        // DMMA fed by 8-byte cp.async
             if (M <= 32) {
@@ -601,7 +604,7 @@ struct AugRun {
         // 2 CTAs per SM): measured slower on B200 (45.1 against 42.4 ms per 1,024 filters at L = 200)
         // default: EIGHT consumer warps per 32 x 64 tile (warp tile 32 x 8): 32.2 against 33.0 ms per 1,024 filters for four
         // warps of 32 x 16 (ukf_aug.solve_tile = 64)
-        const int rc = h->opt_aug_solve_tile == 0 ? gemm_tma<32, 64, 1, 8, 3, true>(g, h->aug_attr_set[7])
+        const int rc = h->opt_aug_solve_tile == 0 ? gemm_tma<32, 64, 1, 8, 3, true, 4>(g, h->aug_attr_set[7])
                      : h->opt_aug_solve_tile != 128 ? gemm_tma<32, 64, 1, 4, 3, true>(g, h->aug_attr_set[2])
                                                     : gemm_tma<32, 128, 1, 4, 3, true>(g, h->aug_attr_set[5]);
         if (rc == LSLAM_OK) h->launches++;

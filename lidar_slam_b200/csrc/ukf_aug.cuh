@@ -346,7 +346,7 @@ __global__ void __launch_bounds__(32 * WARPS_M * WARPS_N) aug_gemm_dmma_kernel(c
 template <int TM, int TN, int WARPS_N, int S, bool SOLVE> constexpr size_t aug_tma_smem()
 {
     return (size_t)S * kAugBK * (TM + 4 + TN + 4) * sizeof(double) + (2 * S + 2) * sizeof(Mbar) + 128 +
-           (SOLVE ? (size_t)(32 * 36 + 32 * (TN + 4 * WARPS_N)) * sizeof(double) : 0);
+           (SOLVE ? (size_t)(32 * 36) * sizeof(double) : 0);          // Dinv; the V tiles reuse the operand ring
 }
 
 template <int TM, int TN, int WARPS_M, int WARPS_N, int S, bool SOLVE, int MINB = 1>
@@ -372,8 +372,9 @@ aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const 
     double *sm = reinterpret_cast<double *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
 #endif
     Mbar *full = reinterpret_cast<Mbar *>(sm + (size_t)S * STAGE), *empty = full + S;
-    Mbar *dbar = empty + S;                                           // SOLVE: Dinv has landed
-    double *Ds = reinterpret_cast<double *>(empty + S + 2);           // SOLVE: Dinv [32][36], then V tiles [NW][32][WN + 4]
+    Mbar *dbar = empty + S, *cbar = empty + S + 1;                    // SOLVE: Dinv has landed; every consumer warp is out of the k-loop
+    double *Ds = reinterpret_cast<double *>(empty + S + 2);           // SOLVE: Dinv [32][36]
+    static_assert(!SOLVE || (size_t)S * STAGE >= (size_t)NW * 32 * (WN + 4), "SOLVE: the V tiles must fit in the operand ring");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     // fragment liveness per consumer warp (see aug_gemm_dmma_kernel); a warp without a live fragment leaves
     auto live_mask = [&](int w) {
@@ -391,6 +392,7 @@ aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const 
         for (int w = 0; w < NW; ++w) nlive += live_mask(w) != 0;
         for (int s = 0; s < S; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], nlive > 0 ? nlive : 1); }
         mbar_init(dbar, 1);
+        mbar_init(cbar, nlive > 0 ? nlive : 1);
         mbar_fence_init();
     }
     __syncthreads();
@@ -484,8 +486,13 @@ aug_gemm_tma_kernel(const AugGemm g, const LSLAM_GRID_CONSTANT Tmap mapA, const 
     const double *A = g.A + (size_t)f * g.sA, *B = g.B + (size_t)f * g.sB;
     double *C = g.C + (size_t)f * g.sC, *C2 = g.C2 ? g.C2 + (size_t)f * g.sC2 : nullptr;
     if (SOLVE) {
+        // the V tiles go where the operand ring was (4 CTAs per SM instead of 3): wait until every live consumer warp
+        // has left the k-loop - the producer issued its last copy long before, nothing writes the ring any more
         constexpr int LDV = WN + 4;
-        double *Vs = Ds + 32 * 36 + (size_t)warp * 32 * LDV;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(cbar);
+        mbar_wait(cbar, 0);
+        double *Vs = sm + (size_t)warp * 32 * LDV;
 #pragma unroll
         for (int a = 0; a < FM; ++a) {
             const int i = 8 * a + fcol;
