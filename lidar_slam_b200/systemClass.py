@@ -69,7 +69,7 @@ class DeviceUKF:
     def _set(self, key, value, shape):
         t = self._torch
         v = np.broadcast_to(np.asarray(value, dtype=np.float64), (self.F,) + shape)
-        self.state[key] = t.from_numpy(np.ascontiguousarray(v)).to(self.eng.device)
+        self.state[key] = t.from_numpy(np.array(v, order="C")).to(self.eng.device)
         self._have_sig = False
 
     x = property(lambda self: self._get("x"), lambda self, v: self._set("x", v, (3,)))
