@@ -221,6 +221,22 @@ int lslam_ukf_aug_step(void *handle, double *x, double *P, const double *u, cons
                        int32_t L, const double *params_h, int32_t flags, int32_t *status, void *workspace,
                        int64_t workspace_bytes, void *stream);
 
+/* The same step with NO allocation anywhere: the scratch is a file-scope static device array of
+ * LSLAM_STATIC_SCRATCH_BYTES inside the library (every GPU that loads liblslam.so holds it until the
+ * process exits).  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Arguments and results are those of lslam_ukf_aug_step, bit for bit; the caller
+ * still passes every input and output.  All F filters must fit the array in ONE batch:
+ * lslam_ukf_aug_workspace_bytes(L, F) <= LSLAM_STATIC_SCRATCH_BYTES (e.g. 2 filters at L = 200,
+ * 545 at L = 12), otherwise LSLAM_ERR_CAPACITY.  Calls no cudaMalloc / cudaFree / allocating
+ * routine.  Every call on a device shares the one array, which keeps the last call's contents
+ * (nothing in it has to start at zero: each array is written before it is read); two calls that
+ * overlap on the GPU - different streams, or different handles / threads on one device - RACE on
+ * it: serialise them on one stream. */
+#define LSLAM_STATIC_SCRATCH_BYTES (32u << 20)
+int lslam_ukf_aug_step_static(void *handle, double *x, double *P, const double *u, const double *z, int32_t F,
+                              int32_t L, const double *params_h, int32_t flags, int32_t *status, void *stream);
+
 /* ---- OLS-flavour RANSAC ------------------------------------------------------------
  * Replaces sklearn.linear_model.RANSACRegressor(residual_threshold=3).fit(x[i:k], y[i:k]) +
  * inlier_mask_ / estimator_.coef_ / predict of /root/reference/line_detection.py:51-73 for every

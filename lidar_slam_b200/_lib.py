@@ -51,6 +51,7 @@ SIGNATURES = {
     "lslam_ukf_aug_workspace_bytes": (ctypes.c_int, [_i32, _i32, ctypes.POINTER(_i64)]),
     "lslam_ukf_aug_step": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, ctypes.POINTER(_f64), _i32, _vp, _vp,
                                           _i64, _vp]),
+    "lslam_ukf_aug_step_static": (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, ctypes.POINTER(_f64), _i32, _vp, _vp]),
     "lslam_ransac_ols": (ctypes.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _f64, _f64, _u64, _u64,
                                         _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "lslam_express_to_cart": (ctypes.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _vp, _vp, _vp]),
@@ -198,6 +199,11 @@ class Handle:
     def ukf_aug_step(self, x, P, u, z, F, L, params, flags, status, workspace, workspace_bytes, stream=0):
         self._check(self.cdll.lslam_ukf_aug_step(self._h, x, P, u, z, F, L, self._params(params), flags, status,
                                                  workspace, int(workspace_bytes), stream))
+
+    def ukf_aug_step_static(self, x, P, u, z, F, L, params, flags, status, stream=0):
+        """lslam_ukf_aug_step with the scratch in the library's static device array (no allocation)."""
+        self._check(self.cdll.lslam_ukf_aug_step_static(self._h, x, P, u, z, F, L, self._params(params), flags, status,
+                                                        stream))
 
     def synth_scans(self, xy, B, beams, seed, scan_base, noise_mm, dropout, stream=0):
         self._check(self.cdll.lslam_synth_scans(self._h, xy, B, beams, int(seed) & (2**64 - 1),

@@ -814,6 +814,60 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
     return LSLAM_OK;
 }
 
+// ---- augmented-state UKF without any allocation: scratch in a static device array ---------------
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it): the same
+// step as lslam_ukf_aug_step with its workspace in the file-scope array below (LSLAM_STATIC_SCRATCH_BYTES, held by every
+// GPU that loads the library until the process exits).  In host code the array's NAME is a host-side stand-in, not a device
+// address: the address the kernels get comes from cudaGetSymbolAddress, looked up once per device with that device current.
+static __device__ __align__(256) unsigned char g_static_scratch[LSLAM_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kStaticScratchMaxDevices = 64;
+void *g_static_scratch_addr[kStaticScratchMaxDevices] = {};     // device address of g_static_scratch on device d, or null
+
+// device address of g_static_scratch on the handle's device (which must be current); no allocation
+int static_scratch_address(Handle *h, void **out)
+{
+    if (h->device < 0 || h->device >= kStaticScratchMaxDevices)
+        return fail(h, LSLAM_ERR_CAPACITY, "static scratch: device ordinal %d beyond %d", h->device, kStaticScratchMaxDevices);
+    void *p = __atomic_load_n(&g_static_scratch_addr[h->device], __ATOMIC_ACQUIRE);
+    if (p == nullptr) {
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || p == nullptr)
+            return fail(h, LSLAM_ERR_CUDA, "cudaGetSymbolAddress(g_static_scratch) on device %d: %s", h->device,
+                        e != cudaSuccess ? cudaGetErrorString(e) : "null address");
+        __atomic_store_n(&g_static_scratch_addr[h->device], p, __ATOMIC_RELEASE);   // every thread computes the same value
+    }
+    *out = p;
+    return LSLAM_OK;
+}
+} // namespace
+
+extern "C" int lslam_ukf_aug_step_static(void *handle, double *x, double *P, const double *u, const double *z, int32_t F,
+                                         int32_t L, const double *params_h, int32_t flags, int32_t *status, void *stream)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr) return LSLAM_ERR_BAD_ARG;
+    if (F < 0 || L < 1 || L > 1024)
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ukf_aug_step_static: need F >= 0, 1 <= L <= 1024");
+    if (F == 0) return LSLAM_OK;
+    int64_t need = 0;
+    if (lslam_ukf_aug_workspace_bytes(L, F, &need) != LSLAM_OK || need > (int64_t)LSLAM_STATIC_SCRATCH_BYTES)
+        return fail(h, LSLAM_ERR_CAPACITY,
+                    "lslam_ukf_aug_step_static: %d filters of L = %d need %lld bytes of scratch, the static array holds %lld "
+                    "(LSLAM_STATIC_SCRATCH_BYTES); use lslam_ukf_aug_step with a caller-owned workspace",
+                    (int)F, (int)L, (long long)need, (long long)LSLAM_STATIC_SCRATCH_BYTES);
+    void *scratch = nullptr;
+    {
+        DeviceGuard g(h->device);
+        const int rc = static_scratch_address(h, &scratch);
+        if (rc != LSLAM_OK) return rc;
+    }
+    // nothing in the workspace has to start at zero: every array is written before it is read (the NaN-filled-workspace
+    // tests of lslam_ukf_aug_step), so the previous call's contents are simply overwritten
+    return lslam_ukf_aug_step(handle, x, P, u, z, F, L, params_h, flags, status, scratch, (int64_t)LSLAM_STATIC_SCRATCH_BYTES, stream);
+}
+
 // ---- input stage, synthetic scans, fp64 probe --------------------------------------------
 extern "C" int lslam_polar_to_cart(void *handle, const double *dist, const double *ang_deg, double *xy,
                                    int64_t npts, void *stream)

@@ -34,7 +34,7 @@
 #define __forceinline__ inline
 #define __launch_bounds__(...)
 #define __restrict__
-#define __align__(n) alignas(n)
+#define __align__(n) __attribute__((aligned(n)))
 
 struct dim3 {
     unsigned x, y, z;
@@ -252,6 +252,8 @@ static inline cudaError_t cudaDeviceGetAttribute(int *v, cudaDeviceAttr a, int) 
 template <class K> static inline cudaError_t cudaFuncSetAttribute(K, cudaFuncAttribute, int) { return cudaSuccess; }
 static inline cudaError_t cudaMalloc(void **p, size_t n) { *p = std::calloc(1, n ? n : 1); return *p ? cudaSuccess : 2; }
 static inline cudaError_t cudaFree(void *p) { std::free(p); return cudaSuccess; }
+// in the emulation a __device__ array IS host memory, so its name is its address
+template <class T> static inline cudaError_t cudaGetSymbolAddress(void **p, T &sym) { *p = (void *)&sym; return cudaSuccess; }
 static inline cudaError_t cudaMemset(void *p, int v, size_t n) { std::memset(p, v, n); return cudaSuccess; }
 static inline cudaError_t cudaMemsetAsync(void *p, int v, size_t n, cudaStream_t = nullptr) { std::memset(p, v, n); return cudaSuccess; }
 static inline cudaError_t cudaMemcpyAsync(void *d, const void *s, size_t n, cudaMemcpyKind, cudaStream_t = nullptr) { std::memcpy(d, s, n); return cudaSuccess; }
