@@ -42,11 +42,13 @@ int lslam_create(int device, void **handle);
 int lslam_destroy(void *handle);
 const char *lslam_last_error(void *handle);
 /* ABI version of the loaded library (LSLAM_ABI_VERSION at build time). */
-#define LSLAM_ABI_VERSION 5
+#define LSLAM_ABI_VERSION 6
 int lslam_abi_version(void);
 /* Launch-shape tuning knobs; 0 restores the built-in heuristic.  Results never depend on them.
- *   "ransac.kernel"  0 default, 1 phase-structured kernel, 2 warp-specialised persistent kernel
- *   "ransac.tpt"     trials per work item (1, 2, 4);  "ransac.slots_per_cta"  chunk slots per tile
+ *   "ransac.kernel"  0 default, 1 phase-structured kernel, 2 warp-specialised persistent kernel, 3 tile kernel
+ *   "ransac.screen"  tile kernel: 0 / 2 distance screened in fp32 on centred points, 1 in fp64
+ *   "ransac.prefetch" tile kernel: tiles a CTA prefetches ahead towards L2 (0 off, 1 one wave of CTAs)
+ *   "ransac.tpt"     trials per work item (1, 2, 4, 6, 8);  "ransac.slots_per_cta"  chunk slots per tile
  *   "ransac.scorers", "ransac.posts", "ransac.ring"   warp counts / ring depth of kernel 2
  *   "ransac.threads" CTA size of kernel 1 */
 int lslam_set_option(void *handle, const char *key, int64_t value);
@@ -76,6 +78,12 @@ int lslam_polar_to_cart(void *handle, const double *dist, const double *ang_deg,
  *             of chunk c of scan b samples the pair derived from counter
  *             (t>>1, c, scan_base+b) - see oracle/philox.py; results do not depend on
  *             how a job is split into batches or over GPUs
+ *   pairs     NULL = that sampler, or [B,C,trials,2] explicit sample index pairs (8-byte aligned): trial t of
+ *             chunk slot (b,c) uses points pairs[b,c,t,0..1] of the chunk - what upstream's
+ *             random_state.choice(n, 2, replace=False) drew, so a seeded skimage.measure.ransac run
+ *             (ransac_functions.py:23-24 with random_state=s) can be replayed pair for pair; indices are
+ *             clamped into the chunk; a chunk upstream left early (sum of squares <= 0) is padded with
+ *             repeats of any pair already tried (a repeat never displaces its first occurrence)
  * outputs (per chunk slot, [B,C,...])
  *   line      [B,C,8]  a, b, origin_x, origin_y, dir_x, dir_y, tip_x, tip_y
  *                      (dir normalised to dir_x > 0; a = dir_y/dir_x unguarded like :26)
@@ -90,7 +98,7 @@ int lslam_polar_to_cart(void *handle, const double *dist, const double *ang_deg,
  */
 int lslam_ransac_lines(void *handle, const double *xy, const int32_t *npts, int32_t B, int32_t N,
                        int32_t chunk, int32_t trials, double thr, uint64_t seed,
-                       uint64_t scan_base, double *line, int32_t *ninl, int32_t *win_trial,
+                       uint64_t scan_base, const int32_t *pairs, double *line, int32_t *ninl, int32_t *win_trial,
                        int32_t *win_pair, double *ssum, uint32_t *inl_mask, void *stream);
 
 /* Diagnostics of the last lslam_ransac_lines calls on this handle (synchronises `stream`):

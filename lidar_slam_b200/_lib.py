@@ -18,7 +18,7 @@ LSLAM_ERR_NO_MODEL = -3
 LSLAM_ERR_CUDA = -4
 LSLAM_ERR_NONFINITE = -5
 LSLAM_ERR_CAPACITY = -6
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 _vp = ctypes.c_void_p
 _i32 = ctypes.c_int32
@@ -35,7 +35,7 @@ SIGNATURES = {
     "lslam_set_option": (ctypes.c_int, [_vp, ctypes.c_char_p, _i64]),
     "lslam_launch_count": (_i64, [_vp]),
     "lslam_polar_to_cart": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i64, _vp]),
-    "lslam_ransac_lines": (ctypes.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _f64, _u64, _u64,
+    "lslam_ransac_lines": (ctypes.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _f64, _u64, _u64, _vp,
                                           _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "lslam_ransac_counters": (ctypes.c_int, [_vp, ctypes.POINTER(_i64), _vp]),
     "lslam_associate": (ctypes.c_int, [_vp, _vp, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp,
@@ -140,10 +140,10 @@ class Handle:
                                                   float(noise_mm), float(dropout), stream))
 
     def ransac_lines(self, xy, npts, B, N, chunk, trials, thr, seed, scan_base,
-                     line, ninl, win_trial, win_pair, ssum, inl_mask, stream=0):
+                     line, ninl, win_trial, win_pair, ssum, inl_mask, stream=0, pairs=None):
         self._check(self.cdll.lslam_ransac_lines(
             self._h, xy, npts, B, N, chunk, trials, float(thr), int(seed) & (2**64 - 1),
-            int(scan_base) & (2**64 - 1), line, ninl, win_trial, win_pair, ssum, inl_mask, stream))
+            int(scan_base) & (2**64 - 1), pairs, line, ninl, win_trial, win_pair, ssum, inl_mask, stream))
 
     def ransac_counters(self, stream=0):
         out = (_i64 * 3)()

@@ -107,11 +107,12 @@ class Engine:
         return out
 
     def ransac_lines(self, xy, npts=None, chunk=CHUNK, trials=MAX_TRIALS, thr=THRESHOLD,
-                     seed=0, scan_base=0, out=None):
+                     seed=0, scan_base=0, out=None, pairs=None):
         """Batched landmark extraction (ransac_functions.py:20-31 per chunk).
 
-        xy [B, N, 2] float64 on this device; npts [B] int32 or None.  Returns the dict of
-        lslam_ransac_lines outputs (include/lslam.h); ``inl_mask`` words are int32 bit
+        xy [B, N, 2] float64 on this device; npts [B] int32 or None; pairs None (Philox sampler) or
+        [B, C, trials, 2] int32 explicit sample pairs (what upstream's RandomState drew).  Returns the
+        dict of lslam_ransac_lines outputs (include/lslam.h); ``inl_mask`` words are int32 bit
         patterns.  Asynchronous on the current stream.
         """
         xy = self._check(xy, torch.float64, "xy")
@@ -124,11 +125,16 @@ class Engine:
                 raise ValueError("npts must have B elements")
         if out is None:
             out = self.alloc_ransac_out(B, N, chunk)
+        if pairs is not None:
+            pairs = self._check(pairs, torch.int32, "pairs")
+            if tuple(pairs.shape) != (B, (N + chunk - 1) // chunk, int(trials), 2):
+                raise ValueError("pairs must be [B, C, trials, 2]")
         self.handle.ransac_lines(
             xy.data_ptr(), npts.data_ptr() if npts is not None else None, B, N, int(chunk),
             int(trials), float(thr), seed, scan_base, out["line"].data_ptr(), out["ninl"].data_ptr(),
             out["win_trial"].data_ptr(), out["win_pair"].data_ptr(),
-            out["ssum"].data_ptr() if "ssum" in out else None, out["inl_mask"].data_ptr(), self._stream())
+            out["ssum"].data_ptr() if "ssum" in out else None, out["inl_mask"].data_ptr(), self._stream(),
+            pairs=pairs.data_ptr() if pairs is not None else None)
         return out
 
     def ransac_ols(self, xy, npts=None, window=50, trials=100, thr=3.0, stop_probability=0.99, seed=0,

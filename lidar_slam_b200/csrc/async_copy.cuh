@@ -76,6 +76,13 @@ __device__ __forceinline__ void tma_load_3d(void *dst, const Tmap *map, int c0, 
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
                  ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar)) : "memory");
 }
+// ---- per-thread asynchronous 16-byte copies global -> shared (cp.async, SASS LDGSTS): no register staging, so a
+// thread can have any number of them in flight; cp_async_wait_all() blocks until this thread's copies have landed.
+__device__ __forceinline__ void cp_async16(void *dst, const void *src)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 #define LSLAM_GRID_CONSTANT __grid_constant__
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
@@ -141,6 +148,8 @@ inline void tma_load_3d(void *dst, const Tmap *m, int c0, int c1, int c2, Mbar *
     bar->tx.fetch_sub((int64_t)sizeof(double) * m->box[0] * m->box[1] * m->box[2]);
     mbar_emu_check(bar);
 }
+inline void cp_async16(void *dst, const void *src) { std::memcpy(dst, src, 16); }
+inline void cp_async_wait_all() {}
 #define LSLAM_GRID_CONSTANT
 inline void prefetch_l2(const void *) {}
 

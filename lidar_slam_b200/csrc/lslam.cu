@@ -5,6 +5,7 @@
 #include "lslam_common.cuh"
 #include "ransac.cuh"
 #include "ransac_ws.cuh"
+#include "ransac_tile.cuh"
 #include "aux_kernels.cuh"
 #include "assoc.cuh"
 #include "ukf.cuh"
@@ -34,6 +35,7 @@ extern "C" int lslam_create(int device, void **handle)
     DeviceGuard g(device);
     cudaError_t e = cudaDeviceGetAttribute(&h->sms, cudaDevAttrMultiProcessorCount, device);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, device);
     if (e == cudaSuccess) e = cudaMalloc((void **)&h->counters_d, 8 * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMemset(h->counters_d, 0, 8 * sizeof(unsigned long long));
     if (e == cudaSuccess) {
@@ -89,7 +91,7 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
     Handle *h = (Handle *)handle;
     if (h == nullptr || key == nullptr) return LSLAM_ERR_BAD_ARG;
     if (!strcmp(key, "ransac.tpt")) {
-        if (value != 0 && value != 1 && value != 2 && value != 4) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.tpt must be 0, 1, 2 or 4");
+        if (value != 0 && value != 1 && value != 2 && value != 4 && value != 6 && value != 8) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.tpt must be 0, 1, 2, 4, 6 or 8");
         h->opt_tpt = (int)value;
     } else if (!strcmp(key, "ransac.slots_per_cta")) {
         if (value < 0 || value > 4096) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.slots_per_cta out of range");
@@ -98,14 +100,17 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
         if (value < 0 || value > 1024 || value % 32) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.threads must be a multiple of 32 <= 1024");
         h->opt_threads = (int)value;
     } else if (!strcmp(key, "ransac.screen")) {
-        if (value < 0 || value > 2) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.screen: 0 default, 1 fp64, 2 fp32");
+        if (value < 0 || value > 2) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.screen (tile kernel): 0 default (fp32), 1 fp64 high words, 2 fp32");
         h->opt_screen = (int)value;
     } else if (!strcmp(key, "ransac.kernel")) {
-        if (value < 0 || value > 2) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.kernel: 0 default, 1 phase-structured, 2 warp-specialised");
+        if (value < 0 || value > 3) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.kernel: 0 default, 1 phase-structured, 2 warp-specialised, 3 tile");
         h->opt_kernel = (int)value;
     } else if (!strcmp(key, "ransac.scorers") || !strcmp(key, "ransac.posts")) {
         if (value < 0 || value > 29) return fail(h, LSLAM_ERR_BAD_ARG, "%s out of range (0..29)", key);
         (key[7] == 's' ? h->opt_scorers : h->opt_posts) = (int)value;
+    } else if (!strcmp(key, "ransac.prefetch")) {
+        if (value < -1 || value > (1 << 20)) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.prefetch: 0 off (default), 1 one wave of CTAs ahead, n tiles ahead");
+        h->opt_prefetch = (int)value;
     } else if (!strcmp(key, "ransac.ring")) {
         if (value < 0 || value == 1 || value > 16) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.ring must be 0 or 2..16");
         h->opt_ring = (int)value;
@@ -128,10 +133,10 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
 }
 
 // ---- RANSAC ------------------------------------------------------------------------------
-template <int TPT, int MAXT, int MINB, bool F32>
+template <int TPT, int MAXT, int MINB>
 static int launch_ransac(Handle *h, RansacArgs a, int threads_target, cudaStream_t st)
 {
-    auto kern = ransac_lines_kernel<TPT, MAXT, MINB, F32>;
+    auto kern = ransac_lines_kernel<TPT, MAXT, MINB>;
     a.ipc = (a.trials + TPT - 1) / TPT;
     if (threads_target > MAXT) threads_target = MAXT;
     // chunk slots per CTA: enough work items to fill the CTA, bounded by shared memory
@@ -150,7 +155,7 @@ static int launch_ransac(Handle *h, RansacArgs a, int threads_target, cudaStream
         threads = (threads + 31) & ~31;
         if (threads > MAXT) threads = MAXT & ~31;
         if (threads < 4 * G) threads = ((4 * G + 31) & ~31) > MAXT ? (MAXT & ~31) : ((4 * G + 31) & ~31);
-        smem = ransac_smem_bytes(G, a.chunk, a.trials, a.W, threads / 32, F32);
+        smem = ransac_smem_bytes(G, a.chunk, a.trials, a.W, threads / 32);
         if (smem <= (size_t)h->smem_optin || G == 1) break;
     }
     if (smem > (size_t)h->smem_optin)
@@ -164,6 +169,69 @@ static int launch_ransac(Handle *h, RansacArgs a, int threads_target, cudaStream
     h->launches++;
     LSLAM_CUDA_TRY(h, cudaGetLastError());
     return LSLAM_OK;
+}
+
+// tile kernel (ransac_tile.cuh): one work item per thread, G = threads / ipc chunk slots per CTA.
+// Returns LSLAM_ERR_CAPACITY (without touching the handle's error text) when the shape does not fit it.
+template <int TPT, int MAXT, int MINB, bool F32>
+static int launch_ransac_tile(Handle *h, RansacArgs a, int threads, cudaStream_t st, bool probe_only = false)
+{
+    auto kern = ransac_tile_kernel<TPT, MAXT, MINB, F32>;
+    a.ipc = (a.trials + TPT - 1) / TPT;
+    if (threads > MAXT) threads = MAXT;
+    threads &= ~31;
+    if (threads < 32 || a.ipc > threads) return LSLAM_ERR_CAPACITY;
+    int G = threads / a.ipc;
+    if (h->opt_slots && h->opt_slots < G) G = h->opt_slots;
+    if ((long long)G > a.nslots) G = (int)a.nslots;
+    size_t smem = 0;
+    for (;; --G) {
+        smem = tile_smem_bytes(G, a.chunk, a.ipc, TPT, a.W, threads / 32, F32);
+        if (smem <= (size_t)h->smem_optin || G == 1) break;
+    }
+    if (smem > (size_t)h->smem_optin) return LSLAM_ERR_CAPACITY;
+    if (probe_only) return LSLAM_OK;
+    // no more threads than the work items of G slots need (rounded up to warps, at least the lanes of the refit groups)
+    int need = G * a.ipc > G * kTileLG ? G * a.ipc : G * kTileLG;
+    need = (need + 31) & ~31;
+    if (need < threads) threads = need;
+    a.G = G;
+    a.inv_thr = 1.0 / a.thr;
+    // CTAs resident at a time (registers: MINB per SM by the launch bounds; shared memory) = how far ahead a CTA prefetches
+    int per_sm = (int)((size_t)h->smem_sm / (smem + 1024));
+    if (per_sm > MINB * MAXT / threads) per_sm = MINB * MAXT / threads;
+    if (per_sm < 1) per_sm = 1;
+    // measured on B200 (C2): no gain from the prefetch (4.66 against 4.55 ms at 256 threads) - off unless asked for;
+    // ransac.prefetch = 1 asks for one wave of CTAs ahead
+    a.prefetch_ahead = h->opt_prefetch <= 0 ? 0 : (h->opt_prefetch == 1 ? per_sm * h->sms : h->opt_prefetch);
+    const long long grid = (a.nslots + G - 1) / G;
+    if (grid > 0x7fffffffLL) return fail(h, LSLAM_ERR_CAPACITY, "batch too large for one launch");
+    LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    LSLAM_LAUNCH(kern, (unsigned)grid, (unsigned)threads, smem, st, a);
+    h->launches++;
+    LSLAM_CUDA_TRY(h, cudaGetLastError());
+    return LSLAM_OK;
+}
+
+static int dispatch_ransac_tile(Handle *h, const RansacArgs &a, int tpt, int threads, cudaStream_t st, bool probe_only = false)
+{
+    // screening precision of the hot loop: fp32 on centred points by default, ransac.screen = 1 keeps fp64 (high words)
+    if (h->opt_screen == 1) {
+        switch (tpt) {
+        case 2: return launch_ransac_tile<2, 256, 6, false>(h, a, threads, st, probe_only);
+        case 6: return launch_ransac_tile<6, 256, 3, false>(h, a, threads, st, probe_only);
+        case 8: return launch_ransac_tile<8, 256, 2, false>(h, a, threads, st, probe_only);
+        default: return threads > 256 ? launch_ransac_tile<4, 512, 2, false>(h, a, threads, st, probe_only)
+                                      : launch_ransac_tile<4, 256, 4, false>(h, a, threads, st, probe_only);
+        }
+    }
+    switch (tpt) {
+    case 2: return launch_ransac_tile<2, 256, 6, true>(h, a, threads, st, probe_only);
+    case 6: return launch_ransac_tile<6, 256, 4, true>(h, a, threads, st, probe_only);
+    case 8: return launch_ransac_tile<8, 256, 3, true>(h, a, threads, st, probe_only);
+    default: return threads > 256 ? launch_ransac_tile<4, 512, 2, true>(h, a, threads, st, probe_only)
+                                  : launch_ransac_tile<4, 256, 4, true>(h, a, threads, st, probe_only);
+    }
 }
 
 // warp-specialised persistent kernel (ransac_ws.cuh): one CTA per SM
@@ -217,7 +285,7 @@ static int dispatch_ransac_ws(Handle *h, RansacArgs a, cudaStream_t st)
 
 extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t *npts, int32_t B, int32_t N,
                                   int32_t chunk, int32_t trials, double thr, uint64_t seed,
-                                  uint64_t scan_base, double *line, int32_t *ninl, int32_t *win_trial,
+                                  uint64_t scan_base, const int32_t *pairs, double *line, int32_t *ninl, int32_t *win_trial,
                                   int32_t *win_pair, double *ssum, uint32_t *inl_mask, void *stream)
 {
     Handle *h = (Handle *)handle;
@@ -246,14 +314,26 @@ extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t 
     // when a chunk carries enough scoring work to amortise its per-chunk stages (C3: 410 points x 1024
     // trials, 22.5 vs 20.6 TFLOP/s); the phase-structured kernel wins on small chunks (C2: 14.3 vs 13.1)
     const bool big_chunks = (long long)chunk * trials >= 65536;
-    const int kernel = h->opt_kernel ? h->opt_kernel : (big_chunks ? 2 : 1);
-    const int tpt = h->opt_tpt ? h->opt_tpt : ((kernel == 2 && big_chunks) ? 4 : 2);
-    const int threads = h->opt_threads ? h->opt_threads : 256;
-    // screening precision of the phase-structured kernel: 1 = fp64, 2 = fp32 (FFMA2 trial pairs); default fp64
-    // until the fp32 path has its own measured win (ransac.screen)
-    const bool f32 = h->opt_screen == 2;
     cudaStream_t st = (cudaStream_t)stream;
     a.ws_ns = a.ws_np = a.ws_nb = 0;
+    a.inv_thr = 0.0; a.prefetch_ahead = 0;
+    a.pairs = pairs;
+    if (pairs != nullptr && ((uintptr_t)pairs & 7) != 0) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ransac_lines: pairs must be 8-byte aligned");
+    // tile kernel: 512-thread CTAs (20 chunk slots at 100 trials, two CTAs per SM) measured best on C2: 4.33 against 4.55 ms at 256
+    const int threads = h->opt_threads ? h->opt_threads : 512, threads1 = h->opt_threads ? h->opt_threads : 256;
+    // small chunks (the reference's 100 x 100): the tile kernel (3) when the shape fits it - one work item per thread,
+    // every trial's inlier words in shared memory - else the phase-structured kernel (1)
+    int kernel = h->opt_kernel;
+    if (kernel == 0)
+        kernel = (big_chunks && pairs == nullptr) ? 2 : (dispatch_ransac_tile(h, a, h->opt_tpt ? h->opt_tpt : 4, threads, st, true) == LSLAM_OK ? 3 : 1);
+    if (kernel == 3) {
+        const int rc = dispatch_ransac_tile(h, a, h->opt_tpt ? h->opt_tpt : 4, threads, st);
+        if (rc != LSLAM_ERR_CAPACITY || h->opt_kernel == 0) return rc;
+        return fail(h, LSLAM_ERR_CAPACITY, "ransac.kernel = 3 needs ceil(trials / tpt) <= threads and the trials' inlier words in shared memory "
+                                           "(chunk=%d, trials=%d)", chunk, trials);
+    }
+    if (kernel == 2 && pairs != nullptr) kernel = 1;              // the warp-specialised kernel has no explicit-pairs path
+    const int tpt = h->opt_tpt ? h->opt_tpt : ((kernel == 2 && big_chunks) ? 4 : 2);
     if (kernel == 2) {
         switch (tpt) {
         case 1: return dispatch_ransac_ws<1>(h, a, st);
@@ -262,9 +342,9 @@ extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t 
         }
     }
     switch (tpt) {
-    case 1: return launch_ransac<1, 512, 2, false>(h, a, threads, st);
-    case 2: return f32 ? launch_ransac<2, 512, 2, true>(h, a, threads, st) : launch_ransac<2, 512, 2, false>(h, a, threads, st);
-    default: return f32 ? launch_ransac<4, 512, 1, true>(h, a, threads, st) : launch_ransac<4, 512, 1, false>(h, a, threads, st);
+    case 1: return launch_ransac<1, 512, 2>(h, a, threads1, st);
+    case 2: return launch_ransac<2, 512, 2>(h, a, threads1, st);
+    default: return launch_ransac<4, 512, 1>(h, a, threads1, st);
     }
 }
 

@@ -133,7 +133,7 @@ __device__ __forceinline__ ChunkBand chunk_band(int max_abs_hi /* max over coord
 //   [eabs, chunk scale] keeps the bound tight where it matters (residuals of the order of thr)
 //   plus 2^-38 * ssf for the differing summation orders and roundings (n <= 8192).
 // The bound is linear in ssf, E(ssf) = alpha + beta * ssf, so a sweep over the trials needs no sqrt.
-struct SsumBound { double alpha, beta, kappa; };   // E(ssf) = alpha + beta * ssf + kappa * sqrt(ssf)
+struct SsumBound { double alpha, beta, kappa; };   // E(ssf) = alpha + beta * ssf (kappa: unused, 0)
 __device__ __forceinline__ double ssum_err(const SsumBound &b, double v)
 {
     double e = fma(b.beta, v, b.alpha);
@@ -154,64 +154,17 @@ __device__ __forceinline__ SsumBound ssum_bound_coeffs(double eabs, int n, doubl
     return b;
 }
 
-// ---- fp32 screening (ransac.cuh, F32 instantiations) ----------------------------------------
-// The hot loop may evaluate the signed distance in fp32.  Per chunk the points are centred on one of
-// the chunk's own points c0 (v = p - c0, formed in fp64) and rounded, q = fl32(v); per trial the unit
-// normal n and the offset c = -n.(o - c0) (o = midpoint of the sample pair) are rounded from their fp64
-// values; s_f = fma(q_y, n_y, fma(q_x, n_x, c)).  With R = max |p - c0|_2 over the chunk and u = 2^-24:
-//   q rounding      <= u (|n_x||v_x| + |n_y||v_y|) <= u R            (Cauchy-Schwarz, |n| = 1)
-//   n rounding      <= u R                  c rounding <= u |o - c0| <= u R
-//   inner fma       <= u (|q_x n_x| + |c|) <= 2 u R     outer fma <= u |s| <= u |p - o| <= 2 u R
-// so |s_f - s| <= 7 u R; the fp64 quantities (normal from a Newton-refined rsqrt, c, the literal
-// residual itself) add O(2^-40 R).  delta = 4.25e-7 R (7 u = 4.172e-7) bounds | |s_f| - r_literal |.
-// The inlier test runs on u_f = fl32(s_f^2 - t2), t2 = fl32(thr^2):  u_f = (s_f^2 - thr^2 + d)(1 + e),
-// |d| <= u thr^2, |e| <= u.  If | |s_f| - thr | < band then |s_f^2 - thr^2| < band (2 thr + band); hence
-//   |u_f| >= bu := (band (2 thr + band) + 1.001 u thr^2)(1 + 2^-22)   ==>   | |s_f| - thr | >= band,
-// and with band = 1.05 delta the sign of u_f is the literal decision r < thr (a trial with any |u_f| < bu
-// is re-scored literally).  Residual sums: per point |r^2 - s_f^2| <= delta (2|s_f| + delta), so with
-// V = sum s_f^2:  |sum r^2 - V| <= 2 delta sqrt(n V) + n delta^2  (Cauchy-Schwarz), and the fp32 chain
-// ss_f of fma(s,s,ss) satisfies |ss_f - V| <= 1.001 n u V.  E(ss_f) = alpha + beta ss_f + kappa sqrt(ss_f).
-struct Screen32 { float bu; double delta; bool force_literal; };
-
-__device__ __forceinline__ Screen32 screen32_params(double R, double thr)
+// the same with 1 / thr supplied (its rounding, 2^-53 relative, disappears in the factor 1.0001)
+__device__ __forceinline__ SsumBound ssum_bound_coeffs_inv(double eabs, int n, double thr, double inv_thr)
 {
-    Screen32 b;
-    b.delta = 4.25e-7 * R;
-    const double band = 1.05 * b.delta;
-    // outside these ranges every trial of the chunk is scored literally: fp32 range of s^2 and thr^2, a
-    // threshold the band is not small against, thr <= 0 or NaN, R not finite
-    b.force_literal = !(R >= 0x1p-40 && R <= 0x1p40 && thr <= 0x1p40 && 4.0 * band <= thr);
-    const double bu = (band * (2.0 * thr + band) + 1.001 * 0x1p-24 * thr * thr) * (1.0 + 0x1p-22);
-    b.bu = b.force_literal ? 0.0f : __double2float_ru(bu);
-    return b;
-}
-
-__device__ __forceinline__ SsumBound ssum_bound_coeffs32(double delta, int n)
-{
-    const double nn = (double)n, nu = nn * 0x1p-24;
+    const double scale = eabs * 0x1p36;
+    if (!(thr > eabs) || thr > scale) return ssum_bound_coeffs(eabs, n, thr);
+    const double nn = (double)n;
     SsumBound b;
-    b.alpha = 1.001 * nn * delta * delta;
-    b.beta = 1.01 * nu;
-    b.kappa = 2.01 * delta * sqrt(nn);
+    b.alpha = 1.0001 * eabs * nn * (thr + eabs);
+    b.beta = 1.0001 * fma(eabs, inv_thr, 0x1p-38);
+    b.kappa = 0.0;
     return b;
-}
-
-// packed fp32 pair in a 64-bit register and the sm_100 two-lane FMA (SASS FFMA2)
-__device__ __forceinline__ unsigned long long f32x2_pack(float lo, float hi)
-{
-    return ((unsigned long long)__float_as_uint(hi) << 32) | (unsigned long long)__float_as_uint(lo);
-}
-__device__ __forceinline__ float f32x2_lo(unsigned long long v) { return __uint_as_float((unsigned)v); }
-__device__ __forceinline__ float f32x2_hi(unsigned long long v) { return __uint_as_float((unsigned)(v >> 32)); }
-__device__ __forceinline__ unsigned long long f32x2_fma(unsigned long long a, unsigned long long b, unsigned long long c)
-{
-#ifndef LSLAM_EMU
-    unsigned long long d;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
-    return d;
-#else
-    return f32x2_pack(fmaf(f32x2_lo(a), f32x2_lo(b), f32x2_lo(c)), fmaf(f32x2_hi(a), f32x2_hi(b), f32x2_hi(c)));
-#endif
 }
 
 // ---- principal axis of a 2x2 scatter matrix (closed form of the SVD upstream uses) --------
@@ -226,6 +179,24 @@ __device__ __forceinline__ void principal_axis(double sxx, double sxy, double sy
     else { vx = sxy; vy = h - del; }
     const double nn = sqrt(fma(vx, vx, vy * vy));
     if (nn != 0.0) { vx /= nn; vy /= nn; } else { vx = 1.0; vy = 0.0; }
+    if (vx < 0.0 || (vx == 0.0 && vy < 0.0)) { vx = -vx; vy = -vy; }
+    dx = vx; dy = vy;
+}
+
+// the same with reciprocal square roots instead of sqrt + divisions (results agree to a few ulp; the refit is held to 1e-5)
+__device__ __forceinline__ void principal_axis_rsqrt(double sxx, double sxy, double syy, double &dx, double &dy)
+{
+    const double del = 0.5 * (sxx - syy);
+    const double h2 = fma(del, del, sxy * sxy);
+    double vx = 1.0, vy = 0.0;
+    if (h2 > 0.0) {
+        const double h = h2 * rsqrt(h2);
+        if (del >= 0.0) { vx = del + h; vy = sxy; }
+        else { vx = sxy; vy = h - del; }
+        const double n2 = fma(vx, vx, vy * vy);
+        if (n2 > 0.0 && n2 < 1.7976931348623157e308) { const double inv = rsqrt(n2); vx *= inv; vy *= inv; }
+        else principal_axis(sxx, sxy, syy, vx, vy);
+    }
     if (vx < 0.0 || (vx == 0.0 && vy < 0.0)) { vx = -vx; vy = -vy; }
     dx = vx; dy = vy;
 }

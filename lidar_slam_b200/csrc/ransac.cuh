@@ -25,6 +25,7 @@
 // trials are evaluated.
 #pragma once
 #include "lslam_core.cuh"
+#include "async_copy.cuh"
 
 #ifdef LSLAM_EMU
 #define LSLAM_SMEM_DECL unsigned char *smem_raw = emu::block_smem()
@@ -49,6 +50,9 @@ struct RansacArgs {
     int ipc;                        // work items (threads) per chunk = ceil(trials / TPT)
     long long nslots;               // B * C
     int ws_ns, ws_np, ws_nb;        // warp-specialised kernel: scorer warps, post warps, ring depth
+    const int32_t *pairs;           // [B,C,trials,2] explicit sample pairs, or nullptr = the Philox sampler
+    double inv_thr;                 // 1 / thr (tile kernel: keeps a division out of the per-slot set-up)
+    int prefetch_ahead;             // tile kernel: CTA b prefetches tile b + prefetch_ahead towards L2 (0 = off)
 };
 
 constexpr int kMaxCand = 8;         // candidates with precomputed models; more -> generic loop
@@ -57,9 +61,26 @@ constexpr int kCntExact = 0x40000000;
 constexpr int kStatusNoModel = -3;
 constexpr int kStatusNonFinite = -5;
 
+// the sample pair of trial t of global chunk slot gslot: the caller's explicit pair (indices clamped into the chunk),
+// or the Philox sampler (lslam_core.cuh sample_pair)
+__device__ __forceinline__ void explicit_pair(const RansacArgs &a, long long gslot, uint32_t t, uint32_t n, int &i, int &j)
+{
+    const int2 v = __ldg(reinterpret_cast<const int2 *>(a.pairs) + gslot * a.trials + t);
+    const int hi = (int)n - 1;
+    i = v.x < 0 ? 0 : (v.x > hi ? hi : v.x);
+    j = v.y < 0 ? 0 : (v.y > hi ? hi : v.y);
+}
+__device__ __forceinline__ void trial_pair(const RansacArgs &a, long long gslot, uint64_t scan, uint32_t c, uint32_t t, uint32_t n,
+                                           int &i, int &j)
+{
+    if (a.pairs != nullptr) explicit_pair(a, gslot, t, n, i, j);
+    else sample_pair(a.seed, scan, c, t, n, i, j);
+}
+
 // per-slot state in shared memory
 struct SlotState {
     unsigned long long scan;        // global scan index (Philox counter words 2,3)
+    long long gslot;                // global chunk slot index (explicit sample pairs)
     double best_ss;                 // literal residual sum of the winner
     int off, n, valid, c;           // first point (index into the staged points), count, flag, chunk idx
     int scale_hi;                   // high word of the largest |coordinate|
@@ -67,19 +88,14 @@ struct SlotState {
     int mx, ncand, minhi_q;         // maximal inlier count, number of candidates, quantised bound
     int best_t, best_i, best_j;     // winner trial and its sample pair
     int status;                     // 0 ok, else the value written to ninl
-    int force_lit;                  // fp32 screening: chunk outside its range, every trial scored literally
-    double c0x, c0y;                // fp32 screening: the point the chunk is centred on
-    double delta;                   // fp32 screening: bound on | |s_f| - r_literal |
-    float bu;                       // fp32 screening: |s_f^2 - thr^2| below this -> literal re-score
-    float pad_f;
     int cand_t[kMaxCand], cand_i[kMaxCand], cand_j[kMaxCand];
 };
 
 __host__ __device__ inline size_t align16(size_t b) { return (b + 15) & ~(size_t)15; }
 
-__host__ __device__ inline size_t ransac_smem_bytes(int G, int chunk, int T, int W, int nwarps, bool f32 = false)
+__host__ __device__ inline size_t ransac_smem_bytes(int G, int chunk, int T, int W, int nwarps)
 {
-    size_t b = (size_t)G * chunk * (f32 ? 8 : 16);           // points: double2, or float2 when screening in fp32
+    size_t b = (size_t)G * chunk * 16;                       // points: double2
     b += (size_t)G * T * 8;                                  // fast residual sums
     b += align16((size_t)G * T * 4);                         // counts
     b += align16((size_t)G * sizeof(SlotState));
@@ -128,8 +144,7 @@ __device__ __forceinline__ bool trial_is_candidate(int cv, double v, int mx, int
 
 // ---- CTA-level view of shared memory ---------------------------------------------------
 struct RansacSmem {
-    double2 *pts;       // staged points (fp64 screening)
-    float2 *ptsf;       // staged points rounded to fp32 (fp32 screening; the fp64 points stay in global memory)
+    double2 *pts;       // staged points
     double *ssf;
     int *cnt;
     SlotState *slot;
@@ -140,13 +155,11 @@ struct RansacSmem {
     int *geo;           // b0, c0, number of staged points
 };
 
-__device__ __forceinline__ RansacSmem carve_smem(unsigned char *raw, int G, int chunk, int T, int W, int nwarps,
-                                                 bool f32 = false)
+__device__ __forceinline__ RansacSmem carve_smem(unsigned char *raw, int G, int chunk, int T, int W, int nwarps)
 {
     RansacSmem s;
     unsigned char *p = raw;
-    s.pts = reinterpret_cast<double2 *>(p);
-    s.ptsf = reinterpret_cast<float2 *>(p);   p += (size_t)G * chunk * (f32 ? 8 : 16);
+    s.pts = reinterpret_cast<double2 *>(p);   p += (size_t)G * chunk * 16;
     s.ssf = reinterpret_cast<double *>(p);    p += (size_t)G * T * 8;
     s.cnt = reinterpret_cast<int *>(p);       p += align16((size_t)G * T * 4);
     s.slot = reinterpret_cast<SlotState *>(p); p += align16((size_t)G * sizeof(SlotState));
@@ -161,7 +174,8 @@ __device__ __forceinline__ RansacSmem carve_smem(unsigned char *raw, int G, int 
 // Exact, slow path for one chunk: literal score of EVERY trial and the sequential accept rule.
 // Used only when the fast pass was caught disagreeing with the literal count (never observed;
 // counted in counters[2]).  Leaves the winner in the slot state and its mask in smask.
-__device__ void slot_exact_fallback(const RansacArgs &a, SlotState *st, const double2 *P, uint32_t *smask_q,
+template <class Slot>
+__device__ void slot_exact_fallback(const RansacArgs &a, Slot *st, const double2 *P, uint32_t *smask_q,
                                     uint32_t *wtmp_w, int lane)
 {
     const int n = st->n, T = a.trials;
@@ -170,7 +184,7 @@ __device__ void slot_exact_fallback(const RansacArgs &a, SlotState *st, const do
     for (int t = 0; t < T; ++t) {
         int i, j, cl;
         double sl;
-        sample_pair(a.seed, st->scan, (uint32_t)st->c, (uint32_t)t, (uint32_t)n, i, j);
+        trial_pair(a, st->gslot, st->scan, (uint32_t)st->c, (uint32_t)t, (uint32_t)n, i, j);
         warp_literal_score(P, n, lit_pair_model(P[i], P[j]), a.thr, lane, cl, sl, wtmp_w);
         __syncwarp();
         if (cl > best_n || (cl == best_n && sl < best_ss)) {
@@ -186,18 +200,13 @@ __device__ void slot_exact_fallback(const RansacArgs &a, SlotState *st, const do
     __syncwarp();
 }
 
-// F32: the hot loop screens in fp32 (two trials per FFMA2, lslam_core.cuh "fp32 screening"); the staged
-// points are float2 and every fp64 use of the points (sample pairs, literal scores, refit) reads global
-// memory through L1.  Exactness is kept by the same flag / re-score / candidate machinery with the wider
-// fp32 band and bound.
-template <int TPT, int MAXT, int MINB, bool F32>
+template <int TPT, int MAXT, int MINB>
 __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacArgs a)
 {
-    static_assert(!F32 || TPT % 2 == 0, "fp32 screening packs trial pairs");
     LSLAM_SMEM_DECL;
     const int T = a.trials, G = a.G, chunk = a.chunk, W = a.W;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
-    const RansacSmem sm = carve_smem(smem_raw, G, chunk, T, W, nwarps, F32);
+    const RansacSmem sm = carve_smem(smem_raw, G, chunk, T, W, nwarps);
     const long long slot0 = (long long)blockIdx.x * G;
     const long long rem_slots = a.nslots - slot0;
     const int nsl = rem_slots < (long long)G ? (int)rem_slots : G;
@@ -216,23 +225,20 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
     __syncthreads();
     const int b0 = sm.geo[0], c0 = sm.geo[1], nstage = sm.geo[2];
     const long long gp0 = (long long)b0 * a.N + (long long)c0 * chunk;   // first staged point
-    const double2 *gpts = a.xy + gp0;
-    // the slot's fp64 points: shared memory, or (fp32 screening) global memory through L1
-#define LSLAM_SLOT_PTS(st_) (F32 ? gpts + (st_)->off : sm.pts + (st_)->off)
-    // residual-sum error bound of a slot, by screening precision
+#define LSLAM_SLOT_PTS(st_) (sm.pts + (st_)->off)
+    // residual-sum error bound of a slot
     auto slot_bound = [&](const SlotState *st_, int n_) -> SsumBound {
-        if (F32) return ssum_bound_coeffs32(st_->delta, n_);
         return ssum_bound_coeffs(chunk_band(st_->scale_hi).eabs, n_, a.thr);
     };
 
     // ---- stage the CTA's points (contiguous in global memory): 16 B per thread, coalesced;
     //      track the largest |coordinate| of the CTA on the way ----
-    if constexpr (!F32) {
+    {
         const double2 *src = a.xy + gp0;
         int mh = 0;
         for (int k = tid; k < nstage; k += blockDim.x) {
             const double2 p = __ldg(src + k);
-            if (!F32) sm.pts[k] = p;
+            sm.pts[k] = p;
             const int hx = __double2hiint(p.x) & 0x7fffffff, hy = __double2hiint(p.y) & 0x7fffffff;
             mh = mh > hx ? mh : hx;
             mh = mh > hy ? mh : hy;
@@ -252,6 +258,7 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
         n = n < 0 ? 0 : (n > chunk ? chunk : n);
         SlotState *st = sm.slot + q;
         st->scan = a.scan_base + (uint64_t)b;
+        st->gslot = slot0 + q;
         st->best_ss = 0.0;
         st->off = (int)((long long)b * a.N + (long long)c * chunk - gp0);
         st->n = n;
@@ -281,138 +288,8 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
         __syncthreads();
     }
 
-    if constexpr (F32) {
-        // ---- fp32 screening: warp per slot - centre the chunk on its middle point, round to fp32, and
-        //      derive the slot's radius -> error bound delta and re-check limit bu (lslam_core.cuh) ----
-        for (int q = warp; q < nsl; q += nwarps) {
-            SlotState *st = sm.slot + q;
-            const int n = st->n;
-            const double2 *P = gpts + st->off;
-            float2 *Pf = sm.ptsf + st->off;
-            const double2 c = n > 0 ? __ldg(P + (n >> 1)) : make_double2(0.0, 0.0);
-            double r2 = 0.0;
-            int mh = 0;
-            for (int k = lane; k < n; k += 32) {
-                const double2 p = __ldg(P + k);
-                const int hx = __double2hiint(p.x) & 0x7fffffff, hy = __double2hiint(p.y) & 0x7fffffff;
-                mh = mh > hx ? mh : hx;
-                mh = mh > hy ? mh : hy;
-                const double vx = p.x - c.x, vy = p.y - c.y;
-                Pf[k] = make_float2((float)vx, (float)vy);
-                r2 = fmax(r2, fma(vx, vx, vy * vy));
-            }
-            mh = __reduce_max_sync(LSLAM_FULL_MASK, mh);
-#pragma unroll
-            for (int o = 16; o >= 1; o >>= 1) r2 = fmax(r2, __shfl_xor_sync(LSLAM_FULL_MASK, r2, o));
-            if (lane == 0) {
-                st->scale_hi = mh;
-                const Screen32 sc = screen32_params(sqrt(r2) * 1.0000001, a.thr);
-                st->c0x = c.x; st->c0y = c.y; st->delta = sc.delta; st->bu = sc.bu;
-                st->force_lit = sc.force_literal ? 1 : 0;
-            }
-        }
-        __syncthreads();
-    }
-
     // ================= score: thread per (chunk, TPT trials), loop over the chunk's points =========
     const int items = nsl * a.ipc;
-    if constexpr (F32) {
-    // ---- fp32 screening: TPT/2 packed trial pairs per thread; per point and pair 4 FFMA2 (signed distance
-    //      2, sum of squares 1, s^2 - thr^2 1) + 2 SHF (sign bits) + 1 FMNMX3 (closest approach of the pair)
-    const float thr2f = (float)(a.thr * a.thr);
-    const unsigned long long mthr2 = f32x2_pack(-thr2f, -thr2f);
-    for (int item = tid; item < items; item += blockDim.x) {
-        const int q = item / a.ipc, tb = item - q * a.ipc;
-        SlotState *st = sm.slot + q;
-        const bool force_lit = st->force_lit != 0;
-        const float bu = st->bu;
-        const bool skip = !st->valid || chunk_band(st->scale_hi).bad;
-        const double2 *P = LSLAM_SLOT_PTS(st);
-        const float2 *Pf = sm.ptsf + st->off;
-        const double c0x = st->c0x, c0y = st->c0y;
-        const uint64_t scan = st->scan;
-        const uint32_t c = (uint32_t)st->c;
-        const int t0 = tb * TPT;
-        const uint32_t n = (uint32_t)st->n;
-        constexpr int NP = TPT / 2;
-        unsigned long long nx2[NP], ny2[NP], ng2[NP], ss2[NP];
-        unsigned bits[TPT];
-        int cnt[TPT];
-        float mab[NP];
-        bool deg[TPT];
-#pragma unroll
-        for (int pr = 0; pr < NP; ++pr) {
-            const int t = t0 + 2 * pr;
-            const Philox4 ph = philox4x32_10((uint32_t)t >> 1, c, (uint32_t)scan, (uint32_t)(scan >> 32),
-                                             (uint32_t)a.seed, (uint32_t)(a.seed >> 32));
-            float fx[2] = {0.f, 0.f}, fy[2] = {0.f, 0.f}, fc[2] = {0.f, 0.f};
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                deg[2 * pr + h] = false; bits[2 * pr + h] = 0u; cnt[2 * pr + h] = 0;
-                if (!skip && !force_lit && t + h < T) {
-                    int i, j;
-                    pair_from_words(h ? ph.r[2] : ph.r[0], h ? ph.r[3] : ph.r[1], n, i, j);
-                    const double2 pi = __ldg(P + i), pj = __ldg(P + j);
-                    const FastLine f = fast_pair_model(make_double2(pi.x - c0x, pi.y - c0y),
-                                                       make_double2(pj.x - c0x, pj.y - c0y));
-                    fx[h] = (float)f.nx; fy[h] = (float)f.ny; fc[h] = (float)f.negc; deg[2 * pr + h] = f.degenerate;
-                }
-            }
-            nx2[pr] = f32x2_pack(fx[0], fx[1]); ny2[pr] = f32x2_pack(fy[0], fy[1]); ng2[pr] = f32x2_pack(fc[0], fc[1]);
-            ss2[pr] = 0ull; mab[pr] = __int_as_float(0x7f800000);
-        }
-#define LSLAM_PHE32_STEP(PT)                                                                   \
-    {                                                                                          \
-        const float2 p_ = (PT);                                                                \
-        const unsigned long long px_ = f32x2_pack(p_.x, p_.x), py_ = f32x2_pack(p_.y, p_.y);   \
-        _Pragma("unroll") for (int k_ = 0; k_ < NP; ++k_) {                                    \
-            const unsigned long long s_ = f32x2_fma(py_, ny2[k_], f32x2_fma(px_, nx2[k_], ng2[k_])); \
-            ss2[k_] = f32x2_fma(s_, s_, ss2[k_]);                                              \
-            const unsigned long long u_ = f32x2_fma(s_, s_, mthr2);                            \
-            bits[2 * k_] = __funnelshift_l((unsigned)u_, bits[2 * k_], 1);                     \
-            bits[2 * k_ + 1] = __funnelshift_l((unsigned)(u_ >> 32), bits[2 * k_ + 1], 1);     \
-            mab[k_] = fminf(mab[k_], fminf(fabsf(f32x2_lo(u_)), fabsf(f32x2_hi(u_))));         \
-        }                                                                                      \
-    }
-        const int n_eff = (skip || force_lit) ? 0 : (int)n;
-        int k = 0;
-        for (; k + 32 <= n_eff; k += 32) {
-#pragma unroll 8
-            for (int kk = 0; kk < 32; ++kk) LSLAM_PHE32_STEP(Pf[k + kk]);
-#pragma unroll
-            for (int k_ = 0; k_ < TPT; ++k_) cnt[k_] += __popc(bits[k_]);
-        }
-        const int rem = n_eff - k;
-        if (rem > 0) {
-            int kk = 0;
-            for (; kk + 4 <= rem; kk += 4) {
-                LSLAM_PHE32_STEP(Pf[k + kk]);
-                LSLAM_PHE32_STEP(Pf[k + kk + 1]);
-                LSLAM_PHE32_STEP(Pf[k + kk + 2]);
-                LSLAM_PHE32_STEP(Pf[k + kk + 3]);
-            }
-            for (; kk < rem; ++kk) LSLAM_PHE32_STEP(Pf[k + kk]);
-#pragma unroll
-            for (int k_ = 0; k_ < TPT; ++k_) cnt[k_] += __popc(bits[k_] & ((1u << rem) - 1u));
-        }
-#undef LSLAM_PHE32_STEP
-        bool any_flag = false;
-#pragma unroll
-        for (int k_ = 0; k_ < TPT; ++k_) {
-            const int t = t0 + k_;
-            if (t < T) {
-                const float ssf_ = (k_ & 1) ? f32x2_hi(ss2[k_ >> 1]) : f32x2_lo(ss2[k_ >> 1]);
-                // literal re-score wanted: coincident samples, a chunk outside the fp32 screening range,
-                // a point of either trial of the pair inside the band, or a non-finite fast sum
-                const bool flag = deg[k_] || force_lit || mab[k_ >> 1] < bu || !(ssf_ <= 3.4028234e38f);
-                sm.cnt[q * T + t] = skip ? 0 : (flag ? kCntFlagged : cnt[k_]);
-                sm.ssf[q * T + t] = (double)ssf_;
-                any_flag |= flag && !skip;
-            }
-        }
-        if (any_flag) st->flag = 1;
-    }
-    } else {
     for (int item = tid; item < items; item += blockDim.x) {
         const int q = item / a.ipc, tb = item - q * a.ipc;
         SlotState *st = sm.slot + q;
@@ -441,7 +318,8 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
             if (!skip && t < T) {
                 int i, j;
                 const bool odd = t & 1;
-                pair_from_words(odd ? ph.r[2] : ph.r[0], odd ? ph.r[3] : ph.r[1], n, i, j);
+                if (a.pairs != nullptr) explicit_pair(a, st->gslot, (uint32_t)t, n, i, j);
+                else pair_from_words(odd ? ph.r[2] : ph.r[0], odd ? ph.r[3] : ph.r[1], n, i, j);
                 const FastLine f = fast_pair_model(P[i], P[j]);
                 nx[k] = f.nx; ny[k] = f.ny; ng[k] = f.negc; deg[k] = f.degenerate;
             }
@@ -496,7 +374,6 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
         }
         if (any_flag) st->flag = 1;
     }
-    }
     __syncthreads();
 
     // ================= select: warp per chunk - flagged re-score, max count, candidate list ========
@@ -521,7 +398,7 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
                     m &= m - 1;
                     int i, j, cl;
                     double sl;
-                    sample_pair(a.seed, st->scan, (uint32_t)st->c, (uint32_t)tt, (uint32_t)n, i, j);
+                    trial_pair(a, st->gslot, st->scan, (uint32_t)st->c, (uint32_t)tt, (uint32_t)n, i, j);
                     warp_literal_score(P, n, lit_pair_model(P[i], P[j]), a.thr, lane, cl, sl, nullptr);
                     if (lane == 0) { cq[tt] = cl | kCntExact; sq[tt] = sl; }
                     ++n_relit;
@@ -613,7 +490,7 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
         if (st->status == 0 && ci < st->ncand) {
             const double2 *P = LSLAM_SLOT_PTS(st);
             int i, j;
-            sample_pair(a.seed, st->scan, (uint32_t)st->c, (uint32_t)st->cand_t[ci], (uint32_t)st->n, i, j);
+            trial_pair(a, st->gslot, st->scan, (uint32_t)st->c, (uint32_t)st->cand_t[ci], (uint32_t)st->n, i, j);
             st->cand_i[ci] = i;
             st->cand_j[ci] = j;
             // a single unflagged candidate with no residual sum requested is decided on the fast model
@@ -684,7 +561,7 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_lines_kernel(const RansacAr
                     m &= m - 1;
                     int i, j, cl;
                     double sl;
-                    sample_pair(a.seed, st->scan, (uint32_t)st->c, (uint32_t)tt, (uint32_t)n, i, j);
+                    trial_pair(a, st->gslot, st->scan, (uint32_t)st->c, (uint32_t)tt, (uint32_t)n, i, j);
                     warp_literal_score(P, n, lit_pair_model(P[i], P[j]), a.thr, lane, cl, sl, wt);
                     __syncwarp();
                     if (cl != mx) fault = true;

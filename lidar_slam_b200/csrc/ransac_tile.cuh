@@ -1,0 +1,651 @@
+// ransac_tile.cuh - K3: batched 2-point RANSAC for SMALL chunks (the reference's own 100 points x 100 trials),
+// one launch.  Replaces, per chunk, /root/reference/ransac_functions.py:23-30 (skimage.measure.ransac with
+// LineModelND, then slope/intercept/tip).  Semantics = oracle/ransac_line.py; every integer output and the residual
+// sum are bit-exact, the refit is held to 1e-5.
+//
+// Round-2 redesign of ransac.cuh for the shape where per-chunk overhead, not the scoring loop, was the loss
+// (profiles/r03a_ransac_c2_ncu_summary.txt: seven block barriers, hot loop only 59.5 % of the instructions):
+//
+//   * hot loop = 2 DFMA + FADD + SHF + FMNMX/2 per point-hypothesis (round 1: 3 DFMA + DADD + SHF + FMNMX/2;
+//     tools/probe/mix_probe4.cu: 9.7 against 13.3 issue cycles per PHE-warp):
+//       - the inlier test |s| < thr runs on the HIGH WORDS of |s| and thr as one fp32 subtraction (the high word of a
+//         positive double is order-preserving as a float); a trial with a point whose high word is within one unit of
+//         thr's is re-scored literally (tile_flag_limit) - the re-check band is 2^-20 relative to thr instead of
+//         2^-36 relative to the chunk scale, still far below the sensor noise;
+//       - the fast residual sum (only used to rank trials tied on the count, inside a rigorous error bound) is NOT
+//         accumulated per point: sum_k s_k^2 is a quadratic form in the line coefficients whose matrix is the
+//         chunk's second-moment matrix about one of its own points (tile_moment_sum, bound in tile_moment_err);
+//   * F32 instantiation (default): the signed distance itself is evaluated in fp32 on the chunk's points centred on its
+//     middle point (2 FFMA + FADD + SHF + FMNMX/2; 6.4 against 9.7 cycles).  |s_f - s| <= 7 u R (u = 2^-24, R = the
+//     chunk's radius about that point; derivation below at tile_screen32), so a trial whose closest approach to the
+//     threshold is inside delta + u thr is flagged and re-scored literally; every output stays bit-exact;
+//   * every trial's inlier bits are kept in shared memory (one STS per 32 points), so the winner's mask is read,
+//     not rebuilt;
+//   * one work item (TPT trials of one chunk) per thread, per-trial results stay in registers; the chunk-wide
+//     maximum (count, then smallest upper bound of the residual sum) is ONE 64-bit shared-memory atomicMax per
+//     thread; trials flagged for the literal formula are re-scored warp-cooperatively on the spot;
+//   * three block barriers per tile (stage+moments | score | candidates | decide+refit+stores by lane groups).
+#pragma once
+#include "ransac.cuh"
+#include <type_traits>
+
+namespace lslam {
+
+constexpr int kTileLG = 8;             // lanes that stage / refit one chunk slot
+
+struct TileSlot {
+    unsigned long long scan;           // global scan index (Philox counter words 2, 3)
+    long long gslot;                   // global chunk slot index (explicit sample pairs)
+    unsigned long long key;            // max over trials of (count << 32) | (0x7fffffff - key_up(upper bound of sum r^2))
+    double c0x, c0y;                   // centre of the moments: the chunk's middle point
+    double Sx, Sy, Sxx, Sxy, Syy;      // moments of q = fl(p - c0)
+    double best_ss;
+    double alpha, beta;                // bound on |sum r^2 - sum s^2| = alpha + beta * sum s^2 (ssum_bound_coeffs)
+    double A, nn;                      // Sxx + Syy and n as a double
+    float bandf, pad_f;                // fp32 screening: | |s_f| - thr_f | below this -> literal re-score
+    int off, n, valid, c;
+    int scale_hi;                      // high word of the largest |coordinate| of the slot
+    int force_lit;                     // every trial is scored literally (threshold / scale outside the fast path's range)
+    int mx, ncand, status;
+    int best_t, best_i, best_j;
+    int mask_base, mask_stride;        // the winner's inlier words: mw[mask_base + w * mask_stride]
+    int cand_exact;                    // bit p: candidate p was re-scored literally (its count / mask are the literal ones)
+    int cand_t[kMaxCand], cand_i[kMaxCand], cand_j[kMaxCand];
+};
+
+struct TileSmem {
+    double2 *pts;
+    float2 *ptsf;       // fp32 screening: the points centred on the slot's middle point, slot q at q * chunk_pad
+    int2 *keys;         // [G][TPT][ipc] (key_down(lower bound), key_up(upper bound)) of every trial's residual sum
+    uint32_t *mw;       // [G][W][TPT][ipc] inlier words of every trial, then [G][W] literal winner masks
+    uint32_t *wtmp;     // [nwarps][W]
+    TileSlot *slot;
+    int smask0;         // index of the literal winner masks inside mw
+};
+
+__host__ __device__ inline size_t tile_smem_bytes(int G, int chunk, int ipc, int tpt, int W, int nwarps, bool f32)
+{
+    size_t b = (size_t)G * chunk * 16;
+    if (f32) b += (size_t)G * ((chunk + 1) & ~1) * 8;
+    b += (size_t)G * tpt * ipc * 8;
+    b += align16(((size_t)G * W * tpt * ipc + (size_t)G * W) * 4);
+    b += align16((size_t)nwarps * W * 4);
+    b += align16((size_t)G * sizeof(TileSlot));
+    return b;
+}
+
+__device__ __forceinline__ TileSmem tile_carve(unsigned char *raw, int G, int chunk, int ipc, int tpt, int W, int nwarps, bool f32)
+{
+    TileSmem s;
+    unsigned char *p = raw;
+    s.pts = reinterpret_cast<double2 *>(p);  p += (size_t)G * chunk * 16;
+    s.ptsf = reinterpret_cast<float2 *>(p);  if (f32) p += (size_t)G * ((chunk + 1) & ~1) * 8;
+    s.keys = reinterpret_cast<int2 *>(p);    p += (size_t)G * tpt * ipc * 8;
+    s.mw = reinterpret_cast<uint32_t *>(p);  p += align16(((size_t)G * W * tpt * ipc + (size_t)G * W) * 4);
+    s.smask0 = G * W * tpt * ipc;
+    s.wtmp = reinterpret_cast<uint32_t *>(p); p += align16((size_t)nwarps * W * 4);
+    s.slot = reinterpret_cast<TileSlot *>(p);
+    return s;
+}
+
+// ---- inlier test on high words -------------------------------------------------------------------------------
+// hs = high word of s reinterpreted as a float, th = high word of thr as a float; f = |hs| - th (one FADD, exact for
+// neighbouring floats).  sign(f) set  <=>  hi(|s|) < hi(thr)  =>  |s| < thr.  If the high words differ by two units or
+// more, |s| and thr differ by more than 2^(e_thr - 21), and tile_fast_ok() makes sure that exceeds the bound
+// 2^(e2 - 36) on | |s| - r_literal | (lslam_core.cuh): the fast decision is the literal one.  Otherwise
+// (|f| < tile_flag_limit) the trial is flagged and re-scored with the literal formula.
+__device__ __forceinline__ float tile_flag_limit(float th)
+{
+    const float up = __int_as_float(__float_as_int(th) + 1);
+    return 1.5f * (up - th);           // covers a difference of one unit on either side, also across a binade
+}
+// the fast path needs: thr a normal positive double in a sane range, and the chunk scale 2^e2 at most 2^15 thr
+__device__ __forceinline__ bool tile_fast_ok(double thr, int scale_hi)
+{
+    const int et = (__double2hiint(thr) >> 20) & 0x7ff, es = (scale_hi >> 20) & 0x7ff;
+    return thr > 0.0 && et >= 1023 - 400 && et <= 1023 + 400 && (es + 1) - et <= 15;
+}
+
+// ---- fp32 screening ---------------------------------------------------------------------------------------------
+// Points centred on a point c0 of the chunk and rounded, q = fl32(p - c0) (difference formed in fp64); per trial the
+// unit normal (nx, ny) and cp = nx c0x + ny c0y + ng (the line's offset relative to c0, |cp| <= R because the line
+// passes through two points of the chunk) rounded from their fp64 values; s_f = fma(q_y, n_y, fma(q_x, n_x, cp)).  With
+// R = max |p - c0|_2 over the chunk and u = 2^-24:
+//   q rounding <= u R,  n rounding <= u R,  cp rounding <= u R,  inner fma <= 2 u R,  outer fma <= u |s_f| <= 2 u R
+// so |s_f - s| <= 7 u R, and the fp64 quantities (normal from a Newton-refined rsqrt, cp, the literal residual itself)
+// add O(2^-40 R):  delta = 4.25e-7 R (7 u = 4.172e-7) bounds | |s_f| - r_literal |.  The test runs on f = |s_f| - thr_f,
+// thr_f = fl32(thr) (|thr_f - thr| <= u thr; the subtraction is exact near zero and otherwise off by a factor 1 + u):
+//   |f| >= bandf = (delta + u thr)(1 + 2^-20)  ==>  sign(f) is the literal decision r < thr.
+struct TileScreen32 { float bandf; bool force_literal; };
+__device__ __forceinline__ float tile_sqrt_up(double r2)
+{
+#ifndef LSLAM_EMU
+    return __fsqrt_ru(__double2float_ru(r2));
+#else
+    const float f = __double2float_ru(r2);
+    float s = sqrtf(f);
+    while ((double)s * (double)s < (double)f) s = nextafterf(s, INFINITY);
+    return s;
+#endif
+}
+__device__ __forceinline__ TileScreen32 tile_screen32(double R, double thr)
+{
+    TileScreen32 b;
+    const double band = (4.25e-7 * R + 0x1p-24 * thr) * (1.0 + 0x1p-20);
+    // outside these ranges every trial of the chunk is scored literally: fp32 range of the products, a threshold the
+    // band is not small against, thr <= 0 or NaN, R not finite
+    b.force_literal = !(R >= 0x1p-40 && R <= 0x1p40 && thr >= 0x1p-40 && thr <= 0x1p40 && 4.0 * band <= thr);
+    b.bandf = b.force_literal ? 0.0f : __double2float_ru(band);
+    return b;
+}
+
+// ---- residual sum from moments -------------------------------------------------------------------------------
+// For the line (nx, ny, ng) and the centred points q_k = fl(p_k - c0):  sigma_k = nx qx_k + ny qy_k + cp with
+// cp = fl(nx c0x + ny c0y + ng) differs from the hot loop's s_k by < 2^-50 S (roundings of q, cp and the two FMAs),
+// far inside the per-point bound eabs = 2^-36 S that ssum_bound_coeffs() already allows between |s_k| and the
+// literal residual.  sum_k sigma_k^2 = nx^2 Sxx + 2 nx ny Sxy + ny^2 Syy + 2 cp (nx Sx + ny Sy) + n cp^2 exactly; the
+// evaluation below (moments summed with FMAs in any order, ~12 roundings here) is off by at most
+//   (2.5 n + 10) eps (A + n cp^2),  A = Sxx + Syy,  eps = 2^-53
+// (each moment carries <= n eps of its absolute sum; Cauchy-Schwarz and AM-GM fold the mixed terms into A + n cp^2).
+// tile_moment_err() returns twice that with n + 32 for n.
+__device__ __forceinline__ double tile_moment_sum(double nx, double ny, double cp, double nn, const TileSlot *st)
+{
+    const double a1 = fma(nx, st->Sxx, ny * st->Sxy), a2 = fma(nx, st->Sxy, ny * st->Syy);
+    const double quad = fma(nx, a1, ny * a2), lin = fma(nx, st->Sx, ny * st->Sy);
+    return fma(cp, fma(nn, cp, 2.0 * lin), quad);
+}
+__device__ __forceinline__ double tile_moment_err(double cp, double nn, double A)
+{
+    return (5.0 * (nn + 32.0) + 20.0) * 0x1p-53 * 1.01 * fma(nn * cp, cp, A);
+}
+
+// literal score of one hypothesis by a whole warp, mask words stored with a stride
+__device__ __forceinline__ void warp_literal_score_strided(const double2 *P, int n, const LitLine m, double thr, int lane,
+                                                           int &cnt, double &ssum, uint32_t *mask_out, int stride)
+{
+    double part = 0.0;
+    int c = 0;
+    for (int k0 = 0; k0 < n; k0 += 32) {
+        const int k = k0 + lane;
+        bool in = false;
+        if (k < n) {
+            const double r = lit_residual(m, P[k]);
+            in = r < thr;
+            part = __dadd_rn(part, __dmul_rn(r, r));
+        }
+        const unsigned b = __ballot_sync(LSLAM_FULL_MASK, in);
+        c += __popc(b);
+        if (mask_out != nullptr && lane == 0) mask_out[(k0 >> 5) * stride] = b;
+    }
+    cnt = c;
+    ssum = warp_tree32(part);
+}
+
+template <int TPT, int MAXT, int MINB, bool F32>
+__global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArgs a)
+{
+    static_assert(TPT % 2 == 0, "a Philox block serves two trials");
+    constexpr int LG = kTileLG;
+    LSLAM_SMEM_DECL;
+    const int T = a.trials, G = a.G, chunk = a.chunk, W = a.W, ipc = a.ipc;
+    const int chunk_pad = (chunk + 1) & ~1;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const TileSmem sm = tile_carve(smem_raw, G, chunk, ipc, TPT, W, nwarps, F32);
+    const long long slot0 = (long long)blockIdx.x * G;
+    const long long rem_slots = a.nslots - slot0;
+    const int nsl = rem_slots < (long long)G ? (int)rem_slots : G;
+
+    // ================= stage + moments: LG lanes per slot =====================================================
+    {
+        const int grp = tid / LG, r = tid % LG, ngrp = blockDim.x / LG;
+        for (int qb = 0; qb < nsl; qb += ngrp) {                  // uniform trip count: the shuffles below are warp-wide
+            if (qb + warp * (32 / LG) >= nsl) {                   // (warp-uniform) none of this warp's groups has a slot
+                // the last such warp pulls the points of the tile a later CTA will stage (prefetch_ahead tiles on)
+                // towards L2, so that its copies do not wait for DRAM
+                if (qb == 0 && warp == nwarps - 1 && a.prefetch_ahead > 0) {
+                    const long long s1 = slot0 + (long long)a.prefetch_ahead * G;
+                    if (s1 < a.nslots) {
+                        const long long s2 = s1 + G < a.nslots ? s1 + G : a.nslots;
+                        const long long b1 = s1 / a.C, b2 = s2 / a.C;
+                        const long long p1 = b1 * a.N + (s1 - b1 * a.C) * chunk, p2 = b2 * a.N + (s2 - b2 * a.C) * chunk;
+                        const char *base = reinterpret_cast<const char *>(a.xy);
+                        const long long lim = (long long)a.B * a.N * 16;
+                        for (long long ofs = (p1 * 16 & ~127LL) + 128LL * lane; ofs < p2 * 16 && ofs < lim; ofs += 128 * 32) prefetch_l2(base + ofs);
+                    }
+                }
+                break;
+            }
+            // CTA geometry (32-bit division whenever the slot index fits)
+            long long b0;
+            int c0;
+            if (slot0 <= 0x7fffffffLL) {
+                const unsigned s = (unsigned)slot0, bq = s / (unsigned)a.C;
+                b0 = bq; c0 = (int)(s - bq * (unsigned)a.C);
+            } else {
+                b0 = slot0 / a.C; c0 = (int)(slot0 - b0 * a.C);
+            }
+            const long long gp0 = b0 * a.N + (long long)c0 * chunk;       // first staged point
+            const int q = qb + grp;
+            const bool act = q < nsl;
+            int n = 0, off = 0, c = 0;
+            long long b = b0;
+            if (act) {
+                const int cq = c0 + q, bb = cq / a.C;
+                c = cq - bb * a.C; b = b0 + bb;
+                int nb = a.npts ? a.npts[b] : a.N;
+                nb = nb < 0 ? 0 : (nb > a.N ? a.N : nb);
+                n = nb - c * chunk;
+                n = n < 0 ? 0 : (n > chunk ? chunk : n);
+                off = (int)((long long)bb * a.N + (long long)(c - c0) * chunk);
+            }
+            const double2 *src = a.xy + gp0 + off;
+            double2 *dst = sm.pts + off;
+            // asynchronous copies (no register staging: all of a lane's loads are in flight at once), then one pass
+            // over the staged points for the slot's scale and its moments about its middle point
+            for (int k = r; k < n; k += LG) cp_async16(dst + k, src + k);
+            cp_async_wait_all();
+            __syncwarp();
+            // functions.py:64-76: full chunks, or a remainder of MORE than 2 points
+            const bool valid = (n >= 2) && (n == chunk || n > 2);
+            const double2 cc = n > 0 ? dst[n >> 1] : make_double2(0.0, 0.0);
+            float2 *dstf = sm.ptsf + (size_t)(act ? q : 0) * chunk_pad;
+            int mh = 0;
+            double sx = 0.0, sy = 0.0, sxx = 0.0, sxy = 0.0, syy = 0.0, r2 = 0.0;
+            for (int k = r; k < n; k += LG) {
+                const double2 p = dst[k];
+                const int hx = __double2hiint(p.x) & 0x7fffffff, hy = __double2hiint(p.y) & 0x7fffffff;
+                mh = mh > hx ? mh : hx;
+                mh = mh > hy ? mh : hy;
+                const double qx = p.x - cc.x, qy = p.y - cc.y;
+                sx += qx; sy += qy;
+                sxx = fma(qx, qx, sxx); sxy = fma(qx, qy, sxy); syy = fma(qy, qy, syy);
+                if constexpr (F32) {
+                    dstf[k] = make_float2((float)qx, (float)qy);
+                    r2 = fmax(r2, fma(qx, qx, qy * qy));
+                }
+            }
+#pragma unroll
+            for (int o = LG / 2; o >= 1; o >>= 1) { const int v = __shfl_xor_sync(LSLAM_FULL_MASK, mh, o); mh = mh > v ? mh : v; }
+            const ChunkBand cb = chunk_band(mh);
+#pragma unroll
+            for (int o = LG / 2; o >= 1; o >>= 1) {
+                sx += __shfl_xor_sync(LSLAM_FULL_MASK, sx, o);
+                sy += __shfl_xor_sync(LSLAM_FULL_MASK, sy, o);
+                sxx += __shfl_xor_sync(LSLAM_FULL_MASK, sxx, o);
+                sxy += __shfl_xor_sync(LSLAM_FULL_MASK, sxy, o);
+                syy += __shfl_xor_sync(LSLAM_FULL_MASK, syy, o);
+                if constexpr (F32) r2 = fmax(r2, __shfl_xor_sync(LSLAM_FULL_MASK, r2, o));
+            }
+            if (act && r == 0) {
+                TileSlot *st = sm.slot + q;
+                st->scan = a.scan_base + (uint64_t)b;
+                st->gslot = slot0 + q;
+                st->key = 0ull;
+                st->c0x = cc.x; st->c0y = cc.y;
+                st->Sx = sx; st->Sy = sy; st->Sxx = sxx; st->Sxy = sxy; st->Syy = syy;
+                st->best_ss = 0.0;
+                const SsumBound sbq = ssum_bound_coeffs_inv(cb.eabs, n, a.thr, a.inv_thr);
+                st->alpha = sbq.alpha; st->beta = sbq.beta; st->A = sxx + syy; st->nn = (double)n;
+                st->off = off; st->n = n; st->valid = valid ? 1 : 0; st->c = c;
+                st->scale_hi = mh;
+                bool force = cb.force_literal;
+                st->bandf = 0.0f; st->pad_f = 0.0f;
+                if constexpr (F32) {
+                    // an upper bound of the radius is enough: fp32 square root rounded up (overflow -> inf, underflow -> 0:
+                    // both outside the screening range, the slot is then scored literally)
+                    const TileScreen32 sc = tile_screen32((double)tile_sqrt_up(r2), a.thr);
+                    st->bandf = sc.bandf;
+                    force = force || sc.force_literal;
+                } else {
+                    force = force || !tile_fast_ok(a.thr, mh);
+                }
+                st->force_lit = force ? 1 : 0;
+                st->mx = 0; st->ncand = 0;
+                st->status = !valid ? 0x7fffffff : (cb.bad ? kStatusNonFinite : 0);   // 0x7fffffff: unused slot
+                st->best_t = -1; st->best_i = -1; st->best_j = -1;
+                st->mask_base = 0; st->mask_stride = 0; st->cand_exact = 0;
+            }
+        }
+    }
+    __syncthreads();
+
+    // ================= score: one work item (TPT trials of one chunk) per thread =============================
+    const int items = nsl * ipc;
+    const bool has_item = tid < items;
+    const int q = has_item ? tid / ipc : 0, tb = has_item ? tid - q * ipc : 0;
+    TileSlot *st = sm.slot + q;
+    const int n = st->n, t0 = tb * TPT;
+    const bool skip = !has_item || st->status != 0;
+    const double2 *P = sm.pts + st->off;
+    const int row0 = (q * W * TPT) * ipc + tb;                    // trial k, word w: mw[row0 + (w * TPT + k) * ipc]
+    int2 *krow = sm.keys + (size_t)q * TPT * ipc + tb;            // trial k: krow[k * ipc]
+    int cnt[TPT];
+    unsigned live = 0, exact = 0;                                 // bit k: trial t0 + k exists / was scored literally
+    {
+        const bool force_lit = st->force_lit != 0;
+        const uint64_t scan = st->scan;
+        // the hot loop's line: fp64 (nx, ny, ng) on the staged points, or fp32 (nx, ny, cp) on the centred points
+        typedef typename std::conditional<F32, float, double>::type real;
+        real nx[TPT], ny[TPT], ng[TPT];
+        unsigned bits[TPT];
+        float mab[TPT];
+        unsigned flagm = 0;
+        const double nn = st->nn, A = st->A, sb_alpha = st->alpha, sb_beta = st->beta, c0x = st->c0x, c0y = st->c0y;
+#pragma unroll
+        for (int k = 0; k < TPT; k += 2) {
+            const Philox4 ph = philox4x32_10((uint32_t)(t0 + k) >> 1, (uint32_t)st->c, (uint32_t)scan, (uint32_t)(scan >> 32),
+                                             (uint32_t)a.seed, (uint32_t)(a.seed >> 32));
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                nx[k + h] = 0; ny[k + h] = 0; ng[k + h] = 0;
+                bits[k + h] = 0u; cnt[k + h] = 0; mab[k + h] = __int_as_float(0x7f800000);
+                if (!skip && t0 + k + h < T) {
+                    live |= 1u << (k + h);
+                    int i, j;
+                    if (a.pairs != nullptr) explicit_pair(a, slot0 + q, (uint32_t)(t0 + k + h), (uint32_t)n, i, j);
+                    else pair_from_words(h ? ph.r[2] : ph.r[0], h ? ph.r[3] : ph.r[1], (uint32_t)n, i, j);
+                    const FastLine f = fast_pair_model(P[i], P[j]);
+                    // residual sum from the moments with its error bound -> the two keys the tie-break needs
+                    const double cp = fma(f.nx, c0x, fma(f.ny, c0y, f.negc));
+                    const double M = tile_moment_sum(f.nx, f.ny, cp, nn, st);
+                    const double e2 = tile_moment_err(cp, nn, A);
+                    const double E = fma(sb_beta, (M > 0.0 ? M : 0.0) + e2, sb_alpha) + e2;
+                    krow[(k + h) * ipc] = make_int2(key_down(M - E), key_up(M + E));
+                    // literal re-score wanted: coincident samples, a chunk outside the fast path's range, a non-finite
+                    // sum / bound - or (after the loop) a point too close to the threshold
+                    if (f.degenerate || force_lit || !(fabs(M) + E <= 1.7976931348623157e308)) flagm |= 1u << (k + h);
+                    if constexpr (F32) { nx[k + h] = (float)f.nx; ny[k + h] = (float)f.ny; ng[k + h] = (float)cp; }
+                    else { nx[k + h] = f.nx; ny[k + h] = f.ny; ng[k + h] = f.negc; }
+                }
+            }
+        }
+        const int n_eff = (skip || force_lit) ? 0 : n;
+        int k = 0, w = 0;
+        float flim;
+        if constexpr (F32) {
+            const float thf = (float)a.thr;
+            flim = st->bandf;
+            const float2 *Pf = sm.ptsf + (size_t)q * chunk_pad;
+            const float4 *Pf4 = reinterpret_cast<const float4 *>(Pf);     // two points per LDS.128 (chunk_pad is even)
+#define LSLAM_TILE_STEP2(XA, YA, XB, YB)                                                          \
+    {                                                                                             \
+        _Pragma("unroll") for (int k_ = 0; k_ < TPT; ++k_) {                                      \
+            const float fa_ = fabsf(fmaf((YA), ny[k_], fmaf((XA), nx[k_], ng[k_]))) - thf;        \
+            const float fb_ = fabsf(fmaf((YB), ny[k_], fmaf((XB), nx[k_], ng[k_]))) - thf;        \
+            bits[k_] = __funnelshift_l(__float_as_uint(fa_), bits[k_], 1);                        \
+            bits[k_] = __funnelshift_l(__float_as_uint(fb_), bits[k_], 1);                        \
+            mab[k_] = fminf(mab[k_], fminf(fabsf(fa_), fabsf(fb_)));                              \
+        }                                                                                         \
+    }
+            for (; k + 32 <= n_eff; k += 32, ++w) {
+#pragma unroll 4
+                for (int kk = 0; kk < 32; kk += 2) { const float4 pp = Pf4[(k + kk) >> 1]; LSLAM_TILE_STEP2(pp.x, pp.y, pp.z, pp.w); }
+#pragma unroll
+                for (int k_ = 0; k_ < TPT; ++k_) {
+                    const unsigned m = __brev(bits[k_]);              // bit j = point 32 w + j
+                    cnt[k_] += __popc(m);
+                    sm.mw[row0 + (w * TPT + k_) * ipc] = m;
+                }
+            }
+            const int rem = n_eff - k;
+            if (rem > 0) {
+                // the tail in pairs; an odd last point is paired with itself (its bit is shifted in twice, one shift is undone)
+                for (int kk = 0; kk < rem; kk += 2) {
+                    float4 pp;
+                    if (kk + 1 < rem) pp = Pf4[(k + kk) >> 1];
+                    else { const float2 p1 = Pf[k + kk]; pp = make_float4(p1.x, p1.y, p1.x, p1.y); }
+                    LSLAM_TILE_STEP2(pp.x, pp.y, pp.z, pp.w);
+                }
+                const int sh = rem & 1;
+#pragma unroll
+                for (int k_ = 0; k_ < TPT; ++k_) {
+                    const unsigned m = __brev((bits[k_] >> sh) << (32 - rem));
+                    cnt[k_] += __popc(m);
+                    sm.mw[row0 + (w * TPT + k_) * ipc] = m;
+                }
+            }
+#undef LSLAM_TILE_STEP2
+        } else {
+            const float thf = __int_as_float(__double2hiint(a.thr));
+            flim = tile_flag_limit(thf);
+#define LSLAM_TILE_STEP2(PA, PB)                                                                  \
+    {                                                                                             \
+        const double2 pa_ = (PA), pb_ = (PB);                                                     \
+        _Pragma("unroll") for (int k_ = 0; k_ < TPT; ++k_) {                                      \
+            const double sa_ = fma(pa_.y, ny[k_], fma(pa_.x, nx[k_], ng[k_]));                    \
+            const double sb_ = fma(pb_.y, ny[k_], fma(pb_.x, nx[k_], ng[k_]));                    \
+            const float fa_ = fabsf(__int_as_float(__double2hiint(sa_))) - thf;                   \
+            const float fb_ = fabsf(__int_as_float(__double2hiint(sb_))) - thf;                   \
+            bits[k_] = __funnelshift_l(__float_as_uint(fa_), bits[k_], 1);                        \
+            bits[k_] = __funnelshift_l(__float_as_uint(fb_), bits[k_], 1);                        \
+            mab[k_] = fminf(mab[k_], fminf(fabsf(fa_), fabsf(fb_)));                              \
+        }                                                                                         \
+    }
+            for (; k + 32 <= n_eff; k += 32, ++w) {
+#pragma unroll 4
+                for (int kk = 0; kk < 32; kk += 2) LSLAM_TILE_STEP2(P[k + kk], P[k + kk + 1]);
+#pragma unroll
+                for (int k_ = 0; k_ < TPT; ++k_) {
+                    const unsigned m = __brev(bits[k_]);              // bit j = point 32 w + j
+                    cnt[k_] += __popc(m);
+                    sm.mw[row0 + (w * TPT + k_) * ipc] = m;
+                }
+            }
+            const int rem = n_eff - k;
+            if (rem > 0) {
+                for (int kk = 0; kk < rem; kk += 2) {
+                    const int kb = kk + 1 < rem ? kk + 1 : kk;        // an odd last point is paired with itself
+                    LSLAM_TILE_STEP2(P[k + kk], P[k + kb]);
+                }
+                const int sh = rem & 1;
+#pragma unroll
+                for (int k_ = 0; k_ < TPT; ++k_) {
+                    const unsigned m = __brev((bits[k_] >> sh) << (32 - rem));
+                    cnt[k_] += __popc(m);
+                    sm.mw[row0 + (w * TPT + k_) * ipc] = m;
+                }
+            }
+#undef LSLAM_TILE_STEP2
+        }
+#pragma unroll
+        for (int k_ = 0; k_ < TPT; ++k_)
+            if (mab[k_] < flim && ((live >> k_) & 1u)) flagm |= 1u << k_;     // a point too close to the threshold
+        flagm &= live;
+
+        // flagged trials: literal score by the whole warp, on the spot; the literal mask replaces the fast one
+        unsigned fm = __ballot_sync(LSLAM_FULL_MASK, flagm != 0u);
+        unsigned n_relit = 0;
+        while (fm) {
+            const int src = __ffs((int)fm) - 1;
+            fm &= fm - 1;
+            const int fq = __shfl_sync(LSLAM_FULL_MASK, q, src), ftb = __shfl_sync(LSLAM_FULL_MASK, tb, src);
+            unsigned fl = __shfl_sync(LSLAM_FULL_MASK, flagm, src);
+            const TileSlot *fs = sm.slot + fq;
+            const double2 *FP = sm.pts + fs->off;
+            const int frow0 = (fq * W * TPT) * ipc + ftb;
+            while (fl) {
+                const int kf = __ffs((int)fl) - 1;
+                fl &= fl - 1;
+                int i, j, cl;
+                double sl;
+                trial_pair(a, slot0 + fq, fs->scan, (uint32_t)fs->c, (uint32_t)(ftb * TPT + kf), (uint32_t)fs->n, i, j);
+                warp_literal_score_strided(FP, fs->n, lit_pair_model(FP[i], FP[j]), a.thr, lane, cl, sl, sm.mw + frow0 + kf * ipc,
+                                           TPT * ipc);
+                ++n_relit;
+                if (lane == src) {
+                    krow[kf * ipc] = make_int2(key_down(sl), key_up(sl));
+                    exact |= 1u << kf;
+#pragma unroll
+                    for (int k_ = 0; k_ < TPT; ++k_)
+                        if (k_ == kf) cnt[k_] = cl;
+                }
+            }
+        }
+        if (lane == 0 && n_relit) atomicAdd(a.counters + 0, (unsigned long long)n_relit);
+
+        // chunk-wide maximum: count, then the smallest upper bound of the literal residual sum
+        unsigned long long best = 0ull;
+#pragma unroll
+        for (int k_ = 0; k_ < TPT; ++k_) {
+            if ((live >> k_) & 1u) {
+                const unsigned long long key = ((unsigned long long)(unsigned)cnt[k_] << 32) | (unsigned)(0x7fffffff - krow[k_ * ipc].y);
+                best = best > key ? best : key;
+            }
+        }
+        if (live) atomicMax(&st->key, best);
+    }
+    __syncthreads();
+
+    // ================= candidates: trials tied on the maximal count whose lower bound reaches the smallest upper bound
+    if (!skip) {
+        const unsigned long long key = st->key;
+        const int mx = (int)(key >> 32), minhi = 0x7fffffff - (int)(unsigned)key;
+        if (tb == 0) {
+            st->mx = mx;
+            if (mx < 2) st->status = kStatusNoModel;              // upstream's final estimate() needs 2 points
+        }
+        if (mx >= 2) {
+            unsigned cm = 0;
+#pragma unroll
+            for (int k_ = 0; k_ < TPT; ++k_)
+                if (((live >> k_) & 1u) && cnt[k_] == mx && krow[k_ * ipc].x <= minhi) cm |= 1u << k_;
+            while (cm) {                                          // rare: about one trial per chunk
+                const int kc = __ffs((int)cm) - 1;
+                cm &= cm - 1;
+                const int pos = atomicAdd(&st->ncand, 1);
+                if (pos < kMaxCand) {
+                    int i, j;
+                    trial_pair(a, slot0 + q, st->scan, (uint32_t)st->c, (uint32_t)(t0 + kc), (uint32_t)n, i, j);
+                    st->cand_t[pos] = t0 + kc; st->cand_i[pos] = i; st->cand_j[pos] = j;
+                    if ((exact >> kc) & 1u) atomicOr(&st->cand_exact, 1 << pos);
+                    if (pos == 0) { st->mask_base = row0 + kc * ipc; st->mask_stride = TPT * ipc; }
+                }
+            }
+        }
+    }
+    __syncthreads();
+
+    // ================= decide (only where the literal formula is needed) + refit + stores: LG lanes per slot ====
+    constexpr int SPW = 32 / LG;                                  // slots per warp
+    for (int qw = warp * SPW; qw < nsl; qw += nwarps * SPW) {
+        // ---- literal tie-break, a warp per slot: several candidates, or the caller wants the residual sum ----
+        for (int qq = qw; qq < qw + SPW && qq < nsl; ++qq) {
+            TileSlot *s2 = sm.slot + qq;
+            if (s2->status != 0) continue;
+            const int ncand = s2->ncand;
+            if (ncand == 1 && a.ssum == nullptr) {
+                if (lane == 0) {
+                    s2->best_t = s2->cand_t[0]; s2->best_i = s2->cand_i[0]; s2->best_j = s2->cand_j[0];
+                    s2->best_ss = __longlong_as_double(0x7ff8000000000000LL);
+                }
+                continue;
+            }
+            const double2 *P2 = sm.pts + s2->off;
+            uint32_t *wt = sm.wtmp + (size_t)warp * W;
+            uint32_t *mq = sm.mw + sm.smask0 + qq * W;
+            bool fault = false;
+            int best_t = -1, best_i = -1, best_j = -1;
+            double best_ss = __longlong_as_double(0x7ff0000000000000LL);
+            if (ncand <= kMaxCand) {
+                // candidates were appended in no particular order: smallest sum wins, the earlier trial on a tie -
+                // the sequential accept rule (first best in trial order)
+                for (int ci = 0; ci < ncand; ++ci) {
+                    int cl;
+                    double sl;
+                    const int ti = s2->cand_t[ci], ii = s2->cand_i[ci], jj = s2->cand_j[ci];
+                    warp_literal_score(P2, s2->n, lit_pair_model(P2[ii], P2[jj]), a.thr, lane, cl, sl, wt);
+                    __syncwarp();
+                    if (cl != s2->mx) fault = true;
+                    if (sl < best_ss || (sl == best_ss && ti < best_t)) {
+                        best_ss = sl; best_t = ti; best_i = ii; best_j = jj;
+                        for (int w = lane; w * 32 < s2->n; w += 32) mq[w] = wt[w];
+                    }
+                    __syncwarp();
+                }
+                if (lane == 0 && ncand > 1) atomicAdd(a.counters + 1, (unsigned long long)(ncand - 1));
+            }
+            if (lane == 0) {
+                s2->best_t = best_t; s2->best_i = best_i; s2->best_j = best_j; s2->best_ss = best_ss;
+                s2->mask_base = sm.smask0 + qq * W; s2->mask_stride = 1;
+            }
+            __syncwarp();
+            if (fault || best_t < 0) {
+                // more candidates than the list holds (e.g. noise-free collinear data), or a fast count that disagrees
+                // with the literal one (error bound violated - never observed, counted): the exact sequential rule
+                if (lane == 0 && fault) atomicAdd(a.counters + 2, 1ULL);
+                slot_exact_fallback(a, s2, P2, mq, wt, lane);
+            }
+        }
+        __syncwarp();
+
+        // ---- refit + outputs: LineModelND.estimate(data[inliers]) as the principal axis of the 2x2 scatter,
+        //      accumulated relative to the winner's first sample point (an inlier, so the shift is benign) ----
+        const int qr = qw + lane / LG, r = lane % LG;
+        const bool act = qr < nsl;
+        const TileSlot *s3 = sm.slot + (act ? qr : qw);
+        const bool ok = act && s3->status == 0;
+        const double2 *P3 = sm.pts + s3->off;
+        const uint32_t *mrow = sm.mw + s3->mask_base;
+        const int ms = s3->mask_stride, n3 = s3->n;
+        double sx = 0.0, sy = 0.0, sxx = 0.0, sxy = 0.0, syy = 0.0;
+        double2 p0 = make_double2(0.0, 0.0);
+        if (ok) {
+            p0 = P3[s3->best_i];
+            for (int k = r; k < n3; k += LG) {
+                if ((mrow[(k >> 5) * ms] >> (k & 31)) & 1u) {
+                    const double2 p = P3[k];
+                    const double dx = p.x - p0.x, dy = p.y - p0.y;
+                    sx += dx; sy += dy;
+                    sxx = fma(dx, dx, sxx); sxy = fma(dx, dy, sxy); syy = fma(dy, dy, syy);
+                }
+            }
+        }
+#pragma unroll
+        for (int o = LG / 2; o >= 1; o >>= 1) {
+            sx += __shfl_xor_sync(LSLAM_FULL_MASK, sx, o);
+            sy += __shfl_xor_sync(LSLAM_FULL_MASK, sy, o);
+            sxx += __shfl_xor_sync(LSLAM_FULL_MASK, sxx, o);
+            sxy += __shfl_xor_sync(LSLAM_FULL_MASK, sxy, o);
+            syy += __shfl_xor_sync(LSLAM_FULL_MASK, syy, o);
+        }
+        if (act) {
+            const long long s = slot0 + qr;
+            const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+            double out = qnan;                                   // lane r stores element r of the line record
+            if (ok) {
+                const double rm = 1.0 / (double)s3->mx;
+                const double mdx = sx * rm, mdy = sy * rm;
+                const double ox = p0.x + mdx, oy = p0.y + mdy;
+                double dx, dy;
+                principal_axis_rsqrt(fma(-sx, mdx, sxx), fma(-sx, mdy, sxy), fma(-sy, mdy, syy), dx, dy);
+                int last = 0;
+                for (int w = (n3 - 1) >> 5; w >= 0; --w) {
+                    const unsigned mw_ = mrow[w * ms];
+                    if (mw_) { last = w * 32 + 31 - __clz((int)mw_); break; }
+                }
+                // ransac_functions.py:26-30 (no guard for dir_x == 0, like the reference)
+                const double sl = __ddiv_rn(dy, dx);
+                const double ic = __dsub_rn(oy, __dmul_rn(sl, ox));
+                const double tipx = P3[last].x;
+                const double tipy = __dadd_rn(__dmul_rn(tipx, sl), ic);
+                out = r == 0 ? sl : r == 1 ? ic : r == 2 ? ox : r == 3 ? oy : r == 4 ? dx : r == 5 ? dy : r == 6 ? tipx : tipy;
+            }
+            static_assert(LG == 8, "one lane per element of the line record");
+            a.line[s * 8 + r] = out;
+            if (r == 0) a.ninl[s] = ok ? s3->mx : (s3->status == 0x7fffffff ? 0 : s3->status);
+            if (r == 1) a.win_trial[s] = ok ? s3->best_t : -1;
+            if (r == 2) a.win_pair[2 * s] = ok ? s3->best_i : -1;
+            if (r == 3) a.win_pair[2 * s + 1] = ok ? s3->best_j : -1;
+            if (r == 4 && a.ssum != nullptr) a.ssum[s] = ok ? s3->best_ss : qnan;
+        }
+        // inlier masks of this warp's slots: consecutive slots are consecutive in global memory
+        const int nq = (nsl - qw) < SPW ? (nsl - qw) : SPW;
+        for (int i = lane; i < nq * W; i += 32) {
+            const int qi = i / W, w = i - qi * W;
+            const TileSlot *s4 = sm.slot + qw + qi;
+            a.mask[(slot0 + qw) * W + i] = (s4->status == 0 && w * 32 < s4->n) ? sm.mw[s4->mask_base + w * s4->mask_stride] : 0u;
+        }
+    }
+}
+
+} // namespace lslam

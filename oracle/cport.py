@@ -39,8 +39,9 @@ def _p(a, ty):
 
 
 def ransac_lines(xy, npts=None, chunk=100, trials=100, thr=20.0, seed=0, scan_base=0,
-                 nthreads=0):
-    """Batched C oracle; same argument meaning and output layout as lslam_ransac_lines."""
+                 nthreads=0, pairs=None):
+    """Batched C oracle; same argument meaning and output layout as lslam_ransac_lines
+    (pairs: None = Philox sampler, or [B, C, trials, 2] int32 explicit sample pairs)."""
     xy = np.ascontiguousarray(xy, dtype=np.float64)
     B, N, _ = xy.shape
     C = (N + chunk - 1) // chunk
@@ -55,10 +56,13 @@ def ransac_lines(xy, npts=None, chunk=100, trials=100, thr=20.0, seed=0, scan_ba
         "ssum": np.empty((B, C), np.float64),
         "inl_mask": np.empty((B, C, W), np.uint32),
     }
-    rc = lib().oracle_ransac_lines(
+    if pairs is not None:
+        pairs = np.ascontiguousarray(pairs, dtype=np.int32)
+        assert pairs.shape == (B, C, trials, 2), pairs.shape
+    rc = lib().oracle_ransac_lines_pairs(
         _p(xy, c_double_p), _p(npts, c_int32_p), ctypes.c_int32(B), ctypes.c_int32(N),
         ctypes.c_int32(chunk), ctypes.c_int32(trials), ctypes.c_double(thr),
-        ctypes.c_uint64(seed), ctypes.c_uint64(scan_base),
+        ctypes.c_uint64(seed), ctypes.c_uint64(scan_base), _p(pairs, c_int32_p),
         _p(out["line"], c_double_p), _p(out["ninl"], c_int32_p),
         _p(out["win_trial"], c_int32_p), _p(out["win_pair"], c_int32_p),
         _p(out["ssum"], c_double_p), _p(out["inl_mask"], c_uint32_p),

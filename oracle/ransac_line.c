@@ -123,16 +123,34 @@ static void refit(const double *p, int n, const uint32_t *mask, int cnt, double 
 
 /* One chunk: the ransac loop + refit + slope/intercept/tip (ransac_functions.py:23-30).
  * Returns inlier count (>= 2) or -3 (LSLAM_ERR_NO_MODEL).  line = a,b,ox,oy,dx,dy,tipx,tipy */
+/* pairs: NULL = the Philox sampler, else [trials][2] explicit sample indices (clamped into the chunk), e.g. what a
+ * seeded upstream run's random_state.choice(n, 2, replace=False) drew. */
+int oracle_ransac_chunk_pairs(const double *p, int n, int trials, double thr, uint64_t seed,
+                              uint64_t scan, uint32_t chunk, const int32_t *pairs, double line[8],
+                              int32_t *win_trial, int32_t win_pair[2], double *ssum_out, uint32_t *mask);
 int oracle_ransac_chunk(const double *p, int n, int trials, double thr, uint64_t seed,
                         uint64_t scan, uint32_t chunk, double line[8], int32_t *win_trial,
                         int32_t win_pair[2], double *ssum_out, uint32_t *mask)
+{
+    return oracle_ransac_chunk_pairs(p, n, trials, thr, seed, scan, chunk, NULL, line, win_trial, win_pair, ssum_out, mask);
+}
+
+int oracle_ransac_chunk_pairs(const double *p, int n, int trials, double thr, uint64_t seed,
+                              uint64_t scan, uint32_t chunk, const int32_t *pairs, double line[8],
+                              int32_t *win_trial, int32_t win_pair[2], double *ssum_out, uint32_t *mask)
 {
     int best_n = 0, win = -1, wi = -1, wj = -1;
     double best_ssum = INFINITY, bm[4] = { 0, 0, 0, 0 };
     for (int t = 0; t < trials; ++t) {
         int32_t i, j;
         double m[4], ssum;
-        sample_pair(seed, scan, chunk, (uint32_t)t, (uint32_t)n, &i, &j);
+        if (pairs) {
+            i = pairs[2 * t]; j = pairs[2 * t + 1];
+            i = i < 0 ? 0 : (i > n - 1 ? n - 1 : i);
+            j = j < 0 ? 0 : (j > n - 1 ? n - 1 : j);
+        } else {
+            sample_pair(seed, scan, chunk, (uint32_t)t, (uint32_t)n, &i, &j);
+        }
         pair_model(p, i, j, m);
         int cnt = score(p, n, m, thr, &ssum, NULL);
         if (cnt > best_n || (cnt == best_n && ssum < best_ssum)) {
@@ -166,10 +184,26 @@ int oracle_ransac_chunk(const double *p, int n, int trials, double thr, uint64_t
  * xy[B,N,2]; npts[B] or NULL (all N); C = ceil(N/chunk) chunk slots per scan; a slot is
  * processed when it is a full chunk or a remainder of more than 2 points
  * (functions.py:71), otherwise ninl = 0 / win_trial = -1. */
+int oracle_ransac_lines_pairs(const double *xy, const int32_t *npts, int32_t B, int32_t N,
+                              int32_t chunk, int32_t trials, double thr, uint64_t seed,
+                              uint64_t scan_base, const int32_t *pairs, double *line, int32_t *ninl,
+                              int32_t *win_trial, int32_t *win_pair, double *ssum, uint32_t *inl_mask,
+                              int32_t nthreads);
 int oracle_ransac_lines(const double *xy, const int32_t *npts, int32_t B, int32_t N,
                         int32_t chunk, int32_t trials, double thr, uint64_t seed,
                         uint64_t scan_base, double *line, int32_t *ninl, int32_t *win_trial,
                         int32_t *win_pair, double *ssum, uint32_t *inl_mask, int32_t nthreads)
+{
+    return oracle_ransac_lines_pairs(xy, npts, B, N, chunk, trials, thr, seed, scan_base, NULL, line, ninl, win_trial,
+                                     win_pair, ssum, inl_mask, nthreads);
+}
+
+/* pairs: NULL or [B,C,trials,2] (include/lslam.h lslam_ransac_lines) */
+int oracle_ransac_lines_pairs(const double *xy, const int32_t *npts, int32_t B, int32_t N,
+                              int32_t chunk, int32_t trials, double thr, uint64_t seed,
+                              uint64_t scan_base, const int32_t *pairs, double *line, int32_t *ninl,
+                              int32_t *win_trial, int32_t *win_pair, double *ssum, uint32_t *inl_mask,
+                              int32_t nthreads)
 {
     int C = (N + chunk - 1) / chunk, W = (chunk + 31) / 32;
     if (nthreads <= 0) {
@@ -192,9 +226,10 @@ int oracle_ransac_lines(const double *xy, const int32_t *npts, int32_t B, int32_
             ssum[bc] = NAN;
             continue;
         }
-        ninl[bc] = oracle_ransac_chunk(xy + ((size_t)b * N + s) * 2, n, trials, thr, seed,
-                                       scan_base + (uint64_t)b, (uint32_t)c, line + bc * 8,
-                                       win_trial + bc, win_pair + 2 * bc, ssum + bc, mk);
+        ninl[bc] = oracle_ransac_chunk_pairs(xy + ((size_t)b * N + s) * 2, n, trials, thr, seed,
+                                             scan_base + (uint64_t)b, (uint32_t)c,
+                                             pairs ? pairs + (size_t)bc * trials * 2 : NULL, line + bc * 8,
+                                             win_trial + bc, win_pair + 2 * bc, ssum + bc, mk);
     }
     return 0;
 }

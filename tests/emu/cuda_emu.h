@@ -43,12 +43,14 @@ struct dim3 {
 struct alignas(16) double2 { double x, y; };
 struct alignas(8) float2 { float x, y; };
 struct alignas(8) int2 { int x, y; };
+struct alignas(16) float4 { float x, y, z, w; };
 struct alignas(8) uint2 { unsigned x, y; };
 struct alignas(16) uint4 { unsigned x, y, z, w; };
 struct alignas(16) int4 { int x, y, z, w; };
 static inline double2 make_double2(double x, double y) { return double2{x, y}; }
 static inline float2 make_float2(float x, float y) { return float2{x, y}; }
 static inline int2 make_int2(int x, int y) { return int2{x, y}; }
+static inline float4 make_float4(float x, float y, float z, float w) { return float4{x, y, z, w}; }
 static inline uint2 make_uint2(unsigned x, unsigned y) { return uint2{x, y}; }
 static inline uint4 make_uint4(unsigned x, unsigned y, unsigned z, unsigned w) { return uint4{x, y, z, w}; }
 
@@ -225,6 +227,11 @@ static inline int atomicMax(int *p, int v) {
     while (old < v && !__atomic_compare_exchange_n(p, &old, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) {}
     return old;
 }
+static inline unsigned long long atomicMax(unsigned long long *p, unsigned long long v) {
+    unsigned long long old = __atomic_load_n(p, __ATOMIC_SEQ_CST);
+    while (old < v && !__atomic_compare_exchange_n(p, &old, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) {}
+    return old;
+}
 static inline unsigned atomicOr(unsigned *p, unsigned v) { return __atomic_fetch_or(p, v, __ATOMIC_SEQ_CST); }
 static inline int atomicOr(int *p, int v) { return __atomic_fetch_or(p, v, __ATOMIC_SEQ_CST); }
 
@@ -233,7 +240,7 @@ typedef int cudaError_t;
 typedef void *cudaStream_t;
 typedef struct { std::chrono::steady_clock::time_point t; } *cudaEvent_t;
 enum { cudaSuccess = 0, cudaErrorInvalidValue = 1 };
-enum cudaDeviceAttr { cudaDevAttrMultiProcessorCount, cudaDevAttrMaxSharedMemoryPerBlockOptin,
+enum cudaDeviceAttr { cudaDevAttrMultiProcessorCount, cudaDevAttrMaxSharedMemoryPerBlockOptin, cudaDevAttrMaxSharedMemoryPerMultiprocessor,
                       cudaDevAttrComputeCapabilityMajor, cudaDevAttrComputeCapabilityMinor };
 enum cudaFuncAttribute { cudaFuncAttributeMaxDynamicSharedMemorySize };
 enum cudaMemcpyKind { cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpyDeviceToDevice, cudaMemcpyDefault };
@@ -244,6 +251,7 @@ static inline cudaError_t cudaDeviceGetAttribute(int *v, cudaDeviceAttr a, int) 
     switch (a) {
     case cudaDevAttrMultiProcessorCount: *v = 4; break;          // keeps emulated grids small
     case cudaDevAttrMaxSharedMemoryPerBlockOptin: *v = 232448; break;
+    case cudaDevAttrMaxSharedMemoryPerMultiprocessor: *v = 233472; break;
     case cudaDevAttrComputeCapabilityMajor: *v = 10; break;
     case cudaDevAttrComputeCapabilityMinor: *v = 0; break;
     }

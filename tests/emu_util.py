@@ -44,7 +44,7 @@ def ptr(a):
 
 
 def emu_ransac_lines(xy, npts=None, chunk=100, trials=100, thr=20.0, seed=0, scan_base=0, handle=None,
-                     want_ssum=None):
+                     want_ssum=None, pairs=None):
     """lslam_ransac_lines on the emulated library with NumPy buffers standing in for device
     memory.  Same outputs as oracle.cport.ransac_lines."""
     h = handle or emu_handle()
@@ -66,7 +66,8 @@ def emu_ransac_lines(xy, npts=None, chunk=100, trials=100, thr=20.0, seed=0, sca
         del out["ssum"]
     h.ransac_lines(ptr(xy), ptr(npts), B, N, chunk, trials, thr, seed, scan_base,
                    ptr(out["line"]), ptr(out["ninl"]), ptr(out["win_trial"]), ptr(out["win_pair"]),
-                   ptr(out.get("ssum")), ptr(out["inl_mask"]))
+                   ptr(out.get("ssum")), ptr(out["inl_mask"]),
+                   pairs=ptr(None if pairs is None else np.ascontiguousarray(pairs, dtype=np.int32)))
     return out
 
 

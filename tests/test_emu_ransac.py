@@ -9,8 +9,8 @@ from lidar_slam_b200 import synth
 from tests.parity_util import assert_ransac_equal
 
 
-@pytest.fixture(params=[(2, True, 0), (1, True, 1), (1, False, 1), (1, True, 2), (1, False, 2)],
-                ids=["ws", "phased", "phased-nossum", "phased-f32", "phased-f32-nossum"], autouse=True)
+@pytest.fixture(params=[(2, True, 0), (1, True, 0), (1, False, 0), (3, True, 0), (3, False, 0), (3, True, 1), (3, False, 1)],
+                ids=["ws", "phased", "phased-nossum", "tile", "tile-nossum", "tile-f64", "tile-f64-nossum"], autouse=True)
 def ransac_kernel(request, emu):
     """Every test runs on both RANSAC kernels: 2 = warp-specialised persistent (csrc/ransac_ws.cuh),
     1 = phase-structured (csrc/ransac.cuh) - the latter also without the optional residual-sum output,
