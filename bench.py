@@ -38,9 +38,16 @@ E2E_SLICES = 16                                    # slices of the overlapped ho
 PHE_PER_SCAN = BEAMS * TRIALS                      # point-hypothesis evaluations per scan
 FLOP_PER_PHE = 8                                   # algorithmic fp64 flop per PHE
 BYTES_PER_SCAN = BEAMS * 16 + 4 * 96               # 5,760 in + 4 x 96 out = 6,144 B
-# DRAM bytes per scan of the RANSAC kernel from the ncu --set full capture of 262,144 scans
-# (profiles/r01f_ransac_c2_ncu_summary.txt: 1.5106 GB read + 0.1072 GB written)
-NCU_DRAM_BYTES_PER_SCAN = (1.510555e9 + 107.172864e6) / 262144
+# DRAM bytes per scan of the RANSAC kernel: profiles/ransac_traffic.json, written from the latest ncu --set full
+# capture of the CURRENT kernel (tools/ncu_traffic.py); None when the file is absent
+
+
+def ncu_traffic():
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "ransac_traffic.json")))
+        return (float(t["dram_bytes_read"]) + float(t["dram_bytes_write"])) / float(t["scans"]), t
+    except Exception:
+        return None, None
 
 
 def parse():
@@ -54,7 +61,11 @@ def parse():
     p.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-aug", action="store_true", help="skip the configs[3] leg (augmented-state UKF)")
-    p.add_argument("--aug-filters", type=int, default=1024)
+    p.add_argument("--aug-filters", type=int, default=10000, help="configs[3]: 10,000 filters")
+    p.add_argument("--no-legs", action="store_true", help="skip the configs[1] / configs[2] RANSAC-only legs and the OLS leg")
+    p.add_argument("--no-points", action="store_true", help="skip the e2e leg that also returns the projected inlier points")
+    p.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                   help="weak: --scans per GPU (default, the headline); strong: --scans in total, split over the GPUs")
     p.add_argument("--slices", type=int, default=0, help="slices of the overlapped host path (0 = default)")
     p.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                    help="N > 1 result gather: fused into the UKF kernel over peer memory, or an NCCL all_gather")
@@ -117,6 +128,76 @@ class ClockSampler:
 
 
 # ---- CPU legs (the only place bench.py touches oracle/) -----------------------------------------
+def host_threads():
+    """All the host threads this process may use - set explicitly, because torchrun exports OMP_NUM_THREADS=1 to its
+    workers and the reference arm would otherwise be a one-thread run at N > 1."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except Exception:
+        n = os.cpu_count() or 1
+    os.environ["OMP_NUM_THREADS"] = str(n)
+    try:
+        from oracle import cport
+        cport.set_threads(n)
+        n = cport.max_threads()
+    except Exception:
+        pass
+    return n
+
+
+def numpy_rates(n1=24, npool=None):
+    """The same job in Python/NumPy (oracle/numpy_pipeline.py: per-trial NumPy calls like skimage / filterpy make), on
+    one core and on a multiprocessing.Pool of all cores.  Returns dict."""
+    import multiprocessing as mp
+    import numpy as np
+    from lidar_slam_b200 import synth
+    from oracle import numpy_pipeline as npp
+    cores = len(os.sched_getaffinity(0))
+    xy = synth.random_room_scans(n1, seed=11)
+    n, dt = npp.run_scans((xy, 0, 0))
+    out = {"numpy_1core": {"value": n / dt, "unit": "scans/s", "cores": 1, "kind": "port (Python/NumPy restatement)",
+                           "sample": "%d scans, %.1f s" % (n, dt)}}
+    npool = npool or 12 * cores
+    xy = synth.random_room_scans(npool, seed=12)
+    parts = [(xy[i::cores], i, 0) for i in range(cores)]
+    try:
+        with mp.get_context("fork").Pool(cores) as pool:
+            t0 = time.perf_counter()
+            done = pool.map(npp.run_scans, parts)
+            wall = time.perf_counter() - t0
+        # the pool's wall time includes each worker's (untimed-in-the-other-arms) map set-up: use the slowest worker's own clock
+        slow = max(d for _, d in done)
+        out["numpy_pool"] = {"value": sum(k for k, _ in done) / slow, "unit": "scans/s", "cores": cores,
+                             "kind": "port (Python/NumPy restatement, multiprocessing.Pool)",
+                             "sample": "%d scans, slowest worker %.1f s (pool wall %.1f s)" % (npool, slow, wall)}
+    except Exception as e:
+        out["numpy_pool"] = {"unavailable": str(e)[:100]}
+    return out
+
+
+def sklearn_ols_rate(nwin=300):
+    """R7 as the reference runs it (line_detection.py:57-58): sklearn RANSACRegressor(residual_threshold=3).fit per
+    50-point window, timed as-is."""
+    import numpy as np
+    try:
+        from sklearn.linear_model import RANSACRegressor
+    except Exception as e:
+        return {"unavailable": str(e)[:100]}
+    from lidar_slam_b200 import synth
+    xy = synth.random_room_scans((nwin * 50 + 359) // 360, seed=13).reshape(-1, 2)[:nwin * 50].reshape(nwin, 50, 2)
+    t0 = time.perf_counter()
+    ok = 0
+    for w in xy:
+        try:
+            RANSACRegressor(residual_threshold=3, random_state=0).fit(w[:, :1], w[:, 1])
+            ok += 1
+        except ValueError:
+            pass
+    dt = time.perf_counter() - t0
+    return {"value": nwin / dt, "unit": "windows/s", "cores": 1, "kind": "reference (scikit-learn as-is)",
+            "sample": "%d windows of 50 points, %.1f s, %d fitted" % (nwin, dt, ok)}
+
+
 def cpu_pipeline_rate(nscans, seed=0):
     """Scans/s of the CPU restatement of the same job (oracle/: express-packet decode + polar->cartesian,
     RANSAC, association and UKF in C, OpenMP over scans, all host threads) on `nscans` synthetic
@@ -127,7 +208,7 @@ def cpu_pipeline_rate(nscans, seed=0):
     from oracle import cport
     from tests import pipeline_util
     pk = synth.random_room_express(nscans, PACKETS, seed=seed)
-    threads = cport.max_threads()
+    threads = host_threads()
     xy, _, _ = cport.express_to_cart(pk, BEAMS)
     r0 = cport.ransac_lines(xy)                                    # untimed set-up: the known map
     tables = pipeline_util.map_from_lines(r0["line"], r0["ninl"], TABLE_M)
@@ -245,10 +326,67 @@ def aug_leg(eng, F, steps, fp64_peak, L=200):
                                                           % (fp64_peak * 1e12 / flop / 1e3 if fp64_peak > 0 else 0.0)}}}
 
 
+def l2_flush_buffer(torch, dev):
+    return torch.empty(256 << 20, dtype=torch.uint8, device=dev)          # > the 126 MB L2
+
+
+def ransac_leg(eng, name, B, beams, chunk, trials, steps, fp64_peak, flush):
+    """BASELINE.json configs[1] / configs[2]: RANSAC line extraction only (lslam_ransac_lines with its default kernel
+    choice and knobs), scans resident in HBM.  These batches are smaller than L2, so L2 is flushed (a 256 MB memset)
+    before every timed launch; each launch is timed on its own with CUDA events."""
+    import torch
+    xy = eng.synth_scans(B, beams=beams, seed=5)
+    out = eng.alloc_ransac_out(B, beams, chunk, ssum=False)
+    C = (beams + chunk - 1) // chunk
+    ms = []
+    for r in range(steps + 3):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        eng.ransac_lines(xy, chunk=chunk, trials=trials, thr=THR, seed=0, out=out)
+        e1.record()
+        torch.cuda.synchronize()
+        if r >= 3:
+            ms.append(e0.elapsed_time(e1))
+    t = statistics.median(ms)
+    phe = B * beams * trials
+    tf = phe * FLOP_PER_PHE / (t * 1e-3) * 1e-12
+    ok = int((out["ninl"] >= 2).sum().item())
+    return {"workload": "%s: %d scans x %d beams, chunk %d (%d lines per scan), %d hypotheses per line, RANSAC + refit only"
+                        % (name, B, beams, chunk, C, trials),
+            "kernel_ms": t, "scans_per_s": B / (t * 1e-3), "hyps_per_s": B * C * trials / (t * 1e-3), "lines_found": ok,
+            "l2": "flushed before every launch (input %.1f MB < 126 MB L2)" % (B * beams * 16 / 1e6),
+            "roofline": {"bound": "fp64-issue", "achieved": tf, "peak": fp64_peak, "unit": "TFLOP/s",
+                         "frac": tf / fp64_peak if fp64_peak > 0 else None,
+                         "algorithmic_flop": phe * FLOP_PER_PHE,
+                         "hbm_gbs": (B * beams * 16 + B * C * 96) / (t * 1e-3) * 1e-9}}
+
+
+def ols_leg(eng, steps, flush, B=65536):
+    """R7 / N4 (line_detection.py:51-73): every 50-point window of B scans through lslam_ransac_ols."""
+    import torch
+    xy = eng.synth_scans(B, seed=6)
+    ms = []
+    for r in range(steps + 2):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        o = eng.ransac_ols(xy, window=50, thr=3.0)
+        e1.record()
+        torch.cuda.synchronize()
+        if r >= 2:
+            ms.append(e0.elapsed_time(e1))
+    t = statistics.median(ms)
+    nwin = B * 8
+    return {"workload": "line_detection.py flavour: %d windows of <= 50 points, RANSACRegressor(residual_threshold=3) semantics" % nwin,
+            "kernel_ms": t, "windows_per_s": nwin / (t * 1e-3), "mean_trials": float(o["n_trials"].float().mean().item()),
+            "hbm_gbs": (B * 360 * 16 + nwin * 84) / (t * 1e-3) * 1e-9}
+
+
 def workload_config(args, world):
     return {"workload": "BASELINE.json configs[4]: 1M synthetic 360-beam scans end-to-end "
                         "(RANSAC 4 chunks x 100 trials + association M=8 + UKF n=3) per GPU",
-            "scans_per_gpu_per_step": args.scans, "beams": BEAMS, "chunk": CHUNK, "trials": TRIALS,
+            "scans_per_gpu_per_step": args.scans if args.scaling == "weak" else args.scans // world, "beams": BEAMS, "chunk": CHUNK, "trials": TRIALS,
             "threshold_mm": THR, "table_capacity": TABLE_M,
             "input": "synthetic sensor: %d express packets (84 B, 32 measures) per revolution, first %d measures "
                      "form the scan; `value` starts from the decoded points resident in HBM, `e2e` and the CPU "
@@ -280,7 +418,7 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     eng = batch.Engine(local)
-    S = args.scans
+    S = args.scans if args.scaling == "weak" else args.scans // world
     pipe = pipeline.ScanPipeline(eng, S, beams=BEAMS, chunk=CHUNK, trials=TRIALS, thr=THR,
                                  table_capacity=TABLE_M, seed=0, scan_base=rank * S)
     # untimed set-up: the synthetic sensor's bytes, decoded once; xy stays resident in HBM
@@ -400,10 +538,111 @@ def main():
         e2e_xy["input"] = "cartesian float64 points, 5760 B per scan"
         del xy_h
 
+    # ---- the same end to end INCLUDING what landmark_extraction itself returns: the projected inlier points
+    #      (ransac_functions.py:28,46-55) compacted on the device (lslam_project_inliers) and copied to the host
+    e2e_points = None
+    if not args.no_e2e and not args.no_points and world == 1:
+        pk_h = pipe.alloc_host_io("packets", PACKETS)
+        pk_h.copy_(pk)
+        torch.cuda.synchronize()
+        for _ in range(2):
+            pipe.step_host(pk_h, slices=E2E_SLICES, points=True)
+        torch.cuda.synchronize()
+        n0e = eng.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        nsteps = max(2, args.steps // 2)
+        e0.record()
+        rows = 0
+        for _ in range(nsteps):
+            out_h = pipe.step_host(pk_h, slices=E2E_SLICES, points=True)
+            torch.cuda.current_stream().synchronize()
+            rows = sum(int(v.shape[0]) for v in out_h["points"])
+            _ = float(out_h["points"][0][0, 0])
+        e1.record()
+        torch.cuda.synchronize()
+        ems = e0.elapsed_time(e1)
+        h2d, d2h = pipe.io_bytes(pk_h)
+        e2e_points = {"value": S * nsteps / (ems * 1e-3), "unit": "scans/s", "h2d_bytes_per_step": h2d,
+                      "d2h_bytes_per_step": d2h + rows * 16 + 8 * E2E_SLICES, "ms_per_step": ems / nsteps, "slices": E2E_SLICES,
+                      "gpu_launches": eng.launch_count() - n0e, "points_per_step": rows,
+                      "input": "express packets in; per-scan results AND every chunk's projected inlier points out"}
+        del pk_h
+
+    # ---- N > 1: the fused gather's records against an NCCL all_gather of the same step (once, untimed)
+    gather_check = None
+    if world > 1 and pipe.peer_gather is not None:
+        res = pipe.step(xy)
+        pipe.peer_gather.barrier()
+        want = ldist.ResultGather()(res)
+        torch.cuda.synchronize()
+        got = pipe.peer_gather.result()
+        same = (torch.equal(got["state"][..., :3].contiguous().view(torch.uint8), want["x"].view(torch.uint8)) and
+                torch.equal(got["state"][..., 3:].contiguous().view(torch.uint8), want["P"].reshape(world, S, 9).view(torch.uint8)) and
+                torch.equal(got["ids"], want["match_id"]))
+        t = torch.tensor([1.0 if same else 0.0], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        gather_check = "bit-identical to nccl all_gather on every rank" if t.item() == 1.0 else "MISMATCH"
+
+    # ---- N > 1, weak run: the same job as STRONG scaling beside it (configs[4] as written: 1M scans in total)
+    strong = None
+    if world > 1 and args.scaling == "weak":
+        S2 = args.scans // world
+        pipe2 = pipeline.ScanPipeline(eng, S2, beams=BEAMS, chunk=CHUNK, trials=TRIALS, thr=THR, table_capacity=TABLE_M,
+                                      seed=0, scan_base=rank * S2)
+        xy2 = xy[:S2]
+        r2 = eng.ransac_lines(xy2, chunk=CHUNK, trials=TRIALS, thr=THR, seed=0, scan_base=rank * S2, out=pipe2.rout)
+        pipe2.install_map_from_lines(r2["line"], r2["ninl"])
+        pipe2.ukf["u"].fill_(1.0)
+        g2 = None
+        if pipe.peer_gather is not None:
+            try:
+                g2 = pipe2.enable_peer_gather()
+            except Exception:
+                g2 = None
+        gat2 = ldist.ResultGather()
+
+        def step2():
+            r = pipe2.step(xy2)
+            if g2 is not None:
+                g2.barrier()
+            else:
+                gat2(r)
+        for _ in range(5):
+            step2()
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        nst = 4 * args.steps
+        e0.record()
+        for _ in range(nst):
+            step2()
+        e1.record()
+        torch.cuda.synchronize()
+        dist.barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        strong = {"scaling": "strong", "scans_total_per_step": S2 * world, "scans_per_gpu_per_step": S2, "steps": nst,
+                  "ms_per_step": float(t.item()) / nst, "value": S2 * world * nst / (float(t.item()) * 1e-3), "unit": "scans/s",
+                  "gather": "fused peer stores" if g2 is not None else "nccl all_gather",
+                  "limit": "3 launches + the cross-rank barrier per step; the gather's tail does not shrink with the shard"}
+        del pipe2
+
+    # ---- BASELINE.json configs[1], configs[2] (RANSAC only) and the OLS flavour, beside the headline
+    legs = None
+    if world == 1 and not args.no_legs:
+        flush = l2_flush_buffer(torch, eng.device)
+        legs = {"ransac_c2": ransac_leg(eng, "BASELINE.json configs[1]", 4096, 360, 100, 100, args.steps, fp64_peak, flush),
+                "ransac_c3": ransac_leg(eng, "BASELINE.json configs[2]", 256, 8192, 410, 1024, args.steps, fp64_peak, flush),
+                "ransac_ols": ols_leg(eng, args.steps, flush)}
+        del flush
+
     # ---- BASELINE.json configs[3]: augmented-state UKF (pose + 200 landmarks, n = 403), reported beside the headline
     aug = None
     if world == 1 and not args.no_aug:
-        aug = aug_leg(eng, args.aug_filters, args.steps, fp64_peak)
+        del pipe
+        torch.cuda.empty_cache()
+        aug = aug_leg(eng, args.aug_filters, max(2, min(args.steps, 3)), fp64_peak)
 
     if rank == 0:
         value = world * S * args.steps / (ms * 1e-3)
@@ -414,12 +653,18 @@ def main():
             pass
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
         ach_tflops = S * PHE_PER_SCAN * FLOP_PER_PHE / (k_ms * 1e-3) * 1e-12
+        per_scan, tsrc = ncu_traffic()
         roofline = {
-            "kernel": "ransac_lines_kernel", "bound": "fp64-issue", "achieved": ach_tflops, "peak": fp64_peak,
+            "kernel": "ransac_tile_kernel (lslam_ransac_lines, default kernel choice)", "bound": "fp64-issue",
+            "achieved": ach_tflops, "peak": fp64_peak,
             "unit": "TFLOP/s", "frac": ach_tflops / fp64_peak if fp64_peak > 0 else None,
-            "traffic": S * NCU_DRAM_BYTES_PER_SCAN if (S % 4 == 0 and BEAMS == 360) else None,
-            "traffic_source": "ncu dram__bytes_read+write of one launch at 262,144 scans, scaled per scan "
-                              "(profiles/r01f_ransac_c2_ncu_summary.txt); algorithmic bytes per launch: %d" % (S * BYTES_PER_SCAN),
+            "flop_basis": "algorithmic: SURVEY.md 8(d) 8 fp64 flop per point-hypothesis evaluation x 36,000 per scan; the kernel "
+                          "EXECUTES fewer fp64 operations than that (distances screened in fp32 with an exact re-check band, "
+                          "residual sums from chunk moments - DESIGN.md 4.1), so this is a rate of useful work, not a pipe utilisation",
+            "traffic": S * per_scan if (per_scan is not None and S % 4 == 0 and BEAMS == 360) else None,
+            "traffic_source": ("ncu dram__bytes_read+write of one launch of the current kernel at %d scans, scaled per scan (%s)"
+                               % (tsrc["scans"], tsrc["file"])) if tsrc else "no capture recorded (profiles/ransac_traffic.json absent)",
+            "algorithmic_bytes": S * BYTES_PER_SCAN,
             "peak_source": "measured in this run: lslam_fp64_peak (dependent DFMA chains, 2 flop each)",
             "kernel_ms": k_ms, "hyps_per_s": S * 4 * TRIALS / (k_ms * 1e-3),
             "hbm": {"achieved": S * BYTES_PER_SCAN / (k_ms * 1e-3) * 1e-9, "peak": hbm_peak, "unit": "GB/s",
@@ -432,16 +677,21 @@ def main():
             rate, threads, secs = cpu_pipeline_rate(n)
             cpu = {"value": rate, "unit": "scans/s", "cores": threads, "kind": "port",
                    "sample": "%d of the %d scans of one step from packet bytes, C oracle (OpenMP), %.1f s" % (n, S, secs)}
+            cpu.update(numpy_rates())
+            cpu["sklearn_ols"] = sklearn_ols_rate()
         line = {
             "metric": "scans/s (RANSAC+assoc+UKF)", "value": value, "unit": "scans/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": workload_config(args, world),
             "stages": ["ransac", "associate", "ukf"], "hit_rate": hit_rate, "gather": gather_mode,
             "ransac_hyps_per_s": world * S * 4 * TRIALS * args.steps / (ms * 1e-3),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_xy": e2e_xy, "gpu_launches": launches,
-            "clocks": clocks, "parity_faults": faults, "ukf_aug": aug,
+            "clocks": clocks, "parity_faults": faults, "ukf_aug": aug, "e2e_points": e2e_points,
+            "gather_check": gather_check, "strong_scaling": strong,
         }
+        if legs:
+            line.update(legs)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -101,6 +101,18 @@ int lslam_ransac_lines(void *handle, const double *xy, const int32_t *npts, int3
                        uint64_t scan_base, const int32_t *pairs, double *line, int32_t *ninl, int32_t *win_trial,
                        int32_t *win_pair, double *ssum, uint32_t *inl_mask, void *stream);
 
+/* The points landmark_extraction returns (ransac_functions.py:28,46,49,53,55): for every chunk slot with a model,
+ * xBase = the x of its inliers in data order, yBase = a' * xBase + b' (a product and a sum, each rounded, like NumPy)
+ * with (a', b') = ab[slot*ab_stride + 0..1]: `proj_ab` of lslam_associate (ab_stride 2: the matched STORED landmark's
+ * coefficients on a hit, :46, the new line's on a miss, :49,53) or the `line` records themselves (ab_stride 8).
+ *   xy, npts, B, N, chunk, inl_mask, ninl   as given to / written by lslam_ransac_lines
+ *   offsets [B*C] or NULL  first output row of each slot (e.g. an exclusive prefix sum of max(ninl, 0): compact
+ *                          layout); NULL = slot * chunk (padded layout [B,C,chunk,2], rows >= ninl untouched)
+ *   points  [rows,2]       (x, y) per inlier, 16-byte aligned */
+int lslam_project_inliers(void *handle, const double *xy, const int32_t *npts, int32_t B, int32_t N, int32_t chunk,
+                          const uint32_t *inl_mask, const int32_t *ninl, const double *ab, int32_t ab_stride,
+                          const int64_t *offsets, double *points, void *stream);
+
 /* Diagnostics of the last lslam_ransac_lines calls on this handle (synchronises `stream`):
  *   counters_h[0] trials re-scored with the literal formula (threshold band / degenerate pair)
  *   counters_h[1] literal candidate evaluations in the tie-break stage

@@ -37,6 +37,7 @@ SIGNATURES = {
     "lslam_polar_to_cart": (ctypes.c_int, [_vp, _vp, _vp, _vp, _i64, _vp]),
     "lslam_ransac_lines": (ctypes.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _i32, _f64, _u64, _u64, _vp,
                                           _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "lslam_project_inliers": (ctypes.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _vp]),
     "lslam_ransac_counters": (ctypes.c_int, [_vp, ctypes.POINTER(_i64), _vp]),
     "lslam_associate": (ctypes.c_int, [_vp, _vp, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp,
                                        _f64, _f64, _f64, _i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp]),
@@ -144,6 +145,10 @@ class Handle:
         self._check(self.cdll.lslam_ransac_lines(
             self._h, xy, npts, B, N, chunk, trials, float(thr), int(seed) & (2**64 - 1),
             int(scan_base) & (2**64 - 1), pairs, line, ninl, win_trial, win_pair, ssum, inl_mask, stream))
+
+    def project_inliers(self, xy, npts, B, N, chunk, inl_mask, ninl, ab, ab_stride, offsets, points, stream=0):
+        self._check(self.cdll.lslam_project_inliers(self._h, xy, npts, B, N, chunk, inl_mask, ninl, ab, ab_stride, offsets,
+                                                    points, stream))
 
     def ransac_counters(self, stream=0):
         out = (_i64 * 3)()

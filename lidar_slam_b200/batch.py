@@ -137,6 +137,38 @@ class Engine:
             pairs=pairs.data_ptr() if pairs is not None else None)
         return out
 
+    def project_inliers(self, xy, r, ab=None, npts=None, chunk=CHUNK, compact=True, out=None):
+        """The projected inlier points landmark_extraction returns (ransac_functions.py:28,46-55), on the device:
+        for every chunk slot with a model, (x, a' x + b') of its inliers in data order.  ``r`` = the dict of
+        ransac_lines; ``ab`` = ``proj_ab`` of associate ([.., 2], the reference's choice of coefficients) or None for
+        the slots' own lines.  compact=True returns (points [total, 2], offsets [B*C + 1] int64); compact=False
+        returns points [B, C, chunk, 2] (rows >= ninl of a slot are NaN)."""
+        xy = self._check(xy, torch.float64, "xy")
+        B, N = int(xy.shape[0]), int(xy.shape[1])
+        C = (N + chunk - 1) // chunk
+        ninl = self._check(r["ninl"], torch.int32, "ninl")
+        mask = self._check(r["inl_mask"], torch.int32, "inl_mask")
+        if ab is None:
+            ab, stride = self._check(r["line"], torch.float64, "line"), 8
+        else:
+            ab, stride = self._check(ab, torch.float64, "ab"), 2
+            if ab.numel() != B * C * 2:
+                raise ValueError("ab must hold [B*C, 2] coefficients")
+        if npts is not None:
+            npts = self._check(npts, torch.int32, "npts")
+        offsets = None
+        if compact:
+            offsets = torch.zeros(B * C + 1, dtype=torch.int64, device=self.device)
+            torch.cumsum(ninl.reshape(-1).clamp(min=0), 0, out=offsets[1:])
+            if out is None:
+                out = torch.empty((int(offsets[-1].item()), 2), dtype=torch.float64, device=self.device)
+        elif out is None:
+            out = torch.full((B, C, chunk, 2), float("nan"), dtype=torch.float64, device=self.device)
+        self.handle.project_inliers(xy.data_ptr(), npts.data_ptr() if npts is not None else None, B, N, int(chunk),
+                                    mask.data_ptr(), ninl.data_ptr(), ab.data_ptr(), stride,
+                                    offsets.data_ptr() if offsets is not None else None, out.data_ptr(), self._stream())
+        return (out, offsets) if compact else out
+
     def ransac_ols(self, xy, npts=None, window=50, trials=100, thr=3.0, stop_probability=0.99, seed=0,
                    scan_base=0, pairs=None):
         """Batched OLS-flavour RANSAC (line_detection.py:51-73: RANSACRegressor(residual_threshold=3) per

@@ -19,6 +19,43 @@ __global__ void polar_to_cart_kernel(const double *dist, const double *ang_deg, 
     xy[k] = make_double2(__dmul_rn(d, c), __dmul_rn(d, s));
 }
 
+// R6b: the projected inlier points landmark_extraction returns (/root/reference/ransac_functions.py:28,46,49,53,55):
+//   xBase = data[inliers, 0];  yBase = a' * xBase + b'   (a', b' = the matched STORED landmark's on a hit, the new line's
+//   on a miss: `proj_ab` of lslam_associate, or the line record itself) - a vertical projection, not an orthogonal one.
+// One warp per chunk slot (grid-stride): lane l owns point 32 w + l of mask word w; an inlier's position among the
+// slot's inliers is the popcount of the lower bits, so the points come out compacted in data order.  Output rows
+// [first, first + ninl) with first = offsets[slot] (compact layout) or slot * chunk (padded layout).
+__global__ void project_inliers_kernel(const double2 *xy, const int32_t *npts, long long nslots, int N, int chunk, int C, int W,
+                                       const uint32_t *mask, const int32_t *ninl, const double *ab, int ab_stride,
+                                       const long long *offsets, double2 *points)
+{
+    const int lane = threadIdx.x & 31;
+    const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long s = warp0; s < nslots; s += nwarps) {
+        if (ninl[s] < 2) continue;                                // unused slot or status code: nothing to project
+        const long long b = s / C;
+        const int c = (int)(s - b * C);
+        int nb = npts ? npts[b] : N;
+        nb = nb < 0 ? 0 : (nb > N ? N : nb);
+        int n = nb - c * chunk;
+        n = n < 0 ? 0 : (n > chunk ? chunk : n);
+        const double2 *P = xy + b * N + (long long)c * chunk;
+        const double pa = ab[s * ab_stride], pb = ab[s * ab_stride + 1];
+        double2 *out = points + (offsets ? offsets[s] : s * chunk);
+        int base = 0;
+        for (int w = 0; w * 32 < n; ++w) {
+            const unsigned word = mask[s * W + w];
+            const int k = w * 32 + lane;
+            if (k < n && ((word >> lane) & 1u)) {
+                const double x = P[k].x;
+                out[base + __popc(word & ((1u << lane) - 1u))] = make_double2(x, __dadd_rn(__dmul_rn(pa, x), pb));
+            }
+            base += __popc(word);
+        }
+    }
+}
+
 __device__ __forceinline__ double u01(uint32_t r) { return ((double)r + 0.5) * 0x1p-32; }
 
 // Headless stand-in for the capture process: scan `scan_base + b` is one revolution in a

@@ -348,6 +348,32 @@ extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t 
     }
 }
 
+extern "C" int lslam_project_inliers(void *handle, const double *xy, const int32_t *npts, int32_t B, int32_t N, int32_t chunk,
+                                     const uint32_t *inl_mask, const int32_t *ninl, const double *ab, int32_t ab_stride,
+                                     const int64_t *offsets, double *points, void *stream)
+{
+    Handle *h = (Handle *)handle;
+    if (h == nullptr) return LSLAM_ERR_BAD_ARG;
+    if (!xy || !inl_mask || !ninl || !ab || !points) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_project_inliers: null buffer");
+    if (B < 0 || N < 1 || chunk < 2 || chunk > 8192 || ab_stride < 2)
+        return fail(h, LSLAM_ERR_BAD_ARG, "lslam_project_inliers: need B >= 0, N >= 1, 2 <= chunk <= 8192, ab_stride >= 2");
+    if ((((uintptr_t)xy | (uintptr_t)points) & 15) != 0) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_project_inliers: xy and points must be 16-byte aligned");
+    if (B == 0) return LSLAM_OK;
+    DeviceGuard g(h->device);
+    const int C = (N + chunk - 1) / chunk, W = (chunk + 31) / 32;
+    const long long nslots = (long long)B * C;
+    const int threads = 256;
+    long long grid = (nslots * 32 + threads - 1) / threads;
+    const long long cap = (long long)h->sms * 16;                 // grid-stride beyond 16 CTAs per SM
+    if (grid > cap) grid = cap;
+    LSLAM_LAUNCH(project_inliers_kernel, (unsigned)grid, threads, 0, (cudaStream_t)stream, reinterpret_cast<const double2 *>(xy), npts,
+                 nslots, (int)N, (int)chunk, C, W, inl_mask, ninl, ab, (int)ab_stride, (const long long *)offsets,
+                 reinterpret_cast<double2 *>(points));
+    h->launches++;
+    LSLAM_CUDA_TRY(h, cudaGetLastError());
+    return LSLAM_OK;
+}
+
 extern "C" int lslam_ransac_counters(void *handle, int64_t counters_h[3], void *stream)
 {
     Handle *h = (Handle *)handle;

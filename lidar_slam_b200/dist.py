@@ -66,17 +66,22 @@ class ResultGather:
 class PeerGather:
     """Gather buffers in symmetric memory + the descriptor lslam_ukf_step_gather needs.
 
-    state [world, F, 12] float64 (x[3], P[9] of every filter of every rank) and ids
-    [world, F, id_slots] int32, identical on every rank once ``barrier()`` has passed on the stream
-    that ran the step.  ``multicast=None`` uses the multicast mapping when there is one."""
+    state [2, world, F, 12] float64 (x[3], P[9] of every filter of every rank) and ids
+    [2, world, F, id_slots] int32: TWO copies, written alternately by step parity.  After ``barrier()`` has passed
+    on the stream that ran step k, ``result()`` is step k's records, identical on every rank.  One barrier per step is
+    enough: a peer that runs ahead writes step k + 1 into the OTHER copy, and cannot start step k + 2 (which reuses
+    step k's copy) before it has passed barrier k + 1 - which needs this rank's arrival there.  So the records of
+    step k stay valid until this rank itself queues ``barrier()`` for step k + 1; read (or copy) them before that.
+    ``multicast=None`` uses the multicast mapping when there is one."""
 
     def __init__(self, filters_per_rank, id_slots, device, group=None, multicast=None):
         import torch.distributed._symmetric_memory as symm_mem
         group = group or dist.group.WORLD
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.F, self.id_slots = int(filters_per_rank), int(id_slots)
-        self.state = symm_mem.empty((self.world, self.F, 12), dtype=torch.float64, device=device)
-        self.ids = symm_mem.empty((self.world, self.F, max(self.id_slots, 1)), dtype=torch.int32, device=device)
+        self.state = symm_mem.empty((2, self.world, self.F, 12), dtype=torch.float64, device=device)
+        self.ids = symm_mem.empty((2, self.world, self.F, max(self.id_slots, 1)), dtype=torch.int32, device=device)
+        self._parity, self._done = 0, 0          # copy the running step writes / copy of the last completed step
         self.h_state = symm_mem.rendezvous(self.state, group)
         self.h_ids = symm_mem.rendezvous(self.ids, group)
         has_mc = bool(self.h_state.has_multicast_support and self.h_state.multicast_ptr and self.h_ids.multicast_ptr)
@@ -86,7 +91,8 @@ class PeerGather:
 
     def descriptor(self, ids, s0=0):
         """For a call that runs the local filters [s0, s0 + n): ``ids`` = its [n, id_slots] int32 tensor."""
-        d = {"world": self.world, "first_record": self.rank * self.F + s0, "ids": ids if self.id_slots else None,
+        d = {"world": self.world, "first_record": (self._parity * self.world + self.rank) * self.F + s0,
+             "ids": ids if self.id_slots else None,
              "id_slots": self.id_slots}
         if self.multicast:
             d["mc_state"], d["mc_ids"] = int(self.h_state.multicast_ptr), int(self.h_ids.multicast_ptr)
@@ -95,8 +101,12 @@ class PeerGather:
         return d
 
     def barrier(self):
-        """Cross-rank barrier on the current stream: every rank's stores of the step have landed."""
+        """End of a step: cross-rank barrier on the current stream (every rank's stores of the step have landed), then
+        the next step writes the other copy."""
         self.h_state.barrier(channel=0)
+        self._done = self._parity
+        self._parity ^= 1
 
     def result(self):
-        return {"state": self.state, "ids": self.ids}
+        """Records of the last completed step: state [world, F, 12], ids [world, F, id_slots] (views)."""
+        return {"state": self.state[self._done], "ids": self.ids[self._done]}

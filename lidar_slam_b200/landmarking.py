@@ -10,6 +10,8 @@ Python list into a device table and calls ``lslam_associate`` (csrc/assoc.cuh). 
 are the scalar convenience API the reference exposes; ``table_from_landmarks`` /
 ``apply_table_to_landmarks`` are the packing helpers between the list and the device layout.
 """
+import ctypes
+import ctypes.util
 import math
 
 import numpy as np
@@ -18,6 +20,15 @@ LIFE = 40
 TOLERANCE_A = 0.1
 TOLERANCE_B = 10
 TOLERANCE = 100
+
+
+if hasattr(math, "fma"):                    # Python >= 3.13
+    _fma = math.fma
+else:                                       # the C library's correctly rounded fma
+    _libm = ctypes.CDLL(ctypes.util.find_library("m") or "libm.so.6")
+    _libm.fma.restype = ctypes.c_double
+    _libm.fma.argtypes = [ctypes.c_double] * 3
+    _fma = _libm.fma
 
 
 class Landmark:
@@ -69,7 +80,11 @@ class Landmark:
     # -- geometry (reference :57-77) --
     @staticmethod
     def _gap(p, q):
-        return math.sqrt((p[0] - q[0]) * (p[0] - q[0]) + (p[1] - q[1]) * (p[1] - q[1]))
+        """np.linalg.norm(p - q) of the reference (:58, :63) with the rounding the device path pins:
+        sqrt(fma(vy, vy, vx * vx)) - what NumPy's BLAS dot gives here (tests/golden/landmarking_golden.npz holds a
+        vector sitting on the 100 mm gate), so Landmark.is_equal on the host and lslam_associate agree to the bit."""
+        vx, vy = float(p[0]) - float(q[0]), float(p[1]) - float(q[1])
+        return math.sqrt(_fma(vy, vy, vx * vx))
 
     def distance_end_origin(self, landmark):
         return self._gap(self.end, landmark.get_pos())

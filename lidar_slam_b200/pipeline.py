@@ -34,11 +34,13 @@ class ScanPipeline:
         self._view_cache = {}
         self._ov = None
         self.peer_gather = None
+        self._pts = None              # projected inlier points (step_host(points=True)): device + pinned host buffers
 
     def enable_peer_gather(self, group=None, multicast=None):
         """N > 1: publish every step's (x, P, match_id) into all ranks' gather buffers from inside the UKF
         kernel (lidar_slam_b200/dist.PeerGather).  Call ``self.peer_gather.barrier()`` after the step
-        before reading ``self.peer_gather.result()``."""
+        before reading ``self.peer_gather.result()``; the records stay valid until the NEXT step's barrier() is
+        queued on this rank (the buffers are double-buffered by step parity, one barrier per step is enough)."""
         from . import dist as ldist
         self.peer_gather = ldist.PeerGather(self.S, self.C, self.eng.device, group=group, multicast=multicast)
         return self.peer_gather
@@ -79,7 +81,28 @@ class ScanPipeline:
         gd = self.peer_gather.descriptor(a["match_id"], s0) if self.peer_gather is not None else None
         eng.ukf_step(v["ukf"], r["line"], a["hit_pos"], lm_valid=a["match"], valid_min=0, u=u, gather=gd)
         return {"line": r["line"], "ninl": r["ninl"], "match": a["match"], "match_id": a["match_id"],
-                "x": v["ukf"]["x"], "P": v["ukf"]["P"]}
+                "x": v["ukf"]["x"], "P": v["ukf"]["P"], "inl_mask": r["inl_mask"], "proj_ab": a["proj_ab"]}
+
+    def project(self, xy, res, s0=0, s1=None):
+        """The projected inlier points of streams [s0, s1) (what landmark_extraction returns per chunk,
+        ransac_functions.py:28,46-55) compacted in (stream, chunk, data) order into the pipeline's device buffer.
+        Returns (points view [<= (s1-s0)*N, 2], offsets [(s1-s0)*C + 1] int64); offsets[-1] = rows written."""
+        s1 = self.S if s1 is None else s1
+        if self._pts is None:
+            dev = self.eng.device
+            self._pts = {"dev": torch.empty((self.S * self.N, 2), dtype=torch.float64, device=dev),
+                         "off": torch.zeros((self.S * self.C + 1,), dtype=torch.int64, device=dev),
+                         "host": torch.empty((self.S * self.N, 2), dtype=torch.float64).pin_memory(),
+                         "total": torch.zeros((self.S,), dtype=torch.int64).pin_memory()}
+        n = (s1 - s0) * self.C
+        off = self._pts["off"][s0 * self.C:s0 * self.C + n + 1]
+        off[0] = 0
+        torch.cumsum(res["ninl"].reshape(-1).clamp(min=0), 0, out=off[1:])
+        out = self._pts["dev"][s0 * self.N:s1 * self.N]
+        self.eng.handle.project_inliers(xy.data_ptr(), None, s1 - s0, self.N, self.chunk, res["inl_mask"].data_ptr(),
+                                        res["ninl"].data_ptr(), res["proj_ab"].data_ptr(), 2, off.data_ptr(),
+                                        out.data_ptr(), self.eng._stream())
+        return out, off
 
     # ---- a known map (benchmark / test set-up; data movement only) -----------------------------
     def install_map_from_lines(self, line, ninl, life=batch.Engine.LIFE):
@@ -129,7 +152,7 @@ class ScanPipeline:
             self._host_out = {k: torch.empty(sh, dtype=dt).pin_memory() for k, (sh, dt) in shapes.items()}
         return self._host_out
 
-    def step_host(self, host_in, slices=1):
+    def step_host(self, host_in, slices=1, points=False):
         """One step from pinned host memory to pinned host memory.
 
         host_in: [S, N, 2] float64 scans, or [S, P, 84] uint8 express packets (decoded on the device:
@@ -139,7 +162,10 @@ class ScanPipeline:
         the PCIe transfers in both directions overlap the kernels (slice k's kernels wait for slice
         k's input only).  The current stream waits for all three at the end; the caller synchronises
         it before reading the returned pinned tensors (result_keys(), plus "status" per scan for
-        packets)."""
+        packets).  points=True also returns what landmark_extraction itself returns - the projected inlier points
+        (ransac_functions.py:28,46-55) - as out["points"] = list of pinned views [rows_k, 2], one per slice, in
+        (stream, chunk, data) order: the row count of a slice is only known on the device, so the host waits for
+        each slice's count (8 bytes) before it queues that slice's copy; the kernels of later slices keep running."""
         packets = host_in.dtype == torch.uint8
         dev = self.eng.device
         if packets:
@@ -164,6 +190,13 @@ class ScanPipeline:
                 out[k].copy_(res[k], non_blocking=True)
             if packets:
                 out["status"].copy_(self.status_dev, non_blocking=True)
+            if points:
+                pts, off = self.project(self.xy_dev, res)
+                self._pts["total"][:1].copy_(off[-1:], non_blocking=True)
+                torch.cuda.current_stream(dev).synchronize()
+                rows = int(self._pts["total"][0])
+                self._pts["host"][:rows].copy_(pts[:rows], non_blocking=True)
+                out = dict(out, points=[self._pts["host"][:rows]])
             return out
         if self._ov is None or self._ov["K"] != K:
             self._ov = {"K": K, "in": torch.cuda.Stream(dev), "run": torch.cuda.Stream(dev),
@@ -188,6 +221,9 @@ class ScanPipeline:
                 if packets:
                     self.eng.express_to_cart(dev_in[a:b], self.N, xy=self.xy_dev[a:b], status=self.status_dev[a:b])
                 res = self.step(self.xy_dev[a:b], s0=a, s1=b)
+                if points:
+                    pts_k, off_k = self.project(self.xy_dev[a:b], res, a, b)
+                    self._pts["total"][k:k + 1].copy_(off_k[-1:], non_blocking=True)
                 ov["ev_run"][k].record()
             with torch.cuda.stream(ov["out"]):
                 ov["out"].wait_event(ov["ev_run"][k])
@@ -196,6 +232,17 @@ class ScanPipeline:
                 if packets:
                     out["status"][a:b].copy_(self.status_dev[a:b], non_blocking=True)
                 ov["ev_out"][k].record()
+        if points:
+            views = []
+            for k, (a, b) in enumerate(bounds):
+                ov["ev_run"][k].synchronize()                  # slice k's row count has landed
+                rows = int(self._pts["total"][k])
+                with torch.cuda.stream(ov["out"]):
+                    self._pts["host"][a * self.N:a * self.N + rows].copy_(self._pts["dev"][a * self.N:a * self.N + rows],
+                                                                          non_blocking=True)
+                    ov["ev_out"][k].record()
+                views.append(self._pts["host"][a * self.N:a * self.N + rows])
+            out = dict(out, points=views)
         ov["primed"] = True
         for st in ("in", "run", "out"):
             cur.wait_stream(ov[st])

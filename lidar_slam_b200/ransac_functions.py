@@ -62,12 +62,13 @@ def landmark_extraction(pointsToBeFitted, landmarkNumber, landmarks):
     del pointsToBeFitted[:]                                         # :22
     if MIN_SAMPLES != 2:
         raise ValueError("the CUDA path implements min_samples=2 (LineModelND from two points)")
-    if data.ndim != 2 or data.shape[1] != 2 or data.shape[0] < 2:
-        raise ValueError("`min_samples` must be in range (0, <number-of-samples>)")   # upstream's message
+    if data.ndim != 2 or data.shape[1] != 2 or data.shape[0] <= MIN_SAMPLES:
+        # upstream's check and message: min_samples must be smaller than the number of samples (n = 2 included)
+        raise ValueError("`min_samples` must be in range (0, <number-of-samples>)")
     n = int(data.shape[0])
     # ---- RANSAC + refit + slope/intercept/tip: one chunk = one slot of a B=1 batch ----
-    r = eng.ransac_lines(torch.from_numpy(data[None]).to(eng.device), chunk=n, trials=MAX_TRIALS,
-                         thr=THRESHOLD, seed=SEED, scan_base=int(landmarkNumber))
+    xy_dev = torch.from_numpy(data[None]).to(eng.device)
+    r = eng.ransac_lines(xy_dev, chunk=n, trials=MAX_TRIALS, thr=THRESHOLD, seed=SEED, scan_base=int(landmarkNumber))
     ninl = int(r["ninl"][0, 0])
     if ninl < 2:
         if ninl == batch._lib.LSLAM_ERR_NONFINITE:
@@ -76,12 +77,10 @@ def landmark_extraction(pointsToBeFitted, landmarkNumber, landmarks):
         raise AttributeError("'NoneType' object has no attribute 'params'")
     line = r["line"][0, 0].cpu().numpy()
     a, b, ox, oy, tipX, tipY = line[0], line[1], line[2], line[3], line[6], line[7]
-    inliers = _mask_to_bool(r["inl_mask"][0, 0].cpu().numpy().view(np.uint32), n)
-    xBase = np.array(data[inliers, 0])                              # :28
     fittedLine = Landmark(float(a), float(b), landmarkNumber, float(ox), float(oy), float(tipX), float(tipY))
     _say("ransacking...")
     # ---- association against the caller's list (first match in list order, reference-exact) ----
-    pa, pb, newLandmark = a, b, True
+    proj_ab, newLandmark = None, True                              # None: the new line's own a, b (:49, :53)
     if len(landmarks) > 0:
         rows, life, ids, count = table_from_landmarks(landmarks)
         dev = eng.device
@@ -100,15 +99,17 @@ def landmark_extraction(pointsToBeFitted, landmarkNumber, landmarks):
                 print("Excluded landmark: {}".format(before[k]))
         apply_table_to_landmarks(landmarks, tables["life"][0].cpu().numpy(), new_ids, new_count)
         if match >= 0:                                              # :44-47 the STORED landmark's a, b
-            pa, pb = (float(v) for v in out["proj_ab"][0, 0].cpu().numpy())
+            proj_ab = out["proj_ab"]
             newLandmark = False
         else:
             _say("New landmark found! Landmarks: {}".format(len(landmarks)))
-    yBase = pa * xBase + pb                                         # :46 / :49 / :53
+    # xBase = data[inliers, 0], yBase = a' * xBase + b' (:28, :46 / :49 / :53) on the device: lslam_project_inliers
+    pts, _ = eng.project_inliers(xy_dev, r, ab=proj_ab, chunk=n)
+    pts = pts.cpu().numpy()
     if QPointF is not None:
-        qPointsList = [QPointF(xBase[i], yBase[i]) for i in range(xBase.shape[0])]
+        qPointsList = [QPointF(p[0], p[1]) for p in pts]            # :55
     else:
-        qPointsList = np.stack([xBase, yBase], axis=-1)
+        qPointsList = pts
     return qPointsList, fittedLine, newLandmark
 
 
@@ -213,21 +214,15 @@ class RevolutionAdapter:
             xy[c, :len(pts)] = pts
             npts[c] = len(pts)
         self.pending = []
-        r = eng.ransac_lines(torch.from_numpy(xy).to(eng.device), npts=torch.from_numpy(npts).to(eng.device),
-                             chunk=ck, trials=MAX_TRIALS, thr=THRESHOLD, seed=SEED,
+        xy_dev, npts_dev = torch.from_numpy(xy).to(eng.device), torch.from_numpy(npts).to(eng.device)
+        r = eng.ransac_lines(xy_dev, npts=npts_dev, chunk=ck, trials=MAX_TRIALS, thr=THRESHOLD, seed=SEED,
                              scan_base=self.scan_index)
         self.scan_index += C
         line = r["line"].reshape(1, C, 8)
         a = eng.associate(line, self.tables, q_valid=r["ninl"].reshape(1, C), mode=0, append=True,
                           tolA=TOLERANCE_A, tolB=TOLERANCE_B, tol=TOLERANCE, life_init=LIFE)
+        # the revolution's projected inlier points, compacted in chunk order, on the device (lslam_project_inliers)
+        pts, _ = eng.project_inliers(xy_dev, r, ab=a["proj_ab"], npts=npts_dev, chunk=ck)
         ninl = r["ninl"].reshape(C).cpu().numpy()
-        masks = r["inl_mask"].reshape(C, -1).cpu().numpy().view(np.uint32)
-        proj = a["proj_ab"][0].cpu().numpy()
-        pts = []
-        for c in range(C):
-            if ninl[c] < 2:
-                continue
-            xb = xy[c, :npts[c], 0][_mask_to_bool(masks[c], int(npts[c]))]
-            pts.append(np.stack([xb, proj[c, 0] * xb + proj[c, 1]], -1))
-        return {"points": np.concatenate(pts, 0) if pts else np.zeros((0, 2)), "line": line[0].cpu().numpy(),
+        return {"points": pts.cpu().numpy(), "line": line[0].cpu().numpy(),
                 "ninl": ninl, "match": a["match"][0].cpu().numpy(), "match_id": a["match_id"][0].cpu().numpy()}

@@ -97,12 +97,13 @@ class DeviceUKF:
 
     def _params(self, dt):
         p = self.points_fn
-        return self.eng.ukf_params(dt=dt, alpha=p.alpha, beta=p.beta, kappa=p.kappa, var_dist=self._R[0, 0],
-                                   var_angle=self._R[1, 1], Q=self._Q)
+        from . import UKFMethods                                  # R, L read at call time: user edits of the module constants count
+        return self.eng.ukf_params(dt=dt, wheel_r=float(UKFMethods.R), base_l=float(UKFMethods.L), alpha=p.alpha, beta=p.beta,
+                                   kappa=p.kappa, var_dist=self._R[0, 0], var_angle=self._R[1, 1], Q=self._Q)
 
     def _dev(self, a, shape):
         a = np.broadcast_to(np.asarray(a, dtype=np.float64), (self.F,) + shape)
-        return self._torch.from_numpy(np.ascontiguousarray(a)).to(self.eng.device)
+        return self._torch.from_numpy(np.array(a, order="C")).to(self.eng.device)     # a writable copy (broadcast views are not)
 
     def predict(self, dt=None, u=None, **fx_args):
         """filterpy's predict(dt=None, **fx_args); the reference's fx takes ``u = [vl, vr]``."""

@@ -76,6 +76,11 @@ def max_threads():
     return int(lib().oracle_max_threads())
 
 
+def set_threads(n):
+    """OpenMP threads of every later call (a launcher may have exported OMP_NUM_THREADS=1)."""
+    lib().oracle_set_threads(ctypes.c_int(int(n)))
+
+
 # ---- UKF (oracle/ukf.c) ----------------------------------------------------------------------
 UKF_PREDICT, UKF_UPDATE, UKF_REDRAW = 1, 2, 4
 

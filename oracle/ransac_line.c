@@ -234,6 +234,16 @@ int oracle_ransac_lines_pairs(const double *xy, const int32_t *npts, int32_t B, 
     return 0;
 }
 
+/* omp_set_num_threads for every later oracle_* call with nthreads <= 0 (torchrun exports OMP_NUM_THREADS=1) */
+void oracle_set_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int oracle_max_threads(void)
 {
 #ifdef _OPENMP

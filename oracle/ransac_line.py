@@ -177,6 +177,15 @@ def extract_line(data, landmark_number=0, **kw):
             "id": landmark_number, "info": info}
 
 
+def project_inliers(data, inliers, a, b):
+    """The points landmark_extraction returns (ransac_functions.py:28,46,49,53,55): ``xBase = data[inliers, 0]``,
+    ``yBase = a * xBase + b`` with (a, b) the matched stored landmark's coefficients on a hit (:46) or the new
+    line's (:49, :53) - a vertical projection; NumPy rounds the product and the sum separately."""
+    xBase = np.asarray(data, dtype=np.float64)[np.asarray(inliers, dtype=bool), 0]
+    yBase = a * xBase + b
+    return np.stack([xBase, yBase], axis=-1)
+
+
 def chunk_bounds(npts, chunk):
     """Chunking of one revolution as /root/reference/functions.py:64-76 does it.
 

@@ -51,7 +51,7 @@ def main():
             assert torch.equal(x.contiguous().view(torch.uint8), want["x"].view(torch.uint8)), (multicast, step, "x")
             assert torch.equal(P.contiguous().view(torch.uint8), want["P"].view(torch.uint8)), (multicast, step, "P")
             assert torch.equal(got["ids"], want["match_id"]), (multicast, step, "ids")
-            pg.barrier()                       # nobody overwrites the buffers while a peer still compares
+            # no second barrier: a peer that is already in the next step writes the OTHER copy (PeerGather docstring)
         if rank == 0:
             print("peer gather ok: multicast=%s used=%s world=%d" % (multicast, pg.multicast, world), flush=True)
     dist.destroy_process_group()

@@ -71,6 +71,34 @@ def emu_ransac_lines(xy, npts=None, chunk=100, trials=100, thr=20.0, seed=0, sca
     return out
 
 
+def emu_project_inliers(xy, r, ab=None, npts=None, chunk=100, compact=True, handle=None):
+    """lslam_project_inliers on the emulated library; r = the dict of emu_ransac_lines."""
+    h = handle or emu_handle()
+    xy = np.ascontiguousarray(xy, dtype=np.float64)
+    B, N, _ = xy.shape
+    C = (N + chunk - 1) // chunk
+    ninl = np.ascontiguousarray(r["ninl"], dtype=np.int32)
+    mask = np.ascontiguousarray(r["inl_mask"]).view(np.uint32)
+    if ab is None:
+        ab, stride = np.ascontiguousarray(r["line"], dtype=np.float64), 8
+    else:
+        ab, stride = np.ascontiguousarray(ab, dtype=np.float64), 2
+    if npts is not None:
+        npts = np.ascontiguousarray(npts, dtype=np.int32)
+    offsets = None
+    if compact:
+        offsets = np.zeros(B * C + 1, np.int64)
+        offsets[1:] = np.cumsum(np.maximum(ninl.reshape(-1), 0))
+        out = np.full((int(offsets[-1]) + 4, 2), -7.0)            # 4 guard rows
+    else:
+        out = np.full((B, C, chunk, 2), np.nan)
+    h.project_inliers(ptr(xy), ptr(npts), B, N, chunk, ptr(mask), ptr(ninl), ptr(ab), stride, ptr(offsets), ptr(out))
+    if compact:
+        assert (out[-4:] == -7.0).all(), "lslam_project_inliers wrote past the last row"
+        return out[:-4], offsets
+    return out
+
+
 def emu_associate(queries, tables, q_valid=None, mode=0, append=True, layout=0, handle=None,
                   tolA=0.1, tolB=10, tol=100, life_init=40, hit_pos=None):
     """lslam_associate on the emulated library.  queries [T,Q,6|8]; tables = dict with rows

@@ -94,3 +94,41 @@ def test_overlapped_and_packet_host_paths(gpu_engine, kind, slices):
     assert torch.equal(a.tables["life"], b.tables["life"])
     h2d, d2h = b.io_bytes(h_in)
     assert h2d == h_in.numel() * h_in.element_size()
+
+
+@pytest.mark.parametrize("slices", [1, 3])
+def test_host_step_returns_the_projected_inlier_points(gpu_engine, slices):
+    """step_host(points=True): what landmark_extraction itself returns (ransac_functions.py:28,46-55) for every chunk of
+    every stream - x of the inliers, y = a' x + b' with the MATCHED stored landmark's coefficients - against the oracle
+    projection of the same masks, bit for bit, in (stream, chunk, data) order."""
+    import torch
+    from lidar_slam_b200 import pipeline
+    from oracle import ransac_line as rl
+    from tests.parity_util import mask_to_bool
+    eng = gpu_engine
+    S = 500
+    xy = eng.synth_scans(S, seed=31)
+    p = pipeline.ScanPipeline(eng, S, seed=3)
+    r0 = eng.ransac_lines(xy, seed=3)
+    p.install_map_from_lines(r0["line"], r0["ninl"])
+    h_in = p.alloc_host_io()
+    h_in.copy_(xy)
+    torch.cuda.synchronize()
+    for _ in range(2):
+        out = p.step_host(h_in, slices=slices, points=True)
+        torch.cuda.synchronize()
+        got = torch.cat(list(out["points"]), 0).numpy()
+        ninl = out["ninl"].numpy()
+        masks = p.rout["inl_mask"].cpu().numpy().view(np.uint32)
+        ab = p.aout["proj_ab"].cpu().numpy()
+        xyh = h_in.numpy()
+        parts = []
+        for s in range(S):
+            for c in range(4):
+                if ninl[s, c] < 2:
+                    continue
+                a0, a1 = c * 100, min(360, c * 100 + 100)
+                parts.append(rl.project_inliers(xyh[s, a0:a1], mask_to_bool(masks[s, c], a1 - a0), ab[s, c, 0], ab[s, c, 1]))
+        want = np.concatenate(parts, 0)
+        assert got.shape == want.shape and np.array_equal(got.view(np.uint64), want.view(np.uint64))
+        assert (out["match_id"].numpy() >= 0).mean() > 0.9           # the stored landmarks' coefficients were used

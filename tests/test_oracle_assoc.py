@@ -101,3 +101,17 @@ def test_c_twin_matches_python(cport, mode):
         au.assert_assoc_equal(want, (o["match"], o["match_id"], o["proj_ab"], t2), "C twin")
         hit = o["match"] >= 0
         assert np.isnan(o["hit_pos"][~hit]).all() and not np.isnan(o["hit_pos"][hit]).any()
+
+
+def test_dropin_landmark_gap_has_the_pinned_rounding():
+    """Landmark.is_equal on the host (lidar_slam_b200/landmarking.py) and lslam_associate on the device must agree on a
+    landmark sitting exactly on the 100 mm gate: both use sqrt(fma(vy, vy, vx * vx)) (oracle/assoc.py::norm2, pinned to
+    the reference's np.linalg.norm by tests/golden/landmarking_golden.npz)."""
+    from lidar_slam_b200 import landmarking as dl
+    from oracle import assoc as oa
+    rng = np.random.default_rng(3)
+    p = rng.normal(0, 3000, (2000, 2))
+    q = p + rng.normal(0, 80, (2000, 2))
+    for a, b in zip(p, q):
+        assert dl.Landmark._gap(a, b) == oa.norm2(a[0] - b[0], a[1] - b[1])
+    assert dl.Landmark._gap((0.0, 0.0), (60.0, 80.0)) == 100.0
