@@ -229,7 +229,8 @@ static int dispatch_ransac_tile(Handle *h, const RansacArgs &a, int tpt, int thr
     case 2: return launch_ransac_tile<2, 256, 6, true>(h, a, threads, st, probe_only);
     case 6: return launch_ransac_tile<6, 256, 4, true>(h, a, threads, st, probe_only);
     case 8: return launch_ransac_tile<8, 256, 3, true>(h, a, threads, st, probe_only);
-    default: return threads > 256 ? launch_ransac_tile<4, 512, 2, true>(h, a, threads, st, probe_only)
+    default: return threads > 512 ? launch_ransac_tile<4, 1024, 1, true>(h, a, threads, st, probe_only)
+                  : threads > 256 ? launch_ransac_tile<4, 512, 2, true>(h, a, threads, st, probe_only)
                                   : launch_ransac_tile<4, 256, 4, true>(h, a, threads, st, probe_only);
     }
 }

@@ -31,7 +31,8 @@
 
 namespace lslam {
 
-constexpr int kTileLG = 8;             // lanes that stage / refit one chunk slot
+constexpr int kTileLG = 8;             // lanes that stage / refit one chunk slot (8, 16 or 32): the narrow phases are latency-
+                                       // bound, so more lanes per slot (fewer points per lane, more warps busy) shorten them
 
 struct TileSlot {
     unsigned long long scan;           // global scan index (Philox counter words 2, 3)
@@ -591,13 +592,14 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArg
         double2 p0 = make_double2(0.0, 0.0);
         if (ok) {
             p0 = P3[s3->best_i];
+            // loads are unconditional and independent of the mask test (they pipeline); an outlier contributes zeros
+#pragma unroll 4
             for (int k = r; k < n3; k += LG) {
-                if ((mrow[(k >> 5) * ms] >> (k & 31)) & 1u) {
-                    const double2 p = P3[k];
-                    const double dx = p.x - p0.x, dy = p.y - p0.y;
-                    sx += dx; sy += dy;
-                    sxx = fma(dx, dx, sxx); sxy = fma(dx, dy, sxy); syy = fma(dy, dy, syy);
-                }
+                const double2 p = P3[k];
+                const bool in = (mrow[(k >> 5) * ms] >> (k & 31)) & 1u;
+                const double dx = in ? p.x - p0.x : 0.0, dy = in ? p.y - p0.y : 0.0;
+                sx += dx; sy += dy;
+                sxx = fma(dx, dx, sxx); sxy = fma(dx, dy, sxy); syy = fma(dy, dy, syy);
             }
         }
 #pragma unroll
@@ -628,15 +630,16 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArg
                 const double ic = __dsub_rn(oy, __dmul_rn(sl, ox));
                 const double tipx = P3[last].x;
                 const double tipy = __dadd_rn(__dmul_rn(tipx, sl), ic);
-                out = r == 0 ? sl : r == 1 ? ic : r == 2 ? ox : r == 3 ? oy : r == 4 ? dx : r == 5 ? dy : r == 6 ? tipx : tipy;
+                out = (r & 7) == 0 ? sl : (r & 7) == 1 ? ic : (r & 7) == 2 ? ox : (r & 7) == 3 ? oy : (r & 7) == 4 ? dx : (r & 7) == 5 ? dy : (r & 7) == 6 ? tipx : tipy;
             }
-            static_assert(LG == 8, "one lane per element of the line record");
-            a.line[s * 8 + r] = out;
-            if (r == 0) a.ninl[s] = ok ? s3->mx : (s3->status == 0x7fffffff ? 0 : s3->status);
-            if (r == 1) a.win_trial[s] = ok ? s3->best_t : -1;
-            if (r == 2) a.win_pair[2 * s] = ok ? s3->best_i : -1;
-            if (r == 3) a.win_pair[2 * s + 1] = ok ? s3->best_j : -1;
-            if (r == 4 && a.ssum != nullptr) a.ssum[s] = ok ? s3->best_ss : qnan;
+            static_assert(LG >= 8, "one lane per element of the line record");
+            constexpr int R0 = LG >= 16 ? 8 : 0;                 // the scalar outputs: on lanes 8.. when the group has them
+            if (r < 8) a.line[s * 8 + r] = out;
+            if (r == R0) a.ninl[s] = ok ? s3->mx : (s3->status == 0x7fffffff ? 0 : s3->status);
+            if (r == R0 + 1) a.win_trial[s] = ok ? s3->best_t : -1;
+            if (r == R0 + 2) a.win_pair[2 * s] = ok ? s3->best_i : -1;
+            if (r == R0 + 3) a.win_pair[2 * s + 1] = ok ? s3->best_j : -1;
+            if (r == R0 + 4 && a.ssum != nullptr) a.ssum[s] = ok ? s3->best_ss : qnan;
         }
         // inlier masks of this warp's slots: consecutive slots are consecutive in global memory
         const int nq = (nsl - qw) < SPW ? (nsl - qw) : SPW;

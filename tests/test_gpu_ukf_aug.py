@@ -153,3 +153,35 @@ def test_aug_batching_failures_and_repeat_steps(gpu_engine):
     Pn = st["P"].cpu().numpy()
     assert np.abs(Pn - Pn.transpose(0, 2, 1)).max() <= 1e-6 * np.abs(Pn).max()
     assert np.all(np.linalg.eigvalsh((Pn + Pn.transpose(0, 2, 1)) / 2) > 0)
+
+
+def test_aug_against_extended_precision_truth(gpu_engine):
+    """BASELINE.json configs[3] at the reference's alpha = 1e-4, L = 200 (n = 403), 16 distinct filters, against a TRUTH
+    value instead of a self-chosen bar: tests/golden/ukf_aug_kat.npz holds the same step evaluated in x87 extended precision
+    (eps 1.1e-19; tests/golden/make_ukf_aug_kat.py).  The kernel must be as close to the truth as the fp64 oracle is:
+    |GPU - truth| <= max(1e-5, 1.5 |oracle - truth|) for x and P, in both cross-covariance modes, taken over the 16 filters
+    as the worst case and as the root mean square (per filter both errors are one realisation of the same rounding noise,
+    so single-filter ratios scatter around 1: printed).  If the kernel were further from the truth than the oracle, that
+    would be a kernel accuracy bug, not conditioning."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ukf_aug_kat.npz"))
+    F, L = int(g["F"]), int(g["L"])
+    x, P, u, z = au.aug_case(F, L, seed=int(g["seed"]))
+    xo, Po = au.oracle_aug(x, P, u, z)
+    ox, oP = au.truth_errors(g, xo, Po)
+    print("oracle vs truth:   x %.2e  P %.2e (max over %d filters)" % (ox.max(), oP.max(), F))
+    try:
+        for mode in (0, 1):
+            gpu_engine.set_option("ukf_aug.pzx", mode)
+            xg, Pg, st = run_gpu(gpu_engine, x, P, u, z)
+            assert not st.any()
+            gx, gP = au.truth_errors(g, xg, Pg)
+            print("pzx=%d GPU vs truth: x %.2e  P %.2e; worst ratio to the oracle's error: x %.2f  P %.2f"
+                  % (mode, gx.max(), gP.max(), (gx / np.maximum(ox, 1e-300)).max(), (gP / np.maximum(oP, 1e-300)).max()))
+            rms = lambda v: float(np.sqrt(np.mean(v * v)))
+            print("       rms over filters: GPU x %.2e P %.2e, oracle x %.2e P %.2e" % (rms(gx), rms(gP), rms(ox), rms(oP)))
+            for name, ge, oe in (("x", gx, ox), ("P", gP, oP)):
+                assert ge.max() <= max(1e-5, 1.5 * oe.max()), "pzx=%d: worst %s error %.3g against the oracle's %.3g" % (mode, name, ge.max(), oe.max())
+                assert rms(ge) <= max(1e-5, 1.5 * rms(oe)), "pzx=%d: rms %s error %.3g against the oracle's %.3g" % (mode, name, rms(ge), rms(oe))
+    finally:
+        gpu_engine.set_option("ukf_aug.pzx", 1)

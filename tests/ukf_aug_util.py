@@ -73,3 +73,16 @@ def assert_aug_close(want, got, what="", rtol=1e-5, cond=None, cond_factor=8.0):
     assert ex <= tx, "%s x: max rel err %.3g > %.3g" % (what, ex, tx)
     assert eP <= tP, "%s P: max scaled err %.3g > %.3g" % (what, eP, tP)
     return ex, eP
+
+
+def truth_errors(g, x, P):
+    """Per-filter errors of (x [F, n], P [F, n, n]) against the extended-precision truth of tests/golden/ukf_aug_kat.npz
+    (tests/golden/make_ukf_aug_kat.py): x in full, P on its diagonal and the stored sample of entries; same scaling as
+    _errors (x: |dx| / max(|x|, 10); P: |dP_ij| / sqrt(P_ii P_jj))."""
+    xt, pd, ps, si, sj = g["x"], g["P_diag"], g["P_sample"], g["sample_i"], g["sample_j"]
+    F = xt.shape[0]
+    ex = (np.abs(x - xt) / np.maximum(np.abs(xt), 10.0)).max(axis=1)
+    dg = np.sqrt(np.abs(pd))
+    e_diag = np.abs(np.einsum("fii->fi", P) - pd) / (dg * dg)
+    e_samp = np.abs(P[:, si, sj] - ps) / (dg[:, si] * dg[:, sj])
+    return ex, np.maximum(e_diag.max(axis=1), e_samp.max(axis=1)).reshape(F)
