@@ -71,12 +71,13 @@ __device__ __forceinline__ void multimem_store(int32_t *mc_addr, int32_t v)
 #endif
 }
 
-__host__ __device__ inline size_t ukf_smem_doubles_per_warp(int G) { return (size_t)(18 * 2 * G + 4 * G * G) * (32 / G); }
+__host__ __device__ inline size_t ukf_smem_doubles_per_warp(int G) { return (size_t)(19 * 2 * G + 4 * G * G) * (32 / G); }
 
 __device__ __forceinline__ double ukf_normalize_angle(double a)
 {
     const double kPi = 3.141592653589793, kTwoPi = 2 * 3.141592653589793;
-    double m = fmod(a, kTwoPi);                     // exact; Python's float % then fixes the sign
+    // fmod is exact, and for |a| < 2 pi it returns a itself: the common case skips the ~50-instruction routine
+    double m = fabs(a) < kTwoPi ? a : fmod(a, kTwoPi);   // Python's float % then fixes the sign
     if (m != 0.0) { if (m < 0.0) m = __dadd_rn(m, kTwoPi); }
     else m = 0.0;
     if (m > kPi) m = __dsub_rn(m, kTwoPi);
@@ -123,7 +124,7 @@ __global__ void __launch_bounds__(128) ukf_kernel(const UkfArgs a)
     LSLAM_SMEM_DECL;
     constexpr int NG = 32 / G;                 // groups (filters) per warp
     constexpr int DZ = 2 * G;                  // leading dimension of the measurement arrays
-    constexpr int oE = 0, oPxz = 7 * DZ, oK = 10 * DZ, oY = 13 * DZ, oSd = 14 * DZ, oM = 15 * DZ, oS = 18 * DZ;
+    constexpr int oE = 0, oPxz = 7 * DZ, oK = 10 * DZ, oY = 13 * DZ, oSd = 14 * DZ, oM = 15 * DZ, oRd = 18 * DZ, oS = 19 * DZ;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     const int grp = lane / G, g = lane % G;
     double *smw = reinterpret_cast<double *>(smem_raw) + (size_t)warp * ukf_smem_doubles_per_warp(G);
@@ -317,25 +318,41 @@ __global__ void __launch_bounds__(128) ukf_kernel(const UkfArgs a)
                     for (int p = 0; p < j; ++p) t = __fma_rn(-UKF_SM(oS + p * DZ + j), UKF_SM(oS + p * DZ + i), t);
                     UKF_SM(oS + j * DZ + i) = __ddiv_rn(t, d);
                 }
-                if (g == 0) UKF_SM(oS + j * DZ + j) = d;
+                if (g == 0) { UKF_SM(oS + j * DZ + j) = d; UKF_SM(oRd + j) = __ddiv_rn(1.0, d); }   // the solves multiply by 1 / d
             }
             __syncwarp();
         }
         if (m > 0 && !spd) { st |= kUkfStS; }
         const bool upd = m > 0 && spd;
-        // ---- K rows: U^T w = Pxz_r, U k = w (lanes 0..2 of the group, one row each) ----
+        // ---- K rows: U^T w = Pxz_r, U k = w (lanes 0..2 of the group, one row each).  Right-looking: as soon as w_p is
+        //      known it is subtracted from every later right-hand side, so the dependent chain is one division + one fma
+        //      per step instead of a sum of length p; every scalar still sees its terms in the order oracle/ukf.c pins
+        //      (p ascending in the forward solve, descending in the back substitution) ----
         if (upd && g < 3) {
             const int r = g;
-            for (int i = 0; i < dz; ++i) {
-                double s = UKF_SM(oPxz + r * DZ + i);
-                for (int p = 0; p < i; ++p) s = __fma_rn(-UKF_SM(oS + p * DZ + i), UKF_SM(oK + r * DZ + p), s);
-                UKF_SM(oK + r * DZ + i) = __ddiv_rn(s, UKF_SM(oS + i * DZ + i));
+            double w[DZ];
+#pragma unroll
+            for (int i = 0; i < DZ; ++i) w[i] = i < dz ? UKF_SM(oPxz + r * DZ + i) : 0.0;
+#pragma unroll
+            for (int p = 0; p < DZ; ++p) {
+                if (p < dz) {
+                    w[p] = __dmul_rn(w[p], UKF_SM(oRd + p));
+#pragma unroll
+                    for (int i = p + 1; i < DZ; ++i)
+                        if (i < dz) w[i] = __fma_rn(-UKF_SM(oS + p * DZ + i), w[p], w[i]);
+                }
             }
-            for (int i = dz - 1; i >= 0; --i) {
-                double s = UKF_SM(oK + r * DZ + i);
-                for (int p = i + 1; p < dz; ++p) s = __fma_rn(-UKF_SM(oS + i * DZ + p), UKF_SM(oK + r * DZ + p), s);
-                UKF_SM(oK + r * DZ + i) = __ddiv_rn(s, UKF_SM(oS + i * DZ + i));
+#pragma unroll
+            for (int p = DZ - 1; p >= 0; --p) {
+                if (p < dz) {
+                    w[p] = __dmul_rn(w[p], UKF_SM(oRd + p));
+#pragma unroll
+                    for (int i = p - 1; i >= 0; --i) w[i] = __fma_rn(-UKF_SM(oS + i * DZ + p), w[p], w[i]);
+                }
             }
+#pragma unroll
+            for (int i = 0; i < DZ; ++i)
+                if (i < dz) UKF_SM(oK + r * DZ + i) = w[i];
         }
         __syncwarp();
         // ---- M = S K^T: rows 2q, 2q+1 by lane q ----

@@ -61,7 +61,8 @@ static double normalize_angle(double a)
 }
 
 /* upper Cholesky of the n x n matrix c*A (row-major, lda), upper triangle read; U row-major n x n */
-static int chol_upper_scaled(const double *A, int n, int lda, double c, double *U, int ldu)
+/* rdiag: NULL, or receives 1 / U[j][j] (the solves with this factor then multiply instead of dividing) */
+static int chol_upper_scaled(const double *A, int n, int lda, double c, double *U, int ldu, double *rdiag)
 {
     for (int j = 0; j < n; ++j) {
         double s = c * A[j * lda + j];
@@ -69,6 +70,7 @@ static int chol_upper_scaled(const double *A, int n, int lda, double c, double *
         if (!(s > 0.0)) return 1;
         const double d = sqrt(s);
         U[j * ldu + j] = d;
+        if (rdiag) rdiag[j] = 1.0 / d;
         for (int i = j + 1; i < n; ++i) {
             double t = c * A[j * lda + i];
             for (int p = 0; p < j; ++p) t = fma(-U[p * ldu + j], U[p * ldu + i], t);
@@ -82,7 +84,7 @@ static int chol_upper_scaled(const double *A, int n, int lda, double c, double *
 static int sigma_points(const double x[3], const double P[9], double c, double sg[UKF_NS][3])
 {
     double U[9];
-    if (chol_upper_scaled(P, 3, 3, c, U, 3)) return 1;
+    if (chol_upper_scaled(P, 3, 3, c, U, 3, NULL)) return 1;
     for (int i = 0; i < 3; ++i) sg[0][i] = x[i];
     for (int k = 0; k < 3; ++k)
         for (int i = 0; i < 3; ++i) {
@@ -205,18 +207,22 @@ static void ukf_one(double x[3], double P[9], const double u[2], const double *z
             Pxz[i * LD + j] = s;
         }
     /* S = U^T U (upper Cholesky, as above with c = 1); K_r solves K_r S = Pxz_r: U^T w = b, U k = w */
-    if (chol_upper_scaled(S, dz, LD, 1.0, G, LD)) { *status = st | UKF_ST_S; return; }
+    double rd[2 * UKF_LMAX];                                        /* 1 / diagonal of the factor: the two solves multiply */
+    if (chol_upper_scaled(S, dz, LD, 1.0, G, LD, rd)) { *status = st | UKF_ST_S; return; }
     for (int r = 0; r < 3; ++r) {
         double w[2 * UKF_LMAX];
         for (int i = 0; i < dz; ++i) {
             double s = Pxz[r * LD + i];
             for (int p = 0; p < i; ++p) s = fma(-G[p * LD + i], w[p], s);
-            w[i] = s / G[i * LD + i];
+            w[i] = s * rd[i];
         }
+        /* back substitution: the terms of row i are subtracted in DESCENDING column order (p = dz-1 ... i+1), the order
+         * in which the unknowns become available - the CUDA kernel updates every remaining right-hand side as soon as
+         * k_p is known (csrc/ukf.cuh), and this file pins the operation order it is bit-identical to */
         for (int i = dz - 1; i >= 0; --i) {
             double s = w[i];
-            for (int p = i + 1; p < dz; ++p) s = fma(-G[i * LD + p], K[r * LD + p], s);
-            K[r * LD + i] = s / G[i * LD + i];
+            for (int p = dz - 1; p > i; --p) s = fma(-G[i * LD + p], K[r * LD + p], s);
+            K[r * LD + i] = s * rd[i];
         }
     }
     double yr[2 * UKF_LMAX];
