@@ -114,18 +114,9 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
     } else if (!strcmp(key, "ransac.ring")) {
         if (value < 0 || value == 1 || value > 16) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.ring must be 0 or 2..16");
         h->opt_ring = (int)value;
-    } else if (!strcmp(key, "ukf_aug.gemm")) {
-        if (value < 0 || value > 2) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.gemm: 0 default (DMMA fed by TMA), 1 DFMA, 2 DMMA fed by cp.async");
-        h->opt_aug_gemm = (int)value;
     } else if (!strcmp(key, "ukf_aug.pzx")) {
         if (value < 0 || value > 1) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.pzx: 1 default (paired + / - points), 0 literal sum over all sigma points");
         h->opt_aug_pzx = (int)value;
-    } else if (!strcmp(key, "ukf_aug.solve_tile")) {
-        if (value != 0 && value != 64 && value != 128) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.solve_tile: 0 default (32 x 64, 8 warps), 64 (4 warps), 128 (32 x 128)");
-        h->opt_aug_solve_tile = (int)value;
-    } else if (!strcmp(key, "ukf_aug.tile")) {
-        if (value != 0 && value != 64 && value != 128) return fail(h, LSLAM_ERR_BAD_ARG, "ukf_aug.tile: 0 default (32 x 64), 64 (64 x 64), 128 (128 x 128)");
-        h->opt_aug_tile = (int)value;
     } else {
         return fail(h, LSLAM_ERR_BAD_ARG, "unknown option '%s'", key);
     }
@@ -654,43 +645,15 @@ struct AugRun {
         g.lda = lda; g.ldb = ldb; g.ldc = ldc; g.alpha = alpha; g.beta = beta; g.w0 = w0; g.skip = skip; g.upper = upper;
         g.noise = noise; for (int i = 0; i < 9; ++i) g.nq[i] = nq[i];
         g.C2 = C2; g.sC2 = sC2; g.ldc2 = ldc2; g.scale2 = scale2; g.Dinv = nullptr; g.sDinv = 0;
-        g.ktri = h->opt_aug_gemm == 0 ? ktri : 0; g.mirror = mirror;
+        g.ktri = ktri; g.mirror = mirror;
         noise = 0; C2 = nullptr; ktri = 0; mirror = 0;
-        if (h->opt_aug_gemm == 0) {                               // DMMA fed by TMA (default)
-            // CTA tile: 64 x 64, EIGHT consumer warps (4 x 2, warp tile 16 x 32) and THREE CTAs per SM (launch bounds cap the
-            // registers at 72) by default: 24 DMMA warps per SM.  Per 1,024 filters: four warps of 32 x 32 at 3 CTAs/SM (ukf_aug.tile = 64)
-            // 33.9 ms, eight warps at 2 CTAs/SM (96 registers) 33.0 ms, at 3 CTAs/SM 31.6 ms, at 4 CTAs/SM (3 stages, spills) 36.0 ms
-            // (2 x 4 warps: as 4 x 2; 4 x 4 warps: +3.7 ms; 5 ring stages: +0.2 ms) - each with the 4-warp SOLVE kernel.  ukf_aug.tile = 128 selects 128 x 128 (16 consumer warps, one
-            // CTA per SM, half the L2 -> shared traffic per flop): measured SLOWER on B200 (Pzx 2.96 vs 2.54 ms per
-            // 256 filters) - L2 is at 10 % of its throughput with either tile, the DMMA pipe is what saturates.
-            // Also measured and dropped: 64 x 128 with 8 consumer warps (52.4 against 42.4 ms per 1,024 filters) and
-            // 64 x 64 at 4 CTAs per SM (3 stages, 96 registers: 43.7 ms).
-            // Final shape of the big products: 32 x 64 tiles, eight consumer warps of 32 x 8, FOUR CTAs per SM (53 KB, 55
-            // registers) = 32 DMMA warps per SM: 29.6 ms per 1,024 filters (64 x 64 with 8 warps at 3 CTAs/SM, ukf_aug.tile = 64:
-            // 30.8 ms; 32 x 64 at 5 CTAs/SM with 3 stages and 40 registers: 31.3 ms; 2 x 4 warps of 16 x 16: 30.9 ms).
+        // CTA tile of the big products: 32 x 64, eight consumer warps of 32 x 8, FOUR CTAs per SM (53 KB, 55 registers) = 32 DMMA
+        // warps per SM: 29.6 ms per 1,024 filters.  Measured and dropped: 64 x 64 tiles with 4 or 8 warps
+        // (30.8 - 33.9 ms), 128 x 128 (one CTA per SM: slower, L2 was never the limit), 64 x 128, 5 CTAs per SM with 3 stages.
+        {
             const int rc = M <= 32 ? gemm_tma<32, 64, 1, 4>(g, h->aug_attr_set[0])
-                         : (M > 64 && h->opt_aug_tile == 128) ? gemm_tma<128, 128, 4, 4>(g, h->aug_attr_set[3])
-                         : h->opt_aug_tile == 64 ? gemm_tma<64, 64, 4, 2, 4, false, 3>(g, h->aug_attr_set[6])
-                                                 : gemm_tma<32, 64, 1, 8, 4, false, 4>(g, h->aug_attr_set[8]);
+                                   : gemm_tma<32, 64, 1, 8, 4, false, 4>(g, h->aug_attr_set[8]);
             if (rc != LSLAM_OK) return rc;
-        } else if (h->opt_aug_gemm == 2) {                        // DMMA fed by 8-byte cp.async
-            if (M <= 32) {
-                auto kern = aug_gemm_dmma_kernel<32, 64, 1, 4>;
-                LSLAM_LAUNCH(kern, dim3((N + 63) / 64, 1, F), 128, (aug_dmma_smem<32, 64>()), st, g);
-            } else {
-                auto kern = aug_gemm_dmma_kernel<64, 64, 2, 2>;
-                if (!h->aug_attr_set[4]) {
-                    LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)aug_dmma_smem<64, 64>()));
-                    h->aug_attr_set[4] = true;
-                }
-                LSLAM_LAUNCH(kern, dim3((N + 63) / 64, (M + 63) / 64, F), 128, (aug_dmma_smem<64, 64>()), st, g);
-            }
-        } else if (M <= 32) {
-            dim3 grid((N + kAugTile - 1) / kAugTile, 1, F);
-            LSLAM_LAUNCH(aug_gemm_tn_kernel<32>, grid, 256, aug_gemm_smem(32), st, g);
-        } else {
-            dim3 grid((N + kAugTile - 1) / kAugTile, (M + 63) / 64, F);
-            LSLAM_LAUNCH(aug_gemm_tn_kernel<64>, grid, 256, aug_gemm_smem(64), st, g);
         }
         h->launches++;
         return LSLAM_OK;
@@ -707,13 +670,9 @@ struct AugRun {
         g.noise = 0; for (int i = 0; i < 9; ++i) g.nq[i] = 0.0;
         g.C2 = nullptr; g.sC2 = 0; g.ldc2 = 0; g.scale2 = 0.0;
         g.Dinv = Dinv + (size_t)blk * 1024; g.sDinv = sDinv; g.ktri = 0; g.mirror = 0;
-        // 32 x 64 tiles (warp tile 32 x 16, 3 CTAs per SM); ukf_aug.solve_tile = 128 selects 32 x 128 (warp tile 32 x 32,
-        // 2 CTAs per SM): measured slower on B200 (45.1 against 42.4 ms per 1,024 filters at L = 200)
-        // default: EIGHT consumer warps per 32 x 64 tile (warp tile 32 x 8): 32.2 against 33.0 ms per 1,024 filters for four
-        // warps of 32 x 16 (ukf_aug.solve_tile = 64)
-        const int rc = h->opt_aug_solve_tile == 0 ? gemm_tma<32, 64, 1, 8, 3, true, 4>(g, h->aug_attr_set[7])
-                     : h->opt_aug_solve_tile != 128 ? gemm_tma<32, 64, 1, 4, 3, true>(g, h->aug_attr_set[2])
-                                                    : gemm_tma<32, 128, 1, 4, 3, true>(g, h->aug_attr_set[5]);
+        // EIGHT consumer warps per 32 x 64 tile (warp tile 32 x 8), the V tiles parked in the operand ring: 4 CTAs per SM.
+        // Measured and dropped: four warps of 32 x 16 (+ 0.8 ms per 1,024 filters), 32 x 128 tiles (+ 6 %).
+        const int rc = gemm_tma<32, 64, 1, 8, 3, true, 4>(g, h->aug_attr_set[7]);
         if (rc == LSLAM_OK) h->launches++;
         return rc;
     }
@@ -725,49 +684,27 @@ struct AugRun {
     // The inverted diagonal blocks stay in this->Dinv for a following solve with the same factor.
     int chol(double *A, long long sA, int ld, int dim, int32_t *status, int fail_bit)
     {
-        const bool fused = h->opt_aug_gemm == 0;
         for (int jb = 0; jb < dim; jb += 32) {
             const int nb = dim - jb < 32 ? dim - jb : 32;
-            if (fused) {
-                Tmap mu;                                          // the block's 32 columns of the rows above it
-                int rc0 = tmap_encode_3d(h, &mu, A + jb, nb, jb, F, ld, sA, 36);
-                if (rc0 != LSLAM_OK) return rc0;
-                LSLAM_LAUNCH(aug_chol_diag_kernel, dim3(F), 160, kAugDiagSmem, st, A, sA, ld, jb, nb, Dinv + (size_t)(jb / 32) * 1024, sDinv,
-                             status, fail_bit, mu);
-                h->launches++;
-                const int rc = gemm_solve(A + jb, sA, ld, A + jb + nb, sA, ld, A + (size_t)jb * ld + jb + nb, sA, ld, nb, dim - jb - nb, jb,
-                                          jb / 32, status);
-                if (rc != LSLAM_OK) return rc;
-                continue;
-            }
-            if (jb > 0) {
-                const int rc = gemm(A + jb, sA, ld, A + jb, sA, ld, A + (size_t)jb * ld + jb, sA, ld, nb, dim - jb, jb,
-                                    0.0, -1.0, 1.0, status, 1);
-                if (rc != LSLAM_OK) return rc;
-            }
-            LSLAM_LAUNCH(aug_chol_panel_kernel, dim3(F), 256, kAugBlockSmem, st, A, sA, dim, ld, jb, nb, status, fail_bit);
+            Tmap mu;                                              // the block's 32 columns of the rows above it
+            int rc0 = tmap_encode_3d(h, &mu, A + jb, nb, jb, F, ld, sA, 36);
+            if (rc0 != LSLAM_OK) return rc0;
+            LSLAM_LAUNCH(aug_chol_diag_kernel, dim3(F), 160, kAugDiagSmem, st, A, sA, ld, jb, nb, Dinv + (size_t)(jb / 32) * 1024, sDinv,
+                         status, fail_bit, mu);
             h->launches++;
+            const int rc = gemm_solve(A + jb, sA, ld, A + jb + nb, sA, ld, A + (size_t)jb * ld + jb + nb, sA, ld, nb, dim - jb - nb, jb,
+                                      jb / 32, status);
+            if (rc != LSLAM_OK) return rc;
         }
         return LSLAM_OK;
     }
     // W = U^-T W in place (U: dim x dim factor just produced by chol(), W: dim x ncols), block rows top down
     int forward_solve(const double *U, long long sU, int ldu, int dim, double *W, long long sW, int ldw, int ncols, const int32_t *status)
     {
-        const bool fused = h->opt_aug_gemm == 0;
         for (int jb = 0; jb < dim; jb += 32) {
             const int nb = dim - jb < 32 ? dim - jb : 32;
-            if (fused) {
-                const int rc = gemm_solve(U + jb, sU, ldu, W, sW, ldw, W + (size_t)jb * ldw, sW, ldw, nb, ncols, jb, jb / 32, status);
-                if (rc != LSLAM_OK) return rc;
-                continue;
-            }
-            if (jb > 0) {
-                const int rc = gemm(U + jb, sU, ldu, W, sW, ldw, W + (size_t)jb * ldw, sW, ldw, nb, ncols, jb, 0.0, -1.0, 1.0, status, 0);
-                if (rc != LSLAM_OK) return rc;
-            }
-            LSLAM_LAUNCH(aug_trsm_block_kernel, dim3((ncols + 255) / 256, F), 256, kAugBlockSmem, st, U, sU, ldu, W, sW, ldw, ncols, jb, nb, 0,
-                         status);
-            h->launches++;
+            const int rc = gemm_solve(U + jb, sU, ldu, W, sW, ldw, W + (size_t)jb * ldw, sW, ldw, nb, ncols, jb, jb / 32, status);
+            if (rc != LSLAM_OK) return rc;
         }
         return LSLAM_OK;
     }
@@ -844,7 +781,7 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
         // paired cross-covariance (ukf_aug.pzx = 1, default): when the residuals Y are those of sigma points about their own
         // centre (re-draw, or no predict), Pzx = wi sum_r (e_{1+r} - e_{1+n+r}) y_{1+r}^T - half the depth, and only the
         // + half of Y is needed (see the update below)
-        const bool paired = h->opt_aug_pzx != 0 && h->opt_aug_gemm == 0 && (redraw || !pred);
+        const bool paired = h->opt_aug_pzx != 0 && (redraw || !pred);
         // sigma points of (x, P): U^T U = (n + lambda) P.  The points themselves are not stored: every consumer
         // recomputes them from (x, U) (aug_sigma_value)
         LSLAM_LAUNCH(aug_scale_upper_kernel, gew, 256, 0, st, (const double *)a.P, nn, n, a.U, nl, ldn, n, c, (const int32_t *)a.status);

@@ -23,10 +23,7 @@ struct Handle {
     int64_t launches = 0;
     int opt_tpt = 0, opt_slots = 0, opt_threads = 0;
     int opt_kernel = 0, opt_scorers = 0, opt_posts = 0, opt_ring = 0, opt_screen = 0, opt_prefetch = 0;
-    int opt_aug_gemm = 0;              // ukf_aug.gemm: 0 DMMA fed by TMA (default), 1 DFMA, 2 DMMA fed by cp.async
-    int opt_aug_tile = 0;              // ukf_aug.tile: CTA tile of the big GEMMs, 0 default (64), 128
     int opt_aug_pzx = 1;               // ukf_aug.pzx: 1 paired cross-covariance product (default), 0 literal
-    int opt_aug_solve_tile = 0;        // ukf_aug.solve_tile: column tile of the SOLVE GEMMs, 0 default (64), 128
     bool aug_attr_set[10] = {};
     double *express_tab_d = nullptr;   // sin/cos tables of the packet decoder (csrc/express.cuh)
     unsigned long long *counters_d = nullptr;

@@ -25,10 +25,9 @@
 //                   (filterpy forms inv(S) and K explicitly; same x, P to rounding, 129 MFMA less per step)
 //   update          x = xbar + W^T v;  P = Pbar - W^T W, both triangles stored from the GEMM epilogue into the caller's P
 // One GEMM form serves all of them: C[i,j] = beta C[i,j] + alpha sum_k w_k A[k,i] B[k,j] with A and B
-// stored k-major ("TN"), which is how the sigma-point arrays and the factor rows lie in memory.  The default
-// kernel is aug_gemm_tma_kernel (TMA producer warp + DMMA consumer warps); aug_gemm_tn_kernel (DFMA) and
-// aug_gemm_dmma_kernel (cp.async) with the substitution kernels aug_chol_panel_kernel / aug_trsm_block_kernel are
-// the earlier formulations, kept selectable (ukf_aug.gemm = 1, 2) as measured baselines.  DESIGN.md 4.6 has the numbers.
+// stored k-major ("TN"), which is how the sigma-point arrays and the factor rows lie in memory: aug_gemm_tma_kernel
+// (TMA producer warp + DMMA consumer warps).  The earlier formulations (a DFMA tile kernel, DMMA fed by cp.async, substitution-
+// based panel / solve kernels: 2 x slower) were removed from the library in round 2; DESIGN.md 4.6 keeps their numbers.
 #pragma once
 #include "lslam_core.cuh"
 #include "async_copy.cuh"
@@ -89,103 +88,9 @@ __device__ __forceinline__ void aug_gemm_store(const AugGemm &g, double *C, doub
     if (C2 != nullptr) C2[(size_t)i * g.ldc2 + j] = __dmul_rn(g.scale2, v);
 }
 
-constexpr int kAugTile = 64, kAugBK = 16, kAugStages = 3;
-constexpr size_t aug_gemm_smem(int TM) { return (size_t)kAugStages * kAugBK * (TM + kAugTile) * sizeof(double); }
-constexpr size_t kAugBlockSmem = (32 * 33 + 2) * sizeof(double);
+constexpr int kAugBK = 16;
 constexpr size_t kAugMeanSmem = (8 * 32 * 2 + 32) * sizeof(double);
 constexpr size_t kAugUpdateXSmem = 8 * 33 * sizeof(double);
-
-#ifndef LSLAM_EMU
-__device__ __forceinline__ void cp_async8(double *dst_smem, const double *src, bool valid)
-{
-    const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
-    const int bytes = valid ? 8 : 0;               // src-size 0: nothing is read, the 8 bytes are zero-filled
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(d), "l"(src), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-#else
-inline void cp_async8(double *dst, const double *src, bool valid) { *dst = valid ? *src : 0.0; }
-inline void cp_async_commit() {}
-template <int N> inline void cp_async_wait() {}
-#endif
-
-template <int TM>
-__global__ void __launch_bounds__(256) aug_gemm_tn_kernel(const AugGemm g)
-{
-    LSLAM_SMEM_DECL;
-    constexpr int RA = TM / 32;                                       // row pairs per thread (2 or 1)
-    constexpr int STAGE = kAugBK * (TM + kAugTile);                   // doubles per stage: A tile then B tile
-    double *sm = reinterpret_cast<double *>(smem_raw);
-    const int f = blockIdx.z;
-    if (g.skip != nullptr && g.skip[f] != 0) return;
-    const int i0 = blockIdx.y * TM, j0 = blockIdx.x * kAugTile;
-    if (g.upper && i0 > j0 + kAugTile - 1) return;
-    const double *A = g.A + (size_t)f * g.sA, *B = g.B + (size_t)f * g.sB;
-    double *C = g.C + (size_t)f * g.sC, *C2 = g.C2 ? g.C2 + (size_t)f * g.sC2 : nullptr;
-    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-    const int ntiles = (g.K + kAugBK - 1) / kAugBK;
-    auto issue = [&](int t) {
-        if (t < ntiles) {
-            double *as = sm + (size_t)(t % kAugStages) * STAGE, *bs = as + kAugBK * TM;
-            const int k0 = t * kAugBK;
-            for (int e = threadIdx.x; e < kAugBK * TM; e += 256) {
-                const int kk = e / TM, c = e % TM;
-                const bool ok = k0 + kk < g.K && i0 + c < g.M;
-                cp_async8(as + e, ok ? A + (size_t)(k0 + kk) * g.lda + i0 + c : A, ok);
-            }
-            for (int e = threadIdx.x; e < kAugBK * kAugTile; e += 256) {
-                const int kk = e >> 6, c = e & 63;
-                const bool ok = k0 + kk < g.K && j0 + c < g.N;
-                cp_async8(bs + e, ok ? B + (size_t)(k0 + kk) * g.ldb + j0 + c : B, ok);
-            }
-        }
-        cp_async_commit();                                            // one group per tile slot, even when empty
-    };
-    double acc[2 * RA][4];
-#pragma unroll
-    for (int a = 0; a < 2 * RA; ++a)
-#pragma unroll
-        for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
-    issue(0);
-    issue(1);
-    for (int t = 0; t < ntiles; ++t) {
-        cp_async_wait<1>();                                           // tile t has landed (t+1 may be in flight)
-        __syncthreads();                                              // ... for every thread; tile t-1 fully read
-        issue(t + 2);                                                 // refills the stage tile t-1 used
-        const double *as = sm + (size_t)(t % kAugStages) * STAGE, *bs = as + kAugBK * TM;
-#pragma unroll
-        for (int kk = 0; kk < kAugBK; ++kk) {
-            double2 av[RA], bv[2];
-#pragma unroll
-            for (int a = 0; a < RA; ++a) av[a] = *reinterpret_cast<const double2 *>(as + kk * TM + 32 * a + 2 * ty);
-#pragma unroll
-            for (int b = 0; b < 2; ++b) bv[b] = *reinterpret_cast<const double2 *>(bs + kk * kAugTile + 32 * b + 2 * tx);
-#pragma unroll
-            for (int a = 0; a < RA; ++a)
-#pragma unroll
-                for (int b = 0; b < 2; ++b) {
-                    acc[2 * a][2 * b] = fma(av[a].x, bv[b].x, acc[2 * a][2 * b]);
-                    acc[2 * a][2 * b + 1] = fma(av[a].x, bv[b].y, acc[2 * a][2 * b + 1]);
-                    acc[2 * a + 1][2 * b] = fma(av[a].y, bv[b].x, acc[2 * a + 1][2 * b]);
-                    acc[2 * a + 1][2 * b + 1] = fma(av[a].y, bv[b].y, acc[2 * a + 1][2 * b + 1]);
-                }
-        }
-    }
-    cp_async_wait<0>();
-#pragma unroll
-    for (int a = 0; a < 2 * RA; ++a) {
-        const int i = i0 + 32 * (a >> 1) + 2 * ty + (a & 1);
-        if (i >= g.M) continue;
-        const double a0 = g.w0 != 0.0 ? g.w0 * A[i] : 0.0;
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-            const int j = j0 + 32 * (b >> 1) + 2 * tx + (b & 1);
-            if (j >= g.N || (g.upper && j < i)) continue;
-            aug_gemm_store(g, C, C2, B, i, j, a0, acc[a][b]);
-        }
-    }
-}
 
 // ---- the same GEMM on the fp64 tensor-core instruction (DMMA) ---------------------------------------------
 // mma.sync.m8n8k4.f64: one warp instruction = an 8 x 8 x 4 product, 256 FMA, one operand double per lane.
@@ -219,109 +124,6 @@ inline void dmma_m8n8k4(double &c0, double &c1, double a, double b)
     }
 }
 #endif
-
-template <int TM, int TN> constexpr size_t aug_dmma_smem() { return (size_t)kAugStages * kAugBK * (TM + 4 + TN + 4) * sizeof(double); }
-
-// CTA tile TM x TN, WARPS_M x WARPS_N warps, warp tile (TM / WARPS_M) x (TN / WARPS_N).
-template <int TM, int TN, int WARPS_M, int WARPS_N>
-__global__ void __launch_bounds__(32 * WARPS_M * WARPS_N) aug_gemm_dmma_kernel(const AugGemm g)
-{
-    LSLAM_SMEM_DECL;
-    constexpr int NT = 32 * WARPS_M * WARPS_N, WM = TM / WARPS_M, WN = TN / WARPS_N, FM = WM / 8, FN = WN / 8;
-    constexpr int LDA = TM + 4, LDB = TN + 4, STAGE = kAugBK * (LDA + LDB);
-    static_assert(TM % 16 == 0 && TN % 16 == 0 && WM % 8 == 0 && WN % 8 == 0, "tile shape");
-    double *sm = reinterpret_cast<double *>(smem_raw);
-    const int f = blockIdx.z;
-    if (g.skip != nullptr && g.skip[f] != 0) return;
-    const int i0 = blockIdx.y * TM, j0 = blockIdx.x * TN;
-    if (g.upper && i0 > j0 + TN - 1) return;
-    const double *A = g.A + (size_t)f * g.sA, *B = g.B + (size_t)f * g.sB;
-    double *C = g.C + (size_t)f * g.sC, *C2 = g.C2 ? g.C2 + (size_t)f * g.sC2 : nullptr;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int wm0 = (warp / WARPS_N) * WM, wn0 = (warp % WARPS_N) * WN;
-    // fragment liveness (warp-uniform): an 8 x 8 fragment is skipped when it lies outside C or, for an
-    // upper-triangle product, entirely below the diagonal - n = 403 is 6.3 tiles of 64 but 50.4 fragments
-    unsigned live = 0;
-#pragma unroll
-    for (int a = 0; a < FM; ++a)
-#pragma unroll
-        for (int b = 0; b < FN; ++b) {
-            const int fi = i0 + wm0 + 8 * a, fj = j0 + wn0 + 8 * b;
-            if (fi < g.M && fj < g.N && !(g.upper && fi > fj + 7)) live |= 1u << (a * FN + b);
-        }
-    const bool dead = live == 0;
-    const bool full = live == (FM * FN == 32 ? 0xffffffffu : (1u << (FM * FN)) - 1u);
-    const int ntiles = (g.K + kAugBK - 1) / kAugBK;
-    auto issue = [&](int t) {
-        if (t < ntiles) {
-            double *as = sm + (size_t)(t % kAugStages) * STAGE, *bs = as + kAugBK * LDA;
-            const int k0 = t * kAugBK;
-            for (int e = threadIdx.x; e < kAugBK * TM; e += NT) {
-                const int kk = e / TM, c = e % TM;
-                const bool ok = k0 + kk < g.K && i0 + c < g.M;
-                cp_async8(as + kk * LDA + c, ok ? A + (size_t)(k0 + kk) * g.lda + i0 + c : A, ok);
-            }
-            for (int e = threadIdx.x; e < kAugBK * TN; e += NT) {
-                const int kk = e / TN, c = e % TN;
-                const bool ok = k0 + kk < g.K && j0 + c < g.N;
-                cp_async8(bs + kk * LDB + c, ok ? B + (size_t)(k0 + kk) * g.ldb + j0 + c : B, ok);
-            }
-        }
-        cp_async_commit();
-    };
-    double acc[FM][FN][2];
-#pragma unroll
-    for (int a = 0; a < FM; ++a)
-#pragma unroll
-        for (int b = 0; b < FN; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
-    const int frag = (lane & 3), fcol = (lane >> 2);
-    issue(0);
-    issue(1);
-    for (int t = 0; t < ntiles; ++t) {
-        cp_async_wait<1>();
-        __syncthreads();
-        issue(t + 2);
-        if (dead) continue;
-        const double *as = sm + (size_t)(t % kAugStages) * STAGE + wm0 + fcol;
-        const double *bs = sm + (size_t)(t % kAugStages) * STAGE + kAugBK * LDA + wn0 + fcol;
-#pragma unroll
-        for (int ks = 0; ks < kAugBK; ks += 4) {
-            double av[FM], bv[FN];
-#pragma unroll
-            for (int a = 0; a < FM; ++a) av[a] = as[(ks + frag) * LDA + 8 * a];
-#pragma unroll
-            for (int b = 0; b < FN; ++b) bv[b] = bs[(ks + frag) * LDB + 8 * b];
-            if (full) {
-#pragma unroll
-                for (int a = 0; a < FM; ++a)
-#pragma unroll
-                    for (int b = 0; b < FN; ++b) dmma_m8n8k4(acc[a][b][0], acc[a][b][1], av[a], bv[b]);
-            } else {
-#pragma unroll
-                for (int a = 0; a < FM; ++a)
-#pragma unroll
-                    for (int b = 0; b < FN; ++b)
-                        if ((live >> (a * FN + b)) & 1u) dmma_m8n8k4(acc[a][b][0], acc[a][b][1], av[a], bv[b]);
-            }
-        }
-    }
-    cp_async_wait<0>();
-    if (dead) return;
-#pragma unroll
-    for (int a = 0; a < FM; ++a) {
-        const int i = i0 + wm0 + 8 * a + fcol;
-        if (i >= g.M) continue;
-        const double a0 = g.w0 != 0.0 ? g.w0 * A[i] : 0.0;
-#pragma unroll
-        for (int b = 0; b < FN; ++b)
-#pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                const int j = j0 + wn0 + 8 * b + 2 * frag + q;
-                if (j >= g.N || (g.upper && j < i)) continue;
-                aug_gemm_store(g, C, C2, B, i, j, a0, acc[a][b][q]);
-            }
-    }
-}
 
 // ---- the DMMA GEMM fed by the TMA engine (default) ---------------------------------------------------------
 // ncu on the cp.async version above (profiles/r01m_aug_gemm_ncu_summary.txt): DMMA is 7.6 % of the issued
@@ -731,116 +533,6 @@ __global__ void __launch_bounds__(160) aug_chol_diag_kernel(double *Abase, long 
     }
 }
 
-// ---- blocked Cholesky (upper, U^T U = A, in place; only the upper triangle is read / written) --------
-// Panel step jb (width nb <= 32), one CTA per matrix: factor the nb x nb diagonal block, then the panel
-// row U[jb:jb+nb, jb+nb:n] = D^-T A[jb:jb+nb, jb+nb:n].  The trailing update A22 -= panel^T panel is the
-// GEMM above.  A non-positive pivot sets bit `fail_bit` of status[f] (scipy raises LinAlgError) and the
-// matrix is left alone from then on.
-__global__ void __launch_bounds__(256) aug_chol_panel_kernel(double *Abase, long long sA, int n, int lda, int jb, int nb,
-                                                             int32_t *status, int fail_bit)
-{
-    LSLAM_SMEM_DECL;
-    double (*D)[33] = reinterpret_cast<double (*)[33]>(smem_raw);
-    int &bad = *reinterpret_cast<int *>(smem_raw + 32 * 33 * sizeof(double));
-    const int f = blockIdx.x;
-    if (status[f] != 0) return;
-    double *A = Abase + (size_t)f * sA;
-    const int tid = threadIdx.x;
-    if (tid == 0) bad = 0;
-    for (int e = tid; e < nb * nb; e += blockDim.x) {
-        const int r = e / nb, c = e % nb;
-        D[r][c] = c >= r ? A[(size_t)(jb + r) * lda + jb + c] : 0.0;
-    }
-    __syncthreads();
-    // unblocked factorisation of the diagonal block by the first warp (row by row, lanes over columns)
-    if (tid < 32) {
-        for (int j = 0; j < nb; ++j) {
-            double s = D[j][j];
-            for (int k = 0; k < j; ++k) s = fma(-D[k][j], D[k][j], s);
-            if (!(s > 0.0)) { if (tid == 0) bad = 1; break; }
-            const double d = sqrt(s);
-            __syncwarp();
-            if (tid == 0) D[j][j] = d;
-            const int c = j + 1 + tid;
-            if (c < nb) {
-                double v = D[j][c];
-                for (int k = 0; k < j; ++k) v = fma(-D[k][j], D[k][c], v);
-                D[j][c] = v / d;
-            }
-            __syncwarp();
-        }
-    }
-    __syncthreads();
-    if (bad) { if (tid == 0) status[f] |= fail_bit; return; }
-    for (int e = tid; e < nb * nb; e += blockDim.x) {
-        const int r = e / nb, c = e % nb;
-        if (c >= r) A[(size_t)(jb + r) * lda + jb + c] = D[r][c];
-    }
-    // panel row: column c of the panel solves D^T u = a  (forward substitution down the nb rows)
-    for (int c = jb + nb + tid; c < n; c += blockDim.x) {
-        double u[32];
-#pragma unroll
-        for (int r = 0; r < 32; ++r) {
-            if (r < nb) {
-                double v = A[(size_t)(jb + r) * lda + c];
-                for (int k = 0; k < r; ++k) v = fma(-D[k][r], u[k], v);
-                u[r] = v / D[r][r];
-            }
-        }
-#pragma unroll
-        for (int r = 0; r < 32; ++r)
-            if (r < nb) A[(size_t)(jb + r) * lda + c] = u[r];
-    }
-}
-
-// ---- blocked triangular solve W = U^-T [Pzx | r] with S = U^T U (the backward step is kept for callers
-// that want K^T = U^-1 W itself; the filter step does not) ---------------------------------------------
-// forward (U^T W = Pzx) block step: rows [jb, jb+nb) of W, after the GEMM subtracted the rows above:
-//   W[jb+r, :] = (W[jb+r, :] - sum_{k<r} U[jb+k, jb+r] W[jb+k, :]) / U[jb+r, jb+r]
-// backward (U K^T = W) block step, rows descending inside the block:
-//   X[jb+r, :] = (X[jb+r, :] - sum_{k>r} U[jb+r, jb+k] X[jb+k, :]) / U[jb+r, jb+r]
-__global__ void __launch_bounds__(256) aug_trsm_block_kernel(const double *Ubase, long long sU, int ldu, double *Xbase,
-                                                             long long sX, int ldx, int ncols, int jb, int nb, int backward,
-                                                             const int32_t *status)
-{
-    LSLAM_SMEM_DECL;
-    double (*D)[33] = reinterpret_cast<double (*)[33]>(smem_raw);
-    const int f = blockIdx.y;
-    if (status[f] != 0) return;
-    const double *U = Ubase + (size_t)f * sU;
-    double *X = Xbase + (size_t)f * sX;
-    for (int e = threadIdx.x; e < nb * nb; e += blockDim.x) {
-        const int r = e / nb, c = e % nb;
-        D[r][c] = c >= r ? U[(size_t)(jb + r) * ldu + jb + c] : 0.0;
-    }
-    __syncthreads();
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= ncols) return;
-    double x[32];
-    if (!backward) {
-#pragma unroll
-        for (int r = 0; r < 32; ++r) {
-            if (r < nb) {
-                double v = X[(size_t)(jb + r) * ldx + c];
-                for (int k = 0; k < r; ++k) v = fma(-D[k][r], x[k], v);
-                x[r] = v / D[r][r];
-            }
-        }
-    } else {
-#pragma unroll
-        for (int rr = 0; rr < 32; ++rr) {
-            const int r = nb - 1 - rr;
-            if (r >= 0) {
-                double v = X[(size_t)(jb + r) * ldx + c];
-                for (int k = r + 1; k < nb; ++k) v = fma(-D[r][k], x[k], v);
-                x[r] = v / D[r][r];
-            }
-        }
-    }
-#pragma unroll
-    for (int r = 0; r < 32; ++r)
-        if (r < nb) X[(size_t)(jb + r) * ldx + c] = x[r];
-}
 
 // ---- elementwise stages -----------------------------------------------------------------------
 struct AugArgs {

@@ -66,22 +66,6 @@ def test_aug_scratch_is_written_before_it_is_read(flags):
     assert np.isfinite(b[0]).all() and np.isfinite(b[1]).all()
 
 
-@pytest.mark.parametrize("gemm", [1, 2])
-def test_aug_baseline_gemm_paths(gemm):
-    """The earlier formulations (ukf_aug.gemm = 1 DFMA tiles, 2 DMMA fed by cp.async; substitution-based panel and solve
-    kernels) stay selectable as measured baselines and hold the same bar."""
-    x, P, u, z = au.aug_case(2, 18, seed=31)
-    want = au.oracle_aug(x, P, u, z)
-    cond = au.oracle_conditioning(x, P, u, z, want)
-    h = eu.emu_handle()
-    try:
-        h.set_option("ukf_aug.gemm", gemm)
-        xg, Pg, st = eu.emu_ukf_aug_step(x, P, u, z)
-    finally:
-        h.set_option("ukf_aug.gemm", 0)
-    assert not st.any()
-    au.assert_aug_close(want, (xg, Pg), "emu gemm mode %d" % gemm, cond=cond)
-
 
 def test_aug_bad_arguments():
     h = eu.emu_handle()

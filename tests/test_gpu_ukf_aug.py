@@ -58,21 +58,6 @@ def test_aug_literal_and_paired_cross_covariance(gpu_engine, L, F):
     assert dx < 1e-6 and dP < 1e-6, (dx, dP)
 
 
-@pytest.mark.parametrize("gemm", [1, 2])
-def test_aug_baseline_gemm_paths(gpu_engine, gemm):
-    """ukf_aug.gemm = 1 (DFMA tile kernel) and 2 (DMMA fed by cp.async), with the substitution-based panel / solve kernels:
-    the earlier formulations kept as measured baselines hold the same parity bar."""
-    x, P, u, z = au.aug_case(3, 40, seed=77)
-    want = au.oracle_aug(x, P, u, z)
-    cond = au.oracle_conditioning(x, P, u, z, want)
-    try:
-        gpu_engine.set_option("ukf_aug.gemm", gemm)
-        xg, Pg, st = run_gpu(gpu_engine, x, P, u, z)
-    finally:
-        gpu_engine.set_option("ukf_aug.gemm", 0)
-    assert not st.any()
-    au.assert_aug_close(want, (xg, Pg), "gemm mode %d" % gemm, cond=cond)
-
 
 @pytest.mark.parametrize("flags", [1, 2, 3])
 def test_aug_halves(gpu_engine, flags):

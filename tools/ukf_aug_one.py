@@ -1,5 +1,5 @@
 """Time lslam_ukf_aug_step: F augmented filters with L landmarks in the state (n = 3 + 2L).
-usage: ukf_aug_one.py [L] [F] [reps] [gemm: 0 DMMA+TMA (default), 1 DFMA, 2 DMMA+cp.async] [tile: 0 (default 64), 128] [solve_tile] [pzx: 1 paired (default), 0 literal]"""
+usage: ukf_aug_one.py [L] [F] [reps] [pzx: 1 paired (default), 0 literal]"""
 import sys
 
 import numpy as np
@@ -14,13 +14,7 @@ F = int(sys.argv[2]) if len(sys.argv) > 2 else 1024
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 eng = batch.Engine(0)
 if len(sys.argv) > 4:
-    eng.set_option("ukf_aug.gemm", int(sys.argv[4]))
-if len(sys.argv) > 5:
-    eng.set_option("ukf_aug.tile", int(sys.argv[5]))
-if len(sys.argv) > 6:
-    eng.set_option("ukf_aug.solve_tile", int(sys.argv[6]))
-if len(sys.argv) > 7:
-    eng.set_option("ukf_aug.pzx", int(sys.argv[7]))
+    eng.set_option("ukf_aug.pzx", int(sys.argv[4]))
 dev = eng.device
 x, P, u, z = synth.random_aug_filters(min(F, 16), L, seed=0)
 rep = (F + len(x) - 1) // len(x)
