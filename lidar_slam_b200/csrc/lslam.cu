@@ -231,9 +231,11 @@ template <int TPT, int MAXT>
 static int launch_ransac_ws(Handle *h, RansacArgs a, cudaStream_t st)
 {
     auto kern = ransac_ws_kernel<TPT, MAXT>;
-    // chunk slots per tile: about 800 work items (25 rounds of 32), bounded by the ring in shared memory
-    int G = h->opt_slots ? h->opt_slots : (800 + a.ipc / 2) / a.ipc;
-    if (G < 2) G = 2;
+    // chunk slots per tile: about 600 work items, bounded by the ring in shared memory (C3 at 4 trials per item: 2 slots,
+    // 0.607 ms against 0.62 at 4 and 0.79 at 1 - profiles/r2i_ws_sweep_c3.txt)
+    int G = h->opt_slots ? h->opt_slots : (600 + a.ipc / 2) / a.ipc;
+    if (G < 2 && !h->opt_slots) G = 2;
+    if (G < 1) G = 1;
     if ((long long)G > a.nslots) G = (int)a.nslots;
     const int want_nb = h->opt_ring ? h->opt_ring : 3;
     int NB = 0;
@@ -265,10 +267,10 @@ template <int TPT>
 static int dispatch_ransac_ws(Handle *h, RansacArgs a, cudaStream_t st)
 {
     a.ipc = (a.trials + TPT - 1) / TPT;
-    // measured (profiles/r01e_ransac_sweep_ws.json): big chunks want scorers, small chunks want post warps
+    // measured (profiles/r2i_ws_sweep_c3.txt, r01e_ransac_sweep_ws.json): big chunks want scorers, small chunks want post warps
     const bool big = (long long)a.chunk * a.trials >= 65536;
-    a.ws_ns = h->opt_scorers ? h->opt_scorers : (big ? 12 : 8);
-    a.ws_np = h->opt_posts ? h->opt_posts : (big ? 4 : 8);
+    a.ws_ns = h->opt_scorers ? h->opt_scorers : (big ? 14 : 8);
+    a.ws_np = h->opt_posts ? h->opt_posts : (big ? 2 : 8);
     const int warps = a.ws_ns + a.ws_np + 2;
     if (warps > 32) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.scorers + ransac.posts must not exceed 30 warps");
     if (warps <= 20) return launch_ransac_ws<TPT, 640>(h, a, st);
@@ -325,12 +327,13 @@ extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t 
                                            "(chunk=%d, trials=%d)", chunk, trials);
     }
     if (kernel == 2 && pairs != nullptr) kernel = 1;              // the warp-specialised kernel has no explicit-pairs path
-    const int tpt = h->opt_tpt ? h->opt_tpt : ((kernel == 2 && big_chunks) ? 4 : 2);
+    // warp-specialised kernel: 4 trials per work item (measured on C3: 0.607 ms against 0.615 at 2 and 0.69 at 8); phased kernel: 2
+    const int tpt = h->opt_tpt ? h->opt_tpt : (kernel == 2 ? 4 : 2);
     if (kernel == 2) {
         switch (tpt) {
-        case 1: return dispatch_ransac_ws<1>(h, a, st);
         case 2: return dispatch_ransac_ws<2>(h, a, st);
-        default: return dispatch_ransac_ws<4>(h, a, st);
+        case 4: return dispatch_ransac_ws<4>(h, a, st);
+        default: return dispatch_ransac_ws<8>(h, a, st);
         }
     }
     switch (tpt) {

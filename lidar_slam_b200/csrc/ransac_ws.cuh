@@ -21,12 +21,12 @@
 // (full / scored / postdone / free); there is no block-wide barrier after start-up.
 #pragma once
 #include "async_copy.cuh"
-#include "ransac.cuh"
+#include "ransac_tile.cuh"     // the tile kernel's screening arithmetic: tile_screen32, tile_moment_sum / _err, tile_sqrt_up
 
 namespace lslam {
 
 struct WsCtl {                      // per ring buffer
-    Mbar full, scored, postdone, freeb;
+    Mbar full, ready, scored, postdone, freeb;   // ready: the loader has centred the points and filled the slot table
     int next_round;
     int pad;
 };
@@ -34,7 +34,11 @@ struct WsCtl {                      // per ring buffer
 struct WsSlotInfo {                 // written by the loader warp
     unsigned long long scan;        // global scan index (Philox counter words 2, 3)
     int off, n, c, valid;           // first point within the staged tile, points, chunk index, flag
-    int scale_hi, pad;              // high word of the largest |coordinate| of the chunk
+    int scale_hi, force_lit;        // high word of the largest |coordinate| of the chunk; every trial scored literally
+    // screening data of the tile kernel's arithmetic (ransac_tile.cuh): centre, moments of the centred points, bound of
+    // | sum r^2 - M | = alpha + beta M (alpha includes the moment form's own error at the chunk's radius), fp32 band
+    double c0x, c0y, Sx, Sy, Sxx, Sxy, Syy, nn, alpha, beta;
+    float bandf, pad_f;
 };
 
 struct WsRec {                      // post -> epilogue
@@ -49,7 +53,7 @@ struct WsPostScratch {              // per post warp (followed by 2*W mask words
 };
 
 struct WsLayout {
-    size_t ctl, bufs, buf_stride, o_ssf, o_cm, o_pij, o_info, o_rec, post, post_stride, total;
+    size_t ctl, bufs, buf_stride, o_ptsf, o_ssf, o_cm, o_pij, o_info, o_rec, post, post_stride, total;
 };
 
 __host__ __device__ inline size_t align128(size_t b) { return (b + 127) & ~(size_t)127; }
@@ -59,7 +63,8 @@ __host__ __device__ inline WsLayout ws_layout(int G, int chunk, int T, int W, in
     WsLayout L;
     L.ctl = 0;
     L.bufs = align128((size_t)NB * sizeof(WsCtl));
-    L.o_ssf = align128((size_t)G * chunk * 16);
+    L.o_ptsf = align128((size_t)G * chunk * 16);                   // fp64 points first (one bulk copy), then their centred fp32 twins
+    L.o_ssf = L.o_ptsf + align128((size_t)G * ((chunk + 1) & ~1) * 8);
     L.o_cm = L.o_ssf + align128((size_t)G * T * 8);
     L.o_pij = L.o_cm + align128((size_t)G * T * 4);
     L.o_info = L.o_pij + align128((size_t)G * T * 4);
@@ -92,83 +97,134 @@ __device__ __forceinline__ void ws_wait(Mbar *bar, unsigned parity)
 __device__ __forceinline__ uint32_t ws_pack(int cnt, float mab) { return ((uint32_t)__float_as_int(mab) & 0x7fff0000u) | (uint32_t)cnt; }
 
 // ---- scorer: one work item = TPT consecutive trials of one chunk --------------------------------
+// The tile kernel's arithmetic (ransac_tile.cuh): the signed distance in fp32 on the chunk's centred points (2 FFMA +
+// FADD + SHF per point-hypothesis, one FMNMX3 per two), a trial whose closest approach to the threshold is inside the
+// slot's band is handed to the post warps for a literal re-score (packed word 0); the fast residual sum comes from the
+// chunk's moments, once per trial.
+// Called by ALL lanes of a scorer warp (has = the lane has a work item): flagged trials are re-scored literally by the
+// whole warp on the spot and marked exact (packed word 0x7f00....), so the post warps only see finished scores.
+constexpr uint32_t kWsExact = 0x7f000000u;
 template <int TPT>
-__device__ __forceinline__ void ws_score_item(const RansacArgs &a, int item, const WsSlotInfo *info,
-                                              const double2 *pts, double *ssf, uint32_t *cm, uint32_t *pij)
+__device__ __forceinline__ void ws_score_item(const RansacArgs &a, int item, bool has, int lane, const WsSlotInfo *info,
+                                              const double2 *pts, const float2 *ptsf, double *ssf, uint32_t *cm, uint32_t *pij)
 {
+    static_assert(TPT % 2 == 0, "a Philox block serves two trials");
     const int T = a.trials;
-    const int q = item / a.ipc, tb = item - q * a.ipc;
-    const WsSlotInfo g = info[q];
-    const double2 *P = pts + g.off;
+    const int q = has ? item / a.ipc : 0, tb = has ? item - q * a.ipc : 0;
+    const WsSlotInfo *g = info + q;
+    const double2 *P = pts + g->off;
     const int t0 = tb * TPT;
-    const uint32_t n = (uint32_t)g.n;
+    const uint32_t n = (uint32_t)g->n;
+    const bool valid = has && g->valid != 0, force_lit = g->force_lit != 0;
+    const unsigned long long scan = g->scan;
 
-    double nx[TPT], ny[TPT], ng[TPT], ss[TPT];
-    unsigned bits[TPT], pr[TPT];
+    float nx[TPT], ny[TPT], ng[TPT];
+    unsigned bits[TPT];
     int cnt[TPT];
-    float mab[TPT];
-    Philox4 ph;
+    float mab[TPT / 2];
+    unsigned deg = 0;
 #pragma unroll
-    for (int k = 0; k < TPT; ++k) {
-        const int t = t0 + k;
-        if ((k & 1) == 0 || TPT == 1)
-            ph = philox4x32_10((uint32_t)t >> 1, (uint32_t)g.c, (uint32_t)g.scan, (uint32_t)(g.scan >> 32),
-                               (uint32_t)a.seed, (uint32_t)(a.seed >> 32));
-        nx[k] = 0.0; ny[k] = 0.0; ng[k] = 0.0; ss[k] = 0.0;
-        bits[k] = 0u; pr[k] = 0u; cnt[k] = 0; mab[k] = __int_as_float(0x7f800000);
-        if (g.valid && t < T) {
-            int i, j;
-            const bool odd = t & 1;
-            pair_from_words(odd ? ph.r[2] : ph.r[0], odd ? ph.r[3] : ph.r[1], n, i, j);
-            pr[k] = (uint32_t)i | ((uint32_t)j << 16);
-            const FastLine f = fast_pair_model(P[i], P[j]);
-            nx[k] = f.nx; ny[k] = f.ny; ng[k] = f.negc;
-            if (f.degenerate) mab[k] = 0.0f;                     // coincident samples: literal re-score
+    for (int k = 0; k < TPT; k += 2) {
+        const Philox4 ph = philox4x32_10((uint32_t)(t0 + k) >> 1, (uint32_t)g->c, (uint32_t)scan, (uint32_t)(scan >> 32),
+                                         (uint32_t)a.seed, (uint32_t)(a.seed >> 32));
+        mab[k / 2] = __int_as_float(0x7f800000);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int t = t0 + k + h;
+            nx[k + h] = 0.f; ny[k + h] = 0.f; ng[k + h] = 0.f;
+            bits[k + h] = 0u; cnt[k + h] = 0;
+            if (valid && t < T) {
+                int i, j;
+                pair_from_words(h ? ph.r[2] : ph.r[0], h ? ph.r[3] : ph.r[1], n, i, j);
+                pij[q * T + t] = (uint32_t)i | ((uint32_t)j << 16);
+                const FastLine f = fast_pair_model(P[i], P[j]);
+                const double cp = fma(f.nx, g->c0x, fma(f.ny, g->c0y, f.negc));
+                const double a1 = fma(f.nx, g->Sxx, f.ny * g->Sxy), a2 = fma(f.nx, g->Sxy, f.ny * g->Syy);
+                const double M = fma(cp, fma(g->nn, cp, 2.0 * fma(f.nx, g->Sx, f.ny * g->Sy)), fma(f.nx, a1, f.ny * a2));
+                ssf[q * T + t] = M;
+                if (f.degenerate || force_lit || !(fabs(M) <= 1.7976931348623157e308)) deg |= 1u << (k + h);
+                nx[k + h] = (float)f.nx; ny[k + h] = (float)f.ny; ng[k + h] = (float)cp;
+            }
         }
     }
-#define LSLAM_WS_STEP(PT)                                                        \
-    {                                                                            \
-        const double2 p_ = (PT);                                                 \
-        _Pragma("unroll") for (int k_ = 0; k_ < TPT; ++k_) {                     \
-            const double s_ = fma(p_.y, ny[k_], fma(p_.x, nx[k_], ng[k_]));      \
-            ss[k_] = fma(s_, s_, ss[k_]);                                        \
-            const int hi_ = __double2hiint(fabs(s_) - a.thr);                    \
-            bits[k_] = __funnelshift_l((unsigned)hi_, bits[k_], 1);              \
-            mab[k_] = fminf(mab[k_], fabsf(__int_as_float(hi_)));                \
-        }                                                                        \
+    const float thf = (float)a.thr, flim = g->bandf;
+    const float2 *Pf = ptsf + (size_t)q * ((a.chunk + 1) & ~1);
+    const float4 *Pf4 = reinterpret_cast<const float4 *>(Pf);
+#define LSLAM_WS_STEP2(XA, YA, XB, YB)                                                            \
+    {                                                                                             \
+        _Pragma("unroll") for (int k_ = 0; k_ < TPT; k_ += 2) {                                   \
+            const float fa0_ = fabsf(fmaf((YA), ny[k_], fmaf((XA), nx[k_], ng[k_]))) - thf;       \
+            const float fb0_ = fabsf(fmaf((YB), ny[k_], fmaf((XB), nx[k_], ng[k_]))) - thf;       \
+            const float fa1_ = fabsf(fmaf((YA), ny[k_ + 1], fmaf((XA), nx[k_ + 1], ng[k_ + 1]))) - thf; \
+            const float fb1_ = fabsf(fmaf((YB), ny[k_ + 1], fmaf((XB), nx[k_ + 1], ng[k_ + 1]))) - thf; \
+            bits[k_] = __funnelshift_l(__float_as_uint(fa0_), bits[k_], 1);                       \
+            bits[k_] = __funnelshift_l(__float_as_uint(fb0_), bits[k_], 1);                       \
+            bits[k_ + 1] = __funnelshift_l(__float_as_uint(fa1_), bits[k_ + 1], 1);               \
+            bits[k_ + 1] = __funnelshift_l(__float_as_uint(fb1_), bits[k_ + 1], 1);               \
+            mab[k_ / 2] = fminf(fminf(mab[k_ / 2], fminf(fabsf(fa0_), fabsf(fb0_))), fminf(fabsf(fa1_), fabsf(fb1_))); \
+        }                                                                                         \
     }
-    const int n_eff = g.valid ? (int)n : 0;
+    const int n_eff = (valid && !force_lit) ? (int)n : 0;
     int k = 0;
     for (; k + 32 <= n_eff; k += 32) {
-#pragma unroll 8
-        for (int kk = 0; kk < 32; ++kk) LSLAM_WS_STEP(P[k + kk]);
+#pragma unroll 4
+        for (int kk = 0; kk < 32; kk += 2) { const float4 pp = Pf4[(k + kk) >> 1]; LSLAM_WS_STEP2(pp.x, pp.y, pp.z, pp.w); }
 #pragma unroll
         for (int k_ = 0; k_ < TPT; ++k_) cnt[k_] += __popc(bits[k_]);
     }
     const int rem = n_eff - k;
     if (rem > 0) {
-        int kk = 0;
-        for (; kk + 4 <= rem; kk += 4) {
-            LSLAM_WS_STEP(P[k + kk]);
-            LSLAM_WS_STEP(P[k + kk + 1]);
-            LSLAM_WS_STEP(P[k + kk + 2]);
-            LSLAM_WS_STEP(P[k + kk + 3]);
+        // the tail in pairs; an odd last point is paired with itself (its bit is shifted in twice, one shift is undone)
+#pragma unroll 2
+        for (int kk = 0; kk < rem; kk += 2) {
+            float4 pp;
+            if (kk + 1 < rem) pp = Pf4[(k + kk) >> 1];
+            else { const float2 p1 = Pf[k + kk]; pp = make_float4(p1.x, p1.y, p1.x, p1.y); }
+            LSLAM_WS_STEP2(pp.x, pp.y, pp.z, pp.w);
         }
-        for (; kk < rem; ++kk) LSLAM_WS_STEP(P[k + kk]);
+        const int sh = rem & 1;
 #pragma unroll
-        for (int k_ = 0; k_ < TPT; ++k_) cnt[k_] += __popc(bits[k_] & ((1u << rem) - 1u));
+        for (int k_ = 0; k_ < TPT; ++k_) cnt[k_] += __popc((bits[k_] >> sh) << (32 - rem));
     }
-#undef LSLAM_WS_STEP
+#undef LSLAM_WS_STEP2
+    unsigned flagm = 0;
 #pragma unroll
     for (int k_ = 0; k_ < TPT; ++k_) {
         const int t = t0 + k_;
-        if (t < T) {
-            const bool finite = ss[k_] <= 1.7976931348623157e308;
-            ssf[q * T + t] = ss[k_];
-            cm[q * T + t] = ws_pack(cnt[k_], finite ? mab[k_] : 0.0f);
-            pij[q * T + t] = pr[k_];
+        if (valid && t < T) {
+            const bool flagged = ((deg >> k_) & 1u) || mab[k_ / 2] < flim;
+            if (flagged) flagm |= 1u << k_;
+            cm[q * T + t] = ws_pack(cnt[k_], __int_as_float(0x7f800000));
+        } else if (has && t < T) {
+            cm[q * T + t] = ws_pack(0, 0.0f); ssf[q * T + t] = 0.0; pij[q * T + t] = 0u;
         }
     }
+    // flagged trials: literal score by the whole warp, on the spot
+    const ChunkBand cbq = chunk_band(g->scale_hi);
+    if (cbq.bad) flagm = 0;                                       // non-finite chunk: the post warp reports it
+    __syncwarp();                                                 // the pairs written above are read by the other lanes below
+    unsigned fm = __ballot_sync(LSLAM_FULL_MASK, flagm != 0u);
+    unsigned n_relit = 0;
+    while (fm) {
+        const int src = __ffs((int)fm) - 1;
+        fm &= fm - 1;
+        const int fq = __shfl_sync(LSLAM_FULL_MASK, q, src), ft0 = __shfl_sync(LSLAM_FULL_MASK, t0, src);
+        unsigned fl = __shfl_sync(LSLAM_FULL_MASK, flagm, src);
+        const WsSlotInfo *fg = info + fq;
+        const double2 *FP = pts + fg->off;
+        while (fl) {
+            const int kf = __ffs((int)fl) - 1;
+            fl &= fl - 1;
+            const int tt = ft0 + kf;
+            int cl;
+            double sl;
+            const uint32_t pw_ = pij[fq * T + tt];
+            warp_literal_score(FP, fg->n, lit_pair_model(FP[pw_ & 0xffffu], FP[pw_ >> 16]), a.thr, lane, cl, sl, nullptr);
+            ++n_relit;
+            if (lane == src) { cm[fq * T + tt] = kWsExact | (uint32_t)cl; ssf[fq * T + tt] = sl; }
+        }
+    }
+    if (lane == 0 && n_relit) atomicAdd(a.counters + 0, (unsigned long long)n_relit);
 }
 
 // ---- post: from the scores of one chunk to its record, inside one warp --------------------------
@@ -195,9 +251,11 @@ __device__ __forceinline__ void ws_post_chunk(const RansacArgs &a, long long s, 
     if (!g.valid) { ws_rec_status(rec, 0x7fffffff, a, s, lane); return; }    // unused slot
     const int n = g.n;
     const double2 *P = pts + g.off;
-    const ChunkBand cb = chunk_band(g.scale_hi);
+    ChunkBand cb = chunk_band(g.scale_hi);
     if (cb.bad) { ws_rec_status(rec, kStatusNonFinite, a, s, lane); return; }
-    const SsumBound sb = ssum_bound_coeffs(cb.eabs, n, a.thr);
+    cb.force_literal = cb.force_literal || g.force_lit != 0;
+    SsumBound sb;                                                 // | sum r^2 - M | <= alpha + beta M (the loader's slot table)
+    sb.alpha = g.alpha; sb.beta = g.beta; sb.kappa = 0.0;
     int *cq = reinterpret_cast<int *>(cmq);
     int mx = 0, minhi_q = 0x7fffffff, ncand = 0;
     unsigned n_relit = 0;
@@ -212,7 +270,9 @@ __device__ __forceinline__ void ws_post_chunk(const RansacArgs &a, long long s, 
             const uint32_t w = t < T ? cmq[t] : 0x7fff0000u;
             v[k] = t < T ? sq[t] : 0.0;
             cv[k] = t < T ? (int)(w & 0xffffu) : -1;
-            fl[k] = __ballot_sync(LSLAM_FULL_MASK, t < T && (cb.force_literal || (int)(w & 0x7fff0000u) < cb.band_hi));
+            if (t < T && (w & 0x7fff0000u) == kWsExact) cv[k] |= kCntExact;      // re-scored literally by its scorer warp
+            fl[k] = __ballot_sync(LSLAM_FULL_MASK, t < T && (w & 0x7fff0000u) != kWsExact &&
+                                                       (cb.force_literal || (int)(w & 0x7fff0000u) < cb.band_hi));
         }
         if (fl[0] | fl[1] | fl[2] | fl[3]) {                    // literal re-scores (0.16 % of the trials)
 #pragma unroll
@@ -265,7 +325,8 @@ __device__ __forceinline__ void ws_post_chunk(const RansacArgs &a, long long s, 
             const int t = t0 + lane;
             const uint32_t w = t < T ? cmq[t] : 0x7fff0000u;
             int cv = (int)(w & 0xffffu);
-            const bool flag = t < T && (cb.force_literal || (int)(w & 0x7fff0000u) < cb.band_hi);
+            if (t < T && (w & 0x7fff0000u) == kWsExact) cv |= kCntExact;            // re-scored literally by its scorer warp
+            const bool flag = t < T && !(cv & kCntExact) && (cb.force_literal || (int)(w & 0x7fff0000u) < cb.band_hi);
             unsigned m = __ballot_sync(LSLAM_FULL_MASK, flag);
             while (m) {
                 const int tt = t0 + __ffs((int)m) - 1;
@@ -453,6 +514,7 @@ __global__ void __launch_bounds__(MAXT, 1) ransac_ws_kernel(const RansacArgs a)
     if (tid == 0) {
         for (int b = 0; b < NB; ++b) {
             mbar_init(&ctl[b].full, 1);
+            mbar_init(&ctl[b].ready, 1);
             mbar_init(&ctl[b].scored, (unsigned)NS + 1u);
             mbar_init(&ctl[b].postdone, (unsigned)NP);
             mbar_init(&ctl[b].freeb, 1);
@@ -491,7 +553,9 @@ __global__ void __launch_bounds__(MAXT, 1) ransac_ws_kernel(const RansacArgs a)
                 g.off = (int)(bb * a.N + (long long)c * a.chunk - gp0);
                 g.n = n; g.c = c;
                 g.valid = (n >= 2) && (n == a.chunk || n > 2);
-                g.scale_hi = 0; g.pad = 0;
+                g.scale_hi = 0; g.force_lit = 0;
+                g.c0x = 0.0; g.c0y = 0.0; g.Sx = 0.0; g.Sy = 0.0; g.Sxx = 0.0; g.Sxy = 0.0; g.Syy = 0.0;
+                g.nn = (double)n; g.alpha = 0.0; g.beta = 0.0; g.bandf = 0.0f; g.pad_f = 0.0f;
                 info[q] = g;
             }
             __syncwarp();
@@ -505,18 +569,53 @@ __global__ void __launch_bounds__(MAXT, 1) ransac_ws_kernel(const RansacArgs a)
                 bulk_g2s(buf, a.xy + gp0, bytes, &ctl[b].full);
             }
             ws_wait<200>(&ctl[b].full, (unsigned)(use & 1));
-            for (int q = 0; q < nsl; ++q) {                                 // coordinate scale per chunk
+            // per chunk slot, by the whole warp: coordinate scale, the points centred on the chunk's middle point and rounded
+            // to fp32 (what the scorers' loop reads), their moments and radius -> the slot's screening data
+            float2 *ptsf = reinterpret_cast<float2 *>(buf + L.o_ptsf);
+            const int chunk_pad = (a.chunk + 1) & ~1;
+            for (int q = 0; q < nsl; ++q) {
                 const int off = info[q].off, n = info[q].n;
+                const double2 cc = n > 0 ? pts[off + (n >> 1)] : make_double2(0.0, 0.0);
+                float2 *dstf = ptsf + (size_t)q * chunk_pad;
                 int mh = 0;
+                double sx = 0.0, sy = 0.0, sxx = 0.0, sxy = 0.0, syy = 0.0, r2 = 0.0;
                 for (int i = lane; i < n; i += 32) {
                     const double2 p = pts[off + i];
                     const int hx = __double2hiint(p.x) & 0x7fffffff, hy = __double2hiint(p.y) & 0x7fffffff;
                     mh = mh > hx ? mh : hx;
                     mh = mh > hy ? mh : hy;
+                    const double qx = p.x - cc.x, qy = p.y - cc.y;
+                    sx += qx; sy += qy;
+                    sxx = fma(qx, qx, sxx); sxy = fma(qx, qy, sxy); syy = fma(qy, qy, syy);
+                    dstf[i] = make_float2((float)qx, (float)qy);
+                    r2 = fmax(r2, fma(qx, qx, qy * qy));
                 }
                 mh = __reduce_max_sync(LSLAM_FULL_MASK, mh);
-                if (lane == 0) info[q].scale_hi = mh;
+#pragma unroll
+                for (int o = 16; o >= 1; o >>= 1) {
+                    sx += __shfl_xor_sync(LSLAM_FULL_MASK, sx, o);
+                    sy += __shfl_xor_sync(LSLAM_FULL_MASK, sy, o);
+                    sxx += __shfl_xor_sync(LSLAM_FULL_MASK, sxx, o);
+                    sxy += __shfl_xor_sync(LSLAM_FULL_MASK, sxy, o);
+                    syy += __shfl_xor_sync(LSLAM_FULL_MASK, syy, o);
+                    r2 = fmax(r2, __shfl_xor_sync(LSLAM_FULL_MASK, r2, o));
+                }
+                if (lane == 0) {
+                    WsSlotInfo *g = info + q;
+                    const ChunkBand cb = chunk_band(mh);
+                    const double R = (double)tile_sqrt_up(r2);                     // upper bound of the radius (inf / 0: out of range)
+                    const TileScreen32 scr = tile_screen32(R, a.thr);
+                    const SsumBound sb = ssum_bound_coeffs(cb.eabs, n, a.thr);
+                    // the moment form's own error at the largest |cp| a line through two points of the chunk can have (the radius)
+                    const double e2 = tile_moment_err(R, (double)n, sxx + syy);
+                    g->scale_hi = mh;
+                    g->force_lit = (cb.force_literal || scr.force_literal || !(e2 <= 1.7976931348623157e308)) ? 1 : 0;
+                    g->c0x = cc.x; g->c0y = cc.y; g->Sx = sx; g->Sy = sy; g->Sxx = sxx; g->Sxy = sxy; g->Syy = syy;
+                    g->alpha = fma(1.0 + sb.beta, e2, sb.alpha); g->beta = sb.beta; g->bandf = scr.bandf;
+                }
             }
+            __syncwarp();
+            if (lane == 0) { mbar_arrive(&ctl[b].ready); }
             __syncwarp();
             if (lane == 0) mbar_arrive(&ctl[b].scored);
         }
@@ -542,16 +641,16 @@ __global__ void __launch_bounds__(MAXT, 1) ransac_ws_kernel(const RansacArgs a)
             const long long remain = a.nslots - tile * G;
             const int nsl = remain < (long long)G ? (int)remain : G;
             const int items = nsl * a.ipc, nrounds = (items + 31) >> 5;
-            ws_wait<100>(&ctl[b].full, (unsigned)((k / NB) & 1));
+            ws_wait<100>(&ctl[b].ready, (unsigned)((k / NB) & 1));
             for (;;) {
                 int r = 0;
                 if (lane == 0) r = atomicAdd(&ctl[b].next_round, 1);
                 r = __shfl_sync(LSLAM_FULL_MASK, r, 0);
                 if (r >= nrounds) break;
                 const int item = r * 32 + lane;
-                if (item < items)
-                    ws_score_item<TPT>(a, item, reinterpret_cast<const WsSlotInfo *>(buf + L.o_info),
-                                       reinterpret_cast<const double2 *>(buf), reinterpret_cast<double *>(buf + L.o_ssf),
+                ws_score_item<TPT>(a, item, item < items, lane, reinterpret_cast<const WsSlotInfo *>(buf + L.o_info),
+                                       reinterpret_cast<const double2 *>(buf), reinterpret_cast<const float2 *>(buf + L.o_ptsf),
+                                       reinterpret_cast<double *>(buf + L.o_ssf),
                                        reinterpret_cast<uint32_t *>(buf + L.o_cm), reinterpret_cast<uint32_t *>(buf + L.o_pij));
             }
             __syncwarp();
