@@ -9,16 +9,18 @@
 // concurrently on a ring of NB tile buffers in shared memory:
 //   loader    (1 warp)     per tile: slot table (geometry of the G chunk slots), TMA bulk copy of the
 //                          tile's points (cp.async.bulk, SASS UBLKCP, completion on an mbarrier), then
-//                          the per-chunk coordinate scale the re-check band is derived from
-//   scorers   (NS warps)   the hot loop only: thread per (chunk, TPT trials), 3 DFMA + 1 DADD per
-//                          point-hypothesis; rounds of 32 work items are claimed from a shared-memory
-//                          counter, so a warp flows into the next tile as soon as one runs dry
-//   post      (NP warps)   warp per chunk: re-check band, literal re-scores, candidate selection,
-//                          literal tie-break, refit sums -> a small per-slot record
+//                          per chunk: centred fp32 copies of the points, second moments, bound coefficients and
+//                          the fp32 re-check band (the tile kernel's arithmetic, ransac_tile.cuh)
+//   scorers   (NS warps)   the hot loop only: thread per (chunk, TPT trials), fp32 screening of every
+//                          point-hypothesis, residual sum from the chunk moments; rounds of 32 work items are
+//                          claimed from a shared-memory counter, so a warp flows into the next tile as soon as
+//                          one runs dry; a work item's flagged trials are re-scored literally by the whole warp
+//   post      (NP warps)   warp per chunk: candidate selection, literal tie-break, refit sums -> a small
+//                          per-slot record
 //   epilogue  (1 warp)     LANE per chunk slot: the scalar tail (divisions, principal axis, slope,
 //                          intercept, tip) and the result stores, for all slots of a tile at once
-// Tiles flow loader -> scorers -> post -> epilogue -> loader through four mbarriers per ring slot
-// (full / scored / postdone / free); there is no block-wide barrier after start-up.
+// Tiles flow loader -> scorers -> post -> epilogue -> loader through five mbarriers per ring slot
+// (full / ready / scored / postdone / free); there is no block-wide barrier after start-up.
 #pragma once
 #include "async_copy.cuh"
 #include "ransac_tile.cuh"     // the tile kernel's screening arithmetic: tile_screen32, tile_moment_sum / _err, tile_sqrt_up

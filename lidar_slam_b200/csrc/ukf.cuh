@@ -71,7 +71,7 @@ __device__ __forceinline__ void multimem_store(int32_t *mc_addr, int32_t v)
 #endif
 }
 
-__host__ __device__ inline size_t ukf_smem_doubles_per_warp(int G) { return (size_t)(19 * 2 * G + 4 * G * G) * (32 / G); }
+__host__ __device__ inline size_t ukf_smem_doubles_per_warp(int G) { return (size_t)(15 * 2 * G + (G >= 16 ? 4 * G * G : 0)) * (32 / G); }
 
 __device__ __forceinline__ double ukf_normalize_angle(double a)
 {
@@ -124,7 +124,10 @@ __global__ void __launch_bounds__(128) ukf_kernel(const UkfArgs a)
     LSLAM_SMEM_DECL;
     constexpr int NG = 32 / G;                 // groups (filters) per warp
     constexpr int DZ = 2 * G;                  // leading dimension of the measurement arrays
-    constexpr int oE = 0, oPxz = 7 * DZ, oK = 10 * DZ, oY = 13 * DZ, oSd = 14 * DZ, oM = 15 * DZ, oRd = 18 * DZ, oS = 19 * DZ;
+    // shared memory per filter: E [7][DZ] residual columns; Aug [4][DZ] Pxz rows 0..2 and y (the right-hand sides, then W and v);
+    // Row [2][DZ] the current row of U, double-buffered (G <= 8) or the diagonal of S and 1 / diag U (G >= 16); Res [2*DZ]
+    // the nine final sums; S [DZ][DZ] only for G >= 16
+    constexpr int oE = 0, oAug = 7 * DZ, oPxz = oAug, oY = oAug + 3 * DZ, oRow = 11 * DZ, oSd = oRow, oRd = oRow + DZ, oRes = 13 * DZ, oS = 15 * DZ;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     const int grp = lane / G, g = lane % G;
     double *smw = reinterpret_cast<double *>(smem_raw) + (size_t)warp * ukf_smem_doubles_per_warp(G);
@@ -283,115 +286,149 @@ __global__ void __launch_bounds__(128) ukf_kernel(const UkfArgs a)
             for (int i = 0; i < 3; ++i) { UKF_SM(oPxz + i * DZ + 2 * q) = pd[i]; UKF_SM(oPxz + i * DZ + 2 * q + 1) = pb[i]; }
         }
         __syncwarp();
-        // ---- S = sum_k Wc_k e_k e_k^T + R: rows q and dz-1-q by lane q (lower triangle, mirrored) ----
-        if (mine) {
-#pragma unroll 1
-            for (int half = 0; half < 2; ++half) {
-                const int i = half ? dz - 1 - q : q;
-                double ei[7];
+        // The gain K = Pxz S^-1 is never formed: with S = U^T U and the forward solves U^T [w_0 w_1 w_2 v] = [Pxz^T y],
+        // K y = W^T v and K S K^T = W^T W (oracle/ukf.c pins exactly this order).
+        bool spd = true;
+        if constexpr (G <= 8) {
+            // ---- register-resident, right-looking: lane g owns columns c0 = g and c1 = g + G of the upper triangle
+            //      (entries j <= c) and, for g < 4, one right-hand side (Pxz rows 0..2, y) as an extra column ----
+            const int c0 = g, c1 = g + G;
+            double A0[DZ], A1[DZ], A2[DZ];                      // A0 holds G entries; the rest is never touched
+            {
+                double we0[7], we1[7];
 #pragma unroll
-                for (int k = 0; k < 7; ++k) ei[k] = UKF_SM(oE + k * DZ + i);
-                for (int j = 0; j <= i; ++j) {
-                    double s = 0.0;
+                for (int k = 0; k < 7; ++k) {
+                    we0[k] = c0 < dz ? __dmul_rn(Wc[k], UKF_SM(oE + k * DZ + c0)) : 0.0;
+                    we1[k] = c1 < dz ? __dmul_rn(Wc[k], UKF_SM(oE + k * DZ + c1)) : 0.0;
+                }
 #pragma unroll
-                    for (int k = 0; k < 7; ++k) s = __fma_rn(Wc[k], __dmul_rn(ei[k], UKF_SM(oE + k * DZ + j)), s);
-                    if (i == j) {
-                        s = __dadd_rn(s, (i & 1) ? a.var_angle : a.var_dist);
-                        UKF_SM(oSd + i) = s;
+                for (int j = 0; j < DZ; ++j) {
+                    double s0 = 0.0, s1 = 0.0;
+                    if (j < dzmax) {
+#pragma unroll
+                        for (int k = 0; k < 7; ++k) {
+                            const double ej = UKF_SM(oE + k * DZ + j);
+                            if (j < G) s0 = __fma_rn(we0[k], ej, s0);
+                            s1 = __fma_rn(we1[k], ej, s1);
+                        }
                     }
-                    UKF_SM(oS + i * DZ + j) = s;                // strict lower keeps S, upper will hold U
-                    UKF_SM(oS + j * DZ + i) = s;
+                    const double rv = (j & 1) ? a.var_angle : a.var_dist;
+                    if (j < G) A0[j] = (j <= c0 && c0 < dz) ? (j == c0 ? __dadd_rn(s0, rv) : s0) : 0.0;
+                    A1[j] = (j <= c1 && c1 < dz) ? (j == c1 ? __dadd_rn(s1, rv) : s1) : 0.0;
+                    A2[j] = (g < 4 && j < dz) ? UKF_SM(oAug + g * DZ + j) : 0.0;
                 }
             }
-        }
-        __syncwarp();
-        // ---- upper Cholesky U^T U = S in the upper triangle (diagonal included), cooperative ----
-        bool spd = true;
-        for (int j = 0; j < dzmax; ++j) {
-            if (j < dz) {
-                double s = UKF_SM(oSd + j);                     // every lane of the group: the pivot
-                for (int p = 0; p < j; ++p) { const double v = UKF_SM(oS + p * DZ + j); s = __fma_rn(-v, v, s); }
-                if (!(s > 0.0)) spd = false;
-                const double d = __dsqrt_rn(spd ? s : 1.0);
-                for (int i = j + 1 + g; i < dz; i += G) {       // row j of U, columns dealt to the lanes
-                    double t = UKF_SM(oS + i * DZ + j);         // S[j][i] = S[i][j], read from the lower triangle
-                    for (int p = 0; p < j; ++p) t = __fma_rn(-UKF_SM(oS + p * DZ + j), UKF_SM(oS + p * DZ + i), t);
-                    UKF_SM(oS + j * DZ + i) = __ddiv_rn(t, d);
+#pragma unroll
+            for (int p = 0; p < DZ; ++p) {
+                if (p < dzmax) {
+                    const double piv = __shfl_sync(LSLAM_FULL_MASK, p < G ? A0[p] : A1[p], (lane & ~(G - 1)) | (p % G));
+                    const bool ok = piv > 0.0;
+                    if (p < dz && !ok) spd = false;
+                    const double rd = __ddiv_rn(1.0, __dsqrt_rn(ok ? piv : 1.0));
+                    // row p of U: the lane's entries, scaled, and published for the other lanes' updates
+                    if (p < G) { if (c0 > p) { A0[p] = __dmul_rn(A0[p], rd); UKF_SM(oRow + (p & 1) * DZ + c0) = A0[p]; } }
+                    if (c1 > p) { A1[p] = __dmul_rn(A1[p], rd); UKF_SM(oRow + (p & 1) * DZ + c1) = A1[p]; }
+                    A2[p] = __dmul_rn(A2[p], rd);
+                    __syncwarp();
+#pragma unroll
+                    for (int j = p + 1; j < DZ; ++j) {
+                        if (j < dzmax) {
+                            const double u = UKF_SM(oRow + (p & 1) * DZ + j);
+                            if (j < G) { if (j <= c0) A0[j] = __fma_rn(-u, A0[p], A0[j]); }
+                            if (j <= c1) A1[j] = __fma_rn(-u, A1[p], A1[j]);
+                            A2[j] = __fma_rn(-u, A2[p], A2[j]);
+                        }
+                    }
                 }
-                if (g == 0) { UKF_SM(oS + j * DZ + j) = d; UKF_SM(oRd + j) = __ddiv_rn(1.0, d); }   // the solves multiply by 1 / d
+            }
+            if (g < 4) {
+#pragma unroll
+                for (int j = 0; j < DZ; ++j)
+                    if (j < dz) UKF_SM(oAug + g * DZ + j) = A2[j];
+            }
+        } else {
+            // ---- S = sum_k (Wc_k e_ki) e_kj + R: rows q and dz-1-q by lane q (lower triangle, mirrored) ----
+            if (mine) {
+#pragma unroll 1
+                for (int half = 0; half < 2; ++half) {
+                    const int i = half ? dz - 1 - q : q;
+                    double ei[7];
+#pragma unroll
+                    for (int k = 0; k < 7; ++k) ei[k] = __dmul_rn(Wc[k], UKF_SM(oE + k * DZ + i));
+                    for (int j = 0; j <= i; ++j) {
+                        double s = 0.0;
+#pragma unroll
+                        for (int k = 0; k < 7; ++k) s = __fma_rn(ei[k], UKF_SM(oE + k * DZ + j), s);
+                        if (i == j) {
+                            s = __dadd_rn(s, (i & 1) ? a.var_angle : a.var_dist);
+                            UKF_SM(oSd + i) = s;
+                        }
+                        UKF_SM(oS + i * DZ + j) = s;            // strict lower keeps S, upper will hold U
+                        UKF_SM(oS + j * DZ + i) = s;
+                    }
+                }
             }
             __syncwarp();
+            // ---- upper Cholesky U^T U = S in the upper triangle, cooperative; row j scaled by 1 / U_jj ----
+            for (int j = 0; j < dzmax; ++j) {
+                if (j < dz) {
+                    double s = UKF_SM(oSd + j);                 // every lane of the group: the pivot
+                    for (int p = 0; p < j; ++p) { const double v = UKF_SM(oS + p * DZ + j); s = __fma_rn(-v, v, s); }
+                    if (!(s > 0.0)) spd = false;
+                    const double rd = __ddiv_rn(1.0, __dsqrt_rn(spd ? s : 1.0));
+                    for (int i = j + 1 + g; i < dz; i += G) {   // row j of U, columns dealt to the lanes
+                        double t = UKF_SM(oS + i * DZ + j);     // S[j][i] = S[i][j], read from the lower triangle
+                        for (int p = 0; p < j; ++p) t = __fma_rn(-UKF_SM(oS + p * DZ + j), UKF_SM(oS + p * DZ + i), t);
+                        UKF_SM(oS + j * DZ + i) = __dmul_rn(t, rd);
+                    }
+                    if (g == 0) UKF_SM(oRd + j) = rd;
+                }
+                __syncwarp();
+            }
+            // ---- forward solves U^T w = rhs (lanes 0..3 of the group: Pxz rows 0..2, y), right-looking in registers: as soon
+            //      as w_p is known it is subtracted from every later right-hand side ----
+            if (m > 0 && spd && g < 4) {
+                double w[DZ];
+#pragma unroll
+                for (int i = 0; i < DZ; ++i) w[i] = i < dz ? UKF_SM(oAug + g * DZ + i) : 0.0;
+#pragma unroll
+                for (int p = 0; p < DZ; ++p) {
+                    if (p < dz) {
+                        w[p] = __dmul_rn(w[p], UKF_SM(oRd + p));
+#pragma unroll
+                        for (int i = p + 1; i < DZ; ++i)
+                            if (i < dz) w[i] = __fma_rn(-UKF_SM(oS + p * DZ + i), w[p], w[i]);
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < DZ; ++i)
+                    if (i < dz) UKF_SM(oAug + g * DZ + i) = w[i];
+            }
         }
         if (m > 0 && !spd) { st |= kUkfStS; }
         const bool upd = m > 0 && spd;
-        // ---- K rows: U^T w = Pxz_r, U k = w (lanes 0..2 of the group, one row each).  Right-looking: as soon as w_p is
-        //      known it is subtracted from every later right-hand side, so the dependent chain is one division + one fma
-        //      per step instead of a sum of length p; every scalar still sees its terms in the order oracle/ukf.c pins
-        //      (p ascending in the forward solve, descending in the back substitution) ----
-        if (upd && g < 3) {
-            const int r = g;
-            double w[DZ];
-#pragma unroll
-            for (int i = 0; i < DZ; ++i) w[i] = i < dz ? UKF_SM(oPxz + r * DZ + i) : 0.0;
-#pragma unroll
-            for (int p = 0; p < DZ; ++p) {
-                if (p < dz) {
-                    w[p] = __dmul_rn(w[p], UKF_SM(oRd + p));
-#pragma unroll
-                    for (int i = p + 1; i < DZ; ++i)
-                        if (i < dz) w[i] = __fma_rn(-UKF_SM(oS + p * DZ + i), w[p], w[i]);
-                }
-            }
-#pragma unroll
-            for (int p = DZ - 1; p >= 0; --p) {
-                if (p < dz) {
-                    w[p] = __dmul_rn(w[p], UKF_SM(oRd + p));
-#pragma unroll
-                    for (int i = p - 1; i >= 0; --i) w[i] = __fma_rn(-UKF_SM(oS + i * DZ + p), w[p], w[i]);
-                }
-            }
-#pragma unroll
-            for (int i = 0; i < DZ; ++i)
-                if (i < dz) UKF_SM(oK + r * DZ + i) = w[i];
+        __syncwarp();
+        // ---- the nine sums W^T W (6, symmetric) and W^T v (3), dealt to the lanes of the group ----
+        for (int t = g; t < 9; t += G) {
+            const int ri = t < 3 ? 0 : (t < 5 ? 1 : (t < 6 ? 2 : t - 6));
+            const int rj = t < 3 ? t : (t < 5 ? t - 2 : (t < 6 ? 2 : 3));
+            double s = 0.0;
+            if (upd)
+                for (int j = 0; j < dz; ++j) s = __fma_rn(UKF_SM(oAug + ri * DZ + j), UKF_SM(oAug + rj * DZ + j), s);
+            UKF_SM(oRes + t) = s;
         }
         __syncwarp();
-        // ---- M = S K^T: rows 2q, 2q+1 by lane q ----
-        if (upd && mine) {
-#pragma unroll 1
-            for (int half = 0; half < 2; ++half) {
-                const int j = 2 * q + half;
-                double s0 = 0.0, s1 = 0.0, s2 = 0.0;
-                for (int c = 0; c < dz; ++c) {
-                    const double sv = c == j ? UKF_SM(oSd + j) : (c < j ? UKF_SM(oS + j * DZ + c) : UKF_SM(oS + c * DZ + j));
-                    s0 = __fma_rn(sv, UKF_SM(oK + 0 * DZ + c), s0);
-                    s1 = __fma_rn(sv, UKF_SM(oK + 1 * DZ + c), s1);
-                    s2 = __fma_rn(sv, UKF_SM(oK + 2 * DZ + c), s2);
-                }
-                UKF_SM(oM + j * 3 + 0) = s0; UKF_SM(oM + j * 3 + 1) = s1; UKF_SM(oM + j * 3 + 2) = s2;
-            }
-        }
-        __syncwarp();
-        // ---- x = x + K y ; P = P - K M (replicated) ----
+        // ---- x = x + W^T v ; P = P - W^T W (replicated) ----
         if (upd) {
-            double xn[3], Pn[9];
 #pragma unroll
-            for (int i = 0; i < 3; ++i) {
-                double s = 0.0;
-                for (int j = 0; j < dz; ++j) s = __fma_rn(UKF_SM(oK + i * DZ + j), UKF_SM(oY + j), s);
-                xn[i] = __dadd_rn(x[i], s);
-            }
+            for (int i = 0; i < 3; ++i) x[i] = __dadd_rn(x[i], UKF_SM(oRes + 6 + i));
 #pragma unroll
             for (int i = 0; i < 3; ++i)
 #pragma unroll
                 for (int r = 0; r < 3; ++r) {
-                    double s = 0.0;
-                    for (int j = 0; j < dz; ++j) s = __fma_rn(UKF_SM(oK + i * DZ + j), UKF_SM(oM + j * 3 + r), s);
-                    Pn[i * 3 + r] = __dsub_rn(P[i * 3 + r], s);
+                    const int lo = i < r ? i : r, hi = i < r ? r : i;
+                    P[i * 3 + r] = __dsub_rn(P[i * 3 + r], UKF_SM(oRes + (lo == 0 ? hi : (lo == 1 ? 2 + hi : 5))));
                 }
-#pragma unroll
-            for (int i = 0; i < 3; ++i) x[i] = xn[i];
-#pragma unroll
-            for (int i = 0; i < 9; ++i) P[i] = Pn[i];
         }
     }
     // ================= outputs ==================================================================

@@ -19,12 +19,13 @@
  *   means      acc = fma(value_k, Wm_k, acc) for k ascending from acc = 0 ; angles through
  *              atan2(sum Wm sin, sum Wm cos)                                  (UKFMethods.py:37-57)
  *   residuals  a - b, angles through normalize_angle = Python floor-mod 2pi then fold to (-pi, pi]
- *   covariances  C_ij = fma(Wc_k, v_i w_j, C_ij) for k ascending from 0 ; S and P computed on the
- *              lower triangle and mirrored ; + Q / + R after the sum
- *   gain       K = Pxz S^-1 by Cholesky S = G G^T (same recurrence as above) and two triangular
- *              solves per row of Pxz, s = fma(-G, w, s) in ascending index order
- *   update     x = x + K y (acc = fma(K_ij, y_j, acc), j ascending) ; P = P - K (S K^T), both
- *              products as ascending fma sums
+ *   covariances  C_ij = fma(Wc_k, v_i w_j, C_ij) for k ascending from 0 for P and Pxz ; S with the weight folded into the
+ *              row's residual first, S_ij = fma(Wc_k e_ki, e_kj, S_ij) for j <= i, mirrored ; + Q / + R after the sum
+ *   gain       never formed.  S = U^T U (upper Cholesky, the recurrence above, row j scaled by rd_j = 1 / U_jj) ; one
+ *              forward solve U^T [w_0 w_1 w_2 v] = [Pxz_0 Pxz_1 Pxz_2 y]^T, s = fma(-U_pj, w_p, s) for p ascending, then
+ *              w_j = s rd_j.  With K = Pxz S^-1 = W^T U^-T:  K y = W^T v  and  K S K^T = W^T W  exactly, so
+ *   update     x = x + W^T v ; P = P - W^T W, ascending fma sums over the measurement index (filterpy's
+ *              x + K y, P - K S K^T without the back substitution and the two products S K^T, K (S K^T))
  * libm: sin, cos, atan2, sqrt, fmod.  sqrt and fmod are exact in IEEE terms; sin/cos/atan2 differ
  * from the CUDA math library by an ulp or so, which is what the 1e-5 parity tolerance absorbs.
  *
@@ -61,8 +62,7 @@ static double normalize_angle(double a)
 }
 
 /* upper Cholesky of the n x n matrix c*A (row-major, lda), upper triangle read; U row-major n x n */
-/* rdiag: NULL, or receives 1 / U[j][j] (the solves with this factor then multiply instead of dividing) */
-static int chol_upper_scaled(const double *A, int n, int lda, double c, double *U, int ldu, double *rdiag)
+static int chol_upper_scaled(const double *A, int n, int lda, double c, double *U, int ldu)
 {
     for (int j = 0; j < n; ++j) {
         double s = c * A[j * lda + j];
@@ -70,7 +70,6 @@ static int chol_upper_scaled(const double *A, int n, int lda, double c, double *
         if (!(s > 0.0)) return 1;
         const double d = sqrt(s);
         U[j * ldu + j] = d;
-        if (rdiag) rdiag[j] = 1.0 / d;
         for (int i = j + 1; i < n; ++i) {
             double t = c * A[j * lda + i];
             for (int p = 0; p < j; ++p) t = fma(-U[p * ldu + j], U[p * ldu + i], t);
@@ -81,10 +80,29 @@ static int chol_upper_scaled(const double *A, int n, int lda, double c, double *
     return 0;
 }
 
+/* upper Cholesky S = U^T U of the n x n matrix A (upper triangle read); row j is scaled by rd[j] = 1 / U[j][j] */
+static int chol_upper_rd(const double *A, int n, int lda, double *U, int ldu, double *rd)
+{
+    for (int j = 0; j < n; ++j) {
+        double s = A[j * lda + j];
+        for (int p = 0; p < j; ++p) s = fma(-U[p * ldu + j], U[p * ldu + j], s);
+        if (!(s > 0.0)) return 1;
+        const double d = sqrt(s);
+        U[j * ldu + j] = d;
+        rd[j] = 1.0 / d;
+        for (int i = j + 1; i < n; ++i) {
+            double t = A[j * lda + i];
+            for (int p = 0; p < j; ++p) t = fma(-U[p * ldu + j], U[p * ldu + i], t);
+            U[j * ldu + i] = t * rd[j];
+        }
+    }
+    return 0;
+}
+
 static int sigma_points(const double x[3], const double P[9], double c, double sg[UKF_NS][3])
 {
     double U[9];
-    if (chol_upper_scaled(P, 3, 3, c, U, 3, NULL)) return 1;
+    if (chol_upper_scaled(P, 3, 3, c, U, 3)) return 1;
     for (int i = 0; i < 3; ++i) sg[0][i] = x[i];
     for (int k = 0; k < 3; ++k)
         for (int i = 0; i < 3; ++i) {
@@ -191,64 +209,49 @@ static void ukf_one(double x[3], double P[9], const double u[2], const double *z
         yk[k][2] = normalize_angle(sf[k][2] - x[2]);
     }
     static const int LD = 2 * UKF_LMAX;
-    double S[2 * UKF_LMAX * 2 * UKF_LMAX], G[2 * UKF_LMAX * 2 * UKF_LMAX], Pxz[3 * 2 * UKF_LMAX], K[3 * 2 * UKF_LMAX];
-    for (int i = 0; i < dz; ++i)
+    double S[2 * UKF_LMAX * 2 * UKF_LMAX], G[2 * UKF_LMAX * 2 * UKF_LMAX], Pxz[3 * 2 * UKF_LMAX];
+    for (int i = 0; i < dz; ++i) {
+        double we[UKF_NS];
+        for (int k = 0; k < UKF_NS; ++k) we[k] = Wc[k] * e[k][i];
         for (int j = 0; j <= i; ++j) {
             double s = 0.0;
-            for (int k = 0; k < UKF_NS; ++k) s = fma(Wc[k], e[k][i] * e[k][j], s);
+            for (int k = 0; k < UKF_NS; ++k) s = fma(we[k], e[k][j], s);
             if (i == j) s = s + ((i & 1) ? pr->var_angle : pr->var_dist);
             S[i * LD + j] = s;
             S[j * LD + i] = s;
         }
+    }
     for (int i = 0; i < 3; ++i)
         for (int j = 0; j < dz; ++j) {
             double s = 0.0;
             for (int k = 0; k < UKF_NS; ++k) s = fma(Wc[k], yk[k][i] * e[k][j], s);
             Pxz[i * LD + j] = s;
         }
-    /* S = U^T U (upper Cholesky, as above with c = 1); K_r solves K_r S = Pxz_r: U^T w = b, U k = w */
-    double rd[2 * UKF_LMAX];                                        /* 1 / diagonal of the factor: the two solves multiply */
-    if (chol_upper_scaled(S, dz, LD, 1.0, G, LD, rd)) { *status = st | UKF_ST_S; return; }
-    for (int r = 0; r < 3; ++r) {
-        double w[2 * UKF_LMAX];
-        for (int i = 0; i < dz; ++i) {
-            double s = Pxz[r * LD + i];
-            for (int p = 0; p < i; ++p) s = fma(-G[p * LD + i], w[p], s);
-            w[i] = s * rd[i];
-        }
-        /* back substitution: the terms of row i are subtracted in DESCENDING column order (p = dz-1 ... i+1), the order
-         * in which the unknowns become available - the CUDA kernel updates every remaining right-hand side as soon as
-         * k_p is known (csrc/ukf.cuh), and this file pins the operation order it is bit-identical to */
-        for (int i = dz - 1; i >= 0; --i) {
-            double s = w[i];
-            for (int p = dz - 1; p > i; --p) s = fma(-G[i * LD + p], K[r * LD + p], s);
-            K[r * LD + i] = s * rd[i];
-        }
-    }
     double yr[2 * UKF_LMAX];
     for (int q = 0; q < m; ++q) {
         yr[2 * q] = zz[2 * q] - zp[2 * q];
         yr[2 * q + 1] = normalize_angle(zz[2 * q + 1] - zp[2 * q + 1]);
     }
-    double xn[3];
+    /* S = U^T U; forward solves U^T w_r = Pxz_r (r = 0..2) and U^T v = y: K is never formed (header) */
+    double rd[2 * UKF_LMAX];
+    if (chol_upper_rd(S, dz, LD, G, LD, rd)) { *status = st | UKF_ST_S; return; }
+    double w[4][2 * UKF_LMAX];
+    for (int r = 0; r < 4; ++r)
+        for (int i = 0; i < dz; ++i) {
+            double s = r < 3 ? Pxz[r * LD + i] : yr[i];
+            for (int p = 0; p < i; ++p) s = fma(-G[p * LD + i], w[r][p], s);
+            w[r][i] = s * rd[i];
+        }
+    double xn[3], Pn[9];
     for (int i = 0; i < 3; ++i) {
         double s = 0.0;
-        for (int j = 0; j < dz; ++j) s = fma(K[i * LD + j], yr[j], s);
+        for (int j = 0; j < dz; ++j) s = fma(w[i][j], w[3][j], s);
         xn[i] = x[i] + s;
     }
-    /* P = P - K (S K^T) */
-    double M[2 * UKF_LMAX * 3];
-    for (int j = 0; j < dz; ++j)
-        for (int r = 0; r < 3; ++r) {
-            double s = 0.0;
-            for (int q = 0; q < dz; ++q) s = fma(S[j * LD + q], K[r * LD + q], s);
-            M[j * 3 + r] = s;
-        }
-    double Pn[9];
     for (int i = 0; i < 3; ++i)
         for (int r = 0; r < 3; ++r) {
             double s = 0.0;
-            for (int j = 0; j < dz; ++j) s = fma(K[i * LD + j], M[j * 3 + r], s);
+            for (int j = 0; j < dz; ++j) s = fma(w[i][j], w[r][j], s);
             Pn[i * 3 + r] = P[i * 3 + r] - s;
         }
     memcpy(x, xn, sizeof xn);
