@@ -71,7 +71,11 @@ __device__ __forceinline__ void multimem_store(int32_t *mc_addr, int32_t v)
 #endif
 }
 
-__host__ __device__ inline size_t ukf_smem_doubles_per_warp(int G) { return (size_t)(15 * 2 * G + (G >= 16 ? 4 * G * G : 0)) * (32 / G); }
+constexpr int kUkfHandoff = 33;               // doubles per filter handed from the predict to the update: x 3, P 9, sigma points 21
+__host__ __device__ inline size_t ukf_smem_doubles_per_warp(int G)
+{
+    return (size_t)(kUkfHandoff + 1) * 32 + (size_t)(15 * 2 * G + (G >= 16 ? 4 * G * G : 0)) * (32 / G);
+}
 
 __device__ __forceinline__ double ukf_normalize_angle(double a)
 {
@@ -122,18 +126,21 @@ template <int G>
 __global__ void __launch_bounds__(128) ukf_kernel(const UkfArgs a)
 {
     LSLAM_SMEM_DECL;
-    constexpr int NG = 32 / G;                 // groups (filters) per warp
+    constexpr int NG = 32 / G;                 // groups (filters) per warp and pass
     constexpr int DZ = 2 * G;                  // leading dimension of the measurement arrays
-    // shared memory per filter: E [7][DZ] residual columns; Aug [4][DZ] Pxz rows 0..2 and y (the right-hand sides, then W and v);
-    // Row [2][DZ] the current row of U, double-buffered (G <= 8) or the diagonal of S and 1 / diag U (G >= 16); Res [2*DZ]
-    // the nine final sums; S [DZ][DZ] only for G >= 16
+    // shared memory per filter of a pass: E [7][DZ] residual columns; Aug [4][DZ] Pxz rows 0..2 and y (the right-hand sides, then
+    // W and v); Row [2][DZ] the current row of U, double-buffered (G <= 8) or the diagonal of S and 1 / diag U (G >= 16);
+    // Res [2*DZ] the nine final sums; S [DZ][DZ] only for G >= 16
     constexpr int oE = 0, oAug = 7 * DZ, oPxz = oAug, oY = oAug + 3 * DZ, oRow = 11 * DZ, oSd = oRow, oRd = oRow + DZ, oRes = 13 * DZ, oS = 15 * DZ;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     const int grp = lane / G, g = lane % G;
-    double *smw = reinterpret_cast<double *>(smem_raw) + (size_t)warp * ukf_smem_doubles_per_warp(G);
+    // per warp: the hand-off area of its 32 filters (x, P, sigma points; element e of filter l at e * 32 + l, then status and
+    // flags as ints), then the scratch of the NG filters of a pass
+    double *H = reinterpret_cast<double *>(smem_raw) + (size_t)warp * ukf_smem_doubles_per_warp(G);
+    int *Hi = reinterpret_cast<int *>(H + kUkfHandoff * 32);
+    double *smw = H + (kUkfHandoff + 1) * 32;
 #define UKF_SM(e) smw[(e) * NG + grp]
-    const long long f = ((long long)blockIdx.x * nwarps + warp) * NG + grp;
-    const bool live = f < a.F;
+    const long long fb = ((long long)blockIdx.x * nwarps + warp) * 32;    // the warp's first filter
     const unsigned gmask = (G == 32 ? 0xffffffffu : ((1u << G) - 1u)) << (grp * G);
 
     double Wm[7], Wc[7];
@@ -141,88 +148,113 @@ __global__ void __launch_bounds__(128) ukf_kernel(const UkfArgs a)
     for (int k = 0; k < 7; ++k) { Wm[k] = a.wi; Wc[k] = a.wi; }
     Wm[0] = a.wm0; Wc[0] = a.wc0;
 
-    double x[3] = {0.0, 0.0, 0.0}, P[9] = {1.0, 0.0, 0.0, 0.0, 1.0, 0.0, 0.0, 0.0, 1.0};
-    double sf[7][3];
+    // ================= predict: THREAD per filter (lane l owns filter fb + l) ===================
+    {
+        const long long f = fb + lane;
+        const bool live = f < a.F;
+        double x[3] = {0.0, 0.0, 0.0}, P[9] = {1.0, 0.0, 0.0, 0.0, 1.0, 0.0, 0.0, 0.0, 1.0};
+        double sf[7][3];
+        int st = 0;
+        bool run = live, wrote_prior = false;
+        if (live) {
+#pragma unroll
+            for (int i = 0; i < 3; ++i) x[i] = a.x[f * 3 + i];
+#pragma unroll
+            for (int i = 0; i < 9; ++i) P[i] = a.P[f * 9 + i];
+        }
+#pragma unroll
+        for (int k = 0; k < 7; ++k) { sf[k][0] = 0.0; sf[k][1] = 0.0; sf[k][2] = 0.0; }
+        if (a.flags & kUkfPredict) {
+            double sg[7][3];
+            if (run && !ukf_sigma_points(x, P, a.cscale, sg)) { st = kUkfStSigma; run = false; }
+            if (run) {
+                const double u0 = a.u ? a.u[f * 2] : 0.0, u1 = a.u ? a.u[f * 2 + 1] : 0.0;
+                const double wth = __dmul_rn(a.dt, __dadd_rn(__dmul_rn(-a.r_over_l, u0), __dmul_rn(a.r_over_l, u1)));
+                double a0 = 0.0, a1 = 0.0, ss = 0.0, sc = 0.0;
+#pragma unroll
+                for (int k = 0; k < 7; ++k) {                   // UKFMethods.py:17-24
+                    double sn, cs;
+                    sincos(sg[k][2], &sn, &cs);
+                    const double rc = __dmul_rn(a.half_r, cs), rs = __dmul_rn(a.half_r, sn);
+                    sf[k][0] = __dadd_rn(sg[k][0], __dmul_rn(a.dt, __dadd_rn(__dmul_rn(rc, u0), __dmul_rn(rc, u1))));
+                    sf[k][1] = __dadd_rn(sg[k][1], __dmul_rn(a.dt, __dadd_rn(__dmul_rn(rs, u0), __dmul_rn(rs, u1))));
+                    sf[k][2] = __dadd_rn(sg[k][2], wth);
+                    sincos(sf[k][2], &sn, &cs);                 // UKFMethods.py:37-45
+                    ss = __fma_rn(sn, Wm[k], ss);
+                    sc = __fma_rn(cs, Wm[k], sc);
+                    a0 = __fma_rn(sf[k][0], Wm[k], a0);
+                    a1 = __fma_rn(sf[k][1], Wm[k], a1);
+                }
+                x[0] = a0; x[1] = a1; x[2] = atan2(ss, sc);
+                double Pn[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};  // lower triangle 00 10 11 20 21 22
+#pragma unroll
+                for (int k = 0; k < 7; ++k) {
+                    const double y0 = __dsub_rn(sf[k][0], x[0]), y1 = __dsub_rn(sf[k][1], x[1]);
+                    const double y2 = ukf_normalize_angle(__dsub_rn(sf[k][2], x[2]));
+                    Pn[0] = __fma_rn(Wc[k], __dmul_rn(y0, y0), Pn[0]);
+                    Pn[1] = __fma_rn(Wc[k], __dmul_rn(y1, y0), Pn[1]);
+                    Pn[2] = __fma_rn(Wc[k], __dmul_rn(y1, y1), Pn[2]);
+                    Pn[3] = __fma_rn(Wc[k], __dmul_rn(y2, y0), Pn[3]);
+                    Pn[4] = __fma_rn(Wc[k], __dmul_rn(y2, y1), Pn[4]);
+                    Pn[5] = __fma_rn(Wc[k], __dmul_rn(y2, y2), Pn[5]);
+                }
+                P[0] = __dadd_rn(Pn[0], a.Q[0]); P[1] = __dadd_rn(Pn[1], a.Q[1]); P[2] = __dadd_rn(Pn[3], a.Q[2]);
+                P[3] = __dadd_rn(Pn[1], a.Q[3]); P[4] = __dadd_rn(Pn[2], a.Q[4]); P[5] = __dadd_rn(Pn[4], a.Q[5]);
+                P[6] = __dadd_rn(Pn[3], a.Q[6]); P[7] = __dadd_rn(Pn[4], a.Q[7]); P[8] = __dadd_rn(Pn[5], a.Q[8]);
+                if (a.flags & kUkfRedraw) {                     // a failed re-draw: the prior stands, the update is skipped
+                    if (!ukf_sigma_points(x, P, a.cscale, sf)) { st = kUkfStRedraw; run = false; wrote_prior = true; }
+                }
+                if (run && a.sigmas_f != nullptr) {
+#pragma unroll
+                    for (int k = 0; k < 7; ++k)
+#pragma unroll
+                        for (int i = 0; i < 3; ++i) a.sigmas_f[(f * 7 + k) * 3 + i] = sf[k][i];
+                }
+            }
+        } else if (a.flags & kUkfUpdate) {
+            if (run) {
+                if (a.sigmas_f != nullptr) {
+#pragma unroll
+                    for (int k = 0; k < 7; ++k)
+#pragma unroll
+                        for (int i = 0; i < 3; ++i) sf[k][i] = a.sigmas_f[(f * 7 + k) * 3 + i];
+                } else if (!ukf_sigma_points(x, P, a.cscale, sf)) { st = kUkfStRedraw; run = false; }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 3; ++i) H[i * 32 + lane] = x[i];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) H[(3 + i) * 32 + lane] = P[i];
+#pragma unroll
+        for (int k = 0; k < 7; ++k)
+#pragma unroll
+            for (int i = 0; i < 3; ++i) H[(12 + k * 3 + i) * 32 + lane] = sf[k][i];
+        Hi[lane] = st;
+        Hi[32 + lane] = (run ? 1 : 0) | (wrote_prior ? 2 : 0);
+    }
+    __syncwarp();
+
+    // ================= update: a GROUP of G lanes per filter, NG filters per pass ================
+    if (a.flags & kUkfUpdate) {
+#pragma unroll 1
+    for (int pass = 0; pass < G; ++pass) {
+    if (fb + (long long)pass * NG >= a.F) break;
+    const int fl = pass * NG + grp;
+    const long long f = fb + fl;
+    const bool run = (Hi[32 + fl] & 1) != 0;
     int st = 0;
-    bool run = live;
-    if (live) {
+    double x[3], P[9], sf[7][3];
 #pragma unroll
-        for (int i = 0; i < 3; ++i) x[i] = a.x[f * 3 + i];
+    for (int i = 0; i < 3; ++i) x[i] = H[i * 32 + fl];
 #pragma unroll
-        for (int i = 0; i < 9; ++i) P[i] = a.P[f * 9 + i];
-    }
+    for (int i = 0; i < 9; ++i) P[i] = H[(3 + i) * 32 + fl];
 #pragma unroll
-    for (int k = 0; k < 7; ++k) { sf[k][0] = 0.0; sf[k][1] = 0.0; sf[k][2] = 0.0; }
-
-    // ================= predict (replicated over the lanes of the group) =======================
-    if (a.flags & kUkfPredict) {
-        double sg[7][3];
-        if (run && !ukf_sigma_points(x, P, a.cscale, sg)) { st = kUkfStSigma; run = false; }
-        if (run) {
-            const double u0 = a.u ? a.u[f * 2] : 0.0, u1 = a.u ? a.u[f * 2 + 1] : 0.0;
-            const double wth = __dmul_rn(a.dt, __dadd_rn(__dmul_rn(-a.r_over_l, u0), __dmul_rn(a.r_over_l, u1)));
-            double a0 = 0.0, a1 = 0.0, ss = 0.0, sc = 0.0;
+    for (int k = 0; k < 7; ++k)
 #pragma unroll
-            for (int k = 0; k < 7; ++k) {                       // UKFMethods.py:17-24
-                double sn, cs;
-                sincos(sg[k][2], &sn, &cs);
-                const double rc = __dmul_rn(a.half_r, cs), rs = __dmul_rn(a.half_r, sn);
-                sf[k][0] = __dadd_rn(sg[k][0], __dmul_rn(a.dt, __dadd_rn(__dmul_rn(rc, u0), __dmul_rn(rc, u1))));
-                sf[k][1] = __dadd_rn(sg[k][1], __dmul_rn(a.dt, __dadd_rn(__dmul_rn(rs, u0), __dmul_rn(rs, u1))));
-                sf[k][2] = __dadd_rn(sg[k][2], wth);
-                sincos(sf[k][2], &sn, &cs);                     // UKFMethods.py:37-45
-                ss = __fma_rn(sn, Wm[k], ss);
-                sc = __fma_rn(cs, Wm[k], sc);
-                a0 = __fma_rn(sf[k][0], Wm[k], a0);
-                a1 = __fma_rn(sf[k][1], Wm[k], a1);
-            }
-            x[0] = a0; x[1] = a1; x[2] = atan2(ss, sc);
-            double Pn[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};      // lower triangle 00 10 11 20 21 22
-#pragma unroll
-            for (int k = 0; k < 7; ++k) {
-                const double y0 = __dsub_rn(sf[k][0], x[0]), y1 = __dsub_rn(sf[k][1], x[1]);
-                const double y2 = ukf_normalize_angle(__dsub_rn(sf[k][2], x[2]));
-                Pn[0] = __fma_rn(Wc[k], __dmul_rn(y0, y0), Pn[0]);
-                Pn[1] = __fma_rn(Wc[k], __dmul_rn(y1, y0), Pn[1]);
-                Pn[2] = __fma_rn(Wc[k], __dmul_rn(y1, y1), Pn[2]);
-                Pn[3] = __fma_rn(Wc[k], __dmul_rn(y2, y0), Pn[3]);
-                Pn[4] = __fma_rn(Wc[k], __dmul_rn(y2, y1), Pn[4]);
-                Pn[5] = __fma_rn(Wc[k], __dmul_rn(y2, y2), Pn[5]);
-            }
-            P[0] = __dadd_rn(Pn[0], a.Q[0]); P[1] = __dadd_rn(Pn[1], a.Q[1]); P[2] = __dadd_rn(Pn[3], a.Q[2]);
-            P[3] = __dadd_rn(Pn[1], a.Q[3]); P[4] = __dadd_rn(Pn[2], a.Q[4]); P[5] = __dadd_rn(Pn[4], a.Q[5]);
-            P[6] = __dadd_rn(Pn[3], a.Q[6]); P[7] = __dadd_rn(Pn[4], a.Q[7]); P[8] = __dadd_rn(Pn[5], a.Q[8]);
-            bool wrote_prior = false;
-            if (a.flags & kUkfRedraw) {
-                if (!ukf_sigma_points(x, P, a.cscale, sf)) { st = kUkfStRedraw; run = false; wrote_prior = true; }
-            }
-            if (wrote_prior && g == 0) {                        // prior stands, update skipped
-#pragma unroll
-                for (int i = 0; i < 3; ++i) a.x[f * 3 + i] = x[i];
-#pragma unroll
-                for (int i = 0; i < 9; ++i) a.P[f * 9 + i] = P[i];
-            }
-            if (run && a.sigmas_f != nullptr && g == 0) {
-#pragma unroll
-                for (int k = 0; k < 7; ++k)
-#pragma unroll
-                    for (int i = 0; i < 3; ++i) a.sigmas_f[(f * 7 + k) * 3 + i] = sf[k][i];
-            }
-        }
-    } else if (a.flags & kUkfUpdate) {
-        if (run) {
-            if (a.sigmas_f != nullptr) {
-#pragma unroll
-                for (int k = 0; k < 7; ++k)
-#pragma unroll
-                    for (int i = 0; i < 3; ++i) sf[k][i] = a.sigmas_f[(f * 7 + k) * 3 + i];
-            } else if (!ukf_sigma_points(x, P, a.cscale, sf)) { st = kUkfStRedraw; run = false; }
-        }
-    }
-
+        for (int i = 0; i < 3; ++i) sf[k][i] = H[(12 + k * 3 + i) * 32 + fl];
     // ================= update ===================================================================
     int m = 0, sel = 0;
-    if (a.flags & kUkfUpdate) {
+    {
         const bool ok = run && g < a.L && (a.lm_valid == nullptr || a.lm_valid[f * a.L + g] >= a.valid_min);
         const unsigned bits = (__ballot_sync(LSLAM_FULL_MASK, ok) & gmask) >> (grp * G);
         m = __popc(bits);
@@ -430,40 +462,56 @@ __global__ void __launch_bounds__(128) ukf_kernel(const UkfArgs a)
                     P[i * 3 + r] = __dsub_rn(P[i * 3 + r], UKF_SM(oRes + (lo == 0 ? hi : (lo == 1 ? 2 + hi : 5))));
                 }
         }
-    }
-    // ================= outputs ==================================================================
-    if (live && g == 0) {
-        if (run) {
+        if (g == 0 && (upd || st != 0)) {                       // the posterior (and the status) back into the hand-off area
+            if (upd) {
 #pragma unroll
-            for (int i = 0; i < 3; ++i) a.x[f * 3 + i] = x[i];
+                for (int i = 0; i < 3; ++i) H[i * 32 + fl] = x[i];
 #pragma unroll
-            for (int i = 0; i < 9; ++i) a.P[f * 9 + i] = P[i];
+                for (int i = 0; i < 9; ++i) H[(3 + i) * 32 + fl] = P[i];
+            }
+            Hi[fl] |= st;
         }
-        if (a.status != nullptr) a.status[f] = st;
+    }
+    __syncwarp();
+    }   // pass
+    }   // update
+    __syncwarp();
+    // ================= outputs: thread per filter ================================================
+    {
+        const long long f = fb + lane;
+        if (f < a.F) {
+            const int fl = Hi[32 + lane];
+            if (fl != 0) {                                      // ran, or stopped after writing the prior
+#pragma unroll
+                for (int i = 0; i < 3; ++i) a.x[f * 3 + i] = H[i * 32 + lane];
+#pragma unroll
+                for (int i = 0; i < 9; ++i) a.P[f * 9 + i] = H[(3 + i) * 32 + lane];
+            }
+            if (a.status != nullptr) a.status[f] = Hi[lane];
+        }
     }
     // ================= fused all-gather over peer memory =========================================
-    // The group publishes what this call left in (x, P) - and the slots' landmark ids - into record
-    // gather_first + f of EVERY rank's gather buffer: one multimem store per element when the buffers have a
-    // multicast mapping (NVSwitch replicates it), else one peer store per rank over NVLink.  The stores
-    // are fire-and-forget and overlap the remaining filters' arithmetic; the caller orders them
-    // against the readers with a cross-rank barrier after the kernel (lidar_slam_b200/dist.py).
+    // The warp publishes what this call left in (x, P) of its 32 filters - and the slots' landmark ids - into records
+    // gather_first + f of EVERY rank's gather buffer, consecutive lanes to consecutive addresses: one multimem store per
+    // element when the buffers have a multicast mapping (NVSwitch replicates it), else one peer store per rank over
+    // NVLink.  The stores are fire-and-forget and overlap the other warps' arithmetic; the caller orders them against the
+    // readers with a cross-rank barrier after the kernel (lidar_slam_b200/dist.py).
     if (a.gather_world > 0) {
-        __syncwarp();
-        if (live) {
-            const size_t rec = (size_t)a.gather_first + (size_t)f;
-            for (int e = g; e < 12; e += G) {
-                const double v = e < 3 ? a.x[f * 3 + e] : a.P[f * 9 + (e - 3)];
-                if (a.gather_state_mc != nullptr) multimem_store(a.gather_state_mc + rec * 12 + e, v);
+        const long long left = a.F - fb;
+        const int nf = left >= 32 ? 32 : (left > 0 ? (int)left : 0);
+        const size_t rec0 = (size_t)a.gather_first + (size_t)fb;
+        for (int idx = lane; idx < nf * 12; idx += 32) {
+            const double v = H[(idx % 12) * 32 + idx / 12];
+            if (a.gather_state_mc != nullptr) multimem_store(a.gather_state_mc + rec0 * 12 + idx, v);
+            else
+                for (int p = 0; p < a.gather_world; ++p) a.gather_state[p][rec0 * 12 + idx] = v;
+        }
+        if (a.gather_ids != nullptr) {
+            for (int idx = lane; idx < nf * a.gather_L; idx += 32) {
+                const int32_t v = a.gather_ids[fb * a.gather_L + idx];
+                if (a.gather_ids_mc != nullptr) multimem_store(a.gather_ids_mc + rec0 * a.gather_L + idx, v);
                 else
-                    for (int p = 0; p < a.gather_world; ++p) a.gather_state[p][rec * 12 + e] = v;
-            }
-            if (a.gather_ids != nullptr) {
-                for (int e = g; e < a.gather_L; e += G) {
-                    const int32_t v = a.gather_ids[f * a.gather_L + e];
-                    if (a.gather_ids_mc != nullptr) multimem_store(a.gather_ids_mc + rec * a.gather_L + e, v);
-                    else
-                        for (int p = 0; p < a.gather_world; ++p) a.gather_idbuf[p][rec * a.gather_L + e] = v;
-                }
+                    for (int p = 0; p < a.gather_world; ++p) a.gather_idbuf[p][rec0 * a.gather_L + idx] = v;
             }
         }
     }
