@@ -231,7 +231,9 @@ int lslam_ukf_update(void *handle, double *x, double *P, const double *z, int32_
  * 2n + 1 sigma points.  The gain is applied through the Cholesky factor of S and one forward solve
  * W = U^-T [Pzx | r]: x = xbar + W^T v, P = Pbar - W^T W (filterpy forms inv(S) and K; same x, P to rounding).
  *   x [F,n], P [F,n,n] in/out;  u [F,2] or NULL;  z [F,L,2] (range, bearing) per landmark;
- *   params_h, flags, status as for lslam_ukf_step; a filter whose status is non-zero keeps its (x, P).
+ *   params_h, flags, status as for lslam_ukf_step, with the same resulting state: LSLAM_UKF_ST_SIGMA leaves (x, P) untouched;
+ *   after a predict, LSLAM_UKF_ST_REDRAW / LSLAM_UKF_ST_S leave the PRIOR (filterpy's predict() has stored it before the
+ *   re-draw, and only update() fails) - bit for bit what a predict-only call returns.
  *   workspace: device scratch; filters are processed in batches of as many as fit
  *   (lslam_ukf_aug_workspace_bytes(L, k) bytes hold k filters; at least one must fit).  1 <= L <= 1024.
  *   The workspace must be 16-byte aligned (its arrays are read through TMA tensor maps).

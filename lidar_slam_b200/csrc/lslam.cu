@@ -852,6 +852,10 @@ extern "C" int lslam_ukf_aug_step(void *handle, double *x, double *P, const doub
             h->launches++;
             run.mirror = 1; run.C2 = a.P; run.sC2 = nn; run.ldc2 = n; run.scale2 = 1.0;
             AUG_TRY(run.gemm(a.Kt, zn, n1, a.Kt, zn, n1, a.Pbar, nl, ldn, n, n, dz, 0.0, -1.0, 1.0, a.status, 1));
+            if (pred) {                                           // failed re-draw / S after a predict: the prior stands
+                LSLAM_LAUNCH(aug_commit_prior_kernel, gew, 256, 0, st, a);
+                h->launches++;
+            }
         } else {
             LSLAM_LAUNCH(aug_commit_kernel, gew, 256, 0, st, a, xres, (const double *)a.Pbar);
             h->launches++;

@@ -810,4 +810,20 @@ __global__ void aug_commit_kernel(const AugArgs a, const double *xnew, const dou
     }
 }
 
+// A filter whose re-draw (prior not positive definite) or S factorisation failed after a predict keeps the PRIOR, as
+// filterpy does (predict() has stored x, P before the sigma points are re-drawn) and as the n = 3 kernel does: the
+// later kernels skipped it, so xbar and the upper triangle of Pbar still hold what the predict left.
+__global__ void aug_commit_prior_kernel(const AugArgs a)
+{
+    const int f = blockIdx.y;
+    const int st = a.status[f];
+    if ((st & (kUkfStRedraw | kUkfStS)) == 0 || (st & kUkfStSigma) != 0) return;
+    const long long nn = (long long)a.n * a.n, nl = (long long)a.n * a.ldn;
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < nn; e += (long long)gridDim.x * blockDim.x) {
+        const int r = (int)(e / a.n), c = (int)(e % a.n);
+        a.P[(size_t)f * nn + e] = a.Pbar[(size_t)f * nl + (c >= r ? (long long)r * a.ldn + c : (long long)c * a.ldn + r)];
+        if (e < a.n) a.x[(size_t)f * a.n + e] = a.xbar[(size_t)f * a.ldn + e];
+    }
+}
+
 } // namespace lslam

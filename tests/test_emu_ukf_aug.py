@@ -82,3 +82,30 @@ def test_aug_bad_arguments():
         h.ukf_aug_step(eu.ptr(x), eu.ptr(P), eu.ptr(u), eu.ptr(z), 1, 0, par, 7, eu.ptr(st), eu.ptr(ws), ws.size)
     with pytest.raises(LslamError):
         h.ukf_aug_workspace_bytes(0, 1)
+
+
+def test_failed_redraw_or_S_leaves_the_prior_in_both_filters():
+    """filterpy's predict() has stored the prior before the sigma points are re-drawn, and update() is what fails on a
+    bad S: in both cases the filter is left at the PRIOR.  The n = 3 kernel and the augmented path must agree on that
+    (status LSLAM_UKF_ST_REDRAW = 2 / LSLAM_UKF_ST_S = 4): the result equals a predict-only call bit for bit."""
+    from oracle import cport
+    bad_q = cport.ukf_params(Q=-1e3 * np.eye(3))            # prior covariance not positive definite -> re-draw fails
+    bad_r = cport.ukf_params(var_dist=-1e12)                # S not positive definite
+    x, P, u, z = au.aug_case(3, 3, seed=9)
+    for params, bit in ((bad_q, 2), (bad_r, 4)):
+        prior = eu.emu_ukf_aug_step(x, P, u, None, params=params, flags=1)
+        got = eu.emu_ukf_aug_step(x, P, u, z, params=params, flags=7, workspace_filters=2)
+        assert got[2].tolist() == [bit] * 3 and not prior[2].any()
+        assert np.array_equal(got[0], prior[0]) and np.array_equal(got[1], prior[1])
+        assert not np.array_equal(got[0], x)
+    # the same two failures in the n = 3 filter
+    rng = np.random.default_rng(4)
+    F, L = 5, 4
+    x3 = rng.normal(0, 1, (F, 3)); P3 = np.tile(np.diag([.1, .1, .05]), (F, 1, 1)); u3 = rng.uniform(.5, 1.5, (F, 2))
+    lm = rng.normal(0, 1500, (F, L, 2))
+    z3 = np.stack([np.hypot(lm[..., 0], lm[..., 1]), np.arctan2(lm[..., 1], lm[..., 0])], -1)
+    for params, bit in ((bad_q, 2), (bad_r, 4)):
+        prior = eu.emu_ukf_step(x3, P3, u3, None, None, params=params, flags=1)
+        got = eu.emu_ukf_step(x3, P3, u3, z3, lm, params=params, flags=7)
+        assert got[2].tolist() == [bit] * F and not prior[2].any()
+        assert np.array_equal(got[0], prior[0]) and np.array_equal(got[1], prior[1])

@@ -170,3 +170,36 @@ def test_aug_against_extended_precision_truth(gpu_engine):
                 assert rms(ge) <= max(1e-5, 1.5 * rms(oe)), "pzx=%d: rms %s error %.3g against the oracle's %.3g" % (mode, name, rms(ge), rms(oe))
     finally:
         gpu_engine.set_option("ukf_aug.pzx", 1)
+
+
+def test_failed_redraw_or_S_leaves_the_prior_in_both_filters(gpu_engine):
+    """As tests/test_emu_ukf_aug.py: a failed re-draw (status 2) or S factorisation (status 4) after a predict leaves
+    the PRIOR - bit for bit what a predict-only call returns - in the augmented path and in the n = 3 kernel."""
+    import torch
+    from oracle import cport
+    eng = gpu_engine
+    bad_q = cport.ukf_params(Q=-1e3 * np.eye(3))
+    bad_r = cport.ukf_params(var_dist=-1e12)
+    x, P, u, z = au.aug_case(5, 40, seed=9)
+    for params, bit in ((bad_q, 2), (bad_r, 4)):
+        prior = run_gpu(eng, x, P, u, z, flags=1, params=params)
+        got = run_gpu(eng, x, P, u, z, flags=7, params=params, workspace_filters=2)
+        assert got[2].tolist() == [bit] * 5 and not prior[2].any()
+        assert np.array_equal(got[0], prior[0]) and np.array_equal(got[1], prior[1])
+        assert not np.array_equal(got[0], x)
+    rng = np.random.default_rng(4)
+    F, L = 70, 8
+    lm = rng.normal(0, 1500, (F, L, 2))
+    z3 = torch.from_numpy(np.stack([np.hypot(lm[..., 0], lm[..., 1]), np.arctan2(lm[..., 1], lm[..., 0])], -1)).to(eng.device)
+    lmt = torch.from_numpy(lm).to(eng.device)
+    for params, bit in ((bad_q, 2), (bad_r, 4)):
+        outs = []
+        for flags in (1, 7):
+            st = eng.alloc_ukf(F, L)
+            st["params"] = list(params)
+            st["u"].fill_(1.0)
+            eng.ukf_step(st, z3, lmt, flags=flags)
+            torch.cuda.synchronize()
+            outs.append((st["x"].cpu().numpy(), st["P"].cpu().numpy(), st["status"].cpu().numpy()))
+        assert outs[1][2].tolist() == [bit] * F and not outs[0][2].any()
+        assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
