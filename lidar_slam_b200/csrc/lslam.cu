@@ -108,9 +108,6 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
     } else if (!strcmp(key, "ransac.scorers") || !strcmp(key, "ransac.posts")) {
         if (value < 0 || value > 29) return fail(h, LSLAM_ERR_BAD_ARG, "%s out of range (0..29)", key);
         (key[7] == 's' ? h->opt_scorers : h->opt_posts) = (int)value;
-    } else if (!strcmp(key, "ransac.prefetch")) {
-        if (value < -1 || value > (1 << 20)) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.prefetch: 0 off (default), 1 one wave of CTAs ahead, n tiles ahead");
-        h->opt_prefetch = (int)value;
     } else if (!strcmp(key, "ransac.ring")) {
         if (value < 0 || value == 1 || value > 16) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.ring must be 0 or 2..16");
         h->opt_ring = (int)value;
@@ -188,16 +185,9 @@ static int launch_ransac_tile(Handle *h, RansacArgs a, int threads, cudaStream_t
     if (need < threads) threads = need;
     a.G = G;
     a.inv_thr = 1.0 / a.thr;
-    // CTAs resident at a time (registers: MINB per SM by the launch bounds; shared memory) = how far ahead a CTA prefetches
-    int per_sm = (int)((size_t)h->smem_sm / (smem + 1024));
-    if (per_sm > MINB * MAXT / threads) per_sm = MINB * MAXT / threads;
-    if (per_sm < 1) per_sm = 1;
-    // measured on B200 (C2): no gain from the prefetch (4.66 against 4.55 ms at 256 threads) - off unless asked for;
-    // ransac.prefetch = 1 asks for one wave of CTAs ahead
-    a.prefetch_ahead = h->opt_prefetch <= 0 ? 0 : (h->opt_prefetch == 1 ? per_sm * h->sms : h->opt_prefetch);
+    LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long grid = (a.nslots + G - 1) / G;
     if (grid > 0x7fffffffLL) return fail(h, LSLAM_ERR_CAPACITY, "batch too large for one launch");
-    LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     LSLAM_LAUNCH(kern, (unsigned)grid, (unsigned)threads, smem, st, a);
     h->launches++;
     LSLAM_CUDA_TRY(h, cudaGetLastError());
@@ -310,7 +300,7 @@ extern "C" int lslam_ransac_lines(void *handle, const double *xy, const int32_t 
     const bool big_chunks = (long long)chunk * trials >= 65536;
     cudaStream_t st = (cudaStream_t)stream;
     a.ws_ns = a.ws_np = a.ws_nb = 0;
-    a.inv_thr = 0.0; a.prefetch_ahead = 0;
+    a.inv_thr = 0.0;
     a.pairs = pairs;
     if (pairs != nullptr && ((uintptr_t)pairs & 7) != 0) return fail(h, LSLAM_ERR_BAD_ARG, "lslam_ransac_lines: pairs must be 8-byte aligned");
     // tile kernel: 512-thread CTAs (20 chunk slots at 100 trials, two CTAs per SM) measured best on C2: 4.33 against 4.55 ms at 256

@@ -52,7 +52,6 @@ struct RansacArgs {
     int ws_ns, ws_np, ws_nb;        // warp-specialised kernel: scorer warps, post warps, ring depth
     const int32_t *pairs;           // [B,C,trials,2] explicit sample pairs, or nullptr = the Philox sampler
     double inv_thr;                 // 1 / thr (tile kernel: keeps a division out of the per-slot set-up)
-    int prefetch_ahead;             // tile kernel: CTA b prefetches tile b + prefetch_ahead towards L2 (0 = off)
 };
 
 constexpr int kMaxCand = 8;         // candidates with precomputed models; more -> generic loop

@@ -22,8 +22,9 @@
 //   * every trial's inlier bits are kept in shared memory (one STS per 32 points), so the winner's mask is read,
 //     not rebuilt;
 //   * one work item (TPT trials of one chunk) per thread, per-trial results stay in registers; the chunk-wide
-//     maximum (count, then smallest upper bound of the residual sum) is ONE 64-bit shared-memory atomicMax per
-//     thread; trials flagged for the literal formula are re-scored warp-cooperatively on the spot;
+//     maximum (count, then smallest upper bound of the residual sum) is a max-scan over the slot's lanes and one 64-bit
+//     shared-memory atomicMax by its last lane; trials with a point too close to the threshold are re-scored
+//     warp-cooperatively on the spot, with the fp64 fast line first and the literal formula only if that is too close as well;
 //   * three block barriers per tile (stage+moments | score | candidates | decide+refit+stores by lane groups).
 #pragma once
 #include "ransac.cuh"
@@ -48,30 +49,43 @@ struct TileSlot {
     int scale_hi;                      // high word of the largest |coordinate| of the slot
     int force_lit;                     // every trial is scored literally (threshold / scale outside the fast path's range)
     int mx, ncand, status;
+    int band_hi;                       // high word of the fp64 re-check band 2^(e2-36) (chunk_band)
     int best_t, best_i, best_j;
-    int mask_base, mask_stride;        // the winner's inlier words: mw[mask_base + w * mask_stride]
     int cand_exact;                    // bit p: candidate p was re-scored literally (its count / mask are the literal ones)
     int cand_t[kMaxCand], cand_i[kMaxCand], cand_j[kMaxCand];
 };
 
+// Shared memory of a CTA: two regions of equal size.  Region p holds a tile's points (fp64, then the centred fp32 copies),
+// region p ^ 1 its per-trial scratch (tie-break keys, inlier words of every trial); the winner's inlier words are copied out
+// of the scratch into `smask` when the candidates are collected.  The phase functions below take the parity p so that a CTA
+// can walk several tiles with the roles swapping (stage tile i + 1 into the dead scratch of tile i while tile i is refitted);
+// the kernel as shipped runs one tile per CTA with p = 0 - the persistent form measured slower.
 struct TileSmem {
-    double2 *pts;
-    float2 *ptsf;       // fp32 screening: the points centred on the slot's middle point, slot q at q * chunk_pad
-    int2 *keys;         // [G][TPT][ipc] (key_down(lower bound), key_up(upper bound)) of every trial's residual sum
-    uint32_t *mw;       // [G][W][TPT][ipc] inlier words of every trial, then [G][W] literal winner masks
+    unsigned char *region0;    // region p at region0 + p * rbytes (no arrays here: an index known at run time would put them in local memory)
+    size_t rbytes;
+    uint32_t *smask;    // [G][W] the winner's inlier words
     uint32_t *wtmp;     // [nwarps][W]
-    TileSlot *slot;
-    int smask0;         // index of the literal winner masks inside mw
+    unsigned char *slot0;      // slot state of the tile whose points are in region p: at slot0 + p * sbytes
+    size_t sbytes;
+    __device__ __forceinline__ unsigned char *region(int p) const { return region0 + (size_t)p * rbytes; }
+    __device__ __forceinline__ TileSlot *slot(int p) const { return reinterpret_cast<TileSlot *>(slot0 + (size_t)p * sbytes); }
+    size_t ptsf_off, mw_off;   // byte offsets inside a region: points | fp32 copies,  keys | trial masks
 };
+
+__host__ __device__ inline size_t tile_region_bytes(int G, int chunk, int ipc, int tpt, int W, bool f32)
+{
+    size_t pts = (size_t)G * chunk * 16;
+    if (f32) pts += (size_t)G * ((chunk + 1) & ~1) * 8;
+    const size_t scr = (size_t)G * tpt * ipc * 8 + (size_t)G * W * tpt * ipc * 4;
+    return align16(pts > scr ? pts : scr);
+}
 
 __host__ __device__ inline size_t tile_smem_bytes(int G, int chunk, int ipc, int tpt, int W, int nwarps, bool f32)
 {
-    size_t b = (size_t)G * chunk * 16;
-    if (f32) b += (size_t)G * ((chunk + 1) & ~1) * 8;
-    b += (size_t)G * tpt * ipc * 8;
-    b += align16(((size_t)G * W * tpt * ipc + (size_t)G * W) * 4);
+    size_t b = 2 * tile_region_bytes(G, chunk, ipc, tpt, W, f32);
+    b += align16((size_t)G * W * 4);
     b += align16((size_t)nwarps * W * 4);
-    b += align16((size_t)G * sizeof(TileSlot));
+    b += 2 * align16((size_t)G * sizeof(TileSlot));
     return b;
 }
 
@@ -79,13 +93,13 @@ __device__ __forceinline__ TileSmem tile_carve(unsigned char *raw, int G, int ch
 {
     TileSmem s;
     unsigned char *p = raw;
-    s.pts = reinterpret_cast<double2 *>(p);  p += (size_t)G * chunk * 16;
-    s.ptsf = reinterpret_cast<float2 *>(p);  if (f32) p += (size_t)G * ((chunk + 1) & ~1) * 8;
-    s.keys = reinterpret_cast<int2 *>(p);    p += (size_t)G * tpt * ipc * 8;
-    s.mw = reinterpret_cast<uint32_t *>(p);  p += align16(((size_t)G * W * tpt * ipc + (size_t)G * W) * 4);
-    s.smask0 = G * W * tpt * ipc;
-    s.wtmp = reinterpret_cast<uint32_t *>(p); p += align16((size_t)nwarps * W * 4);
-    s.slot = reinterpret_cast<TileSlot *>(p);
+    const size_t rb = tile_region_bytes(G, chunk, ipc, tpt, W, f32);
+    s.region0 = p; s.rbytes = rb; p += 2 * rb;
+    s.ptsf_off = (size_t)G * chunk * 16;
+    s.mw_off = (size_t)G * tpt * ipc * 8;
+    s.smask = reinterpret_cast<uint32_t *>(p); p += align16((size_t)G * W * 4);
+    s.wtmp = reinterpret_cast<uint32_t *>(p);  p += align16((size_t)nwarps * W * 4);
+    s.slot0 = p; s.sbytes = align16((size_t)G * sizeof(TileSlot));
     return s;
 }
 
@@ -117,6 +131,9 @@ __device__ __forceinline__ bool tile_fast_ok(double thr, int scale_hi)
 // add O(2^-40 R):  delta = 4.25e-7 R (7 u = 4.172e-7) bounds | |s_f| - r_literal |.  The test runs on f = |s_f| - thr_f,
 // thr_f = fl32(thr) (|thr_f - thr| <= u thr; the subtraction is exact near zero and otherwise off by a factor 1 + u):
 //   |f| >= bandf = (delta + u thr)(1 + 2^-20)  ==>  sign(f) is the literal decision r < thr.
+// The fp64 side (the Newton-refined normal, cp, and the literal residual itself, whose origin fl((p_i + p_j) / 2) is rounded at
+// the chunk's coordinate scale S) adds at most ~2^-51 S; the slack between delta and 7 u R is 2^-26.9 R, so the screening is
+// only used while S <= 2^22 R (a cluster of points 4 million radii away from the origin is scored literally).
 struct TileScreen32 { float bandf; bool force_literal; };
 __device__ __forceinline__ float tile_sqrt_up(double r2)
 {
@@ -129,15 +146,34 @@ __device__ __forceinline__ float tile_sqrt_up(double r2)
     return s;
 #endif
 }
-__device__ __forceinline__ TileScreen32 tile_screen32(double R, double thr)
+__device__ __forceinline__ TileScreen32 tile_screen32(double R, double thr, double S)
 {
     TileScreen32 b;
     const double band = (4.25e-7 * R + 0x1p-24 * thr) * (1.0 + 0x1p-20);
     // outside these ranges every trial of the chunk is scored literally: fp32 range of the products, a threshold the
-    // band is not small against, thr <= 0 or NaN, R not finite
-    b.force_literal = !(R >= 0x1p-40 && R <= 0x1p40 && thr >= 0x1p-40 && thr <= 0x1p40 && 4.0 * band <= thr);
+    // band is not small against, thr <= 0 or NaN, R not finite, a radius tiny against the coordinates
+    b.force_literal = !(R >= 0x1p-40 && R <= 0x1p40 && thr >= 0x1p-40 && thr <= 0x1p40 && 4.0 * band <= thr && S <= 0x1p22 * R);
     b.bandf = b.force_literal ? 0.0f : __double2float_ru(band);
     return b;
+}
+
+// the line of a trial relative to the slot's centre c0:  s(p) = n . (p - c0) + cp,  cp = n . (c0 - p_i).  The unit normal
+// comes from the fp64 difference p_j - p_i (Newton-refined rsqrt, relative error < 2^-42); cp is formed from the differences
+// c0 - p_i (no cancellation at the coordinate scale).  Rounded once to fp32 they are the hot loop's line: the "n rounding"
+// and "cp rounding" terms u R of the bound above.  degenerate: coincident samples or an absurd scale -> literal score.
+struct TileLine { double nx, ny, cp; bool degenerate; };
+__device__ __forceinline__ TileLine tile_line(double2 pi, double2 pj, double c0x, double c0y)
+{
+    const double dx = pj.x - pi.x, dy = pj.y - pi.y;
+    const double n2 = fma(dx, dx, dy * dy);
+    TileLine l;
+    l.degenerate = !(n2 > 0x1p-100 && n2 < 0x1p100);     // also keeps (float)n2 in range
+    const double n2s = l.degenerate ? 1.0 : n2;
+    double y = (double)rsqrtf((float)n2s);
+    y = y * fma(-0.5 * n2s * y, y, 1.5);
+    l.nx = -dy * y; l.ny = dx * y;
+    l.cp = fma(l.nx, c0x - pi.x, l.ny * (c0y - pi.y));
+    return l;
 }
 
 // ---- residual sum from moments -------------------------------------------------------------------------------
@@ -158,6 +194,31 @@ __device__ __forceinline__ double tile_moment_sum(double nx, double ny, double c
 __device__ __forceinline__ double tile_moment_err(double cp, double nn, double A)
 {
     return (5.0 * (nn + 32.0) + 20.0) * 0x1p-53 * 1.01 * fma(nn * cp, cp, A);
+}
+
+// score of one hypothesis by a whole warp with the fp64 fast line (lslam_core.cuh FastLine: |s| is within 2^-40 S of the
+// literal residual, the re-check band 2^(e2-36) is sixteen times that): the count and the mask are the literal ones unless
+// `near` comes back set (a point inside the band, or a non-finite distance) - then the caller scores literally
+__device__ __forceinline__ void warp_fast64_score_strided(const double2 *P, int n, const FastLine m, double thr, int band_hi, int lane,
+                                                          int &cnt, bool &near, uint32_t *mask_out, int stride)
+{
+    int c = 0;
+    bool nr = false;
+    for (int k0 = 0; k0 < n; k0 += 32) {
+        const int k = k0 + lane;
+        bool in = false;
+        if (k < n) {
+            const double2 p = P[k];
+            const double u = fabs(fma(p.y, m.ny, fma(p.x, m.nx, m.negc))) - thr;
+            in = u < 0.0;
+            nr = nr || (__double2hiint(u) & 0x7fffffff) < band_hi || !(fabs(u) <= 1.7976931348623157e308);
+        }
+        const unsigned b = __ballot_sync(LSLAM_FULL_MASK, in);
+        c += __popc(b);
+        if (lane == 0) mask_out[(k0 >> 5) * stride] = b;
+    }
+    cnt = c;
+    near = __any_sync(LSLAM_FULL_MASK, nr);
 }
 
 // literal score of one hypothesis by a whole warp, mask words stored with a stride
@@ -182,144 +243,301 @@ __device__ __forceinline__ void warp_literal_score_strided(const double2 *P, int
     ssum = warp_tree32(part);
 }
 
-template <int TPT, int MAXT, int MINB, bool F32>
-__global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArgs a)
+// ================= stage + moments of one tile: LG lanes per slot, warps [w0, w0 + nw) ====================
+template <int TPT, bool F32>
+__device__ __forceinline__ void tile_stage(const RansacArgs &a, int tile, int par, int w0, int nw)
 {
-    static_assert(TPT % 2 == 0, "a Philox block serves two trials");
+    LSLAM_SMEM_DECL;                                              // the CTA's dynamic shared memory, known to be shared memory here
     constexpr int LG = kTileLG;
-    LSLAM_SMEM_DECL;
-    const int T = a.trials, G = a.G, chunk = a.chunk, W = a.W, ipc = a.ipc;
+    constexpr int SPW = 32 / LG;
+    const int G = a.G, chunk = a.chunk, W = a.W, ipc = a.ipc;
     const int chunk_pad = (chunk + 1) & ~1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
     const TileSmem sm = tile_carve(smem_raw, G, chunk, ipc, TPT, W, nwarps, F32);
-    const long long slot0 = (long long)blockIdx.x * G;
+    (void)chunk_pad; (void)tid; (void)nwarps;
+
+    const long long slot0 = (long long)tile * G;
     const long long rem_slots = a.nslots - slot0;
     const int nsl = rem_slots < (long long)G ? (int)rem_slots : G;
-
-    // ================= stage + moments: LG lanes per slot =====================================================
-    {
-        const int grp = tid / LG, r = tid % LG, ngrp = blockDim.x / LG;
-        for (int qb = 0; qb < nsl; qb += ngrp) {                  // uniform trip count: the shuffles below are warp-wide
-            if (qb + warp * (32 / LG) >= nsl) {                   // (warp-uniform) none of this warp's groups has a slot
-                // the last such warp pulls the points of the tile a later CTA will stage (prefetch_ahead tiles on)
-                // towards L2, so that its copies do not wait for DRAM
-                if (qb == 0 && warp == nwarps - 1 && a.prefetch_ahead > 0) {
-                    const long long s1 = slot0 + (long long)a.prefetch_ahead * G;
-                    if (s1 < a.nslots) {
-                        const long long s2 = s1 + G < a.nslots ? s1 + G : a.nslots;
-                        const long long b1 = s1 / a.C, b2 = s2 / a.C;
-                        const long long p1 = b1 * a.N + (s1 - b1 * a.C) * chunk, p2 = b2 * a.N + (s2 - b2 * a.C) * chunk;
-                        const char *base = reinterpret_cast<const char *>(a.xy);
-                        const long long lim = (long long)a.B * a.N * 16;
-                        for (long long ofs = (p1 * 16 & ~127LL) + 128LL * lane; ofs < p2 * 16 && ofs < lim; ofs += 128 * 32) prefetch_l2(base + ofs);
-                    }
-                }
-                break;
-            }
-            // CTA geometry (32-bit division whenever the slot index fits)
-            long long b0;
-            int c0;
-            if (slot0 <= 0x7fffffffLL) {
-                const unsigned s = (unsigned)slot0, bq = s / (unsigned)a.C;
-                b0 = bq; c0 = (int)(s - bq * (unsigned)a.C);
-            } else {
-                b0 = slot0 / a.C; c0 = (int)(slot0 - b0 * a.C);
-            }
-            const long long gp0 = b0 * a.N + (long long)c0 * chunk;       // first staged point
-            const int q = qb + grp;
-            const bool act = q < nsl;
-            int n = 0, off = 0, c = 0;
-            long long b = b0;
-            if (act) {
-                const int cq = c0 + q, bb = cq / a.C;
-                c = cq - bb * a.C; b = b0 + bb;
-                int nb = a.npts ? a.npts[b] : a.N;
-                nb = nb < 0 ? 0 : (nb > a.N ? a.N : nb);
-                n = nb - c * chunk;
-                n = n < 0 ? 0 : (n > chunk ? chunk : n);
-                off = (int)((long long)bb * a.N + (long long)(c - c0) * chunk);
-            }
-            const double2 *src = a.xy + gp0 + off;
-            double2 *dst = sm.pts + off;
-            // asynchronous copies (no register staging: all of a lane's loads are in flight at once), then one pass
-            // over the staged points for the slot's scale and its moments about its middle point
-            for (int k = r; k < n; k += LG) cp_async16(dst + k, src + k);
-            cp_async_wait_all();
-            __syncwarp();
-            // functions.py:64-76: full chunks, or a remainder of MORE than 2 points
-            const bool valid = (n >= 2) && (n == chunk || n > 2);
-            const double2 cc = n > 0 ? dst[n >> 1] : make_double2(0.0, 0.0);
-            float2 *dstf = sm.ptsf + (size_t)(act ? q : 0) * chunk_pad;
-            int mh = 0;
-            double sx = 0.0, sy = 0.0, sxx = 0.0, sxy = 0.0, syy = 0.0, r2 = 0.0;
-            for (int k = r; k < n; k += LG) {
-                const double2 p = dst[k];
-                const int hx = __double2hiint(p.x) & 0x7fffffff, hy = __double2hiint(p.y) & 0x7fffffff;
-                mh = mh > hx ? mh : hx;
-                mh = mh > hy ? mh : hy;
-                const double qx = p.x - cc.x, qy = p.y - cc.y;
-                sx += qx; sy += qy;
-                sxx = fma(qx, qx, sxx); sxy = fma(qx, qy, sxy); syy = fma(qy, qy, syy);
-                if constexpr (F32) {
-                    dstf[k] = make_float2((float)qx, (float)qy);
-                    r2 = fmax(r2, fma(qx, qx, qy * qy));
-                }
-            }
-#pragma unroll
-            for (int o = LG / 2; o >= 1; o >>= 1) { const int v = __shfl_xor_sync(LSLAM_FULL_MASK, mh, o); mh = mh > v ? mh : v; }
-            const ChunkBand cb = chunk_band(mh);
-#pragma unroll
-            for (int o = LG / 2; o >= 1; o >>= 1) {
-                sx += __shfl_xor_sync(LSLAM_FULL_MASK, sx, o);
-                sy += __shfl_xor_sync(LSLAM_FULL_MASK, sy, o);
-                sxx += __shfl_xor_sync(LSLAM_FULL_MASK, sxx, o);
-                sxy += __shfl_xor_sync(LSLAM_FULL_MASK, sxy, o);
-                syy += __shfl_xor_sync(LSLAM_FULL_MASK, syy, o);
-                if constexpr (F32) r2 = fmax(r2, __shfl_xor_sync(LSLAM_FULL_MASK, r2, o));
-            }
-            if (act && r == 0) {
-                TileSlot *st = sm.slot + q;
-                st->scan = a.scan_base + (uint64_t)b;
-                st->gslot = slot0 + q;
-                st->key = 0ull;
-                st->c0x = cc.x; st->c0y = cc.y;
-                st->Sx = sx; st->Sy = sy; st->Sxx = sxx; st->Sxy = sxy; st->Syy = syy;
-                st->best_ss = 0.0;
-                const SsumBound sbq = ssum_bound_coeffs_inv(cb.eabs, n, a.thr, a.inv_thr);
-                st->alpha = sbq.alpha; st->beta = sbq.beta; st->A = sxx + syy; st->nn = (double)n;
-                st->off = off; st->n = n; st->valid = valid ? 1 : 0; st->c = c;
-                st->scale_hi = mh;
-                bool force = cb.force_literal;
-                st->bandf = 0.0f; st->pad_f = 0.0f;
-                if constexpr (F32) {
-                    // an upper bound of the radius is enough: fp32 square root rounded up (overflow -> inf, underflow -> 0:
-                    // both outside the screening range, the slot is then scored literally)
-                    const TileScreen32 sc = tile_screen32((double)tile_sqrt_up(r2), a.thr);
-                    st->bandf = sc.bandf;
-                    force = force || sc.force_literal;
-                } else {
-                    force = force || !tile_fast_ok(a.thr, mh);
-                }
-                st->force_lit = force ? 1 : 0;
-                st->mx = 0; st->ncand = 0;
-                st->status = !valid ? 0x7fffffff : (cb.bad ? kStatusNonFinite : 0);   // 0x7fffffff: unused slot
-                st->best_t = -1; st->best_i = -1; st->best_j = -1;
-                st->mask_base = 0; st->mask_stride = 0; st->cand_exact = 0;
+    double2 *pts = reinterpret_cast<double2 *>(sm.region(par));
+    float2 *ptsf = reinterpret_cast<float2 *>(sm.region(par) + sm.ptsf_off);
+    const int wrel = warp - w0;
+    const int grp = wrel * SPW + lane / LG, r = lane % LG, ngrp = nw * SPW;
+    // CTA geometry (32-bit division whenever the slot index fits)
+    long long b0;
+    int c0;
+    if (slot0 <= 0x7fffffffLL) {
+        const unsigned s = (unsigned)slot0, bq = s / (unsigned)a.C;
+        b0 = bq; c0 = (int)(s - bq * (unsigned)a.C);
+    } else {
+        b0 = slot0 / a.C; c0 = (int)(slot0 - b0 * a.C);
+    }
+    const long long gp0 = b0 * a.N + (long long)c0 * chunk;       // first staged point
+    for (int qb = 0; qb < nsl; qb += ngrp) {                  // uniform trip count: the shuffles below are warp-wide
+        if (qb + wrel * SPW >= nsl) break;                    // (warp-uniform) none of this warp's groups has a slot
+        const int q = qb + grp;
+        const bool act = q < nsl;
+        int n = 0, off = 0, c = 0;
+        long long b = b0;
+        if (act) {
+            const int cq = c0 + q, bb = cq / a.C;
+            c = cq - bb * a.C; b = b0 + bb;
+            int nb = a.npts ? a.npts[b] : a.N;
+            nb = nb < 0 ? 0 : (nb > a.N ? a.N : nb);
+            n = nb - c * chunk;
+            n = n < 0 ? 0 : (n > chunk ? chunk : n);
+            off = (int)((long long)bb * a.N + (long long)(c - c0) * chunk);
+        }
+        const double2 *src = a.xy + gp0 + off;
+        double2 *dst = pts + off;
+        // asynchronous copies (no register staging: all of a lane's loads are in flight at once), then one pass
+        // over the staged points for the slot's scale and its moments about its middle point
+        for (int k = r; k < n; k += LG) cp_async16(dst + k, src + k);
+        cp_async_wait_all();
+        __syncwarp();
+        // functions.py:64-76: full chunks, or a remainder of MORE than 2 points
+        const bool valid = (n >= 2) && (n == chunk || n > 2);
+        const double2 cc = n > 0 ? dst[n >> 1] : make_double2(0.0, 0.0);
+        float2 *dstf = ptsf + (size_t)(act ? q : 0) * chunk_pad;
+        int mh = 0;
+        double sx = 0.0, sy = 0.0, sxx = 0.0, sxy = 0.0, syy = 0.0, r2 = 0.0;
+        for (int k = r; k < n; k += LG) {
+            const double2 p = dst[k];
+            const int hx = __double2hiint(p.x) & 0x7fffffff, hy = __double2hiint(p.y) & 0x7fffffff;
+            mh = mh > hx ? mh : hx;
+            mh = mh > hy ? mh : hy;
+            const double qx = p.x - cc.x, qy = p.y - cc.y;
+            sx += qx; sy += qy;
+            sxx = fma(qx, qx, sxx); sxy = fma(qx, qy, sxy); syy = fma(qy, qy, syy);
+            if constexpr (F32) {
+                dstf[k] = make_float2((float)qx, (float)qy);
+                r2 = fmax(r2, fma(qx, qx, qy * qy));
             }
         }
+#pragma unroll
+        for (int o = LG / 2; o >= 1; o >>= 1) { const int v = __shfl_xor_sync(LSLAM_FULL_MASK, mh, o); mh = mh > v ? mh : v; }
+        const ChunkBand cb = chunk_band(mh);
+#pragma unroll
+        for (int o = LG / 2; o >= 1; o >>= 1) {
+            sx += __shfl_xor_sync(LSLAM_FULL_MASK, sx, o);
+            sy += __shfl_xor_sync(LSLAM_FULL_MASK, sy, o);
+            sxx += __shfl_xor_sync(LSLAM_FULL_MASK, sxx, o);
+            sxy += __shfl_xor_sync(LSLAM_FULL_MASK, sxy, o);
+            syy += __shfl_xor_sync(LSLAM_FULL_MASK, syy, o);
+            if constexpr (F32) r2 = fmax(r2, __shfl_xor_sync(LSLAM_FULL_MASK, r2, o));
+        }
+        if (act && r == 0) {
+            TileSlot *st = sm.slot(par) + q;
+            st->scan = a.scan_base + (uint64_t)b;
+            st->gslot = slot0 + q;
+            st->key = 0ull;
+            st->c0x = cc.x; st->c0y = cc.y;
+            st->Sx = sx; st->Sy = sy; st->Sxx = sxx; st->Sxy = sxy; st->Syy = syy;
+            st->best_ss = 0.0;
+            const SsumBound sbq = ssum_bound_coeffs_inv(cb.eabs, n, a.thr, a.inv_thr);
+            st->alpha = sbq.alpha; st->beta = sbq.beta; st->A = sxx + syy; st->nn = (double)n;
+            st->off = off; st->n = n; st->valid = valid ? 1 : 0; st->c = c;
+            st->scale_hi = mh;
+            bool force = cb.force_literal;
+            st->bandf = 0.0f; st->pad_f = 0.0f;
+            if constexpr (F32) {
+                // an upper bound of the radius is enough: fp32 square root rounded up (overflow -> inf, underflow -> 0:
+                // both outside the screening range, the slot is then scored literally)
+                const TileScreen32 sc = tile_screen32((double)tile_sqrt_up(r2), a.thr, cb.eabs * 0x1p36);
+                st->bandf = sc.bandf;
+                force = force || sc.force_literal;
+            } else {
+                force = force || !tile_fast_ok(a.thr, mh);
+            }
+            st->force_lit = force ? 1 : 0;
+            st->mx = 0; st->ncand = 0; st->band_hi = cb.band_hi;
+            st->status = !valid ? 0x7fffffff : (cb.bad ? kStatusNonFinite : 0);   // 0x7fffffff: unused slot
+            st->best_t = -1; st->best_i = -1; st->best_j = -1;
+            st->cand_exact = 0;
+        }
     }
-    __syncthreads();
+}
+
+// ================= decide (only where the literal formula is needed) + refit + stores of one tile: LG lanes per
+// slot, warps [0, nw).  Reads the tile's points, its slots and the winner masks - not its scratch region. ======
+template <int TPT, bool F32>
+__device__ __forceinline__ void tile_refit(const RansacArgs &a, int tile, int par, int nw)
+{
+    LSLAM_SMEM_DECL;
+    constexpr int LG = kTileLG;
+    constexpr int SPW = 32 / LG;
+    const int G = a.G, chunk = a.chunk, W = a.W, ipc = a.ipc;
+    const int chunk_pad = (chunk + 1) & ~1;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const TileSmem sm = tile_carve(smem_raw, G, chunk, ipc, TPT, W, nwarps, F32);
+    (void)chunk_pad; (void)tid; (void)nwarps;
+
+    const long long slot0 = (long long)tile * G;
+    const long long rem_slots = a.nslots - slot0;
+    const int nsl = rem_slots < (long long)G ? (int)rem_slots : G;
+    const double2 *pts = reinterpret_cast<const double2 *>(sm.region(par));
+    TileSlot *slots = sm.slot(par);
+    for (int qw = warp * SPW; qw < nsl; qw += nw * SPW) {
+        // ---- the common case, all slots of the warp at once: one candidate and no residual sum wanted - it is the winner ----
+        unsigned hard;                                            // bit i: slot qw + i needs the literal tie-break
+        {
+            const int qd = qw + lane / LG;
+            bool need = false;
+            if (lane % LG == 0 && qd < nsl) {
+                TileSlot *s1 = slots + qd;
+                if (s1->status == 0) {
+                    if (s1->ncand == 1 && a.ssum == nullptr) {
+                        s1->best_t = s1->cand_t[0]; s1->best_i = s1->cand_i[0]; s1->best_j = s1->cand_j[0];
+                        s1->best_ss = __longlong_as_double(0x7ff8000000000000LL);
+                    } else need = true;
+                }
+            }
+            hard = __ballot_sync(LSLAM_FULL_MASK, need);
+        }
+        // ---- literal tie-break, a warp per slot: several candidates, or the caller wants the residual sum ----
+        while (hard) {
+            const int qq = qw + (__ffs((int)hard) - 1) / LG;
+            hard &= hard - 1;
+            TileSlot *s2 = slots + qq;
+            const int ncand = s2->ncand;
+            const double2 *P2 = pts + s2->off;
+            uint32_t *wt = sm.wtmp + (size_t)warp * W;
+            uint32_t *mq = sm.smask + qq * W;
+            bool fault = false;
+            int best_t = -1, best_i = -1, best_j = -1;
+            double best_ss = __longlong_as_double(0x7ff0000000000000LL);
+            if (ncand <= kMaxCand) {
+                // candidates were appended in no particular order: smallest sum wins, the earlier trial on a tie -
+                // the sequential accept rule (first best in trial order)
+                for (int ci = 0; ci < ncand; ++ci) {
+                    int cl;
+                    double sl;
+                    const int ti = s2->cand_t[ci], ii = s2->cand_i[ci], jj = s2->cand_j[ci];
+                    warp_literal_score(P2, s2->n, lit_pair_model(P2[ii], P2[jj]), a.thr, lane, cl, sl, wt);
+                    __syncwarp();
+                    if (cl != s2->mx) fault = true;
+                    if (sl < best_ss || (sl == best_ss && ti < best_t)) {
+                        best_ss = sl; best_t = ti; best_i = ii; best_j = jj;
+                        for (int w = lane; w * 32 < s2->n; w += 32) mq[w] = wt[w];
+                    }
+                    __syncwarp();
+                }
+                if (lane == 0 && ncand > 1) atomicAdd(a.counters + 1, (unsigned long long)(ncand - 1));
+            }
+            if (lane == 0) { s2->best_t = best_t; s2->best_i = best_i; s2->best_j = best_j; s2->best_ss = best_ss; }
+            __syncwarp();
+            if (fault || best_t < 0) {
+                // more candidates than the list holds (e.g. noise-free collinear data), or a fast count that disagrees
+                // with the literal one (error bound violated - never observed, counted): the exact sequential rule
+                if (lane == 0 && fault) atomicAdd(a.counters + 2, 1ULL);
+                slot_exact_fallback(a, s2, P2, mq, wt, lane);
+            }
+        }
+        __syncwarp();
+
+        // ---- refit + outputs: LineModelND.estimate(data[inliers]) as the principal axis of the 2x2 scatter,
+        //      accumulated relative to the winner's first sample point (an inlier, so the shift is benign) ----
+        const int qr = qw + lane / LG, r = lane % LG;
+        const bool act = qr < nsl;
+        const TileSlot *s3 = slots + (act ? qr : qw);
+        const bool ok = act && s3->status == 0;
+        const double2 *P3 = pts + s3->off;
+        const uint32_t *mrow = sm.smask + (act ? qr : qw) * W;
+        const int n3 = s3->n;
+        double sx = 0.0, sy = 0.0, sxx = 0.0, sxy = 0.0, syy = 0.0;
+        double2 p0 = make_double2(0.0, 0.0);
+        // independent of the sums below, so started first: 1 / count, and the tip (the LAST inlier in data order)
+        double rm = 0.0, tipx = 0.0;
+        if (ok) {
+            rm = 1.0 / (double)s3->mx;
+            int last = 0;
+            for (int w = (n3 - 1) >> 5; w >= 0; --w) {
+                const unsigned mw_ = mrow[w];
+                if (mw_) { last = w * 32 + 31 - __clz((int)mw_); break; }
+            }
+            tipx = P3[last].x;
+            p0 = P3[s3->best_i];
+            // loads are unconditional and independent of the mask test (they pipeline); an outlier contributes zeros
+#pragma unroll 4
+            for (int k = r; k < n3; k += LG) {
+                const double2 p = P3[k];
+                const bool in = (mrow[k >> 5] >> (k & 31)) & 1u;
+                const double dx = in ? p.x - p0.x : 0.0, dy = in ? p.y - p0.y : 0.0;
+                sx += dx; sy += dy;
+                sxx = fma(dx, dx, sxx); sxy = fma(dx, dy, sxy); syy = fma(dy, dy, syy);
+            }
+        }
+#pragma unroll
+        for (int o = LG / 2; o >= 1; o >>= 1) {
+            sx += __shfl_xor_sync(LSLAM_FULL_MASK, sx, o);
+            sy += __shfl_xor_sync(LSLAM_FULL_MASK, sy, o);
+            sxx += __shfl_xor_sync(LSLAM_FULL_MASK, sxx, o);
+            sxy += __shfl_xor_sync(LSLAM_FULL_MASK, sxy, o);
+            syy += __shfl_xor_sync(LSLAM_FULL_MASK, syy, o);
+        }
+        if (act) {
+            const long long s = slot0 + qr;
+            const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+            double out = qnan;                                   // lane r stores element r of the line record
+            if (ok) {
+                const double mdx = sx * rm, mdy = sy * rm;
+                const double ox = p0.x + mdx, oy = p0.y + mdy;
+                double dx, dy;
+                principal_axis_rsqrt(fma(-sx, mdx, sxx), fma(-sx, mdy, sxy), fma(-sy, mdy, syy), dx, dy);
+                // ransac_functions.py:26-30 (no guard for dir_x == 0, like the reference)
+                const double sl = __ddiv_rn(dy, dx);
+                const double ic = __dsub_rn(oy, __dmul_rn(sl, ox));
+                const double tipy = __dadd_rn(__dmul_rn(tipx, sl), ic);
+                out = (r & 7) == 0 ? sl : (r & 7) == 1 ? ic : (r & 7) == 2 ? ox : (r & 7) == 3 ? oy : (r & 7) == 4 ? dx : (r & 7) == 5 ? dy : (r & 7) == 6 ? tipx : tipy;
+            }
+            static_assert(LG >= 8, "one lane per element of the line record");
+            constexpr int R0 = LG >= 16 ? 8 : 0;                 // the scalar outputs: on lanes 8.. when the group has them
+            if (r < 8) a.line[s * 8 + r] = out;
+            if (r == R0) a.ninl[s] = ok ? s3->mx : (s3->status == 0x7fffffff ? 0 : s3->status);
+            if (r == R0 + 1) a.win_trial[s] = ok ? s3->best_t : -1;
+            if (r == R0 + 2) a.win_pair[2 * s] = ok ? s3->best_i : -1;
+            if (r == R0 + 3) a.win_pair[2 * s + 1] = ok ? s3->best_j : -1;
+            if (r == R0 + 4 && a.ssum != nullptr) a.ssum[s] = ok ? s3->best_ss : qnan;
+        }
+        // inlier masks of this warp's slots: consecutive slots are consecutive in global memory
+        const int nq = (nsl - qw) < SPW ? (nsl - qw) : SPW;
+        for (int i = lane; i < nq * W; i += 32) {
+            const int qi = i / W, w = i - qi * W;
+            const TileSlot *s4 = slots + qw + qi;
+            a.mask[(slot0 + qw) * W + i] = (s4->status == 0 && w * 32 < s4->n) ? sm.smask[(qw + qi) * W + w] : 0u;
+        }
+    }
+}
+
+// score + candidates of one tile: one work item (TPT trials of one chunk) per thread.  Inlined into the kernel, with the
+// kernel's own parameter (constant-bank operands).
+template <int TPT, bool F32>
+__device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int par)
+{
+    LSLAM_SMEM_DECL;
+    const int T = a.trials, G = a.G, chunk = a.chunk, W = a.W, ipc = a.ipc;
+    const int chunk_pad = (chunk + 1) & ~1;
+    const int tid = threadIdx.x;
+    const int lane = tid & 31, nwarps = blockDim.x >> 5;
+    const TileSmem sm = tile_carve(smem_raw, G, chunk, ipc, TPT, W, nwarps, F32);
+    const long long slot0 = (long long)tile * G;
+    const long long rem_slots = a.nslots - slot0;
+    const int nsl = rem_slots < (long long)G ? (int)rem_slots : G;
+    double2 *const pts = reinterpret_cast<double2 *>(sm.region(par));
+    float2 *const ptsf = reinterpret_cast<float2 *>(sm.region(par) + sm.ptsf_off);
+    int2 *const keys = reinterpret_cast<int2 *>(sm.region(par ^ 1));                    // [G][TPT][ipc]
+    uint32_t *const mw = reinterpret_cast<uint32_t *>(sm.region(par ^ 1) + sm.mw_off);  // [G][W][TPT][ipc]
 
     // ================= score: one work item (TPT trials of one chunk) per thread =============================
     const int items = nsl * ipc;
     const bool has_item = tid < items;
     const int q = has_item ? tid / ipc : 0, tb = has_item ? tid - q * ipc : 0;
-    TileSlot *st = sm.slot + q;
+    TileSlot *st = sm.slot(par) + q;
     const int n = st->n, t0 = tb * TPT;
     const bool skip = !has_item || st->status != 0;
-    const double2 *P = sm.pts + st->off;
+    const double2 *P = pts + st->off;
     const int row0 = (q * W * TPT) * ipc + tb;                    // trial k, word w: mw[row0 + (w * TPT + k) * ipc]
-    int2 *krow = sm.keys + (size_t)q * TPT * ipc + tb;            // trial k: krow[k * ipc]
+    int2 *krow = keys + (size_t)q * TPT * ipc + tb;               // trial k: krow[k * ipc]
     int cnt[TPT];
     unsigned live = 0, exact = 0;                                 // bit k: trial t0 + k exists / was scored literally
     {
@@ -330,7 +548,7 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArg
         real nx[TPT], ny[TPT], ng[TPT];
         unsigned bits[TPT];
         float mab[TPT];
-        unsigned flagm = 0;
+        unsigned flagl = 0;                                       // bit k: trial t0 + k must be scored literally
         const double nn = st->nn, A = st->A, sb_alpha = st->alpha, sb_beta = st->beta, c0x = st->c0x, c0y = st->c0y;
 #pragma unroll
         for (int k = 0; k < TPT; k += 2) {
@@ -345,18 +563,26 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArg
                     int i, j;
                     if (a.pairs != nullptr) explicit_pair(a, slot0 + q, (uint32_t)(t0 + k + h), (uint32_t)n, i, j);
                     else pair_from_words(h ? ph.r[2] : ph.r[0], h ? ph.r[3] : ph.r[1], (uint32_t)n, i, j);
-                    const FastLine f = fast_pair_model(P[i], P[j]);
+                    double fnx, fny, cp;
+                    bool degen;
+                    if constexpr (F32) {
+                        const TileLine f = tile_line(P[i], P[j], c0x, c0y);
+                        fnx = f.nx; fny = f.ny; cp = f.cp; degen = f.degenerate;
+                        nx[k + h] = (float)fnx; ny[k + h] = (float)fny; ng[k + h] = (float)cp;
+                    } else {
+                        const FastLine f = fast_pair_model(P[i], P[j]);
+                        fnx = f.nx; fny = f.ny; degen = f.degenerate;
+                        cp = fma(f.nx, c0x, fma(f.ny, c0y, f.negc));
+                        nx[k + h] = f.nx; ny[k + h] = f.ny; ng[k + h] = f.negc;
+                    }
                     // residual sum from the moments with its error bound -> the two keys the tie-break needs
-                    const double cp = fma(f.nx, c0x, fma(f.ny, c0y, f.negc));
-                    const double M = tile_moment_sum(f.nx, f.ny, cp, nn, st);
+                    const double M = tile_moment_sum(fnx, fny, cp, nn, st);
                     const double e2 = tile_moment_err(cp, nn, A);
                     const double E = fma(sb_beta, (M > 0.0 ? M : 0.0) + e2, sb_alpha) + e2;
                     krow[(k + h) * ipc] = make_int2(key_down(M - E), key_up(M + E));
-                    // literal re-score wanted: coincident samples, a chunk outside the fast path's range, a non-finite
-                    // sum / bound - or (after the loop) a point too close to the threshold
-                    if (f.degenerate || force_lit || !(fabs(M) + E <= 1.7976931348623157e308)) flagm |= 1u << (k + h);
-                    if constexpr (F32) { nx[k + h] = (float)f.nx; ny[k + h] = (float)f.ny; ng[k + h] = (float)cp; }
-                    else { nx[k + h] = f.nx; ny[k + h] = f.ny; ng[k + h] = f.negc; }
+                    // literal score wanted: coincident samples, a chunk outside the fast path's range, a non-finite sum /
+                    // bound.  (A point too close to the threshold - known after the loop - gets the fp64 fast line first.)
+                    if (degen || force_lit || !(fabs(M) + E <= 1.7976931348623157e308)) flagl |= 1u << (k + h);
                 }
             }
         }
@@ -366,7 +592,7 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArg
         if constexpr (F32) {
             const float thf = (float)a.thr;
             flim = st->bandf;
-            const float2 *Pf = sm.ptsf + (size_t)q * chunk_pad;
+            const float2 *Pf = ptsf + (size_t)q * chunk_pad;
             const float4 *Pf4 = reinterpret_cast<const float4 *>(Pf);     // two points per LDS.128 (chunk_pad is even)
 #define LSLAM_TILE_STEP2(XA, YA, XB, YB)                                                          \
     {                                                                                             \
@@ -385,7 +611,7 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArg
                 for (int k_ = 0; k_ < TPT; ++k_) {
                     const unsigned m = __brev(bits[k_]);              // bit j = point 32 w + j
                     cnt[k_] += __popc(m);
-                    sm.mw[row0 + (w * TPT + k_) * ipc] = m;
+                    mw[row0 + (w * TPT + k_) * ipc] = m;
                 }
             }
             const int rem = n_eff - k;
@@ -402,7 +628,7 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArg
                 for (int k_ = 0; k_ < TPT; ++k_) {
                     const unsigned m = __brev((bits[k_] >> sh) << (32 - rem));
                     cnt[k_] += __popc(m);
-                    sm.mw[row0 + (w * TPT + k_) * ipc] = m;
+                    mw[row0 + (w * TPT + k_) * ipc] = m;
                 }
             }
 #undef LSLAM_TILE_STEP2
@@ -429,7 +655,7 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArg
                 for (int k_ = 0; k_ < TPT; ++k_) {
                     const unsigned m = __brev(bits[k_]);              // bit j = point 32 w + j
                     cnt[k_] += __popc(m);
-                    sm.mw[row0 + (w * TPT + k_) * ipc] = m;
+                    mw[row0 + (w * TPT + k_) * ipc] = m;
                 }
             }
             const int rem = n_eff - k;
@@ -443,39 +669,55 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArg
                 for (int k_ = 0; k_ < TPT; ++k_) {
                     const unsigned m = __brev((bits[k_] >> sh) << (32 - rem));
                     cnt[k_] += __popc(m);
-                    sm.mw[row0 + (w * TPT + k_) * ipc] = m;
+                    mw[row0 + (w * TPT + k_) * ipc] = m;
                 }
             }
 #undef LSLAM_TILE_STEP2
         }
+        // a point too close to the threshold for the fast distance to decide: re-scored with the fp64 fast line (F32), or
+        // literally (the fp64 high-word test has no finer fast form)
+        unsigned flagb = 0;
 #pragma unroll
         for (int k_ = 0; k_ < TPT; ++k_)
-            if (mab[k_] < flim && ((live >> k_) & 1u)) flagm |= 1u << k_;     // a point too close to the threshold
-        flagm &= live;
+            if (mab[k_] < flim) flagb |= 1u << k_;
+        if constexpr (!F32) { flagl |= flagb; flagb = 0; }
+        flagl &= live;
+        flagb &= live & ~flagl;
 
-        // flagged trials: literal score by the whole warp, on the spot; the literal mask replaces the fast one
-        unsigned fm = __ballot_sync(LSLAM_FULL_MASK, flagm != 0u);
+        // flagged trials: scored again by the whole warp, on the spot - with the fp64 fast line (its own re-check band is
+        // 2^-36 of the coordinate scale: the count and the mask are then the literal ones), or with the literal formula
+        // (trials flagged for it at the set-up, or a point inside the fp64 band as well); the new mask replaces the fast one
+        unsigned fm = __ballot_sync(LSLAM_FULL_MASK, (flagl | flagb) != 0u);
         unsigned n_relit = 0;
         while (fm) {
             const int src = __ffs((int)fm) - 1;
             fm &= fm - 1;
             const int fq = __shfl_sync(LSLAM_FULL_MASK, q, src), ftb = __shfl_sync(LSLAM_FULL_MASK, tb, src);
-            unsigned fl = __shfl_sync(LSLAM_FULL_MASK, flagm, src);
-            const TileSlot *fs = sm.slot + fq;
-            const double2 *FP = sm.pts + fs->off;
+            const unsigned fll = __shfl_sync(LSLAM_FULL_MASK, flagl, src);
+            unsigned fl = fll | __shfl_sync(LSLAM_FULL_MASK, flagb, src);
+            const TileSlot *fs = sm.slot(par) + fq;
+            const double2 *FP = pts + fs->off;
             const int frow0 = (fq * W * TPT) * ipc + ftb;
             while (fl) {
                 const int kf = __ffs((int)fl) - 1;
                 fl &= fl - 1;
-                int i, j, cl;
-                double sl;
+                int i, j, cl = 0;
+                double sl = 0.0;
                 trial_pair(a, slot0 + fq, fs->scan, (uint32_t)fs->c, (uint32_t)(ftb * TPT + kf), (uint32_t)fs->n, i, j);
-                warp_literal_score_strided(FP, fs->n, lit_pair_model(FP[i], FP[j]), a.thr, lane, cl, sl, sm.mw + frow0 + kf * ipc,
-                                           TPT * ipc);
-                ++n_relit;
+                bool lit = (fll >> kf) & 1u;
+                if (!lit)
+                    warp_fast64_score_strided(FP, fs->n, fast_pair_model(FP[i], FP[j]), a.thr, fs->band_hi, lane, cl, lit,
+                                              mw + frow0 + kf * ipc, TPT * ipc);
+                if (lit) {
+                    warp_literal_score_strided(FP, fs->n, lit_pair_model(FP[i], FP[j]), a.thr, lane, cl, sl, mw + frow0 + kf * ipc,
+                                               TPT * ipc);
+                    ++n_relit;
+                }
                 if (lane == src) {
-                    krow[kf * ipc] = make_int2(key_down(sl), key_up(sl));
-                    exact |= 1u << kf;
+                    if (lit) {
+                        krow[kf * ipc] = make_int2(key_down(sl), key_up(sl));
+                        exact |= 1u << kf;
+                    }
 #pragma unroll
                     for (int k_ = 0; k_ < TPT; ++k_)
                         if (k_ == kf) cnt[k_] = cl;
@@ -493,7 +735,16 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArg
                 best = best > key ? best : key;
             }
         }
-        if (live) atomicMax(&st->key, best);
+        // the work items of a slot are consecutive threads: an inclusive max-scan over the slot's lanes of this warp leaves the
+        // slot's maximum in its last lane, which alone touches the slot's key (a 64-bit shared-memory atomicMax is a
+        // compare-and-swap loop: 25 lanes contending for one word took four rounds of it)
+        const int seg_lo = q * ipc - (tid - lane), seg0 = has_item ? (seg_lo > 0 ? seg_lo : 0) : lane;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long o = __shfl_up_sync(LSLAM_FULL_MASK, best, d);
+            if (lane - d >= seg0 && o > best) best = o;
+        }
+        if (has_item && best != 0ull && (tb == ipc - 1 || lane == 31)) atomicMax(&st->key, best);
     }
     __syncthreads();
 
@@ -519,136 +770,30 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArg
                     trial_pair(a, slot0 + q, st->scan, (uint32_t)st->c, (uint32_t)(t0 + kc), (uint32_t)n, i, j);
                     st->cand_t[pos] = t0 + kc; st->cand_i[pos] = i; st->cand_j[pos] = j;
                     if ((exact >> kc) & 1u) atomicOr(&st->cand_exact, 1 << pos);
-                    if (pos == 0) { st->mask_base = row0 + kc * ipc; st->mask_stride = TPT * ipc; }
+                    // the first candidate's inlier words leave the scratch region; with several candidates the literal
+                    // tie-break writes the winner's
+                    if (pos == 0)
+                        for (int w2 = 0; w2 * 32 < n; ++w2) sm.smask[q * W + w2] = mw[row0 + (w2 * TPT + kc) * ipc];
                 }
             }
         }
     }
     __syncthreads();
+}
 
-    // ================= decide (only where the literal formula is needed) + refit + stores: LG lanes per slot ====
-    constexpr int SPW = 32 / LG;                                  // slots per warp
-    for (int qw = warp * SPW; qw < nsl; qw += nwarps * SPW) {
-        // ---- literal tie-break, a warp per slot: several candidates, or the caller wants the residual sum ----
-        for (int qq = qw; qq < qw + SPW && qq < nsl; ++qq) {
-            TileSlot *s2 = sm.slot + qq;
-            if (s2->status != 0) continue;
-            const int ncand = s2->ncand;
-            if (ncand == 1 && a.ssum == nullptr) {
-                if (lane == 0) {
-                    s2->best_t = s2->cand_t[0]; s2->best_i = s2->cand_i[0]; s2->best_j = s2->cand_j[0];
-                    s2->best_ss = __longlong_as_double(0x7ff8000000000000LL);
-                }
-                continue;
-            }
-            const double2 *P2 = sm.pts + s2->off;
-            uint32_t *wt = sm.wtmp + (size_t)warp * W;
-            uint32_t *mq = sm.mw + sm.smask0 + qq * W;
-            bool fault = false;
-            int best_t = -1, best_i = -1, best_j = -1;
-            double best_ss = __longlong_as_double(0x7ff0000000000000LL);
-            if (ncand <= kMaxCand) {
-                // candidates were appended in no particular order: smallest sum wins, the earlier trial on a tie -
-                // the sequential accept rule (first best in trial order)
-                for (int ci = 0; ci < ncand; ++ci) {
-                    int cl;
-                    double sl;
-                    const int ti = s2->cand_t[ci], ii = s2->cand_i[ci], jj = s2->cand_j[ci];
-                    warp_literal_score(P2, s2->n, lit_pair_model(P2[ii], P2[jj]), a.thr, lane, cl, sl, wt);
-                    __syncwarp();
-                    if (cl != s2->mx) fault = true;
-                    if (sl < best_ss || (sl == best_ss && ti < best_t)) {
-                        best_ss = sl; best_t = ti; best_i = ii; best_j = jj;
-                        for (int w = lane; w * 32 < s2->n; w += 32) mq[w] = wt[w];
-                    }
-                    __syncwarp();
-                }
-                if (lane == 0 && ncand > 1) atomicAdd(a.counters + 1, (unsigned long long)(ncand - 1));
-            }
-            if (lane == 0) {
-                s2->best_t = best_t; s2->best_i = best_i; s2->best_j = best_j; s2->best_ss = best_ss;
-                s2->mask_base = sm.smask0 + qq * W; s2->mask_stride = 1;
-            }
-            __syncwarp();
-            if (fault || best_t < 0) {
-                // more candidates than the list holds (e.g. noise-free collinear data), or a fast count that disagrees
-                // with the literal one (error bound violated - never observed, counted): the exact sequential rule
-                if (lane == 0 && fault) atomicAdd(a.counters + 2, 1ULL);
-                slot_exact_fallback(a, s2, P2, mq, wt, lane);
-            }
-        }
-        __syncwarp();
-
-        // ---- refit + outputs: LineModelND.estimate(data[inliers]) as the principal axis of the 2x2 scatter,
-        //      accumulated relative to the winner's first sample point (an inlier, so the shift is benign) ----
-        const int qr = qw + lane / LG, r = lane % LG;
-        const bool act = qr < nsl;
-        const TileSlot *s3 = sm.slot + (act ? qr : qw);
-        const bool ok = act && s3->status == 0;
-        const double2 *P3 = sm.pts + s3->off;
-        const uint32_t *mrow = sm.mw + s3->mask_base;
-        const int ms = s3->mask_stride, n3 = s3->n;
-        double sx = 0.0, sy = 0.0, sxx = 0.0, sxy = 0.0, syy = 0.0;
-        double2 p0 = make_double2(0.0, 0.0);
-        if (ok) {
-            p0 = P3[s3->best_i];
-            // loads are unconditional and independent of the mask test (they pipeline); an outlier contributes zeros
-#pragma unroll 4
-            for (int k = r; k < n3; k += LG) {
-                const double2 p = P3[k];
-                const bool in = (mrow[(k >> 5) * ms] >> (k & 31)) & 1u;
-                const double dx = in ? p.x - p0.x : 0.0, dy = in ? p.y - p0.y : 0.0;
-                sx += dx; sy += dy;
-                sxx = fma(dx, dx, sxx); sxy = fma(dx, dy, sxy); syy = fma(dy, dy, syy);
-            }
-        }
-#pragma unroll
-        for (int o = LG / 2; o >= 1; o >>= 1) {
-            sx += __shfl_xor_sync(LSLAM_FULL_MASK, sx, o);
-            sy += __shfl_xor_sync(LSLAM_FULL_MASK, sy, o);
-            sxx += __shfl_xor_sync(LSLAM_FULL_MASK, sxx, o);
-            sxy += __shfl_xor_sync(LSLAM_FULL_MASK, sxy, o);
-            syy += __shfl_xor_sync(LSLAM_FULL_MASK, syy, o);
-        }
-        if (act) {
-            const long long s = slot0 + qr;
-            const double qnan = __longlong_as_double(0x7ff8000000000000LL);
-            double out = qnan;                                   // lane r stores element r of the line record
-            if (ok) {
-                const double rm = 1.0 / (double)s3->mx;
-                const double mdx = sx * rm, mdy = sy * rm;
-                const double ox = p0.x + mdx, oy = p0.y + mdy;
-                double dx, dy;
-                principal_axis_rsqrt(fma(-sx, mdx, sxx), fma(-sx, mdy, sxy), fma(-sy, mdy, syy), dx, dy);
-                int last = 0;
-                for (int w = (n3 - 1) >> 5; w >= 0; --w) {
-                    const unsigned mw_ = mrow[w * ms];
-                    if (mw_) { last = w * 32 + 31 - __clz((int)mw_); break; }
-                }
-                // ransac_functions.py:26-30 (no guard for dir_x == 0, like the reference)
-                const double sl = __ddiv_rn(dy, dx);
-                const double ic = __dsub_rn(oy, __dmul_rn(sl, ox));
-                const double tipx = P3[last].x;
-                const double tipy = __dadd_rn(__dmul_rn(tipx, sl), ic);
-                out = (r & 7) == 0 ? sl : (r & 7) == 1 ? ic : (r & 7) == 2 ? ox : (r & 7) == 3 ? oy : (r & 7) == 4 ? dx : (r & 7) == 5 ? dy : (r & 7) == 6 ? tipx : tipy;
-            }
-            static_assert(LG >= 8, "one lane per element of the line record");
-            constexpr int R0 = LG >= 16 ? 8 : 0;                 // the scalar outputs: on lanes 8.. when the group has them
-            if (r < 8) a.line[s * 8 + r] = out;
-            if (r == R0) a.ninl[s] = ok ? s3->mx : (s3->status == 0x7fffffff ? 0 : s3->status);
-            if (r == R0 + 1) a.win_trial[s] = ok ? s3->best_t : -1;
-            if (r == R0 + 2) a.win_pair[2 * s] = ok ? s3->best_i : -1;
-            if (r == R0 + 3) a.win_pair[2 * s + 1] = ok ? s3->best_j : -1;
-            if (r == R0 + 4 && a.ssum != nullptr) a.ssum[s] = ok ? s3->best_ss : qnan;
-        }
-        // inlier masks of this warp's slots: consecutive slots are consecutive in global memory
-        const int nq = (nsl - qw) < SPW ? (nsl - qw) : SPW;
-        for (int i = lane; i < nq * W; i += 32) {
-            const int qi = i / W, w = i - qi * W;
-            const TileSlot *s4 = sm.slot + qw + qi;
-            a.mask[(slot0 + qw) * W + i] = (s4->status == 0 && w * 32 < s4->n) ? sm.mw[s4->mask_base + w * s4->mask_stride] : 0u;
-        }
-    }
+template <int TPT, int MAXT, int MINB, bool F32>
+__global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArgs a)
+{
+    static_assert(TPT % 2 == 0, "a Philox block serves two trials");
+    // One tile per CTA.  Co-resident CTAs fall out of step and hide each other's narrow phases (a persistent CTA staging
+    // its next tile while it refits the current one measured SLOWER on B200: 5.1 against 4.3 ms on C2 - the CTAs of an SM
+    // then run in lockstep and idle together)
+    const int tile = blockIdx.x, nwarps = blockDim.x >> 5;
+    tile_stage<TPT, F32>(a, tile, 0, 0, nwarps);
+    __syncthreads();
+    tile_score<TPT, F32>(a, tile, 0);                             // score | barrier | candidates
+    __syncthreads();
+    tile_refit<TPT, F32>(a, tile, 0, nwarps);
 }
 
 } // namespace lslam

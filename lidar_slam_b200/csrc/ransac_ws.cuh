@@ -606,7 +606,7 @@ __global__ void __launch_bounds__(MAXT, 1) ransac_ws_kernel(const RansacArgs a)
                     WsSlotInfo *g = info + q;
                     const ChunkBand cb = chunk_band(mh);
                     const double R = (double)tile_sqrt_up(r2);                     // upper bound of the radius (inf / 0: out of range)
-                    const TileScreen32 scr = tile_screen32(R, a.thr);
+                    const TileScreen32 scr = tile_screen32(R, a.thr, cb.eabs * 0x1p36);
                     const SsumBound sb = ssum_bound_coeffs(cb.eabs, n, a.thr);
                     // the moment form's own error at the largest |cp| a line through two points of the chunk can have (the radius)
                     const double e2 = tile_moment_err(R, (double)n, sxx + syy);

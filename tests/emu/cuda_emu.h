@@ -32,6 +32,7 @@
 #define __device__
 #define __host__
 #define __forceinline__ inline
+#define __noinline__
 #define __launch_bounds__(...)
 #define __restrict__
 #define __align__(n) __attribute__((aligned(n)))
@@ -258,6 +259,8 @@ static inline cudaError_t cudaDeviceGetAttribute(int *v, cudaDeviceAttr a, int) 
     return cudaSuccess;
 }
 template <class K> static inline cudaError_t cudaFuncSetAttribute(K, cudaFuncAttribute, int) { return cudaSuccess; }
+// two CTAs "resident" per SM: persistent kernels then walk several tiles per CTA in the emulation as well
+template <class K> static inline cudaError_t cudaOccupancyMaxActiveBlocksPerMultiprocessor(int *n, K, int, size_t) { *n = 2; return cudaSuccess; }
 static inline cudaError_t cudaMalloc(void **p, size_t n) { *p = std::calloc(1, n ? n : 1); return *p ? cudaSuccess : 2; }
 static inline cudaError_t cudaFree(void *p) { std::free(p); return cudaSuccess; }
 // in the emulation a __device__ array IS host memory, so its name is its address

@@ -27,4 +27,9 @@ CMD3="python tools/ukf_one.py 1048576 4"
 timeout 300 $CMD3 > $OUT/${TAG}_plain3.log 2>&1 && \
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:ukf_kernel -s 2 -c 1 -f -o $OUT/${TAG}_ukf $CMD3 > $OUT/${TAG}_ncu_full_ukf.log 2>&1
 echo "full ukf rc=$?" ; cat $OUT/${TAG}_plain3.log
-timeout 300 python tools/ukf_one.py 1048576 8 ; timeout 300 python tools/ukf_one.py 131072 32
+CMD4="python tools/ukf_one.py 1048576 8"
+timeout 300 $CMD4 > $OUT/${TAG}_plain4.log 2>&1 && \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:ukf_kernel -s 2 -c 1 -f -o $OUT/${TAG}_ukf_L8 $CMD4 > $OUT/${TAG}_ncu_full_ukf8.log 2>&1
+echo "full ukf L8 rc=$?" ; cat $OUT/${TAG}_plain4.log
+timeout 300 python tools/ukf_one.py 131072 32
+echo "== no-alloc test alone" ; timeout 300 python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -3
