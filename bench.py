@@ -34,7 +34,8 @@ if ROOT not in sys.path:
 
 BEAMS, CHUNK, TRIALS, THR, TABLE_M = 360, 100, 100, 20.0, 8
 PACKETS = 12                                       # express packets per revolution (32 measures each)
-E2E_SLICES = 16                                    # slices of the overlapped host path
+E2E_SLICES = 16                                    # slices of the overlapped host path, one step in flight
+E2E_SLICES_PIPELINED = 8                           # ... two steps in flight (22.5 ms per step against 23.3 at 16 and 22.4 at 4)
 PHE_PER_SCAN = BEAMS * TRIALS                      # point-hypothesis evaluations per scan
 FLOP_PER_PHE = 8                                   # algorithmic fp64 flop per PHE
 BYTES_PER_SCAN = BEAMS * 16 + 4 * 96               # 5,760 in + 4 x 96 out = 6,144 B
@@ -397,9 +398,9 @@ def workload_config(args, world):
 # ---- our arm ---------------------------------------------------------------------------------------
 def main():
     args = parse()
-    global E2E_SLICES
+    global E2E_SLICES, E2E_SLICES_PIPELINED
     if args.slices > 0:
-        E2E_SLICES = args.slices
+        E2E_SLICES = E2E_SLICES_PIPELINED = args.slices
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -495,19 +496,37 @@ def main():
     assert int(pipe.ukf["status"].abs().sum().item()) == 0, "UKF status flags set"
 
     # ---- end to end through the host-buffer API --------------------------------------------
-    def e2e_leg(host_in):
-        for _ in range(2):
-            pipe.step_host(host_in, slices=E2E_SLICES)
+    def e2e_leg(host_in, pipelined=True, slices=None):
+        """K steps through ScanPipeline.step_host, host buffers in and out.  pipelined: a step is queued before the host
+        has read the previous step's results (two pinned result sets alternate), so step k + 1's uploads overlap step k's
+        kernels - what a stream of revolutions allows; every step still uploads its own input and the host reads every
+        step's results inside the timed region.  pipelined=False: the host waits for each step before queueing the next."""
+        slices = slices or (E2E_SLICES_PIPELINED if pipelined else E2E_SLICES)
+        for _ in range(3):                                                   # untimed: both pinned result sets exist afterwards
+            pipe.step_host(host_in, slices=slices, wait=not pipelined)
+        pipe.drain()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         n0e = eng.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(args.steps):
-            out_h = pipe.step_host(host_in, slices=E2E_SLICES)
-            torch.cuda.current_stream().synchronize()                        # results are on the host
-            _ = float(out_h["ninl"][0, 0])
+        if pipelined:
+            pending = None
+            for _ in range(args.steps):
+                out_h = pipe.step_host(host_in, slices=slices, wait=False)
+                if pending is not None:
+                    pending["done"].synchronize()                                # the previous step's results are on the host
+                    _ = float(pending["ninl"][0, 0])
+                pending = out_h
+            pending["done"].synchronize()
+            _ = float(pending["ninl"][0, 0])
+            pipe.drain()
+        else:
+            for _ in range(args.steps):
+                out_h = pipe.step_host(host_in, slices=slices)
+                torch.cuda.current_stream().synchronize()                        # results are on the host
+                _ = float(out_h["ninl"][0, 0])
         e1.record()
         torch.cuda.synchronize()
         ems = e0.elapsed_time(e1)
@@ -518,7 +537,8 @@ def main():
         h2d, d2h = pipe.io_bytes(host_in)
         return {"value": world * S * args.steps / (ems * 1e-3), "unit": "scans/s",
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ems / args.steps,
-                "slices": E2E_SLICES, "gpu_launches": eng.launch_count() - n0e}
+                "slices": slices, "gpu_launches": eng.launch_count() - n0e,
+                "steps_in_flight": 2 if pipelined else 1}
 
     e2e = e2e_xy = None
     if not args.no_e2e:
@@ -529,6 +549,11 @@ def main():
         torch.cuda.synchronize()
         e2e = e2e_leg(pk_h)
         e2e["input"] = "RPLidar express packets, %d x 84 B per scan, decoded on the device" % PACKETS
+        e2e["mode"] = ("two steps in flight: step k + 1 is queued (uploads running) before the host has read step k's results; "
+                       "every step uploads its own input and the host reads every step's results inside the timed region")
+        # the same with the host waiting for every step before it queues the next (rounds 1-2's e2e figure)
+        e2e_sync = e2e_leg(pk_h, pipelined=False)
+        e2e["one_step_in_flight"] = {"value": e2e_sync["value"], "ms_per_step": e2e_sync["ms_per_step"]}
         del pk_h
         # the same with cartesian float64 scans in (what scanning() queues, functions.py:59-66)
         xy_h = pipe.alloc_host_io("xy")

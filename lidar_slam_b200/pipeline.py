@@ -31,6 +31,7 @@ class ScanPipeline:
         self.pk_dev = None
         self.status_dev = None
         self._host_out = None
+        self._flip = 0                # pinned result set of the last pipelined step
         self._view_cache = {}
         self._ov = None
         self.peer_gather = None
@@ -144,16 +145,26 @@ class ScanPipeline:
             return torch.empty((self.S, packets_per_scan, 84), dtype=torch.uint8).pin_memory()
         raise ValueError("kind must be 'xy' or 'packets'")
 
-    def _ensure_host_out(self):
+    def _ensure_host_out(self, which=0):
+        """Pinned result buffers; set 1 only exists once a caller pipelines steps (step_host(wait=False))."""
         if self._host_out is None:
+            self._host_out = [None, None]
+        if self._host_out[which] is None:
             shapes = {"line": ((self.S, self.C, 8), torch.float64), "ninl": ((self.S, self.C), torch.int32),
                       "match_id": ((self.S, self.C), torch.int32), "x": ((self.S, 3), torch.float64),
                       "P": ((self.S, 3, 3), torch.float64), "status": ((self.S,), torch.int32)}
-            self._host_out = {k: torch.empty(sh, dtype=dt).pin_memory() for k, (sh, dt) in shapes.items()}
-        return self._host_out
+            self._host_out[which] = {k: torch.empty(sh, dtype=dt).pin_memory() for k, (sh, dt) in shapes.items()}
+        return self._host_out[which]
 
-    def step_host(self, host_in, slices=1, points=False):
+    def step_host(self, host_in, slices=1, points=False, wait=True):
         """One step from pinned host memory to pinned host memory.
+
+        wait=False (slices > 1, points=False) PIPELINES successive steps: the call returns as soon as the step is queued,
+        without making the current stream wait for it, so the next call's uploads run while this step's kernels do (the
+        events between the three streams keep every buffer's reuse in order).  The results then carry an extra entry
+        "done", a CUDA event recorded after the step's last device->host copy: synchronise it before reading them.  Two
+        sets of pinned result buffers alternate, so a step's results stay valid until the call after the next; call
+        drain() before timing or before touching the pipeline's state from the current stream.
 
         host_in: [S, N, 2] float64 scans, or [S, P, 84] uint8 express packets (decoded on the device:
         lslam_express_to_cart).  With slices == 1 everything is queued on the current stream.  With
@@ -177,9 +188,13 @@ class ScanPipeline:
             self.xy_dev = torch.empty((self.S, self.N, 2), dtype=torch.float64, device=dev)
         if not packets:
             dev_in = self.xy_dev
-        out = self._ensure_host_out()
-        keys = self.result_keys()
         K = max(1, min(int(slices), self.S))
+        if not wait and (K == 1 or points):
+            raise ValueError("step_host(wait=False) needs slices > 1 and points=False")
+        if not wait:
+            self._flip ^= 1
+        out = self._ensure_host_out(0 if wait else self._flip)
+        keys = self.result_keys()
         bounds = [(self.S * k // K, self.S * (k + 1) // K) for k in range(K)]
         if K == 1:
             dev_in.copy_(host_in, non_blocking=True)
@@ -244,9 +259,20 @@ class ScanPipeline:
                 views.append(self._pts["host"][a * self.N:a * self.N + rows])
             out = dict(out, points=views)
         ov["primed"] = True
+        if not wait:
+            done = torch.cuda.Event()
+            done.record(ov["out"])
+            return dict(out, done=done)
         for st in ("in", "run", "out"):
             cur.wait_stream(ov[st])
         return out
+
+    def drain(self):
+        """After pipelined steps (step_host(wait=False)): the current stream waits for everything they queued."""
+        if self._ov is not None:
+            cur = torch.cuda.current_stream(self.eng.device)
+            for st in ("in", "run", "out"):
+                cur.wait_stream(self._ov[st])
 
     def io_bytes(self, host_in=None):
         h2d = self.S * self.N * 16 if host_in is None else host_in.numel() * host_in.element_size()

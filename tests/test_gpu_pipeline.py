@@ -96,6 +96,50 @@ def test_overlapped_and_packet_host_paths(gpu_engine, kind, slices):
     assert h2d == h_in.numel() * h_in.element_size()
 
 
+@pytest.mark.parametrize("kind", ["xy", "packets"])
+def test_pipelined_host_steps(gpu_engine, kind):
+    """step_host(wait=False): steps queued back to back (step k + 1 before the host has read step k) give, step for
+    step, the results of the device-resident path; a step's pinned results stay valid until the call after the next."""
+    import torch
+    from lidar_slam_b200 import pipeline
+    eng = gpu_engine
+    S, steps = 3000, 5
+    pk = eng.synth_express(S, 12, seed=9)
+    xy, _, st = eng.express_to_cart(pk, 360)
+    assert not st.any().item()
+    a = pipeline.ScanPipeline(eng, S, seed=4, scan_base=11)
+    b = pipeline.ScanPipeline(eng, S, seed=4, scan_base=11)
+    r0 = eng.ransac_lines(xy, seed=4, scan_base=11)
+    a.install_map_from_lines(r0["line"], r0["ninl"])
+    b.install_map_from_lines(r0["line"], r0["ninl"])
+    h_in = b.alloc_host_io(kind, 12)
+    h_in.copy_(pk if kind == "packets" else xy)
+    want = []
+    for _ in range(steps):
+        ra = a.step(xy)
+        torch.cuda.synchronize()
+        want.append({k: ra[k].cpu().clone() for k in b.result_keys()})
+    torch.cuda.synchronize()
+
+    def check(i, res):
+        res["done"].synchronize()
+        for k in b.result_keys():
+            assert torch.equal(want[i][k].view(torch.uint8), res[k].view(torch.uint8)), "step %d %s" % (i, k)
+
+    pending = None
+    for i in range(steps):
+        res = b.step_host(h_in, slices=4, wait=False)
+        if pending is not None:
+            check(i - 1, pending)
+        pending = res
+    check(steps - 1, pending)
+    b.drain()
+    torch.cuda.synchronize()
+    assert torch.equal(a.tables["life"], b.tables["life"])
+    with pytest.raises(ValueError):
+        b.step_host(h_in, slices=1, wait=False)
+
+
 @pytest.mark.parametrize("slices", [1, 3])
 def test_host_step_returns_the_projected_inlier_points(gpu_engine, slices):
     """step_host(points=True): what landmark_extraction itself returns (ransac_functions.py:28,46-55) for every chunk of
