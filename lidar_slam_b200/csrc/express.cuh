@@ -21,7 +21,7 @@ constexpr int kExpressBytes = 84;
 constexpr int kExpressWords = 21;
 constexpr int kExpressMaxWarps = 12;
 constexpr int kExpressRow = kExpressWords + 3;                 // words per warp row in shared memory
-constexpr int kExpressSmem = kExpressRow * kExpressMaxWarps * 4 + 16;
+constexpr int kExpressSmem = 2 * kExpressRow * kExpressMaxWarps * 4 + 16;   // two packet rows per warp
 // sin/cos tables of the decoder: 360 whole degrees + 2048 steps of 1/2048 degree, (sin, cos) pairs
 constexpr int kExpressTabPairs = 360 + 2048;
 constexpr int kExpressTabDoubles = 2 * kExpressTabPairs;
@@ -41,109 +41,133 @@ __device__ __forceinline__ double py_mod(double a, double m)
 
 __device__ __forceinline__ unsigned express_byte(const uint32_t *w, int off) { return (w[off >> 2] >> ((off & 3) * 8)) & 0xffu; }
 
+// position of row r of the sub-degree table in shared memory (see the staging loop of express_to_cart_kernel)
+__device__ __forceinline__ int express_swz(int r) { return r ^ ((r >> 7) & 7); }
+
 // status bits per revolution
 constexpr int kExpressBadSync = 1, kExpressBadChecksum = 2;
 
-// Persistent warps, one packet per warp iteration, no block-level synchronisation: packet pk of the
-// batch (revolution pk / P, position pk % P) goes to warp pk mod (warps in the grid).  The next
-// packet's words are loaded before the current one is decoded (software pipelining), so every warp keeps
-// two 84-byte loads and one 512-byte store in flight.  `status` must be zero on entry (the entry point
-// clears it): a rejected packet ORs its bit into its revolution's word.
-__global__ void express_to_cart_kernel(const uint32_t *__restrict__ packets, long long nscans, int P, int beams,
-                                       double2 *__restrict__ xy, double2 *__restrict__ meas, int32_t *__restrict__ status,
-                                       const double2 *__restrict__ trig)
+// Persistent warps, TWO consecutive packets per warp iteration, no block-level synchronisation: packets 2 j and 2 j + 1 of
+// the batch go to warp j mod (warps in the grid); lanes 0-15 decode the first, lanes 16-31 the second, a lane per CABIN
+// (5 bytes = two measures), so the byte extraction and the angle base are shared by two points and every lane stores 32
+// contiguous bytes.  Addressing is incremental (a packet pointer, an output index and the position in the revolution advance
+// by constants), the floor-mods are conditional additions (their operands are 15-bit fields).  The next pair's words are
+// loaded before the current one is decoded (software pipelining in registers; a four-deep cp.async ring of 4-byte copies
+// measured slower, 2.16 against 2.01 ms per 1M revolutions).  `status` must be zero on entry (the entry point clears it):
+// a rejected packet ORs its bit into its revolution's word.
+__global__ void __launch_bounds__(32 * kExpressMaxWarps, 3)
+express_to_cart_kernel(const uint32_t *__restrict__ packets, long long nscans, int P, int beams, double2 *__restrict__ xy,
+                       double2 *__restrict__ meas, int32_t *__restrict__ status, const double2 *__restrict__ trig)
 {
     LSLAM_SMEM_DECL;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-    uint32_t *ww = reinterpret_cast<uint32_t *>(smem_raw) + warp * kExpressRow;       // this warp's packet bytes
+    const int half = lane >> 4, cab = lane & 15;
+    uint32_t *ww = reinterpret_cast<uint32_t *>(smem_raw) + warp * 2 * kExpressRow;   // this warp's two packets
     // (sin, cos) of d degrees [0, 360) and of b/2048 degree [0, 2048): staged once per CTA
     double2 *tab = reinterpret_cast<double2 *>(smem_raw + ((kExpressSmem + 15) & ~15));
-    for (int k = threadIdx.x; k < kExpressTabPairs; k += blockDim.x) tab[k] = trig[k];
+    // The sub-degree table is read at (k2048 & 2047), and at a steady rotation that index moves by a multiple of 128 from one
+    // measure to the next (30 degrees per packet = 1920 / 2048 degree per measure): rows 2 KB apart, all in the same four
+    // banks.  XOR-ing bits 7-9 of the row into its low three bits spreads them over the eight 16-byte bank groups (express_swz).
+    for (int k = threadIdx.x; k < kExpressTabPairs; k += blockDim.x) tab[k < 360 ? k : 360 + express_swz(k - 360)] = trig[k];
     __syncthreads();
     const double nan = __longlong_as_double(0x7ff8000000000000LL);
-    const long long stride = (long long)gridDim.x * wpb, first = (long long)blockIdx.x * wpb + warp;
+    const long long stride = 2 * (long long)gridDim.x * wpb, first = 2 * ((long long)blockIdx.x * wpb + warp);
     const long long npk = nscans * P;
     if (first >= npk) return;
-    // All addressing is incremental: a packet pointer, an output index and the packet's position in its revolution advance
-    // by constants (the 64-bit index products per packet cost 12 % of the kernel; with them gone it runs at 2.7 TB/s of
-    // stores + 0.5 TB/s of loads, 83 % of the store rate of a device-to-device copy - two packets per warp iteration with a
-    // lane per cabin, half the instructions per point, measured the same 2.24 ms per 1M revolutions).
     const long long stride_scan = stride / P;
     const int stride_p = (int)(stride - stride_scan * P);
-    long long scan = first / P;
+    long long scan = first / P;                                                // of the pair's FIRST packet (warp-uniform)
     int p = (int)(first - scan * P);
-    const uint32_t *pkt = packets + (size_t)first * kExpressWords;            // this warp's current packet
+    const uint32_t *pkt = packets + (size_t)first * kExpressWords;
     const long long pkt_step = stride * kExpressWords;
-    long long obase = scan * beams + (long long)p * 32;                        // output index of the packet's first measure
+    long long obase = scan * beams + (long long)p * 32;                        // output index of the first packet's first measure
     const long long o_step = stride_scan * beams + (long long)stride_p * 32, o_wrap = (long long)beams - (long long)P * 32;
-    const unsigned char *wb = reinterpret_cast<const unsigned char *>(ww);
-    // lane constants: the cabin of this measure and where its bytes sit in the packet
-    const int ci = 5 * (lane >> 1), lo = (lane & 1) ? ci + 6 : ci + 4, sh_a = (lane & 1) ? 4 : 0;
-    auto load = [&](const uint32_t *pk_, int pp, uint32_t &w_, uint32_t &n_) {
-        w_ = lane < kExpressWords ? pk_[lane] : 0u;
-        n_ = (pp + 1 == P) ? *(pk_ - (ptrdiff_t)pp * kExpressWords) : pk_[kExpressWords];   // next packet's first word
+    const unsigned char *wb = reinterpret_cast<const unsigned char *>(ww + half * kExpressRow) + 4 + 5 * cab;   // my cabin
+    // words of both packets (42 consecutive words: lanes 0-20 the first, again the second) and, per half, the first word of
+    // the packet that FOLLOWS mine in its revolution (its start angle; after the last packet: the first packet's)
+    auto load = [&](const uint32_t *pk_, int pp, bool two, uint32_t &wa_, uint32_t &wb_, uint32_t &n_) {
+        wa_ = lane < kExpressWords ? pk_[lane] : 0u;
+        wb_ = (two && lane < kExpressWords) ? pk_[kExpressWords + lane] : 0u;
+        int pm = pp + half;                                                    // my packet's position in its revolution
+        if (pm == P) pm = 0;
+        const uint32_t *mine = pk_ + half * kExpressWords;
+        n_ = (half && !two) ? 0u : ((pm + 1 == P) ? *(mine - (ptrdiff_t)pm * kExpressWords) : mine[kExpressWords]);
     };
-    uint32_t w, nw0;
-    load(pkt, p, w, nw0);
+    uint32_t wA, wB, nw0;
+    load(pkt, p, first + 1 < npk, wA, wB, nw0);
     for (long long pk = first; pk < npk; pk += stride) {
-        // prefetch the following packet of this warp
+        const bool two = pk + 1 < npk;
+        // prefetch the following pair of this warp
         long long scan_n = scan + stride_scan, obase_n = obase + o_step;
         int p_n = p + stride_p;
         if (p_n >= P) { p_n -= P; ++scan_n; obase_n += o_wrap; }
         const uint32_t *pkt_n = pkt + pkt_step;
-        uint32_t w_n = 0u, nw0_n = 0u;
-        if (pk + stride < npk) load(pkt_n, p_n, w_n, nw0_n);
+        uint32_t wA_n = 0u, wB_n = 0u, nw0_n = 0u;
+        if (pk + stride < npk) load(pkt_n, p_n, pk + stride + 1 < npk, wA_n, wB_n, nw0_n);
 
-        if (lane < kExpressWords) ww[lane] = w;
+        if (lane < kExpressWords) { ww[lane] = wA; ww[kExpressRow + lane] = wB; }
         // checksum over bytes 2..83 = all words with the two sync bytes masked off
-        uint32_t x = __reduce_xor_sync(0xffffffffu, lane == 0 ? (w & 0xffff0000u) : w);
+        const uint32_t xa = __reduce_xor_sync(0xffffffffu, lane == 0 ? (wA & 0xffff0000u) : wA);
+        const uint32_t xb = __reduce_xor_sync(0xffffffffu, lane == 0 ? (wB & 0xffff0000u) : wB);
+        const uint32_t w0a = __shfl_sync(0xffffffffu, wA, 0), w0b = __shfl_sync(0xffffffffu, wB, 0);
+        uint32_t x = half ? xb : xa;
+        const uint32_t w0 = half ? w0b : w0a;
         x ^= x >> 16;
         x = (x ^ (x >> 8)) & 0xffu;
-        const uint32_t w0 = __shfl_sync(0xffffffffu, w, 0);
         int st = 0;
         if (((w0 >> 4) & 0xfu) != 0xAu || ((w0 >> 12) & 0xfu) != 0x5u) st |= kExpressBadSync;
         else if (x != ((w0 & 0xfu) | (((w0 >> 8) & 0xfu) << 4))) st |= kExpressBadChecksum;
         __syncwarp();
-        if (p * 32 + lane < beams) {
-            const unsigned b_lo = wb[lo], b_hi = wb[lo + 1], b_a = wb[ci + 8];
-            const int dist = (int)(b_lo >> 2) + (int)(b_hi << 6);                       // lidar.py:85,88
-            int code = (int)((b_a >> sh_a) & 0xfu) + (int)((b_lo & 3u) << 4);
-            if (code & 16) code -= 32;                                                   // twos_comp(., 5)
+        // my packet: position in its revolution, revolution, output index of its first measure
+        int pm = p + half;
+        long long scan_m = scan, o = obase + 32 * half;
+        if (pm == P) { pm = 0; ++scan_m; o += o_wrap; }
+        const int k = pm * 32 + 2 * cab;                                       // index of the cabin's first measure in the revolution
+        if ((two || !half) && k < beams) {
+            const unsigned b0 = wb[0], b1 = wb[1], b2 = wb[2], b3 = wb[3], b4 = wb[4];
+            const int dist0 = (int)(b0 >> 2) + (int)(b1 << 6), dist1 = (int)(b2 >> 2) + (int)(b3 << 6);   // lidar.py:85,88
+            int code0 = (int)(b4 & 0xfu) + (int)((b0 & 3u) << 4), code1 = (int)(b4 >> 4) + (int)((b2 & 3u) << 4);
+            if (code0 & 16) code0 -= 32;                                                 // twos_comp(., 5)
+            if (code1 & 16) code1 -= 32;
             // lidar.py:80,185  angle = (start + ((next - start) % 360)/32 * trame - dtheta) % 360 with
             // start = q6/64, dtheta = code/8.  Every term is a multiple of 1/2048 degree below 2^11, so
             // the reference's float arithmetic is exact and the same value comes out of integers in
-            // units of 1/2048 degree (Python's % on floats = floor-mod).  The operands are 15-bit fields, which bounds
-            // both differences: the floor-mods are a few conditional additions instead of integer divisions.
+            // units of 1/2048 degree (Python's % on floats = floor-mod).
             const int sq = (int)((w0 >> 16) & 0x7fffu);                                   // start, q6
             const int nq = (int)((nw0 >> 16) & 0x7fffu);                                  // next start, q6
             int dq = nq - sq;                                                             // in (-32768, 32768); mod 360 * 64
             if (dq < 0) dq += 23040;
             if (dq < 0) dq += 23040;
             if (dq >= 23040) dq -= 23040;
-            int k2048 = sq * 32 + dq * (lane + 1) - code * 256;                           // in (-4096, 3 * 360 * 2048); mod 360 * 2048
-            if (k2048 >= 737280) k2048 -= 737280;
-            if (k2048 >= 737280) k2048 -= 737280;
-            if (k2048 < 0) k2048 += 737280;
-            const double d = (double)dist;
-            const long long o = obase + lane;
-            if (st == 0) {
-                // functions.py:59-60: x = d cos(pi/2 - theta), y = d sin(pi/2 - theta), theta = ang pi/180,
-                // i.e. x = d sin(theta), y = d cos(theta).  ang is an exact multiple of 1/2048 degree:
-                // theta = (a + b/2048) degrees, and the angle-sum formulas on two table entries give
-                // sin/cos to ~1 ulp without the ~100 fp64 instructions of a general sincos.
-                const double2 A = tab[k2048 >> 11], Bq = tab[360 + (k2048 & 2047)];       // (sin, cos)
-                const double sn = fma(A.x, Bq.y, A.y * Bq.x);                             // sin(a + b)
-                const double cs = fma(A.y, Bq.y, -(A.x * Bq.x));                          // cos(a + b)
-                xy[o] = make_double2(__dmul_rn(d, sn), __dmul_rn(d, cs));
-                if (meas) meas[o] = make_double2((double)k2048 * (1.0 / 2048.0), d);
-            } else {
-                xy[o] = make_double2(nan, nan);
-                if (meas) meas[o] = make_double2(nan, nan);
+            const int base = sq * 32 + dq * (2 * cab + 1);                                // trame = measure index + 1
+            o += 2 * cab;
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                if (j == 1 && k + 1 >= beams) break;
+                int k2048 = base + (j ? dq : 0) - (j ? code1 : code0) * 256;              // in (-4096, 3 * 360 * 2048); mod 360 * 2048
+                if (k2048 >= 737280) k2048 -= 737280;
+                if (k2048 >= 737280) k2048 -= 737280;
+                if (k2048 < 0) k2048 += 737280;
+                const double d = (double)(j ? dist1 : dist0);
+                if (st == 0) {
+                    // functions.py:59-60: x = d cos(pi/2 - theta), y = d sin(pi/2 - theta), theta = ang pi/180,
+                    // i.e. x = d sin(theta), y = d cos(theta).  ang is an exact multiple of 1/2048 degree:
+                    // theta = (a + b/2048) degrees, and the angle-sum formulas on two table entries give
+                    // sin/cos to ~1 ulp without the ~100 fp64 instructions of a general sincos.
+                    const double2 A = tab[k2048 >> 11], Bq = tab[360 + express_swz(k2048 & 2047)];   // (sin, cos)
+                    const double sn = fma(A.x, Bq.y, A.y * Bq.x);                         // sin(a + b)
+                    const double cs = fma(A.y, Bq.y, -(A.x * Bq.x));                      // cos(a + b)
+                    xy[o + j] = make_double2(__dmul_rn(d, sn), __dmul_rn(d, cs));
+                    if (meas) meas[o + j] = make_double2((double)k2048 * (1.0 / 2048.0), d);
+                } else {
+                    xy[o + j] = make_double2(nan, nan);
+                    if (meas) meas[o + j] = make_double2(nan, nan);
+                }
             }
         }
-        if (st != 0 && lane == 0 && status) atomicOr(status + scan, st);
+        if (st != 0 && cab == 0 && (two || !half) && status) atomicOr(status + scan_m, st);
         __syncwarp();
-        w = w_n; nw0 = nw0_n; scan = scan_n; p = p_n; pkt = pkt_n; obase = obase_n;
+        wA = wA_n; wB = wB_n; nw0 = nw0_n; scan = scan_n; p = p_n; pkt = pkt_n; obase = obase_n;
     }
 }
 

@@ -1013,14 +1013,20 @@ extern "C" int lslam_express_to_cart(void *handle, const uint8_t *packets, int64
         return fail(h, LSLAM_ERR_BAD_ARG, "lslam_express_to_cart: xy/meas must be 16-byte, packets 4-byte aligned");
     if (nscans == 0) return LSLAM_OK;
     DeviceGuard g(h->device);
-    unsigned grid; int threads;
-    express_shape(h, nscans, packets_per_scan, &grid, &threads);
-    threads = 32 * kExpressMaxWarps;
+    const int threads = 32 * kExpressMaxWarps;
     if (status) LSLAM_CUDA_TRY(h, cudaMemsetAsync(status, 0, sizeof(int32_t) * (size_t)nscans, (cudaStream_t)stream));
     auto kern = express_to_cart_kernel;
 #ifndef LSLAM_EMU
     LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kExpressDecodeSmem));
 #endif
+    // persistent warps (a pair of packets per iteration): exactly the CTAs that are resident at a time - a grid larger than
+    // that runs its tail as a second, half-empty wave
+    int per_sm = 0;
+    LSLAM_CUDA_TRY(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, (size_t)kExpressDecodeSmem));
+    if (per_sm < 1) per_sm = 1;
+    const long long pairs = ((long long)nscans * packets_per_scan + 1) / 2, want = (pairs + kExpressMaxWarps - 1) / kExpressMaxWarps;
+    const long long cap = (long long)per_sm * h->sms;
+    const unsigned grid = (unsigned)(want < cap ? want : cap);
     LSLAM_LAUNCH(kern, grid, threads, kExpressDecodeSmem, (cudaStream_t)stream, reinterpret_cast<const uint32_t *>(packets),
                  (long long)nscans, (int)packets_per_scan, (int)beams, reinterpret_cast<double2 *>(xy),
                  reinterpret_cast<double2 *>(meas), status, reinterpret_cast<const double2 *>(h->express_tab_d));
