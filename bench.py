@@ -696,6 +696,12 @@ def main():
                     "frac": S * BYTES_PER_SCAN / (k_ms * 1e-3) * 1e-9 / hbm_peak,
                     "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
         }
+        if tsrc and "issue_active_pct" in tsrc:
+            # north_star's other yardstick ("HBM or issue roofline"): issue slots in use, from the same ncu capture - a
+            # profiler figure of the current kernel at the captured size, not measured in this run
+            roofline["issue"] = {"achieved": tsrc["issue_active_pct"], "peak": 100.0, "unit": "% of issue slots active",
+                                 "frac": tsrc["issue_active_pct"] / 100.0, "warps_active_pct": tsrc.get("warps_active_pct"),
+                                 "source": "ncu smsp__issue_active.avg.pct_of_peak_sustained_active (%s)" % tsrc["file"]}
         cpu = None
         if world == 1 and not args.no_cpu:
             n = args.cpu_sample or 16384

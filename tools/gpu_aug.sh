@@ -16,3 +16,8 @@ echo "launches rc=$?" ; python tools/aug_launch_summary.py $OUT/${TAG}_aug_launc
 echo "== aug ncu full (Pzx GEMM = 27th GEMM launch)"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:aug_gemm_tma -s 26 -c 1 -f -o $OUT/${TAG}_aug_gemm $CMD > $OUT/${TAG}_aug_ncu_full.log 2>&1
 echo "full rc=$?"
+echo "== aug ncu full (a SOLVE GEMM late in a factorisation, the diagonal-block kernel)"
+timeout 900 ncu --set full --clock-control none --import-source on -k "regex:aug_gemm_tma_kernel<32, 64, 1, 8, 3, 1" -s 30 -c 1 -f -o $OUT/${TAG}_aug_solve $CMD > $OUT/${TAG}_aug_ncu_solve.log 2>&1
+echo "solve rc=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:aug_chol_diag -s 20 -c 1 -f -o $OUT/${TAG}_aug_diag $CMD > $OUT/${TAG}_aug_ncu_diag.log 2>&1
+echo "diag rc=$?"

@@ -22,6 +22,10 @@ for h, u, v in zip(hdr, units, vals):
         out["kernel"] = v
     if h == "gpu__time_duration.sum":
         out["ncu_duration"] = v + " " + u
+    if h == "smsp__issue_active.avg.pct_of_peak_sustained_active":
+        out["issue_active_pct"] = float(v.replace(",", ""))
+    if h == "sm__warps_active.avg.pct_of_peak_sustained_active":
+        out["warps_active_pct"] = float(v.replace(",", ""))
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 json.dump(out, open(os.path.join(root, "profiles", "ransac_traffic.json"), "w"), indent=1)
 print(out)
