@@ -16,6 +16,8 @@ from . import batch
 
 
 class ScanPipeline:
+    _OV_STREAMS = ("in", "dec", "ran", "run", "out")     # the overlapped host path's streams (step_host with slices > 1)
+
     def __init__(self, eng, streams, beams=360, chunk=batch.CHUNK, trials=batch.MAX_TRIALS,
                  thr=batch.THRESHOLD, table_capacity=8, seed=0, scan_base=0):
         self.eng = eng
@@ -67,15 +69,24 @@ class ScanPipeline:
         Asynchronous on the current stream.  Returns the dict of result tensors (views of buffers
         owned by the pipeline, overwritten next step).  ``ransac_events`` = (start, end)
         torch.cuda.Event pair recorded around the RANSAC launch."""
-        eng = self.eng
         s1 = self.S if s1 is None else s1
-        v = self._views(s0, s1)
         if ransac_events is not None:
             ransac_events[0].record()
-        r = eng.ransac_lines(xy, chunk=self.chunk, trials=self.trials, thr=self.thr, seed=self.seed,
-                             scan_base=self.scan_base + s0, out=v["rout"])
+        r = self._step_ransac(xy, s0, s1)
         if ransac_events is not None:
             ransac_events[1].record()
+        return self._step_post(r, s0, s1, u)
+
+    def _step_ransac(self, xy, s0, s1):
+        """First kernel of a step (line extraction) for streams [s0, s1), on the current stream."""
+        v = self._views(s0, s1)
+        return self.eng.ransac_lines(xy, chunk=self.chunk, trials=self.trials, thr=self.thr, seed=self.seed,
+                                     scan_base=self.scan_base + s0, out=v["rout"])
+
+    def _step_post(self, r, s0, s1, u=None):
+        """Association and filter kernels of a step for streams [s0, s1), on the current stream; r = _step_ransac's result."""
+        eng = self.eng
+        v = self._views(s0, s1)
         a = eng.associate(r["line"], v["tables"], q_valid=r["ninl"], out=v["aout"])
         # measurement slot c = chunk c's line: range/bearing of its inlier centroid against the matched
         # stored landmark's position; slots whose line missed (match < 0) are not used
@@ -214,13 +225,15 @@ class ScanPipeline:
                 out = dict(out, points=[self._pts["host"][:rows]])
             return out
         if self._ov is None or self._ov["K"] != K:
-            self._ov = {"K": K, "in": torch.cuda.Stream(dev), "run": torch.cuda.Stream(dev),
+            self._ov = {"K": K, "in": torch.cuda.Stream(dev), "run": torch.cuda.Stream(dev), "dec": torch.cuda.Stream(dev),
+                        "ran": torch.cuda.Stream(dev), "ev_ran": [torch.cuda.Event() for _ in range(K)],
                         "out": torch.cuda.Stream(dev), "ev_in": [torch.cuda.Event() for _ in range(K)],
+                        "ev_dec": [torch.cuda.Event() for _ in range(K)],
                         "ev_run": [torch.cuda.Event() for _ in range(K)],
                         "ev_out": [torch.cuda.Event() for _ in range(K)], "primed": False}
         ov = self._ov
         cur = torch.cuda.current_stream(dev)
-        for st in ("in", "run", "out"):
+        for st in self._OV_STREAMS:
             ov[st].wait_stream(cur)
         for k, (a, b) in enumerate(bounds):
             with torch.cuda.stream(ov["in"]):
@@ -229,13 +242,27 @@ class ScanPipeline:
                 dev_in[a:b].copy_(host_in[a:b], non_blocking=True)
                 ov["ev_in"][k].record()
         for k, (a, b) in enumerate(bounds):
-            with torch.cuda.stream(ov["run"]):
-                ov["run"].wait_event(ov["ev_in"][k])
-                if ov["primed"]:
-                    ov["run"].wait_event(ov["ev_out"][k])     # the previous step's results have left
-                if packets:
+            if packets:
+                # the packet decode (store-bound) on a stream of its own: slice k + 1 is decoded while slice k's association
+                # and filter kernels run (the RANSAC kernel fills every SM, so it only overlaps that kernel's tail)
+                with torch.cuda.stream(ov["dec"]):
+                    ov["dec"].wait_event(ov["ev_in"][k])
+                    if ov["primed"]:
+                        ov["dec"].wait_event(ov["ev_run"][k])  # the previous step's kernels have read this slice's points
+                        ov["dec"].wait_event(ov["ev_out"][k])  # ... and its status words have left
                     self.eng.express_to_cart(dev_in[a:b], self.N, xy=self.xy_dev[a:b], status=self.status_dev[a:b])
-                res = self.step(self.xy_dev[a:b], s0=a, s1=b)
+                    ov["ev_dec"][k].record()
+            with torch.cuda.stream(ov["ran"]):
+                ov["ran"].wait_event(ov["ev_dec" if packets else "ev_in"][k])
+                if ov["primed"]:
+                    ov["ran"].wait_event(ov["ev_out"][k])     # the previous step's results have left
+                rr = self._step_ransac(self.xy_dev[a:b], a, b)
+                ov["ev_ran"][k].record()
+            # association + filter on the next stream: they leave most of an SM's warp slots empty, and slice k + 1's line
+            # extraction fills in beside them
+            with torch.cuda.stream(ov["run"]):
+                ov["run"].wait_event(ov["ev_ran"][k])
+                res = self._step_post(rr, a, b)
                 if points:
                     pts_k, off_k = self.project(self.xy_dev[a:b], res, a, b)
                     self._pts["total"][k:k + 1].copy_(off_k[-1:], non_blocking=True)
@@ -263,7 +290,7 @@ class ScanPipeline:
             done = torch.cuda.Event()
             done.record(ov["out"])
             return dict(out, done=done)
-        for st in ("in", "run", "out"):
+        for st in self._OV_STREAMS:
             cur.wait_stream(ov[st])
         return out
 
@@ -271,7 +298,7 @@ class ScanPipeline:
         """After pipelined steps (step_host(wait=False)): the current stream waits for everything they queued."""
         if self._ov is not None:
             cur = torch.cuda.current_stream(self.eng.device)
-            for st in ("in", "run", "out"):
+            for st in self._OV_STREAMS:
                 cur.wait_stream(self._ov[st])
 
     def io_bytes(self, host_in=None):
