@@ -605,7 +605,7 @@ __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int pa
         }                                                                                         \
     }
             for (; k + 32 <= n_eff; k += 32, ++w) {
-#pragma unroll 4
+#pragma unroll
                 for (int kk = 0; kk < 32; kk += 2) { const float4 pp = Pf4[(k + kk) >> 1]; LSLAM_TILE_STEP2(pp.x, pp.y, pp.z, pp.w); }
 #pragma unroll
                 for (int k_ = 0; k_ < TPT; ++k_) {
