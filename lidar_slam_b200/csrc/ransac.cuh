@@ -129,8 +129,10 @@ __device__ __forceinline__ void warp_literal_score(const double2 *P, int n, cons
 }
 
 // order-preserving 32-bit keys of non-negative doubles (high word), rounded down / up
-__device__ __forceinline__ int key_down(double v) { return v > 0.0 ? __double2hiint(v) : 0; }
-__device__ __forceinline__ int key_up(double v) { return v > 0.0 ? __double2hiint(v) + 1 : 1; }
+// (the high word of a double <= 0 is negative as an int, or 0 for +0: an integer max instead of an fp64 compare + select;
+//  a NaN maps to a huge key - every caller scores such a trial literally)
+__device__ __forceinline__ int key_down(double v) { const int h = __double2hiint(v); return h > 0 ? h : 0; }
+__device__ __forceinline__ int key_up(double v) { const int h = __double2hiint(v); return (h > 0 ? h : 0) + 1; }
 
 // candidate test of trial t for the tie-break: tied on the maximal count and its lower bound
 // does not exceed the smallest upper bound

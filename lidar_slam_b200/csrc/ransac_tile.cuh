@@ -44,6 +44,7 @@ struct TileSlot {
     double best_ss;
     double alpha, beta;                // bound on |sum r^2 - sum s^2| = alpha + beta * sum s^2 (ssum_bound_coeffs)
     double A, nn;                      // Sxx + Syy and n as a double
+    double kb;                         // (1 + beta) x the factor of tile_moment_err: the moment form's own error inside the bound
     float bandf, pad_f;                // fp32 screening: | |s_f| - thr_f | below this -> literal re-score
     int off, n, valid, c;
     int scale_hi;                      // high word of the largest |coordinate| of the slot
@@ -191,9 +192,10 @@ __device__ __forceinline__ double tile_moment_sum(double nx, double ny, double c
     const double quad = fma(nx, a1, ny * a2), lin = fma(nx, st->Sx, ny * st->Sy);
     return fma(cp, fma(nn, cp, 2.0 * lin), quad);
 }
+__device__ __forceinline__ double tile_moment_err_factor(double nn) { return (5.0 * (nn + 32.0) + 20.0) * 0x1p-53 * 1.01; }
 __device__ __forceinline__ double tile_moment_err(double cp, double nn, double A)
 {
-    return (5.0 * (nn + 32.0) + 20.0) * 0x1p-53 * 1.01 * fma(nn * cp, cp, A);
+    return tile_moment_err_factor(nn) * fma(nn * cp, cp, A);
 }
 
 // score of one hypothesis by a whole warp with the fp64 fast line (lslam_core.cuh FastLine: |s| is within 2^-40 S of the
@@ -215,7 +217,7 @@ __device__ __forceinline__ void warp_fast64_score_strided(const double2 *P, int 
         }
         const unsigned b = __ballot_sync(LSLAM_FULL_MASK, in);
         c += __popc(b);
-        if (lane == 0) mask_out[(k0 >> 5) * stride] = b;
+        if (lane == 0) mask_out[(k0 >> 5) * stride] = __brev(b);     // the per-trial words are kept bit-reversed (tile_score)
     }
     cnt = c;
     near = __any_sync(LSLAM_FULL_MASK, nr);
@@ -237,7 +239,7 @@ __device__ __forceinline__ void warp_literal_score_strided(const double2 *P, int
         }
         const unsigned b = __ballot_sync(LSLAM_FULL_MASK, in);
         c += __popc(b);
-        if (mask_out != nullptr && lane == 0) mask_out[(k0 >> 5) * stride] = b;
+        if (mask_out != nullptr && lane == 0) mask_out[(k0 >> 5) * stride] = __brev(b);   // bit-reversed like the fast words
     }
     cnt = c;
     ssum = warp_tree32(part);
@@ -336,6 +338,7 @@ __device__ __forceinline__ void tile_stage(const RansacArgs &a, int tile, int pa
             st->best_ss = 0.0;
             const SsumBound sbq = ssum_bound_coeffs_inv(cb.eabs, n, a.thr, a.inv_thr);
             st->alpha = sbq.alpha; st->beta = sbq.beta; st->A = sxx + syy; st->nn = (double)n;
+            st->kb = (1.0 + sbq.beta) * tile_moment_err_factor((double)n);
             st->off = off; st->n = n; st->valid = valid ? 1 : 0; st->c = c;
             st->scale_hi = mh;
             bool force = cb.force_literal;
@@ -538,6 +541,8 @@ __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int pa
     const double2 *P = pts + st->off;
     const int row0 = (q * W * TPT) * ipc + tb;                    // trial k, word w: mw[row0 + (w * TPT + k) * ipc]
     int2 *krow = keys + (size_t)q * TPT * ipc + tb;               // trial k: krow[k * ipc]
+    // (the per-trial inlier words in `mw` are kept BIT-REVERSED, as the funnel shifts of the loop leave them: only the
+    //  winner's words are reversed, when they are copied to `smask` - 4 BREV per chunk instead of 16 per thread)
     int cnt[TPT];
     unsigned live = 0, exact = 0;                                 // bit k: trial t0 + k exists / was scored literally
     {
@@ -549,7 +554,7 @@ __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int pa
         unsigned bits[TPT];
         float mab[TPT];
         unsigned flagl = 0;                                       // bit k: trial t0 + k must be scored literally
-        const double nn = st->nn, A = st->A, sb_alpha = st->alpha, sb_beta = st->beta, c0x = st->c0x, c0y = st->c0y;
+        const double nn = st->nn, A = st->A, sb_alpha = st->alpha, sb_beta = st->beta, kb = st->kb, c0x = st->c0x, c0y = st->c0y;
 #pragma unroll
         for (int k = 0; k < TPT; k += 2) {
             const Philox4 ph = philox4x32_10((uint32_t)(t0 + k) >> 1, (uint32_t)st->c, (uint32_t)scan, (uint32_t)(scan >> 32),
@@ -576,13 +581,15 @@ __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int pa
                         nx[k + h] = f.nx; ny[k + h] = f.ny; ng[k + h] = f.negc;
                     }
                     // residual sum from the moments with its error bound -> the two keys the tie-break needs
+                    // E = beta (M+ + e2) + alpha + e2 with e2 = tile_moment_err(cp): the per-slot factors are folded (kb)
                     const double M = tile_moment_sum(fnx, fny, cp, nn, st);
-                    const double e2 = tile_moment_err(cp, nn, A);
-                    const double E = fma(sb_beta, (M > 0.0 ? M : 0.0) + e2, sb_alpha) + e2;
-                    krow[(k + h) * ipc] = make_int2(key_down(M - E), key_up(M + E));
+                    const double E = fma(kb, fma(nn * cp, cp, A), fma(sb_beta, M > 0.0 ? M : 0.0, sb_alpha));
+                    const double up = M + E;
+                    krow[(k + h) * ipc] = make_int2(key_down(M - E), key_up(up));
                     // literal score wanted: coincident samples, a chunk outside the fast path's range, a non-finite sum /
-                    // bound.  (A point too close to the threshold - known after the loop - gets the fp64 fast line first.)
-                    if (degen || force_lit || !(fabs(M) + E <= 1.7976931348623157e308)) flagl |= 1u << (k + h);
+                    // bound (exponent field of M + E all ones; E >= 0, so an infinite or NaN M or E always shows there).
+                    // (A point too close to the threshold - known after the loop - gets the fp64 fast line first.)
+                    if (degen || force_lit || (__double2hiint(up) & 0x7ff00000) == 0x7ff00000) flagl |= 1u << (k + h);
                 }
             }
         }
@@ -609,7 +616,7 @@ __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int pa
                 for (int kk = 0; kk < 32; kk += 2) { const float4 pp = Pf4[(k + kk) >> 1]; LSLAM_TILE_STEP2(pp.x, pp.y, pp.z, pp.w); }
 #pragma unroll
                 for (int k_ = 0; k_ < TPT; ++k_) {
-                    const unsigned m = __brev(bits[k_]);              // bit j = point 32 w + j
+                    const unsigned m = bits[k_];                      // bit 31 - j = point 32 w + j (reversed: see below)
                     cnt[k_] += __popc(m);
                     mw[row0 + (w * TPT + k_) * ipc] = m;
                 }
@@ -626,7 +633,7 @@ __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int pa
                 const int sh = rem & 1;
 #pragma unroll
                 for (int k_ = 0; k_ < TPT; ++k_) {
-                    const unsigned m = __brev((bits[k_] >> sh) << (32 - rem));
+                    const unsigned m = (bits[k_] >> sh) << (32 - rem);
                     cnt[k_] += __popc(m);
                     mw[row0 + (w * TPT + k_) * ipc] = m;
                 }
@@ -653,7 +660,7 @@ __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int pa
                 for (int kk = 0; kk < 32; kk += 2) LSLAM_TILE_STEP2(P[k + kk], P[k + kk + 1]);
 #pragma unroll
                 for (int k_ = 0; k_ < TPT; ++k_) {
-                    const unsigned m = __brev(bits[k_]);              // bit j = point 32 w + j
+                    const unsigned m = bits[k_];                      // bit 31 - j = point 32 w + j (reversed: see below)
                     cnt[k_] += __popc(m);
                     mw[row0 + (w * TPT + k_) * ipc] = m;
                 }
@@ -667,7 +674,7 @@ __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int pa
                 const int sh = rem & 1;
 #pragma unroll
                 for (int k_ = 0; k_ < TPT; ++k_) {
-                    const unsigned m = __brev((bits[k_] >> sh) << (32 - rem));
+                    const unsigned m = (bits[k_] >> sh) << (32 - rem);
                     cnt[k_] += __popc(m);
                     mw[row0 + (w * TPT + k_) * ipc] = m;
                 }
@@ -773,7 +780,7 @@ __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int pa
                     // the first candidate's inlier words leave the scratch region; with several candidates the literal
                     // tie-break writes the winner's
                     if (pos == 0)
-                        for (int w2 = 0; w2 * 32 < n; ++w2) sm.smask[q * W + w2] = mw[row0 + (w2 * TPT + kc) * ipc];
+                        for (int w2 = 0; w2 * 32 < n; ++w2) sm.smask[q * W + w2] = __brev(mw[row0 + (w2 * TPT + kc) * ipc]);
                 }
             }
         }
