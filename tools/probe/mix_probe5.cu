@@ -25,7 +25,7 @@ __global__ void __launch_bounds__(256) mix(float *sink, int iters, float thf)
     __syncthreads();
     const int lane = threadIdx.x & 31;
     float acc = 0.f;
-    if (V == 0) {
+    if (V == 0 || V >= 3) {
         constexpr int CH = 4;
         float nx[CH], ny[CH], ng[CH], mab[CH];
         unsigned bits[CH];
@@ -40,16 +40,24 @@ __global__ void __launch_bounds__(256) mix(float *sink, int iters, float thf)
                 for (int c = 0; c < CH; ++c) {
                     const float fa = fabsf(fmaf(pp.y, ny[c], fmaf(pp.x, nx[c], ng[c]))) - thf;
                     const float fb = fabsf(fmaf(pp.w, ny[c], fmaf(pp.z, nx[c], ng[c]))) - thf;
-                    bits[c] = __funnelshift_l(__float_as_uint(fa), bits[c], 1);
-                    bits[c] = __funnelshift_l(__float_as_uint(fb), bits[c], 1);
-                    mab[c] = fminf(mab[c], fminf(fabsf(fa), fabsf(fb)));
+                    if (V != 3) {
+                        bits[c] = __funnelshift_l(__float_as_uint(fa), bits[c], 1);
+                        bits[c] = __funnelshift_l(__float_as_uint(fb), bits[c], 1);
+                    } else {
+                        bits[c] += __float_as_uint(fa) >> 31;                 // count only (LEA.HI)
+                        bits[c] += __float_as_uint(fb) >> 31;
+                    }
+                    if (V == 0 || V == 3) mab[c] = fminf(mab[c], fminf(fabsf(fa), fabsf(fb)));   // FMNMX3
+                    if (V == 5) { mab[c] = fminf(mab[c], fabsf(fa)); mab[c] = fminf(mab[c], fabsf(fb)); }   // 2 x FMNMX
+                    if (V == 6) mab[c] = fminf(mab[c], fabsf(fa * fb));                                    // FMUL + FMNMX
+                    if (V == 7) mab[c] = fmaf(fa, fb, mab[c]);                                             // stand-in: one FFMA
                 }
             }
         }
 #pragma unroll
         for (int c = 0; c < CH; ++c) acc += bits[c] + mab[c];
     } else {
-        constexpr int RT = V > 0 ? V : 1;                    // row tiles (16 trials each) per warp
+        constexpr int RT = (V == 1 || V == 2) ? V : 1;                    // row tiles (16 trials each) per warp
         unsigned a0[RT], a1[RT], a2[RT], a3[RT], bits0[RT], bits1[RT];
         float cp0[RT], cp1[RT], mab0[RT], mab1[RT];
 #pragma unroll
@@ -97,7 +105,7 @@ void run(const char *name, int blocks_per_sm)
     cudaEventRecord(e1); cudaEventSynchronize(e1);
     float ms; cudaEventElapsedTime(&ms, e0, e1);
     // PHE per thread and outer iteration: V0 32 points x 4 trials = 128; V>=1: 16 mma x RT row tiles x 128 PHE per warp / 32 lanes = 64 RT
-    const double per_thread = V == 0 ? 128.0 : 64.0 * V;
+    const double per_thread = (V == 0 || V >= 3) ? 128.0 : 64.0 * V;
     const double phe = (double)blocks * threads * iters * per_thread;
     const double cyc = (ms * 1e-3 * khz * 1e3 * sms * 4) / (phe / 32.0);
     printf("%-58s blocks/SM %d  %8.3f ms  %7.2f G PHE/s  %5.2f cycles/PHE-warp/SMSP\n", name, blocks_per_sm, ms, phe / ms * 1e-6, cyc);
@@ -151,6 +159,11 @@ int main()
         run<0>("T0 fp32 2FFMA+FADD+SHF+FMNMX3/2, 4 trials/thread", bps);
         run<1>("T1 mma.m16n8k8.tf32 + FADD+SHF+FMNMX3/2, 1 row tile", bps);
         run<2>("T2 mma.m16n8k8.tf32 + FADD+SHF+FMNMX3/2, 2 row tiles", bps);
+        run<3>("T3 fp32 2FFMA+FADD+LEA.HI(count)+FMNMX3/2, 4 trials/thread", bps);
+        run<4>("T4 fp32 2FFMA+FADD+SHF, no min tracking", bps);
+        run<5>("T5 fp32 2FFMA+FADD+SHF+FMNMX (2-input, 1 per PHE)", bps);
+        run<6>("T6 fp32 2FFMA+FADD+SHF+(FMUL+FMNMX)/2", bps);
+        run<7>("T7 fp32 2FFMA+FADD+SHF+FFMA/2 (no min)", bps);
     }
     return 0;
 }
