@@ -46,7 +46,6 @@ const char *lslam_last_error(void *handle);
 int lslam_abi_version(void);
 /* Launch-shape tuning knobs; 0 restores the built-in heuristic.  Results never depend on them.
  *   "ransac.kernel"  0 default, 1 phase-structured kernel, 2 warp-specialised persistent kernel, 3 tile kernel
- *   "ransac.screen"  tile kernel: 0 / 2 distance screened in fp32 on centred points, 1 in fp64
  *   "ransac.tpt"     trials per work item (1, 2, 4, 6, 8);  "ransac.slots_per_cta"  chunk slots per tile
  *   "ransac.scorers", "ransac.posts", "ransac.ring"   warp counts / ring depth of kernel 2
  *   "ransac.threads" CTA size of kernel 1 */

@@ -99,9 +99,6 @@ extern "C" int lslam_set_option(void *handle, const char *key, int64_t value)
     } else if (!strcmp(key, "ransac.threads")) {
         if (value < 0 || value > 1024 || value % 32) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.threads must be a multiple of 32 <= 1024");
         h->opt_threads = (int)value;
-    } else if (!strcmp(key, "ransac.screen")) {
-        if (value < 0 || value > 2) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.screen (tile kernel): 0 default (fp32), 1 fp64 high words, 2 fp32");
-        h->opt_screen = (int)value;
     } else if (!strcmp(key, "ransac.kernel")) {
         if (value < 0 || value > 3) return fail(h, LSLAM_ERR_BAD_ARG, "ransac.kernel: 0 default, 1 phase-structured, 2 warp-specialised, 3 tile");
         h->opt_kernel = (int)value;
@@ -161,10 +158,10 @@ static int launch_ransac(Handle *h, RansacArgs a, int threads_target, cudaStream
 
 // tile kernel (ransac_tile.cuh): one work item per thread, G = threads / ipc chunk slots per CTA.
 // Returns LSLAM_ERR_CAPACITY (without touching the handle's error text) when the shape does not fit it.
-template <int TPT, int MAXT, int MINB, bool F32>
+template <int TPT, int MAXT, int MINB>
 static int launch_ransac_tile(Handle *h, RansacArgs a, int threads, cudaStream_t st, bool probe_only = false)
 {
-    auto kern = ransac_tile_kernel<TPT, MAXT, MINB, F32>;
+    auto kern = ransac_tile_kernel<TPT, MAXT, MINB>;
     a.ipc = (a.trials + TPT - 1) / TPT;
     if (threads > MAXT) threads = MAXT;
     threads &= ~31;
@@ -174,7 +171,7 @@ static int launch_ransac_tile(Handle *h, RansacArgs a, int threads, cudaStream_t
     if ((long long)G > a.nslots) G = (int)a.nslots;
     size_t smem = 0;
     for (;; --G) {
-        smem = tile_smem_bytes(G, a.chunk, a.ipc, TPT, a.W, threads / 32, F32);
+        smem = tile_smem_bytes(G, a.chunk, a.ipc, TPT, a.W, threads / 32);
         if (smem <= (size_t)h->smem_optin || G == 1) break;
     }
     if (smem > (size_t)h->smem_optin) return LSLAM_ERR_CAPACITY;
@@ -196,23 +193,13 @@ static int launch_ransac_tile(Handle *h, RansacArgs a, int threads, cudaStream_t
 
 static int dispatch_ransac_tile(Handle *h, const RansacArgs &a, int tpt, int threads, cudaStream_t st, bool probe_only = false)
 {
-    // screening precision of the hot loop: fp32 on centred points by default, ransac.screen = 1 keeps fp64 (high words)
-    if (h->opt_screen == 1) {
-        switch (tpt) {
-        case 2: return launch_ransac_tile<2, 256, 6, false>(h, a, threads, st, probe_only);
-        case 6: return launch_ransac_tile<6, 256, 3, false>(h, a, threads, st, probe_only);
-        case 8: return launch_ransac_tile<8, 256, 2, false>(h, a, threads, st, probe_only);
-        default: return threads > 256 ? launch_ransac_tile<4, 512, 2, false>(h, a, threads, st, probe_only)
-                                      : launch_ransac_tile<4, 256, 4, false>(h, a, threads, st, probe_only);
-        }
-    }
     switch (tpt) {
-    case 2: return launch_ransac_tile<2, 256, 6, true>(h, a, threads, st, probe_only);
-    case 6: return launch_ransac_tile<6, 256, 4, true>(h, a, threads, st, probe_only);
-    case 8: return launch_ransac_tile<8, 256, 3, true>(h, a, threads, st, probe_only);
-    default: return threads > 512 ? launch_ransac_tile<4, 1024, 1, true>(h, a, threads, st, probe_only)
-                  : threads > 256 ? launch_ransac_tile<4, 512, 2, true>(h, a, threads, st, probe_only)
-                                  : launch_ransac_tile<4, 256, 4, true>(h, a, threads, st, probe_only);
+    case 2: return launch_ransac_tile<2, 256, 6>(h, a, threads, st, probe_only);
+    case 6: return launch_ransac_tile<6, 256, 4>(h, a, threads, st, probe_only);
+    case 8: return launch_ransac_tile<8, 256, 3>(h, a, threads, st, probe_only);
+    default: return threads > 512 ? launch_ransac_tile<4, 1024, 1>(h, a, threads, st, probe_only)
+                  : threads > 256 ? launch_ransac_tile<4, 512, 2>(h, a, threads, st, probe_only)
+                                  : launch_ransac_tile<4, 256, 4>(h, a, threads, st, probe_only);
     }
 }
 

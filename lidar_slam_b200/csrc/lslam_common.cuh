@@ -22,7 +22,7 @@ struct Handle {
     int smem_sm = 0;
     int64_t launches = 0;
     int opt_tpt = 0, opt_slots = 0, opt_threads = 0;
-    int opt_kernel = 0, opt_scorers = 0, opt_posts = 0, opt_ring = 0, opt_screen = 0;
+    int opt_kernel = 0, opt_scorers = 0, opt_posts = 0, opt_ring = 0;
     int opt_aug_pzx = 1;               // ukf_aug.pzx: 1 paired cross-covariance product (default), 0 literal
     bool aug_attr_set[10] = {};
     double *express_tab_d = nullptr;   // sin/cos tables of the packet decoder (csrc/express.cuh)

@@ -6,19 +6,16 @@
 // Round-2 redesign of ransac.cuh for the shape where per-chunk overhead, not the scoring loop, was the loss
 // (profiles/r03a_ransac_c2_ncu_summary.txt: seven block barriers, hot loop only 59.5 % of the instructions):
 //
-//   * hot loop = 2 DFMA + FADD + SHF + FMNMX/2 per point-hypothesis (round 1: 3 DFMA + DADD + SHF + FMNMX/2;
-//     tools/probe/mix_probe4.cu: 9.7 against 13.3 issue cycles per PHE-warp):
-//       - the inlier test |s| < thr runs on the HIGH WORDS of |s| and thr as one fp32 subtraction (the high word of a
-//         positive double is order-preserving as a float); a trial with a point whose high word is within one unit of
-//         thr's is re-scored literally (tile_flag_limit) - the re-check band is 2^-20 relative to thr instead of
-//         2^-36 relative to the chunk scale, still far below the sensor noise;
-//       - the fast residual sum (only used to rank trials tied on the count, inside a rigorous error bound) is NOT
-//         accumulated per point: sum_k s_k^2 is a quadratic form in the line coefficients whose matrix is the
-//         chunk's second-moment matrix about one of its own points (tile_moment_sum, bound in tile_moment_err);
-//   * F32 instantiation (default): the signed distance itself is evaluated in fp32 on the chunk's points centred on its
-//     middle point (2 FFMA + FADD + SHF + FMNMX/2; 6.4 against 9.7 cycles).  |s_f - s| <= 7 u R (u = 2^-24, R = the
-//     chunk's radius about that point; derivation below at tile_screen32), so a trial whose closest approach to the
-//     threshold is inside delta + u thr is flagged and re-scored literally; every output stays bit-exact;
+//   * hot loop = 2 FFMA + FADD + 1 SHF per point-hypothesis, all fp32 (round 1: 3 DFMA + DADD + SHF + FMNMX/2): the
+//     signed distance is evaluated in fp32 on the chunk's points centred on its middle point.  |s_f - s| <= 7 u R
+//     (u = 2^-24, R = the chunk's radius about that point; derivation below at tile_screen32), so a point with
+//     | |s_f| - thr_f | inside delta + u thr cannot be decided in fp32: its trial is flagged and re-scored in fp64; every
+//     output stays bit-exact.  Line and threshold are scaled by a power of two such that "outside that band" is one
+//     exponent bit of the difference: a funnel shift by TWO collects the inlier (sign) and the far-from-threshold bit
+//     of each point - no running minimum of the distance to the threshold;
+//   * the fast residual sum (only used to rank trials tied on the count, inside a rigorous error bound) is NOT
+//     accumulated per point: sum_k s_k^2 is a quadratic form in the line coefficients whose matrix is the
+//     chunk's second-moment matrix about one of its own points (tile_moment_sum, bound in tile_moment_err);
 //   * every trial's inlier bits are kept in shared memory (one STS per 32 points), so the winner's mask is read,
 //     not rebuilt;
 //   * one work item (TPT trials of one chunk) per thread, per-trial results stay in registers; the chunk-wide
@@ -28,7 +25,6 @@
 //   * three block barriers per tile (stage+moments | score | candidates | decide+refit+stores by lane groups).
 #pragma once
 #include "ransac.cuh"
-#include <type_traits>
 
 namespace lslam {
 
@@ -45,7 +41,7 @@ struct TileSlot {
     double alpha, beta;                // bound on |sum r^2 - sum s^2| = alpha + beta * sum s^2 (ssum_bound_coeffs)
     double A, nn;                      // Sxx + Syy and n as a double
     double kb;                         // (1 + beta) x the factor of tile_moment_err: the moment form's own error inside the bound
-    float bandf, pad_f;                // fp32 screening: | |s_f| - thr_f | below this -> literal re-score
+    float bandf, kscale;               // fp32 screening: band of | |s_f| - thr_f | that needs a re-score; 2 / band' (tile_screen32)
     int off, n, valid, c;
     int scale_hi;                      // high word of the largest |coordinate| of the slot
     int force_lit;                     // every trial is scored literally (threshold / scale outside the fast path's range)
@@ -73,28 +69,28 @@ struct TileSmem {
     size_t ptsf_off, mw_off;   // byte offsets inside a region: points | fp32 copies,  keys | trial masks
 };
 
-__host__ __device__ inline size_t tile_region_bytes(int G, int chunk, int ipc, int tpt, int W, bool f32)
+__host__ __device__ inline size_t tile_region_bytes(int G, int chunk, int ipc, int tpt, int W)
 {
     size_t pts = (size_t)G * chunk * 16;
-    if (f32) pts += (size_t)G * ((chunk + 1) & ~1) * 8;
+    pts += (size_t)G * ((chunk + 1) & ~1) * 8;
     const size_t scr = (size_t)G * tpt * ipc * 8 + (size_t)G * W * tpt * ipc * 4;
     return align16(pts > scr ? pts : scr);
 }
 
-__host__ __device__ inline size_t tile_smem_bytes(int G, int chunk, int ipc, int tpt, int W, int nwarps, bool f32)
+__host__ __device__ inline size_t tile_smem_bytes(int G, int chunk, int ipc, int tpt, int W, int nwarps)
 {
-    size_t b = 2 * tile_region_bytes(G, chunk, ipc, tpt, W, f32);
+    size_t b = 2 * tile_region_bytes(G, chunk, ipc, tpt, W);
     b += align16((size_t)G * W * 4);
     b += align16((size_t)nwarps * W * 4);
     b += 2 * align16((size_t)G * sizeof(TileSlot));
     return b;
 }
 
-__device__ __forceinline__ TileSmem tile_carve(unsigned char *raw, int G, int chunk, int ipc, int tpt, int W, int nwarps, bool f32)
+__device__ __forceinline__ TileSmem tile_carve(unsigned char *raw, int G, int chunk, int ipc, int tpt, int W, int nwarps)
 {
     TileSmem s;
     unsigned char *p = raw;
-    const size_t rb = tile_region_bytes(G, chunk, ipc, tpt, W, f32);
+    const size_t rb = tile_region_bytes(G, chunk, ipc, tpt, W);
     s.region0 = p; s.rbytes = rb; p += 2 * rb;
     s.ptsf_off = (size_t)G * chunk * 16;
     s.mw_off = (size_t)G * tpt * ipc * 8;
@@ -102,24 +98,6 @@ __device__ __forceinline__ TileSmem tile_carve(unsigned char *raw, int G, int ch
     s.wtmp = reinterpret_cast<uint32_t *>(p);  p += align16((size_t)nwarps * W * 4);
     s.slot0 = p; s.sbytes = align16((size_t)G * sizeof(TileSlot));
     return s;
-}
-
-// ---- inlier test on high words -------------------------------------------------------------------------------
-// hs = high word of s reinterpreted as a float, th = high word of thr as a float; f = |hs| - th (one FADD, exact for
-// neighbouring floats).  sign(f) set  <=>  hi(|s|) < hi(thr)  =>  |s| < thr.  If the high words differ by two units or
-// more, |s| and thr differ by more than 2^(e_thr - 21), and tile_fast_ok() makes sure that exceeds the bound
-// 2^(e2 - 36) on | |s| - r_literal | (lslam_core.cuh): the fast decision is the literal one.  Otherwise
-// (|f| < tile_flag_limit) the trial is flagged and re-scored with the literal formula.
-__device__ __forceinline__ float tile_flag_limit(float th)
-{
-    const float up = __int_as_float(__float_as_int(th) + 1);
-    return 1.5f * (up - th);           // covers a difference of one unit on either side, also across a binade
-}
-// the fast path needs: thr a normal positive double in a sane range, and the chunk scale 2^e2 at most 2^15 thr
-__device__ __forceinline__ bool tile_fast_ok(double thr, int scale_hi)
-{
-    const int et = (__double2hiint(thr) >> 20) & 0x7ff, es = (scale_hi >> 20) & 0x7ff;
-    return thr > 0.0 && et >= 1023 - 400 && et <= 1023 + 400 && (es + 1) - et <= 15;
 }
 
 // ---- fp32 screening ---------------------------------------------------------------------------------------------
@@ -135,7 +113,11 @@ __device__ __forceinline__ bool tile_fast_ok(double thr, int scale_hi)
 // The fp64 side (the Newton-refined normal, cp, and the literal residual itself, whose origin fl((p_i + p_j) / 2) is rounded at
 // the chunk's coordinate scale S) adds at most ~2^-51 S; the slack between delta and 7 u R is 2^-26.9 R, so the screening is
 // only used while S <= 2^22 R (a cluster of points 4 million radii away from the origin is scored literally).
-struct TileScreen32 { float bandf; bool force_literal; };
+// The tile kernel does not compare |f| with bandf point by point: it scales the line and the threshold by kscale = 2 / band',
+// band' = the power of two >= bandf, so that the scaled f = kscale (|s_f| - thr_f) - bit for bit the unscaled one times a power
+// of two - has |f| >= band' exactly when its exponent bit 30 is set.  One funnel shift by TWO then takes both the sign (inlier)
+// and that bit (far from the threshold) of every point.  band' <= 1 is required (kscale >= 2: scaling up cannot underflow).
+struct TileScreen32 { float bandf; float kscale; bool force_literal; };
 __device__ __forceinline__ float tile_sqrt_up(double r2)
 {
 #ifndef LSLAM_EMU
@@ -155,6 +137,13 @@ __device__ __forceinline__ TileScreen32 tile_screen32(double R, double thr, doub
     // band is not small against, thr <= 0 or NaN, R not finite, a radius tiny against the coordinates
     b.force_literal = !(R >= 0x1p-40 && R <= 0x1p40 && thr >= 0x1p-40 && thr <= 0x1p40 && 4.0 * band <= thr && S <= 0x1p22 * R);
     b.bandf = b.force_literal ? 0.0f : __double2float_ru(band);
+    b.kscale = 0.0f;
+    if (!b.force_literal) {
+        const int bits = __float_as_int(b.bandf);                                  // positive and normal here
+        const int e = ((bits >> 23) & 0xff) + ((bits & 0x7fffff) ? 1 : 0);          // biased exponent of band'
+        if (e > 127) b.force_literal = true;                                        // band' > 1: a chunk kilometres wide
+        else b.kscale = __int_as_float((254 - e + 1) << 23);                        // 2 / band' = 2^(1 - (e - 127))
+    }
     return b;
 }
 
@@ -246,7 +235,7 @@ __device__ __forceinline__ void warp_literal_score_strided(const double2 *P, int
 }
 
 // ================= stage + moments of one tile: LG lanes per slot, warps [w0, w0 + nw) ====================
-template <int TPT, bool F32>
+template <int TPT>
 __device__ __forceinline__ void tile_stage(const RansacArgs &a, int tile, int par, int w0, int nw)
 {
     LSLAM_SMEM_DECL;                                              // the CTA's dynamic shared memory, known to be shared memory here
@@ -255,7 +244,7 @@ __device__ __forceinline__ void tile_stage(const RansacArgs &a, int tile, int pa
     const int G = a.G, chunk = a.chunk, W = a.W, ipc = a.ipc;
     const int chunk_pad = (chunk + 1) & ~1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
-    const TileSmem sm = tile_carve(smem_raw, G, chunk, ipc, TPT, W, nwarps, F32);
+    const TileSmem sm = tile_carve(smem_raw, G, chunk, ipc, TPT, W, nwarps);
     (void)chunk_pad; (void)tid; (void)nwarps;
 
     const long long slot0 = (long long)tile * G;
@@ -311,10 +300,8 @@ __device__ __forceinline__ void tile_stage(const RansacArgs &a, int tile, int pa
             const double qx = p.x - cc.x, qy = p.y - cc.y;
             sx += qx; sy += qy;
             sxx = fma(qx, qx, sxx); sxy = fma(qx, qy, sxy); syy = fma(qy, qy, syy);
-            if constexpr (F32) {
-                dstf[k] = make_float2((float)qx, (float)qy);
-                r2 = fmax(r2, fma(qx, qx, qy * qy));
-            }
+            dstf[k] = make_float2((float)qx, (float)qy);
+            r2 = fmax(r2, fma(qx, qx, qy * qy));
         }
 #pragma unroll
         for (int o = LG / 2; o >= 1; o >>= 1) { const int v = __shfl_xor_sync(LSLAM_FULL_MASK, mh, o); mh = mh > v ? mh : v; }
@@ -326,7 +313,7 @@ __device__ __forceinline__ void tile_stage(const RansacArgs &a, int tile, int pa
             sxx += __shfl_xor_sync(LSLAM_FULL_MASK, sxx, o);
             sxy += __shfl_xor_sync(LSLAM_FULL_MASK, sxy, o);
             syy += __shfl_xor_sync(LSLAM_FULL_MASK, syy, o);
-            if constexpr (F32) r2 = fmax(r2, __shfl_xor_sync(LSLAM_FULL_MASK, r2, o));
+            r2 = fmax(r2, __shfl_xor_sync(LSLAM_FULL_MASK, r2, o));
         }
         if (act && r == 0) {
             TileSlot *st = sm.slot(par) + q;
@@ -341,18 +328,11 @@ __device__ __forceinline__ void tile_stage(const RansacArgs &a, int tile, int pa
             st->kb = (1.0 + sbq.beta) * tile_moment_err_factor((double)n);
             st->off = off; st->n = n; st->valid = valid ? 1 : 0; st->c = c;
             st->scale_hi = mh;
-            bool force = cb.force_literal;
-            st->bandf = 0.0f; st->pad_f = 0.0f;
-            if constexpr (F32) {
-                // an upper bound of the radius is enough: fp32 square root rounded up (overflow -> inf, underflow -> 0:
-                // both outside the screening range, the slot is then scored literally)
-                const TileScreen32 sc = tile_screen32((double)tile_sqrt_up(r2), a.thr, cb.eabs * 0x1p36);
-                st->bandf = sc.bandf;
-                force = force || sc.force_literal;
-            } else {
-                force = force || !tile_fast_ok(a.thr, mh);
-            }
-            st->force_lit = force ? 1 : 0;
+            // an upper bound of the radius is enough: fp32 square root rounded up (overflow -> inf, underflow -> 0:
+            // both outside the screening range, the slot is then scored literally)
+            const TileScreen32 sc = tile_screen32((double)tile_sqrt_up(r2), a.thr, cb.eabs * 0x1p36);
+            st->bandf = sc.bandf; st->kscale = sc.kscale;
+            st->force_lit = (cb.force_literal || sc.force_literal) ? 1 : 0;
             st->mx = 0; st->ncand = 0; st->band_hi = cb.band_hi;
             st->status = !valid ? 0x7fffffff : (cb.bad ? kStatusNonFinite : 0);   // 0x7fffffff: unused slot
             st->best_t = -1; st->best_i = -1; st->best_j = -1;
@@ -363,7 +343,7 @@ __device__ __forceinline__ void tile_stage(const RansacArgs &a, int tile, int pa
 
 // ================= decide (only where the literal formula is needed) + refit + stores of one tile: LG lanes per
 // slot, warps [0, nw).  Reads the tile's points, its slots and the winner masks - not its scratch region. ======
-template <int TPT, bool F32>
+template <int TPT>
 __device__ __forceinline__ void tile_refit(const RansacArgs &a, int tile, int par, int nw)
 {
     LSLAM_SMEM_DECL;
@@ -372,7 +352,7 @@ __device__ __forceinline__ void tile_refit(const RansacArgs &a, int tile, int pa
     const int G = a.G, chunk = a.chunk, W = a.W, ipc = a.ipc;
     const int chunk_pad = (chunk + 1) & ~1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
-    const TileSmem sm = tile_carve(smem_raw, G, chunk, ipc, TPT, W, nwarps, F32);
+    const TileSmem sm = tile_carve(smem_raw, G, chunk, ipc, TPT, W, nwarps);
     (void)chunk_pad; (void)tid; (void)nwarps;
 
     const long long slot0 = (long long)tile * G;
@@ -514,7 +494,7 @@ __device__ __forceinline__ void tile_refit(const RansacArgs &a, int tile, int pa
 
 // score + candidates of one tile: one work item (TPT trials of one chunk) per thread.  Inlined into the kernel, with the
 // kernel's own parameter (constant-bank operands).
-template <int TPT, bool F32>
+template <int TPT>
 __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int par)
 {
     LSLAM_SMEM_DECL;
@@ -522,7 +502,7 @@ __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int pa
     const int chunk_pad = (chunk + 1) & ~1;
     const int tid = threadIdx.x;
     const int lane = tid & 31, nwarps = blockDim.x >> 5;
-    const TileSmem sm = tile_carve(smem_raw, G, chunk, ipc, TPT, W, nwarps, F32);
+    const TileSmem sm = tile_carve(smem_raw, G, chunk, ipc, TPT, W, nwarps);
     const long long slot0 = (long long)tile * G;
     const long long rem_slots = a.nslots - slot0;
     const int nsl = rem_slots < (long long)G ? (int)rem_slots : G;
@@ -548,11 +528,10 @@ __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int pa
     {
         const bool force_lit = st->force_lit != 0;
         const uint64_t scan = st->scan;
-        // the hot loop's line: fp64 (nx, ny, ng) on the staged points, or fp32 (nx, ny, cp) on the centred points
-        typedef typename std::conditional<F32, float, double>::type real;
-        real nx[TPT], ny[TPT], ng[TPT];
-        unsigned bits[TPT];
-        float mab[TPT];
+        // the hot loop's line in fp32 on the centred points, scaled by the slot's kscale (a power of two: tile_screen32)
+        float nx[TPT], ny[TPT], ng[TPT];
+        unsigned be[TPT], bo[TPT], far[TPT];                      // two bits per point: of the even / odd points of a word; AND of them
+        const float ks = st->kscale;
         unsigned flagl = 0;                                       // bit k: trial t0 + k must be scored literally
         const double nn = st->nn, A = st->A, sb_alpha = st->alpha, sb_beta = st->beta, kb = st->kb, c0x = st->c0x, c0y = st->c0y;
 #pragma unroll
@@ -562,24 +541,16 @@ __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int pa
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 nx[k + h] = 0; ny[k + h] = 0; ng[k + h] = 0;
-                bits[k + h] = 0u; cnt[k + h] = 0; mab[k + h] = __int_as_float(0x7f800000);
+                be[k + h] = 0u; bo[k + h] = 0u; cnt[k + h] = 0; far[k + h] = 0xffffffffu;
                 if (!skip && t0 + k + h < T) {
                     live |= 1u << (k + h);
                     int i, j;
                     if (a.pairs != nullptr) explicit_pair(a, slot0 + q, (uint32_t)(t0 + k + h), (uint32_t)n, i, j);
                     else pair_from_words(h ? ph.r[2] : ph.r[0], h ? ph.r[3] : ph.r[1], (uint32_t)n, i, j);
-                    double fnx, fny, cp;
-                    bool degen;
-                    if constexpr (F32) {
-                        const TileLine f = tile_line(P[i], P[j], c0x, c0y);
-                        fnx = f.nx; fny = f.ny; cp = f.cp; degen = f.degenerate;
-                        nx[k + h] = (float)fnx; ny[k + h] = (float)fny; ng[k + h] = (float)cp;
-                    } else {
-                        const FastLine f = fast_pair_model(P[i], P[j]);
-                        fnx = f.nx; fny = f.ny; degen = f.degenerate;
-                        cp = fma(f.nx, c0x, fma(f.ny, c0y, f.negc));
-                        nx[k + h] = f.nx; ny[k + h] = f.ny; ng[k + h] = f.negc;
-                    }
+                    const TileLine f = tile_line(P[i], P[j], c0x, c0y);
+                    const double fnx = f.nx, fny = f.ny, cp = f.cp;
+                    const bool degen = f.degenerate;
+                    nx[k + h] = (float)fnx * ks; ny[k + h] = (float)fny * ks; ng[k + h] = (float)cp * ks;   // exact scalings
                     // residual sum from the moments with its error bound -> the two keys the tie-break needs
                     // E = beta (M+ + e2) + alpha + e2 with e2 = tile_moment_err(cp): the per-slot factors are folded (kb)
                     const double M = tile_moment_sum(fnx, fny, cp, nn, st);
@@ -594,11 +565,15 @@ __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int pa
             }
         }
         const int n_eff = (skip || force_lit) ? 0 : n;
-        int k = 0, w = 0;
-        float flim;
-        if constexpr (F32) {
-            const float thf = (float)a.thr;
-            flim = st->bandf;
+        {
+            // f = ks (|s_f| - thr_f), bit for bit (ks is a power of two).  Its sign bit = inlier; its exponent bit 30 is set
+            // exactly when |f| >= 2, i.e. when the unscaled | |s_f| - thr_f | >= band' >= bandf - the point is far enough
+            // from the threshold for the fp32 decision to be the literal one.  A funnel shift by two takes both bits; the
+            // even and the odd points of a 32-point word go to two registers, so that the inlier bits of the first (odd bit
+            // positions) and of the second shifted down by one (even positions) merge into the word of all 32 with ONE
+            // LOP3, bit 31 - j = point j.  (The loop is bound by issue cycles: the running minimum of |f| this replaces
+            // was 18 % of them - tools/probe/mix_probe5.cu.)
+            const float thf = (float)a.thr * ks;
             const float2 *Pf = ptsf + (size_t)q * chunk_pad;
             const float4 *Pf4 = reinterpret_cast<const float4 *>(Pf);     // two points per LDS.128 (chunk_pad is even)
 #define LSLAM_TILE_STEP2(XA, YA, XB, YB)                                                          \
@@ -606,88 +581,50 @@ __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int pa
         _Pragma("unroll") for (int k_ = 0; k_ < TPT; ++k_) {                                      \
             const float fa_ = fabsf(fmaf((YA), ny[k_], fmaf((XA), nx[k_], ng[k_]))) - thf;        \
             const float fb_ = fabsf(fmaf((YB), ny[k_], fmaf((XB), nx[k_], ng[k_]))) - thf;        \
-            bits[k_] = __funnelshift_l(__float_as_uint(fa_), bits[k_], 1);                        \
-            bits[k_] = __funnelshift_l(__float_as_uint(fb_), bits[k_], 1);                        \
-            mab[k_] = fminf(mab[k_], fminf(fabsf(fa_), fabsf(fb_)));                              \
+            be[k_] = __funnelshift_l(__float_as_uint(fa_), be[k_], 2);                            \
+            bo[k_] = __funnelshift_l(__float_as_uint(fb_), bo[k_], 2);                            \
         }                                                                                         \
     }
+            int k = 0, w = 0;
             for (; k + 32 <= n_eff; k += 32, ++w) {
 #pragma unroll
                 for (int kk = 0; kk < 32; kk += 2) { const float4 pp = Pf4[(k + kk) >> 1]; LSLAM_TILE_STEP2(pp.x, pp.y, pp.z, pp.w); }
 #pragma unroll
                 for (int k_ = 0; k_ < TPT; ++k_) {
-                    const unsigned m = bits[k_];                      // bit 31 - j = point 32 w + j (reversed: see below)
+                    const unsigned m = (be[k_] & 0xaaaaaaaau) | ((bo[k_] >> 1) & 0x55555555u);   // bit 31 - j = point 32 w + j
+                    far[k_] &= be[k_] & bo[k_];
                     cnt[k_] += __popc(m);
                     mw[row0 + (w * TPT + k_) * ipc] = m;
                 }
             }
             const int rem = n_eff - k;
             if (rem > 0) {
-                // the tail in pairs; an odd last point is paired with itself (its bit is shifted in twice, one shift is undone)
+                // the tail in pairs; an odd last point is paired with itself (its copy is masked out of the word)
                 for (int kk = 0; kk < rem; kk += 2) {
                     float4 pp;
                     if (kk + 1 < rem) pp = Pf4[(k + kk) >> 1];
                     else { const float2 p1 = Pf[k + kk]; pp = make_float4(p1.x, p1.y, p1.x, p1.y); }
                     LSLAM_TILE_STEP2(pp.x, pp.y, pp.z, pp.w);
                 }
-                const int sh = rem & 1;
+                const int sh = 32 - ((rem + 1) & ~1);                              // 32 - 2 x pairs: 0 .. 30
+                const unsigned keep = 0xffffffffu << (32 - rem), low = ~(0xffffffffu << sh);
 #pragma unroll
                 for (int k_ = 0; k_ < TPT; ++k_) {
-                    const unsigned m = (bits[k_] >> sh) << (32 - rem);
-                    cnt[k_] += __popc(m);
-                    mw[row0 + (w * TPT + k_) * ipc] = m;
-                }
-            }
-#undef LSLAM_TILE_STEP2
-        } else {
-            const float thf = __int_as_float(__double2hiint(a.thr));
-            flim = tile_flag_limit(thf);
-#define LSLAM_TILE_STEP2(PA, PB)                                                                  \
-    {                                                                                             \
-        const double2 pa_ = (PA), pb_ = (PB);                                                     \
-        _Pragma("unroll") for (int k_ = 0; k_ < TPT; ++k_) {                                      \
-            const double sa_ = fma(pa_.y, ny[k_], fma(pa_.x, nx[k_], ng[k_]));                    \
-            const double sb_ = fma(pb_.y, ny[k_], fma(pb_.x, nx[k_], ng[k_]));                    \
-            const float fa_ = fabsf(__int_as_float(__double2hiint(sa_))) - thf;                   \
-            const float fb_ = fabsf(__int_as_float(__double2hiint(sb_))) - thf;                   \
-            bits[k_] = __funnelshift_l(__float_as_uint(fa_), bits[k_], 1);                        \
-            bits[k_] = __funnelshift_l(__float_as_uint(fb_), bits[k_], 1);                        \
-            mab[k_] = fminf(mab[k_], fminf(fabsf(fa_), fabsf(fb_)));                              \
-        }                                                                                         \
-    }
-            for (; k + 32 <= n_eff; k += 32, ++w) {
-#pragma unroll 4
-                for (int kk = 0; kk < 32; kk += 2) LSLAM_TILE_STEP2(P[k + kk], P[k + kk + 1]);
-#pragma unroll
-                for (int k_ = 0; k_ < TPT; ++k_) {
-                    const unsigned m = bits[k_];                      // bit 31 - j = point 32 w + j (reversed: see below)
-                    cnt[k_] += __popc(m);
-                    mw[row0 + (w * TPT + k_) * ipc] = m;
-                }
-            }
-            const int rem = n_eff - k;
-            if (rem > 0) {
-                for (int kk = 0; kk < rem; kk += 2) {
-                    const int kb = kk + 1 < rem ? kk + 1 : kk;        // an odd last point is paired with itself
-                    LSLAM_TILE_STEP2(P[k + kk], P[k + kb]);
-                }
-                const int sh = rem & 1;
-#pragma unroll
-                for (int k_ = 0; k_ < TPT; ++k_) {
-                    const unsigned m = (bits[k_] >> sh) << (32 - rem);
+                    const unsigned e_ = be[k_] << sh, o_ = bo[k_] << sh;
+                    const unsigned m = ((e_ & 0xaaaaaaaau) | ((o_ >> 1) & 0x55555555u)) & keep;
+                    far[k_] &= (e_ & o_) | low;
                     cnt[k_] += __popc(m);
                     mw[row0 + (w * TPT + k_) * ipc] = m;
                 }
             }
 #undef LSLAM_TILE_STEP2
         }
-        // a point too close to the threshold for the fast distance to decide: re-scored with the fp64 fast line (F32), or
-        // literally (the fp64 high-word test has no finer fast form)
+        // a point too close to the threshold for the fp32 distance to decide (some "far" bit clear): the trial is re-scored
+        // with the fp64 fast line
         unsigned flagb = 0;
 #pragma unroll
         for (int k_ = 0; k_ < TPT; ++k_)
-            if (mab[k_] < flim) flagb |= 1u << k_;
-        if constexpr (!F32) { flagl |= flagb; flagb = 0; }
+            if ((far[k_] & 0x55555555u) != 0x55555555u) flagb |= 1u << k_;
         flagl &= live;
         flagb &= live & ~flagl;
 
@@ -788,7 +725,7 @@ __device__ __forceinline__ void tile_score(const RansacArgs &a, int tile, int pa
     __syncthreads();
 }
 
-template <int TPT, int MAXT, int MINB, bool F32>
+template <int TPT, int MAXT, int MINB>
 __global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArgs a)
 {
     static_assert(TPT % 2 == 0, "a Philox block serves two trials");
@@ -796,11 +733,11 @@ __global__ void __launch_bounds__(MAXT, MINB) ransac_tile_kernel(const RansacArg
     // its next tile while it refits the current one measured SLOWER on B200: 5.1 against 4.3 ms on C2 - the CTAs of an SM
     // then run in lockstep and idle together)
     const int tile = blockIdx.x, nwarps = blockDim.x >> 5;
-    tile_stage<TPT, F32>(a, tile, 0, 0, nwarps);
+    tile_stage<TPT>(a, tile, 0, 0, nwarps);
     __syncthreads();
-    tile_score<TPT, F32>(a, tile, 0);                             // score | barrier | candidates
+    tile_score<TPT>(a, tile, 0);                             // score | barrier | candidates
     __syncthreads();
-    tile_refit<TPT, F32>(a, tile, 0, nwarps);
+    tile_refit<TPT>(a, tile, 0, nwarps);
 }
 
 } // namespace lslam

@@ -9,19 +9,17 @@ from lidar_slam_b200 import synth
 from tests.parity_util import assert_ransac_equal
 
 
-@pytest.fixture(params=[(2, True, 0), (1, True, 0), (1, False, 0), (3, True, 0), (3, False, 0), (3, True, 1), (3, False, 1)],
-                ids=["ws", "phased", "phased-nossum", "tile", "tile-nossum", "tile-f64", "tile-f64-nossum"], autouse=True)
+@pytest.fixture(params=[(2, True), (1, True), (1, False), (3, True), (3, False)],
+                ids=["ws", "phased", "phased-nossum", "tile", "tile-nossum"], autouse=True)
 def ransac_kernel(request, emu):
     """Every test runs on both RANSAC kernels: 2 = warp-specialised persistent (csrc/ransac_ws.cuh),
     1 = phase-structured (csrc/ransac.cuh) - the latter also without the optional residual-sum output,
     which switches the decide stage of unambiguous chunks to the fast model."""
     h = emu.emu_handle()
     h.set_option("ransac.kernel", request.param[0])
-    h.set_option("ransac.screen", request.param[2])
     emu.WANT_SSUM = request.param[1]
     yield request.param[0]
     h.set_option("ransac.kernel", 0)
-    h.set_option("ransac.screen", 0)
     emu.WANT_SSUM = True
 
 

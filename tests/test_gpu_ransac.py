@@ -16,18 +16,16 @@ pytestmark = pytest.mark.gpu
 WANT_SSUM = True
 
 
-@pytest.fixture(params=[(2, True, 0), (1, True, 0), (1, False, 0), (3, True, 0), (3, False, 0), (3, True, 1), (3, False, 1)],
-                ids=["ws", "phased", "phased-nossum", "tile", "tile-nossum", "tile-f64", "tile-f64-nossum"], autouse=True)
+@pytest.fixture(params=[(2, True), (1, True), (1, False), (3, True), (3, False)],
+                ids=["ws", "phased", "phased-nossum", "tile", "tile-nossum"], autouse=True)
 def ransac_kernel(request, gpu_engine):
     """Both RANSAC kernels: 2 = warp-specialised persistent, 1 = phase-structured (also without the
     optional residual-sum output: the fast decide path)."""
     global WANT_SSUM
     gpu_engine.set_option("ransac.kernel", request.param[0])
-    gpu_engine.set_option("ransac.screen", request.param[2])
     WANT_SSUM = request.param[1]
     yield request.param[0]
     gpu_engine.set_option("ransac.kernel", 0)
-    gpu_engine.set_option("ransac.screen", 0)
     WANT_SSUM = True
 
 

@@ -58,8 +58,8 @@ def test_numpy_and_c_restatements_agree_on_replayed_pairs(cport, legacy):
     assert not np.array_equal(got["win_pair"], cport.ransac_lines(xy)["win_pair"])
 
 
-@pytest.mark.parametrize("kernel,screen", [(1, 0), (3, 0), (3, 1), (0, 0)])
-def test_emulated_kernels_replay_pairs(emu, cport, kernel, screen):
+@pytest.mark.parametrize("kernel", [1, 3, 0])
+def test_emulated_kernels_replay_pairs(emu, cport, kernel):
     xy = synth.random_room_scans(7, seed=22)
     npts = np.array([360, 301, 360, 2, 259, 360, 360], np.int32)
     pairs, _ = batch_pairs(xy, npts, 100, 100, 5)
@@ -68,13 +68,11 @@ def test_emulated_kernels_replay_pairs(emu, cport, kernel, screen):
     h = emu.emu_handle()
     try:
         h.set_option("ransac.kernel", kernel)
-        h.set_option("ransac.screen", screen)
         for ssum in (True, False):
             got = emu.emu_ransac_lines(xy, npts=npts, pairs=pairs, want_ssum=ssum)
-            assert_ransac_equal(want, got, "kernel %d screen %d" % (kernel, screen))
+            assert_ransac_equal(want, got, "kernel %d" % kernel)
     finally:
         h.set_option("ransac.kernel", 0)
-        h.set_option("ransac.screen", 0)
 
 
 def test_emulated_big_chunks_with_pairs_use_a_kernel_that_supports_them(emu, cport):
@@ -86,8 +84,8 @@ def test_emulated_big_chunks_with_pairs_use_a_kernel_that_supports_them(emu, cpo
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("kernel,screen", [(0, 0), (1, 0), (3, 0), (3, 1)])
-def test_gpu_replays_pairs(gpu_engine, cport, kernel, screen):
+@pytest.mark.parametrize("kernel", [0, 1, 3])
+def test_gpu_replays_pairs(gpu_engine, cport, kernel):
     import torch
     xy = synth.random_room_scans(300, seed=24)
     npts = np.full(300, 360, np.int32)
@@ -98,15 +96,13 @@ def test_gpu_replays_pairs(gpu_engine, cport, kernel, screen):
     eng = gpu_engine
     try:
         eng.set_option("ransac.kernel", kernel)
-        eng.set_option("ransac.screen", screen)
         dev = eng.device
         out = eng.ransac_lines(torch.from_numpy(xy).to(dev), npts=torch.from_numpy(npts).to(dev),
                                pairs=torch.from_numpy(pairs).to(dev))
         torch.cuda.synchronize()
-        assert_ransac_equal(want, {k: v.cpu().numpy() for k, v in out.items()}, "gpu kernel %d screen %d" % (kernel, screen))
+        assert_ransac_equal(want, {k: v.cpu().numpy() for k, v in out.items()}, "gpu kernel %d" % kernel)
     finally:
         eng.set_option("ransac.kernel", 0)
-        eng.set_option("ransac.screen", 0)
 
 
 # ---- upstream's own results, when someone with scikit-image has made the golden file ------------------------

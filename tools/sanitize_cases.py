@@ -24,13 +24,11 @@ def want(name):
     return not only or name in only
 
 
-def ransac(kernel, screen, xy, npts, **kw):
+def ransac(kernel, xy, npts, **kw):
     eng.set_option("ransac.kernel", kernel)
-    eng.set_option("ransac.screen", screen)
     r = eng.ransac_lines(torch.from_numpy(xy).to(dev), npts=None if npts is None else torch.from_numpy(npts).to(dev), **kw)
     torch.cuda.synchronize()
     eng.set_option("ransac.kernel", 0)
-    eng.set_option("ransac.screen", 0)
     return {k: v.cpu().numpy() for k, v in r.items()}
 
 
@@ -40,12 +38,12 @@ npts[3] = 301
 npts[7] = 2
 if want("ransac"):
     w = cport.ransac_lines(xy, npts=npts, seed=3)
-    for kernel, screen in ((1, 0), (2, 0), (3, 0), (3, 1)):
-        assert_ransac_equal(w, ransac(kernel, screen, xy, npts, seed=3), "kernel %d screen %d" % (kernel, screen))
+    for kernel in (1, 2, 3):
+        assert_ransac_equal(w, ransac(kernel, xy, npts, seed=3), "kernel %d" % kernel)
     big = synth.random_room_scans(2, beams=820, seed=2)
     w = cport.ransac_lines(big, chunk=410, trials=256, seed=1)
     for kernel in (1, 2, 3):
-        assert_ransac_equal(w, ransac(kernel, 0, big, None, chunk=410, trials=256, seed=1), "big kernel %d" % kernel)
+        assert_ransac_equal(w, ransac(kernel, big, None, chunk=410, trials=256, seed=1), "big kernel %d" % kernel)
     print("ransac ok", flush=True)
 
 if want("pipeline"):
