@@ -117,6 +117,48 @@ def test_threshold_edge_points_are_rechecked(emu, cport):
     assert c["literal_rescored"] > 0 and c["faults"] == 0
 
 
+def test_word_tails_of_every_length(emu, cport):
+    """The tile kernel's scoring loop packs two bits per point, the even and the odd points of a 32-point word in two registers:
+    chunk lengths that leave tails of 1 .. 31 points (odd and even, with and without full words before them)."""
+    xy = synth.random_room_scans(2, seed=31)
+    for chunk in (33, 34, 35, 47, 48, 62, 63, 64, 65, 95, 97):
+        want = cport.ransac_lines(xy, chunk=chunk, trials=48, seed=chunk)
+        got = emu.emu_ransac_lines(xy, chunk=chunk, trials=48, seed=chunk)
+        assert_ransac_equal(want, got, "chunk %d" % chunk)
+    npts = np.array([90, 77], np.int32)                    # ragged: a last chunk shorter than the others
+    want = cport.ransac_lines(xy, npts=npts, chunk=37, trials=48, seed=5)
+    assert_ransac_equal(want, emu.emu_ransac_lines(xy, npts=npts, chunk=37, trials=48, seed=5), "ragged chunk 37")
+    assert emu.emu_handle().ransac_counters()["faults"] == 0
+
+
+def test_screening_range_edges(emu, cport):
+    """fp32 screening (tile_screen32): the re-check band is scaled to a power of two; outside its range the slot is scored
+    literally.  Chunks kilometres wide (band' > 1), a cluster far from the origin (coordinates 2^22 radii away), thresholds
+    the band is not small against, and points inside the fp32 band but outside the fp64 one."""
+    rng = np.random.default_rng(7)
+    t = np.linspace(-1000, 1000, 100)
+    y = 0.05 * t + rng.normal(0, 8, 100)
+    near = np.zeros(100)
+    near[4::9] = 20.0 + 5e-4
+    near[5::9] = 20.0 - 5e-4
+    near[6::9] = 20.0 + 1.5e-3
+    near[7::9] = 20.0 - 1.5e-3
+    cases = {
+        "km-wide": (np.stack([t * 5000.0, y * 5000.0], -1), 20.0),
+        "10-km-wide": (np.stack([t * 2e4, y], -1), 20.0),
+        "far-from-origin": (np.stack([t * 0.1 + 1e9, y * 0.1 - 3e9], -1), 20.0),
+        "band-fp32-only": (np.stack([np.arange(100.0) * 16.0, near], -1), 20.0),
+        "small-threshold": (np.stack([t, y], -1), 1e-3),
+        "threshold-0.5": (np.stack([t, y * 0.05], -1), 0.5),
+        "large-threshold": (np.stack([t, y], -1), 5e3),
+    }
+    for name, (data, thr) in cases.items():
+        want = cport.ransac_lines(data[None], thr=thr, seed=9)
+        got = emu.emu_ransac_lines(data[None], thr=thr, seed=9)
+        assert_ransac_equal(want, got, name)
+    assert emu.emu_handle().ransac_counters()["faults"] == 0
+
+
 def test_status_codes(emu):
     bad = synth.random_room_scans(1, seed=1)
     bad[0, 150, 0] = np.nan

@@ -141,6 +141,44 @@ def test_degenerate_geometry(gpu_engine, cport):
     assert c["faults"] == 0 and c["literal_rescored"] > 0
 
 
+def test_word_tails_of_every_length(gpu_engine, cport):
+    """As tests/test_emu_ransac.py: chunk lengths that leave tails of 1 .. 31 points in the tile kernel's two-bit words."""
+    xy = synth.random_room_scans(64, seed=31)
+    for chunk in (33, 34, 35, 47, 48, 62, 63, 64, 65, 95, 97):
+        want = cport.ransac_lines(xy, chunk=chunk, trials=48, seed=chunk)
+        assert_ransac_equal(want, run_gpu(gpu_engine, xy, chunk=chunk, trials=48, seed=chunk), "chunk %d" % chunk)
+    npts = np.tile(np.array([90, 77, 360, 38], np.int32), 16)
+    want = cport.ransac_lines(xy, npts=npts, chunk=37, trials=48, seed=5)
+    assert_ransac_equal(want, run_gpu(gpu_engine, xy, npts=npts, chunk=37, trials=48, seed=5), "ragged chunk 37")
+    assert gpu_engine.ransac_counters()["faults"] == 0
+
+
+def test_screening_range_edges(gpu_engine, cport):
+    """As tests/test_emu_ransac.py: the fp32 screening's range (tile_screen32) - chunks kilometres wide, a cluster far from
+    the origin, thresholds the band is not small against, points inside the fp32 band but outside the fp64 one."""
+    rng = np.random.default_rng(7)
+    t = np.linspace(-1000, 1000, 100)
+    y = 0.05 * t + rng.normal(0, 8, 100)
+    near = np.zeros(100)
+    near[4::9] = 20.0 + 5e-4
+    near[5::9] = 20.0 - 5e-4
+    near[6::9] = 20.0 + 1.5e-3
+    near[7::9] = 20.0 - 1.5e-3
+    cases = {
+        "km-wide": (np.stack([t * 5000.0, y * 5000.0], -1), 20.0),
+        "10-km-wide": (np.stack([t * 2e4, y], -1), 20.0),
+        "far-from-origin": (np.stack([t * 0.1 + 1e9, y * 0.1 - 3e9], -1), 20.0),
+        "band-fp32-only": (np.stack([np.arange(100.0) * 16.0, near], -1), 20.0),
+        "small-threshold": (np.stack([t, y], -1), 1e-3),
+        "threshold-0.5": (np.stack([t, y * 0.05], -1), 0.5),
+        "large-threshold": (np.stack([t, y], -1), 5e3),
+    }
+    for name, (data, thr) in cases.items():
+        want = cport.ransac_lines(data[None], thr=thr, seed=9)
+        assert_ransac_equal(want, run_gpu(gpu_engine, data[None], thr=thr, seed=9), name)
+    assert gpu_engine.ransac_counters()["faults"] == 0
+
+
 def test_full_size_properties(gpu_engine):
     """At full size (262,144 device-generated scans) the oracle is too slow; check
     size-independent properties: determinism, batch-split invariance (scan_base), inlier count
