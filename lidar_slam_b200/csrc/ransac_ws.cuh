@@ -40,7 +40,7 @@ struct WsSlotInfo {                 // written by the loader warp
     // screening data of the tile kernel's arithmetic (ransac_tile.cuh): centre, moments of the centred points, bound of
     // | sum r^2 - M | = alpha + beta M (alpha includes the moment form's own error at the chunk's radius), fp32 band
     double c0x, c0y, Sx, Sy, Sxx, Sxy, Syy, nn, alpha, beta;
-    float bandf, pad_f;
+    float bandf, kscale;            // tile_screen32: the band, and 2 / (the power of two >= band) - the loop's scaling
 };
 
 struct WsRec {                      // post -> epilogue
@@ -99,10 +99,10 @@ __device__ __forceinline__ void ws_wait(Mbar *bar, unsigned parity)
 __device__ __forceinline__ uint32_t ws_pack(int cnt, float mab) { return ((uint32_t)__float_as_int(mab) & 0x7fff0000u) | (uint32_t)cnt; }
 
 // ---- scorer: one work item = TPT consecutive trials of one chunk --------------------------------
-// The tile kernel's arithmetic (ransac_tile.cuh): the signed distance in fp32 on the chunk's centred points (2 FFMA +
-// FADD + SHF per point-hypothesis, one FMNMX3 per two), a trial whose closest approach to the threshold is inside the
-// slot's band is handed to the post warps for a literal re-score (packed word 0); the fast residual sum comes from the
-// chunk's moments, once per trial.
+// The tile kernel's arithmetic (ransac_tile.cuh): the signed distance in fp32 on the chunk's centred points, line and
+// threshold scaled by the slot's kscale so that a funnel shift by two takes the inlier bit (sign) and the far-from-the-
+// threshold bit (exponent bit 30) of every point: 2 FFMA + FADD + SHF per point-hypothesis.  A trial with a point inside
+// the slot's band is re-scored literally; the fast residual sum comes from the chunk's moments, once per trial.
 // Called by ALL lanes of a scorer warp (has = the lane has a work item): flagged trials are re-scored literally by the
 // whole warp on the spot and marked exact (packed word 0x7f00....), so the post warps only see finished scores.
 constexpr uint32_t kWsExact = 0x7f000000u;
@@ -123,18 +123,18 @@ __device__ __forceinline__ void ws_score_item(const RansacArgs &a, int item, boo
     float nx[TPT], ny[TPT], ng[TPT];
     unsigned bits[TPT];
     int cnt[TPT];
-    float mab[TPT / 2];
+    unsigned far[TPT];                                            // AND of the scored words (the far bits matter)
     unsigned deg = 0;
+    const float ks = g->kscale;
 #pragma unroll
     for (int k = 0; k < TPT; k += 2) {
         const Philox4 ph = philox4x32_10((uint32_t)(t0 + k) >> 1, (uint32_t)g->c, (uint32_t)scan, (uint32_t)(scan >> 32),
                                          (uint32_t)a.seed, (uint32_t)(a.seed >> 32));
-        mab[k / 2] = __int_as_float(0x7f800000);
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const int t = t0 + k + h;
             nx[k + h] = 0.f; ny[k + h] = 0.f; ng[k + h] = 0.f;
-            bits[k + h] = 0u; cnt[k + h] = 0;
+            bits[k + h] = 0u; cnt[k + h] = 0; far[k + h] = 0xffffffffu;
             if (valid && t < T) {
                 int i, j;
                 pair_from_words(h ? ph.r[2] : ph.r[0], h ? ph.r[3] : ph.r[1], n, i, j);
@@ -145,38 +145,35 @@ __device__ __forceinline__ void ws_score_item(const RansacArgs &a, int item, boo
                 const double M = fma(cp, fma(g->nn, cp, 2.0 * fma(f.nx, g->Sx, f.ny * g->Sy)), fma(f.nx, a1, f.ny * a2));
                 ssf[q * T + t] = M;
                 if (f.degenerate || force_lit || !(fabs(M) <= 1.7976931348623157e308)) deg |= 1u << (k + h);
-                nx[k + h] = (float)f.nx; ny[k + h] = (float)f.ny; ng[k + h] = (float)cp;
+                nx[k + h] = (float)f.nx * ks; ny[k + h] = (float)f.ny * ks; ng[k + h] = (float)cp * ks;   // exact scalings
             }
         }
     }
-    const float thf = (float)a.thr, flim = g->bandf;
+    const float thf = (float)a.thr * ks;
     const float2 *Pf = ptsf + (size_t)q * ((a.chunk + 1) & ~1);
     const float4 *Pf4 = reinterpret_cast<const float4 *>(Pf);
+    // f = ks (|s_f| - thr_f): sign bit = inlier, exponent bit 30 set <=> the unscaled | |s_f| - thr_f | >= band' >= bandf
+    // (tile_screen32).  16 points per word: inlier bits in the odd positions, far bits in the even ones.
 #define LSLAM_WS_STEP2(XA, YA, XB, YB)                                                            \
     {                                                                                             \
-        _Pragma("unroll") for (int k_ = 0; k_ < TPT; k_ += 2) {                                   \
-            const float fa0_ = fabsf(fmaf((YA), ny[k_], fmaf((XA), nx[k_], ng[k_]))) - thf;       \
-            const float fb0_ = fabsf(fmaf((YB), ny[k_], fmaf((XB), nx[k_], ng[k_]))) - thf;       \
-            const float fa1_ = fabsf(fmaf((YA), ny[k_ + 1], fmaf((XA), nx[k_ + 1], ng[k_ + 1]))) - thf; \
-            const float fb1_ = fabsf(fmaf((YB), ny[k_ + 1], fmaf((XB), nx[k_ + 1], ng[k_ + 1]))) - thf; \
-            bits[k_] = __funnelshift_l(__float_as_uint(fa0_), bits[k_], 1);                       \
-            bits[k_] = __funnelshift_l(__float_as_uint(fb0_), bits[k_], 1);                       \
-            bits[k_ + 1] = __funnelshift_l(__float_as_uint(fa1_), bits[k_ + 1], 1);               \
-            bits[k_ + 1] = __funnelshift_l(__float_as_uint(fb1_), bits[k_ + 1], 1);               \
-            mab[k_ / 2] = fminf(fminf(mab[k_ / 2], fminf(fabsf(fa0_), fabsf(fb0_))), fminf(fabsf(fa1_), fabsf(fb1_))); \
+        _Pragma("unroll") for (int k_ = 0; k_ < TPT; ++k_) {                                      \
+            const float fa_ = fabsf(fmaf((YA), ny[k_], fmaf((XA), nx[k_], ng[k_]))) - thf;        \
+            const float fb_ = fabsf(fmaf((YB), ny[k_], fmaf((XB), nx[k_], ng[k_]))) - thf;        \
+            bits[k_] = __funnelshift_l(__float_as_uint(fa_), bits[k_], 2);                        \
+            bits[k_] = __funnelshift_l(__float_as_uint(fb_), bits[k_], 2);                        \
         }                                                                                         \
     }
     const int n_eff = (valid && !force_lit) ? (int)n : 0;
     int k = 0;
-    for (; k + 32 <= n_eff; k += 32) {
+    for (; k + 16 <= n_eff; k += 16) {
 #pragma unroll 4
-        for (int kk = 0; kk < 32; kk += 2) { const float4 pp = Pf4[(k + kk) >> 1]; LSLAM_WS_STEP2(pp.x, pp.y, pp.z, pp.w); }
+        for (int kk = 0; kk < 16; kk += 2) { const float4 pp = Pf4[(k + kk) >> 1]; LSLAM_WS_STEP2(pp.x, pp.y, pp.z, pp.w); }
 #pragma unroll
-        for (int k_ = 0; k_ < TPT; ++k_) cnt[k_] += __popc(bits[k_]);
+        for (int k_ = 0; k_ < TPT; ++k_) { cnt[k_] += __popc(bits[k_] & 0xaaaaaaaau); far[k_] &= bits[k_]; }
     }
     const int rem = n_eff - k;
     if (rem > 0) {
-        // the tail in pairs; an odd last point is paired with itself (its bit is shifted in twice, one shift is undone)
+        // the tail in pairs; an odd last point is paired with itself (shifted in twice, one shift is undone)
 #pragma unroll 2
         for (int kk = 0; kk < rem; kk += 2) {
             float4 pp;
@@ -184,9 +181,13 @@ __device__ __forceinline__ void ws_score_item(const RansacArgs &a, int item, boo
             else { const float2 p1 = Pf[k + kk]; pp = make_float4(p1.x, p1.y, p1.x, p1.y); }
             LSLAM_WS_STEP2(pp.x, pp.y, pp.z, pp.w);
         }
-        const int sh = rem & 1;
+        const unsigned keep = 0xffffffffu >> (32 - 2 * rem);                   // rem < 16
 #pragma unroll
-        for (int k_ = 0; k_ < TPT; ++k_) cnt[k_] += __popc((bits[k_] >> sh) << (32 - rem));
+        for (int k_ = 0; k_ < TPT; ++k_) {
+            const unsigned w_ = (bits[k_] >> (2 * (rem & 1))) & keep;
+            cnt[k_] += __popc(w_ & 0xaaaaaaaau);
+            far[k_] &= w_ | ~keep;
+        }
     }
 #undef LSLAM_WS_STEP2
     unsigned flagm = 0;
@@ -194,7 +195,7 @@ __device__ __forceinline__ void ws_score_item(const RansacArgs &a, int item, boo
     for (int k_ = 0; k_ < TPT; ++k_) {
         const int t = t0 + k_;
         if (valid && t < T) {
-            const bool flagged = ((deg >> k_) & 1u) || mab[k_ / 2] < flim;
+            const bool flagged = ((deg >> k_) & 1u) || (far[k_] & 0x55555555u) != 0x55555555u;
             if (flagged) flagm |= 1u << k_;
             cm[q * T + t] = ws_pack(cnt[k_], __int_as_float(0x7f800000));
         } else if (has && t < T) {
@@ -557,7 +558,7 @@ __global__ void __launch_bounds__(MAXT, 1) ransac_ws_kernel(const RansacArgs a)
                 g.valid = (n >= 2) && (n == a.chunk || n > 2);
                 g.scale_hi = 0; g.force_lit = 0;
                 g.c0x = 0.0; g.c0y = 0.0; g.Sx = 0.0; g.Sy = 0.0; g.Sxx = 0.0; g.Sxy = 0.0; g.Syy = 0.0;
-                g.nn = (double)n; g.alpha = 0.0; g.beta = 0.0; g.bandf = 0.0f; g.pad_f = 0.0f;
+                g.nn = (double)n; g.alpha = 0.0; g.beta = 0.0; g.bandf = 0.0f; g.kscale = 0.0f;
                 info[q] = g;
             }
             __syncwarp();
@@ -613,7 +614,7 @@ __global__ void __launch_bounds__(MAXT, 1) ransac_ws_kernel(const RansacArgs a)
                     g->scale_hi = mh;
                     g->force_lit = (cb.force_literal || scr.force_literal || !(e2 <= 1.7976931348623157e308)) ? 1 : 0;
                     g->c0x = cc.x; g->c0y = cc.y; g->Sx = sx; g->Sy = sy; g->Sxx = sxx; g->Sxy = sxy; g->Syy = syy;
-                    g->alpha = fma(1.0 + sb.beta, e2, sb.alpha); g->beta = sb.beta; g->bandf = scr.bandf;
+                    g->alpha = fma(1.0 + sb.beta, e2, sb.alpha); g->beta = sb.beta; g->bandf = scr.bandf; g->kscale = scr.kscale;
                 }
             }
             __syncwarp();
