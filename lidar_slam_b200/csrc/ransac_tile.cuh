@@ -206,7 +206,7 @@ __device__ __forceinline__ void warp_fast64_score_strided(const double2 *P, int 
         }
         const unsigned b = __ballot_sync(LSLAM_FULL_MASK, in);
         c += __popc(b);
-        if (lane == 0) mask_out[(k0 >> 5) * stride] = __brev(b);     // the per-trial words are kept bit-reversed (tile_score)
+        if (mask_out != nullptr && lane == 0) mask_out[(k0 >> 5) * stride] = __brev(b);   // the per-trial words are kept bit-reversed (tile_score)
     }
     cnt = c;
     near = __any_sync(LSLAM_FULL_MASK, nr);

@@ -202,7 +202,9 @@ __device__ __forceinline__ void ws_score_item(const RansacArgs &a, int item, boo
             cm[q * T + t] = ws_pack(0, 0.0f); ssf[q * T + t] = 0.0; pij[q * T + t] = 0u;
         }
     }
-    // flagged trials: literal score by the whole warp, on the spot
+    // flagged trials: scored again by the whole warp, on the spot - with the fp64 fast line first (its own re-check band is
+    // 2^-36 of the coordinate scale: the count is then the literal one and the moment-based sum stays), literally if a
+    // point is inside that band as well or the trial was marked for it at the set-up (degenerate pair, slot out of range)
     const ChunkBand cbq = chunk_band(g->scale_hi);
     if (cbq.bad) flagm = 0;                                       // non-finite chunk: the post warp reports it
     __syncwarp();                                                 // the pairs written above are read by the other lanes below
@@ -213,18 +215,28 @@ __device__ __forceinline__ void ws_score_item(const RansacArgs &a, int item, boo
         fm &= fm - 1;
         const int fq = __shfl_sync(LSLAM_FULL_MASK, q, src), ft0 = __shfl_sync(LSLAM_FULL_MASK, t0, src);
         unsigned fl = __shfl_sync(LSLAM_FULL_MASK, flagm, src);
+        const unsigned fdeg = __shfl_sync(LSLAM_FULL_MASK, deg, src);
+        const int fband = __shfl_sync(LSLAM_FULL_MASK, cbq.band_hi, src);
         const WsSlotInfo *fg = info + fq;
         const double2 *FP = pts + fg->off;
         while (fl) {
             const int kf = __ffs((int)fl) - 1;
             fl &= fl - 1;
             const int tt = ft0 + kf;
-            int cl;
-            double sl;
+            int cl = 0;
+            double sl = 0.0;
             const uint32_t pw_ = pij[fq * T + tt];
-            warp_literal_score(FP, fg->n, lit_pair_model(FP[pw_ & 0xffffu], FP[pw_ >> 16]), a.thr, lane, cl, sl, nullptr);
-            ++n_relit;
-            if (lane == src) { cm[fq * T + tt] = kWsExact | (uint32_t)cl; ssf[fq * T + tt] = sl; }
+            const double2 pi_ = FP[pw_ & 0xffffu], pj_ = FP[pw_ >> 16];
+            bool lit = (fdeg >> kf) & 1u;
+            if (!lit) warp_fast64_score_strided(FP, fg->n, fast_pair_model(pi_, pj_), a.thr, fband, lane, cl, lit, nullptr, 0);
+            if (lit) {
+                warp_literal_score(FP, fg->n, lit_pair_model(pi_, pj_), a.thr, lane, cl, sl, nullptr);
+                ++n_relit;
+            }
+            if (lane == src) {
+                if (lit) { cm[fq * T + tt] = kWsExact | (uint32_t)cl; ssf[fq * T + tt] = sl; }
+                else cm[fq * T + tt] = ws_pack(cl, __int_as_float(0x7f800000));
+            }
         }
     }
     if (lane == 0 && n_relit) atomicAdd(a.counters + 0, (unsigned long long)n_relit);
