@@ -43,6 +43,18 @@ def test_philox_batches(gpu_engine, N, window, B):
     assert want["ninl"][7, 0] == -3 and (want["ninl"][5] == 0).all()
 
 
+@pytest.mark.parametrize("trials", [1, 5, 31, 32, 33, 64, 100, 257])
+def test_trial_budgets_and_stop_probabilities(gpu_engine, trials):
+    """As tests/test_oracle_ols.py: budgets around the kernel's groups of 32 speculative trials, clean / noisy / mixed windows,
+    three stop probabilities."""
+    xy = np.concatenate([wall_windows(64, 100, seed=trials, noise=0.0, outliers=0.0),
+                         wall_windows(64, 100, seed=trials + 1, noise=40.0, outliers=0.5), wall_windows(64, 100, seed=trials + 2)])
+    for prob in (0.99, 0.5, 1.0):
+        want = cport.ransac_ols(xy, trials=trials, probability=prob, seed=11)
+        got = gpu_ols(gpu_engine, xy, trials=trials, stop_probability=prob, seed=11)
+        assert_ols_equal(want, got, "trials %d p %.2f" % (trials, prob))
+
+
 def test_bad_arguments(gpu_engine):
     import torch
     from lidar_slam_b200._lib import LslamError

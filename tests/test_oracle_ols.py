@@ -57,6 +57,23 @@ def test_philox_sampler_batches(N, window):
     assert r["n_trials"] == want["n_trials"][0, 0] and r["coef"] == want["fit"][0, 0, 0]
 
 
+@pytest.mark.parametrize("trials", [1, 5, 31, 32, 33, 64, 100, 257])
+def test_trial_budgets_and_stop_probabilities(trials):
+    """The kernel evaluates 32 trials at a time, one per lane, and replays upstream's accept rule over them: budgets that end
+    inside, at and just past a group of 32, clean walls (every trial ties on the count: the bound drops to one trial), noisy
+    windows (the bound stays at the budget), and other stop probabilities (incl. 1.0: max_trials = inf -> the budget)."""
+    clean = wall_windows(4, 100, seed=trials, noise=0.0, outliers=0.0)
+    noisy = wall_windows(4, 100, seed=trials + 1, noise=40.0, outliers=0.5)
+    mixed = wall_windows(4, 100, seed=trials + 2)
+    xy = np.concatenate([clean, noisy, mixed])
+    for prob in (0.99, 0.5, 1.0):
+        want = cport.ransac_ols(xy, trials=trials, probability=prob, seed=11)
+        got = emu_ransac_ols(xy, trials=trials, probability=prob, seed=11)
+        assert_ols_equal(want, got, "trials %d p %.2f" % (trials, prob))
+        assert (want["n_trials"] <= trials).all() and (want["n_trials"][:4] >= 1).all()
+    assert (cport.ransac_ols(xy, trials=trials, probability=0.99, seed=11)["n_trials"][:4] == 1).all()   # clean walls: one trial
+
+
 def test_no_consensus_and_nonfinite():
     xy = wall_windows(3, 50, seed=1)
     xy[1, :, 1] = np.nan                                    # every residual NaN -> every trial skipped
