@@ -11,6 +11,7 @@
 // masks with a handful of integer ops per event, so the walk costs O(events), not O(M).
 #pragma once
 #include "lslam_core.cuh"
+#include <cmath>
 
 namespace lslam {
 
@@ -23,6 +24,7 @@ struct AssocArgs {
     int32_t *life, *ids;       // [T, M]
     int32_t *count, *next_id;  // [T]
     double tolA, tolB, tol;
+    double tol_sq;             // largest double s with sqrt_rn(s) <= tol (assoc_gate_sq), -1 if there is none: the gate on squares
     int life_init, mode, append;
     int32_t *match, *match_id; // [T, Q]
     double *proj_ab;           // [T, Q, 2] or null
@@ -39,17 +41,41 @@ __device__ __forceinline__ double norm2_pinned(double vx, double vy)
     return __dsqrt_rn(__fma_rn(vy, vy, __dmul_rn(vx, vx)));
 }
 
-// landmarking.py:66-77, self = stored entry e[6], other = query q[6]; also returns the smaller
-// of the two gate distances (used by the nearest mode)
+// The gate ||v|| <= tol without the square root: the correctly rounded sqrt is monotonic, so sqrt_rn(s) <= tol  <=>  s <= S*
+// with S* the largest double whose rounded root does not exceed tol - found on the host by stepping from tol * tol (the
+// host's sqrt is the same correctly rounded operation).  NaN sums fail both forms; tol < 0 or NaN: no s passes (S* = -1).
+inline double assoc_gate_sq(double tol)
+{
+    if (!(tol >= 0.0)) return -1.0;
+    if (tol > 1.3407807929942596e154) return HUGE_VAL;          // tol * tol overflows: every finite (and infinite) sum passes
+    double s = tol * tol;
+    while (std::sqrt(s) > tol) s = std::nextafter(s, 0.0);
+    for (;;) {
+        const double up = std::nextafter(s, HUGE_VAL);
+        if (!(std::sqrt(up) <= tol) || up == s) break;
+        s = up;
+    }
+    return s;
+}
+
+// landmarking.py:66-77, self = stored entry e[6], other = query q[6].  WANT_D: also return the smaller of the two gate
+// distances (the nearest mode ranks by it); without it the two square roots are not taken at all - the gates are
+// compared on the squared sums against tol_sq, the same decision bit for bit (assoc_gate_sq).
+template <bool WANT_D>
 __device__ __forceinline__ bool landmark_is_equal(const double *e, const double *q, double tolA, double tolB,
-                                                  double tol, double &dmin)
+                                                  double tol, double tol_sq, double &dmin)
 {
     const double distA = fabs(__dsub_rn(e[0], q[0]));
     const double distB = fabs(__dsub_rn(e[1], q[1]));
-    const double dEO = norm2_pinned(__dsub_rn(e[4], q[2]), __dsub_rn(e[5], q[3]));   // end_s - pos_q
-    const double dOE = norm2_pinned(__dsub_rn(e[2], q[4]), __dsub_rn(e[3], q[5]));   // pos_s - end_q
-    dmin = dEO < dOE ? dEO : dOE;
-    return distA <= tolA && distB <= tolB && (dEO <= tol || dOE <= tol);
+    const double ax = __dsub_rn(e[4], q[2]), ay = __dsub_rn(e[5], q[3]);             // end_s - pos_q
+    const double bx = __dsub_rn(e[2], q[4]), by = __dsub_rn(e[3], q[5]);             // pos_s - end_q
+    if (WANT_D) {
+        const double dEO = norm2_pinned(ax, ay), dOE = norm2_pinned(bx, by);
+        dmin = dEO < dOE ? dEO : dOE;
+        return distA <= tolA && distB <= tolB && (dEO <= tol || dOE <= tol);
+    }
+    const double sEO = __fma_rn(ay, ay, __dmul_rn(ax, ax)), sOE = __fma_rn(by, by, __dmul_rn(bx, bx));
+    return distA <= tolA && distB <= tolB && (sEO <= tol_sq || sOE <= tol_sq);
 }
 
 // GS lanes (8, 16 or 32) serve one table; a warp serves 32/GS tables.  GS < 32 requires M <= GS (one
@@ -111,7 +137,7 @@ __global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
                 const int m = tb + g;
                 const bool in = m < cnt;
                 double dmin;
-                const bool eq = in && landmark_is_equal(ent + (size_t)m * 6, q, a.tolA, a.tolB, a.tol, dmin);
+                const bool eq = in && landmark_is_equal<false>(ent + (size_t)m * 6, q, a.tolA, a.tolB, a.tol, a.tol_sq, dmin);
                 const int lf = in ? life[m] : 0;
                 const bool die = in && !eq && lf <= 1;           // decrease_life() would return True
                 const unsigned eqm = GBALLOT(eq);
@@ -139,7 +165,7 @@ __global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
             for (int tb = 0; tb < cnt; tb += GS) {
                 const int m = tb + g;
                 double dmin = best;
-                const bool eq = m < cnt && landmark_is_equal(ent + (size_t)m * 6, q, a.tolA, a.tolB, a.tol, dmin);
+                const bool eq = m < cnt && landmark_is_equal<true>(ent + (size_t)m * 6, q, a.tolA, a.tolB, a.tol, a.tol_sq, dmin);
                 double cand = eq ? dmin : __longlong_as_double(0x7ff0000000000000LL);
                 int ci = eq ? m : 0x7fffffff;
 #pragma unroll

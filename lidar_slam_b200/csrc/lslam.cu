@@ -388,7 +388,7 @@ extern "C" int lslam_associate(void *handle, const double *query, int32_t qstrid
     a.query = query; a.q_valid = q_valid; a.qstride = qstride; a.layout = layout;
     a.T = T; a.Q = Q; a.M = M;
     a.table = table; a.life = life; a.ids = ids; a.count = count; a.next_id = next_id;
-    a.tolA = tolA; a.tolB = tolB; a.tol = tol; a.life_init = life_init; a.mode = mode; a.append = append;
+    a.tolA = tolA; a.tolB = tolB; a.tol = tol; a.tol_sq = assoc_gate_sq(tol); a.life_init = life_init; a.mode = mode; a.append = append;
     a.match = match; a.match_id = match_id; a.proj_ab = proj_ab; a.hit_pos = hit_pos;
     const size_t smem = per_table * NG * nwarps;
     const long long per_cta = (long long)nwarps * NG;

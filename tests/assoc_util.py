@@ -36,6 +36,35 @@ def random_streams(T, Q, M, seed=0, prefill=0, short_lives=True):
     return queries, valid, tables
 
 
+def gate_boundary_streams(T=512, seed=0, tol=100.0):
+    """T one-entry tables and one query each whose only open gate, ||end_s - pos_q||, sits within a few ulps of the
+    tolerance on either side (the other gate is far away): the decision hangs on the last bit of the rounded norm."""
+    rng = np.random.default_rng(seed)
+    tables = {"rows": np.zeros((T, 1, 6)), "life": np.full((T, 1), 9, np.int32), "ids": np.zeros((T, 1), np.int32),
+              "count": np.ones(T, np.int32), "next_id": np.ones(T, np.int32)}
+    queries = np.zeros((T, 1, 6))
+    th = rng.uniform(0, 2 * np.pi, T)
+    v = tol * np.stack([np.cos(th), np.sin(th)], -1)
+    for k in range(T):                                      # nudge the vector by a few ulps in or out
+        for _ in range(int(rng.integers(0, 4))):
+            v[k] = np.nextafter(v[k], v[k] * (2.0 if rng.random() < 0.5 else 0.5))
+    pos_q = rng.uniform(-2000, 2000, (T, 2))
+    tables["rows"][:, 0, 0] = 0.5
+    tables["rows"][:, 0, 1] = 10.0
+    tables["rows"][:, 0, 2:4] = pos_q + 5000.0              # pos_s: far from the query's end
+    tables["rows"][:, 0, 4:6] = pos_q + v                   # end_s
+    queries[:, 0, 0] = 0.5
+    queries[:, 0, 1] = 10.0
+    queries[:, 0, 2:4] = pos_q
+    queries[:, 0, 4:6] = pos_q - 5000.0
+    v[::7] = [60.0, 80.0]                                   # exactly on the gate (3-4-5): || . || == tol, a hit
+    tables["rows"][::7, 0, 4:6] = 0.0 + v[::7]
+    queries[::7, 0, 2:4] = 0.0
+    tables["rows"][::7, 0, 2:4] = 5000.0
+    queries[::7, 0, 4:6] = -5000.0
+    return queries, None, tables
+
+
 def oracle_associate(queries, valid, tables, mode=0, append=True):
     """oracle/assoc.py over every stream; returns outputs and the updated tables (copies)."""
     T, Q, _ = queries.shape

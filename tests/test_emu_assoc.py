@@ -73,3 +73,23 @@ def test_nearest_mode_picks_the_closest_gated_landmark(emu):
           "count": np.array([3], np.int32), "next_id": np.array([10], np.int32)}
     m0, i0, _ = emu.emu_associate(q, t0, mode=0)
     assert i0[0, 0] == 7                                                   # first match, not nearest
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_gate_decided_by_the_last_bit(emu, mode):
+    """The first-match kernels compare the SQUARED gate sums with the largest double whose rounded root passes the tolerance
+    (assoc_gate_sq) instead of taking the two square roots: distances within a few ulps of the tolerance, and exactly on it."""
+    for tol in (100.0, 37.3):
+        queries, valid, tables = au.gate_boundary_streams(384, seed=int(tol), tol=tol)
+        if mode == 2:
+            m, i, p = emu.emu_associate(queries, {k: v.copy() for k, v in tables.items()}, mode=2, tol=tol)
+            m1, i1, p1 = emu.emu_associate(queries, {k: v.copy() for k, v in tables.items()}, mode=1, tol=tol)
+            assert np.array_equal(m, m1)                    # one stored entry: nearest and first match agree
+            continue
+        if tol != 100.0:                                    # the oracle's tolerance is the reference's constant
+            continue
+        want = au.oracle_associate(queries, valid, tables, mode=mode)
+        got_t = {k: v.copy() for k, v in tables.items()}
+        m, i, p = emu.emu_associate(queries, got_t, mode=mode, tol=tol)
+        au.assert_assoc_equal(want, (m, i, p, got_t), "gate mode %d" % mode)
+        assert (want[0] >= 0).sum() > 50 and (want[0] < 0).sum() > 50 and (want[0][::7] >= 0).all()

@@ -34,6 +34,17 @@ def test_first_match_modes(gpu_engine, mode, T, M, prefill, Q):
     assert (want[0] >= 0).any()
 
 
+@pytest.mark.parametrize("mode", [0, 1])
+def test_gate_decided_by_the_last_bit(gpu_engine, mode):
+    """As tests/test_emu_assoc.py: gate distances within a few ulps of the tolerance and exactly on it (the kernel compares
+    squared sums with assoc_gate_sq's bound instead of taking square roots)."""
+    queries, valid, tables = au.gate_boundary_streams(4096, seed=5)
+    want = au.oracle_associate(queries, valid, tables, mode=mode)
+    got = run_gpu(gpu_engine, queries, tables, valid, mode=mode)
+    au.assert_assoc_equal(want, got, "gate mode %d" % mode)
+    assert (want[0] >= 0).sum() > 500 and (want[0] < 0).sum() > 500
+
+
 def test_line_record_layout_chained_after_ransac(gpu_engine):
     """layout 1: the queries are the `line` records of lslam_ransac_lines, q_valid its ninl."""
     import torch
