@@ -83,7 +83,7 @@ __device__ __forceinline__ bool landmark_is_equal(const double *e, const double 
 // quarters of every warp idle.  Collectives are restricted to the group's lanes: groups of one warp
 // run different tables and diverge freely.
 template <int GS>
-__global__ void __launch_bounds__(256) associate_kernel(const AssocArgs a)
+__global__ void __launch_bounds__(256, 4) associate_kernel(const AssocArgs a)
 {
     LSLAM_SMEM_DECL;
     constexpr int NG = 32 / GS;
