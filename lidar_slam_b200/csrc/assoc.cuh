@@ -11,6 +11,7 @@
 // masks with a handful of integer ops per event, so the walk costs O(events), not O(M).
 #pragma once
 #include "lslam_core.cuh"
+#include "async_copy.cuh"
 #include <cmath>
 
 namespace lslam {
@@ -29,11 +30,19 @@ struct AssocArgs {
     int32_t *match, *match_id; // [T, Q]
     double *proj_ab;           // [T, Q, 2] or null
     double *hit_pos;           // [T, Q, 2] or null
+    int stage_q;               // the table's Q queries (+ q_valid) are staged in shared memory with the table (they fit)
+    int async16;               // table, life, ids and queries are copied by 16-byte cp.async (alignment / sizes checked on the host)
 };
 
 constexpr int kLifeRemoved = -1;
 
-__host__ __device__ inline size_t assoc_smem_per_warp(int M) { return (size_t)M * (6 * 8 + 2 * 4); }
+// shared memory of one table: entries [M][6], life [M], ids [M]; with stage_q also the queries [Q][qstride] and q_valid [Q]
+__host__ __device__ inline size_t assoc_smem_per_table(int M, int Q, int qstride, int stage_q)
+{
+    size_t b = (((size_t)M * (6 * 8 + 2 * 4)) + 15) & ~(size_t)15;
+    if (stage_q) b += (((size_t)Q * qstride * 8 + (size_t)Q * 4) + 15) & ~(size_t)15;
+    return b;
+}
 
 // ||(vx, vy)|| with the rounding pinned in oracle/assoc.py: sqrt(fma(vy, vy, vx*vx))
 __device__ __forceinline__ double norm2_pinned(double vx, double vy)
@@ -95,25 +104,47 @@ __global__ void __launch_bounds__(256, 4) associate_kernel(const AssocArgs a)
     if (tl >= a.T) return;                      // the whole group leaves together
     const int t = (int)tl;
     const int M = a.M;
-    unsigned char *base = smem_raw + (size_t)(warp * NG + grp) * ((assoc_smem_per_warp(M) + 15) & ~(size_t)15);
+    unsigned char *base = smem_raw + (size_t)(warp * NG + grp) * assoc_smem_per_table(M, a.Q, a.qstride, a.stage_q);
     double *ent = reinterpret_cast<double *>(base);                 // [M][6]
     int *life = reinterpret_cast<int *>(ent + (size_t)M * 6);       // [M]
     int *ids = life + M;                                            // [M]
+    double *qbuf = reinterpret_cast<double *>(base + ((((size_t)M * (6 * 8 + 2 * 4)) + 15) & ~(size_t)15));   // [Q][qstride] (stage_q)
+    int *qv = reinterpret_cast<int *>(qbuf + (size_t)a.Q * a.qstride);                                       // [Q]
 #define GBALLOT(pred) ((__ballot_sync(gmask, (pred)) >> (grp * GS)) & gfull)
 
-    int cnt = a.count[t];
-    cnt = cnt < 0 ? 0 : (cnt > M ? M : cnt);
-    int next_id = a.next_id[t];
+    // Everything the walk reads comes in ONE global round trip: the copies below do not depend on the live count (all M slots
+    // are copied; slots past the count are never looked at), and the queries of the table come with it instead of one
+    // dependent load per query inside the loop.  With async16 the copies are cp.async (no register staging: all in flight).
+    int cnt, next_id;
     {
         const double *src = a.table + (size_t)t * M * 6;
-        for (int k = g; k < cnt * 6; k += GS) ent[k] = src[k];
-        for (int k = g; k < cnt; k += GS) { life[k] = a.life[(size_t)t * M + k]; ids[k] = a.ids[(size_t)t * M + k]; }
+        const int32_t *lsrc = a.life + (size_t)t * M, *isrc = a.ids + (size_t)t * M;
+        const double *qsrc = a.query + (size_t)t * a.Q * a.qstride;
+        if (a.async16) {
+            for (int k = g; k < M * 3; k += GS) cp_async16(ent + 2 * k, src + 2 * k);
+            for (int k = g; k < (M >> 2); k += GS) { cp_async16(life + 4 * k, lsrc + 4 * k); cp_async16(ids + 4 * k, isrc + 4 * k); }
+            if (a.stage_q)
+                for (int k = g; k < ((a.Q * a.qstride) >> 1); k += GS) cp_async16(qbuf + 2 * k, qsrc + 2 * k);
+        }
+        cnt = a.count[t];
+        next_id = a.next_id[t];
+        if (a.stage_q && a.q_valid != nullptr)
+            for (int k = g; k < a.Q; k += GS) qv[k] = a.q_valid[(size_t)t * a.Q + k];
+        cnt = cnt < 0 ? 0 : (cnt > M ? M : cnt);
+        if (a.async16) {
+            cp_async_wait_all();
+        } else {
+            for (int k = g; k < cnt * 6; k += GS) ent[k] = src[k];
+            for (int k = g; k < cnt; k += GS) { life[k] = lsrc[k]; ids[k] = isrc[k]; }
+            if (a.stage_q)
+                for (int k = g; k < a.Q * a.qstride; k += GS) qbuf[k] = qsrc[k];
+        }
     }
     __syncwarp(gmask);
 
     for (int qi = 0; qi < a.Q; ++qi) {
         const size_t qo = (size_t)t * a.Q + qi;
-        if (a.q_valid != nullptr && a.q_valid[qo] <= 0) {
+        if (a.q_valid != nullptr && (a.stage_q ? qv[qi] : a.q_valid[qo]) <= 0) {
             if (g == 0) {
                 a.match[qo] = -2; a.match_id[qo] = -1;
                 const double qn = __longlong_as_double(0x7ff8000000000000LL);
@@ -122,7 +153,7 @@ __global__ void __launch_bounds__(256, 4) associate_kernel(const AssocArgs a)
             }
             continue;
         }
-        const double *qs = a.query + qo * a.qstride;
+        const double *qs = a.stage_q ? qbuf + (size_t)qi * a.qstride : a.query + qo * a.qstride;
         double q[6];
         q[0] = qs[0]; q[1] = qs[1]; q[2] = qs[2]; q[3] = qs[3];
         q[4] = a.layout ? qs[6] : qs[4];

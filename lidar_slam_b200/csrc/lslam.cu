@@ -380,7 +380,10 @@ extern "C" int lslam_associate(void *handle, const double *query, int32_t qstrid
     // lane group per table: the smallest of 8 / 16 / 32 lanes that covers the table in one tile
     const int GS = M <= 8 ? 8 : (M <= 16 ? 16 : 32);
     const int NG = 32 / GS;
-    const size_t per_table = (assoc_smem_per_warp(M) + 15) & ~(size_t)15;
+    // the table's queries ride along with the table in shared memory while at least four warps still fit
+    int stage_q = 1;
+    size_t per_table = assoc_smem_per_table(M, Q, qstride, 1);
+    if ((size_t)h->smem_optin / (per_table * NG) < 4) { stage_q = 0; per_table = assoc_smem_per_table(M, Q, qstride, 0); }
     int nwarps = (int)((size_t)h->smem_optin / (per_table * NG));
     if (nwarps < 1) return fail(h, LSLAM_ERR_CAPACITY, "lslam_associate: table capacity M=%d does not fit shared memory", M);
     if (nwarps > 8) nwarps = 8;
@@ -390,6 +393,10 @@ extern "C" int lslam_associate(void *handle, const double *query, int32_t qstrid
     a.table = table; a.life = life; a.ids = ids; a.count = count; a.next_id = next_id;
     a.tolA = tolA; a.tolB = tolB; a.tol = tol; a.tol_sq = assoc_gate_sq(tol); a.life_init = life_init; a.mode = mode; a.append = append;
     a.match = match; a.match_id = match_id; a.proj_ab = proj_ab; a.hit_pos = hit_pos;
+    a.stage_q = stage_q;
+    // 16-byte asynchronous copies need every per-table block to start and end on 16 bytes
+    a.async16 = (M % 4 == 0) && (((size_t)Q * qstride) % 2 == 0 || !stage_q) &&
+                ((((uintptr_t)table | (uintptr_t)life | (uintptr_t)ids | (stage_q ? (uintptr_t)query : 0)) & 15) == 0);
     const size_t smem = per_table * NG * nwarps;
     const long long per_cta = (long long)nwarps * NG;
     const unsigned grid = (unsigned)((T + per_cta - 1) / per_cta);
