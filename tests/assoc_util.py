@@ -96,3 +96,15 @@ def assert_assoc_equal(want, got, what=""):
         "%s projection coefficients differ" % what
     for k in ("count", "next_id", "life", "ids", "rows"):
         assert np.array_equal(wt[k], gt[k]), "%s table field %s differs" % (what, k)
+
+
+def misaligned_copy(a):
+    """A C-contiguous copy of `a` whose first byte sits 8 (float64) or 4 (int32) bytes past a 16-byte boundary: what the
+    association kernel's 16-byte asynchronous copies cannot take (it must fall back to plain loads)."""
+    a = np.ascontiguousarray(a)
+    raw = np.zeros(a.nbytes + 64, np.uint8)
+    off = (-raw.ctypes.data) % 16 + a.itemsize
+    v = raw[off:off + a.nbytes].view(a.dtype).reshape(a.shape)
+    v[...] = a
+    assert v.ctypes.data % 16 == a.itemsize and v.flags.c_contiguous
+    return v

@@ -93,3 +93,21 @@ def test_gate_decided_by_the_last_bit(emu, mode):
         m, i, p = emu.emu_associate(queries, got_t, mode=mode, tol=tol)
         au.assert_assoc_equal(want, (m, i, p, got_t), "gate mode %d" % mode)
         assert (want[0] >= 0).sum() > 50 and (want[0] < 0).sum() > 50 and (want[0][::7] >= 0).all()
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("M,prefill,Q,what", [(8, 6, 7, "misaligned"), (12, 9, 5, "misaligned"), (8, 6, 400, "unstaged"),
+                                              (8, 6, 400, "unstaged-misaligned")])
+def test_load_paths(emu, mode, M, prefill, Q, what):
+    """The three ways the kernel brings a table and its queries in give the same answers: 16-byte asynchronous copies
+    (every other test), plain loads because a buffer is not 16-byte aligned, and queries too many to be staged in shared
+    memory with the table (read from global memory inside the walk)."""
+    queries, valid, tables = au.random_streams(5, Q, M, seed=3 * M + mode, prefill=prefill)
+    want = au.oracle_associate(queries, valid, tables, mode=mode)
+    got_t = {k: v.copy() for k, v in tables.items()}
+    if "misaligned" in what:
+        queries = au.misaligned_copy(queries)
+        for k in ("rows", "life", "ids"):
+            got_t[k] = au.misaligned_copy(got_t[k])
+    m, i, p = emu.emu_associate(queries, got_t, q_valid=valid, mode=mode)
+    au.assert_assoc_equal(want, (m, i, p, got_t), "%s mode %d" % (what, mode))

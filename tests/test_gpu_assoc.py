@@ -45,6 +45,41 @@ def test_gate_decided_by_the_last_bit(gpu_engine, mode):
     assert (want[0] >= 0).sum() > 500 and (want[0] < 0).sum() > 500
 
 
+def _misaligned_dev(a, dev):
+    """Device copy of `a` that starts one element past a 16-byte boundary."""
+    import torch
+    a = np.ascontiguousarray(a)
+    flat = torch.zeros(a.size + 4, dtype=torch.from_numpy(a).dtype, device=dev)
+    v = flat[1:1 + a.size].view(a.shape)
+    v.copy_(torch.from_numpy(a))
+    assert v.data_ptr() % 16 == a.itemsize
+    return v
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("T,M,prefill,Q,what", [(257, 8, 6, 7, "misaligned"), (130, 12, 9, 5, "misaligned"),
+                                                (33, 8, 6, 400, "unstaged"), (33, 8, 6, 400, "unstaged-misaligned")])
+def test_load_paths(gpu_engine, mode, T, M, prefill, Q, what):
+    """As tests/test_emu_assoc.py::test_load_paths: plain loads for buffers off the 16-byte grid, queries read from global
+    memory when they do not fit beside the table - same answers as the asynchronous, staged path."""
+    import torch
+    eng = gpu_engine
+    queries, valid, tables = au.random_streams(T, Q, M, seed=3 * M + mode, prefill=prefill)
+    want = au.oracle_associate(queries, valid, tables, mode=mode)
+    if "misaligned" in what:
+        tt = {k: (_misaligned_dev(v, eng.device) if k in ("rows", "life", "ids") else torch.from_numpy(v.copy()).to(eng.device))
+              for k, v in tables.items()}
+        q = _misaligned_dev(queries, eng.device)
+    else:
+        tt = {k: torch.from_numpy(v.copy()).to(eng.device) for k, v in tables.items()}
+        q = torch.from_numpy(queries).to(eng.device)
+    out = eng.associate(q, tt, q_valid=torch.from_numpy(valid).to(eng.device), mode=mode)
+    torch.cuda.synchronize()
+    got = (out["match"].cpu().numpy(), out["match_id"].cpu().numpy(), out["proj_ab"].cpu().numpy(),
+           {k: t.cpu().numpy() for k, t in tt.items()})
+    au.assert_assoc_equal(want, got, "%s mode %d" % (what, mode))
+
+
 def test_line_record_layout_chained_after_ransac(gpu_engine):
     """layout 1: the queries are the `line` records of lslam_ransac_lines, q_valid its ninl."""
     import torch
