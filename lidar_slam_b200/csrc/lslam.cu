@@ -421,7 +421,7 @@ static int launch_ukf(Handle *h, const UkfArgs &a, cudaStream_t st)
     const size_t smem = ukf_smem_doubles_per_warp(G) * sizeof(double) * nwarps;
     if (smem > (size_t)h->smem_optin) return fail(h, LSLAM_ERR_CAPACITY, "lslam_ukf: shared memory");
     LSLAM_CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const long long per_cta = (long long)nwarps * (32 / G);
+    const long long per_cta = (long long)nwarps * 32;        // a warp owns 32 consecutive filters (ukf_kernel: fb)
     const long long grid = (a.F + per_cta - 1) / per_cta;
     if (grid > 0x7fffffffLL) return fail(h, LSLAM_ERR_CAPACITY, "too many filters for one launch");
     LSLAM_LAUNCH(kern, (unsigned)grid, (unsigned)(nwarps * 32), smem, st, a);
