@@ -147,6 +147,9 @@ int lslam_ransac_counters(void *handle, int64_t counters_h[3], void *stream);
  *            (ransac_functions.py:46 on a hit: the STORED landmark's; :49,53 on a miss: the new)
  *   hit_pos  [T,Q,2] or NULL: get_pos() of the matched STORED landmark (what hx measures against,
  *            UKFMethods.py:30); NaN on a miss
+ * Any alignment and any M work.  The fast load path (16-byte asynchronous copies of the table and its queries in one
+ * round trip) needs `query`, `table`, `life` and `ids` 16-byte aligned and M a multiple of 4 (any cudaMalloc'ed,
+ * densely packed buffer with the reference's LANDMARK_NUMBER = 8 qualifies); results are identical either way.
  */
 int lslam_associate(void *handle, const double *query, int32_t qstride, int32_t layout,
                     const int32_t *q_valid, int32_t T, int32_t Q, int32_t M, double *table,
