@@ -18,13 +18,22 @@ CSRC = os.path.join(_ROOT, "lidar_slam_b200", "csrc")
 def build_emu(force=False):
     srcs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))]
     srcs += [os.path.join(_HERE, "emu", "cuda_emu.h"), os.path.join(_ROOT, "include", "lslam.h")]
-    if force or not os.path.exists(EMU_SO) or any(
-            os.path.getmtime(s) > os.path.getmtime(EMU_SO) for s in srcs):
-        gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
-        subprocess.check_call([
-            gxx, "-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared",
-            "-Wall", "-Wno-unknown-pragmas", "-include", os.path.join(_HERE, "emu", "cuda_emu.h"),
-            "-x", "c++", os.path.join(CSRC, "lslam.cu"), "-o", EMU_SO, "-lpthread"])
+    def stale():
+        return force or not os.path.exists(EMU_SO) or any(os.path.getmtime(s) > os.path.getmtime(EMU_SO) for s in srcs)
+    if stale():
+        # one builder at a time (pytest-xdist workers start together), and the library appears under its name only when
+        # it is complete: compile to a temporary name, then rename
+        import fcntl
+        with open(EMU_SO + ".lock", "w") as lock:
+            fcntl.flock(lock, fcntl.LOCK_EX)
+            if stale():
+                gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+                tmp = "%s.%d.tmp" % (EMU_SO, os.getpid())
+                subprocess.check_call([
+                    gxx, "-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared",
+                    "-Wall", "-Wno-unknown-pragmas", "-include", os.path.join(_HERE, "emu", "cuda_emu.h"),
+                    "-x", "c++", os.path.join(CSRC, "lslam.cu"), "-o", tmp, "-lpthread"])
+                os.replace(tmp, EMU_SO)
     return EMU_SO
 
 
