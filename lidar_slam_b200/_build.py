@@ -39,7 +39,8 @@ def build(force=False, verbose=False):
     if not force and os.path.exists(OUT) and all(
             os.path.getmtime(s) <= os.path.getmtime(OUT) for s in sources()):
         return OUT
-    cmd = [nvcc_path()] + NVCC_FLAGS + ["-o", OUT, os.path.join(CSRC, "lslam.cu")]
+    tmp = "%s.%d.tmp" % (OUT, os.getpid())       # the library appears under its name only when it is complete
+    cmd = [nvcc_path()] + NVCC_FLAGS + ["-o", tmp, os.path.join(CSRC, "lslam.cu")]
     # the distro g++ as host compiler (another g++ earlier on PATH lacks some spec files)
     if os.path.exists("/usr/bin/g++"):
         cmd[1:1] = ["-ccbin", "/usr/bin/g++"]
@@ -50,7 +51,10 @@ def build(force=False, verbose=False):
     if verbose or proc.returncode != 0:
         sys.stderr.write(proc.stdout)
     if proc.returncode != 0:
+        if os.path.exists(tmp):
+            os.remove(tmp)
         raise RuntimeError("nvcc failed (%d), see %s" % (proc.returncode, log))
+    os.replace(tmp, OUT)
     return OUT
 
 
